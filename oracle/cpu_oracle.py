@@ -1,0 +1,419 @@
+"""TEST INFRASTRUCTURE ONLY -- CPU restatement of the reference's algorithms for the
+RL post-processing hot path.  Nothing under `areal_b200/`
+imports this module; only `tests/`, `__graft_entry__.smoke()` and the
+`cpu_baseline` / `--impl reference` legs of `bench.py` do, and only as the checker
+or as the timed CPU baseline -- never as the product path.
+
+Parity status: PINNED.  Every function below is checked in
+`tests/test_oracle_golden.py` against golden vectors produced by executing the
+UNMODIFIED reference functions in the build container
+(`oracle/gen_golden.py` -> `tests/golden/*.npz`), and -- where the reference has its
+own known-answer test -- against that test's independent formula
+(`realhf/tests/data/test_dual_clip.py:8-50`).  Exceptions, stated where they occur:
+`gae_2d_olp` (no Python caller and no test in the reference; restated from
+`csrc/cugae/gae.cu:62-89`: parity unpinned) and `vocab_parallel_*` (third-party
+megatron-core 0.13.1 `vocab_parallel_cross_entropy`, absent from /root/reference;
+pinned against the unsharded oracle instead).
+
+All file:line citations are relative to the reference root.
+"""
+from __future__ import annotations
+
+import math
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+
+f32 = np.float32
+
+
+# --------------------------------------------------------------------------- #
+# P1  packed GAE
+# --------------------------------------------------------------------------- #
+def gae1d_nolp_misalign(rewards, values, cu_seqlens, bootstrap, gamma: float, lam: float):
+    """fp32, sequential, same operation order as `pygae1d_nolp_misalign`
+    (realhf/impl/model/utils/ppo_functional.py:292-323): per sequence i, t from last
+    to first, nv = values[cu[i]+i+t+1] (times bootstrap[i] at the last step, :313-315),
+    delta = r + gamma*nv - v (:316), A = delta + gamma*lam*A (:317), ret = A + v (:319).
+    torch multiplies a 0-dim fp32 tensor by a Python float in fp32 (the scalar is cast
+    to fp32), and `gamma * lam` is a Python double product (:317) -- both reproduced.
+    Unlike the reference this does NOT write through to `values`."""
+    r = np.asarray(rewards, dtype=f32)
+    v = np.asarray(values, dtype=f32)
+    cu = np.asarray(cu_seqlens, dtype=np.int64)
+    bs = cu.shape[0] - 1
+    boot = np.asarray(bootstrap).astype(f32)
+    assert v.shape[0] == r.shape[0] + bs
+    g = f32(gamma)
+    gl = f32(gamma * lam)
+    adv = np.zeros_like(r)
+    ret = np.zeros_like(r)
+    for i in range(bs):
+        rs, re = int(cu[i]), int(cu[i + 1])
+        vs = rs + i
+        last = f32(0.0)
+        n = re - rs
+        for t in range(n - 1, -1, -1):
+            nv = v[vs + t + 1]
+            if t == n - 1:
+                nv = f32(nv * boot[i])
+            delta = f32(f32(r[rs + t] + f32(g * nv)) - v[vs + t])
+            last = f32(delta + f32(gl * last))
+            adv[rs + t] = last
+            ret[rs + t] = f32(last + v[vs + t])
+    return adv, ret
+
+
+def gae1d_nolp_misalign_f64(rewards, values, cu_seqlens, bootstrap, gamma: float, lam: float):
+    """fp64 arbiter of the same recurrence: delta is formed exactly as the fp32
+    reference forms it, the recurrence itself is carried in fp64 with the fp32-rounded
+    coefficient.  Used to report both implementations' distance from the exact result
+    (SURVEY section 7 'fp32 reassociation in scans')."""
+    r = np.asarray(rewards, dtype=f32)
+    v = np.asarray(values, dtype=f32)
+    cu = np.asarray(cu_seqlens, dtype=np.int64)
+    bs = cu.shape[0] - 1
+    boot = np.asarray(bootstrap).astype(f32)
+    g = f32(gamma)
+    gl = float(f32(gamma * lam))
+    adv = np.zeros(r.shape[0], dtype=np.float64)
+    for i in range(bs):
+        rs, re = int(cu[i]), int(cu[i + 1])
+        vs = rs + i
+        n = re - rs
+        if n == 0:
+            continue
+        nv = v[vs + 1: vs + n + 1].copy()
+        nv[-1] = f32(nv[-1] * boot[i])
+        delta = ((r[rs:re] + g * nv).astype(f32) - v[vs: vs + n]).astype(f32).astype(np.float64)
+        last = 0.0
+        for t in range(n - 1, -1, -1):
+            last = delta[t] + gl * last
+            adv[rs + t] = last
+    ret = (adv.astype(f32) + v_at_rewards(v, cu)).astype(f32)
+    return adv, ret
+
+
+def v_at_rewards(values, cu_seqlens):
+    """values[cu[i]+i+t] laid out like rewards (the 'misalign' indexing, ppo_functional.py:301-311)."""
+    cu = np.asarray(cu_seqlens, dtype=np.int64)
+    out = np.empty(int(cu[-1]), dtype=np.asarray(values).dtype)
+    for i in range(cu.shape[0] - 1):
+        rs, re = int(cu[i]), int(cu[i + 1])
+        out[rs:re] = values[rs + i: re + i]
+    return out
+
+
+def gae_padded_masked(rewards, values, loss_mask, seq_no_eos_mask, gamma: float, lam: float):
+    """areal-lite's padded [B,S] masked GAE, `PPOActor.compute_advantages`
+    (areal/engine/ppo/actor.py:131-152): nv0 = values[:,S-1]*no_eos (:135); for t=S-2..0:
+    delta = r_t + gamma*nv - v_t (:137); new = delta + gamma*lam*last (:138); m = mask_t;
+    nv = nv*(1-m) + v_t*m (:142); last = last*(1-m) + new*m (:143); adv_t = last;
+    adv[:,S-1] = 0 (:131-133); returns = adv + values (:147).  fp32, same op order."""
+    r = np.asarray(rewards, dtype=f32)
+    v = np.asarray(values, dtype=f32)
+    m_all = np.asarray(loss_mask, dtype=f32)
+    B, S = r.shape
+    g = f32(gamma)
+    gl = f32(gamma * lam)
+    adv = np.zeros((B, S), dtype=f32)
+    last = np.zeros(B, dtype=f32)
+    nv = (v[:, S - 1] * np.asarray(seq_no_eos_mask).astype(f32)).astype(f32)
+    one = f32(1.0)
+    for t in range(S - 2, -1, -1):
+        delta = ((r[:, t] + g * nv).astype(f32) - v[:, t]).astype(f32)
+        new = (delta + (gl * last).astype(f32)).astype(f32)
+        m = m_all[:, t]
+        nv = ((nv * (one - m)).astype(f32) + (v[:, t] * m).astype(f32)).astype(f32)
+        last = ((last * (one - m)).astype(f32) + (new * m).astype(f32)).astype(f32)
+        adv[:, t] = last
+    ret = (adv + v).astype(f32)
+    return adv, ret
+
+
+def gae_2d_olp(rewards, values, done, done_y_indices, cu_num_dones, is_truncate,
+               gamma: float, lam: float):
+    """Segment-table 2D GAE as it EXECUTES in the reference (`gae_kernel_2d_olp`,
+    csrc/cugae/gae.cu:62-89; the `_nolp` host wrapper launches this same kernel,
+    gae.cu:199).  Thread (b, seg) walks [t_start, t_end) backwards; nex_v = 0 when
+    t is the segment tail and done[b,t+1]; a truncated non-final segment zeroes its
+    tail GAE (:85).  No Python caller / test upstream -> parity unpinned."""
+    r = np.asarray(rewards, dtype=f32)
+    v = np.asarray(values, dtype=f32)
+    d = np.asarray(done).astype(bool)
+    idx = np.asarray(done_y_indices, dtype=np.int64)
+    cu = np.asarray(cu_num_dones, dtype=np.int64)
+    trunc = np.asarray(is_truncate).astype(bool)
+    B, H = r.shape
+    g = f32(gamma)
+    gl = f32(f32(gamma) * f32(lam))  # device code multiplies two floats (gae.cu:84)
+    adv = np.zeros((B, H), dtype=f32)
+    ret = np.zeros((B, H), dtype=f32)
+    for b in range(B):
+        breadth = int(cu[b + 1] - cu[b]) + 1
+        for s in range(breadth):
+            t_start = 0 if s == 0 else int(idx[cu[b] + s - 1])
+            t_end = H if s == breadth - 1 else int(idx[cu[b] + s])
+            abandon = (s != breadth - 1) and bool(trunc[cu[b] + s])
+            last = f32(0.0)
+            for t in range(t_end - 1, t_start - 1, -1):
+                nex_v = f32(0.0) if (t == t_end - 1 and d[b, t + 1]) else v[b, t + 1]
+                cur_v = v[b, t]
+                delta = f32(f32(r[b, t] + f32(g * nex_v)) - cur_v)
+                last = f32(delta + f32(gl * last))
+                if t == t_end - 1 and abandon:
+                    last = f32(0.0)
+                adv[b, t] = last
+                ret[b, t] = f32(last + cur_v)
+    return adv, ret
+
+
+# --------------------------------------------------------------------------- #
+# P2  log-prob / entropy from [T,V] logits
+# --------------------------------------------------------------------------- #
+def gather_logprobs_entropy(logits, labels, temperature: float = 1.0, dtype=np.float64):
+    """`_gather_logprobs_entropy` (areal/utils/functional.py:28-34): z = logits.float()/temp;
+    lp = log_softmax(z); entropy = -sum(exp(lp)*lp); logp = lp[label].  `dtype=np.float32`
+    restates the reference's fp32 arithmetic; float64 (default) is the arbiter.  Also
+    returns lse (natural log, of z) and raw row min / max (areal/engine/ppo/actor.py:375-376)."""
+    x = np.asarray(logits)
+    raw = x.astype(np.float32)
+    z = raw.astype(dtype) / dtype(temperature)
+    m = z.max(axis=-1, keepdims=True)
+    e = np.exp(z - m)
+    s = e.sum(axis=-1, keepdims=True)
+    lse = (m + np.log(s))
+    lp = z - lse
+    ent = -(np.exp(lp) * lp).sum(axis=-1)
+    lab = np.asarray(labels, dtype=np.int64)
+    logp = np.take_along_axis(lp, lab[:, None], axis=-1)[:, 0]
+    return logp, ent, lse[:, 0], raw.min(axis=-1), raw.max(axis=-1)
+
+
+def dlogits(logits, labels, temperature, g_logp, g_entropy=None, dtype=np.float64):
+    """Gradient of sum_t g_logp[t]*logp[t] + g_entropy[t]*H[t] w.r.t. the raw logits:
+    d logp_y / d z_v = 1[v=y] - p_v ;  d H / d z_v = -p_v (lp_v + H)
+    (same as `_VocabParallelEntropy.backward`, areal/utils/mcore/functional.py:41-52:
+    -p*(z - sum p z)); times 1/temperature.  Autograd of functional.py:20-34 yields this."""
+    x = np.asarray(logits).astype(np.float32).astype(dtype)
+    z = x / dtype(temperature)
+    m = z.max(axis=-1, keepdims=True)
+    e = np.exp(z - m)
+    s = e.sum(axis=-1, keepdims=True)
+    lp = z - (m + np.log(s))
+    p = np.exp(lp)
+    g = -p * np.asarray(g_logp, dtype=dtype)[:, None]
+    lab = np.asarray(labels, dtype=np.int64)
+    g[np.arange(x.shape[0]), lab] += np.asarray(g_logp, dtype=dtype)
+    if g_entropy is not None:
+        H = -(p * lp).sum(axis=-1, keepdims=True)
+        g += np.asarray(g_entropy, dtype=dtype)[:, None] * (-p * (lp + H))
+    return g / dtype(temperature)
+
+
+def calc_entropy_legacy(logits, dtype=np.float64):
+    """Legacy `calc_entropy` (realhf/impl/model/interface/ppo_interface.py:52-58):
+    p = softmax(logits); -sum p*log(p + 1e-7)."""
+    z = np.asarray(logits).astype(np.float32).astype(dtype)
+    m = z.max(axis=-1, keepdims=True)
+    e = np.exp(z - m)
+    p = e / e.sum(axis=-1, keepdims=True)
+    return -(p * np.log(p + dtype(1e-7))).sum(axis=-1)
+
+
+def vocab_parallel_partials(logits_shard, labels, vocab_start: int, temperature: float):
+    """Per-shard partials of the vocab-sharded log-softmax: row max m (of z),
+    s = sum exp(z-m), u = sum exp(z-m)*z, z_label if the label is local else 0.
+    Follows `_VocabParallelEntropy.forward` (areal/utils/mcore/functional.py:15-34) and
+    `_VocabParallelCrossEntropy` (realhf/impl/model/parallelism/tensor_parallel/modules.py:1063-1118)."""
+    z = np.asarray(logits_shard).astype(np.float32).astype(np.float64) / temperature
+    m = z.max(axis=-1)
+    e = np.exp(z - m[:, None])
+    s = e.sum(axis=-1)
+    u = (e * z).sum(axis=-1)
+    lab = np.asarray(labels, dtype=np.int64) - vocab_start
+    local = (lab >= 0) & (lab < z.shape[1])
+    zl = np.where(local, z[np.arange(z.shape[0]), np.clip(lab, 0, z.shape[1] - 1)], 0.0)
+    return m, s, u, zl
+
+
+def vocab_parallel_combine(parts: Sequence[Tuple[np.ndarray, np.ndarray, np.ndarray, np.ndarray]]):
+    """all_reduce(MAX) of m, rescale, all_reduce(SUM) of (s,u,z_label) -> logp, entropy, lse
+    (mcore/functional.py:16-31: entropy = max + log(sum_exp) - sum softmax*logits)."""
+    M = np.max(np.stack([p[0] for p in parts]), axis=0)
+    S = sum(p[1] * np.exp(p[0] - M) for p in parts)
+    U = sum(p[2] * np.exp(p[0] - M) for p in parts)
+    ZL = sum(p[3] for p in parts)
+    lse = M + np.log(S)
+    return ZL - lse, lse - U / S, lse
+
+
+# --------------------------------------------------------------------------- #
+# P3  PPO losses
+# --------------------------------------------------------------------------- #
+def ppo_actor_loss(logprobs, proximal_logprobs, old_logprobs, advantages, eps_clip: float,
+                   loss_mask, eps_clip_higher: Optional[float] = None,
+                   c_clip: Optional[float] = None, behav_imp_weight_cap: Optional[float] = None,
+                   dtype=np.float32) -> Tuple[float, Dict[str, np.ndarray], np.ndarray]:
+    """`ppo_actor_loss_fn` (areal/utils/functional.py:171-235); the legacy `actor_loss_fn`
+    (realhf/impl/model/utils/ppo_functional.py:51-149) is the same math with
+    eps_clip_higher=None and, when proximal_logprobs is None, denorm=old and no behaviour
+    weight (pass `proximal_logprobs=None`).  Returns (loss, stats, dloss/dlogprobs).
+
+    Gradient (closed form): mask * w * sel * (-A * r) / count, sel = 1 iff the
+    unclipped branch of torch.max is active (L1 > L2, or L1 == L2 with the clamp passing the
+    gradient: for an exact tie torch.max splits 1/2-1/2 and the clamp branch contributes its
+    own 1/2 only when r is inside [lo, hi]) and the dual clip is not active (torch.min:
+    L < L3 -> 1, L == L3 -> 1/2)."""
+    lp = np.asarray(logprobs, dtype=dtype)
+    old = np.asarray(old_logprobs, dtype=dtype)
+    A = np.asarray(advantages, dtype=dtype)
+    mask = np.asarray(loss_mask).astype(bool)
+    decoupled = proximal_logprobs is not None
+    prox = np.asarray(proximal_logprobs, dtype=dtype) if decoupled else old
+    count = int(mask.sum()) or 1                                    # :190
+    with np.errstate(over="ignore", invalid="ignore"):
+        ratio = np.where(mask, np.exp(lp - prox), dtype(0))         # :191
+    lo = dtype(1.0 - eps_clip)
+    hi = dtype(1.0 + (eps_clip if eps_clip_higher is None else eps_clip_higher))
+    clipped = np.clip(ratio, lo, hi)                                # :193-197
+    l1 = -A * ratio
+    l2 = -A * clipped
+    clip_mask = l1 < l2                                             # :201
+    pg = np.maximum(l1, l2)                                         # :202
+    # d pg / d ratio (torch.max tie -> 1/2 each; clamp passes grad iff lo <= r <= hi)
+    inside = (ratio >= lo) & (ratio <= hi)
+    w1 = np.where(l1 > l2, 1.0, np.where(l1 == l2, 0.5, 0.0))
+    w2 = 1.0 - w1
+    dpg = -A * (w1 + w2 * inside)
+    if c_clip is not None:
+        assert c_clip > 1.0
+        l3 = np.sign(A) * dtype(c_clip) * A                         # :205
+        dual_mask = l3 < pg                                         # :206
+        wmin = np.where(pg < l3, 1.0, np.where(pg == l3, 0.5, 0.0))
+        pg = np.minimum(pg, l3)                                     # :207
+        dpg = dpg * wmin
+    else:
+        dual_mask = np.zeros_like(clip_mask)
+    stats: Dict[str, np.ndarray] = {}
+    if decoupled:
+        bk = prox - old                                             # :210
+        with np.errstate(over="ignore"):
+            w = np.exp(bk)
+        bmask = ((w <= dtype(behav_imp_weight_cap)) & mask) if behav_imp_weight_cap is not None else mask
+        bk = np.where(bmask, bk, dtype(0))
+        w = np.where(bmask, w, dtype(0))
+        pg = pg * w                                                 # :219
+        dpg = dpg * w
+        stats.update(behave_imp_weight=w.astype(dtype), behave_approx_kl=bk.astype(dtype),
+                     behave_mask=bmask)
+    logging_loss = pg.astype(dtype)
+    loss = np.where(mask, pg, dtype(0)).astype(np.float64).sum() / count   # :221
+    grad = np.where(mask, dpg * ratio, 0.0) / count                 # d ratio / d lp = ratio
+    stats.update(loss=logging_loss, importance_weight=ratio.astype(dtype),
+                 approx_kl=(lp - prox).astype(dtype), clip_mask=clip_mask & mask,
+                 dual_clip_mask=dual_mask & mask)
+    return float(loss), stats, grad.astype(dtype)
+
+
+def ppo_critic_loss(value, old_value, target_value, value_eps_clip: float, loss_mask=None,
+                    loss_fn_type: str = "mse", dtype=np.float32):
+    """`ppo_critic_loss_fn` (areal/utils/functional.py:247-311) == legacy `critic_loss_fn`
+    (realhf/impl/model/utils/ppo_functional.py:161-225).  Returns (loss, stats, dloss/dvalue).
+    Mean over mask.count_nonzero() with NO `or 1` (:306) -> nan/inf for an all-false mask."""
+    v = np.asarray(value, dtype=dtype)
+    old = np.asarray(old_value, dtype=dtype)
+    tgt = np.asarray(target_value, dtype=dtype)
+
+    def f(x, y):
+        d = x - y
+        if loss_fn_type == "mse":
+            return dtype(0.5) * d * d, d
+        if loss_fn_type == "huber":
+            delta = dtype(10.0)
+            ad = np.abs(d)
+            return (np.where(ad < delta, dtype(0.5) * ad * ad, delta * (ad - dtype(0.5) * delta)),
+                    np.where(ad < delta, d, delta * np.sign(d)))
+        raise NotImplementedError(loss_fn_type)
+
+    eps = dtype(value_eps_clip)
+    diff = v - old
+    vc = old + np.clip(diff, -eps, eps)
+    lo_, dlo = f(v, tgt)
+    lc_, dlc = f(vc, tgt)
+    inside = (diff >= -eps) & (diff <= eps)
+    loss_el = np.maximum(lo_, lc_)
+    w1 = np.where(lo_ > lc_, 1.0, np.where(lo_ == lc_, 0.5, 0.0))
+    g_el = w1 * dlo + (1.0 - w1) * dlc * inside
+    clip_mask = lc_ > lo_
+    if loss_mask is not None:
+        mask = np.asarray(loss_mask).astype(bool)
+        clip_mask = clip_mask & mask
+        cnt = int(mask.sum())
+        with np.errstate(divide="ignore", invalid="ignore"):
+            loss = np.float64(np.where(mask, loss_el, dtype(0)).astype(np.float64).sum()) / np.float64(cnt)
+            grad = np.where(mask, g_el, 0.0) / np.float64(cnt)
+    else:
+        loss = loss_el.astype(np.float64).mean()
+        grad = g_el / loss_el.size
+    return float(loss), dict(clip_mask=clip_mask, loss=loss_el.astype(dtype)), grad.astype(dtype)
+
+
+def ppo_dual_clip_known_answer(logp_new, logp_old, adv, clip_ratio, dual_clip):
+    """Independent dual-clip formula the reference tests `actor_loss_fn` against
+    (realhf/tests/data/test_dual_clip.py:8-50, PPOxFamily): used here the same way."""
+    ratio = np.exp(logp_new - logp_old)
+    surr1 = ratio * adv
+    surr2 = np.clip(ratio, 1 - clip_ratio, 1 + clip_ratio) * adv
+    clip1 = np.minimum(surr1, surr2)
+    if dual_clip is not None:
+        clip2 = np.maximum(clip1, dual_clip * adv)
+        return float(-(np.where(adv < 0, clip2, clip1)).mean())
+    return float(-clip1.mean())
+
+
+# --------------------------------------------------------------------------- #
+# P4  interval ops
+# --------------------------------------------------------------------------- #
+def slice_intervals(src: np.ndarray, intervals) -> np.ndarray:
+    """`_slice_intervals_py` (realhf/impl/model/nn/flatten_param.py:65-75): concatenation of
+    src[s:e] in the GIVEN order."""
+    iv = np.asarray(intervals, dtype=np.int64).reshape(-1, 2)
+    assert (iv[:, 0] >= 0).all() and (iv[:, 1] <= src.shape[0]).all()
+    if iv.shape[0] == 0:
+        return src[:0].copy()
+    return np.concatenate([src[s:e] for s, e in iv])
+
+
+def set_intervals(src: np.ndarray, dst: np.ndarray, intervals) -> None:
+    """`_set_intervals_py` (flatten_param.py:78-90): dst[s:e] = src[off:off+e-s], off running
+    in the given order; asserts the packed source is consumed exactly (:90)."""
+    off = 0
+    for s, e in np.asarray(intervals, dtype=np.int64).reshape(-1, 2):
+        assert s >= 0 and e <= dst.shape[0]
+        dst[s:e] = src[off: off + e - s]
+        off += e - s
+    assert off == src.shape[0]
+
+
+def merge_intervals(intervals: List[Tuple[int, int]]) -> List[Tuple[int, int]]:
+    """`merge_intervals` (csrc/interval_op/interval_op.cpp:4-25): merge (a,b),(b,c)->(a,c)
+    for NEIGHBOURS in input order only; no sorting, no overlap handling."""
+    out: List[Tuple[int, int]] = []
+    for a, b in intervals:
+        if out and out[-1][1] == a:
+            out[-1] = (out[-1][0], b)
+        else:
+            out.append((int(a), int(b)))
+    return out
+
+
+def make_intervals(maxsize: int, n_intervals: int, rng: np.random.RandomState):
+    """Workload generator of the reference test (realhf/tests/cpp_extensions/test_interval_ops.py:20-31):
+    interval i = (i*s, i*s + s//2), s = maxsize // n, then shuffled."""
+    assert maxsize // n_intervals > 1
+    s = maxsize // n_intervals
+    iv = np.stack([np.arange(n_intervals, dtype=np.int64) * s,
+                   np.arange(n_intervals, dtype=np.int64) * s + s // 2], axis=1)
+    rng.shuffle(iv)
+    return iv, n_intervals * (s // 2), s // 2

@@ -1,0 +1,282 @@
+"""TEST INFRASTRUCTURE ONLY -- generates the golden vectors under `tests/golden/` by
+executing the UNMODIFIED reference functions (via `oracle/ref_loader.py`) on seeded
+inputs.  Run in the build container (needs /root/reference):
+
+    python oracle/gen_golden.py
+
+Each .npz stores the inputs and the reference's outputs, so the GPU box (which has no
+/root/reference) can check both the oracle restatement and the CUDA path against them.
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from oracle import ref_loader as R  # noqa: E402
+
+OUT = os.path.join(ROOT, "tests", "golden")
+
+
+def bf16_bits(t: torch.Tensor) -> np.ndarray:
+    return t.detach().contiguous().view(torch.int16).numpy().view(np.uint16)
+
+
+def gen_gae1d(pf):
+    """Grid of realhf/tests/cpp_extensions/test_cugae.py:16-56 (+ mixed bootstrap, which the
+    reference test never exercises, + zero/one-length sequences)."""
+    out = {}
+    k = 0
+    g = torch.Generator().manual_seed(1234)
+    for max_seqlen in (32, 128, 512):
+        for bs in (2, 4):
+            for gamma in (0.9, 1.0):
+                for lam in (0.5, 1.0):
+                    for boot_mode in ("ones", "mixed"):
+                        seqlens = torch.randint(1, max_seqlen, (bs,), dtype=torch.int32, generator=g)
+                        T = int(seqlens.sum())
+                        rewards = torch.randn(T, generator=g)
+                        values = torch.randn(T + bs, generator=g)
+                        boot = (torch.ones(bs, dtype=torch.bool) if boot_mode == "ones"
+                                else torch.rand(bs, generator=g) > 0.5)
+                        cu = torch.nn.functional.pad(seqlens.cumsum(0), (1, 0)).int()
+                        adv, ret = pf.pygae1d_nolp_misalign(rewards, values.clone(), cu, boot, gamma, lam)
+                        p = f"c{k}_"
+                        out[p + "rewards"] = rewards.numpy()
+                        out[p + "values"] = values.numpy()
+                        out[p + "cu"] = cu.numpy()
+                        out[p + "boot"] = boot.numpy()
+                        out[p + "gl"] = np.array([gamma, lam])
+                        out[p + "adv"] = adv.numpy()
+                        out[p + "ret"] = ret.numpy()
+                        k += 1
+    # BASELINE.json configs[0] in miniature (gamma=1, lam=0.95, longer sequences)
+    seqlens = torch.randint(128, 1500, (6,), dtype=torch.int32, generator=g)
+    T = int(seqlens.sum())
+    rewards = torch.randn(T, generator=g)
+    values = torch.randn(T + 6, generator=g)
+    boot = torch.rand(6, generator=g) > 0.5
+    cu = torch.nn.functional.pad(seqlens.cumsum(0), (1, 0)).int()
+    adv, ret = pf.pygae1d_nolp_misalign(rewards, values.clone(), cu, boot, 1.0, 0.95)
+    p = f"c{k}_"
+    out.update({p + "rewards": rewards.numpy(), p + "values": values.numpy(), p + "cu": cu.numpy(),
+                p + "boot": boot.numpy(), p + "gl": np.array([1.0, 0.95]),
+                p + "adv": adv.numpy(), p + "ret": ret.numpy()})
+    k += 1
+    out["n_cases"] = np.array(k)
+    np.savez_compressed(os.path.join(OUT, "gae1d.npz"), **out)
+    print("gae1d cases:", k)
+
+
+def gen_gae_padded():
+    out = {}
+    g = torch.Generator().manual_seed(77)
+    k = 0
+    for (B, S) in ((3, 17), (5, 130), (8, 700)):
+        for (gamma, lam) in ((1.0, 1.0), (1.0, 0.95), (0.99, 0.95)):
+            rewards = torch.randn(B, S, generator=g)
+            values = torch.randn(B, S, generator=g)
+            lens = torch.randint(2, S + 1, (B,), generator=g)
+            prompt = (lens.float() * torch.rand(B, generator=g) * 0.6).long()
+            pos = torch.arange(S)[None, :]
+            lm = ((pos >= prompt[:, None]) & (pos < lens[:, None])).float()
+            lm = lm * (torch.rand(B, S, generator=g) > 0.1).float()   # holes inside the response
+            lm = torch.roll(lm, shifts=-1, dims=-1)                     # actor.py:110
+            no_eos = lens == S
+            adv, ret = R.run_areal_padded_gae(rewards, values, lm, no_eos, gamma, lam)
+            p = f"c{k}_"
+            out.update({p + "rewards": rewards.numpy(), p + "values": values.numpy(),
+                        p + "mask": lm.numpy(), p + "no_eos": no_eos.numpy(),
+                        p + "gl": np.array([gamma, lam]), p + "adv": adv.numpy(), p + "ret": ret.numpy()})
+            k += 1
+    out["n_cases"] = np.array(k)
+    np.savez_compressed(os.path.join(OUT, "gae_padded.npz"), **out)
+    print("gae_padded cases:", k)
+
+
+def gen_logprobs(af):
+    out = {}
+    g = torch.Generator().manual_seed(2024)
+    k = 0
+    for (T, V, scale, temp) in ((32, 4099, 2.0, 1.0), (16, 4099, 8.0, 0.7), (1, 151936, 2.0, 1.0),
+                                (7, 1000, 2.0, 0.7), (5, 8, 3.0, 1.0)):
+        logits = (torch.randn(T, V, generator=g) * scale).bfloat16()
+        labels = torch.randint(0, V, (T,), generator=g)
+        if T >= 16:
+            logits[0, labels[0]] += 30.0            # spike at the label
+            logits[1, (labels[1] + 1) % V] += 30.0  # spike elsewhere
+        lg = logits.clone().requires_grad_()
+        lp, H = af.gather_logprobs_entropy(lg, labels, temp)
+        lp_only = af.gather_logprobs(logits, labels, temp)
+        g_lp = torch.randn(T, generator=g)
+        g_H = torch.randn(T, generator=g) * 0.1
+        (grad_lp,) = torch.autograd.grad((lp * g_lp).sum(), lg, retain_graph=True)
+        (grad_both,) = torch.autograd.grad((lp * g_lp).sum() + (H * g_H).sum(), lg)
+        p = f"c{k}_"
+        out.update({p + "logits_bits": bf16_bits(logits), p + "labels": labels.numpy(),
+                    p + "temp": np.array(temp), p + "logp": lp.detach().numpy(),
+                    p + "logp_only": lp_only.numpy(), p + "entropy": H.detach().numpy(),
+                    p + "g_lp": g_lp.numpy(), p + "g_H": g_H.numpy(),
+                    p + "grad_lp_bits": bf16_bits(grad_lp), p + "grad_both_bits": bf16_bits(grad_both)})
+        k += 1
+    out["n_cases"] = np.array(k)
+    np.savez_compressed(os.path.join(OUT, "logprobs.npz"), **out)
+    print("logprobs cases:", k)
+
+
+def gen_actor_loss(af, pf):
+    out = {}
+    g = torch.Generator().manual_seed(99)
+    k = 0
+    T = 777
+    settings = [
+        dict(eps_clip=0.2, eps_clip_higher=None, c_clip=None, behav_imp_weight_cap=None),
+        dict(eps_clip=0.4, eps_clip_higher=None, c_clip=None, behav_imp_weight_cap=5.0),
+        dict(eps_clip=0.2, eps_clip_higher=0.28, c_clip=3.0, behav_imp_weight_cap=None),
+        dict(eps_clip=0.2, eps_clip_higher=0.28, c_clip=3.0, behav_imp_weight_cap=1.02),
+        dict(eps_clip=0.05, eps_clip_higher=None, c_clip=1.5, behav_imp_weight_cap=5.0),
+    ]
+    for s in settings:
+        for mask_mode in ("rand", "none_valid"):
+            lp0 = -torch.rand(T, generator=g) * 5
+            lp = (lp0 + 0.3 * torch.randn(T, generator=g)).requires_grad_()
+            prox = lp0 + 0.02 * torch.randn(T, generator=g)
+            old = lp0 + 0.05 * torch.randn(T, generator=g)
+            adv = torch.randn(T, generator=g)
+            adv[::50] = 0.0
+            mask = (torch.rand(T, generator=g) > 0.3) if mask_mode == "rand" else torch.zeros(T, dtype=torch.bool)
+            loss, st = af.ppo_actor_loss_fn(lp, prox, old, adv, loss_mask=mask, **s)
+            (grad,) = torch.autograd.grad(loss, lp, allow_unused=True)
+            if grad is None:
+                grad = torch.zeros(T)
+            p = f"c{k}_"
+            out.update({p + "lp": lp.detach().numpy(), p + "prox": prox.numpy(), p + "old": old.numpy(),
+                        p + "adv": adv.numpy(), p + "mask": mask.numpy(),
+                        p + "cfg": np.array([s["eps_clip"],
+                                             np.nan if s["eps_clip_higher"] is None else s["eps_clip_higher"],
+                                             np.nan if s["c_clip"] is None else s["c_clip"],
+                                             np.nan if s["behav_imp_weight_cap"] is None else s["behav_imp_weight_cap"]]),
+                        p + "loss": loss.detach().numpy(), p + "grad": grad.numpy()})
+            for name, val in st.items():
+                out[p + "stat_" + name] = val.detach().numpy()
+            k += 1
+    out["n_cases"] = np.array(k)
+    # legacy signature (realhf ppo_functional.actor_loss_fn), incl. proximal=None
+    j = 0
+    for (eps, c_clip, use_prox, cap) in ((0.2, None, False, None), (0.1, 2.0, False, None),
+                                         (0.2, 3.0, True, 5.0), (0.5, None, True, None)):
+        lp0 = -torch.rand(T, generator=g) * 5
+        lp = (lp0 + 0.3 * torch.randn(T, generator=g)).requires_grad_()
+        old = lp0 + 0.05 * torch.randn(T, generator=g)
+        prox = lp0 + 0.02 * torch.randn(T, generator=g) if use_prox else None
+        adv = torch.randn(T, generator=g)
+        mask = torch.rand(T, generator=g) > 0.3
+        loss, st = pf.actor_loss_fn(lp, old, adv, eps, loss_mask=mask, c_clip=c_clip,
+                                    proximal_logprobs=prox, behav_imp_weight_cap=cap)
+        (grad,) = torch.autograd.grad(loss, lp)
+        p = f"l{j}_"
+        out.update({p + "lp": lp.detach().numpy(), p + "old": old.numpy(), p + "adv": adv.numpy(),
+                    p + "mask": mask.numpy(), p + "has_prox": np.array(use_prox),
+                    p + "prox": (prox if use_prox else torch.zeros(T)).numpy(),
+                    p + "cfg": np.array([eps, np.nan if c_clip is None else c_clip,
+                                         np.nan if cap is None else cap]),
+                    p + "loss": loss.detach().numpy(), p + "grad": grad.numpy()})
+        for name, val in st.items():
+            out[p + "stat_" + name] = val.detach().numpy()
+        j += 1
+    out["n_legacy"] = np.array(j)
+    np.savez_compressed(os.path.join(OUT, "actor_loss.npz"), **out)
+    print("actor_loss cases:", k, "legacy:", j)
+
+
+def gen_critic_loss(af, pf):
+    out = {}
+    g = torch.Generator().manual_seed(5)
+    T = 513
+    k = 0
+    for fn_name, fn in (("areal", af.ppo_critic_loss_fn), ("legacy", pf.critic_loss_fn)):
+        for loss_type in ("mse", "huber"):
+            for use_mask in (True, False):
+                scale = 8.0 if loss_type == "huber" else 1.0
+                old = torch.randn(T, generator=g) * scale
+                val = (old + 0.4 * scale * torch.randn(T, generator=g)).requires_grad_()
+                tgt = old + scale * torch.randn(T, generator=g)
+                mask = (torch.rand(T, generator=g) > 0.3) if use_mask else None
+                loss, st = fn(val, old, tgt, 0.5, loss_mask=mask, loss_fn_type=loss_type)
+                (grad,) = torch.autograd.grad(loss, val)
+                p = f"c{k}_"
+                out.update({p + "value": val.detach().numpy(), p + "old": old.numpy(), p + "target": tgt.numpy(),
+                            p + "has_mask": np.array(use_mask),
+                            p + "mask": (mask if use_mask else torch.ones(T, dtype=torch.bool)).numpy(),
+                            p + "huber": np.array(loss_type == "huber"), p + "eps": np.array(0.5),
+                            p + "loss": loss.detach().numpy(), p + "grad": grad.numpy(),
+                            p + "stat_clip_mask": st["clip_mask"].numpy(), p + "stat_loss": st["loss"].numpy()})
+                k += 1
+    out["n_cases"] = np.array(k)
+    np.savez_compressed(os.path.join(OUT, "critic_loss.npz"), **out)
+    print("critic_loss cases:", k)
+
+
+def gen_intervals(fp):
+    """make_intervals pattern (test_interval_ops.py:20-31) at reduced buffer size + ragged sets."""
+    out = {}
+    rng = np.random.RandomState(0)
+    k = 0
+    cases = []
+    for (maxsize, n) in ((20000, 1), (20000, 100), (20000, 1000), (20003, 2001), (16384, 500)):
+        s = maxsize // n
+        iv = np.array([(i * s, i * s + s // 2) for i in range(n)], dtype=np.int64)
+        rng.shuffle(iv)
+        cases.append((maxsize, iv))
+    # ragged, odd-aligned, touching, and empty intervals
+    starts = np.sort(rng.choice(19000, 300, replace=False)).astype(np.int64)
+    sizes = rng.randint(0, 120, 300).astype(np.int64)
+    ends = np.minimum(starts + sizes, np.append(starts[1:], 20000))
+    iv = np.stack([starts, ends], 1)
+    rng.shuffle(iv)
+    cases.append((20000, iv))
+    for ci, (maxsize, iv) in enumerate(cases):
+        for dt_name, dt in (("bf16", torch.bfloat16), ("fp16", torch.float16), ("fp32", torch.float32)):
+            if dt_name != "bf16" and ci not in (3, 5):
+                continue
+            g = torch.Generator().manual_seed(k)
+            src = torch.randn(maxsize, generator=g).to(dt)
+            packed = fp._slice_intervals_py(src, [tuple(x) for x in iv.tolist()])
+            dst = torch.randn(maxsize, generator=g).to(dt)
+            newvals = torch.randn(packed.shape[0], generator=g).to(dt)
+            dst_after = dst.clone()
+            fp._set_intervals_py(newvals, dst_after, [tuple(x) for x in iv.tolist()])
+            p = f"c{k}_"
+
+            def bits(t):
+                if t.dtype == torch.float32:
+                    return t.numpy().view(np.uint32)
+                return t.contiguous().view(torch.int16).numpy().view(np.uint16)
+            out.update({p + "dtype": np.array(dt_name), p + "intervals": iv, p + "src": bits(src),
+                        p + "packed": bits(packed), p + "dst": bits(dst), p + "newvals": bits(newvals),
+                        p + "dst_after": bits(dst_after)})
+            k += 1
+    out["n_cases"] = np.array(k)
+    np.savez_compressed(os.path.join(OUT, "intervals.npz"), **out)
+    print("interval cases:", k)
+
+
+def main():
+    os.makedirs(OUT, exist_ok=True)
+    assert R.available(), "needs /root/reference"
+    torch.set_num_threads(8)
+    pf = R.load_realhf_ppo_functional()
+    af = R.load_areal_functional()
+    fp = R.load_realhf_flatten_param()
+    gen_gae1d(pf)
+    gen_gae_padded()
+    gen_logprobs(af)
+    gen_actor_loss(af, pf)
+    gen_critic_loss(af, pf)
+    gen_intervals(fp)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,139 @@
+"""TEST INFRASTRUCTURE ONLY -- loads single files of the UNMODIFIED reference
+(`/root/reference`) by file path, with `sys.modules` stubs for the imports this
+image lacks (megatron, omegaconf, realhf.base ...).
+
+Used only in the build container to (a) validate the restatement in
+`oracle/cpu_oracle.py` and (b) generate the committed golden vectors under
+`tests/golden/` (`oracle/gen_golden.py`).  `/root/reference` does not exist on
+the GPU box, so nothing in `-m gpu` tests, `smoke()` or `bench.py` imports this.
+No reference source is copied: the files are executed where they lie.
+"""
+import importlib.util
+import os
+import sys
+import types
+
+REF_ROOT = os.environ.get("AREAL_REFERENCE_ROOT", "/root/reference")
+
+
+def available() -> bool:
+    return os.path.isfile(os.path.join(REF_ROOT, "areal/utils/functional.py"))
+
+
+def _stub(name, **attrs):
+    m = types.ModuleType(name)
+    m.__dict__.update(attrs)
+    sys.modules[name] = m
+    return m
+
+
+def _load(path, modname):
+    spec = importlib.util.spec_from_file_location(modname, os.path.join(REF_ROOT, path))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def load_realhf_ppo_functional():
+    """realhf/impl/model/utils/ppo_functional.py (pygae1d_nolp_misalign :292-323,
+    actor_loss_fn :51-149, critic_loss_fn :161-225)."""
+    saved = {k: sys.modules.get(k) for k in ("realhf", "realhf.base", "realhf.base.pkg_version")}
+    try:
+        pv = _stub("realhf.base.pkg_version", is_available=lambda n: False)
+        base = _stub("realhf.base", pkg_version=pv)
+        _stub("realhf", base=base)
+        return _load("realhf/impl/model/utils/ppo_functional.py", "_ref_ppo_functional")
+    finally:
+        for k, v in saved.items():
+            if v is None:
+                sys.modules.pop(k, None)
+            else:
+                sys.modules[k] = v
+
+
+def load_areal_functional():
+    """areal/utils/functional.py, eager (is_npu_available=True skips torch.compile, :38-40)."""
+    names = ["megatron", "megatron.core", "megatron.core.parallel_state",
+             "megatron.core.tensor_parallel", "areal", "areal.platforms", "areal.utils",
+             "areal.utils.mcore", "areal.utils.mcore.functional", "areal.utils.ulysses"]
+    saved = {k: sys.modules.get(k) for k in names}
+    try:
+        mpu = _stub("megatron.core.parallel_state", is_initialized=lambda: False)
+        tp = _stub("megatron.core.tensor_parallel")
+        core = _stub("megatron.core", parallel_state=mpu, tensor_parallel=tp)
+        _stub("megatron", core=core)
+        _stub("areal")
+        _stub("areal.platforms", is_npu_available=True)
+        _stub("areal.utils")
+        _stub("areal.utils.mcore")
+        _stub("areal.utils.mcore.functional", _VocabParallelEntropy=object)
+        _stub("areal.utils.ulysses",
+              get_ulysses_sequence_parallel_group=lambda: None,
+              get_ulysses_sequence_parallel_world_size=lambda: 1)
+        return _load("areal/utils/functional.py", "_ref_areal_functional")
+    finally:
+        for k, v in saved.items():
+            if v is None:
+                sys.modules.pop(k, None)
+            else:
+                sys.modules[k] = v
+
+
+def load_realhf_flatten_param():
+    """realhf/impl/model/nn/flatten_param.py (`_slice_intervals_py` :65-75,
+    `_set_intervals_py` :78-90); its heavy package imports are stubbed."""
+    import logging as _logging
+    names = ["realhf", "realhf.api", "realhf.api.core", "realhf.api.core.model_api",
+             "realhf.api.core.config", "realhf.base", "realhf.base.constants",
+             "realhf.base.logging", "realhf.impl", "realhf.impl.model", "realhf.impl.model.nn",
+             "realhf.impl.model.nn.real_llm_base", "realhf.impl.model.nn.real_llm_parallel",
+             "realhf._C", "realhf._C.interval_op"]
+    saved = {k: sys.modules.get(k) for k in names}
+    try:
+        for n in ("realhf", "realhf.api", "realhf.api.core", "realhf.impl", "realhf.impl.model",
+                  "realhf.impl.model.nn", "realhf.base"):
+            m = _stub(n)
+            m.__path__ = []
+        _stub("realhf.api.core.model_api", ReaLModelConfig=object, ReaLModelParamKeys=object)
+        sys.modules["realhf.api.core"].model_api = sys.modules["realhf.api.core.model_api"]
+        _stub("realhf.api.core.config", ModelName=object)
+        _stub("realhf.base.constants", use_cuda=lambda: False)
+        _stub("realhf.base.logging", getLogger=_logging.getLogger)
+        sys.modules["realhf.base"].constants = sys.modules["realhf.base.constants"]
+        sys.modules["realhf.base"].logging = sys.modules["realhf.base.logging"]
+        _stub("realhf.impl.model.nn.real_llm_base", ReaLModelParamKeys=object)
+        _stub("realhf.impl.model.nn.real_llm_parallel", get_real_model_param_shape=None,
+              intervals_partition_fn=None, shape_partition_fn=None, tp_partition_key=None)
+        spec = importlib.util.spec_from_file_location(
+            "realhf.impl.model.nn.flatten_param",
+            os.path.join(REF_ROOT, "realhf/impl/model/nn/flatten_param.py"))
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+        return mod
+    finally:
+        for k, v in saved.items():
+            if v is None:
+                sys.modules.pop(k, None)
+            else:
+                sys.modules[k] = v
+
+
+def run_areal_padded_gae(rewards, values, loss_mask, seq_no_eos_mask, discount, gae_lambda):
+    """Executes the GAE loop of `PPOActor.compute_advantages` (areal/engine/ppo/actor.py,
+    from 'advantages_reversed = [' to 'data["returns"] = advantages + values', :136-152)
+    straight from the reference file -- the class itself cannot be imported here."""
+    import textwrap
+    import types as _t
+
+    import torch
+    with open(os.path.join(REF_ROOT, "areal/engine/ppo/actor.py")) as f:
+        lines = f.read().splitlines()
+    start = next(i for i, l in enumerate(lines) if "advantages_reversed = [" in l)
+    end = next(i for i, l in enumerate(lines) if 'data["returns"] = advantages + values' in l)
+    src = textwrap.dedent("\n".join(lines[start:end + 1]))
+    bs, max_seqlen = rewards.shape
+    ns = dict(torch=torch, rewards=rewards, values=values, loss_mask=loss_mask,
+              seq_no_eos_mask=seq_no_eos_mask, bs=bs, max_seqlen=max_seqlen, data={},
+              self=_t.SimpleNamespace(discount=discount, gae_lambda=gae_lambda))
+    exec(compile(src, "actor.py[gae]", "exec"), ns)
+    return ns["advantages"], ns["data"]["returns"]

@@ -1,0 +1,176 @@
+"""CPU: the oracle restatement (oracle/cpu_oracle.py, oracle/oracle.c) against the golden vectors
+produced by the unmodified reference (oracle/gen_golden.py), and against the reference's own
+known-answer test for the dual-clip loss (realhf/tests/data/test_dual_clip.py)."""
+import numpy as np
+import pytest
+
+from oracle import c_oracle as C
+from oracle import cpu_oracle as O
+from tests import helpers as H
+
+
+def test_gae1d_bit_exact_vs_reference():
+    z = H.load("gae1d.npz")
+    n = 0
+    for k, c in H.cases(z):
+        g, l = c["gl"]
+        a, r = O.gae1d_nolp_misalign(c["rewards"], c["values"], c["cu"], c["boot"], float(g), float(l))
+        assert np.array_equal(a, c["adv"]), k
+        assert np.array_equal(r, c["ret"]), k
+        a2, r2 = C.gae1d_nolp_misalign(c["rewards"], c["values"], c["cu"], c["boot"], float(g), float(l))
+        assert np.array_equal(a2, c["adv"]) and np.array_equal(r2, c["ret"]), k
+        a64, _ = O.gae1d_nolp_misalign_f64(c["rewards"], c["values"], c["cu"], c["boot"], float(g), float(l))
+        assert H.rel_err(a64, c["adv"], floor=max(1.0, np.abs(c["adv"]).max(initial=0))) < H.TOL_GAE
+        n += 1
+    assert n == 49
+
+
+def test_gae_padded_bit_exact_vs_reference():
+    z = H.load("gae_padded.npz")
+    for k, c in H.cases(z):
+        g, l = c["gl"]
+        a, r = O.gae_padded_masked(c["rewards"], c["values"], c["mask"], c["no_eos"], float(g), float(l))
+        assert np.array_equal(a, c["adv"]) and np.array_equal(r, c["ret"]), k
+        a2, r2 = C.gae_padded_masked(c["rewards"], c["values"], c["mask"], c["no_eos"], float(g), float(l))
+        assert np.array_equal(a2, c["adv"]) and np.array_equal(r2, c["ret"]), k
+
+
+def test_gae_2d_olp_consistent_with_1d():
+    """No reference test exists for the 2D kernels (parity unpinned); check the restatement
+    reduces to the pinned 1D recurrence when every row is one bootstrapped segment."""
+    rng = np.random.RandomState(3)
+    B, Hh = 4, 33
+    r = rng.randn(B, Hh).astype(np.float32)
+    v = rng.randn(B, Hh + 1).astype(np.float32)
+    done = np.zeros((B, Hh + 1), dtype=bool)
+    adv, ret = O.gae_2d_olp(r, v, done, np.zeros(0, np.int32), np.zeros(B + 1, np.int32),
+                            np.zeros(0, bool), 0.9, 0.5)
+    cu = (np.arange(B + 1) * Hh).astype(np.int32)
+    a1, r1 = O.gae1d_nolp_misalign(r.reshape(-1), v.reshape(-1), cu, np.ones(B, bool), 0.9, 0.5)
+    assert np.allclose(adv.reshape(-1), a1, atol=1e-6) and np.allclose(ret.reshape(-1), r1, atol=1e-6)
+
+
+def test_logprobs_entropy_and_grad_vs_reference():
+    import torch
+    z = H.load("logprobs.npz")
+    for k, c in H.cases(z):
+        logits = H.bf16_from_bits(c["logits_bits"]).float().numpy()
+        temp = float(c["temp"])
+        lp, ent, lse, mn, mx = O.gather_logprobs_entropy(logits, c["labels"], temp)
+        assert H.rel_err(lp, c["logp"]) < 1e-5, k
+        assert H.rel_err(lp, c["logp_only"]) < 1e-5, k
+        assert H.rel_err(ent, c["entropy"]) < 1e-5, k
+        lp32, ent32, *_ = O.gather_logprobs_entropy(logits, c["labels"], temp, dtype=np.float32)
+        assert H.rel_err(lp32, c["logp"]) < 1e-5 and H.rel_err(ent32, c["entropy"]) < 1e-4, k
+        g = O.dlogits(logits, c["labels"], temp, c["g_lp"])
+        ref = H.bf16_from_bits(c["grad_lp_bits"]).float().numpy()
+        # the reference grad is rounded to bf16 (2^-9 relative)
+        assert np.max(np.abs(g - ref) / np.maximum(np.abs(ref), 1e-3)) < 2 ** -7, k
+        g2 = O.dlogits(logits, c["labels"], temp, c["g_lp"], c["g_H"])
+        ref2 = H.bf16_from_bits(c["grad_both_bits"]).float().numpy()
+        assert np.max(np.abs(g2 - ref2) / np.maximum(np.abs(ref2), 1e-3)) < 2 ** -7, k
+        assert np.array_equal(mn, logits.min(-1)) and np.array_equal(mx, logits.max(-1))
+
+
+def test_vocab_parallel_combine_matches_unsharded():
+    rng = np.random.RandomState(0)
+    T, V, n = 9, 1000, 8
+    logits = (rng.randn(T, V) * 3).astype(np.float32)
+    labels = rng.randint(0, V, T)
+    lp, ent, lse, *_ = O.gather_logprobs_entropy(logits, labels, 0.7)
+    parts = [O.vocab_parallel_partials(logits[:, r * V // n:(r + 1) * V // n], labels, r * V // n, 0.7)
+             for r in range(n)]
+    lp2, ent2, lse2 = O.vocab_parallel_combine(parts)
+    assert np.allclose(lp, lp2, atol=1e-10) and np.allclose(ent, ent2, atol=1e-10) and np.allclose(lse, lse2)
+
+
+def _check_stats(st, c, k):
+    for name in ("loss", "importance_weight", "approx_kl", "behave_imp_weight", "behave_approx_kl"):
+        if "stat_" + name in c:
+            assert np.allclose(st[name], c["stat_" + name], rtol=1e-6, atol=1e-7), (k, name)
+    for name in ("clip_mask", "dual_clip_mask", "behave_mask"):
+        if "stat_" + name in c:
+            assert np.array_equal(st[name], c["stat_" + name]), (k, name)
+
+
+def test_actor_loss_vs_reference():
+    z = H.load("actor_loss.npz")
+    for k, c in H.cases(z):
+        eps, eps_hi, c_clip, cap = (H.opt(x) for x in c["cfg"])
+        loss, st, grad = O.ppo_actor_loss(c["lp"], c["prox"], c["old"], c["adv"], eps, c["mask"],
+                                          eps_clip_higher=eps_hi, c_clip=c_clip, behav_imp_weight_cap=cap)
+        assert abs(loss - float(c["loss"])) <= 1e-5 * max(1.0, abs(float(c["loss"]))), k
+        assert np.allclose(grad, c["grad"], rtol=1e-5, atol=1e-8), k
+        _check_stats(st, c, k)
+    for k, c in H.cases(z, prefix="l", count_key="n_legacy"):
+        eps, c_clip, cap = (H.opt(x) for x in c["cfg"])
+        prox = c["prox"] if bool(c["has_prox"]) else None
+        loss, st, grad = O.ppo_actor_loss(c["lp"], prox, c["old"], c["adv"], eps, c["mask"],
+                                          c_clip=c_clip, behav_imp_weight_cap=cap)
+        assert abs(loss - float(c["loss"])) <= 1e-5 * max(1.0, abs(float(c["loss"]))), k
+        assert np.allclose(grad, c["grad"], rtol=1e-5, atol=1e-8), k
+        _check_stats(st, c, k)
+        assert ("behave_mask" in st) == bool(c["has_prox"])
+
+
+@pytest.mark.parametrize("eps_clip", [0.01, 0.05, 0.1, 0.2, 0.5])
+@pytest.mark.parametrize("c_clip", [None, 1.5, 2.0, 5.0])
+@pytest.mark.parametrize("size", [1, 10, 100])
+def test_dual_clip_known_answer(size, eps_clip, c_clip):
+    """Same grid and independent formula as realhf/tests/data/test_dual_clip.py:53-63."""
+    rng = np.random.RandomState(size * 7 + int(eps_clip * 100))
+    old = -np.abs(rng.randn(size)).astype(np.float32)
+    new = -np.abs(rng.randn(size)).astype(np.float32)
+    adv = rng.randn(size).astype(np.float32)
+    want = O.ppo_dual_clip_known_answer(new, old, adv, eps_clip, c_clip)
+    got, _, _ = O.ppo_actor_loss(new, None, old, adv, eps_clip, np.ones(size, bool), c_clip=c_clip)
+    assert np.isclose(got, want, rtol=1e-5, atol=1e-7)
+
+
+def test_critic_loss_vs_reference():
+    z = H.load("critic_loss.npz")
+    for k, c in H.cases(z):
+        mask = c["mask"] if bool(c["has_mask"]) else None
+        loss, st, grad = O.ppo_critic_loss(c["value"], c["old"], c["target"], float(c["eps"]), mask,
+                                           "huber" if bool(c["huber"]) else "mse")
+        assert abs(loss - float(c["loss"])) <= 1e-5 * max(1.0, abs(float(c["loss"]))), k
+        assert np.allclose(grad, c["grad"], rtol=1e-5, atol=1e-9), k
+        assert np.array_equal(st["clip_mask"], c["stat_clip_mask"]), k
+        assert np.allclose(st["loss"], c["stat_loss"], rtol=1e-6, atol=1e-7), k
+
+
+def test_intervals_bit_exact_vs_reference():
+    z = H.load("intervals.npz")
+    for k, c in H.cases(z):
+        iv = c["intervals"]
+        assert np.array_equal(O.slice_intervals(c["src"], iv), c["packed"]), k
+        assert np.array_equal(C.slice_intervals(c["src"], iv), c["packed"]), k
+        d = c["dst"].copy()
+        O.set_intervals(c["newvals"], d, iv)
+        assert np.array_equal(d, c["dst_after"]), k
+        d = c["dst"].copy()
+        C.set_intervals(c["newvals"], d, iv)
+        assert np.array_equal(d, c["dst_after"]), k
+
+
+def test_merge_intervals_vs_reference_cpp():
+    cases = [[], [(0, 4)], [(0, 4), (4, 9), (9, 10)], [(5, 7), (0, 5), (7, 9), (9, 9), (9, 12)],
+             [(0, 2), (3, 5), (5, 8), (1, 3), (3, 4)]]
+    rng = np.random.RandomState(1)
+    pts = np.sort(rng.choice(10000, 400, replace=False))
+    cases.append([(int(a), int(b)) for a, b in zip(pts[:-1], pts[1:]) if rng.rand() > 0.2])
+    want = [[], [(0, 4)], [(0, 10)], [(5, 7), (0, 5), (7, 12)], [(0, 2), (3, 8), (1, 4)]]
+    for i, iv in enumerate(cases):
+        got = O.merge_intervals(iv)
+        assert got == C.merge_intervals(iv) if iv else got == []
+        if i < len(want):
+            assert got == want[i]
+    # the reference's own C++ (built from /root/reference by oracle/build_oracle.py) when present
+    import glob, importlib.util, os
+    so = glob.glob(os.path.join(H.ROOT, "oracle", "_ref", "interval_op*.so"))
+    if so:
+        spec = importlib.util.spec_from_file_location("interval_op", so[0])
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+        for iv in cases:
+            assert [tuple(x) for x in mod.merge_intervals(iv)] == O.merge_intervals(iv)
