@@ -1,0 +1,460 @@
+// extern "C" entry points of libareal_b200.so (declared in include/areal_b200.h): argument
+// validation, parameter-block assembly, launch.  No allocation, no synchronisation.
+#include <math.h>
+#include <stdarg.h>
+#include <string.h>
+
+#include "../../include/areal_b200.h"
+#include "common.cuh"
+#include "gae_scan.h"
+#include "interval_copy.h"
+#include "logits_fused.h"
+#include "ppo_loss.h"
+
+namespace ab {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int check_launch(const char* what) {
+  const cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_error("%s launch failed: %s", what, cudaGetErrorString(e));
+    return kCudaError;
+  }
+  return kOk;
+}
+
+int num_sms() {
+  static int cached[64] = {0};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+  if (cached[dev] == 0) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
+      n = 148;
+    cached[dev] = n;
+  }
+  return cached[dev];
+}
+
+static int dtype_size(int dtype) {
+  return dtype == kFP32 ? 4 : ((dtype == kBF16 || dtype == kFP16) ? 2 : 0);
+}
+
+static int make_cfg(ActorCfg* c, double eps_clip, double eps_clip_higher, double c_clip,
+                    double cap, bool decoupled) {
+  AB_REQUIRE(!isnan(eps_clip), "eps_clip must be a number");
+  c->lo = static_cast<float>(1.0 - eps_clip);
+  c->hi = static_cast<float>(1.0 + (isnan(eps_clip_higher) ? eps_clip : eps_clip_higher));
+  c->has_c = !isnan(c_clip);
+  AB_REQUIRE(!c->has_c || c_clip > 1.0, "c_clip must be > 1.0 (got %f)", c_clip);   // functional.py:204
+  c->c_clip = c->has_c ? static_cast<float>(c_clip) : 0.f;
+  c->has_cap = !isnan(cap);
+  c->cap = c->has_cap ? static_cast<float>(cap) : 0.f;
+  c->decoupled = decoupled ? 1 : 0;
+  return kOk;
+}
+
+static int check_logits(const void* logits, int dtype, int64_t T, int64_t V, int64_t row_stride,
+                        const int64_t* labels, double temperature) {
+  AB_REQUIRE(T >= 0 && V > 0, "bad shape T=%lld V=%lld", (long long)T, (long long)V);
+  AB_REQUIRE(dtype_size(dtype) != 0, "unsupported dtype %d", dtype);
+  AB_REQUIRE(T == 0 || (logits && labels), "logits / labels must not be null");
+  AB_REQUIRE(row_stride >= V, "row_stride (%lld) < V (%lld)", (long long)row_stride, (long long)V);
+  AB_REQUIRE(temperature > 0.0 && isfinite(temperature), "temperature must be finite and > 0");
+  return kOk;
+}
+
+}  // namespace ab
+
+using namespace ab;
+
+extern "C" {
+
+AREAL_B200_API const char* areal_b200_last_error(void) { return g_err; }
+AREAL_B200_API int areal_b200_version(void) { return 100; }
+
+// ---- P1 ------------------------------------------------------------------------------------------
+AREAL_B200_API int64_t areal_b200_gae1d_workspace_bytes(int64_t total_tokens) {
+  return gae1d_workspace_bytes(total_tokens < 0 ? 0 : total_tokens);
+}
+
+AREAL_B200_API int areal_b200_gae1d_nolp_misalign(const float* rewards, const float* values,
+                                   const int32_t* cu_seqlens, const uint8_t* bootstrap,
+                                   int64_t total_tokens, int64_t batch_size, double gamma,
+                                   double lam, float* adv_out, float* ret_out, void* workspace,
+                                   int64_t workspace_bytes, void* stream) {
+  AB_REQUIRE(total_tokens >= 0 && batch_size >= 0, "negative size");
+  if (total_tokens == 0) return kOk;
+  AB_REQUIRE(batch_size > 0, "total_tokens > 0 needs batch_size > 0");
+  AB_REQUIRE(rewards && values && cu_seqlens && bootstrap && adv_out && ret_out, "null pointer");
+  const int64_t need = gae1d_workspace_bytes(total_tokens);
+  if (need > int64_t(sizeof(uint32_t)) * 16) {   // more than the header: look-back needs it
+    if (!workspace || workspace_bytes < need) {
+      set_error("gae1d workspace too small: need %lld bytes, got %lld", (long long)need,
+                (long long)workspace_bytes);
+      return kWorkspaceTooSmall;
+    }
+  }
+  Gae1dParams p;
+  p.rewards = rewards;
+  p.values = values;
+  p.cu = cu_seqlens;
+  p.bootstrap = bootstrap;
+  p.T = total_tokens;
+  p.B = batch_size;
+  p.g = static_cast<float>(gamma);
+  p.gl = static_cast<float>(gamma * lam);
+  p.adv = adv_out;
+  p.ret = ret_out;
+  p.workspace = workspace;
+  p.vec_ok = ((reinterpret_cast<uintptr_t>(rewards) | reinterpret_cast<uintptr_t>(adv_out) |
+               reinterpret_cast<uintptr_t>(ret_out)) & 15) == 0;
+  return launch_gae1d(p, static_cast<cudaStream_t>(stream));
+}
+
+AREAL_B200_API int areal_b200_gae_padded_masked(const float* rewards, const float* values,
+                                 const float* loss_mask, const uint8_t* seq_no_eos, int64_t B,
+                                 int64_t S, double gamma, double lam, float* adv_out,
+                                 float* ret_out, void* stream) {
+  AB_REQUIRE(B >= 0 && S >= 0, "negative size");
+  if (B == 0 || S == 0) return kOk;
+  AB_REQUIRE(rewards && values && loss_mask && seq_no_eos && adv_out && ret_out, "null pointer");
+  GaePaddedParams p;
+  p.rewards = rewards;
+  p.values = values;
+  p.mask = loss_mask;
+  p.no_eos = seq_no_eos;
+  p.B = B;
+  p.S = S;
+  p.g = static_cast<float>(gamma);
+  p.gl = static_cast<float>(gamma * lam);
+  p.adv = adv_out;
+  p.ret = ret_out;
+  return launch_gae_padded(p, static_cast<cudaStream_t>(stream));
+}
+
+AREAL_B200_API int areal_b200_gae2d_olp(const float* rewards, const float* values, const uint8_t* done,
+                         const int32_t* done_y_indices, const int32_t* cu_num_dones,
+                         const uint8_t* is_truncate, int64_t B, int64_t H, int64_t num_dones,
+                         double gamma, double lam, float* adv_out, float* ret_out, void* stream) {
+  AB_REQUIRE(B >= 0 && H >= 0 && num_dones >= 0, "negative size");
+  if (B == 0 || H == 0) return kOk;
+  AB_REQUIRE(rewards && values && done && cu_num_dones && adv_out && ret_out, "null pointer");
+  AB_REQUIRE(num_dones == 0 || (done_y_indices && is_truncate), "null segment table");
+  Gae2dParams p;
+  p.rewards = rewards;
+  p.values = values;
+  p.done = done;
+  p.done_y_indices = done_y_indices;
+  p.cu_num_dones = cu_num_dones;
+  p.is_truncate = is_truncate;
+  p.B = B;
+  p.H = H;
+  p.g = static_cast<float>(gamma);
+  p.gl = static_cast<float>(gamma) * static_cast<float>(lam);
+  p.adv = adv_out;
+  p.ret = ret_out;
+  return launch_gae2d_olp(p, static_cast<cudaStream_t>(stream));
+}
+
+// ---- P2 ------------------------------------------------------------------------------------------
+static void fill_fwd_common(LogitsFwdParams* p, const void* logits, int dtype, int64_t T, int64_t V,
+                            int64_t row_stride, const int64_t* labels, int64_t vocab_start,
+                            double temperature) {
+  memset(p, 0, sizeof(*p));
+  p->logits = logits;
+  p->dtype = dtype;
+  p->T = T;
+  p->V = V;
+  p->row_stride_bytes = row_stride * dtype_size(dtype);
+  p->labels = labels;
+  p->vocab_start = vocab_start;
+  p->inv_temperature = static_cast<float>(1.0 / temperature);
+}
+
+AREAL_B200_API int areal_b200_logits_fwd(const void* logits, int dtype, int64_t T, int64_t V, int64_t row_stride,
+                          const int64_t* labels, double temperature, float* logp, float* entropy,
+                          float* lse, float* raw_min, float* raw_max, void* stream) {
+  int rc = check_logits(logits, dtype, T, V, row_stride, labels, temperature);
+  if (rc) return rc;
+  AB_REQUIRE(T == 0 || (logp && lse), "logp and lse outputs are required");
+  LogitsFwdParams p;
+  fill_fwd_common(&p, logits, dtype, T, V, row_stride, labels, 0, temperature);
+  p.mode = kModeStandard;
+  p.logp = logp;
+  p.entropy = entropy;
+  p.lse = lse;
+  p.raw_min = raw_min;
+  p.raw_max = raw_max;
+  return launch_logits_fwd(p, static_cast<cudaStream_t>(stream));
+}
+
+AREAL_B200_API int areal_b200_logits_partial_fwd(const void* logits, int dtype, int64_t T, int64_t V,
+                                  int64_t row_stride, const int64_t* labels, int64_t vocab_start,
+                                  double temperature, float* parts, float* raw_min, float* raw_max,
+                                  void* stream) {
+  int rc = check_logits(logits, dtype, T, V, row_stride, labels, temperature);
+  if (rc) return rc;
+  AB_REQUIRE(T == 0 || parts, "parts output is required");
+  LogitsFwdParams p;
+  fill_fwd_common(&p, logits, dtype, T, V, row_stride, labels, vocab_start, temperature);
+  p.mode = kModePartial;
+  p.part_m = parts;
+  p.part_s = parts + T;
+  p.part_u = parts + 2 * T;
+  p.part_zl = parts + 3 * T;
+  p.raw_min = raw_min;
+  p.raw_max = raw_max;
+  return launch_logits_fwd(p, static_cast<cudaStream_t>(stream));
+}
+
+AREAL_B200_API int areal_b200_vocab_combine(const float* parts, int64_t R, int64_t T, float* logp, float* entropy,
+                             float* lse, void* stream) {
+  AB_REQUIRE(R > 0 && R <= 4096 && T >= 0, "bad R / T");
+  AB_REQUIRE(T == 0 || (parts && logp && lse), "null pointer");
+  return launch_vocab_combine(parts, static_cast<int>(R), T, logp, entropy, lse,
+                              static_cast<cudaStream_t>(stream));
+}
+
+AREAL_B200_API int areal_b200_logits_bwd(const void* logits, int dtype, int64_t T, int64_t V, int64_t row_stride,
+                          const int64_t* labels, int64_t vocab_start, double temperature,
+                          const float* lse, const float* entropy, const float* g_logp,
+                          const float* g_entropy, const float* scale0, const float* scale1,
+                          void* dlogits, int64_t d_row_stride, void* stream) {
+  int rc = check_logits(logits, dtype, T, V, row_stride, labels, temperature);
+  if (rc) return rc;
+  AB_REQUIRE(T == 0 || (lse && dlogits), "lse and dlogits are required");
+  AB_REQUIRE(d_row_stride >= V, "d_row_stride (%lld) < V", (long long)d_row_stride);
+  AB_REQUIRE(!g_entropy || entropy, "g_entropy needs the forward's entropy");
+  LogitsBwdParams p;
+  memset(&p, 0, sizeof(p));
+  p.logits = logits;
+  p.dlogits = dlogits;
+  p.dtype = dtype;
+  p.T = T;
+  p.V = V;
+  p.row_stride_bytes = row_stride * dtype_size(dtype);
+  p.d_row_stride_bytes = d_row_stride * dtype_size(dtype);
+  p.labels = labels;
+  p.vocab_start = vocab_start;
+  p.inv_temperature = static_cast<float>(1.0 / temperature);
+  p.lse = lse;
+  p.entropy = entropy;
+  p.g_logp = g_logp;
+  p.g_entropy = g_entropy;
+  p.scale0 = scale0;
+  p.scale1 = scale1;
+  return launch_logits_bwd(p, static_cast<cudaStream_t>(stream));
+}
+
+// ---- P3 ------------------------------------------------------------------------------------------
+AREAL_B200_API int64_t areal_b200_loss_workspace_bytes(void) {
+  const int64_t a = loss_workspace_bytes(), b = logits_loss_workspace_bytes();
+  return a > b ? a : b;
+}
+
+static int check_ws(void* workspace, int64_t workspace_bytes) {
+  const int64_t need = areal_b200_loss_workspace_bytes();
+  if (!workspace || workspace_bytes < need) {
+    set_error("loss workspace too small: need %lld bytes, got %lld", (long long)need,
+              (long long)workspace_bytes);
+    return kWorkspaceTooSmall;
+  }
+  return kOk;
+}
+
+AREAL_B200_API int areal_b200_ppo_actor_loss(const float* logprobs, const float* proximal_logprobs,
+                              const float* old_logprobs, const float* advantages,
+                              const uint8_t* loss_mask, int64_t T, double eps_clip,
+                              double eps_clip_higher, double c_clip, double behav_imp_weight_cap,
+                              float* loss_out, float* inv_count_out, float* coef, float* stat_loss,
+                              float* stat_importance_weight, float* stat_approx_kl,
+                              uint8_t* stat_clip_mask, uint8_t* stat_dual_clip_mask,
+                              float* stat_behave_imp_weight, float* stat_behave_approx_kl,
+                              uint8_t* stat_behave_mask, void* workspace, int64_t workspace_bytes,
+                              void* stream) {
+  AB_REQUIRE(T >= 0, "negative T");
+  AB_REQUIRE(loss_out && inv_count_out, "loss_out / inv_count_out required");
+  AB_REQUIRE(T == 0 || (logprobs && old_logprobs && advantages && coef), "null pointer");
+  int rc = check_ws(workspace, workspace_bytes);
+  if (rc) return rc;
+  ActorLossParams p;
+  memset(&p, 0, sizeof(p));
+  rc = make_cfg(&p.cfg, eps_clip, eps_clip_higher, c_clip, behav_imp_weight_cap,
+                proximal_logprobs != nullptr);
+  if (rc) return rc;
+  p.logp = logprobs;
+  p.prox = proximal_logprobs;
+  p.old = old_logprobs;
+  p.adv = advantages;
+  p.mask = loss_mask;
+  p.T = T;
+  p.loss_out = loss_out;
+  p.inv_count_out = inv_count_out;
+  p.coef = coef;
+  p.stat_loss = stat_loss;
+  p.stat_ratio = stat_importance_weight;
+  p.stat_kl = stat_approx_kl;
+  p.clip_mask = stat_clip_mask;
+  p.dual_clip_mask = stat_dual_clip_mask;
+  p.behave_w = stat_behave_imp_weight;
+  p.behave_kl = stat_behave_approx_kl;
+  p.behave_mask = stat_behave_mask;
+  p.workspace = workspace;
+  return launch_actor_loss(p, static_cast<cudaStream_t>(stream));
+}
+
+AREAL_B200_API int areal_b200_ppo_critic_loss(const float* value, const float* old_value,
+                               const float* target_value, const uint8_t* loss_mask, int64_t T,
+                               double value_eps_clip, int use_huber, float* loss_out,
+                               float* inv_count_out, float* coef, float* stat_loss,
+                               uint8_t* stat_clip_mask, void* workspace, int64_t workspace_bytes,
+                               void* stream) {
+  AB_REQUIRE(T >= 0, "negative T");
+  AB_REQUIRE(loss_out && inv_count_out, "loss_out / inv_count_out required");
+  AB_REQUIRE(T == 0 || (value && old_value && target_value && coef), "null pointer");
+  int rc = check_ws(workspace, workspace_bytes);
+  if (rc) return rc;
+  CriticLossParams p;
+  memset(&p, 0, sizeof(p));
+  p.value = value;
+  p.old = old_value;
+  p.target = target_value;
+  p.mask = loss_mask;
+  p.T = T;
+  p.eps = static_cast<float>(value_eps_clip);
+  p.huber = use_huber;
+  p.loss_out = loss_out;
+  p.inv_count_out = inv_count_out;
+  p.coef = coef;
+  p.stat_loss = stat_loss;
+  p.clip_mask = stat_clip_mask;
+  p.workspace = workspace;
+  return launch_critic_loss(p, static_cast<cudaStream_t>(stream));
+}
+
+AREAL_B200_API int areal_b200_scale_by_scalars(const float* coef, const float* scale0, const float* scale1,
+                                int64_t T, float* out, void* stream) {
+  AB_REQUIRE(T >= 0, "negative T");
+  AB_REQUIRE(T == 0 || (coef && scale0 && out), "null pointer");
+  return launch_scale(coef, scale0, scale1, T, out, static_cast<cudaStream_t>(stream));
+}
+
+AREAL_B200_API int areal_b200_fused_actor_fwd(const void* logits, int dtype, int64_t T, int64_t V,
+                               int64_t row_stride, const int64_t* labels, double temperature,
+                               const float* proximal_logprobs, const float* old_logprobs,
+                               const float* advantages, const uint8_t* loss_mask, double eps_clip,
+                               double eps_clip_higher, double c_clip, double behav_imp_weight_cap,
+                               float* logp, float* entropy, float* lse, float* raw_min,
+                               float* raw_max, float* loss_out, float* inv_count_out, float* coef,
+                               float* stat_loss, float* stat_importance_weight,
+                               float* stat_approx_kl, uint8_t* stat_clip_mask,
+                               uint8_t* stat_dual_clip_mask, float* stat_behave_imp_weight,
+                               float* stat_behave_approx_kl, uint8_t* stat_behave_mask,
+                               void* workspace, int64_t workspace_bytes, void* stream) {
+  int rc = check_logits(logits, dtype, T, V, row_stride, labels, temperature);
+  if (rc) return rc;
+  AB_REQUIRE(T > 0, "fused entry needs T > 0");
+  AB_REQUIRE(logp && lse && loss_out && inv_count_out && coef, "required output is null");
+  AB_REQUIRE(old_logprobs && advantages && loss_mask, "old_logprobs / advantages / loss_mask required");
+  rc = check_ws(workspace, workspace_bytes);
+  if (rc) return rc;
+  LogitsFwdParams p;
+  fill_fwd_common(&p, logits, dtype, T, V, row_stride, labels, 0, temperature);
+  rc = make_cfg(&p.cfg, eps_clip, eps_clip_higher, c_clip, behav_imp_weight_cap,
+                proximal_logprobs != nullptr);
+  if (rc) return rc;
+  p.mode = kModeFusedActor;
+  p.logp = logp;
+  p.entropy = entropy;
+  p.lse = lse;
+  p.raw_min = raw_min;
+  p.raw_max = raw_max;
+  p.prox = proximal_logprobs;
+  p.old = old_logprobs;
+  p.adv = advantages;
+  p.loss_mask = loss_mask;
+  p.coef = coef;
+  p.stat_loss = stat_loss;
+  p.stat_ratio = stat_importance_weight;
+  p.stat_kl = stat_approx_kl;
+  p.clip_mask = stat_clip_mask;
+  p.dual_clip_mask = stat_dual_clip_mask;
+  p.behave_w = stat_behave_imp_weight;
+  p.behave_kl = stat_behave_approx_kl;
+  p.behave_mask = stat_behave_mask;
+  p.loss_out = loss_out;
+  p.inv_count_out = inv_count_out;
+  p.workspace = workspace;
+  return launch_logits_fwd(p, static_cast<cudaStream_t>(stream));
+}
+
+// ---- P4 ------------------------------------------------------------------------------------------
+AREAL_B200_API int64_t areal_b200_interval_workspace_bytes(int64_t n_intervals) {
+  return interval_workspace_bytes(n_intervals < 0 ? 0 : n_intervals);
+}
+
+static int interval_common(bool slice, const void* flat_in, void* flat_out, const void* packed_in,
+                           void* packed_out, int64_t flat_numel, int64_t packed_numel,
+                           const int64_t* intervals, int64_t n, int64_t elem_size, void* workspace,
+                           int64_t workspace_bytes, void* stream) {
+  AB_REQUIRE(n >= 0 && flat_numel >= 0 && packed_numel >= 0, "negative size");
+  AB_REQUIRE(elem_size == 1 || elem_size == 2 || elem_size == 4 || elem_size == 8,
+             "elem_size must be 1, 2, 4 or 8 (got %lld)", (long long)elem_size);
+  const int64_t need = interval_workspace_bytes(n);
+  if (!workspace || workspace_bytes < need) {
+    set_error("interval workspace too small: need %lld bytes, got %lld", (long long)need,
+              (long long)workspace_bytes);
+    return kWorkspaceTooSmall;
+  }
+  AB_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 7) == 0, "workspace must be 8-byte aligned");
+  AB_REQUIRE(n == 0 || intervals, "intervals is null");
+  AB_REQUIRE(n == 0 || (reinterpret_cast<uintptr_t>(intervals) & 15) == 0,
+             "intervals must be 16-byte aligned");
+  AB_REQUIRE(packed_numel == 0 || ((slice ? (flat_in && packed_out) : (packed_in && flat_out))),
+             "null buffer");
+  return launch_interval_copy(slice, flat_in, flat_out, packed_in, packed_out, intervals, n,
+                              elem_size, flat_numel, packed_numel, workspace,
+                              static_cast<cudaStream_t>(stream));
+}
+
+AREAL_B200_API int areal_b200_slice_intervals(const void* flat, int64_t flat_numel, void* packed,
+                               int64_t packed_numel, const int64_t* intervals,
+                               int64_t n_intervals, int64_t elem_size, void* workspace,
+                               int64_t workspace_bytes, void* stream) {
+  return interval_common(true, flat, nullptr, nullptr, packed, flat_numel, packed_numel, intervals,
+                         n_intervals, elem_size, workspace, workspace_bytes, stream);
+}
+
+AREAL_B200_API int areal_b200_set_intervals(const void* packed, int64_t packed_numel, void* flat,
+                             int64_t flat_numel, const int64_t* intervals, int64_t n_intervals,
+                             int64_t elem_size, void* workspace, int64_t workspace_bytes,
+                             void* stream) {
+  return interval_common(false, nullptr, flat, packed, nullptr, flat_numel, packed_numel, intervals,
+                         n_intervals, elem_size, workspace, workspace_bytes, stream);
+}
+
+AREAL_B200_API int64_t areal_b200_merge_intervals(const uint64_t* iv, int64_t n, uint64_t* out) {
+  if (n < 0 || (n > 0 && (!iv || !out))) return -1;
+  int64_t k = 0;
+  for (int64_t i = 0; i < n; ++i) {
+    if (k > 0 && out[2 * (k - 1) + 1] == iv[2 * i]) {
+      out[2 * (k - 1) + 1] = iv[2 * i + 1];
+    } else {
+      out[2 * k] = iv[2 * i];
+      out[2 * k + 1] = iv[2 * i + 1];
+      ++k;
+    }
+  }
+  return k;
+}
+
+}  // extern "C"

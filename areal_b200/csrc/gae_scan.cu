@@ -1,0 +1,473 @@
+// Generalised advantage estimation as a segmented REVERSE scan of affine maps.
+//
+// Replaces (reference, relative to its root):
+//   csrc/cugae/gae.cu:10-60            gae_1d_nolp_misalign  (one thread per sequence, serial)
+//   realhf/impl/model/utils/ppo_functional.py:292-323  pygae1d_nolp_misalign (CPU path)
+//   areal/engine/ppo/actor.py:131-152  padded [B,S] masked GAE python loop
+//   csrc/cugae/gae.cu:62-134           gae_2d_olp (and gae_2d_nolp, whose host wrapper runs the
+//                                      olp kernel, gae.cu:199)
+//
+// A_t = delta_t + a_t * A_{t+1} is the affine map x -> b_t + a_t x with a_t = gamma*lambda inside a
+// sequence and a_t = 0 at its last step, so sequence boundaries need no flags: composition
+// (a,b)o(a',b') = (a a', b + a b') annihilates the carry there.  Tokens are tiled 2048 per CTA
+// (256 threads x 8 consecutive tokens, 128-bit loads/stores); each thread folds its 8 maps, the
+// warp does a shuffle suffix-scan, warps combine through shared memory, and tiles chain with a
+// single-pass decoupled look-back (tickets issued right-to-left) that stops as soon as the
+// accumulated `a` is exactly 0, i.e. at the first sequence end.
+//
+// Numerics: delta_t is formed in fp32 with the reference's operation order (no FMA contraction),
+// the scan itself runs in fp64 so the reassociation of the parallel scan cannot be seen in the
+// fp32 result: the output is the correctly rounded recurrence, and its distance to the
+// reference is the reference's own sequential fp32 rounding (tests report both against fp64).
+#include "common.cuh"
+#include "gae_scan.h"
+
+namespace ab {
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kWarps = kThreads / 32;
+constexpr int kItems = 8;
+constexpr int kTile = kThreads * kItems;   // 2048 tokens
+
+struct Affine {
+  double a, b;
+};
+__device__ __forceinline__ Affine ident() { return Affine{1.0, 0.0}; }
+// f after g
+__device__ __forceinline__ Affine compose(const Affine& f, const Affine& g) {
+  return Affine{f.a * g.a, fma(f.a, g.b, f.b)};
+}
+__device__ __forceinline__ Affine shfl_down(const Affine& v, int d) {
+  return Affine{__shfl_down_sync(0xffffffffu, v.a, d), __shfl_down_sync(0xffffffffu, v.b, d)};
+}
+
+// Block-wide suffix scan of per-thread maps (thread x owns positions left of thread x+1).
+// excl  = F_{x+1} o F_{x+2} o ... o F_{last}   (apply to the tile carry-in to get the value
+//         entering thread x from the right);  tile = F_0 o ... o F_last.
+// Contains one __syncthreads(); `wsm` may be rewritten after the caller's next barrier.
+__device__ __forceinline__ void block_suffix_scan(const Affine& agg, Affine* wsm, int warp, int lane,
+                                                  Affine& excl, Affine& tile) {
+  Affine inc = agg;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const Affine o = shfl_down(inc, d);
+    if (lane + d < 32) inc = compose(inc, o);
+  }
+  if (lane == 0) wsm[warp] = inc;
+  __syncthreads();
+  Affine W = ident();
+  for (int w = kWarps - 1; w > warp; --w) W = compose(wsm[w], W);
+  const Affine nxt = shfl_down(inc, 1);
+  excl = (lane < 31) ? compose(nxt, W) : W;
+  tile = W;
+  for (int w = warp; w >= 0; --w) tile = compose(wsm[w], tile);
+}
+
+// ---- decoupled look-back descriptors --------------------------------------------------------------
+struct __align__(16) TileDesc {
+  unsigned int flag;   // 0 = nothing, 1 = aggregate published, 2 = inclusive value published
+  unsigned int pad;
+  double inc;          // A at the first token of the tile (valid when flag == 2)
+  double agg_a, agg_b; // tile map (valid when flag >= 1)
+};
+struct WorkspaceHeader {
+  unsigned int ticket;
+  unsigned int done;
+  unsigned int pad[14];
+};
+static_assert(sizeof(TileDesc) == 32, "TileDesc layout");
+static_assert(sizeof(WorkspaceHeader) == 64, "header layout");
+
+__device__ __forceinline__ unsigned int ld_acquire_u32(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_u32(unsigned int* p, unsigned int v) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ double ld_volatile_f64(const double* p) {
+  double v;
+  asm volatile("ld.volatile.global.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
+  return v;
+}
+
+// ---- 1D packed, misaligned values ------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads)
+gae1d_kernel(const Gae1dParams p) {
+  __shared__ Affine wsm[kWarps];
+  __shared__ double carry_sm;
+  __shared__ unsigned int tile_sm;
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int64_t ntiles = (p.T + kTile - 1) / kTile;
+  WorkspaceHeader* hdr = reinterpret_cast<WorkspaceHeader*>(p.workspace);
+  TileDesc* desc = reinterpret_cast<TileDesc*>(reinterpret_cast<char*>(p.workspace) + sizeof(WorkspaceHeader));
+
+  // tickets are issued right-to-left: ticket 0 is the LAST tile, so a tile only ever waits on tiles
+  // whose CTAs already started (forward progress without co-residency assumptions).
+  int64_t tile;
+  if (ntiles == 1) {
+    tile = 0;
+  } else {
+    if (tid == 0) tile_sm = atomicAdd(&hdr->ticket, 1u);
+    __syncthreads();
+    tile = ntiles - 1 - int64_t(tile_sm);
+  }
+
+  const int64_t j0 = tile * kTile + int64_t(tid) * kItems;
+  int nvalid = 0;
+  if (j0 < p.T) nvalid = (p.T - j0) < kItems ? int(p.T - j0) : kItems;
+
+  float r[kItems], vcur[kItems], delta[kItems];
+  unsigned int last_bits = 0;
+  const double gl = double(p.gl);
+
+  if (nvalid > 0) {
+    // sequence of the first token: smallest i with cu[i+1] > j0
+    int64_t lo = 0, hi = p.B - 1;
+    while (lo < hi) {
+      const int64_t mid = (lo + hi) >> 1;
+      if (int64_t(p.cu[mid + 1]) > j0) hi = mid; else lo = mid + 1;
+    }
+    int64_t seq = lo;
+    int64_t cu_next = p.cu[seq + 1];
+
+    if (p.vec_ok && nvalid == kItems) {
+      const float4 a = __ldg(reinterpret_cast<const float4*>(p.rewards + j0));
+      const float4 b = __ldg(reinterpret_cast<const float4*>(p.rewards + j0) + 1);
+      r[0] = a.x; r[1] = a.y; r[2] = a.z; r[3] = a.w;
+      r[4] = b.x; r[5] = b.y; r[6] = b.z; r[7] = b.w;
+    } else {
+#pragma unroll
+      for (int k = 0; k < kItems; ++k) r[k] = (k < nvalid) ? __ldg(p.rewards + j0 + k) : 0.f;
+    }
+    float vprev = 0.f;
+    bool chain = false;       // vprev holds values[j + seq] for the current token
+#pragma unroll
+    for (int k = 0; k < kItems; ++k) {
+      if (k < nvalid) {
+        const int64_t j = j0 + k;
+        while (seq < p.B - 1 && j >= cu_next) {
+          ++seq;
+          cu_next = p.cu[seq + 1];
+          chain = false;
+        }
+        const bool is_last = (j + 1 == cu_next);
+        const int64_t vi = j + seq;
+        const float v = chain ? vprev : __ldg(p.values + vi);
+        float nv = __ldg(p.values + vi + 1);
+        vprev = nv;
+        chain = !is_last;      // next token of the same sequence reads values[vi + 1]
+        if (is_last) {
+          last_bits |= 1u << k;
+          if (!p.bootstrap[seq]) nv = 0.f;                      // gae.cu:23
+        }
+        vcur[k] = v;
+        // ppo_functional.py:316, fp32, unfused
+        delta[k] = __fsub_rn(__fadd_rn(r[k], __fmul_rn(p.g, nv)), v);
+      }
+    }
+  }
+
+  // fold the thread's maps right-to-left
+  Affine agg = ident();
+#pragma unroll
+  for (int k = kItems - 1; k >= 0; --k) {
+    if (k < nvalid) {
+      const double a = (last_bits >> k) & 1u ? 0.0 : gl;
+      agg.b = fma(a, agg.b, double(delta[k]));
+      agg.a = a * agg.a;
+    }
+  }
+
+  Affine excl, tagg;
+  block_suffix_scan(agg, wsm, warp, lane, excl, tagg);
+
+  double carry = 0.0;
+  if (ntiles > 1) {
+    if (tid == 0) {
+      TileDesc* me = desc + tile;
+      if (tile == ntiles - 1) {
+        me->inc = tagg.b;            // nothing to the right: A_{T} = 0
+        st_release_u32(&me->flag, 2u);
+      } else {
+        me->agg_a = tagg.a;
+        me->agg_b = tagg.b;
+        st_release_u32(&me->flag, 1u);
+        Affine run = ident();        // maps of tiles tile+1 .. k-1
+        for (int64_t k = tile + 1;; ++k) {
+          if (k >= ntiles || run.a == 0.0) {
+            carry = run.b;
+            break;
+          }
+          const TileDesc* d = desc + k;
+          unsigned int f;
+          while ((f = ld_acquire_u32(&d->flag)) == 0u) { __nanosleep(20); }
+          if (f == 2u) {
+            carry = fma(run.a, ld_volatile_f64(&d->inc), run.b);
+            break;
+          }
+          run = compose(run, Affine{ld_volatile_f64(&d->agg_a), ld_volatile_f64(&d->agg_b)});
+        }
+        me->inc = fma(tagg.a, carry, tagg.b);
+        st_release_u32(&me->flag, 2u);
+      }
+      carry_sm = carry;
+    }
+    __syncthreads();
+    carry = carry_sm;
+  }
+
+  if (nvalid > 0) {
+    double A = fma(excl.a, carry, excl.b);   // value entering this thread from the right
+    float adv[kItems], ret[kItems];
+#pragma unroll
+    for (int k = kItems - 1; k >= 0; --k) {
+      if (k < nvalid) {
+        const double a = (last_bits >> k) & 1u ? 0.0 : gl;
+        A = fma(a, A, double(delta[k]));
+        adv[k] = float(A);
+        ret[k] = __fadd_rn(adv[k], vcur[k]);                    // ppo_functional.py:319
+      }
+    }
+    if (p.vec_ok && nvalid == kItems) {
+      float4* ao = reinterpret_cast<float4*>(p.adv + j0);
+      float4* ro = reinterpret_cast<float4*>(p.ret + j0);
+      ao[0] = make_float4(adv[0], adv[1], adv[2], adv[3]);
+      ao[1] = make_float4(adv[4], adv[5], adv[6], adv[7]);
+      ro[0] = make_float4(ret[0], ret[1], ret[2], ret[3]);
+      ro[1] = make_float4(ret[4], ret[5], ret[6], ret[7]);
+    } else {
+#pragma unroll
+      for (int k = 0; k < kItems; ++k)
+        if (k < nvalid) {
+          p.adv[j0 + k] = adv[k];
+          p.ret[j0 + k] = ret[k];
+        }
+    }
+  }
+
+  // the last CTA to finish leaves the workspace zeroed for the next call
+  if (ntiles > 1) {
+    __syncthreads();
+    if (tid == 0) {
+      __threadfence();
+      tile_sm = atomicAdd(&hdr->done, 1u);
+    }
+    __syncthreads();
+    if (tile_sm == static_cast<unsigned int>(ntiles - 1)) {
+      for (int64_t k = tid; k < ntiles; k += kThreads) desc[k].flag = 0u;
+      if (tid == 0) {
+        hdr->ticket = 0u;
+        hdr->done = 0u;
+      }
+    }
+  }
+}
+
+// ---- padded [B,S] masked (areal-lite) ----------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads)
+gae_padded_kernel(const GaePaddedParams p) {
+  __shared__ Affine wsm[kWarps];
+  __shared__ float nv_val[kWarps];
+  __shared__ int nv_has[kWarps];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const double gl = double(p.gl);
+  for (int64_t row = blockIdx.x; row < p.B; row += gridDim.x) {
+    const float* r = p.rewards + row * p.S;
+    const float* v = p.values + row * p.S;
+    const float* m = p.mask + row * p.S;
+    float* adv = p.adv + row * p.S;
+    float* ret = p.ret + row * p.S;
+    const int64_t L = p.S - 1;                                  // positions taking part in the loop
+    float nv_carry = p.no_eos[row] ? v[p.S - 1] : 0.f;          // actor.py:135 (bool * value)
+    double a_carry = 0.0;                                       // adv[:, S-1] = 0
+    if (tid == 0) {
+      adv[p.S - 1] = 0.f;
+      ret[p.S - 1] = v[p.S - 1];                                // returns = advantages + values, :152
+    }
+    const int64_t ntiles = (L + kTile - 1) / kTile;
+    for (int64_t tile = ntiles - 1; tile >= 0; --tile) {
+      const int64_t t0 = tile * kTile + int64_t(tid) * kItems;
+      int nvalid = 0;
+      if (t0 < L) nvalid = (L - t0) < kItems ? int(L - t0) : kItems;
+      float rr[kItems], vv[kItems];
+      unsigned int valid_bits = 0;
+#pragma unroll
+      for (int k = 0; k < kItems; ++k) {
+        if (k < nvalid) {
+          rr[k] = __ldg(r + t0 + k);
+          vv[k] = __ldg(v + t0 + k);
+          if (__ldg(m + t0 + k) != 0.f) valid_bits |= 1u << k;
+        }
+      }
+      // nearest valid value to the right of this thread
+      const int first = valid_bits ? (__ffs(valid_bits) - 1) : -1;
+      float first_val = 0.f;
+#pragma unroll
+      for (int k = 0; k < kItems; ++k)
+        if (k == first) first_val = vv[k];
+      const unsigned int ball = __ballot_sync(0xffffffffu, first >= 0);
+      const unsigned int right = (lane == 31) ? 0u : (ball >> (lane + 1));
+      const int src = right ? (lane + __ffs(right)) : lane;
+      const float wv = __shfl_sync(0xffffffffu, first_val, src);
+      const float warp_first = __shfl_sync(0xffffffffu, first_val, ball ? (__ffs(ball) - 1) : 0);
+      if (lane == 0) {
+        nv_has[warp] = ball != 0u;
+        nv_val[warp] = warp_first;
+      }
+      __syncthreads();                                           // barrier #1
+      float nv_in;                                               // value entering this thread
+      if (right) {
+        nv_in = wv;
+      } else {
+        nv_in = nv_carry;
+        for (int w = kWarps - 1; w > warp; --w)
+          if (nv_has[w]) nv_in = nv_val[w];
+      }
+      float nv_tile = nv_carry;                                  // carry for the next (left) tile
+      for (int w = kWarps - 1; w >= 0; --w)
+        if (nv_has[w]) nv_tile = nv_val[w];
+
+      float delta[kItems];
+      Affine agg = ident();
+      {
+        float nv = nv_in;
+#pragma unroll
+        for (int k = kItems - 1; k >= 0; --k) {
+          if (k < nvalid && ((valid_bits >> k) & 1u)) {
+            delta[k] = __fsub_rn(__fadd_rn(rr[k], __fmul_rn(p.g, nv)), vv[k]);   // actor.py:137
+            agg.b = fma(gl, agg.b, double(delta[k]));                             // :138, :143
+            agg.a = gl * agg.a;
+            nv = vv[k];                                                           // :142
+          }
+        }
+      }
+      Affine excl, tagg;
+      block_suffix_scan(agg, wsm, warp, lane, excl, tagg);       // barrier #2 inside
+      double A = fma(excl.a, a_carry, excl.b);
+#pragma unroll
+      for (int k = kItems - 1; k >= 0; --k) {
+        if (k < nvalid) {
+          if ((valid_bits >> k) & 1u) A = fma(gl, A, double(delta[k]));
+          const float af = float(A);
+          adv[t0 + k] = af;
+          ret[t0 + k] = __fadd_rn(af, vv[k]);
+        }
+      }
+      a_carry = fma(tagg.a, a_carry, tagg.b);
+      nv_carry = nv_tile;
+    }
+    __syncthreads();
+  }
+}
+
+// ---- 2D with a segment table (gae_2d_olp semantics) --------------------------------------------------
+__global__ void __launch_bounds__(kThreads)
+gae2d_olp_kernel(const Gae2dParams p) {
+  __shared__ Affine wsm[kWarps];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const double gl = double(p.gl);
+  for (int64_t row = blockIdx.x; row < p.B; row += gridDim.x) {
+    const float* r = p.rewards + row * p.H;
+    const float* v = p.values + row * (p.H + 1);
+    const uint8_t* done = p.done + row * (p.H + 1);
+    float* adv = p.adv + row * p.H;
+    float* ret = p.ret + row * p.H;
+    const int64_t s0 = p.cu_num_dones[row], s1 = p.cu_num_dones[row + 1];
+    const int32_t* idx = p.done_y_indices + s0;
+    const int64_t nd = s1 - s0;
+    double a_carry = 0.0;
+    const int64_t ntiles = (p.H + kTile - 1) / kTile;
+    for (int64_t tile = ntiles - 1; tile >= 0; --tile) {
+      const int64_t t0 = tile * kTile + int64_t(tid) * kItems;
+      int nvalid = 0;
+      if (t0 < p.H) nvalid = (p.H - t0) < kItems ? int(p.H - t0) : kItems;
+      float delta[kItems], vv[kItems];
+      unsigned int tail_bits = 0, zero_bits = 0;
+      if (nvalid > 0) {
+        // first table entry with idx >= t0 + 1
+        int64_t lo = 0, hi = nd;
+        while (lo < hi) {
+          const int64_t mid = (lo + hi) >> 1;
+          if (int64_t(idx[mid]) >= t0 + 1) hi = mid; else lo = mid + 1;
+        }
+        int64_t q = lo;
+#pragma unroll
+        for (int k = 0; k < kItems; ++k) {
+          if (k < nvalid) {
+            const int64_t t = t0 + k;
+            while (q < nd && int64_t(idx[q]) < t + 1) ++q;
+            const bool at_done = (q < nd) && (int64_t(idx[q]) == t + 1);
+            const bool tail = at_done || (t == p.H - 1);
+            const float cur = __ldg(v + t);
+            float nv = __ldg(v + t + 1);
+            if (tail && done[t + 1]) nv = 0.f;                    // gae.cu:79-81
+            vv[k] = cur;
+            delta[k] = __fsub_rn(__fadd_rn(__ldg(r + t), __fmul_rn(p.g, nv)), cur);
+            if (tail) tail_bits |= 1u << k;
+            if (at_done && p.is_truncate[s0 + q]) zero_bits |= 1u << k;   // gae.cu:76-77, :85
+          }
+        }
+      }
+      Affine agg = ident();
+#pragma unroll
+      for (int k = kItems - 1; k >= 0; --k) {
+        if (k < nvalid) {
+          const double a = (tail_bits >> k) & 1u ? 0.0 : gl;
+          const double b = (zero_bits >> k) & 1u ? 0.0 : double(delta[k]);
+          agg.b = fma(a, agg.b, b);
+          agg.a = a * agg.a;
+        }
+      }
+      Affine excl, tagg;
+      block_suffix_scan(agg, wsm, warp, lane, excl, tagg);
+      double A = fma(excl.a, a_carry, excl.b);
+#pragma unroll
+      for (int k = kItems - 1; k >= 0; --k) {
+        if (k < nvalid) {
+          const double a = (tail_bits >> k) & 1u ? 0.0 : gl;
+          const double b = (zero_bits >> k) & 1u ? 0.0 : double(delta[k]);
+          A = fma(a, A, b);
+          const float af = float(A);
+          adv[t0 + k] = af;
+          ret[t0 + k] = __fadd_rn(af, vv[k]);
+        }
+      }
+      a_carry = fma(tagg.a, a_carry, tagg.b);
+      __syncthreads();   // wsm is rewritten by the next tile
+    }
+  }
+}
+
+}  // namespace
+
+int64_t gae1d_workspace_bytes(int64_t T) {
+  const int64_t ntiles = (T + kTile - 1) / kTile;
+  return int64_t(sizeof(WorkspaceHeader)) + (ntiles > 1 ? ntiles : 0) * int64_t(sizeof(TileDesc));
+}
+
+int launch_gae1d(const Gae1dParams& p, cudaStream_t stream) {
+  if (p.T == 0) return kOk;
+  const int64_t ntiles = (p.T + kTile - 1) / kTile;
+  gae1d_kernel<<<static_cast<unsigned int>(ntiles), kThreads, 0, stream>>>(p);
+  return check_launch("gae1d");
+}
+
+int launch_gae_padded(const GaePaddedParams& p, cudaStream_t stream) {
+  if (p.B == 0 || p.S == 0) return kOk;
+  const int64_t cap = int64_t(num_sms()) * 8;
+  gae_padded_kernel<<<static_cast<unsigned int>(p.B < cap ? p.B : cap), kThreads, 0, stream>>>(p);
+  return check_launch("gae_padded");
+}
+
+int launch_gae2d_olp(const Gae2dParams& p, cudaStream_t stream) {
+  if (p.B == 0 || p.H == 0) return kOk;
+  const int64_t cap = int64_t(num_sms()) * 8;
+  gae2d_olp_kernel<<<static_cast<unsigned int>(p.B < cap ? p.B : cap), kThreads, 0, stream>>>(p);
+  return check_launch("gae2d_olp");
+}
+
+}  // namespace ab

@@ -1,0 +1,223 @@
+// slice_intervals / set_intervals: gather / scatter of N half-open element ranges between a flat
+// parameter buffer and a packed buffer whose offsets are the exclusive cumsum of the range sizes in
+// the GIVEN order.
+//
+// Replaces (reference, relative to its root):
+//   csrc/interval_op/interval_op.cu:12-104  copyDataKernel / set_intervals / slice_intervals
+//                                           (one THREAD memcpy's up to 2048 elements -> uncoalesced;
+//                                            offsets via ATen temporaries; legacy default stream)
+//   realhf/impl/model/nn/flatten_param.py:65-90  _slice_intervals_py / _set_intervals_py
+//
+// Design (B200): (1) one small kernel scans the sizes into packed byte offsets (and validates the
+// ranges against the buffer sizes); (2) the copy kernel cuts the PACKED byte space into equal
+// contiguous chunks, one per warp, so the load is balanced whatever the interval sizes are; a warp
+// binary-searches the interval holding its first byte once, then walks intervals linearly.  Every
+// piece is moved with the widest vector the relative alignment of source and destination allows
+// (16/8/4/2/1 B), 8 independent 128-bit loads in flight per lane, streaming cache hints; heads and
+// tails are byte-granular, so any element size and any alignment is bit-exact.
+#include "common.cuh"
+#include "interval_copy.h"
+
+namespace ab {
+namespace {
+
+constexpr int kScanThreads = 1024;
+constexpr int kCopyThreads = 256;
+constexpr int kCopyWarps = kCopyThreads / 32;
+
+// workspace: int64 status[2] | int64 off[N + 1]   (byte offsets into the packed buffer)
+__global__ void __launch_bounds__(kScanThreads)
+interval_scan_kernel(const int64_t* __restrict__ iv, int64_t n, int64_t elem_size,
+                     int64_t flat_numel, int64_t packed_numel, int64_t* __restrict__ ws) {
+  __shared__ int64_t warp_sums[32];
+  __shared__ int64_t base_sm;
+  __shared__ int bad_sm;
+  int64_t* status = ws;
+  int64_t* off = ws + 2;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) {
+    base_sm = 0;
+    bad_sm = 0;
+  }
+  __syncthreads();
+  constexpr int kPer = 4;
+  for (int64_t start = 0; start < n; start += int64_t(kScanThreads) * kPer) {
+    int64_t sz[kPer];
+    int64_t local = 0;
+    bool bad = false;
+#pragma unroll
+    for (int k = 0; k < kPer; ++k) {
+      const int64_t i = start + int64_t(tid) * kPer + k;
+      sz[k] = 0;
+      if (i < n) {
+        const longlong2 se = reinterpret_cast<const longlong2*>(iv)[i];
+        if (se.x < 0 || se.y < se.x || se.y > flat_numel) bad = true;
+        else sz[k] = (se.y - se.x) * elem_size;
+      }
+      local += sz[k];
+    }
+    if (bad) bad_sm = 1;
+    // block exclusive scan of `local`
+    int64_t inc = local;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int64_t o = __shfl_up_sync(0xffffffffu, inc, d);
+      if (lane >= d) inc += o;
+    }
+    if (lane == 31) warp_sums[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+      int64_t w = warp_sums[lane];
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const int64_t o = __shfl_up_sync(0xffffffffu, w, d);
+        if (lane >= d) w += o;
+      }
+      warp_sums[lane] = w;   // inclusive over warps
+    }
+    __syncthreads();
+    const int64_t base = base_sm;
+    int64_t run = base + (warp ? warp_sums[warp - 1] : 0) + (inc - local);
+#pragma unroll
+    for (int k = 0; k < kPer; ++k) {
+      const int64_t i = start + int64_t(tid) * kPer + k;
+      if (i < n) off[i] = run;
+      run += sz[k];
+    }
+    __syncthreads();
+    if (tid == 0) base_sm = base + warp_sums[31];
+    __syncthreads();
+  }
+  if (tid == 0) {
+    off[n] = base_sm;
+    int64_t st = 0;
+    if (bad_sm) st = 1;
+    else if (base_sm != packed_numel * elem_size) st = 2;
+    status[0] = st;
+    status[1] = base_sm;
+  }
+}
+
+template <typename V>
+__device__ __forceinline__ V ld_stream(const V* p) { return __ldg(p); }
+template <>
+__device__ __forceinline__ uint4 ld_stream<uint4>(const uint4* p) { return ldg_stream_v4(p); }
+template <typename V>
+__device__ __forceinline__ void st_stream(V* p, const V& v) { *p = v; }
+template <>
+__device__ __forceinline__ void st_stream<uint4>(uint4* p, const uint4& v) { stg_stream_v4(p, v); }
+
+template <typename V>
+__device__ __forceinline__ void warp_copy_vec(char* d, const char* s, int64_t n, int lane) {
+  constexpr int W = sizeof(V);
+  if (W > 1) {
+    int64_t head = (W - (reinterpret_cast<uintptr_t>(d) & (W - 1))) & (W - 1);
+    if (head > n) head = n;
+    if (lane < head) d[lane] = s[lane];
+    d += head;
+    s += head;
+    n -= head;
+  }
+  const int64_t nv = n / W;
+  const V* sv = reinterpret_cast<const V*>(s);
+  V* dv = reinterpret_cast<V*>(d);
+  int64_t i = lane;
+  constexpr int kUnroll = 8;
+  for (; i + (kUnroll - 1) * 32 < nv; i += kUnroll * 32) {
+    V t[kUnroll];
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) t[u] = ld_stream<V>(sv + i + u * 32);
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) st_stream<V>(dv + i + u * 32, t[u]);
+  }
+  for (; i < nv; i += 32) st_stream<V>(dv + i, ld_stream<V>(sv + i));
+  if (W > 1) {
+    const int64_t done = nv * W;
+    const int64_t tail = n - done;
+    if (lane < tail) d[done + lane] = s[done + lane];
+  }
+}
+
+__device__ __forceinline__ void warp_copy(char* d, const char* s, int64_t n, int lane) {
+  const uintptr_t diff = reinterpret_cast<uintptr_t>(d) - reinterpret_cast<uintptr_t>(s);
+  if ((diff & 15) == 0) warp_copy_vec<uint4>(d, s, n, lane);
+  else if ((diff & 7) == 0) warp_copy_vec<uint2>(d, s, n, lane);
+  else if ((diff & 3) == 0) warp_copy_vec<uint32_t>(d, s, n, lane);
+  else if ((diff & 1) == 0) warp_copy_vec<uint16_t>(d, s, n, lane);
+  else warp_copy_vec<uint8_t>(d, s, n, lane);
+}
+
+// kSlice: flat -> packed (slice_intervals); otherwise packed -> flat (set_intervals)
+template <bool kSlice>
+__global__ void __launch_bounds__(kCopyThreads)
+interval_copy_kernel(const char* __restrict__ flat_in, char* __restrict__ flat_out,
+                     const char* __restrict__ packed_in, char* __restrict__ packed_out,
+                     const int64_t* __restrict__ iv, int64_t n, int64_t elem_size,
+                     const int64_t* __restrict__ ws, int64_t chunk_bytes) {
+  const int64_t* status = ws;
+  const int64_t* off = ws + 2;
+  if (status[0] != 0) return;   // invalid table: touch nothing (status stays readable by the host)
+  const int lane = threadIdx.x & 31;
+  const int64_t total = off[n];
+  const int64_t gwarp = int64_t(blockIdx.x) * kCopyWarps + (threadIdx.x >> 5);
+  int64_t pos = gwarp * chunk_bytes;
+  if (pos >= total) return;
+  int64_t end = pos + chunk_bytes;
+  if (end > total) end = total;
+  // last interval whose packed offset is <= pos (skips empty intervals sharing the offset)
+  int64_t lo = 0, hi = n;          // first k with off[k] > pos, in [1, n]
+  while (lo < hi) {
+    const int64_t mid = (lo + hi) >> 1;
+    if (off[mid] > pos) hi = mid; else lo = mid + 1;
+  }
+  int64_t k = lo - 1;
+  int64_t k_off = off[k];
+  int64_t k_end = off[k + 1];
+  while (pos < end) {
+    const int64_t piece_end = k_end < end ? k_end : end;
+    const int64_t fpos = iv[2 * k] * elem_size + (pos - k_off);
+    if (kSlice) warp_copy(packed_out + pos, flat_in + fpos, piece_end - pos, lane);
+    else warp_copy(flat_out + fpos, packed_in + pos, piece_end - pos, lane);
+    pos = piece_end;
+    while (pos == k_end && k + 1 < n) {
+      ++k;
+      k_off = k_end;
+      k_end = off[k + 1];
+    }
+  }
+}
+
+}  // namespace
+
+int64_t interval_workspace_bytes(int64_t n) { return (n + 3) * int64_t(sizeof(int64_t)); }
+
+int launch_interval_copy(bool slice, const void* flat_in, void* flat_out, const void* packed_in,
+                         void* packed_out, const int64_t* intervals, int64_t n, int64_t elem_size,
+                         int64_t flat_numel, int64_t packed_numel, void* workspace,
+                         cudaStream_t stream) {
+  int64_t* ws = reinterpret_cast<int64_t*>(workspace);
+  interval_scan_kernel<<<1, kScanThreads, 0, stream>>>(intervals, n, elem_size, flat_numel,
+                                                       packed_numel, ws);
+  int rc = check_launch("interval_scan");
+  if (rc) return rc;
+  const int64_t total = packed_numel * elem_size;
+  if (total == 0 || n == 0) return kOk;
+  // equal contiguous chunks of packed bytes, one per warp; >= 4 KB each, 16 B granular
+  const int64_t target_warps = int64_t(num_sms()) * 8 * kCopyWarps;
+  int64_t chunk = (total + target_warps - 1) / target_warps;
+  if (chunk < 4096) chunk = 4096;
+  chunk = (chunk + 15) & ~int64_t(15);
+  const int64_t nwarps = (total + chunk - 1) / chunk;
+  const unsigned int grid = static_cast<unsigned int>((nwarps + kCopyWarps - 1) / kCopyWarps);
+  if (slice)
+    interval_copy_kernel<true><<<grid, kCopyThreads, 0, stream>>>(
+        reinterpret_cast<const char*>(flat_in), nullptr, nullptr, reinterpret_cast<char*>(packed_out),
+        intervals, n, elem_size, ws, chunk);
+  else
+    interval_copy_kernel<false><<<grid, kCopyThreads, 0, stream>>>(
+        nullptr, reinterpret_cast<char*>(flat_out), reinterpret_cast<const char*>(packed_in), nullptr,
+        intervals, n, elem_size, ws, chunk);
+  return check_launch("interval_copy");
+}
+
+}  // namespace ab

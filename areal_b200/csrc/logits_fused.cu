@@ -1,0 +1,641 @@
+// Fused token log-prob / entropy / (PPO loss) forward and dlogits backward over [T, V] logits.
+//
+// Replaces (reference, relative to its root):
+//   areal/utils/functional.py:20-127   gather_logprobs / gather_logprobs_entropy (+ autograd backward)
+//   areal/engine/ppo/actor.py:375-376  logits.min(-1) / logits.max(-1) re-reads
+//   areal/utils/mcore/functional.py:8-52 and Megatron vocab_parallel_cross_entropy (per-shard partials)
+//   areal/utils/functional.py:171-235  ppo_actor_loss_fn, when the fused epilogue is requested
+//
+// Design (B200): one streaming pass per row with an online softmax.  Persistent CTAs (grid =
+// #SM x resident CTAs) walk rows; a single producer thread stages the row in 16 KB pieces with
+// TMA bulk copies (cp.async.bulk -> UBLKCP) into a shared-memory ring guarded by full/empty
+// mbarriers; 8 consumer warps read the ring with 128-bit LDS, keep (max, sum e, sum e*x, min) in
+// registers and reduce once per row.  No tensor cores: the pass is HBM-bound (2 B/element in,
+// 4 B/element in+out for the backward), MUFU.EX2 is the closest secondary limit (1 per element).
+// Rows that are not 16-byte aligned / not bf16 take the generic LDG kernel at the end of the file.
+#include "common.cuh"
+#include "ppo_math.cuh"
+#include "logits_fused.h"
+
+namespace ab {
+
+namespace {
+
+constexpr int kConsumerWarps = 8;
+constexpr int kConsumers = kConsumerWarps * 32;      // 256
+constexpr int kThreads = kConsumers + 32;            // + 1 producer warp
+constexpr int kStageBytes = 16384;                   // 8192 bf16 per stage
+constexpr int kVecPerThread = kStageBytes / 16 / kConsumers;   // 4 x 16 B per thread per stage
+constexpr int kStages = 4;
+constexpr int kCtasPerSm = 2;
+constexpr size_t kSmemBytes = size_t(kStages) * kStageBytes + 1024;
+
+struct RowState {
+  float m;   // running max of raw logits seen by this thread (-inf initially)
+  float s;   // sum 2^((x - m) * c2)
+  float u;   // sum 2^((x - m) * c2) * x
+  float mn;  // running min of raw logits
+};
+
+__device__ __forceinline__ void state_init(RowState& st) {
+  st.m = -INFINITY;
+  st.s = 0.f;
+  st.u = 0.f;
+  st.mn = INFINITY;
+}
+
+// Move the thread's reference maximum to max(st.m, cm); returns -m_new*c2 for the FFMA below.
+__device__ __forceinline__ float state_rebase(RowState& st, float cm, float c2) {
+  const float m_new = fmaxf(st.m, cm);
+  // st.m == -inf: (-inf - finite)*c2 = -inf -> alpha = 0 (s, u are 0 anyway).
+  const float alpha = (m_new == -INFINITY) ? 1.0f : ex2_approx((st.m - m_new) * c2);
+  st.s *= alpha;
+  st.u *= alpha;
+  st.m = m_new;
+  return -m_new * c2;
+}
+
+__device__ __forceinline__ uint32_t vec_max_bf16(const uint4& q) {
+  return max_bf16x2(max_bf16x2(q.x, q.y), max_bf16x2(q.z, q.w));
+}
+__device__ __forceinline__ uint32_t vec_min_bf16(const uint4& q) {
+  return min_bf16x2(min_bf16x2(q.x, q.y), min_bf16x2(q.z, q.w));
+}
+
+#define AB_ACC2(w, S, U)                         \
+  {                                              \
+    const float x0 = bf16_lo(w), x1 = bf16_hi(w);\
+    const float e0 = ex2_approx(fmaf(x0, c2, nb));\
+    const float e1 = ex2_approx(fmaf(x1, c2, nb));\
+    S##0 += e0;                                  \
+    U##0 = fmaf(e0, x0, U##0);                   \
+    S##1 += e1;                                  \
+    U##1 = fmaf(e1, x1, U##1);                   \
+  }
+
+// accumulate one 16-byte vector (8 bf16) with an already rebased reference (nb = -m*c2)
+__device__ __forceinline__ void vec_accumulate(const uint4& q, float c2, float nb, float& s0,
+                                               float& s1, float& u0, float& u1) {
+  AB_ACC2(q.x, s, u) AB_ACC2(q.y, s, u) AB_ACC2(q.z, s, u) AB_ACC2(q.w, s, u)
+}
+
+template <bool kMinMax>
+__device__ __forceinline__ void consume_full_stage(RowState& st, uint32_t sbase, int tid, float c2) {
+  uint4 q[kVecPerThread];
+#pragma unroll
+  for (int j = 0; j < kVecPerThread; ++j) q[j] = lds_v4(sbase + (tid + j * kConsumers) * 16);
+  uint32_t mx = vec_max_bf16(q[0]);
+#pragma unroll
+  for (int j = 1; j < kVecPerThread; ++j) mx = max_bf16x2(mx, vec_max_bf16(q[j]));
+  if (kMinMax) {
+    uint32_t mn = vec_min_bf16(q[0]);
+#pragma unroll
+    for (int j = 1; j < kVecPerThread; ++j) mn = min_bf16x2(mn, vec_min_bf16(q[j]));
+    st.mn = fminf(st.mn, fminf(bf16_lo(mn), bf16_hi(mn)));
+  }
+  const float nb = state_rebase(st, fmaxf(bf16_lo(mx), bf16_hi(mx)), c2);
+  float s0 = 0.f, s1 = 0.f, u0 = 0.f, u1 = 0.f;
+#pragma unroll
+  for (int j = 0; j < kVecPerThread; ++j) vec_accumulate(q[j], c2, nb, s0, s1, u0, u1);
+  st.s += s0 + s1;
+  st.u += u0 + u1;
+}
+
+template <bool kMinMax>
+__device__ __forceinline__ void consume_vec(RowState& st, const uint4& q, float c2) {
+  const uint32_t mx = vec_max_bf16(q);
+  if (kMinMax) {
+    const uint32_t mn = vec_min_bf16(q);
+    st.mn = fminf(st.mn, fminf(bf16_lo(mn), bf16_hi(mn)));
+  }
+  const float nb = state_rebase(st, fmaxf(bf16_lo(mx), bf16_hi(mx)), c2);
+  float s0 = 0.f, s1 = 0.f, u0 = 0.f, u1 = 0.f;
+  vec_accumulate(q, c2, nb, s0, s1, u0, u1);
+  st.s += s0 + s1;
+  st.u += u0 + u1;
+}
+
+// merge (m,s,u) pairs: result relative to max(m_a, m_b)
+__device__ __forceinline__ void state_merge(float& m, float& s, float& u, float m2, float s2,
+                                            float u2, float c2) {
+  const float M = fmaxf(m, m2);
+  const float a = (m == -INFINITY) ? 0.f : ex2_approx((m - M) * c2);
+  const float b = (m2 == -INFINITY) ? 0.f : ex2_approx((m2 - M) * c2);
+  s = s * a + s2 * b;
+  u = u * a + u2 * b;
+  m = M;
+}
+
+struct RowReduceSmem {
+  float m[2][kConsumerWarps], s[2][kConsumerWarps], u[2][kConsumerWarps], mn[2][kConsumerWarps];
+};
+
+// All consumer threads call; returns true on the single thread (warp 0, lane 0) that holds the row
+// totals in st.  One named barrier per row (double-buffered by `parity`).
+__device__ __forceinline__ bool row_reduce(RowState& st, RowReduceSmem* red, int parity, int warp,
+                                           int lane, float c2) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float m2 = __shfl_xor_sync(0xffffffffu, st.m, o);
+    const float s2 = __shfl_xor_sync(0xffffffffu, st.s, o);
+    const float u2 = __shfl_xor_sync(0xffffffffu, st.u, o);
+    const float n2 = __shfl_xor_sync(0xffffffffu, st.mn, o);
+    state_merge(st.m, st.s, st.u, m2, s2, u2, c2);
+    st.mn = fminf(st.mn, n2);
+  }
+  if (lane == 0) {
+    red->m[parity][warp] = st.m;
+    red->s[parity][warp] = st.s;
+    red->u[parity][warp] = st.u;
+    red->mn[parity][warp] = st.mn;
+  }
+  named_bar_sync(1, kConsumers);
+  if (warp != 0) return false;
+  const int l = lane & (kConsumerWarps - 1);
+  st.m = red->m[parity][l];
+  st.s = red->s[parity][l];
+  st.u = red->u[parity][l];
+  st.mn = red->mn[parity][l];
+#pragma unroll
+  for (int o = kConsumerWarps / 2; o > 0; o >>= 1) {
+    const float m2 = __shfl_xor_sync(0xffffffffu, st.m, o);
+    const float s2 = __shfl_xor_sync(0xffffffffu, st.s, o);
+    const float u2 = __shfl_xor_sync(0xffffffffu, st.u, o);
+    const float n2 = __shfl_xor_sync(0xffffffffu, st.mn, o);
+    state_merge(st.m, st.s, st.u, m2, s2, u2, c2);
+    st.mn = fminf(st.mn, n2);
+  }
+  return lane == 0;
+}
+
+// ---- row epilogue (one thread per row) ---------------------------------------------------------
+__device__ __forceinline__ float load_logit(const void* base, int dtype, int64_t idx) {
+  if (dtype == kBF16) return __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(base)[idx]);
+  if (dtype == kFP16) return __half2float(reinterpret_cast<const __half*>(base)[idx]);
+  return reinterpret_cast<const float*>(base)[idx];
+}
+
+struct LossAcc {
+  float sum;     // sum of masked per-token loss over this CTA's rows (fixed order)
+  float count;   // number of masked-in tokens
+};
+
+__device__ __forceinline__ void row_epilogue(const LogitsFwdParams& p, int64_t row,
+                                             const RowState& st, LossAcc& acc) {
+  const float inv_t = p.inv_temperature;
+  // label logit (one 2..4-byte gather, normally an L2 hit: the row was just streamed)
+  const int64_t lab = p.labels[row] - p.vocab_start;
+  const bool local = lab >= 0 && lab < p.V;
+  const char* rowp = reinterpret_cast<const char*>(p.logits) + row * p.row_stride_bytes;
+  const float xl = local ? load_logit(rowp, p.dtype, lab) : 0.f;
+  if (p.raw_max) p.raw_max[row] = st.m;
+  if (p.raw_min) p.raw_min[row] = st.mn;
+  if (p.mode == kModePartial) {
+    // (m, s, u, z_label) of z = x / temperature for the cross-shard combine
+    p.part_m[row] = st.m * inv_t;
+    p.part_s[row] = st.s;
+    p.part_u[row] = st.u * inv_t;
+    p.part_zl[row] = xl * inv_t;
+    return;
+  }
+  const float ln_s = lg2_approx(st.s) * kLn2;
+  const float lse = fmaf(st.m, inv_t, ln_s);                 // natural log-sum-exp of z
+  const float logp = local ? (xl - st.m) * inv_t - ln_s : __int_as_float(0x7fc00000);
+  const float ent = lse - (st.u / st.s) * inv_t;             // H = lse - E_p[z]
+  p.logp[row] = logp;
+  p.lse[row] = lse;
+  if (p.entropy) p.entropy[row] = ent;
+  if (p.mode == kModeFusedActor) {
+    const bool mask = p.loss_mask[row] != 0;
+    const float prox = p.prox ? p.prox[row] : p.old[row];
+    const ActorTokenOut o = actor_token(logp, prox, p.old[row], p.adv[row], mask, p.cfg);
+    p.coef[row] = o.coef;
+    if (p.stat_loss) p.stat_loss[row] = o.pg;
+    if (p.stat_ratio) p.stat_ratio[row] = o.ratio;
+    if (p.stat_kl) p.stat_kl[row] = o.kl;
+    if (p.clip_mask) p.clip_mask[row] = o.clip;
+    if (p.dual_clip_mask) p.dual_clip_mask[row] = o.dual;
+    if (p.behave_w) p.behave_w[row] = o.w;
+    if (p.behave_kl) p.behave_kl[row] = o.bk;
+    if (p.behave_mask) p.behave_mask[row] = o.bmask;
+    if (mask) {
+      acc.sum += o.pg;
+      acc.count += 1.f;
+    }
+  }
+}
+
+// Fixed-order cross-CTA reduction of (loss sum, count): every CTA stores its partial, takes a
+// ticket, and the last one sums the partials in index order (deterministic) and resets the ticket.
+__device__ __forceinline__ void loss_finalize(const LogitsFwdParams& p, const LossAcc& acc) {
+  float2* partials = reinterpret_cast<float2*>(reinterpret_cast<char*>(p.workspace) + 16);
+  unsigned int* ticket = reinterpret_cast<unsigned int*>(p.workspace);
+  partials[blockIdx.x] = make_float2(acc.sum, acc.count);
+  __threadfence();
+  const unsigned int t = atomicAdd(ticket, 1u);
+  if (t == gridDim.x - 1) {
+    __threadfence();
+    double sum = 0.0, cnt = 0.0;
+    for (unsigned int i = 0; i < gridDim.x; ++i) {
+      const volatile float* v = reinterpret_cast<const volatile float*>(&partials[i]);
+      sum += v[0];
+      cnt += v[1];
+    }
+    const double denom = cnt > 0.0 ? cnt : 1.0;               // count_nonzero() or 1, functional.py:190
+    p.loss_out[0] = static_cast<float>(sum / denom);
+    p.inv_count_out[0] = static_cast<float>(1.0 / denom);
+    *ticket = 0u;
+  }
+}
+
+// ---- TMA-staged forward ------------------------------------------------------------------------
+template <bool kMinMax>
+__global__ void __launch_bounds__(kThreads, kCtasPerSm)
+logits_fwd_tma_kernel(const LogitsFwdParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t full_bar[kStages];
+  __shared__ __align__(8) uint64_t empty_bar[kStages];
+  __shared__ RowReduceSmem red;
+
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5, lane = tid & 31;
+  const uint32_t ring = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const int64_t row_bytes = p.V * 2;
+  const int nchunk = static_cast<int>((row_bytes + kStageBytes - 1) / kStageBytes);
+  const uint32_t tail_bytes = static_cast<uint32_t>(row_bytes - int64_t(nchunk - 1) * kStageBytes);
+
+  if (tid == 0) {
+    for (int i = 0; i < kStages; ++i) {
+      mbar_init(smem_u32(&full_bar[i]), 1);
+      mbar_init(smem_u32(&empty_bar[i]), kConsumerWarps);
+    }
+    mbar_fence_init();
+  }
+  __syncthreads();
+
+  if (warp == kConsumerWarps) {
+    // ===== producer: one elected lane issues the bulk copies =====
+    if (lane == 0) {
+      const uint64_t pol = policy_evict_first();
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int64_t row = blockIdx.x; row < p.T; row += gridDim.x) {
+        const char* src = reinterpret_cast<const char*>(p.logits) + row * p.row_stride_bytes;
+        for (int c = 0; c < nchunk; ++c) {
+          mbar_wait(smem_u32(&empty_bar[stage]), phase ^ 1u);
+          const uint32_t bytes = (c == nchunk - 1) ? tail_bytes : uint32_t(kStageBytes);
+          const uint32_t fb = smem_u32(&full_bar[stage]);
+          mbar_arrive_expect_tx(fb, bytes);
+          tma_load_1d(ring + stage * kStageBytes, src + int64_t(c) * kStageBytes, bytes, fb, pol);
+          if (++stage == kStages) {
+            stage = 0;
+            phase ^= 1u;
+          }
+        }
+      }
+    }
+    return;
+  }
+
+  // ===== consumers =====
+  const float c2 = p.inv_temperature * kLog2e;
+  int stage = 0;
+  uint32_t phase = 0;
+  int parity = 0;
+  LossAcc acc = {0.f, 0.f};
+  for (int64_t row = blockIdx.x; row < p.T; row += gridDim.x) {
+    RowState st;
+    state_init(st);
+    for (int c = 0; c < nchunk; ++c) {
+      mbar_wait(smem_u32(&full_bar[stage]), phase);
+      const uint32_t sbase = ring + stage * kStageBytes;
+      if (c != nchunk - 1 || tail_bytes == kStageBytes) {
+        consume_full_stage<kMinMax>(st, sbase, tid, c2);
+      } else {
+        const int nvec = tail_bytes >> 4;
+#pragma unroll
+        for (int j = 0; j < kVecPerThread; ++j) {
+          const int v = tid + j * kConsumers;
+          if (v < nvec) consume_vec<kMinMax>(st, lds_v4(sbase + v * 16), c2);
+        }
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(smem_u32(&empty_bar[stage]));
+      if (++stage == kStages) {
+        stage = 0;
+        phase ^= 1u;
+      }
+    }
+    if (row_reduce(st, &red, parity, warp, lane, c2)) row_epilogue(p, row, st, acc);
+    parity ^= 1;
+  }
+  if (p.mode == kModeFusedActor && tid == 0) loss_finalize(p, acc);
+}
+
+// ---- generic forward (any alignment, bf16 / fp16 / fp32): one CTA per row, LDG -----------------
+template <typename T>
+__device__ __forceinline__ float to_f32(T v);
+template <>
+__device__ __forceinline__ float to_f32<__nv_bfloat16>(__nv_bfloat16 v) { return __bfloat162float(v); }
+template <>
+__device__ __forceinline__ float to_f32<__half>(__half v) { return __half2float(v); }
+template <>
+__device__ __forceinline__ float to_f32<float>(float v) { return v; }
+
+template <typename T>
+__global__ void __launch_bounds__(kConsumers)
+logits_fwd_generic_kernel(const LogitsFwdParams p) {
+  __shared__ RowReduceSmem red;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const float c2 = p.inv_temperature * kLog2e;
+  int parity = 0;
+  LossAcc acc = {0.f, 0.f};
+  for (int64_t row = blockIdx.x; row < p.T; row += gridDim.x) {
+    const T* x = reinterpret_cast<const T*>(reinterpret_cast<const char*>(p.logits) +
+                                            row * p.row_stride_bytes);
+    RowState st;
+    state_init(st);
+    // 4 independent elements per iteration, one rebase per group
+    int64_t i = tid;
+    for (; i + 3 * kConsumers < p.V; i += 4 * kConsumers) {
+      const float a = to_f32<T>(x[i]), b = to_f32<T>(x[i + kConsumers]);
+      const float c = to_f32<T>(x[i + 2 * kConsumers]), d = to_f32<T>(x[i + 3 * kConsumers]);
+      st.mn = fminf(st.mn, fminf(fminf(a, b), fminf(c, d)));
+      const float nb = state_rebase(st, fmaxf(fmaxf(a, b), fmaxf(c, d)), c2);
+      const float ea = ex2_approx(fmaf(a, c2, nb)), eb = ex2_approx(fmaf(b, c2, nb));
+      const float ec = ex2_approx(fmaf(c, c2, nb)), ed = ex2_approx(fmaf(d, c2, nb));
+      st.s += (ea + eb) + (ec + ed);
+      st.u += fmaf(ea, a, eb * b) + fmaf(ec, c, ed * d);
+    }
+    for (; i < p.V; i += kConsumers) {
+      const float a = to_f32<T>(x[i]);
+      st.mn = fminf(st.mn, a);
+      const float nb = state_rebase(st, a, c2);
+      const float ea = ex2_approx(fmaf(a, c2, nb));
+      st.s += ea;
+      st.u = fmaf(ea, a, st.u);
+    }
+    if (row_reduce(st, &red, parity, warp, lane, c2)) row_epilogue(p, row, st, acc);
+    parity ^= 1;
+  }
+  if (p.mode == kModeFusedActor && tid == 0) loss_finalize(p, acc);
+}
+
+// ---- backward ----------------------------------------------------------------------------------
+// dlogits[t,v] = p_v * (k0 + k1 * x_v) (+ gl at v == label), p_v = 2^(x*c2 - lse*log2e)
+//   k0 = -(gl) - gh*(H - lse),  k1 = -gh/temp,  gl = g_logp*scale/temp,  gh = g_entropy*scale/temp
+struct RowGrad {
+  float k0, k1, gl, nl;   // nl = -lse*log2e
+  bool active;
+};
+
+__device__ __forceinline__ RowGrad row_grad(const LogitsBwdParams& p, int64_t row) {
+  RowGrad g;
+  float scale = p.inv_temperature;
+  if (p.scale0) scale *= p.scale0[0];
+  if (p.scale1) scale *= p.scale1[0];
+  const float glp = p.g_logp ? p.g_logp[row] : 0.f;
+  const float ghp = p.g_entropy ? p.g_entropy[row] : 0.f;
+  g.active = (glp != 0.f) || (ghp != 0.f);
+  const float lse = p.lse[row];
+  g.gl = glp * scale;
+  const float gh = ghp * scale;
+  const float H = p.g_entropy ? p.entropy[row] : 0.f;
+  g.k0 = -g.gl - gh * (H - lse);
+  g.k1 = -gh * p.inv_temperature;
+  g.nl = -lse * kLog2e;
+  return g;
+}
+
+__device__ __forceinline__ uint4 grad_vec(const uint4& q, const RowGrad& g, float c2, int64_t lab_off) {
+  float x[8] = {bf16_lo(q.x), bf16_hi(q.x), bf16_lo(q.y), bf16_hi(q.y),
+                bf16_lo(q.z), bf16_hi(q.z), bf16_lo(q.w), bf16_hi(q.w)};
+  float d[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const float pv = ex2_approx(fmaf(x[i], c2, g.nl));
+    d[i] = pv * fmaf(x[i], g.k1, g.k0);
+  }
+  if (lab_off >= 0 && lab_off < 8) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+      if (i == lab_off) d[i] += g.gl;
+  }
+  uint4 o;
+  o.x = pack_bf16x2(d[0], d[1]);
+  o.y = pack_bf16x2(d[2], d[3]);
+  o.z = pack_bf16x2(d[4], d[5]);
+  o.w = pack_bf16x2(d[6], d[7]);
+  return o;
+}
+
+__global__ void __launch_bounds__(kThreads, kCtasPerSm)
+logits_bwd_tma_kernel(const LogitsBwdParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t full_bar[kStages];
+  __shared__ __align__(8) uint64_t empty_bar[kStages];
+
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5, lane = tid & 31;
+  const uint32_t ring = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const int64_t row_bytes = p.V * 2;
+  const int nchunk = static_cast<int>((row_bytes + kStageBytes - 1) / kStageBytes);
+  const uint32_t tail_bytes = static_cast<uint32_t>(row_bytes - int64_t(nchunk - 1) * kStageBytes);
+
+  if (tid == 0) {
+    for (int i = 0; i < kStages; ++i) {
+      mbar_init(smem_u32(&full_bar[i]), 1);
+      mbar_init(smem_u32(&empty_bar[i]), kConsumerWarps);
+    }
+    mbar_fence_init();
+  }
+  __syncthreads();
+
+  if (warp == kConsumerWarps) {
+    if (lane == 0) {
+      const uint64_t pol = policy_evict_first();
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int64_t row = blockIdx.x; row < p.T; row += gridDim.x) {
+        const float glp = p.g_logp ? p.g_logp[row] : 0.f;
+        const float ghp = p.g_entropy ? p.g_entropy[row] : 0.f;
+        if (glp == 0.f && ghp == 0.f) continue;        // zero row: nothing to read
+        const char* src = reinterpret_cast<const char*>(p.logits) + row * p.row_stride_bytes;
+        for (int c = 0; c < nchunk; ++c) {
+          mbar_wait(smem_u32(&empty_bar[stage]), phase ^ 1u);
+          const uint32_t bytes = (c == nchunk - 1) ? tail_bytes : uint32_t(kStageBytes);
+          const uint32_t fb = smem_u32(&full_bar[stage]);
+          mbar_arrive_expect_tx(fb, bytes);
+          tma_load_1d(ring + stage * kStageBytes, src + int64_t(c) * kStageBytes, bytes, fb, pol);
+          if (++stage == kStages) {
+            stage = 0;
+            phase ^= 1u;
+          }
+        }
+      }
+    }
+    return;
+  }
+
+  const float c2 = p.inv_temperature * kLog2e;
+  int stage = 0;
+  uint32_t phase = 0;
+  for (int64_t row = blockIdx.x; row < p.T; row += gridDim.x) {
+    const RowGrad g = row_grad(p, row);
+    char* dst = reinterpret_cast<char*>(p.dlogits) + row * p.d_row_stride_bytes;
+    if (!g.active) {
+      const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+      for (int64_t off = int64_t(tid) * 16; off < row_bytes; off += int64_t(kConsumers) * 16)
+        stg_stream_v4(dst + off, z);
+      continue;
+    }
+    const int64_t lab = p.labels[row] - p.vocab_start;
+    for (int c = 0; c < nchunk; ++c) {
+      mbar_wait(smem_u32(&full_bar[stage]), phase);
+      const uint32_t sbase = ring + stage * kStageBytes;
+      const int nvec = ((c == nchunk - 1) ? tail_bytes : uint32_t(kStageBytes)) >> 4;
+      uint4 q[kVecPerThread];
+#pragma unroll
+      for (int j = 0; j < kVecPerThread; ++j) {
+        const int v = tid + j * kConsumers;
+        if (v < nvec) q[j] = lds_v4(sbase + v * 16);
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(smem_u32(&empty_bar[stage]));   // smem already in registers
+#pragma unroll
+      for (int j = 0; j < kVecPerThread; ++j) {
+        const int v = tid + j * kConsumers;
+        if (v < nvec) {
+          const int64_t e0 = int64_t(c) * (kStageBytes / 2) + int64_t(v) * 8;
+          stg_stream_v4(dst + e0 * 2, grad_vec(q[j], g, c2, lab - e0));
+        }
+      }
+      if (++stage == kStages) {
+        stage = 0;
+        phase ^= 1u;
+      }
+    }
+  }
+}
+
+template <typename T>
+__device__ __forceinline__ T from_f32(float v);
+template <>
+__device__ __forceinline__ __nv_bfloat16 from_f32<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
+template <>
+__device__ __forceinline__ __half from_f32<__half>(float v) { return __float2half_rn(v); }
+template <>
+__device__ __forceinline__ float from_f32<float>(float v) { return v; }
+
+template <typename T>
+__global__ void __launch_bounds__(kConsumers)
+logits_bwd_generic_kernel(const LogitsBwdParams p) {
+  const int tid = threadIdx.x;
+  const float c2 = p.inv_temperature * kLog2e;
+  for (int64_t row = blockIdx.x; row < p.T; row += gridDim.x) {
+    const RowGrad g = row_grad(p, row);
+    const T* x = reinterpret_cast<const T*>(reinterpret_cast<const char*>(p.logits) +
+                                            row * p.row_stride_bytes);
+    T* d = reinterpret_cast<T*>(reinterpret_cast<char*>(p.dlogits) + row * p.d_row_stride_bytes);
+    const int64_t lab = p.labels[row] - p.vocab_start;
+    if (!g.active) {
+      for (int64_t i = tid; i < p.V; i += kConsumers) d[i] = from_f32<T>(0.f);
+      continue;
+    }
+    for (int64_t i = tid; i < p.V; i += kConsumers) {
+      const float xv = to_f32<T>(x[i]);
+      const float pv = ex2_approx(fmaf(xv, c2, g.nl));
+      float dv = pv * fmaf(xv, g.k1, g.k0);
+      if (i == lab) dv += g.gl;
+      d[i] = from_f32<T>(dv);
+    }
+  }
+}
+
+// ---- cross-shard combine (vocab-sharded path) ----------------------------------------------------
+__global__ void vocab_combine_kernel(const float* __restrict__ parts, int R, int64_t T,
+                                     float* __restrict__ logp, float* __restrict__ entropy,
+                                     float* __restrict__ lse_out) {
+  // parts layout: [R][4][T] = (m, s, u, z_label) per shard, z-units (already divided by temperature)
+  const int64_t t = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+  if (t >= T) return;
+  float M = -INFINITY;
+  for (int r = 0; r < R; ++r) M = fmaxf(M, parts[(int64_t(r) * 4 + 0) * T + t]);
+  float S = 0.f, U = 0.f, ZL = 0.f;
+  for (int r = 0; r < R; ++r) {
+    const float m = parts[(int64_t(r) * 4 + 0) * T + t];
+    const float a = (m == -INFINITY) ? 0.f : expf(m - M);
+    S = fmaf(parts[(int64_t(r) * 4 + 1) * T + t], a, S);
+    U = fmaf(parts[(int64_t(r) * 4 + 2) * T + t], a, U);
+    ZL += parts[(int64_t(r) * 4 + 3) * T + t];
+  }
+  const float lse = M + logf(S);
+  logp[t] = ZL - lse;
+  if (entropy) entropy[t] = lse - U / S;
+  lse_out[t] = lse;
+}
+
+bool tma_ok(const void* ptr, int dtype, int64_t V, int64_t row_stride_bytes) {
+  return dtype == kBF16 && (reinterpret_cast<uintptr_t>(ptr) & 15) == 0 && (V % 8) == 0 &&
+         (row_stride_bytes % 16) == 0;
+}
+
+int grid_for(int64_t T, int per_sm) {
+  const int64_t g = int64_t(num_sms()) * per_sm;
+  return static_cast<int>(T < g ? T : g);
+}
+
+}  // namespace
+
+int64_t logits_loss_workspace_bytes() { return 16 + 8 * int64_t(num_sms()) * 8; }
+
+int launch_logits_fwd(const LogitsFwdParams& p, cudaStream_t stream) {
+  if (p.T == 0) return kOk;
+  const bool minmax = p.raw_min != nullptr;
+  if (tma_ok(p.logits, p.dtype, p.V, p.row_stride_bytes)) {
+    static bool attr_set[2] = {false, false};
+    auto kern = minmax ? logits_fwd_tma_kernel<true> : logits_fwd_tma_kernel<false>;
+    if (!attr_set[minmax]) {
+      AB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kSmemBytes)));
+      attr_set[minmax] = true;
+    }
+    kern<<<grid_for(p.T, kCtasPerSm), kThreads, kSmemBytes, stream>>>(p);
+  } else {
+    const int grid = grid_for(p.T, 8);
+    if (p.dtype == kBF16) logits_fwd_generic_kernel<__nv_bfloat16><<<grid, kConsumers, 0, stream>>>(p);
+    else if (p.dtype == kFP16) logits_fwd_generic_kernel<__half><<<grid, kConsumers, 0, stream>>>(p);
+    else logits_fwd_generic_kernel<float><<<grid, kConsumers, 0, stream>>>(p);
+  }
+  return check_launch("logits_fwd");
+}
+
+int launch_logits_bwd(const LogitsBwdParams& p, cudaStream_t stream) {
+  if (p.T == 0) return kOk;
+  if (tma_ok(p.logits, p.dtype, p.V, p.row_stride_bytes) &&
+      tma_ok(p.dlogits, p.dtype, p.V, p.d_row_stride_bytes)) {
+    static bool attr_set = false;
+    if (!attr_set) {
+      AB_CUDA(cudaFuncSetAttribute(logits_bwd_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   int(kSmemBytes)));
+      attr_set = true;
+    }
+    logits_bwd_tma_kernel<<<grid_for(p.T, kCtasPerSm), kThreads, kSmemBytes, stream>>>(p);
+  } else {
+    const int grid = grid_for(p.T, 8);
+    if (p.dtype == kBF16) logits_bwd_generic_kernel<__nv_bfloat16><<<grid, kConsumers, 0, stream>>>(p);
+    else if (p.dtype == kFP16) logits_bwd_generic_kernel<__half><<<grid, kConsumers, 0, stream>>>(p);
+    else logits_bwd_generic_kernel<float><<<grid, kConsumers, 0, stream>>>(p);
+  }
+  return check_launch("logits_bwd");
+}
+
+int launch_vocab_combine(const float* parts, int R, int64_t T, float* logp, float* entropy,
+                         float* lse, cudaStream_t stream) {
+  if (T == 0) return kOk;
+  const int threads = 256;
+  vocab_combine_kernel<<<static_cast<int>((T + threads - 1) / threads), threads, 0, stream>>>(
+      parts, R, T, logp, entropy, lse);
+  return check_launch("vocab_combine");
+}
+
+}  // namespace ab

@@ -1,0 +1,61 @@
+// Parameter blocks of the fused logits kernels (internal; the public C ABI is include/areal_b200.h).
+#pragma once
+#include "common.cuh"
+#include "ppo_math.cuh"
+
+namespace ab {
+
+enum LogitsMode : int { kModeStandard = 0, kModePartial = 1, kModeFusedActor = 2 };
+
+struct LogitsFwdParams {
+  const void* logits;
+  int dtype;
+  int mode;
+  int64_t T, V;
+  int64_t row_stride_bytes;
+  const int64_t* labels;
+  int64_t vocab_start;
+  float inv_temperature;
+  // standard / fused outputs
+  float* logp;
+  float* entropy;   // nullable
+  float* lse;
+  float* raw_min;   // nullable (enables the min pass)
+  float* raw_max;   // nullable
+  // partial-mode outputs
+  float *part_m, *part_s, *part_u, *part_zl;
+  // fused actor-loss epilogue
+  const float *prox, *old, *adv;
+  const uint8_t* loss_mask;
+  ActorCfg cfg;
+  float* coef;
+  float *stat_loss, *stat_ratio, *stat_kl, *behave_w, *behave_kl;
+  uint8_t *clip_mask, *dual_clip_mask, *behave_mask;
+  float *loss_out, *inv_count_out;
+  void* workspace;
+};
+
+struct LogitsBwdParams {
+  const void* logits;
+  void* dlogits;
+  int dtype;
+  int64_t T, V;
+  int64_t row_stride_bytes, d_row_stride_bytes;
+  const int64_t* labels;
+  int64_t vocab_start;
+  float inv_temperature;
+  const float* lse;
+  const float* entropy;     // required iff g_entropy
+  const float* g_logp;      // nullable
+  const float* g_entropy;   // nullable
+  const float* scale0;      // nullable device scalars multiplying both gradients
+  const float* scale1;
+};
+
+int64_t logits_loss_workspace_bytes();
+int launch_logits_fwd(const LogitsFwdParams& p, cudaStream_t stream);
+int launch_logits_bwd(const LogitsBwdParams& p, cudaStream_t stream);
+int launch_vocab_combine(const float* parts, int R, int64_t T, float* logp, float* entropy,
+                         float* lse, cudaStream_t stream);
+
+}  // namespace ab

@@ -1,0 +1,210 @@
+/* areal_b200 -- C ABI of the B200-native RL post-processing kernels (libareal_b200.so).
+ *
+ * Drop-in boundary for the reference's native extensions and functional ops on this path.  Every
+ * entry point takes plain device pointers, sizes and scalars plus a CUDA stream, launches
+ * asynchronously on that stream, never allocates and never synchronises; it returns 0 on success
+ * or a non-zero status (1 invalid argument, 2 CUDA error, 3 workspace too small, 4 unsupported)
+ * with a message available from areal_b200_last_error() (thread-local).
+ *
+ * "Reference" citations are relative to the root of JamesKrW/AReaL.
+ *
+ * Workspaces: entry points that take `workspace` need `*_workspace_bytes()` bytes of device
+ * memory that the caller ZEROES ONCE after allocation; the kernels leave it zeroed, so one
+ * workspace can be reused by successive calls on the same stream (not by concurrent calls).
+ */
+#ifndef AREAL_B200_H_
+#define AREAL_B200_H_
+
+#include <stdint.h>
+
+#if defined(__GNUC__)
+#define AREAL_B200_API __attribute__((visibility("default")))
+#else
+#define AREAL_B200_API
+#endif
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* element types of logits / dlogits */
+#define AREAL_B200_BF16 0
+#define AREAL_B200_FP16 1
+#define AREAL_B200_FP32 2
+
+AREAL_B200_API const char* areal_b200_last_error(void);
+AREAL_B200_API int areal_b200_version(void);
+
+/* ------------------------------------------------------------------------------------------ *
+ * P1  GAE
+ * ------------------------------------------------------------------------------------------ */
+
+/* Packed 1D "nolp/misalign" GAE.  Replaces `gae_1d_nolp_misalign` (csrc/cugae/gae.cu:30-60,
+ * pybind :210), `cugae.cugae1d_nolp_misalign_func` (realhf/impl/model/utils/ppo_functional.py:
+ * 359-366) and the CPU path `pygae1d_nolp_misalign` (:292-323).
+ *   rewards f32[T], values f32[T+B] (value of token t of sequence i at cu[i]+i+t), cu_seqlens
+ *   i32[B+1] (cu[0]=0, cu[B]=T), bootstrap u8/bool[B]; outputs adv, ret f32[T].
+ *   gamma, lam are taken as double and combined like the Python reference: (float)gamma and
+ *   (float)(gamma*lam).  Inputs are not modified. */
+AREAL_B200_API int64_t areal_b200_gae1d_workspace_bytes(int64_t total_tokens);
+AREAL_B200_API int areal_b200_gae1d_nolp_misalign(const float* rewards, const float* values,
+                                   const int32_t* cu_seqlens, const uint8_t* bootstrap,
+                                   int64_t total_tokens, int64_t batch_size, double gamma,
+                                   double lam, float* adv_out, float* ret_out, void* workspace,
+                                   int64_t workspace_bytes, void* stream);
+
+/* Padded [B,S] masked GAE of areal-lite.  Replaces the Python loop in
+ * `PPOActor.compute_advantages` (areal/engine/ppo/actor.py:131-152).
+ *   rewards, values, loss_mask f32[B,S] contiguous (loss_mask already rolled by -1, :110; any
+ *   non-zero counts), seq_no_eos u8/bool[B]; outputs advantages, returns f32[B,S]. */
+AREAL_B200_API int areal_b200_gae_padded_masked(const float* rewards, const float* values,
+                                 const float* loss_mask, const uint8_t* seq_no_eos, int64_t B,
+                                 int64_t S, double gamma, double lam, float* adv_out,
+                                 float* ret_out, void* stream);
+
+/* Segment-table 2D GAE.  Replaces `gae_2d_olp` AND `gae_2d_nolp` (csrc/cugae/gae.cu:91-134,
+ * 163-206, pybind :213-215): the reference's `_nolp` host wrapper launches the `_olp` kernel
+ * (:199), so both exports have olp semantics.
+ *   rewards f32[B,H], values f32[B,H+1], done u8[B,H+1], done_y_indices i32[num_dones] (ascending
+ *   per row), cu_num_dones i32[B+1], is_truncate u8[num_dones]; outputs f32[B,H]. */
+AREAL_B200_API int areal_b200_gae2d_olp(const float* rewards, const float* values, const uint8_t* done,
+                         const int32_t* done_y_indices, const int32_t* cu_num_dones,
+                         const uint8_t* is_truncate, int64_t B, int64_t H, int64_t num_dones,
+                         double gamma, double lam, float* adv_out, float* ret_out, void* stream);
+
+/* ------------------------------------------------------------------------------------------ *
+ * P2  log-prob / entropy from [T,V] logits, and the dlogits backward
+ * ------------------------------------------------------------------------------------------ */
+
+/* Forward.  Replaces `gather_logprobs` / `gather_logprobs_entropy`
+ * (areal/utils/functional.py:43-127; inner :20-34) and the two extra [T,V] reads
+ * `logits.min(-1)`, `logits.max(-1)` (areal/engine/ppo/actor.py:375-376).
+ *   logits [T,V] of `dtype`, unit stride in V, `row_stride` ELEMENTS between rows; labels i64[T];
+ *   z = float(logits)/temperature.  Outputs f32[T]: logp (required), lse = logsumexp(z)
+ *   (required; saved for the backward), entropy / raw_min / raw_max (each nullable).
+ *   A label outside [0,V) yields logp = NaN for that row (the reference's gather would raise). */
+AREAL_B200_API int areal_b200_logits_fwd(const void* logits, int dtype, int64_t T, int64_t V, int64_t row_stride,
+                          const int64_t* labels, double temperature, float* logp, float* entropy,
+                          float* lse, float* raw_min, float* raw_max, void* stream);
+
+/* Backward: dlogits = d/dlogits of sum_t g_logp[t]*logp[t] + g_entropy[t]*entropy[t], times the
+ * optional device scalars *scale0 * *scale1, rounded once to `dtype`.  Replaces autograd through
+ * the reference's log_softmax path (functional.py:20-34) and `_VocabParallelEntropy.backward`
+ * (areal/utils/mcore/functional.py:41-52).  g_entropy nullable (then entropy may be null); rows
+ * whose gradients are all zero are written as zeros without reading the logits. */
+AREAL_B200_API int areal_b200_logits_bwd(const void* logits, int dtype, int64_t T, int64_t V, int64_t row_stride,
+                          const int64_t* labels, int64_t vocab_start, double temperature,
+                          const float* lse, const float* entropy, const float* g_logp,
+                          const float* g_entropy, const float* scale0, const float* scale1,
+                          void* dlogits, int64_t d_row_stride, void* stream);
+
+/* Vocab-sharded forward, per shard: the (m, s, u, z_label) partials that the reference obtains
+ * with three all-reduces each in `_VocabParallelEntropy.forward`
+ * (areal/utils/mcore/functional.py:15-34) and Megatron's `vocab_parallel_cross_entropy`
+ * (call sites areal/utils/functional.py:55-57, 95-97; vendored copy
+ * realhf/impl/model/parallelism/tensor_parallel/modules.py:1060-1118).
+ *   parts f32[4,T] = rows (max z, sum exp(z-max), sum exp(z-max)*z, z_label or 0); labels are
+ *   GLOBAL vocabulary ids, this shard holds [vocab_start, vocab_start+V). */
+AREAL_B200_API int areal_b200_logits_partial_fwd(const void* logits, int dtype, int64_t T, int64_t V,
+                                  int64_t row_stride, const int64_t* labels, int64_t vocab_start,
+                                  double temperature, float* parts, float* raw_min, float* raw_max,
+                                  void* stream);
+
+/* Combine R shards' partials (parts f32[R,4,T], e.g. the result of one all-gather) into logp,
+ * entropy (nullable) and the global lse, f32[T] each. */
+AREAL_B200_API int areal_b200_vocab_combine(const float* parts, int64_t R, int64_t T, float* logp, float* entropy,
+                             float* lse, void* stream);
+
+/* ------------------------------------------------------------------------------------------ *
+ * P3  PPO losses
+ * ------------------------------------------------------------------------------------------ */
+
+/* Shared by actor / critic / fused entry points: 16 + 8 * (#SM * 8) bytes. */
+AREAL_B200_API int64_t areal_b200_loss_workspace_bytes(void);
+
+/* Decoupled PPO actor loss.  Replaces `ppo_actor_loss_fn` (areal/utils/functional.py:171-235) and
+ * the legacy `actor_loss_fn` (realhf/impl/model/utils/ppo_functional.py:51-149; pass prox = NULL
+ * for its proximal_logprobs=None case, loss_mask = NULL for loss_mask=None).
+ *   eps_clip_higher, c_clip, behav_imp_weight_cap: NaN means "None".
+ *   loss_out[1] = sum(mask ? L : 0) / max(count(mask), 1); inv_count_out[1] = 1/max(count,1);
+ *   coef[T] = count * dloss/dlogprobs (closed form incl. torch.max / torch.min tie splitting), so
+ *   grad_logprobs = upstream * inv_count * coef.  The eight logging vectors are nullable. */
+AREAL_B200_API int areal_b200_ppo_actor_loss(const float* logprobs, const float* proximal_logprobs,
+                              const float* old_logprobs, const float* advantages,
+                              const uint8_t* loss_mask, int64_t T, double eps_clip,
+                              double eps_clip_higher, double c_clip, double behav_imp_weight_cap,
+                              float* loss_out, float* inv_count_out, float* coef, float* stat_loss,
+                              float* stat_importance_weight, float* stat_approx_kl,
+                              uint8_t* stat_clip_mask, uint8_t* stat_dual_clip_mask,
+                              float* stat_behave_imp_weight, float* stat_behave_approx_kl,
+                              uint8_t* stat_behave_mask, void* workspace, int64_t workspace_bytes,
+                              void* stream);
+
+/* PPO critic loss.  Replaces `ppo_critic_loss_fn` (areal/utils/functional.py:247-311) and legacy
+ * `critic_loss_fn` (realhf/impl/model/utils/ppo_functional.py:161-225).  loss_mask nullable (plain
+ * mean).  No `or 1` on the count, like the reference (:306): an all-false mask gives NaN. */
+AREAL_B200_API int areal_b200_ppo_critic_loss(const float* value, const float* old_value,
+                               const float* target_value, const uint8_t* loss_mask, int64_t T,
+                               double value_eps_clip, int use_huber, float* loss_out,
+                               float* inv_count_out, float* coef, float* stat_loss,
+                               uint8_t* stat_clip_mask, void* workspace, int64_t workspace_bytes,
+                               void* stream);
+
+/* out[t] = coef[t] * (*scale0) * (*scale1)  (scale1 nullable): grad of a masked-mean loss from its
+ * saved coefficient, the saved 1/count and the upstream scalar, all on the device. */
+AREAL_B200_API int areal_b200_scale_by_scalars(const float* coef, const float* scale0, const float* scale1,
+                                int64_t T, float* out, void* stream);
+
+/* Fused GRPO/PPO actor step: ONE pass over the logits producing everything `grpo_loss_fn`
+ * (areal/engine/ppo/actor.py:313-391) computes from them: logp, entropy, lse, raw min/max, the
+ * actor loss, its logging vectors and the gradient coefficient.  Same argument meaning as
+ * areal_b200_logits_fwd + areal_b200_ppo_actor_loss.  Backward = areal_b200_logits_bwd with
+ * g_logp = coef, scale0 = inv_count, scale1 = upstream. */
+AREAL_B200_API int areal_b200_fused_actor_fwd(const void* logits, int dtype, int64_t T, int64_t V,
+                               int64_t row_stride, const int64_t* labels, double temperature,
+                               const float* proximal_logprobs, const float* old_logprobs,
+                               const float* advantages, const uint8_t* loss_mask, double eps_clip,
+                               double eps_clip_higher, double c_clip, double behav_imp_weight_cap,
+                               float* logp, float* entropy, float* lse, float* raw_min,
+                               float* raw_max, float* loss_out, float* inv_count_out, float* coef,
+                               float* stat_loss, float* stat_importance_weight,
+                               float* stat_approx_kl, uint8_t* stat_clip_mask,
+                               uint8_t* stat_dual_clip_mask, float* stat_behave_imp_weight,
+                               float* stat_behave_approx_kl, uint8_t* stat_behave_mask,
+                               void* workspace, int64_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------ *
+ * P4  interval ops (parameter reallocation)
+ * ------------------------------------------------------------------------------------------ */
+
+/* (n_intervals + 3) * 8 bytes; need not be zeroed.  After the call, workspace[0] (int64) holds 0
+ * (ok), 1 (an interval is negative / reversed / beyond the flat buffer) or 2 (sum of sizes !=
+ * packed_numel); on a non-zero status no byte of the destination is written. */
+AREAL_B200_API int64_t areal_b200_interval_workspace_bytes(int64_t n_intervals);
+
+/* packed[cumsum offsets] = flat[s:e) for each interval in the given order.  Replaces
+ * `slice_intervals_{fp32,fp16,bf16}` (csrc/interval_op/interval_op.cu:68-104, pybind :110-113) and
+ * `_slice_intervals_py` (realhf/impl/model/nn/flatten_param.py:65-75).  intervals i64[n,2] on the
+ * device; elem_size in bytes (1, 2, 4 or 8); bit-exact copy for any alignment. */
+AREAL_B200_API int areal_b200_slice_intervals(const void* flat, int64_t flat_numel, void* packed,
+                               int64_t packed_numel, const int64_t* intervals,
+                               int64_t n_intervals, int64_t elem_size, void* workspace,
+                               int64_t workspace_bytes, void* stream);
+
+/* flat[s:e) = packed[cumsum offsets] (in place on `flat`).  Replaces
+ * `set_intervals_{fp32,fp16,bf16}` (interval_op.cu:28-66, pybind :106-109) and `_set_intervals_py`
+ * (flatten_param.py:78-90). */
+AREAL_B200_API int areal_b200_set_intervals(const void* packed, int64_t packed_numel, void* flat,
+                             int64_t flat_numel, const int64_t* intervals, int64_t n_intervals,
+                             int64_t elem_size, void* workspace, int64_t workspace_bytes,
+                             void* stream);
+
+/* Host-side.  Replaces `merge_intervals` (csrc/interval_op/interval_op.cpp:4-25): merges (a,b),(b,c)
+ * -> (a,c) for neighbours in input order.  in/out are u64[n,2] host arrays (out capacity n);
+ * returns the number of merged intervals, or -1 on a null pointer. */
+AREAL_B200_API int64_t areal_b200_merge_intervals(const uint64_t* intervals, int64_t n, uint64_t* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* AREAL_B200_H_ */
