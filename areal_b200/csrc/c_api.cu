@@ -180,27 +180,30 @@ static void fill_fwd_common(LogitsFwdParams* p, const void* logits, int dtype, i
   p->inv_temperature = static_cast<float>(1.0 / temperature);
 }
 
-AREAL_B200_API int areal_b200_logits_fwd(const void* logits, int dtype, int64_t T, int64_t V, int64_t row_stride,
-                          const int64_t* labels, double temperature, float* logp, float* entropy,
-                          float* lse, float* raw_min, float* raw_max, void* stream) {
+AREAL_B200_API int areal_b200_logits_fwd(const void* logits, int dtype, int64_t T, int64_t V,
+                                         int64_t row_stride, const int64_t* labels,
+                                         double temperature, float* logp, float* entropy,
+                                         float* row_max, float* ln_sumexp, float* raw_min,
+                                         void* stream) {
   int rc = check_logits(logits, dtype, T, V, row_stride, labels, temperature);
   if (rc) return rc;
-  AB_REQUIRE(T == 0 || (logp && lse), "logp and lse outputs are required");
+  AB_REQUIRE(T == 0 || (logp && row_max && ln_sumexp), "logp, row_max and ln_sumexp outputs are required");
   LogitsFwdParams p;
   fill_fwd_common(&p, logits, dtype, T, V, row_stride, labels, 0, temperature);
   p.mode = kModeStandard;
   p.logp = logp;
   p.entropy = entropy;
-  p.lse = lse;
+  p.row_max = row_max;
+  p.ln_s = ln_sumexp;
   p.raw_min = raw_min;
-  p.raw_max = raw_max;
   return launch_logits_fwd(p, static_cast<cudaStream_t>(stream));
 }
 
-AREAL_B200_API int areal_b200_logits_partial_fwd(const void* logits, int dtype, int64_t T, int64_t V,
-                                  int64_t row_stride, const int64_t* labels, int64_t vocab_start,
-                                  double temperature, float* parts, float* raw_min, float* raw_max,
-                                  void* stream) {
+AREAL_B200_API int areal_b200_logits_partial_fwd(const void* logits, int dtype, int64_t T,
+                                                 int64_t V, int64_t row_stride,
+                                                 const int64_t* labels, int64_t vocab_start,
+                                                 double temperature, float* parts, float* raw_min,
+                                                 void* stream) {
   int rc = check_logits(logits, dtype, T, V, row_stride, labels, temperature);
   if (rc) return rc;
   AB_REQUIRE(T == 0 || parts, "parts output is required");
@@ -209,29 +212,33 @@ AREAL_B200_API int areal_b200_logits_partial_fwd(const void* logits, int dtype, 
   p.mode = kModePartial;
   p.part_m = parts;
   p.part_s = parts + T;
-  p.part_u = parts + 2 * T;
-  p.part_zl = parts + 3 * T;
+  p.part_w = parts + 2 * T;
+  p.part_xl = parts + 3 * T;
   p.raw_min = raw_min;
-  p.raw_max = raw_max;
   return launch_logits_fwd(p, static_cast<cudaStream_t>(stream));
 }
 
-AREAL_B200_API int areal_b200_vocab_combine(const float* parts, int64_t R, int64_t T, float* logp, float* entropy,
-                             float* lse, void* stream) {
+AREAL_B200_API int areal_b200_vocab_combine(const float* parts, int64_t R, int64_t T,
+                                            double temperature, float* logp, float* entropy,
+                                            float* row_max, float* ln_sumexp, void* stream) {
   AB_REQUIRE(R > 0 && R <= 4096 && T >= 0, "bad R / T");
-  AB_REQUIRE(T == 0 || (parts && logp && lse), "null pointer");
-  return launch_vocab_combine(parts, static_cast<int>(R), T, logp, entropy, lse,
-                              static_cast<cudaStream_t>(stream));
+  AB_REQUIRE(temperature > 0.0 && isfinite(temperature), "temperature must be finite and > 0");
+  AB_REQUIRE(T == 0 || (parts && logp && row_max && ln_sumexp), "null pointer");
+  return launch_vocab_combine(parts, static_cast<int>(R), T, static_cast<float>(1.0 / temperature),
+                              logp, entropy, row_max, ln_sumexp, static_cast<cudaStream_t>(stream));
 }
 
-AREAL_B200_API int areal_b200_logits_bwd(const void* logits, int dtype, int64_t T, int64_t V, int64_t row_stride,
-                          const int64_t* labels, int64_t vocab_start, double temperature,
-                          const float* lse, const float* entropy, const float* g_logp,
-                          const float* g_entropy, const float* scale0, const float* scale1,
-                          void* dlogits, int64_t d_row_stride, void* stream) {
+AREAL_B200_API int areal_b200_logits_bwd(const void* logits, int dtype, int64_t T, int64_t V,
+                                         int64_t row_stride, const int64_t* labels,
+                                         int64_t vocab_start, double temperature,
+                                         const float* row_max, const float* ln_sumexp,
+                                         const float* entropy, const float* g_logp,
+                                         const float* g_entropy, const float* scale0,
+                                         const float* scale1, void* dlogits, int64_t d_row_stride,
+                                         void* stream) {
   int rc = check_logits(logits, dtype, T, V, row_stride, labels, temperature);
   if (rc) return rc;
-  AB_REQUIRE(T == 0 || (lse && dlogits), "lse and dlogits are required");
+  AB_REQUIRE(T == 0 || (row_max && ln_sumexp && dlogits), "row_max, ln_sumexp and dlogits are required");
   AB_REQUIRE(d_row_stride >= V, "d_row_stride (%lld) < V", (long long)d_row_stride);
   AB_REQUIRE(!g_entropy || entropy, "g_entropy needs the forward's entropy");
   LogitsBwdParams p;
@@ -246,7 +253,8 @@ AREAL_B200_API int areal_b200_logits_bwd(const void* logits, int dtype, int64_t 
   p.labels = labels;
   p.vocab_start = vocab_start;
   p.inv_temperature = static_cast<float>(1.0 / temperature);
-  p.lse = lse;
+  p.row_max = row_max;
+  p.ln_s = ln_sumexp;
   p.entropy = entropy;
   p.g_logp = g_logp;
   p.g_entropy = g_entropy;
@@ -353,8 +361,8 @@ AREAL_B200_API int areal_b200_fused_actor_fwd(const void* logits, int dtype, int
                                const float* proximal_logprobs, const float* old_logprobs,
                                const float* advantages, const uint8_t* loss_mask, double eps_clip,
                                double eps_clip_higher, double c_clip, double behav_imp_weight_cap,
-                               float* logp, float* entropy, float* lse, float* raw_min,
-                               float* raw_max, float* loss_out, float* inv_count_out, float* coef,
+                               float* logp, float* entropy, float* row_max, float* ln_sumexp,
+                               float* raw_min, float* loss_out, float* inv_count_out, float* coef,
                                float* stat_loss, float* stat_importance_weight,
                                float* stat_approx_kl, uint8_t* stat_clip_mask,
                                uint8_t* stat_dual_clip_mask, float* stat_behave_imp_weight,
@@ -363,7 +371,7 @@ AREAL_B200_API int areal_b200_fused_actor_fwd(const void* logits, int dtype, int
   int rc = check_logits(logits, dtype, T, V, row_stride, labels, temperature);
   if (rc) return rc;
   AB_REQUIRE(T > 0, "fused entry needs T > 0");
-  AB_REQUIRE(logp && lse && loss_out && inv_count_out && coef, "required output is null");
+  AB_REQUIRE(logp && row_max && ln_sumexp && loss_out && inv_count_out && coef, "required output is null");
   AB_REQUIRE(old_logprobs && advantages && loss_mask, "old_logprobs / advantages / loss_mask required");
   rc = check_ws(workspace, workspace_bytes);
   if (rc) return rc;
@@ -375,9 +383,9 @@ AREAL_B200_API int areal_b200_fused_actor_fwd(const void* logits, int dtype, int
   p.mode = kModeFusedActor;
   p.logp = logp;
   p.entropy = entropy;
-  p.lse = lse;
+  p.row_max = row_max;
+  p.ln_s = ln_sumexp;
   p.raw_min = raw_min;
-  p.raw_max = raw_max;
   p.prox = proximal_logprobs;
   p.old = old_logprobs;
   p.adv = advantages;

@@ -31,28 +31,44 @@ constexpr int kCtasPerSm = 2;
 constexpr size_t kSmemBytes = size_t(kStages) * kStageBytes + 1024;
 
 struct RowState {
-  float m;   // running max of raw logits seen by this thread (-inf initially)
-  float s;   // sum 2^((x - m) * c2)
-  float u;   // sum 2^((x - m) * c2) * x
-  float mn;  // running min of raw logits
+  float m;   // running max of the raw logits seen by this thread (-inf initially)
+  float nb;  // fl(-m * c2): every term below is 2^(x*c2 + nb), i.e. relative to this exact offset
+  float s;   // sum e,      e = 2^t,  t = x*c2 + nb  (<= ~0)
+  float w;   // sum e * t   (shifted first moment: small whenever the row is peaked, so the
+             //              entropy keeps its relative accuracy; no extra per-element instruction)
+  float mn;  // running min of the raw logits
 };
 
 __device__ __forceinline__ void state_init(RowState& st) {
   st.m = -INFINITY;
+  st.nb = 0.f;
   st.s = 0.f;
-  st.u = 0.f;
+  st.w = 0.f;
   st.mn = INFINITY;
 }
 
-// Move the thread's reference maximum to max(st.m, cm); returns -m_new*c2 for the FFMA below.
+// Move the thread's reference to max(st.m, cm).  Exactly consistent: the old terms are rescaled by
+// 2^(nb_new - nb_old), the very offsets they were accumulated with.
 __device__ __forceinline__ float state_rebase(RowState& st, float cm, float c2) {
   const float m_new = fmaxf(st.m, cm);
-  // st.m == -inf: (-inf - finite)*c2 = -inf -> alpha = 0 (s, u are 0 anyway).
-  const float alpha = (m_new == -INFINITY) ? 1.0f : ex2_approx((st.m - m_new) * c2);
+  const float nb_new = -m_new * c2;
+  const float delta = (st.m == -INFINITY) ? 0.f : (nb_new - st.nb);   // <= 0
+  const float alpha = ex2_approx(delta);
+  st.w = alpha * fmaf(delta, st.s, st.w);
   st.s *= alpha;
-  st.u *= alpha;
   st.m = m_new;
-  return -m_new * c2;
+  st.nb = nb_new;
+  return nb_new;
+}
+
+// Canonical form: terms relative to the EXACT max, t = (x - m) * c2.  r = m*c2 + nb is the rounding
+// residual of nb, obtained exactly with one FMA.
+__device__ __forceinline__ void state_canonical(RowState& st, float c2) {
+  if (st.s == 0.f) return;
+  const float r = fmaf(st.m, c2, st.nb);
+  const float f = ex2_approx(-r);
+  st.w = f * fmaf(-r, st.s, st.w);
+  st.s *= f;
 }
 
 __device__ __forceinline__ uint32_t vec_max_bf16(const uint4& q) {
@@ -62,21 +78,22 @@ __device__ __forceinline__ uint32_t vec_min_bf16(const uint4& q) {
   return min_bf16x2(min_bf16x2(q.x, q.y), min_bf16x2(q.z, q.w));
 }
 
-#define AB_ACC2(w, S, U)                         \
+#define AB_ACC2(wd, S, W)                        \
   {                                              \
-    const float x0 = bf16_lo(w), x1 = bf16_hi(w);\
-    const float e0 = ex2_approx(fmaf(x0, c2, nb));\
-    const float e1 = ex2_approx(fmaf(x1, c2, nb));\
+    const float t0 = fmaf(bf16_lo(wd), c2, nb);  \
+    const float t1 = fmaf(bf16_hi(wd), c2, nb);  \
+    const float e0 = ex2_approx(t0);             \
+    const float e1 = ex2_approx(t1);             \
     S##0 += e0;                                  \
-    U##0 = fmaf(e0, x0, U##0);                   \
+    W##0 = fmaf(e0, t0, W##0);                   \
     S##1 += e1;                                  \
-    U##1 = fmaf(e1, x1, U##1);                   \
+    W##1 = fmaf(e1, t1, W##1);                   \
   }
 
-// accumulate one 16-byte vector (8 bf16) with an already rebased reference (nb = -m*c2)
+// accumulate one 16-byte vector (8 bf16) against an already rebased reference nb
 __device__ __forceinline__ void vec_accumulate(const uint4& q, float c2, float nb, float& s0,
-                                               float& s1, float& u0, float& u1) {
-  AB_ACC2(q.x, s, u) AB_ACC2(q.y, s, u) AB_ACC2(q.z, s, u) AB_ACC2(q.w, s, u)
+                                               float& s1, float& w0, float& w1) {
+  AB_ACC2(q.x, s, w) AB_ACC2(q.y, s, w) AB_ACC2(q.z, s, w) AB_ACC2(q.w, s, w)
 }
 
 template <bool kMinMax>
@@ -94,11 +111,11 @@ __device__ __forceinline__ void consume_full_stage(RowState& st, uint32_t sbase,
     st.mn = fminf(st.mn, fminf(bf16_lo(mn), bf16_hi(mn)));
   }
   const float nb = state_rebase(st, fmaxf(bf16_lo(mx), bf16_hi(mx)), c2);
-  float s0 = 0.f, s1 = 0.f, u0 = 0.f, u1 = 0.f;
+  float s0 = 0.f, s1 = 0.f, w0 = 0.f, w1 = 0.f;
 #pragma unroll
-  for (int j = 0; j < kVecPerThread; ++j) vec_accumulate(q[j], c2, nb, s0, s1, u0, u1);
+  for (int j = 0; j < kVecPerThread; ++j) vec_accumulate(q[j], c2, nb, s0, s1, w0, w1);
   st.s += s0 + s1;
-  st.u += u0 + u1;
+  st.w += w0 + w1;
 }
 
 template <bool kMinMax>
@@ -109,44 +126,47 @@ __device__ __forceinline__ void consume_vec(RowState& st, const uint4& q, float 
     st.mn = fminf(st.mn, fminf(bf16_lo(mn), bf16_hi(mn)));
   }
   const float nb = state_rebase(st, fmaxf(bf16_lo(mx), bf16_hi(mx)), c2);
-  float s0 = 0.f, s1 = 0.f, u0 = 0.f, u1 = 0.f;
-  vec_accumulate(q, c2, nb, s0, s1, u0, u1);
+  float s0 = 0.f, s1 = 0.f, w0 = 0.f, w1 = 0.f;
+  vec_accumulate(q, c2, nb, s0, s1, w0, w1);
   st.s += s0 + s1;
-  st.u += u0 + u1;
+  st.w += w0 + w1;
 }
 
-// merge (m,s,u) pairs: result relative to max(m_a, m_b)
-__device__ __forceinline__ void state_merge(float& m, float& s, float& u, float m2, float s2,
-                                            float u2, float c2) {
+// merge two canonical (m, s, w) states: shift each by (m - M) * c2
+__device__ __forceinline__ void state_merge(float& m, float& s, float& w, float m2, float s2,
+                                            float w2, float c2) {
   const float M = fmaxf(m, m2);
-  const float a = (m == -INFINITY) ? 0.f : ex2_approx((m - M) * c2);
-  const float b = (m2 == -INFINITY) ? 0.f : ex2_approx((m2 - M) * c2);
-  s = s * a + s2 * b;
-  u = u * a + u2 * b;
+  const float da = (m == -INFINITY) ? 0.f : (m - M) * c2;
+  const float db = (m2 == -INFINITY) ? 0.f : (m2 - M) * c2;
+  const float fa = (m == -INFINITY) ? 0.f : ex2_approx(da);
+  const float fb = (m2 == -INFINITY) ? 0.f : ex2_approx(db);
+  w = fa * fmaf(da, s, w) + fb * fmaf(db, s2, w2);
+  s = s * fa + s2 * fb;
   m = M;
 }
 
 struct RowReduceSmem {
-  float m[2][kConsumerWarps], s[2][kConsumerWarps], u[2][kConsumerWarps], mn[2][kConsumerWarps];
+  float m[2][kConsumerWarps], s[2][kConsumerWarps], w[2][kConsumerWarps], mn[2][kConsumerWarps];
 };
 
 // All consumer threads call; returns true on the single thread (warp 0, lane 0) that holds the row
-// totals in st.  One named barrier per row (double-buffered by `parity`).
+// totals in st (canonical form).  One named barrier per row (double-buffered by `parity`).
 __device__ __forceinline__ bool row_reduce(RowState& st, RowReduceSmem* red, int parity, int warp,
                                            int lane, float c2) {
+  state_canonical(st, c2);
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
     const float m2 = __shfl_xor_sync(0xffffffffu, st.m, o);
     const float s2 = __shfl_xor_sync(0xffffffffu, st.s, o);
-    const float u2 = __shfl_xor_sync(0xffffffffu, st.u, o);
+    const float w2 = __shfl_xor_sync(0xffffffffu, st.w, o);
     const float n2 = __shfl_xor_sync(0xffffffffu, st.mn, o);
-    state_merge(st.m, st.s, st.u, m2, s2, u2, c2);
+    state_merge(st.m, st.s, st.w, m2, s2, w2, c2);
     st.mn = fminf(st.mn, n2);
   }
   if (lane == 0) {
     red->m[parity][warp] = st.m;
     red->s[parity][warp] = st.s;
-    red->u[parity][warp] = st.u;
+    red->w[parity][warp] = st.w;
     red->mn[parity][warp] = st.mn;
   }
   named_bar_sync(1, kConsumers);
@@ -154,15 +174,15 @@ __device__ __forceinline__ bool row_reduce(RowState& st, RowReduceSmem* red, int
   const int l = lane & (kConsumerWarps - 1);
   st.m = red->m[parity][l];
   st.s = red->s[parity][l];
-  st.u = red->u[parity][l];
+  st.w = red->w[parity][l];
   st.mn = red->mn[parity][l];
 #pragma unroll
   for (int o = kConsumerWarps / 2; o > 0; o >>= 1) {
     const float m2 = __shfl_xor_sync(0xffffffffu, st.m, o);
     const float s2 = __shfl_xor_sync(0xffffffffu, st.s, o);
-    const float u2 = __shfl_xor_sync(0xffffffffu, st.u, o);
+    const float w2 = __shfl_xor_sync(0xffffffffu, st.w, o);
     const float n2 = __shfl_xor_sync(0xffffffffu, st.mn, o);
-    state_merge(st.m, st.s, st.u, m2, s2, u2, c2);
+    state_merge(st.m, st.s, st.w, m2, s2, w2, c2);
     st.mn = fminf(st.mn, n2);
   }
   return lane == 0;
@@ -188,22 +208,22 @@ __device__ __forceinline__ void row_epilogue(const LogitsFwdParams& p, int64_t r
   const bool local = lab >= 0 && lab < p.V;
   const char* rowp = reinterpret_cast<const char*>(p.logits) + row * p.row_stride_bytes;
   const float xl = local ? load_logit(rowp, p.dtype, lab) : 0.f;
-  if (p.raw_max) p.raw_max[row] = st.m;
   if (p.raw_min) p.raw_min[row] = st.mn;
   if (p.mode == kModePartial) {
-    // (m, s, u, z_label) of z = x / temperature for the cross-shard combine
-    p.part_m[row] = st.m * inv_t;
+    // (raw max, S, W, raw label logit or 0) for the cross-shard combine
+    p.part_m[row] = st.m;
     p.part_s[row] = st.s;
-    p.part_u[row] = st.u * inv_t;
-    p.part_zl[row] = xl * inv_t;
+    p.part_w[row] = st.w;
+    p.part_xl[row] = xl;
     return;
   }
+  // lse(z) = m/temp + ln S;  E_p[z] = m/temp + ln2 * W/S;  H = lse - E_p[z] = ln S - ln2 * W/S
   const float ln_s = lg2_approx(st.s) * kLn2;
-  const float lse = fmaf(st.m, inv_t, ln_s);                 // natural log-sum-exp of z
   const float logp = local ? (xl - st.m) * inv_t - ln_s : __int_as_float(0x7fc00000);
-  const float ent = lse - (st.u / st.s) * inv_t;             // H = lse - E_p[z]
+  const float ent = ln_s - kLn2 * (st.w / st.s);
   p.logp[row] = logp;
-  p.lse[row] = lse;
+  p.row_max[row] = st.m;
+  p.ln_s[row] = ln_s;
   if (p.entropy) p.entropy[row] = ent;
   if (p.mode == kModeFusedActor) {
     const bool mask = p.loss_mask[row] != 0;
@@ -362,18 +382,19 @@ logits_fwd_generic_kernel(const LogitsFwdParams p) {
       const float c = to_f32<T>(x[i + 2 * kConsumers]), d = to_f32<T>(x[i + 3 * kConsumers]);
       st.mn = fminf(st.mn, fminf(fminf(a, b), fminf(c, d)));
       const float nb = state_rebase(st, fmaxf(fmaxf(a, b), fmaxf(c, d)), c2);
-      const float ea = ex2_approx(fmaf(a, c2, nb)), eb = ex2_approx(fmaf(b, c2, nb));
-      const float ec = ex2_approx(fmaf(c, c2, nb)), ed = ex2_approx(fmaf(d, c2, nb));
+      const float ta = fmaf(a, c2, nb), tb = fmaf(b, c2, nb), tc = fmaf(c, c2, nb), td = fmaf(d, c2, nb);
+      const float ea = ex2_approx(ta), eb = ex2_approx(tb), ec = ex2_approx(tc), ed = ex2_approx(td);
       st.s += (ea + eb) + (ec + ed);
-      st.u += fmaf(ea, a, eb * b) + fmaf(ec, c, ed * d);
+      st.w += fmaf(ea, ta, eb * tb) + fmaf(ec, tc, ed * td);
     }
     for (; i < p.V; i += kConsumers) {
       const float a = to_f32<T>(x[i]);
       st.mn = fminf(st.mn, a);
       const float nb = state_rebase(st, a, c2);
-      const float ea = ex2_approx(fmaf(a, c2, nb));
+      const float ta = fmaf(a, c2, nb);
+      const float ea = ex2_approx(ta);
       st.s += ea;
-      st.u = fmaf(ea, a, st.u);
+      st.w = fmaf(ea, ta, st.w);
     }
     if (row_reduce(st, &red, parity, warp, lane, c2)) row_epilogue(p, row, st, acc);
     parity ^= 1;
@@ -382,10 +403,12 @@ logits_fwd_generic_kernel(const LogitsFwdParams p) {
 }
 
 // ---- backward ----------------------------------------------------------------------------------
-// dlogits[t,v] = p_v * (k0 + k1 * x_v) (+ gl at v == label), p_v = 2^(x*c2 - lse*log2e)
-//   k0 = -(gl) - gh*(H - lse),  k1 = -gh/temp,  gl = g_logp*scale/temp,  gh = g_entropy*scale/temp
+// dlogits[t,v] = p_v * (k0 + k1 * x_v) (+ gl at v == label),  p_v = 2^((x - m)*c2 - log2 S):
+// the max is subtracted first (exact in fp32), so 1 - p_label keeps its accuracy on peaked rows.
+//   gl = g_logp*scale/temp, gh = g_entropy*scale/temp, lse = m/temp + ln S,
+//   k0 = -gl - gh*(H - lse),  k1 = -gh/temp
 struct RowGrad {
-  float k0, k1, gl, nl;   // nl = -lse*log2e
+  float k0, k1, gl, m, nl2s;   // nl2s = -log2 S
   bool active;
 };
 
@@ -397,13 +420,15 @@ __device__ __forceinline__ RowGrad row_grad(const LogitsBwdParams& p, int64_t ro
   const float glp = p.g_logp ? p.g_logp[row] : 0.f;
   const float ghp = p.g_entropy ? p.g_entropy[row] : 0.f;
   g.active = (glp != 0.f) || (ghp != 0.f);
-  const float lse = p.lse[row];
+  g.m = p.row_max[row];
+  const float ln_s = p.ln_s[row];
   g.gl = glp * scale;
   const float gh = ghp * scale;
   const float H = p.g_entropy ? p.entropy[row] : 0.f;
-  g.k0 = -g.gl - gh * (H - lse);
+  // k0 + k1*x = -gl - gh*(H - ln S) - (gh/temp)*(x - m)  -> fold m into k0
   g.k1 = -gh * p.inv_temperature;
-  g.nl = -lse * kLog2e;
+  g.k0 = -g.gl - gh * (H - ln_s) - g.k1 * g.m;
+  g.nl2s = -ln_s * kLog2e;
   return g;
 }
 
@@ -413,7 +438,7 @@ __device__ __forceinline__ uint4 grad_vec(const uint4& q, const RowGrad& g, floa
   float d[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
-    const float pv = ex2_approx(fmaf(x[i], c2, g.nl));
+    const float pv = ex2_approx(fmaf(x[i] - g.m, c2, g.nl2s));
     d[i] = pv * fmaf(x[i], g.k1, g.k0);
   }
   if (lab_off >= 0 && lab_off < 8) {
@@ -544,7 +569,7 @@ logits_bwd_generic_kernel(const LogitsBwdParams p) {
     }
     for (int64_t i = tid; i < p.V; i += kConsumers) {
       const float xv = to_f32<T>(x[i]);
-      const float pv = ex2_approx(fmaf(xv, c2, g.nl));
+      const float pv = ex2_approx(fmaf(xv - g.m, c2, g.nl2s));
       float dv = pv * fmaf(xv, g.k1, g.k0);
       if (i == lab) dv += g.gl;
       d[i] = from_f32<T>(dv);
@@ -554,25 +579,32 @@ logits_bwd_generic_kernel(const LogitsBwdParams p) {
 
 // ---- cross-shard combine (vocab-sharded path) ----------------------------------------------------
 __global__ void vocab_combine_kernel(const float* __restrict__ parts, int R, int64_t T,
-                                     float* __restrict__ logp, float* __restrict__ entropy,
-                                     float* __restrict__ lse_out) {
-  // parts layout: [R][4][T] = (m, s, u, z_label) per shard, z-units (already divided by temperature)
+                                     float inv_t, float* __restrict__ logp,
+                                     float* __restrict__ entropy, float* __restrict__ row_max,
+                                     float* __restrict__ ln_s_out) {
+  // parts layout: [R][4][T] = (raw max, S, W, raw label logit or 0) per shard
   const int64_t t = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
   if (t >= T) return;
+  const float c2 = inv_t * kLog2e;
   float M = -INFINITY;
   for (int r = 0; r < R; ++r) M = fmaxf(M, parts[(int64_t(r) * 4 + 0) * T + t]);
-  float S = 0.f, U = 0.f, ZL = 0.f;
+  float S = 0.f, W = 0.f, XL = 0.f;
   for (int r = 0; r < R; ++r) {
     const float m = parts[(int64_t(r) * 4 + 0) * T + t];
-    const float a = (m == -INFINITY) ? 0.f : expf(m - M);
-    S = fmaf(parts[(int64_t(r) * 4 + 1) * T + t], a, S);
-    U = fmaf(parts[(int64_t(r) * 4 + 2) * T + t], a, U);
-    ZL += parts[(int64_t(r) * 4 + 3) * T + t];
+    if (m != -INFINITY) {
+      const float d = (m - M) * c2;
+      const float f = exp2f(d);
+      const float sr = parts[(int64_t(r) * 4 + 1) * T + t];
+      S = fmaf(sr, f, S);
+      W = fmaf(f, fmaf(d, sr, parts[(int64_t(r) * 4 + 2) * T + t]), W);
+    }
+    XL += parts[(int64_t(r) * 4 + 3) * T + t];
   }
-  const float lse = M + logf(S);
-  logp[t] = ZL - lse;
-  if (entropy) entropy[t] = lse - U / S;
-  lse_out[t] = lse;
+  const float ln_s = logf(S);
+  logp[t] = (XL - M) * inv_t - ln_s;
+  if (entropy) entropy[t] = ln_s - kLn2 * (W / S);
+  row_max[t] = M;
+  ln_s_out[t] = ln_s;
 }
 
 bool tma_ok(const void* ptr, int dtype, int64_t V, int64_t row_stride_bytes) {
@@ -629,12 +661,12 @@ int launch_logits_bwd(const LogitsBwdParams& p, cudaStream_t stream) {
   return check_launch("logits_bwd");
 }
 
-int launch_vocab_combine(const float* parts, int R, int64_t T, float* logp, float* entropy,
-                         float* lse, cudaStream_t stream) {
+int launch_vocab_combine(const float* parts, int R, int64_t T, float inv_t, float* logp,
+                         float* entropy, float* row_max, float* ln_s, cudaStream_t stream) {
   if (T == 0) return kOk;
   const int threads = 256;
   vocab_combine_kernel<<<static_cast<int>((T + threads - 1) / threads), threads, 0, stream>>>(
-      parts, R, T, logp, entropy, lse);
+      parts, R, T, inv_t, logp, entropy, row_max, ln_s);
   return check_launch("vocab_combine");
 }
 

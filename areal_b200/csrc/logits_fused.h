@@ -19,11 +19,11 @@ struct LogitsFwdParams {
   // standard / fused outputs
   float* logp;
   float* entropy;   // nullable
-  float* lse;
+  float* row_max;   // max of the raw logits (exact)
+  float* ln_s;      // ln sum exp((x - row_max)/temp);  logsumexp(z) = row_max/temp + ln_s
   float* raw_min;   // nullable (enables the min pass)
-  float* raw_max;   // nullable
   // partial-mode outputs
-  float *part_m, *part_s, *part_u, *part_zl;
+  float *part_m, *part_s, *part_w, *part_xl;
   // fused actor-loss epilogue
   const float *prox, *old, *adv;
   const uint8_t* loss_mask;
@@ -44,7 +44,8 @@ struct LogitsBwdParams {
   const int64_t* labels;
   int64_t vocab_start;
   float inv_temperature;
-  const float* lse;
+  const float* row_max;     // from the forward (global values on the vocab-sharded path)
+  const float* ln_s;
   const float* entropy;     // required iff g_entropy
   const float* g_logp;      // nullable
   const float* g_entropy;   // nullable
@@ -55,7 +56,7 @@ struct LogitsBwdParams {
 int64_t logits_loss_workspace_bytes();
 int launch_logits_fwd(const LogitsFwdParams& p, cudaStream_t stream);
 int launch_logits_bwd(const LogitsBwdParams& p, cudaStream_t stream);
-int launch_vocab_combine(const float* parts, int R, int64_t T, float* logp, float* entropy,
-                         float* lse, cudaStream_t stream);
+int launch_vocab_combine(const float* parts, int R, int64_t T, float inv_t, float* logp,
+                         float* entropy, float* row_max, float* ln_s, cudaStream_t stream);
 
 }  // namespace ab

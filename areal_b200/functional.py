@@ -61,29 +61,31 @@ def _mask_u8(m: torch.Tensor) -> torch.Tensor:
 # --------------------------------------------------------------------------------------------------
 # log-prob / entropy
 # --------------------------------------------------------------------------------------------------
-def _logits_forward(x, lab, temperature, want_entropy, want_minmax=False):
+def _logits_forward(x, lab, temperature, want_entropy, want_min=False):
     T, V = x.shape
     dev = x.device
-    logp = torch.empty(T, dtype=torch.float32, device=dev)
-    lse = torch.empty(T, dtype=torch.float32, device=dev)
-    ent = torch.empty(T, dtype=torch.float32, device=dev) if want_entropy else None
-    mn = torch.empty(T, dtype=torch.float32, device=dev) if want_minmax else None
-    mx = torch.empty(T, dtype=torch.float32, device=dev) if want_minmax else None
+    f32 = dict(dtype=torch.float32, device=dev)
+    logp = torch.empty(T, **f32)
+    row_max = torch.empty(T, **f32)
+    ln_s = torch.empty(T, **f32)
+    ent = torch.empty(T, **f32) if want_entropy else None
+    mn = torch.empty(T, **f32) if want_min else None
     with torch.cuda.device(dev):
         call("areal_b200_logits_fwd", ptr(x), _lib.DTYPE_CODE[x.dtype], T, V, x.stride(0) if T > 1 else V,
-             ptr(lab), float(temperature), ptr(logp), ptr(ent), ptr(lse), ptr(mn), ptr(mx), stream_ptr(dev))
-    return logp, ent, lse, mn, mx
+             ptr(lab), float(temperature), ptr(logp), ptr(ent), ptr(row_max), ptr(ln_s), ptr(mn),
+             stream_ptr(dev))
+    return logp, ent, row_max, ln_s, mn
 
 
-def _logits_backward(x, lab, temperature, lse, ent, g_logp, g_ent, scale0=None, scale1=None,
+def _logits_backward(x, lab, temperature, row_max, ln_s, ent, g_logp, g_ent, scale0=None, scale1=None,
                      vocab_start=0):
     T, V = x.shape
     dev = x.device
     dlogits = torch.empty((T, V), dtype=x.dtype, device=dev)
     with torch.cuda.device(dev):
         call("areal_b200_logits_bwd", ptr(x), _lib.DTYPE_CODE[x.dtype], T, V, x.stride(0) if T > 1 else V,
-             ptr(lab), int(vocab_start), float(temperature), ptr(lse), ptr(ent), ptr(g_logp), ptr(g_ent),
-             ptr(scale0), ptr(scale1), ptr(dlogits), V, stream_ptr(dev))
+             ptr(lab), int(vocab_start), float(temperature), ptr(row_max), ptr(ln_s), ptr(ent), ptr(g_logp),
+             ptr(g_ent), ptr(scale0), ptr(scale1), ptr(dlogits), V, stream_ptr(dev))
     return dlogits
 
 
@@ -91,8 +93,8 @@ class _GatherLogprobsEntropy(torch.autograd.Function):
     @staticmethod
     def forward(ctx, logits, labels, temperature, want_entropy):
         dev, x, lab, lead, V = _rows(logits, labels)
-        logp, ent, lse, _, _ = _logits_forward(x, lab, temperature, want_entropy)
-        ctx.save_for_backward(x, lab, lse, ent if want_entropy else None)
+        logp, ent, row_max, ln_s, _ = _logits_forward(x, lab, temperature, want_entropy)
+        ctx.save_for_backward(x, lab, row_max, ln_s, ent if want_entropy else None)
         ctx.temperature = float(temperature)
         ctx.in_shape = logits.shape
         ctx.set_materialize_grads(False)
@@ -103,12 +105,12 @@ class _GatherLogprobsEntropy(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, g_logp, g_ent=None):
-        x, lab, lse, ent = ctx.saved_tensors
+        x, lab, row_max, ln_s, ent = ctx.saved_tensors
         gl = None if g_logp is None else _f32(g_logp.reshape(-1))
         gh = None if (g_ent is None or ent is None) else _f32(g_ent.reshape(-1))
         if gl is None and gh is None:
             return None, None, None, None
-        d = _logits_backward(x, lab, ctx.temperature, lse, ent, gl, gh)
+        d = _logits_backward(x, lab, ctx.temperature, row_max, ln_s, ent, gl, gh)
         return d.view(ctx.in_shape), None, None, None
 
 
@@ -131,9 +133,9 @@ def logits_stats(logits: torch.Tensor, labels: torch.Tensor, temperature: float 
     """One pass returning dict(logp, entropy, lse, vocab_min_logits, vocab_max_logits): the values
     `grpo_loss_fn` gets from three separate reads of the logits (actor.py:340, 375-376)."""
     dev, x, lab, lead, V = _rows(logits, labels)
-    logp, ent, lse, mn, mx = _logits_forward(x, lab, temperature, True, True)
-    return dict(logp=logp.view(lead), entropy=ent.view(lead), lse=lse.view(lead),
-                vocab_min_logits=mn.view(lead), vocab_max_logits=mx.view(lead))
+    logp, ent, row_max, ln_s, mn = _logits_forward(x, lab, temperature, True, True)
+    return dict(logp=logp.view(lead), entropy=ent.view(lead), lse=(row_max / temperature + ln_s).view(lead),
+                vocab_min_logits=mn.view(lead), vocab_max_logits=row_max.view(lead))
 
 
 # --------------------------------------------------------------------------------------------------
@@ -295,9 +297,9 @@ class _FusedActor(torch.autograd.Function):
         f32 = dict(dtype=torch.float32, device=dev)
         logp = torch.empty(T, **f32)
         ent = torch.empty(T, **f32)
-        lse = torch.empty(T, **f32)
+        row_max = torch.empty(T, **f32)
+        ln_s = torch.empty(T, **f32)
         mn = torch.empty(T, **f32) if want_minmax else None
-        mx = torch.empty(T, **f32) if want_minmax else None
         loss = torch.empty((), **f32)
         inv = torch.empty(1, **f32)
         coef = torch.empty(T, **f32)
@@ -308,11 +310,11 @@ class _FusedActor(torch.autograd.Function):
             call("areal_b200_fused_actor_fwd", ptr(x), _lib.DTYPE_CODE[x.dtype], T, V,
                  x.stride(0) if T > 1 else V, ptr(lab), float(temperature), ptr(px), ptr(od), ptr(av), ptr(mk),
                  float(eps_clip), _opt(eps_clip_higher), _opt(c_clip), _opt(cap),
-                 ptr(logp), ptr(ent), ptr(lse), ptr(mn), ptr(mx), ptr(loss), ptr(inv), ptr(coef),
+                 ptr(logp), ptr(ent), ptr(row_max), ptr(ln_s), ptr(mn), ptr(loss), ptr(inv), ptr(coef),
                  ptr(f["loss"]), ptr(f["importance_weight"]), ptr(f["approx_kl"]), ptr(_u8(b["clip_mask"])),
                  ptr(_u8(b["dual_clip_mask"])), ptr(f.get("behave_imp_weight")), ptr(f.get("behave_approx_kl")),
                  ptr(_u8(b.get("behave_mask"))), ptr(ws), ws.numel(), stream_ptr(dev))
-        ctx.save_for_backward(x, lab, lse, coef, inv)
+        ctx.save_for_backward(x, lab, row_max, ln_s, coef, inv)
         ctx.temperature = float(temperature)
         ctx.in_shape = logits.shape
         extras = [logp, ent, f["loss"], f["importance_weight"], f["approx_kl"], b["clip_mask"],
@@ -320,16 +322,16 @@ class _FusedActor(torch.autograd.Function):
         if px is not None:
             extras += [f["behave_imp_weight"], f["behave_approx_kl"], b["behave_mask"]]
         if want_minmax:
-            extras += [mn, mx]
+            extras += [mn, row_max.clone()]
         extras = [e.view(lead) for e in extras]
         ctx.mark_non_differentiable(*extras)
         return (loss, *extras)
 
     @staticmethod
     def backward(ctx, g_loss, *unused):
-        x, lab, lse, coef, inv = ctx.saved_tensors
+        x, lab, row_max, ln_s, coef, inv = ctx.saved_tensors
         g = _f32(g_loss.reshape(1))
-        d = _logits_backward(x, lab, ctx.temperature, lse, None, coef, None, inv, g)
+        d = _logits_backward(x, lab, ctx.temperature, row_max, ln_s, None, coef, None, inv, g)
         return (d.view(ctx.in_shape),) + (None,) * 11
 
 

@@ -80,40 +80,50 @@ AREAL_B200_API int areal_b200_gae2d_olp(const float* rewards, const float* value
  * (areal/utils/functional.py:43-127; inner :20-34) and the two extra [T,V] reads
  * `logits.min(-1)`, `logits.max(-1)` (areal/engine/ppo/actor.py:375-376).
  *   logits [T,V] of `dtype`, unit stride in V, `row_stride` ELEMENTS between rows; labels i64[T];
- *   z = float(logits)/temperature.  Outputs f32[T]: logp (required), lse = logsumexp(z)
- *   (required; saved for the backward), entropy / raw_min / raw_max (each nullable).
+ *   z = float(logits)/temperature.  Outputs f32[T]: logp (required); row_max = max_v logits (raw
+ *   units, exact) and ln_sumexp = ln sum_v exp((logits - row_max)/temperature) (both required and
+ *   saved for the backward: logsumexp(z) = row_max/temperature + ln_sumexp, kept as two terms so
+ *   that 1 - p_label survives fp32 on peaked rows); entropy, raw_min nullable.
  *   A label outside [0,V) yields logp = NaN for that row (the reference's gather would raise). */
-AREAL_B200_API int areal_b200_logits_fwd(const void* logits, int dtype, int64_t T, int64_t V, int64_t row_stride,
-                          const int64_t* labels, double temperature, float* logp, float* entropy,
-                          float* lse, float* raw_min, float* raw_max, void* stream);
+AREAL_B200_API int areal_b200_logits_fwd(const void* logits, int dtype, int64_t T, int64_t V,
+                                         int64_t row_stride, const int64_t* labels,
+                                         double temperature, float* logp, float* entropy,
+                                         float* row_max, float* ln_sumexp, float* raw_min,
+                                         void* stream);
 
 /* Backward: dlogits = d/dlogits of sum_t g_logp[t]*logp[t] + g_entropy[t]*entropy[t], times the
  * optional device scalars *scale0 * *scale1, rounded once to `dtype`.  Replaces autograd through
  * the reference's log_softmax path (functional.py:20-34) and `_VocabParallelEntropy.backward`
  * (areal/utils/mcore/functional.py:41-52).  g_entropy nullable (then entropy may be null); rows
- * whose gradients are all zero are written as zeros without reading the logits. */
-AREAL_B200_API int areal_b200_logits_bwd(const void* logits, int dtype, int64_t T, int64_t V, int64_t row_stride,
-                          const int64_t* labels, int64_t vocab_start, double temperature,
-                          const float* lse, const float* entropy, const float* g_logp,
-                          const float* g_entropy, const float* scale0, const float* scale1,
-                          void* dlogits, int64_t d_row_stride, void* stream);
+ * whose gradients are all zero are written as zeros without reading the logits.  On the
+ * vocab-sharded path pass the shard's logits, its vocab_start and the GLOBAL row_max / ln_sumexp. */
+AREAL_B200_API int areal_b200_logits_bwd(const void* logits, int dtype, int64_t T, int64_t V,
+                                         int64_t row_stride, const int64_t* labels,
+                                         int64_t vocab_start, double temperature,
+                                         const float* row_max, const float* ln_sumexp,
+                                         const float* entropy, const float* g_logp,
+                                         const float* g_entropy, const float* scale0,
+                                         const float* scale1, void* dlogits, int64_t d_row_stride,
+                                         void* stream);
 
-/* Vocab-sharded forward, per shard: the (m, s, u, z_label) partials that the reference obtains
- * with three all-reduces each in `_VocabParallelEntropy.forward`
- * (areal/utils/mcore/functional.py:15-34) and Megatron's `vocab_parallel_cross_entropy`
- * (call sites areal/utils/functional.py:55-57, 95-97; vendored copy
- * realhf/impl/model/parallelism/tensor_parallel/modules.py:1060-1118).
- *   parts f32[4,T] = rows (max z, sum exp(z-max), sum exp(z-max)*z, z_label or 0); labels are
- *   GLOBAL vocabulary ids, this shard holds [vocab_start, vocab_start+V). */
-AREAL_B200_API int areal_b200_logits_partial_fwd(const void* logits, int dtype, int64_t T, int64_t V,
-                                  int64_t row_stride, const int64_t* labels, int64_t vocab_start,
-                                  double temperature, float* parts, float* raw_min, float* raw_max,
-                                  void* stream);
+/* Vocab-sharded forward, per shard: the partials that the reference obtains with three
+ * all-reduces each in `_VocabParallelEntropy.forward` (areal/utils/mcore/functional.py:15-34) and
+ * Megatron's `vocab_parallel_cross_entropy` (call sites areal/utils/functional.py:55-57, 95-97;
+ * vendored copy realhf/impl/model/parallelism/tensor_parallel/modules.py:1060-1118).
+ *   parts f32[4,T] = rows (m = shard max of the raw logits, S = sum 2^t, W = sum 2^t * t with
+ *   t = (x - m) * log2(e)/temperature, raw label logit or 0 if the label is not in the shard);
+ *   labels are GLOBAL vocabulary ids, this shard holds [vocab_start, vocab_start+V). */
+AREAL_B200_API int areal_b200_logits_partial_fwd(const void* logits, int dtype, int64_t T,
+                                                 int64_t V, int64_t row_stride,
+                                                 const int64_t* labels, int64_t vocab_start,
+                                                 double temperature, float* parts, float* raw_min,
+                                                 void* stream);
 
 /* Combine R shards' partials (parts f32[R,4,T], e.g. the result of one all-gather) into logp,
- * entropy (nullable) and the global lse, f32[T] each. */
-AREAL_B200_API int areal_b200_vocab_combine(const float* parts, int64_t R, int64_t T, float* logp, float* entropy,
-                             float* lse, void* stream);
+ * entropy (nullable) and the global row_max / ln_sumexp, f32[T] each. */
+AREAL_B200_API int areal_b200_vocab_combine(const float* parts, int64_t R, int64_t T,
+                                            double temperature, float* logp, float* entropy,
+                                            float* row_max, float* ln_sumexp, void* stream);
 
 /* ------------------------------------------------------------------------------------------ *
  * P3  PPO losses
@@ -156,8 +166,8 @@ AREAL_B200_API int areal_b200_scale_by_scalars(const float* coef, const float* s
                                 int64_t T, float* out, void* stream);
 
 /* Fused GRPO/PPO actor step: ONE pass over the logits producing everything `grpo_loss_fn`
- * (areal/engine/ppo/actor.py:313-391) computes from them: logp, entropy, lse, raw min/max, the
- * actor loss, its logging vectors and the gradient coefficient.  Same argument meaning as
+ * (areal/engine/ppo/actor.py:313-391) computes from them: logp, entropy, row_max, ln_sumexp, raw_min, the
+ * actor loss, its logging vectors and the gradient coefficient (row_max doubles as logits.max(-1)).  Same argument meaning as
  * areal_b200_logits_fwd + areal_b200_ppo_actor_loss.  Backward = areal_b200_logits_bwd with
  * g_logp = coef, scale0 = inv_count, scale1 = upstream. */
 AREAL_B200_API int areal_b200_fused_actor_fwd(const void* logits, int dtype, int64_t T, int64_t V,
@@ -165,8 +175,8 @@ AREAL_B200_API int areal_b200_fused_actor_fwd(const void* logits, int dtype, int
                                const float* proximal_logprobs, const float* old_logprobs,
                                const float* advantages, const uint8_t* loss_mask, double eps_clip,
                                double eps_clip_higher, double c_clip, double behav_imp_weight_cap,
-                               float* logp, float* entropy, float* lse, float* raw_min,
-                               float* raw_max, float* loss_out, float* inv_count_out, float* coef,
+                               float* logp, float* entropy, float* row_max, float* ln_sumexp,
+                               float* raw_min, float* loss_out, float* inv_count_out, float* coef,
                                float* stat_loss, float* stat_importance_weight,
                                float* stat_approx_kl, uint8_t* stat_clip_mask,
                                uint8_t* stat_dual_clip_mask, float* stat_behave_imp_weight,
