@@ -184,6 +184,7 @@ class _ActorLoss(torch.autograd.Function):
                  ptr(_u8(b.get("behave_mask"))), ptr(ws), ws.numel(), stream_ptr(dev))
         ctx.save_for_backward(coef, inv)
         ctx.shape = shape
+        ctx.set_materialize_grads(False)
         stats = [f["loss"], f["importance_weight"], f["approx_kl"], b["clip_mask"], b["dual_clip_mask"]]
         if px is not None:
             stats += [f["behave_imp_weight"], f["behave_approx_kl"], b["behave_mask"]]
@@ -193,6 +194,8 @@ class _ActorLoss(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, g_loss, *unused):
+        if g_loss is None:
+            return (None,) * 9
         coef, inv = ctx.saved_tensors
         dev = coef.device
         g = _f32(g_loss.reshape(1))
@@ -249,6 +252,7 @@ class _CriticLoss(torch.autograd.Function):
                  ws.numel(), stream_ptr(dev))
         ctx.save_for_backward(coef, inv)
         ctx.shape = shape
+        ctx.set_materialize_grads(False)
         stat_loss = stat_loss.view(shape)
         clip = clip.view(shape)
         ctx.mark_non_differentiable(stat_loss, clip)
@@ -256,6 +260,8 @@ class _CriticLoss(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, g_loss, *unused):
+        if g_loss is None:
+            return (None,) * 6
         coef, inv = ctx.saved_tensors
         dev = coef.device
         g = _f32(g_loss.reshape(1))
@@ -317,6 +323,7 @@ class _FusedActor(torch.autograd.Function):
         ctx.save_for_backward(x, lab, row_max, ln_s, coef, inv)
         ctx.temperature = float(temperature)
         ctx.in_shape = logits.shape
+        ctx.set_materialize_grads(False)
         extras = [logp, ent, f["loss"], f["importance_weight"], f["approx_kl"], b["clip_mask"],
                   b["dual_clip_mask"]]
         if px is not None:
@@ -329,6 +336,8 @@ class _FusedActor(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, g_loss, *unused):
+        if g_loss is None:
+            return (None,) * 12
         x, lab, row_max, ln_s, coef, inv = ctx.saved_tensors
         g = _f32(g_loss.reshape(1))
         d = _logits_backward(x, lab, ctx.temperature, row_max, ln_s, None, coef, None, inv, g)

@@ -1,0 +1,392 @@
+#!/usr/bin/env python
+"""Headline benchmark of the RL post-processing hot path (BASELINE.json `metric`).
+
+One STEP = what one PPO/GRPO micro-batch costs on this path, for a packed batch of T tokens:
+  (1) packed GAE over the batch               (areal_b200_gae1d_nolp_misalign)
+  (2) fused log-prob + entropy + decoupled PPO actor loss from [T, V] bf16 logits, forward
+                                              (areal_b200_fused_actor_fwd)
+  (3) loss.backward() -> dlogits [T, V] bf16  (areal_b200_logits_bwd)
+called through the public Python API (`areal_b200.functional.fused_actor_loss`, autograd), i.e.
+through the C ABI.  N = 1 workload: BASELINE.json configs[1] (Qwen2.5-1.5B GRPO math shape,
+T = 16,384 packed tokens, V = 151,936).  N > 1 (torchrun, one rank per GPU): the batch is sharded by
+packed sequence, every rank holds its own T tokens (weak scaling), and the only exchange is one
+NCCL all-reduce of (loss numerator, token count) per step.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+`--impl reference` times the reference's own CPU path (oracle port, see oracle/cpu_baseline.py) on the
+box's host cores on a bounded sample of the same workload.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "tokens/s fused logprob+entropy+PPO loss and packed GAE; % of HBM roofline"
+T_TOKENS = 16384
+VOCAB = 151936
+CFG = dict(eps_clip=0.4, eps_clip_higher=None, c_clip=None, behav_imp_weight_cap=5.0)   # examples/math/gsm8k_grpo.yaml:44,57-65
+TEMPERATURE = 1.0
+GAMMA, LAM = 1.0, 0.95
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        try:
+            return float(json.load(open(path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons through NVML while the timed region runs."""
+
+    def __init__(self, index, period=0.02):
+        super().__init__(daemon=True)
+        self.index, self.period = index, period
+        self.samples = []
+        self.stop_flag = False
+        self.max_mhz = None
+        self.ok = False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception:
+            self.ok = False
+
+    def run(self):
+        if not self.ok:
+            return
+        nv = self.nv
+        while not self.stop_flag:
+            try:
+                mhz = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
+                try:
+                    reasons = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    reasons = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                self.samples.append((time.perf_counter(), mhz, reasons))
+            except Exception:
+                pass
+            time.sleep(self.period)
+
+    def summary(self, t0, t1):
+        if not self.ok or not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": ["unavailable"], "samples": 0}
+        inside = [s for s in self.samples if t0 <= s[0] <= t1] or self.samples
+        mhz = sorted(s[1] for s in inside)
+        bits = 0
+        for s in inside:
+            bits |= s[2]
+        names = {0x1: "gpu_idle", 0x2: "applications_clocks_setting", 0x4: "sw_power_cap", 0x8: "hw_slowdown",
+                 0x10: "sync_boost", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+                 0x80: "hw_power_brake_slowdown", 0x100: "display_clock_setting"}
+        reasons = [n for b, n in names.items() if bits & b and n != "gpu_idle"]
+        return {"sm_mhz": mhz[len(mhz) // 2], "sm_max_mhz": self.max_mhz, "reasons": reasons, "samples": len(inside)}
+
+
+def make_batch(torch, dev, T, V, seed):
+    """Synthetic packed batch of the cfg-2 shape: sequences of U[128,4096] tokens packed to
+    T, prompt prefix (5-25 % of each sequence) masked out, logits = randn * 2 in bf16."""
+    import numpy as np
+    rng = np.random.RandomState(seed)
+    lens, left = [], T
+    while left > 0:
+        n = min(left, int(rng.randint(128, 4097)))
+        lens.append(n)
+        left -= n
+    B = len(lens)
+    cu = np.concatenate([[0], np.cumsum(lens)]).astype(np.int32)
+    mask = np.ones(T, dtype=bool)
+    for i in range(B):
+        mask[cu[i]:cu[i] + int(lens[i] * rng.uniform(0.05, 0.25))] = False
+    g = torch.Generator(device=dev).manual_seed(seed)
+    logits = torch.empty(T, V, dtype=torch.bfloat16, device=dev)
+    for i in range(0, T, 2048):
+        n = min(2048, T - i)
+        logits[i:i + n] = (torch.randn(n, V, generator=g, device=dev) * 2.0).bfloat16()
+    labels = torch.randint(0, V, (T,), generator=g, device=dev)
+    batch = dict(
+        logits=logits, labels=labels,
+        loss_mask=torch.from_numpy(mask).to(dev),
+        advantages=torch.randn(T, generator=g, device=dev),
+        rewards=torch.randn(T, generator=g, device=dev),
+        values=torch.randn(T + B, generator=g, device=dev),
+        cu_seqlens=torch.from_numpy(cu).to(dev),
+        bootstrap=torch.from_numpy(rng.rand(B) > 0.5).to(dev),
+        n_seqs=B,
+    )
+    return batch
+
+
+def run_ours(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from areal_b200 import functional as F
+    from areal_b200 import ppo_functional as P
+    from areal_b200 import _lib
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    assert world == args.gpus or world == 1, f"--gpus {args.gpus} but WORLD_SIZE={world}"
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    _lib.lib()   # fail loudly if the CUDA extension is missing
+
+    T, V = T_TOKENS, VOCAB
+    b = make_batch(torch, dev, T, V, seed=rank)
+    # proximal / behaviour log-probs around the true ones
+    with torch.no_grad():
+        lp_true = F.gather_logprobs(b["logits"], b["labels"], TEMPERATURE)
+        g = torch.Generator(device=dev).manual_seed(100 + rank)
+        b["prox_logp"] = lp_true + 0.02 * torch.randn(T, generator=g, device=dev)
+        b["old_logp"] = lp_true + 0.05 * torch.randn(T, generator=g, device=dev)
+    logits = b["logits"].requires_grad_()
+    red = torch.zeros(2, dtype=torch.float32, device=dev)
+
+    ev = {k: [] for k in ("start", "gae", "fwd", "bwd")}
+
+    def step(record=False):
+        if record:
+            e = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+            e[0].record()
+        adv_gae, ret = P.cugae1d_nolp_misalign_func(b["rewards"], b["values"], b["cu_seqlens"], b["bootstrap"], GAMMA, LAM)
+        if record:
+            e[1].record()
+        loss, st = F.fused_actor_loss(logits, b["labels"], TEMPERATURE, b["prox_logp"], b["old_logp"],
+                                      b["advantages"], b["loss_mask"], **CFG)
+        if record:
+            e[2].record()
+        logits.grad = None
+        loss.backward()
+        if record:
+            e[3].record()
+            for k, x in zip(("start", "gae", "fwd", "bwd"), e):
+                ev[k].append(x)
+        if world > 1:
+            red[0] = loss.detach() * st["loss"].numel()
+            red[1] = float(T)
+            dist.all_reduce(red)
+        return loss, st
+
+    def sync_all():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    sync_all()
+    t0 = time.perf_counter()
+    e_start = torch.cuda.Event(enable_timing=True)
+    e_stop = torch.cuda.Event(enable_timing=True)
+    torch.cuda.profiler.start()      # ncu --profile-from-start off captures exactly the timed region
+    e_start.record()
+    for _ in range(args.steps):
+        loss, st = step(record=True)
+    e_stop.record()
+    sync_all()
+    torch.cuda.profiler.stop()
+    t1 = time.perf_counter()
+    sampler.stop_flag = True
+    ms_total = e_start.elapsed_time(e_stop)
+    if world > 1:
+        mt = torch.tensor([ms_total], device=dev)
+        dist.all_reduce(mt, op=dist.ReduceOp.MAX)
+        ms_total = float(mt.item())
+    ms_step = ms_total / args.steps
+    value = world * T / (ms_step * 1e-3)
+
+    # per-kernel device times inside the timed region
+    def avg(a, c):
+        return float(np.mean([x.elapsed_time(y) for x, y in zip(ev[a], ev[c])]))
+    ms_gae, ms_fwd, ms_bwd = avg("start", "gae"), avg("gae", "fwd"), avg("fwd", "bwd")
+    coef_rows = int(torch.count_nonzero(logits.grad[:, :8].float().abs().sum(-1)).item()) if T else 0
+    active = coef_rows / T
+    peak, peak_src = measured_peaks()
+    bwd_bytes = 2.0 * T * V * (1.0 + active)      # write every row, read only rows with a gradient
+    fwd_bytes = 2.0 * T * V + 64.0 * T
+    gae_bytes = 16.0 * T + 9.0 * b["n_seqs"] + 4
+    roof = {"bound": "hbm", "kernel": "logits_bwd_tma_kernel",
+            "achieved": bwd_bytes / (ms_bwd * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+            "frac": bwd_bytes / (ms_bwd * 1e-3) / 1e9 / peak, "traffic": None,
+            "peak_source": peak_src, "ms": ms_bwd,
+            "algorithmic_bytes": bwd_bytes, "active_row_frac": active,
+            "note": "bytes = 2TV written + 2TV*active read (rows whose gradient is zero are not read); "
+                    "the reference's split API needs 4TV"}
+    roof_fwd = {"bound": "hbm", "kernel": "logits_fwd_tma_kernel", "achieved": fwd_bytes / (ms_fwd * 1e-3) / 1e9,
+                "peak": peak, "unit": "GB/s", "frac": fwd_bytes / (ms_fwd * 1e-3) / 1e9 / peak, "ms": ms_fwd,
+                "algorithmic_bytes": fwd_bytes}
+    roof_gae = {"bound": "launch-latency", "kernel": "gae1d_kernel", "ms": ms_gae,
+                "achieved": gae_bytes / (ms_gae * 1e-3) / 1e9, "unit": "GB/s", "algorithmic_bytes": gae_bytes}
+
+    clocks = sampler.summary(t0, t1)
+
+    # ---- end to end through the public API with HOST buffers (pinned), copies inside the timed region
+    e2e = None
+    try:
+        if args.skip_e2e:
+            raise RuntimeError("skipped (--skip-e2e)")
+        e2e = run_e2e(torch, dist, F, P, dev, b, world, max(3, min(args.steps, 5)))
+    except Exception as ex:  # pinned allocation can fail on a small host: say so instead of faking
+        e2e = {"value": None, "unit": "tokens/s", "error": repr(ex)[:200]}
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    line = {
+        "metric": METRIC, "value": value, "unit": "tokens/s", "n_gpus": world, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "bf16", "accumulate_dtype": "f32 (GAE scan f64)", "data": "synthetic",
+        "config": {"workload": "BASELINE.json configs[1]: Qwen2.5-1.5B GRPO math shape, T=16384 packed tokens "
+                               "per GPU, V=151936 bf16 logits; step = packed GAE + fused logprob+entropy+decoupled "
+                               "PPO loss fwd + dlogits bwd", "tokens_per_gpu": T, "vocab": V,
+                   "parallelism": f"dp{world} (batch-sharded by packed sequence)",
+                   "l2": "inputs (4.98 GB logits per GPU) larger than the 126 MB L2; no flush needed",
+                   "loss_cfg": {k: v for k, v in CFG.items()}, "temperature": TEMPERATURE},
+        "roofline": roof, "roofline_fwd": roof_fwd, "roofline_gae": roof_gae,
+        "e2e": e2e, "gpu_launches": 3 * args.steps, "clocks": clocks,
+        "loss": float(loss.detach()),
+    }
+    if world == 1 and not args.skip_cpu:
+        line["cpu_baseline"] = cpu_baseline()
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def run_e2e(torch, dist, F, P, dev, b, world, steps):
+    """Same step, but the inputs start in pinned HOST memory every step and the results are read back:
+    H2D of logits + per-token vectors, GAE + fused fwd + bwd on the device, D2H of the loss and the
+    per-token logp / entropy / advantages."""
+    T, V = b["logits"].shape
+    host = {}
+    for k in ("logits", "labels", "loss_mask", "advantages", "rewards", "values", "cu_seqlens", "bootstrap",
+              "prox_logp", "old_logp"):
+        t = b[k].detach()
+        h = torch.empty(t.shape, dtype=t.dtype, device="cpu", pin_memory=True)
+        h.copy_(t)
+        host[k] = h
+    dst = {k: torch.empty_like(b[k].detach()) for k in host}
+    out_host = {k: torch.empty(T, dtype=torch.float32, pin_memory=True) for k in ("logp", "entropy", "adv", "ret")}
+    loss_host = torch.empty((), dtype=torch.float32, pin_memory=True)
+    h2d = sum(h.numel() * h.element_size() for h in host.values())
+    d2h = 4 + sum(h.numel() * 4 for h in out_host.values())
+
+    def step():
+        for k in host:
+            dst[k].copy_(host[k], non_blocking=True)
+        x = dst["logits"].requires_grad_()
+        adv, ret = P.cugae1d_nolp_misalign_func(dst["rewards"], dst["values"], dst["cu_seqlens"], dst["bootstrap"], GAMMA, LAM)
+        loss, st = F.fused_actor_loss(x, dst["labels"], TEMPERATURE, dst["prox_logp"], dst["old_logp"],
+                                      dst["advantages"], dst["loss_mask"], **CFG)
+        loss.backward()
+        loss_host.copy_(loss.detach(), non_blocking=True)
+        out_host["logp"].copy_(st["logprobs"], non_blocking=True)
+        out_host["entropy"].copy_(st["entropy"], non_blocking=True)
+        out_host["adv"].copy_(adv, non_blocking=True)
+        out_host["ret"].copy_(ret, non_blocking=True)
+        x.grad = None
+        dst["logits"] = x.detach()
+
+    for _ in range(2):
+        step()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize(dev)
+    e0 = torch.cuda.Event(enable_timing=True)
+    e1 = torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        step()
+    e1.record()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize(dev)
+    ms = e0.elapsed_time(e1) / steps
+    if world > 1:
+        mt = torch.tensor([ms], device=dev)
+        dist.all_reduce(mt, op=dist.ReduceOp.MAX)
+        ms = float(mt.item())
+    return {"value": world * T / (ms * 1e-3), "unit": "tokens/s", "h2d_bytes_per_step": int(h2d),
+            "d2h_bytes_per_step": int(d2h), "ms_per_step": ms, "steps": steps,
+            "note": "dominated by the 4.98 GB host->device copy of the logits over PCIe"}
+
+
+def cpu_baseline(sample_rows=1024, steps=2, warmup=1):
+    """The oracle port of the reference's CPU path, timed on this box's host cores on a bounded sample."""
+    import torch
+    from oracle import cpu_baseline as CB
+    threads = os.cpu_count() or 1
+    dt, used = CB.time_steps(sample_rows, VOCAB, steps, warmup, CFG, TEMPERATURE, threads=threads)
+    return {"value": sample_rows / dt, "unit": "tokens/s", "cores": used, "kind": "port",
+            "sample": f"{sample_rows} tokens x V={VOCAB} bf16 (1/{T_TOKENS // sample_rows} of the workload), "
+                      f"{steps} steps after {warmup} warm-up; torch CPU eager log_softmax/entropy/PPO loss + backward "
+                      f"on {used} threads, GAE as the reference's per-token Python loop (1 thread)",
+            "seconds_per_step": dt}
+
+
+def run_reference(args):
+    """Reference arm: the reference's CPU implementation of the path (oracle port) on the host cores."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    sample_rows = 1024
+    steps = max(1, min(args.steps, 5))
+    warmup = max(1, min(args.warmup, 2))
+    import torch
+    from oracle import cpu_baseline as CB
+    threads = os.cpu_count() or 1
+    dt, used = CB.time_steps(sample_rows, VOCAB, steps, warmup, CFG, TEMPERATURE, threads=threads)
+    v = sample_rows / dt
+    cb = {"value": v, "unit": "tokens/s", "cores": used, "kind": "port",
+          "sample": f"each step = {sample_rows} tokens x V={VOCAB} bf16 (bounded sample of the {T_TOKENS}-token "
+                    f"workload); {steps} steps after {warmup} warm-up"}
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": "tokens/s", "n_gpus": args.gpus,
+            "steps": steps, "warmup": warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": "BASELINE.json configs[1] shape (V=151936 bf16), bounded sample of "
+                                   f"{sample_rows} tokens per step on the host CPU; same step composition "
+                                   "(packed GAE + logprob/entropy/PPO loss fwd + bwd)"},
+            "cpu_baseline": cb,
+            "e2e": {"value": v, "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--skip-e2e", action="store_true", help="profiling runs: skip the host-buffer leg")
+    ap.add_argument("--skip-cpu", action="store_true", help="profiling runs: skip the CPU baseline leg")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -174,3 +174,21 @@ def test_merge_intervals_vs_reference_cpp():
         spec.loader.exec_module(mod)
         for iv in cases:
             assert [tuple(x) for x in mod.merge_intervals(iv)] == O.merge_intervals(iv)
+
+
+def test_cpu_baseline_port_matches_golden():
+    """oracle/cpu_baseline.py (the timed CPU port of the reference path) against the reference's outputs."""
+    import torch
+    from oracle import cpu_baseline as CB
+    z = H.load("logprobs.npz")
+    for k, c in H.cases(z):
+        logits = H.bf16_from_bits(c["logits_bits"])
+        lp, ent = CB.logp_entropy_torch(logits, torch.from_numpy(c["labels"]), float(c["temp"]))
+        assert np.allclose(lp.numpy(), c["logp"], rtol=1e-6, atol=1e-6), k
+        assert np.allclose(ent.numpy(), c["entropy"], rtol=1e-5, atol=1e-6), k
+    z = H.load("actor_loss.npz")
+    for k, c in H.cases(z):
+        eps, eps_hi, c_clip, cap = (H.opt(x) for x in c["cfg"])
+        t = lambda a: torch.from_numpy(a)
+        loss = CB.actor_loss_torch(t(c["lp"]), t(c["prox"]), t(c["old"]), t(c["adv"]), eps, t(c["mask"]), eps_hi, c_clip, cap)
+        assert abs(float(loss) - float(c["loss"])) <= 1e-6 * max(1.0, abs(float(c["loss"]))), k
