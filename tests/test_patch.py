@@ -1,0 +1,48 @@
+"""CPU: the drop-in plumbing -- shims are importable under the names the reference imports, the
+`cugae` distribution is visible to importlib.metadata (realhf/base/pkg_version.py:7-11), and
+patch_areal() rebinds from-import sites."""
+import importlib.metadata
+import sys
+import types
+
+
+def test_install_shims_and_dist_info():
+    from areal_b200 import patch
+    mods = patch.install_shims()
+    import cugae
+    assert callable(cugae.cugae1d_nolp_misalign_func)
+    assert importlib.metadata.version("cugae") == "0.1.0"
+    from realhf._C.cugae import gae_1d_nolp_misalign, gae_2d_nolp, gae_2d_olp  # noqa: F401
+    from realhf._C.interval_op import merge_intervals
+    from realhf._C.interval_op_cuda import (set_intervals_bf16, set_intervals_fp16, set_intervals_fp32,  # noqa: F401
+                                            slice_intervals_bf16, slice_intervals_fp16, slice_intervals_fp32)
+    assert merge_intervals([(0, 2), (2, 5), (7, 9)]) == [(0, 5), (7, 9)]
+    assert set(mods) == {"cugae", "interval_op_cuda", "interval_op"}
+
+
+def test_patch_areal_rebinds_from_import_sites():
+    from areal_b200 import functional as F
+    from areal_b200 import patch
+    saved = {k: sys.modules.get(k) for k in ("areal", "areal.utils", "areal.utils.functional",
+                                             "areal.engine", "areal.engine.ppo", "areal.engine.ppo.actor")}
+    try:
+        fun = types.ModuleType("areal.utils.functional")
+        for n in ("gather_logprobs", "gather_logprobs_entropy", "ppo_actor_loss_fn", "ppo_critic_loss_fn"):
+            setattr(fun, n, lambda *a, **k: "reference")
+        actor = types.ModuleType("areal.engine.ppo.actor")
+        actor.gather_logprobs_entropy = fun.gather_logprobs_entropy    # `from ... import ...` binding
+        actor.ppo_actor_loss_fn = fun.ppo_actor_loss_fn
+        sys.modules["areal.utils.functional"] = fun
+        sys.modules["areal.engine.ppo.actor"] = actor
+        patched = patch.patch_areal()
+        assert "areal.utils.functional" in patched and "areal.engine.ppo.actor" in patched
+        assert actor.gather_logprobs_entropy is F.gather_logprobs_entropy
+        assert actor.ppo_actor_loss_fn is F.ppo_actor_loss_fn
+        assert fun.ppo_critic_loss_fn is F.ppo_critic_loss_fn
+        assert not hasattr(actor, "ppo_critic_loss_fn")
+    finally:
+        for k, v in saved.items():
+            if v is None:
+                sys.modules.pop(k, None)
+            else:
+                sys.modules[k] = v
