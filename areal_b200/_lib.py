@@ -25,6 +25,7 @@ SIGNATURES = {
     "areal_b200_version": (c_int, []),
     "areal_b200_gae1d_workspace_bytes": (I64, [I64]),
     "areal_b200_gae1d_nolp_misalign": (c_int, [P, P, P, P, I64, I64, F64, F64, P, P, P, I64, P]),
+    "areal_b200_gae1d_nolp_misalign_static": (c_int, [P, P, P, P, I64, I64, F64, F64, P, P, P]),
     "areal_b200_gae_padded_masked": (c_int, [P, P, P, P, I64, I64, F64, F64, P, P, P]),
     "areal_b200_gae2d_olp": (c_int, [P, P, P, P, P, P, I64, I64, I64, F64, F64, P, P, P]),
     "areal_b200_logits_fwd": (c_int, [P, c_int, I64, I64, I64, P, F64, P, P, P, P, P, P]),

@@ -120,6 +120,33 @@ AREAL_B200_API int areal_b200_gae1d_nolp_misalign(const float* rewards, const fl
   return launch_gae1d(p, static_cast<cudaStream_t>(stream));
 }
 
+AREAL_B200_API int areal_b200_gae1d_nolp_misalign_static(const float* rewards, const float* values,
+                                                         const int32_t* cu_seqlens,
+                                                         const uint8_t* bootstrap,
+                                                         int64_t total_tokens, int64_t batch_size,
+                                                         double gamma, double lam, float* adv_out,
+                                                         float* ret_out, void* stream) {
+  AB_REQUIRE(total_tokens >= 0 && batch_size >= 0, "negative size");
+  if (total_tokens == 0) return kOk;
+  AB_REQUIRE(batch_size > 0, "total_tokens > 0 needs batch_size > 0");
+  AB_REQUIRE(rewards && values && cu_seqlens && bootstrap && adv_out && ret_out, "null pointer");
+  Gae1dParams p;
+  p.rewards = rewards;
+  p.values = values;
+  p.cu = cu_seqlens;
+  p.bootstrap = bootstrap;
+  p.T = total_tokens;
+  p.B = batch_size;
+  p.g = static_cast<float>(gamma);
+  p.gl = static_cast<float>(gamma * lam);
+  p.adv = adv_out;
+  p.ret = ret_out;
+  p.workspace = nullptr;   // filled in by the launcher with the address of the built-in scratch
+  p.vec_ok = ((reinterpret_cast<uintptr_t>(rewards) | reinterpret_cast<uintptr_t>(adv_out) |
+               reinterpret_cast<uintptr_t>(ret_out)) & 15) == 0;
+  return launch_gae1d_static(p, static_cast<cudaStream_t>(stream));
+}
+
 AREAL_B200_API int areal_b200_gae_padded_masked(const float* rewards, const float* values,
                                  const float* loss_mask, const uint8_t* seq_no_eos, int64_t B,
                                  int64_t S, double gamma, double lam, float* adv_out,

@@ -19,8 +19,19 @@
 // the scan itself runs in fp64 so the reassociation of the parallel scan cannot be seen in the
 // fp32 result: the output is the correctly rounded recurrence, and its distance to the
 // reference is the reference's own sequential fp32 rounding (tests report both against fp64).
+#include <mutex>
+
 #include "common.cuh"
 #include "gae_scan.h"
+
+// Scratch of the allocation-free entry point (areal_b200_gae1d_nolp_misalign_static): the look-back
+// header (64 B) plus one 32-byte descriptor per 2048-token tile, for at most 4,194,304 tokens per
+// call -> 65,600 bytes.  Lives in the module image: every GPU that loads the library holds these
+// 64 KB until the process exits.  This name is a HOST-side stand-in in host code, never a device
+// address; the launcher below resolves it with cudaGetSymbolAddress().
+#define AB_GAE1D_STATIC_MAX_TOKENS (int64_t(1) << 22)
+#define AB_GAE1D_STATIC_SCRATCH_BYTES (64 + (AB_GAE1D_STATIC_MAX_TOKENS / 2048) * 32)
+static __device__ __align__(256) unsigned char g_gae1d_static_scratch[AB_GAE1D_STATIC_SCRATCH_BYTES];
 
 namespace ab {
 namespace {
@@ -454,6 +465,52 @@ int launch_gae1d(const Gae1dParams& p, cudaStream_t stream) {
   const int64_t ntiles = (p.T + kTile - 1) / kTile;
   gae1d_kernel<<<static_cast<unsigned int>(ntiles), kThreads, 0, stream>>>(p);
   return check_launch("gae1d");
+}
+
+// Allocation-free launch: same kernel, look-back descriptors in g_gae1d_static_scratch.
+// Set-up happens on the first call per device (with that device current): the symbol is resolved to
+// its address on THAT device and cached.  Every call then clears the part of the array it is about
+// to use (ticket, done counter and the tile flags must start at zero, and the array still holds
+// whatever the previous call -- possibly a larger or an aborted one -- left there).
+int launch_gae1d_static(Gae1dParams p, cudaStream_t stream) {
+  static_assert(AB_GAE1D_STATIC_SCRATCH_BYTES ==
+                    int64_t(sizeof(WorkspaceHeader)) + (AB_GAE1D_STATIC_MAX_TOKENS / kTile) * int64_t(sizeof(TileDesc)),
+                "static scratch size must match the look-back layout");
+  if (p.T == 0) return kOk;
+  if (p.T > AB_GAE1D_STATIC_MAX_TOKENS) {
+    set_error("gae1d (static scratch): %lld tokens exceed the built-in limit of %lld per call; use "
+              "areal_b200_gae1d_nolp_misalign with a caller-provided workspace",
+              (long long)p.T, (long long)AB_GAE1D_STATIC_MAX_TOKENS);
+    return kInvalidArgument;
+  }
+  constexpr int kMaxDevices = 64;
+  static std::mutex mu;
+  static void* scratch_of_device[kMaxDevices] = {nullptr};
+  int dev = -1;
+  AB_CUDA(cudaGetDevice(&dev));
+  AB_REQUIRE(dev >= 0 && dev < kMaxDevices, "device ordinal %d out of range", dev);
+  void* scratch = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    if (scratch_of_device[dev] == nullptr) {
+      void* addr = nullptr;
+      const cudaError_t e = cudaGetSymbolAddress(&addr, g_gae1d_static_scratch);
+      if (e != cudaSuccess || addr == nullptr) {
+        set_error("cudaGetSymbolAddress(g_gae1d_static_scratch) failed on device %d: %s", dev,
+                  cudaGetErrorString(e));
+        return kCudaError;
+      }
+      scratch_of_device[dev] = addr;
+    }
+    scratch = scratch_of_device[dev];
+  }
+  const int64_t ntiles = (p.T + kTile - 1) / kTile;
+  if (ntiles > 1) {
+    AB_CUDA(cudaMemsetAsync(scratch, 0, sizeof(WorkspaceHeader) + size_t(ntiles) * sizeof(TileDesc), stream));
+  }
+  p.workspace = scratch;
+  gae1d_kernel<<<static_cast<unsigned int>(ntiles), kThreads, 0, stream>>>(p);
+  return check_launch("gae1d (static scratch)");
 }
 
 int launch_gae_padded(const GaePaddedParams& p, cudaStream_t stream) {

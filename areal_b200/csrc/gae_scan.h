@@ -44,6 +44,7 @@ struct Gae2dParams {
 
 int64_t gae1d_workspace_bytes(int64_t T);
 int launch_gae1d(const Gae1dParams& p, cudaStream_t stream);
+int launch_gae1d_static(Gae1dParams p, cudaStream_t stream);   // workspace member is ignored
 int launch_gae_padded(const GaePaddedParams& p, cudaStream_t stream);
 int launch_gae2d_olp(const Gae2dParams& p, cudaStream_t stream);
 

@@ -53,6 +53,30 @@ AREAL_B200_API int areal_b200_gae1d_nolp_misalign(const float* rewards, const fl
                                    double lam, float* adv_out, float* ret_out, void* workspace,
                                    int64_t workspace_bytes, void* stream);
 
+/* Allocation-free variant of areal_b200_gae1d_nolp_misalign.  It has NO counterpart in the
+ * reference; it exists for callers that cannot obtain device scratch themselves: a C/C++ or other
+ * non-PyTorch host that binds this ABI directly and so has no caching allocator to draw from, a
+ * process whose framework has already reserved all of HBM (cudaMalloc would fail or fragment the
+ * pool), and latency-critical threads that must not pay the device-wide synchronisation a
+ * cudaMalloc / cudaFree implies.  Same inputs, outputs and results as the entry above, but the
+ * look-back descriptors live in a 65,600-byte array inside the library image (each GPU that loads
+ * the library keeps it until the process exits) instead of a caller workspace; the call itself
+ * performs no cudaMalloc, cudaFree or any other allocating call.
+ *   Limit: total_tokens <= AREAL_B200_GAE1D_STATIC_MAX_TOKENS per call; larger batches are
+ *   rejected with status 1 and a message (use the workspace entry for those).
+ *   Set-up: the first call on each device (made with that device current) resolves the array's
+ *   device address and caches it; make that first call before starting any stream capture.
+ *   Sharing: all calls on a device use the same array.  It keeps the previous call's contents, so
+ *   each call first clears (stream-ordered) the part it will use.  Two calls that can overlap on
+ *   the GPU -- different streams, or different host threads -- race on it: serialise them. */
+#define AREAL_B200_GAE1D_STATIC_MAX_TOKENS 4194304
+AREAL_B200_API int areal_b200_gae1d_nolp_misalign_static(const float* rewards, const float* values,
+                                                         const int32_t* cu_seqlens,
+                                                         const uint8_t* bootstrap,
+                                                         int64_t total_tokens, int64_t batch_size,
+                                                         double gamma, double lam, float* adv_out,
+                                                         float* ret_out, void* stream);
+
 /* Padded [B,S] masked GAE of areal-lite.  Replaces the Python loop in
  * `PPOActor.compute_advantages` (areal/engine/ppo/actor.py:131-152).
  *   rewards, values, loss_mask f32[B,S] contiguous (loss_mask already rolled by -1, :110; any
