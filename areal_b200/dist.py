@@ -1,0 +1,162 @@
+"""Multi-GPU plumbing of the hot path: one process per GPU, `torch.distributed` (NCCL over
+NVLink 5 / NVSwitch) for the few bytes that must cross ranks.
+
+Two ways the path shards:
+
+* by packed sequence (data parallel, BASELINE.json configs[2]): sequences are independent for GAE and
+  rows are independent for the logits pass, so ranks exchange NO tensors; only the masked-mean
+  normalisation needs the global token count -- one all-reduce of two floats, the same exchange the
+  reference engines do for their loss weight (areal/engine/fsdp_engine.py:518-526).
+* by vocabulary (tensor parallel, configs[3]): every rank streams its `[T, V/R]` shard once
+  (areal_b200_logits_partial_fwd), ranks exchange `[4, T]` f32 partials with ONE all-gather, and each
+  combines locally in a fixed order (areal_b200_vocab_combine) -- the reference needs three
+  all-reduces for the entropy (areal/utils/mcore/functional.py:16-31) plus three inside Megatron's
+  vocab_parallel_cross_entropy.  The backward is local to the shard.
+"""
+from __future__ import annotations
+
+from typing import Callable, List, Optional, Sequence, Tuple
+
+import torch
+import torch.distributed as dist
+
+from . import _lib
+from ._lib import call, ptr, stream_ptr
+
+
+# --------------------------------------------------------------------------------------------------
+# batch (sequence) sharding
+# --------------------------------------------------------------------------------------------------
+def partition_sequences(seqlens: Sequence[int], n_parts: int) -> List[List[int]]:
+    """Token-balanced assignment of whole sequences to ranks (longest-first greedy, like the
+    reference's allocate_balanced_mbs, areal/utils/data.py:240-263).  Returns, per rank, the
+    sequence indices in ascending order; every sequence appears exactly once."""
+    if n_parts <= 0:
+        raise ValueError("n_parts must be positive")
+    order = sorted(range(len(seqlens)), key=lambda i: (-int(seqlens[i]), i))
+    loads = [0] * n_parts
+    parts: List[List[int]] = [[] for _ in range(n_parts)]
+    for i in order:
+        r = min(range(n_parts), key=lambda k: (loads[k], k))
+        parts[r].append(i)
+        loads[r] += int(seqlens[i])
+    return [sorted(p) for p in parts]
+
+
+def take_sequences(x: torch.Tensor, cu_seqlens: torch.Tensor, seq_ids: Sequence[int], extra_per_seq: int = 0):
+    """Packed sub-batch holding the given sequences of `x` (dim 0 packed by `cu_seqlens`).
+    `extra_per_seq=1` is the "misaligned" layout of the GAE values (one bootstrap slot per
+    sequence: sequence i occupies [cu[i]+i, cu[i+1]+i+1)).  Returns (packed, new_cu_seqlens)."""
+    cu = cu_seqlens.tolist()
+    pieces, lens = [], []
+    for i in seq_ids:
+        s = cu[i] + i * extra_per_seq
+        e = cu[i + 1] + (i + 1) * extra_per_seq
+        pieces.append(x[s:e])
+        lens.append(cu[i + 1] - cu[i])
+    out = torch.cat(pieces, 0) if pieces else x[:0]
+    new_cu = torch.zeros(len(lens) + 1, dtype=cu_seqlens.dtype, device=cu_seqlens.device)
+    if lens:
+        new_cu[1:] = torch.tensor(lens, dtype=cu_seqlens.dtype, device=cu_seqlens.device).cumsum(0)
+    return out, new_cu
+
+
+def global_loss_scale(local_count: torch.Tensor, group=None) -> Tuple[torch.Tensor, torch.Tensor]:
+    """(local_count / global_count, global_count) with ONE all-reduce of one float.  Multiply the
+    local masked-mean loss by the first value and sum over ranks to get the global masked mean."""
+    total = local_count.detach().to(torch.float32).reshape(1).clone()
+    if dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(total, group=group)
+    total = torch.clamp(total, min=1.0)
+    return local_count.to(torch.float32) / total[0], total[0]
+
+
+def all_reduce_loss(local_loss: torch.Tensor, local_count: torch.Tensor, group=None) -> torch.Tensor:
+    """Global masked-mean loss from per-rank masked means: one all-reduce of (numerator, count)."""
+    buf = torch.stack([local_loss.detach().float() * local_count.float(), local_count.float()])
+    if dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(buf, group=group)
+    return buf[0] / torch.clamp(buf[1], min=1.0)
+
+
+# --------------------------------------------------------------------------------------------------
+# vocab sharding
+# --------------------------------------------------------------------------------------------------
+def gather_partials(parts: torch.Tensor, group=None) -> torch.Tensor:
+    """[4, T] per rank -> [R, 4, T] in rank order (one all-gather; deterministic combine order)."""
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    if world == 1:
+        return parts.unsqueeze(0)
+    parts = parts.contiguous()
+    out = torch.empty((world * parts.shape[0],) + tuple(parts.shape[1:]), dtype=parts.dtype, device=parts.device)
+    dist.all_gather_into_tensor(out, parts, group=group)
+    return out.view((world,) + tuple(parts.shape))
+
+
+def _cuda_partials(shard: torch.Tensor, labels: torch.Tensor, vocab_start: int, temperature: float) -> torch.Tensor:
+    T, V = shard.shape
+    dev = shard.device
+    parts = torch.empty(4, T, dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        call("areal_b200_logits_partial_fwd", ptr(shard), _lib.DTYPE_CODE[shard.dtype], T, V,
+             shard.stride(0) if T > 1 else V, ptr(labels), int(vocab_start), float(temperature), ptr(parts), None,
+             stream_ptr(dev))
+    return parts
+
+
+def _cuda_combine(all_parts: torch.Tensor, temperature: float):
+    R, _, T = all_parts.shape
+    dev = all_parts.device
+    f32 = dict(dtype=torch.float32, device=dev)
+    logp, ent, row_max, ln_s = (torch.empty(T, **f32) for _ in range(4))
+    with torch.cuda.device(dev):
+        call("areal_b200_vocab_combine", ptr(all_parts), R, T, float(temperature), ptr(logp), ptr(ent),
+             ptr(row_max), ptr(ln_s), stream_ptr(dev))
+    return logp, ent, row_max, ln_s
+
+
+def vocab_parallel_forward(shard: torch.Tensor, labels: torch.Tensor, vocab_start: int, temperature: float,
+                           group=None, partials_fn: Optional[Callable] = None,
+                           combine_fn: Optional[Callable] = None):
+    """partial kernel -> all-gather -> combine.  `partials_fn` / `combine_fn` default to the CUDA
+    kernels; tests inject CPU stand-ins to exercise the collective protocol under gloo."""
+    parts = (partials_fn or _cuda_partials)(shard, labels, vocab_start, temperature)
+    allp = gather_partials(parts, group)
+    return (combine_fn or _cuda_combine)(allp, temperature)
+
+
+class _VocabParallelLogprobsEntropy(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, shard, labels, vocab_start, temperature, group):
+        if shard.dim() != 2 or shard.stride(1) != 1:
+            shard = shard.reshape(-1, shard.shape[-1]).contiguous()
+        _lib.require_cuda(shard, labels)
+        lab = labels.reshape(-1).long().contiguous()
+        logp, ent, row_max, ln_s = vocab_parallel_forward(shard, lab, vocab_start, temperature, group)
+        ctx.save_for_backward(shard, lab, row_max, ln_s, ent)
+        ctx.vocab_start, ctx.temperature = int(vocab_start), float(temperature)
+        ctx.set_materialize_grads(False)
+        return logp, ent
+
+    @staticmethod
+    def backward(ctx, g_logp, g_ent):
+        shard, lab, row_max, ln_s, ent = ctx.saved_tensors
+        if g_logp is None and g_ent is None:
+            return None, None, None, None, None
+        from .functional import _f32, _logits_backward
+        gl = None if g_logp is None else _f32(g_logp.reshape(-1))
+        gh = None if g_ent is None else _f32(g_ent.reshape(-1))
+        d = _logits_backward(shard, lab, ctx.temperature, row_max, ln_s, ent, gl, gh, vocab_start=ctx.vocab_start)
+        return d, None, None, None, None
+
+
+def vocab_parallel_logprobs_entropy(shard_logits: torch.Tensor, labels: torch.Tensor, temperature: float = 1.0,
+                                    group=None, vocab_start: Optional[int] = None):
+    """Log-prob of `labels` (GLOBAL vocabulary ids) and entropy from vocab-sharded logits
+    `[T, V/R]`; replaces the Megatron-TP branch of gather_logprobs_entropy
+    (areal/utils/functional.py:91-98).  `vocab_start` defaults to rank * shard_width.  Every rank gets
+    the full `[T]` results (as after the reference's all-reduces); gradients flow to the local shard."""
+    if vocab_start is None:
+        rank = dist.get_rank(group) if dist.is_initialized() else 0
+        vocab_start = rank * shard_logits.shape[-1]
+    return _VocabParallelLogprobsEntropy.apply(shard_logits, labels, vocab_start, temperature, group)

@@ -417,3 +417,34 @@ def make_intervals(maxsize: int, n_intervals: int, rng: np.random.RandomState):
                    np.arange(n_intervals, dtype=np.int64) * s + s // 2], axis=1)
     rng.shuffle(iv)
     return iv, n_intervals * (s // 2), s // 2
+
+
+def shard_partials(logits_shard, labels, vocab_start: int, temperature: float) -> np.ndarray:
+    """Per-shard partials in the layout of `areal_b200_logits_partial_fwd` ([4,T] rows: raw max m,
+    S = sum 2^t, W = sum 2^t * t with t = (x - m) * log2(e)/temperature, raw label logit or 0) -- the
+    same information as vocab_parallel_partials() above (reference: areal/utils/mcore/functional.py:15-34),
+    shifted by the shard max so that every term stays small."""
+    x = np.asarray(logits_shard).astype(np.float32).astype(np.float64)
+    c2 = math.log2(math.e) / temperature
+    m = x.max(axis=-1)
+    t = (x - m[:, None]) * c2
+    e = np.exp2(t)
+    lab = np.asarray(labels, dtype=np.int64) - vocab_start
+    local = (lab >= 0) & (lab < x.shape[1])
+    xl = np.where(local, x[np.arange(x.shape[0]), np.clip(lab, 0, x.shape[1] - 1)], 0.0)
+    return np.stack([m, e.sum(-1), (e * t).sum(-1), xl])
+
+
+def combine_partials(all_parts: np.ndarray, temperature: float):
+    """[R,4,T] -> (logp, entropy, row_max, ln_sumexp): the math of `areal_b200_vocab_combine`
+    (all_reduce(MAX) + rescale + all_reduce(SUM) in the reference, mcore/functional.py:16-31)."""
+    p = np.asarray(all_parts, dtype=np.float64)
+    c2 = math.log2(math.e) / temperature
+    M = p[:, 0].max(axis=0)
+    d = (p[:, 0] - M) * c2
+    f = np.exp2(d)
+    S = (p[:, 1] * f).sum(0)
+    W = (f * (p[:, 2] + d * p[:, 1])).sum(0)
+    XL = p[:, 3].sum(0)
+    ln_s = np.log(S)
+    return (XL - M) / temperature - ln_s, ln_s - math.log(2.0) * W / S, M, ln_s
