@@ -162,10 +162,11 @@ def run_ours(args):
     red = torch.zeros(2, dtype=torch.float32, device=dev)
 
     ev = {k: [] for k in ("start", "gae", "fwd", "bwd")}
+    pool = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(args.steps)]
 
     def step(record=False):
         if record:
-            e = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+            e = pool[len(ev["start"])]
             e[0].record()
         adv_gae, ret = P.cugae1d_nolp_misalign_func(b["rewards"], b["values"], b["cu_seqlens"], b["bootstrap"], GAMMA, LAM)
         if record:
@@ -193,17 +194,20 @@ def run_ours(args):
 
     for _ in range(max(args.warmup, 3)):
         step()
-    sampler = ClockSampler(local_rank)
-    sampler.start()
+    sampler = ClockSampler(local_rank, period=float(os.environ.get('BENCH_CLOCK_PERIOD', '0.02')))
+    if os.environ.get('BENCH_NO_SAMPLER') != '1':
+        sampler.start()
     sync_all()
     t0 = time.perf_counter()
     e_start = torch.cuda.Event(enable_timing=True)
     e_stop = torch.cuda.Event(enable_timing=True)
     torch.cuda.profiler.start()      # ncu --profile-from-start off captures exactly the timed region
     e_start.record()
+    h0 = time.perf_counter()
     for _ in range(args.steps):
         loss, st = step(record=True)
     e_stop.record()
+    host_ms = (time.perf_counter() - h0) * 1e3 / args.steps     # CPU enqueue time per step
     sync_all()
     torch.cuda.profiler.stop()
     t1 = time.perf_counter()
@@ -217,9 +221,14 @@ def run_ours(args):
     value = world * T / (ms_step * 1e-3)
 
     # per-kernel device times inside the timed region
-    def avg(a, c):
-        return float(np.mean([x.elapsed_time(y) for x, y in zip(ev[a], ev[c])]))
-    ms_gae, ms_fwd, ms_bwd = avg("start", "gae"), avg("gae", "fwd"), avg("fwd", "bwd")
+    def spread(a, c):
+        v = sorted(x.elapsed_time(y) for x, y in zip(ev[a], ev[c]))
+        return {"min": v[0], "median": v[len(v) // 2], "mean": float(np.mean(v)), "max": v[-1]}
+    spreads = {"gae": spread("start", "gae"), "fwd": spread("gae", "fwd"), "bwd": spread("fwd", "bwd")}
+    # per-kernel launch duration = MEDIAN over the timed steps of the event-to-event gap on the launch
+    # stream (the mean also counts the host's launch latency whenever the queue runs dry, e.g. on the
+    # first timed step right after the barrier; both are reported in kernel_ms_spread)
+    ms_gae, ms_fwd, ms_bwd = spreads["gae"]["median"], spreads["fwd"]["median"], spreads["bwd"]["median"]
     coef_rows = int(torch.count_nonzero(logits.grad[:, :8].float().abs().sum(-1)).item()) if T else 0
     active = coef_rows / T
     peak, peak_src = measured_peaks()
@@ -265,12 +274,13 @@ def run_ours(args):
                    "l2": "inputs (4.98 GB logits per GPU) larger than the 126 MB L2; no flush needed",
                    "loss_cfg": {k: v for k, v in CFG.items()}, "temperature": TEMPERATURE},
         "roofline": roof, "roofline_fwd": roof_fwd, "roofline_gae": roof_gae,
-        "e2e": e2e, "gpu_launches": 3 * args.steps, "clocks": clocks,
+        "e2e": e2e, "gpu_launches": 3 * args.steps, "clocks": clocks, "host_enqueue_ms_per_step": host_ms,
+        "kernel_ms_spread": spreads,
         "loss": float(loss.detach()),
     }
     if world == 1 and not args.skip_cpu:
         line["cpu_baseline"] = cpu_baseline()
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 
@@ -370,13 +380,26 @@ def run_reference(args):
                                    "(packed GAE + logprob/entropy/PPO loss fwd + bwd)"},
             "cpu_baseline": cb,
             "e2e": {"value": v, "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    emit(line)
+
+
+def emit(line: dict):
+    """Print exactly one JSON line on the real stdout (fd 1 was pointed at stderr in main(), so NCCL /
+    library chatter cannot pollute it)."""
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
+
+
+_REAL_STDOUT = 1
 
 
 def main():
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--skip-e2e", action="store_true", help="profiling runs: skip the host-buffer leg")

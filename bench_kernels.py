@@ -1,0 +1,287 @@
+#!/usr/bin/env python
+"""Per-kernel measurements for DESIGN.md / profiles/ (NOT the driver's bench contract -- that is
+bench.py).  Times every kernel family alone with CUDA events after warm-up, inputs larger than L2 or L2
+flushed between iterations, and -- where present -- the reference's own CUDA kernels rebuilt for
+sm_100a (oracle/_ref/*.so, timing baseline only) and the reference-style torch path.
+
+    python bench_kernels.py [--what gae,padded,intervals,logits,loss,ref] [--out file.json]
+"""
+import argparse
+import glob
+import importlib.util
+import json
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+from areal_b200 import flatten_param as fp  # noqa: E402
+from areal_b200 import functional as F  # noqa: E402
+from areal_b200 import ppo_functional as P  # noqa: E402
+
+DEV = torch.device("cuda:0")
+PEAK = 6539.9
+try:
+    PEAK = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
+except Exception:
+    pass
+_flush = None
+
+
+def flush_l2():
+    global _flush
+    if _flush is None:
+        _flush = torch.empty(256 << 20, dtype=torch.uint8, device=DEV)
+    _flush.zero_()
+
+
+def timeit(fn, iters=20, warmup=5, flush=False):
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    ts = []
+    for _ in range(iters):
+        if flush:
+            flush_l2()
+        e0 = torch.cuda.Event(enable_timing=True)
+        e1 = torch.cuda.Event(enable_timing=True)
+        e0.record()
+        fn()
+        e1.record()
+        torch.cuda.synchronize()
+        ts.append(e0.elapsed_time(e1))
+    ts.sort()
+    return ts[len(ts) // 2]
+
+
+def load_ref(name):
+    so = glob.glob(os.path.join(ROOT, "oracle", "_ref", name + "*.so"))
+    if not so:
+        return None
+    spec = importlib.util.spec_from_file_location(name, so[0])
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def row(name, ms, bytes_, **kw):
+    gbs = bytes_ / (ms * 1e-3) / 1e9
+    d = dict(kernel=name, ms=round(ms, 5), algorithmic_bytes=int(bytes_), gbs=round(gbs, 1),
+             frac_of_measured_peak=round(gbs / PEAK, 4), **kw)
+    print(json.dumps(d), flush=True)
+    return d
+
+
+def make_packed(T, rng, lo=128, hi=4097):
+    lens, left = [], T
+    while left > 0:
+        n = min(left, int(rng.randint(lo, hi)))
+        lens.append(n)
+        left -= n
+    return np.array(lens)
+
+
+def bench_gae(out, ref):
+    rng = np.random.RandomState(0)
+    for logT in (15, 17, 20, 22, 24, 26, 27):
+        T = 1 << logT
+        lens = make_packed(T, rng)
+        B = len(lens)
+        cu = torch.from_numpy(np.concatenate([[0], np.cumsum(lens)]).astype(np.int32)).to(DEV)
+        r = torch.randn(T, device=DEV)
+        v = torch.randn(T + B, device=DEV)
+        boot = torch.rand(B, device=DEV) > 0.5
+        small = (16 * T) < (200 << 20)
+        ms = timeit(lambda: P.gae_1d_nolp_misalign(r, v, cu, boot, 1.0, 0.95), flush=small)
+        out.append(row("gae1d", ms, 16 * T + 9 * B + 4, T=T, B=B, tokens_per_s=T / (ms * 1e-3), l2_flushed=small))
+        if ref is not None and logT <= 24:
+            msr = timeit(lambda: ref.gae_1d_nolp_misalign(r, v, cu, boot, 1.0, 0.95), iters=5, warmup=2, flush=small)
+            out.append(row("reference gae_1d_nolp_misalign (sm_100a rebuild)", msr, 16 * T + 9 * B + 4, T=T, B=B,
+                           tokens_per_s=T / (msr * 1e-3), speedup_ours=msr / ms))
+        del r, v
+
+
+def bench_padded(out):
+    rng = np.random.RandomState(1)
+    for B, S in ((16, 32768), (512, 4096), (4096, 4096)):
+        r = torch.randn(B, S, device=DEV)
+        v = torch.randn(B, S, device=DEV)
+        m = (torch.rand(B, S, device=DEV) > 0.2).float()
+        ne = torch.rand(B, device=DEV) > 0.5
+        small = 20 * B * S < (200 << 20)
+        ms = timeit(lambda: P.gae_padded_masked(r, v, m, ne, 1.0, 0.95), flush=small)
+        out.append(row("gae_padded_masked", ms, 20 * B * S, B=B, S=S, tokens_per_s=B * S / (ms * 1e-3)))
+        if B * S <= 16 * 32768:
+            # the reference: PPOActor.compute_advantages' python loop, restated with torch ops on the GPU
+            def ref_loop():
+                last = torch.zeros(B, device=DEV)
+                nv = v[:, S - 1] * ne
+                adv_rev = [last]
+                for t in reversed(range(S - 1)):
+                    delta = r[:, t] + 1.0 * nv - v[:, t]
+                    new = delta + 0.95 * last
+                    mk = m[:, t]
+                    nv = nv * (1 - mk) + v[:, t] * mk
+                    last = last * (1 - mk) + new * mk
+                    adv_rev.append(last)
+                return torch.stack(adv_rev[::-1], dim=1)
+            msr = timeit(ref_loop, iters=1, warmup=0)
+            out.append(row("reference padded GAE python loop (torch CUDA ops)", msr, 20 * B * S, B=B, S=S,
+                           tokens_per_s=B * S / (msr * 1e-3), speedup_ours=msr / ms))
+
+
+def bench_intervals(out, ref):
+    rng = np.random.RandomState(0)
+    n_elem = int(os.environ.get("INTERVAL_BUFFER_ELEMS", 7_600_000_000))   # cfg 5: 7B-sized flat bf16 buffer
+    src = torch.empty(n_elem, dtype=torch.bfloat16, device=DEV)
+    src.view(torch.int16).random_(-30000, 30000)
+    for n in (1000, 4000, 10000, 100000):
+        s = n_elem // n
+        iv = np.stack([np.arange(n, dtype=np.int64) * s, np.arange(n, dtype=np.int64) * s + s // 2], 1)
+        rng.shuffle(iv)
+        total = n * (s // 2)
+        ivc = torch.from_numpy(iv).to(DEV)
+        ms = timeit(lambda: fp.slice_intervals_bf16(src, ivc, total, s // 2), iters=8, warmup=2)
+        out.append(row("slice_intervals", ms, 4 * total + 16 * n, n_intervals=n, interval_elems=s // 2))
+        packed = fp.slice_intervals_bf16(src, ivc, total, s // 2)
+        ms = timeit(lambda: fp.set_intervals_bf16(packed, src, ivc, s // 2), iters=8, warmup=2)
+        out.append(row("set_intervals", ms, 4 * total + 16 * n, n_intervals=n, interval_elems=s // 2))
+        if ref is not None and n >= 1000:
+            msr = timeit(lambda: ref.slice_intervals_bf16(src, ivc, total, s // 2), iters=3, warmup=1)
+            out.append(row("reference slice_intervals_bf16 (sm_100a rebuild)", msr, 4 * total + 16 * n,
+                           n_intervals=n, speedup_ours=msr / ms))
+        del packed
+    # realistic: TP 1->2 reshard of a Qwen2.5-7B-shaped model: per layer 2 x 3584 row-split intervals
+    rows = []
+    base = 0
+    for layer in range(28):
+        for width in (3584, 18944):          # o_proj [3584,3584], down_proj [3584,18944] split on dim 1
+            for rr in range(3584):
+                rows.append((base + rr * width + width // 2, base + (rr + 1) * width))
+            base += 3584 * width
+    iv = np.array(rows, dtype=np.int64)
+    total = int((iv[:, 1] - iv[:, 0]).sum())
+    ivc = torch.from_numpy(iv).to(DEV)
+    ms = timeit(lambda: fp.slice_intervals_bf16(src, ivc, total, 9472), iters=8, warmup=2)
+    out.append(row("slice_intervals (7B TP reshard rows)", ms, 4 * total + 16 * len(rows), n_intervals=len(rows)))
+    if ref is not None:
+        msr = timeit(lambda: ref.slice_intervals_bf16(src, ivc, total, 9472), iters=3, warmup=1)
+        out.append(row("reference slice_intervals_bf16 (7B TP reshard rows)", msr, 4 * total + 16 * len(rows),
+                       n_intervals=len(rows), speedup_ours=msr / ms))
+    # misaligned (odd element offsets): 2-byte relative alignment
+    iv = np.stack([np.arange(100000, dtype=np.int64) * 20000 + 1, np.arange(100000, dtype=np.int64) * 20000 + 9000], 1)
+    total = int((iv[:, 1] - iv[:, 0]).sum())
+    ivc = torch.from_numpy(iv).to(DEV)
+    ms = timeit(lambda: fp.slice_intervals_bf16(src, ivc, total, 9000), iters=8, warmup=2)
+    out.append(row("slice_intervals (odd offsets, 2-byte relative alignment)", ms, 4 * total + 16 * 100000,
+                   n_intervals=100000))
+    del src
+
+
+def bench_logits(out):
+    T, V = 16384, 151936
+    g = torch.Generator(device=DEV).manual_seed(0)
+    logits = torch.empty(T, V, dtype=torch.bfloat16, device=DEV)
+    for i in range(0, T, 2048):
+        logits[i:i + 2048] = (torch.randn(2048, V, generator=g, device=DEV) * 2).bfloat16()
+    labels = torch.randint(0, V, (T,), generator=g, device=DEV)
+    ms = timeit(lambda: F.gather_logprobs(logits, labels, 1.0))
+    out.append(row("logits_fwd (logp only)", ms, 2 * T * V, tokens_per_s=T / (ms * 1e-3)))
+    ms = timeit(lambda: F.gather_logprobs_entropy(logits, labels, 1.0))
+    out.append(row("logits_fwd (logp+entropy)", ms, 2 * T * V, tokens_per_s=T / (ms * 1e-3)))
+    ms = timeit(lambda: F.logits_stats(logits, labels, 1.0))
+    out.append(row("logits_fwd (logp+entropy+min/max)", ms, 2 * T * V, tokens_per_s=T / (ms * 1e-3)))
+    x = logits.requires_grad_()
+    lp, ent = F.gather_logprobs_entropy(x, labels, 1.0)
+    w = torch.randn(T, device=DEV)
+    for frac in (1.0, 0.8, 0.5):
+        ww = w.clone()
+        ww[torch.rand(T, device=DEV) > frac] = 0
+        act = float((ww != 0).float().mean())
+        ms = timeit(lambda: torch.autograd.grad((lp * ww).sum(), x, retain_graph=True), iters=10, warmup=3)
+        out.append(row("logits_bwd", ms, 2 * T * V * (1 + act), active_rows=act, tokens_per_s=T / (ms * 1e-3)))
+    wh = torch.randn(T, device=DEV)
+    ms = timeit(lambda: torch.autograd.grad((lp * w).sum() + (ent * wh).sum(), x, retain_graph=True), iters=10, warmup=3)
+    out.append(row("logits_bwd (with entropy gradient)", ms, 4 * T * V, tokens_per_s=T / (ms * 1e-3)))
+    del lp, ent
+    # the reference path on the GPU: eager (what torch.compile fuses), 1024-row chunks, fwd and fwd+bwd
+    def ref_fwd(xx):
+        lps, ents = [], []
+        for i in range(0, T, 1024):
+            lsm = torch.nn.functional.log_softmax(xx[i:i + 1024].float() / 1.0, dim=-1)
+            ents.append(-torch.sum(lsm.exp() * lsm, dim=-1))
+            lps.append(lsm.gather(-1, labels[i:i + 1024].unsqueeze(-1)).squeeze(-1))
+        return torch.cat(lps), torch.cat(ents)
+    with torch.no_grad():
+        ms = timeit(lambda: ref_fwd(logits), iters=5, warmup=2)
+    out.append(row("reference eager gather_logprobs_entropy fwd (torch CUDA)", ms, 2 * T * V, tokens_per_s=T / (ms * 1e-3)))
+    def ref_fb():
+        x.grad = None
+        a, b = ref_fwd(x)
+        (a * w).sum().backward()
+    ms = timeit(ref_fb, iters=3, warmup=1)
+    out.append(row("reference eager fwd+bwd (torch CUDA)", ms, 6 * T * V, tokens_per_s=T / (ms * 1e-3)))
+    try:
+        cfwd = torch.compile(lambda xx, ll: (lambda lsm: (lsm.gather(-1, ll.unsqueeze(-1)).squeeze(-1),
+                                                           -torch.sum(lsm.exp() * lsm, dim=-1)))(
+            torch.nn.functional.log_softmax(xx.float() / 1.0, dim=-1)))
+        def comp_fwd():
+            return [cfwd(logits[i:i + 1024], labels[i:i + 1024]) for i in range(0, T, 1024)]
+        with torch.no_grad():
+            ms = timeit(comp_fwd, iters=5, warmup=3)
+        out.append(row("reference torch.compile gather_logprobs_entropy fwd", ms, 2 * T * V, tokens_per_s=T / (ms * 1e-3)))
+    except Exception as e:
+        print("torch.compile reference unavailable:", repr(e)[:200])
+    x.grad = None
+    # fp32 logits (Megatron path) and misaligned rows take the generic kernel
+    Tf = 2048
+    lf = torch.randn(Tf, V, device=DEV)
+    ms = timeit(lambda: F.gather_logprobs_entropy(lf, labels[:Tf], 1.0))
+    out.append(row("logits_fwd generic kernel (fp32 logits)", ms, 4 * Tf * V, tokens_per_s=Tf / (ms * 1e-3)))
+    odd = logits.detach()[:Tf, 1:V - 7]
+    ms = timeit(lambda: F.gather_logprobs_entropy(odd, labels[:Tf] % (V - 8), 1.0))
+    out.append(row("logits_fwd generic kernel (bf16, misaligned rows)", ms, 2 * Tf * (V - 8), tokens_per_s=Tf / (ms * 1e-3)))
+
+
+def bench_loss(out):
+    for T in (16384, 131072, 1 << 22):
+        lp = -torch.rand(T, device=DEV) * 5
+        prox = lp + 0.02 * torch.randn(T, device=DEV)
+        old = lp + 0.05 * torch.randn(T, device=DEV)
+        adv = torch.randn(T, device=DEV)
+        mask = torch.rand(T, device=DEV) > 0.3
+        ms = timeit(lambda: F.ppo_actor_loss_fn(lp, prox, old, adv, 0.4, mask, behav_imp_weight_cap=5.0), flush=T < (1 << 22))
+        out.append(row("ppo_actor_loss", ms, 45 * T, T=T, tokens_per_s=T / (ms * 1e-3)))
+        v = torch.randn(T, device=DEV)
+        ms = timeit(lambda: F.ppo_critic_loss_fn(v, v + 0.1, v - 0.2, 0.5, mask), flush=T < (1 << 22))
+        out.append(row("ppo_critic_loss", ms, 22 * T, T=T, tokens_per_s=T / (ms * 1e-3)))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--what", default="gae,padded,loss,logits,intervals")
+    ap.add_argument("--out", default=None)
+    args = ap.parse_args()
+    what = set(args.what.split(","))
+    out = []
+    ref_gae = load_ref("ref_cugae") if "ref" in what or True else None
+    ref_iop = load_ref("ref_interval_op_cuda")
+    if "gae" in what:
+        bench_gae(out, ref_gae)
+    if "padded" in what:
+        bench_padded(out)
+    if "loss" in what:
+        bench_loss(out)
+    if "logits" in what:
+        bench_logits(out)
+    if "intervals" in what:
+        bench_intervals(out, ref_iop)
+    if args.out:
+        json.dump(out, open(args.out, "w"), indent=1)
+
+
+if __name__ == "__main__":
+    main()
