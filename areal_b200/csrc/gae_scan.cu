@@ -109,23 +109,16 @@ __global__ void __launch_bounds__(kThreads)
 gae1d_kernel(const Gae1dParams p) {
   __shared__ Affine wsm[kWarps];
   __shared__ double carry_sm;
-  __shared__ unsigned int tile_sm;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int64_t ntiles = (p.T + kTile - 1) / kTile;
-  WorkspaceHeader* hdr = reinterpret_cast<WorkspaceHeader*>(p.workspace);
   TileDesc* desc = reinterpret_cast<TileDesc*>(reinterpret_cast<char*>(p.workspace) + sizeof(WorkspaceHeader));
 
-  // tickets are issued right-to-left: ticket 0 is the LAST tile, so a tile only ever waits on tiles
-  // whose CTAs already started (forward progress without co-residency assumptions).
-  int64_t tile;
-  if (ntiles == 1) {
-    tile = 0;
-  } else {
-    if (tid == 0) tile_sm = atomicAdd(&hdr->ticket, 1u);
-    __syncthreads();
-    tile = ntiles - 1 - int64_t(tile_sm);
-  }
+  // Tiles are taken right-to-left in blockIdx order: block 0 owns the LAST tile, so a tile only waits
+  // on tiles of lower-numbered blocks.  Like CUB's decoupled look-back scan this relies on the
+  // hardware dispatching thread blocks in increasing blockIdx order (waiting never blocks a
+  // predecessor from being scheduled).
+  const int64_t tile = ntiles - 1 - int64_t(blockIdx.x);
 
   const int64_t j0 = tile * kTile + int64_t(tid) * kItems;
   int nvalid = 0;
@@ -136,15 +129,7 @@ gae1d_kernel(const Gae1dParams p) {
   const double gl = double(p.gl);
 
   if (nvalid > 0) {
-    // sequence of the first token: smallest i with cu[i+1] > j0
-    int64_t lo = 0, hi = p.B - 1;
-    while (lo < hi) {
-      const int64_t mid = (lo + hi) >> 1;
-      if (int64_t(p.cu[mid + 1]) > j0) hi = mid; else lo = mid + 1;
-    }
-    int64_t seq = lo;
-    int64_t cu_next = p.cu[seq + 1];
-
+    // rewards do not depend on the sequence lookup: get them in flight first
     if (p.vec_ok && nvalid == kItems) {
       const float4 a = __ldg(reinterpret_cast<const float4*>(p.rewards + j0));
       const float4 b = __ldg(reinterpret_cast<const float4*>(p.rewards + j0) + 1);
@@ -154,6 +139,14 @@ gae1d_kernel(const Gae1dParams p) {
 #pragma unroll
       for (int k = 0; k < kItems; ++k) r[k] = (k < nvalid) ? __ldg(p.rewards + j0 + k) : 0.f;
     }
+    // sequence of the first token: smallest i with cu[i+1] > j0
+    int64_t lo = 0, hi = p.B - 1;
+    while (lo < hi) {
+      const int64_t mid = (lo + hi) >> 1;
+      if (int64_t(__ldg(p.cu + mid + 1)) > j0) hi = mid; else lo = mid + 1;
+    }
+    int64_t seq = lo;
+    int64_t cu_next = __ldg(p.cu + seq + 1);
     float vprev = 0.f;
     bool chain = false;       // vprev holds values[j + seq] for the current token
 #pragma unroll
@@ -260,22 +253,6 @@ gae1d_kernel(const Gae1dParams p) {
     }
   }
 
-  // the last CTA to finish leaves the workspace zeroed for the next call
-  if (ntiles > 1) {
-    __syncthreads();
-    if (tid == 0) {
-      __threadfence();
-      tile_sm = atomicAdd(&hdr->done, 1u);
-    }
-    __syncthreads();
-    if (tile_sm == static_cast<unsigned int>(ntiles - 1)) {
-      for (int64_t k = tid; k < ntiles; k += kThreads) desc[k].flag = 0u;
-      if (tid == 0) {
-        hdr->ticket = 0u;
-        hdr->done = 0u;
-      }
-    }
-  }
 }
 
 // ---- padded [B,S] masked (areal-lite) ----------------------------------------------------------------
@@ -463,6 +440,10 @@ int64_t gae1d_workspace_bytes(int64_t T) {
 int launch_gae1d(const Gae1dParams& p, cudaStream_t stream) {
   if (p.T == 0) return kOk;
   const int64_t ntiles = (p.T + kTile - 1) / kTile;
+  if (ntiles > 1) {
+    // the tile flags must start at zero: clear exactly the descriptors this launch uses
+    AB_CUDA(cudaMemsetAsync(p.workspace, 0, sizeof(WorkspaceHeader) + size_t(ntiles) * sizeof(TileDesc), stream));
+  }
   gae1d_kernel<<<static_cast<unsigned int>(ntiles), kThreads, 0, stream>>>(p);
   return check_launch("gae1d");
 }

@@ -14,7 +14,7 @@ struct Gae1dParams {
   float gl;                  // (float)(gamma * lam), product taken in double like the Python reference
   float* adv;
   float* ret;
-  void* workspace;           // look-back descriptors, zeroed before first use (self-cleaning)
+  void* workspace;           // look-back descriptors; cleared by the launcher (stream-ordered)
   int vec_ok;                // rewards / adv / ret 16-byte aligned
 };
 

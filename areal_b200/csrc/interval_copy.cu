@@ -121,16 +121,18 @@ __device__ __forceinline__ void warp_copy_vec(char* d, const char* s, int64_t n,
   const int64_t nv = n / W;
   const V* sv = reinterpret_cast<const V*>(s);
   V* dv = reinterpret_cast<V*>(d);
-  int64_t i = lane;
+  // batches of 8 vectors per lane: all loads of a batch are issued before its first store, for
+  // short pieces too (a 3.5 KB row is one partially filled batch, not 7 dependent round trips)
   constexpr int kUnroll = 8;
-  for (; i + (kUnroll - 1) * 32 < nv; i += kUnroll * 32) {
+  for (int64_t base = lane; base < nv; base += kUnroll * 32) {
     V t[kUnroll];
 #pragma unroll
-    for (int u = 0; u < kUnroll; ++u) t[u] = ld_stream<V>(sv + i + u * 32);
+    for (int u = 0; u < kUnroll; ++u)
+      if (base + u * 32 < nv) t[u] = ld_stream<V>(sv + base + u * 32);
 #pragma unroll
-    for (int u = 0; u < kUnroll; ++u) st_stream<V>(dv + i + u * 32, t[u]);
+    for (int u = 0; u < kUnroll; ++u)
+      if (base + u * 32 < nv) st_stream<V>(dv + base + u * 32, t[u]);
   }
-  for (; i < nv; i += 32) st_stream<V>(dv + i, ld_stream<V>(sv + i));
   if (W > 1) {
     const int64_t done = nv * W;
     const int64_t tail = n - done;

@@ -9,8 +9,10 @@
  * "Reference" citations are relative to the root of JamesKrW/AReaL.
  *
  * Workspaces: entry points that take `workspace` need `*_workspace_bytes()` bytes of device
- * memory that the caller ZEROES ONCE after allocation; the kernels leave it zeroed, so one
- * workspace can be reused by successive calls on the same stream (not by concurrent calls).
+ * memory.  The loss / fused entry points need it ZEROED ONCE after allocation and leave it
+ * zeroed; the GAE and interval entry points initialise what they use themselves (stream-ordered).
+ * One workspace can be reused by successive calls on the same stream, never by calls that may
+ * overlap on the GPU.
  */
 #ifndef AREAL_B200_H_
 #define AREAL_B200_H_
