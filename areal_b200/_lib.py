@@ -32,6 +32,7 @@ SIGNATURES = {
     "areal_b200_logits_bwd": (c_int, [P, c_int, I64, I64, I64, P, I64, F64, P, P, P, P, P, P, P, P, I64, P]),
     "areal_b200_logits_partial_fwd": (c_int, [P, c_int, I64, I64, I64, P, I64, F64, P, P, P]),
     "areal_b200_vocab_combine": (c_int, [P, I64, I64, F64, P, P, P, P, P]),
+    "areal_b200_legacy_entropy": (c_int, [P, c_int, I64, I64, I64, P, P, F64, P, P]),
     "areal_b200_loss_workspace_bytes": (I64, []),
     "areal_b200_ppo_actor_loss": (c_int, [P, P, P, P, P, I64, F64, F64, F64, F64,
                                           P, P, P, P, P, P, P, P, P, P, P, P, I64, P]),

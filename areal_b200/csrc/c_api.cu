@@ -290,6 +290,18 @@ AREAL_B200_API int areal_b200_logits_bwd(const void* logits, int dtype, int64_t 
   return launch_logits_bwd(p, static_cast<cudaStream_t>(stream));
 }
 
+AREAL_B200_API int areal_b200_legacy_entropy(const void* logits, int dtype, int64_t T, int64_t V,
+                                             int64_t row_stride, const float* row_max,
+                                             const float* ln_sumexp, double eps, float* entropy_out,
+                                             void* stream) {
+  AB_REQUIRE(T >= 0 && V > 0, "bad shape T=%lld V=%lld", (long long)T, (long long)V);
+  AB_REQUIRE(dtype_size(dtype) != 0, "unsupported dtype %d", dtype);
+  AB_REQUIRE(row_stride >= V, "row_stride < V");
+  AB_REQUIRE(T == 0 || (logits && row_max && ln_sumexp && entropy_out), "null pointer");
+  return launch_legacy_entropy(logits, dtype, T, V, row_stride * dtype_size(dtype), row_max, ln_sumexp,
+                               static_cast<float>(eps), entropy_out, static_cast<cudaStream_t>(stream));
+}
+
 // ---- P3 ------------------------------------------------------------------------------------------
 AREAL_B200_API int64_t areal_b200_loss_workspace_bytes(void) {
   const int64_t a = loss_workspace_bytes(), b = logits_loss_workspace_bytes();

@@ -577,6 +577,36 @@ logits_bwd_generic_kernel(const LogitsBwdParams p) {
   }
 }
 
+// ---- legacy entropy: -sum p * log(p + 1e-7)  (realhf calc_entropy) ----------------------------------
+// Second, read-only pass given the row statistics of the forward; one CTA per row.
+template <typename T>
+__global__ void __launch_bounds__(kConsumers)
+legacy_entropy_kernel(const void* __restrict__ logits, int64_t T_rows, int64_t V, int64_t row_stride_bytes,
+                      const float* __restrict__ row_max, const float* __restrict__ ln_s, float eps,
+                      float* __restrict__ out) {
+  __shared__ float red[kConsumerWarps];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  for (int64_t row = blockIdx.x; row < T_rows; row += gridDim.x) {
+    const T* x = reinterpret_cast<const T*>(reinterpret_cast<const char*>(logits) + row * row_stride_bytes);
+    const float m = row_max[row];
+    const float nl2s = -ln_s[row] * kLog2e;
+    float acc = 0.f;
+    for (int64_t i = tid; i < V; i += kConsumers) {
+      const float pv = ex2_approx(fmaf(to_f32<T>(x[i]) - m, kLog2e, nl2s));
+      acc = fmaf(pv, lg2_approx(pv + eps), acc);
+    }
+    acc = warp_sum(acc);
+    if (lane == 0) red[warp] = acc;
+    __syncthreads();
+    if (tid == 0) {
+      float t = 0.f;
+      for (int w = 0; w < kConsumerWarps; ++w) t += red[w];
+      out[row] = -t * kLn2;
+    }
+    __syncthreads();
+  }
+}
+
 // ---- cross-shard combine (vocab-sharded path) ----------------------------------------------------
 __global__ void vocab_combine_kernel(const float* __restrict__ parts, int R, int64_t T,
                                      float inv_t, float* __restrict__ logp,
@@ -659,6 +689,20 @@ int launch_logits_bwd(const LogitsBwdParams& p, cudaStream_t stream) {
     else logits_bwd_generic_kernel<float><<<grid, kConsumers, 0, stream>>>(p);
   }
   return check_launch("logits_bwd");
+}
+
+int launch_legacy_entropy(const void* logits, int dtype, int64_t T, int64_t V, int64_t row_stride_bytes,
+                          const float* row_max, const float* ln_s, float eps, float* out,
+                          cudaStream_t stream) {
+  if (T == 0) return kOk;
+  const int grid = grid_for(T, 8);
+  if (dtype == kBF16)
+    legacy_entropy_kernel<__nv_bfloat16><<<grid, kConsumers, 0, stream>>>(logits, T, V, row_stride_bytes, row_max, ln_s, eps, out);
+  else if (dtype == kFP16)
+    legacy_entropy_kernel<__half><<<grid, kConsumers, 0, stream>>>(logits, T, V, row_stride_bytes, row_max, ln_s, eps, out);
+  else
+    legacy_entropy_kernel<float><<<grid, kConsumers, 0, stream>>>(logits, T, V, row_stride_bytes, row_max, ln_s, eps, out);
+  return check_launch("legacy_entropy");
 }
 
 int launch_vocab_combine(const float* parts, int R, int64_t T, float inv_t, float* logp,

@@ -56,6 +56,9 @@ struct LogitsBwdParams {
 int64_t logits_loss_workspace_bytes();
 int launch_logits_fwd(const LogitsFwdParams& p, cudaStream_t stream);
 int launch_logits_bwd(const LogitsBwdParams& p, cudaStream_t stream);
+int launch_legacy_entropy(const void* logits, int dtype, int64_t T, int64_t V, int64_t row_stride_bytes,
+                          const float* row_max, const float* ln_s, float eps, float* out,
+                          cudaStream_t stream);
 int launch_vocab_combine(const float* parts, int R, int64_t T, float inv_t, float* logp,
                          float* entropy, float* row_max, float* ln_s, cudaStream_t stream);
 

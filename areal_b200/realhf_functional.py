@@ -1,0 +1,59 @@
+"""Host-side mirror of the packed log-prob helpers of `realhf/impl/model/utils/functional.py:91-234`
+and of `calc_entropy` (`realhf/impl/model/interface/ppo_interface.py:52-58`) -- the legacy (realhf)
+spelling of P2.  Same names / arguments / shapes; the index builders are O(T) torch ops (the
+reference's are O(T*B) broadcasts, functional.py:118-126, 162-165), the log-softmax is the fused fp32
+streaming kernel (the reference runs log_softmax in the logits' own dtype and returns that dtype:
+results are cast back to it, so they agree to one ulp of that dtype)."""
+from __future__ import annotations
+
+import torch
+
+from . import _lib
+from . import functional as F
+from ._lib import call, ptr, stream_ptr
+
+
+def build_shift_one_indices(x: torch.Tensor, cu_seqlens: torch.Tensor) -> torch.Tensor:
+    """Indices of every token except the FIRST of each sequence (functional.py:91-126)."""
+    total = x.shape[0]
+    keep = torch.ones(total, dtype=torch.bool, device=cu_seqlens.device)
+    keep[cu_seqlens[:-1].long()] = False
+    return keep.nonzero(as_tuple=True)[0]
+
+
+def build_leave_one_indices(x: torch.Tensor, cu_seqlens: torch.Tensor) -> torch.Tensor:
+    """Indices of every token except the LAST of each sequence (functional.py:129-166)."""
+    total = x.shape[0]
+    keep = torch.ones(total, dtype=torch.bool, device=cu_seqlens.device)
+    keep[cu_seqlens[1:].long() - 1] = False
+    return keep.nonzero(as_tuple=True)[0]
+
+
+def gather_logprobs(logits: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
+    """log_softmax(logits)[labels] in the logits' dtype (functional.py:169-186)."""
+    return F.gather_logprobs(logits, labels, 1.0).to(logits.dtype)
+
+
+def gather_packed_shifted_log_probs(logits: torch.Tensor, cu_seqlens: torch.Tensor,
+                                    labels: torch.Tensor) -> torch.Tensor:
+    """Log-prob of token t+1 under the logits at t, for every t but the last of each sequence
+    (functional.py:189-234); shape [tot_seqlen - #seqs], dtype of `logits`, differentiable."""
+    labels = torch.nn.functional.pad(labels[1:], (0, 1), value=0)
+    leave_one_indices = build_leave_one_indices(logits, cu_seqlens)
+    log_probs_labels = gather_logprobs(logits, labels)[leave_one_indices]
+    assert log_probs_labels.shape[0] == logits.shape[0] - cu_seqlens.shape[0] + 1
+    return log_probs_labels
+
+
+@torch.no_grad()
+def calc_entropy(logits: torch.Tensor, cu_seqlens: torch.Tensor) -> torch.Tensor:
+    """-sum softmax * log(softmax + 1e-7) per token, last token of each sequence dropped
+    (ppo_interface.py:52-58), in the logits' dtype."""
+    dev, x, lab, lead, V = F._rows(logits.detach(), torch.zeros(logits.shape[:-1], dtype=torch.long, device=logits.device))
+    _, _, row_max, ln_s, _ = F._logits_forward(x, lab, 1.0, False)
+    T = x.shape[0]
+    out = torch.empty(T, dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        call("areal_b200_legacy_entropy", ptr(x), _lib.DTYPE_CODE[x.dtype], T, V, x.stride(0) if T > 1 else V,
+             ptr(row_max), ptr(ln_s), 1e-7, ptr(out), stream_ptr(dev))
+    return out[build_leave_one_indices(logits, cu_seqlens)].to(logits.dtype)

@@ -151,6 +151,15 @@ AREAL_B200_API int areal_b200_vocab_combine(const float* parts, int64_t R, int64
                                             double temperature, float* logp, float* entropy,
                                             float* row_max, float* ln_sumexp, void* stream);
 
+/* Legacy entropy statistic -sum_v p_v * log(p_v + eps), p = softmax(logits) (temperature already
+ * applied by the caller).  Replaces `calc_entropy` (realhf/impl/model/interface/ppo_interface.py:
+ * 52-58, eps = 1e-7), a no-grad logging value of the legacy actor interface; second read-only pass
+ * that takes row_max / ln_sumexp from areal_b200_logits_fwd (called with temperature 1). */
+AREAL_B200_API int areal_b200_legacy_entropy(const void* logits, int dtype, int64_t T, int64_t V,
+                                             int64_t row_stride, const float* row_max,
+                                             const float* ln_sumexp, double eps, float* entropy_out,
+                                             void* stream);
+
 /* ------------------------------------------------------------------------------------------ *
  * P3  PPO losses
  * ------------------------------------------------------------------------------------------ */

@@ -448,3 +448,37 @@ def combine_partials(all_parts: np.ndarray, temperature: float):
     XL = p[:, 3].sum(0)
     ln_s = np.log(S)
     return (XL - M) / temperature - ln_s, ln_s - math.log(2.0) * W / S, M, ln_s
+
+
+# --------------------------------------------------------------------------- #
+# P2, legacy (realhf) spelling
+# --------------------------------------------------------------------------- #
+def leave_one_indices(total: int, cu_seqlens) -> np.ndarray:
+    """`build_leave_one_indices` (realhf/impl/model/utils/functional.py:129-166): every position but
+    the last of each sequence."""
+    cu = np.asarray(cu_seqlens, dtype=np.int64)
+    keep = np.ones(total, dtype=bool)
+    keep[cu[1:] - 1] = False
+    return np.nonzero(keep)[0]
+
+
+def shift_one_indices(total: int, cu_seqlens) -> np.ndarray:
+    """`build_shift_one_indices` (functional.py:91-126): every position but the first of each sequence."""
+    cu = np.asarray(cu_seqlens, dtype=np.int64)
+    keep = np.ones(total, dtype=bool)
+    keep[cu[:-1]] = False
+    return np.nonzero(keep)[0]
+
+
+def gather_packed_shifted_log_probs(logits, cu_seqlens, ids):
+    """`gather_packed_shifted_log_probs` (functional.py:189-234): labels shifted left by one (last
+    padded with 0), log_softmax gathered, last token of each sequence dropped.  fp64."""
+    ids = np.asarray(ids, dtype=np.int64)
+    lab = np.concatenate([ids[1:], [0]])
+    lp, *_ = gather_logprobs_entropy(logits, lab, 1.0)
+    return lp[leave_one_indices(len(ids), cu_seqlens)]
+
+
+def calc_entropy_packed(logits, cu_seqlens):
+    """`calc_entropy` (realhf/impl/model/interface/ppo_interface.py:52-58)."""
+    return calc_entropy_legacy(logits)[leave_one_indices(np.asarray(logits).shape[0], cu_seqlens)]

@@ -263,6 +263,32 @@ def gen_intervals(fp):
     print("interval cases:", k)
 
 
+def gen_legacy_packed():
+    """realhf spelling of P2: gather_packed_shifted_log_probs / build_*_indices / calc_entropy."""
+    rf = R.load_realhf_functional()
+    out = {}
+    g = torch.Generator().manual_seed(31)
+    k = 0
+    for (lens, V, dt) in (([5, 1, 9, 2], 300, torch.float32), ([40, 17, 3, 60], 1031, torch.bfloat16),
+                          ([33, 31], 512, torch.float32)):
+        T = sum(lens)
+        cu = torch.nn.functional.pad(torch.tensor(lens).cumsum(0), (1, 0)).int()
+        logits = (torch.randn(T, V, generator=g) * 2).to(dt)
+        ids = torch.randint(0, V, (T,), generator=g)
+        lp = rf.gather_packed_shifted_log_probs(logits, cu, ids)
+        ent = R.run_realhf_calc_entropy(logits, cu)
+        p = f"c{k}_"
+        out.update({p + "logits": (bf16_bits(logits) if dt == torch.bfloat16 else logits.numpy()), p + "is_bf16": np.array(dt == torch.bfloat16),
+                    p + "cu": cu.numpy(), p + "ids": ids.numpy(), p + "logp": lp.float().numpy(),
+                    p + "entropy": ent.float().numpy(),
+                    p + "leave_one": rf.build_leave_one_indices(logits, cu).numpy(),
+                    p + "shift_one": rf.build_shift_one_indices(logits, cu).numpy()})
+        k += 1
+    out["n_cases"] = np.array(k)
+    np.savez_compressed(os.path.join(OUT, "legacy_packed.npz"), **out)
+    print("legacy_packed cases:", k)
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     assert R.available(), "needs /root/reference"
@@ -276,6 +302,7 @@ def main():
     gen_actor_loss(af, pf)
     gen_critic_loss(af, pf)
     gen_intervals(fp)
+    gen_legacy_packed()
 
 
 if __name__ == "__main__":

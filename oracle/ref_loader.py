@@ -137,3 +137,46 @@ def run_areal_padded_gae(rewards, values, loss_mask, seq_no_eos_mask, discount, 
               self=_t.SimpleNamespace(discount=discount, gae_lambda=gae_lambda))
     exec(compile(src, "actor.py[gae]", "exec"), ns)
     return ns["advantages"], ns["data"]["returns"]
+
+
+def load_realhf_functional():
+    """realhf/impl/model/utils/functional.py (`build_leave_one_indices` :129-166,
+    `gather_packed_shifted_log_probs` :189-234) with its package imports stubbed."""
+    import logging as _logging
+    names = ["realhf", "realhf.base", "realhf.base.constants", "realhf.base.logging", "realhf.impl",
+             "realhf.impl.model", "realhf.impl.model.utils", "realhf.impl.model.utils.padding"]
+    saved = {k: sys.modules.get(k) for k in names}
+    try:
+        for n in ("realhf", "realhf.base", "realhf.impl", "realhf.impl.model", "realhf.impl.model.utils"):
+            m = _stub(n)
+            m.__path__ = []
+        _stub("realhf.base.constants", tensor_parallel_world_size=lambda: 1)
+        _stub("realhf.base.logging", getLogger=_logging.getLogger)
+        sys.modules["realhf.base"].constants = sys.modules["realhf.base.constants"]
+        sys.modules["realhf.base"].logging = sys.modules["realhf.base.logging"]
+        _stub("realhf.impl.model.utils.padding", pad_input=None, unpad_input=None)
+        return _load("realhf/impl/model/utils/functional.py", "_ref_realhf_functional")
+    finally:
+        for k, v in saved.items():
+            if v is None:
+                sys.modules.pop(k, None)
+            else:
+                sys.modules[k] = v
+
+
+def run_realhf_calc_entropy(logits, cu_seqlens):
+    """Executes the body of `calc_entropy` (realhf/impl/model/interface/ppo_interface.py:52-58,
+    without its torch.compile decorator) straight from the reference file."""
+    import textwrap
+
+    import torch
+    rf = load_realhf_functional()
+    with open(os.path.join(REF_ROOT, "realhf/impl/model/interface/ppo_interface.py")) as f:
+        lines = f.read().splitlines()
+    start = next(i for i, l in enumerate(lines) if l.startswith("def calc_entropy("))
+    end = next(i for i in range(start + 1, len(lines)) if lines[i].startswith("    return entropy"))
+    src = textwrap.dedent("\n".join(lines[start:end + 1]))
+    ns = dict(torch=torch, build_leave_one_indices=rf.build_leave_one_indices)
+    exec(compile(src, "ppo_interface.py[calc_entropy]", "exec"), ns)
+    with torch.no_grad():
+        return ns["calc_entropy"](logits, cu_seqlens)

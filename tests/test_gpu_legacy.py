@@ -1,0 +1,47 @@
+"""GPU parity: the legacy (realhf) spelling of P2 -- gather_packed_shifted_log_probs, the index builders
+and calc_entropy -- through the C ABI vs golden vectors of the unmodified reference functions."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import cpu_oracle as O
+from tests import helpers as H
+
+pytestmark = pytest.mark.gpu
+D = "cuda:0"
+
+
+def test_legacy_packed_golden():
+    from areal_b200 import realhf_functional as RF
+    z = H.load("legacy_packed.npz")
+    for k, c in H.cases(z):
+        bf16 = bool(c["is_bf16"])
+        logits = (H.bf16_from_bits(c["logits"]) if bf16 else torch.from_numpy(c["logits"])).to(D)
+        cu = torch.from_numpy(c["cu"]).to(D)
+        ids = torch.from_numpy(c["ids"]).to(D)
+        assert np.array_equal(RF.build_leave_one_indices(logits, cu).cpu().numpy(), c["leave_one"])
+        assert np.array_equal(RF.build_shift_one_indices(logits, cu).cpu().numpy(), c["shift_one"])
+        x = logits.clone().requires_grad_()
+        lp = RF.gather_packed_shifted_log_probs(x, cu, ids)
+        assert lp.dtype == logits.dtype and lp.shape[0] == logits.shape[0] - (cu.numel() - 1)
+        ent = RF.calc_entropy(logits, cu)
+        assert ent.dtype == logits.dtype and not ent.requires_grad
+        got_lp, got_ent = lp.detach().float().cpu().numpy(), ent.float().cpu().numpy()
+        if bf16:
+            assert np.all(np.abs(got_lp - c["logp"]) <= 2 ** -7 * np.abs(c["logp"]) + 1e-6), k
+            assert np.all(np.abs(got_ent - c["entropy"]) <= 0.05 * np.abs(c["entropy"]) + 1e-3), k
+        else:
+            assert H.rel_err(got_lp, c["logp"]) <= H.TOL_LOGITS, k
+            assert H.rel_err(got_ent, c["entropy"]) <= H.TOL_LOGITS, k
+            assert np.allclose(got_ent, c["entropy"], rtol=1e-4, atol=1e-5), k
+        # gradient flows to the logits through the index select
+        w = torch.randn(lp.shape, device=D)
+        (lp.float() * w).sum().backward()
+        lab = np.concatenate([c["ids"][1:], [0]])
+        gfull = np.zeros(logits.shape[0])
+        gfull[c["leave_one"]] = w.cpu().numpy()
+        ref = O.dlogits(logits.float().cpu().numpy(), lab, 1.0, gfull)
+        got = x.grad.float().cpu().numpy()
+        scale = np.maximum(np.abs(ref).max(-1, keepdims=True), 1e-3 * np.abs(gfull)[:, None]) + 1e-30
+        slack = 2 ** -8 if bf16 else 1e-6
+        assert np.all(np.abs(got - ref) <= slack * np.abs(ref) + (3e-3 if bf16 else 1e-3) * scale + 1e-30), k

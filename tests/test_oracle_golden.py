@@ -192,3 +192,22 @@ def test_cpu_baseline_port_matches_golden():
         t = lambda a: torch.from_numpy(a)
         loss = CB.actor_loss_torch(t(c["lp"]), t(c["prox"]), t(c["old"]), t(c["adv"]), eps, t(c["mask"]), eps_hi, c_clip, cap)
         assert abs(float(loss) - float(c["loss"])) <= 1e-6 * max(1.0, abs(float(c["loss"]))), k
+
+
+def test_legacy_packed_vs_reference():
+    """realhf spelling of P2 (gather_packed_shifted_log_probs, build_*_indices, calc_entropy)."""
+    z = H.load("legacy_packed.npz")
+    for k, c in H.cases(z):
+        bf16 = bool(c["is_bf16"])
+        logits = H.bf16_from_bits(c["logits"]).float().numpy() if bf16 else c["logits"]
+        T = logits.shape[0]
+        assert np.array_equal(O.leave_one_indices(T, c["cu"]), c["leave_one"])
+        assert np.array_equal(O.shift_one_indices(T, c["cu"]), c["shift_one"])
+        lp = O.gather_packed_shifted_log_probs(logits, c["cu"], c["ids"])
+        ent = O.calc_entropy_packed(logits, c["cu"])
+        if bf16:   # the reference computes and returns bf16 here: one bf16 ulp; its bf16 softmax is coarser still
+            assert np.all(np.abs(lp - c["logp"]) <= 2 ** -7 * np.abs(c["logp"]) + 1e-6), k
+            assert np.all(np.abs(ent - c["entropy"]) <= 0.05 * np.abs(c["entropy"]) + 1e-3), k
+        else:
+            assert np.allclose(lp, c["logp"], rtol=1e-5, atol=1e-5), k
+            assert np.allclose(ent, c["entropy"], rtol=1e-5, atol=1e-5), k
