@@ -40,6 +40,10 @@ SIGNATURES = {
     "areal_b200_scale_by_scalars": (c_int, [P, P, P, I64, P, P]),
     "areal_b200_fused_actor_fwd": (c_int, [P, c_int, I64, I64, I64, P, F64, P, P, P, P, F64, F64, F64, F64,
                                            P, P, P, P, P, P, P, P, P, P, P, P, P, P, P, P, P, I64, P]),
+    "areal_b200_fused_actor_fwd_bwd": (c_int, [P, c_int, I64, I64, I64, P, F64, P, P, P, P, F64, F64, F64, F64,
+                                               P, P, P, P, P, P, P, P, P, P, P, P, P, P, P, P,
+                                               P, P, I64, c_int, c_int, P, I64, P]),
+    "areal_b200_rescale_grad_if_needed": (c_int, [P, I64, I64, I64, P, P, P]),
     "areal_b200_interval_workspace_bytes": (I64, [I64]),
     "areal_b200_slice_intervals": (c_int, [P, I64, P, I64, P, I64, I64, P, I64, P]),
     "areal_b200_set_intervals": (c_int, [P, I64, P, I64, P, I64, I64, P, I64, P]),

@@ -444,6 +444,68 @@ AREAL_B200_API int areal_b200_fused_actor_fwd(const void* logits, int dtype, int
   return launch_logits_fwd(p, static_cast<cudaStream_t>(stream));
 }
 
+AREAL_B200_API int areal_b200_fused_actor_fwd_bwd(const void* logits, int dtype, int64_t T, int64_t V,
+                               int64_t row_stride, const int64_t* labels, double temperature,
+                               const float* proximal_logprobs, const float* old_logprobs,
+                               const float* advantages, const uint8_t* loss_mask, double eps_clip,
+                               double eps_clip_higher, double c_clip, double behav_imp_weight_cap,
+                               float* logp, float* entropy, float* row_max, float* ln_sumexp,
+                               float* raw_min, float* loss_out, float* inv_count_out, float* coef,
+                               float* stat_loss, float* stat_importance_weight,
+                               float* stat_approx_kl, uint8_t* stat_clip_mask,
+                               uint8_t* stat_dual_clip_mask, float* stat_behave_imp_weight,
+                               float* stat_behave_approx_kl, uint8_t* stat_behave_mask,
+                               const float* loss_scale, void* dlogits, int64_t d_row_stride,
+                               int cluster_size, int n_buffers, void* workspace,
+                               int64_t workspace_bytes, void* stream) {
+  int rc = check_logits(logits, dtype, T, V, row_stride, labels, temperature);
+  if (rc) return rc;
+  AB_REQUIRE(T > 0, "fused entry needs T > 0");
+  AB_REQUIRE(dlogits && d_row_stride >= V, "dlogits / d_row_stride invalid");
+  AB_REQUIRE(logp && row_max && ln_sumexp && loss_out && inv_count_out && coef, "required output is null");
+  AB_REQUIRE(old_logprobs && advantages && loss_mask, "old_logprobs / advantages / loss_mask required");
+  rc = check_ws(workspace, workspace_bytes);
+  if (rc) return rc;
+  LogitsFwdParams p;
+  fill_fwd_common(&p, logits, dtype, T, V, row_stride, labels, 0, temperature);
+  rc = make_cfg(&p.cfg, eps_clip, eps_clip_higher, c_clip, behav_imp_weight_cap,
+                proximal_logprobs != nullptr);
+  if (rc) return rc;
+  p.mode = kModeFusedActor;
+  p.logp = logp;
+  p.entropy = entropy;
+  p.row_max = row_max;
+  p.ln_s = ln_sumexp;
+  p.raw_min = raw_min;
+  p.prox = proximal_logprobs;
+  p.old = old_logprobs;
+  p.adv = advantages;
+  p.loss_mask = loss_mask;
+  p.coef = coef;
+  p.stat_loss = stat_loss;
+  p.stat_ratio = stat_importance_weight;
+  p.stat_kl = stat_approx_kl;
+  p.clip_mask = stat_clip_mask;
+  p.dual_clip_mask = stat_dual_clip_mask;
+  p.behave_w = stat_behave_imp_weight;
+  p.behave_kl = stat_behave_approx_kl;
+  p.behave_mask = stat_behave_mask;
+  p.loss_out = loss_out;
+  p.inv_count_out = inv_count_out;
+  p.workspace = workspace;
+  return launch_fused_rowres(p, dlogits, d_row_stride * dtype_size(dtype), loss_scale, cluster_size, n_buffers,
+                             static_cast<cudaStream_t>(stream));
+}
+
+AREAL_B200_API int areal_b200_rescale_grad_if_needed(void* dlogits, int64_t T, int64_t V,
+                                                     int64_t d_row_stride, const float* upstream,
+                                                     const float* assumed, void* stream) {
+  AB_REQUIRE(T >= 0 && V > 0 && d_row_stride >= V, "bad shape");
+  AB_REQUIRE(T == 0 || (dlogits && upstream), "null pointer");
+  return launch_rescale_if_needed(dlogits, T, V, d_row_stride * 2, upstream, assumed,
+                                  static_cast<cudaStream_t>(stream));
+}
+
 // ---- P4 ------------------------------------------------------------------------------------------
 AREAL_B200_API int64_t areal_b200_interval_workspace_bytes(int64_t n_intervals) {
   return interval_workspace_bytes(n_intervals < 0 ? 0 : n_intervals);

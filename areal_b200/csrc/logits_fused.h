@@ -56,6 +56,11 @@ struct LogitsBwdParams {
 int64_t logits_loss_workspace_bytes();
 int launch_logits_fwd(const LogitsFwdParams& p, cudaStream_t stream);
 int launch_logits_bwd(const LogitsBwdParams& p, cudaStream_t stream);
+// logits_rowres.cu: single-pass forward + gradient with cluster-resident rows (mode must be kModeFusedActor)
+int launch_fused_rowres(const LogitsFwdParams& p, void* dlogits, int64_t d_row_stride_bytes,
+                        const float* loss_scale, int force_cluster, int force_nbuf, cudaStream_t stream);
+int launch_rescale_if_needed(void* dlogits, int64_t T, int64_t V, int64_t row_stride_bytes,
+                             const float* upstream, const float* assumed, cudaStream_t stream);
 int launch_legacy_entropy(const void* logits, int dtype, int64_t T, int64_t V, int64_t row_stride_bytes,
                           const float* row_max, const float* ln_s, float eps, float* out,
                           cudaStream_t stream);

@@ -344,22 +344,101 @@ class _FusedActor(torch.autograd.Function):
         return (d.view(ctx.in_shape),) + (None,) * 11
 
 
+class _FusedActorRowRes(torch.autograd.Function):
+    """Single-pass variant: forward also writes dlogits (scaled by `loss_scale`); backward hands it out."""
+
+    @staticmethod
+    def forward(ctx, logits, labels, temperature, prox, old, adv, mask, eps_clip, eps_clip_higher, c_clip,
+                cap, want_minmax, loss_scale, cluster_size, n_buffers):
+        dev, x, lab, lead, V = _rows(logits, labels)
+        _lib.require_cuda(x, prox, old, adv, mask, loss_scale)
+        T = x.shape[0]
+        px = None if prox is None else _f32(prox.reshape(-1))
+        od = _f32(old.reshape(-1))
+        av = _f32(adv.reshape(-1))
+        mk = _mask_u8(mask.reshape(-1))
+        f32 = dict(dtype=torch.float32, device=dev)
+        logp = torch.empty(T, **f32)
+        ent = torch.empty(T, **f32)
+        row_max = torch.empty(T, **f32)
+        ln_s = torch.empty(T, **f32)
+        mn = torch.empty(T, **f32) if want_minmax else None
+        loss = torch.empty((), **f32)
+        inv = torch.empty(1, **f32)
+        coef = torch.empty(T, **f32)
+        f, b = _alloc_stats(T, dev, px is not None)
+        dlogits = torch.empty((T, V), dtype=x.dtype, device=dev)
+        scale = _f32(loss_scale.reshape(1))
+        with torch.cuda.device(dev):
+            nbytes = _lib.lib().areal_b200_loss_workspace_bytes()
+            ws = _lib.workspace("loss", dev, nbytes)
+            call("areal_b200_fused_actor_fwd_bwd", ptr(x), _lib.DTYPE_CODE[x.dtype], T, V,
+                 x.stride(0) if T > 1 else V, ptr(lab), float(temperature), ptr(px), ptr(od), ptr(av), ptr(mk),
+                 float(eps_clip), _opt(eps_clip_higher), _opt(c_clip), _opt(cap),
+                 ptr(logp), ptr(ent), ptr(row_max), ptr(ln_s), ptr(mn), ptr(loss), ptr(inv), ptr(coef),
+                 ptr(f["loss"]), ptr(f["importance_weight"]), ptr(f["approx_kl"]), ptr(_u8(b["clip_mask"])),
+                 ptr(_u8(b["dual_clip_mask"])), ptr(f.get("behave_imp_weight")), ptr(f.get("behave_approx_kl")),
+                 ptr(_u8(b.get("behave_mask"))), ptr(scale), ptr(dlogits), V, int(cluster_size), int(n_buffers),
+                 ptr(ws), ws.numel(), stream_ptr(dev))
+        ctx.save_for_backward(dlogits, scale)
+        ctx.in_shape = logits.shape
+        ctx.set_materialize_grads(False)
+        extras = [logp, ent, f["loss"], f["importance_weight"], f["approx_kl"], b["clip_mask"],
+                  b["dual_clip_mask"]]
+        if px is not None:
+            extras += [f["behave_imp_weight"], f["behave_approx_kl"], b["behave_mask"]]
+        if want_minmax:
+            extras += [mn, row_max]
+        extras = [e.view(lead) for e in extras]
+        ctx.mark_non_differentiable(*extras)
+        return (loss, *extras)
+
+    @staticmethod
+    def backward(ctx, g_loss, *unused):
+        if g_loss is None:
+            return (None,) * 15
+        dlogits, scale = ctx.saved_tensors
+        g = _f32(g_loss.reshape(1))
+        T, V = dlogits.shape
+        with torch.cuda.device(dlogits.device):
+            # no-op when the upstream scalar equals the loss_scale given to the forward (the contract)
+            call("areal_b200_rescale_grad_if_needed", ptr(dlogits), T, V, V, ptr(g), ptr(scale),
+                 stream_ptr(dlogits.device))
+        return (dlogits.view(ctx.in_shape),) + (None,) * 14
+
+
 def fused_actor_loss(logits: torch.Tensor, labels: torch.Tensor, temperature: float,
                      proximal_logprobs: Optional[torch.Tensor], old_logprobs: torch.Tensor,
                      advantages: torch.Tensor, loss_mask: torch.Tensor, eps_clip: float,
                      eps_clip_higher: Optional[float] = None, c_clip: Optional[float] = None,
                      behav_imp_weight_cap: Optional[float] = None,
-                     with_logits_minmax: bool = True) -> Tuple[torch.Tensor, Dict]:
+                     with_logits_minmax: bool = True, loss_scale=None,
+                     cluster_size: int = 0, n_buffers: int = 0) -> Tuple[torch.Tensor, Dict]:
     """ONE streaming pass over `logits` giving what `grpo_loss_fn` (areal/engine/ppo/actor.py:313-391)
     computes with gather_logprobs_entropy + ppo_actor_loss_fn + logits.min/max: returns
     (loss, stat) where stat has the 8 `ppo_actor_loss_fn` entries plus `logprobs`, `entropy`
     (detached, as grpo_loss_fn uses them) and `vocab_min_logits` / `vocab_max_logits`.
-    loss.backward() writes dlogits with one more pass (rows with a zero coefficient are not read)."""
+    loss.backward() writes dlogits with one more pass (rows with a zero coefficient are not read).
+
+    `loss_scale` (float or 0-dim/1-element tensor): the scalar the caller will multiply the loss by
+    before `.backward()` -- what the engines do (`loss *= loss_scale; loss.backward()`,
+    areal/engine/fsdp_engine.py:578-586).  When given (bf16, 16-byte aligned rows), ONE kernel reads the
+    logits once and writes dlogits = loss_scale * dloss/dlogits in the same pass (rows stay in a
+    thread-block cluster's shared memory between the two phases); the returned loss is still
+    UNSCALED, and `(loss * loss_scale).backward()` just hands the stored gradient out (it is rescaled,
+    correctly but at the cost of an extra pass, if the upstream scalar turns out to differ)."""
     if c_clip is not None:
         assert c_clip > 1.0, c_clip
-    res = _FusedActor.apply(logits, labels, temperature, proximal_logprobs, old_logprobs, advantages,
-                            loss_mask, eps_clip, eps_clip_higher, c_clip, behav_imp_weight_cap,
-                            with_logits_minmax)
+    if loss_scale is not None and logits.requires_grad:
+        if not torch.is_tensor(loss_scale):
+            loss_scale = torch.full((1,), float(loss_scale), dtype=torch.float32, device=logits.device)
+        res = _FusedActorRowRes.apply(logits, labels, temperature, proximal_logprobs, old_logprobs, advantages,
+                                      loss_mask, eps_clip, eps_clip_higher, c_clip, behav_imp_weight_cap,
+                                      with_logits_minmax, loss_scale, cluster_size, n_buffers)
+    else:
+        res = _FusedActor.apply(logits, labels, temperature, proximal_logprobs, old_logprobs, advantages,
+                                loss_mask, eps_clip, eps_clip_higher, c_clip, behav_imp_weight_cap,
+                                with_logits_minmax)
     it = iter(res)
     loss = next(it)
     stat = dict(logprobs=next(it), entropy=next(it), loss=next(it), importance_weight=next(it),

@@ -218,6 +218,36 @@ AREAL_B200_API int areal_b200_fused_actor_fwd(const void* logits, int dtype, int
                                float* stat_behave_approx_kl, uint8_t* stat_behave_mask,
                                void* workspace, int64_t workspace_bytes, void* stream);
 
+/* Single-pass variant of the fused actor step: the same outputs as areal_b200_fused_actor_fwd AND
+ * dlogits, from ONE read of the logits (4*T*V bytes instead of 6*T*V for forward + backward).  Rows
+ * are kept on chip by a thread-block cluster between the statistics pass and the gradient pass.
+ * For callers that know, when the forward runs, the scalar that will multiply the loss before
+ * .backward() (the engine's loss_scale, areal/engine/fsdp_engine.py:578-586):
+ *   dlogits = (*loss_scale) * d loss / d logits   (loss_scale nullable = 1), loss_out is NOT scaled.
+ * bf16 logits / dlogits, 16-byte aligned rows, V % 8 == 0; status 4 (unsupported) otherwise -- use
+ * the two-pass entry points then.  cluster_size / n_buffers: 0 = choose automatically. */
+AREAL_B200_API int areal_b200_fused_actor_fwd_bwd(const void* logits, int dtype, int64_t T, int64_t V,
+                               int64_t row_stride, const int64_t* labels, double temperature,
+                               const float* proximal_logprobs, const float* old_logprobs,
+                               const float* advantages, const uint8_t* loss_mask, double eps_clip,
+                               double eps_clip_higher, double c_clip, double behav_imp_weight_cap,
+                               float* logp, float* entropy, float* row_max, float* ln_sumexp,
+                               float* raw_min, float* loss_out, float* inv_count_out, float* coef,
+                               float* stat_loss, float* stat_importance_weight,
+                               float* stat_approx_kl, uint8_t* stat_clip_mask,
+                               uint8_t* stat_dual_clip_mask, float* stat_behave_imp_weight,
+                               float* stat_behave_approx_kl, uint8_t* stat_behave_mask,
+                               const float* loss_scale, void* dlogits, int64_t d_row_stride,
+                               int cluster_size, int n_buffers, void* workspace,
+                               int64_t workspace_bytes, void* stream);
+
+/* Companion of the entry above for autograd: multiplies dlogits (bf16, in place) by
+ * *upstream / *assumed unless the two device scalars are equal -- the expected case, in which the
+ * kernel returns at once. */
+AREAL_B200_API int areal_b200_rescale_grad_if_needed(void* dlogits, int64_t T, int64_t V,
+                                                     int64_t d_row_stride, const float* upstream,
+                                                     const float* assumed, void* stream);
+
 /* ------------------------------------------------------------------------------------------ *
  * P4  interval ops (parameter reallocation)
  * ------------------------------------------------------------------------------------------ */

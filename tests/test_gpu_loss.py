@@ -161,3 +161,44 @@ def test_fused_actor_equals_split_path_and_oracle(V):
     got = x1.grad.float().cpu().numpy().astype(np.float64)
     scale = np.maximum(np.abs(ref_grad).max(axis=-1, keepdims=True), 1e-3 * np.abs(2.0 * coef)[:, None] / 0.9) + 1e-30
     assert np.all(np.abs(got - ref_grad) <= 2 ** -8 * np.abs(ref_grad) + 2 * H.TOL_LOGITS * scale + 1e-30)
+
+
+@pytest.mark.parametrize("V,cluster,nbuf", [(151936, 0, 0), (151936, 8, 0), (151936, 4, 0), (151936, 3, 0),
+                                           (32768, 0, 0), (4096, 0, 0), (8200, 2, 0), (8200, 5, 0)])
+def test_single_pass_row_resident_equals_two_pass(V, cluster, nbuf):
+    """fused_actor_loss(..., loss_scale=s): one kernel, rows resident in a thread-block cluster; must
+    give the two-pass path's loss, stats and (loss*s).backward() gradient."""
+    from areal_b200 import functional as F
+    g = torch.Generator().manual_seed(V + cluster)
+    T = 150 if V > 100000 else 333
+    logits = (torch.randn(T, V, generator=g) * 2).bfloat16()
+    labels = torch.randint(0, V, (T,), generator=g)
+    labels[:3] = torch.tensor([0, V - 1, V // 2])
+    lp_ref, *_ = O.gather_logprobs_entropy(logits.float().numpy(), labels.numpy(), 0.9)
+    prox = (torch.from_numpy(lp_ref) + 0.02 * torch.randn(T, generator=g)).float()
+    old = (torch.from_numpy(lp_ref) + 0.05 * torch.randn(T, generator=g)).float()
+    adv = torch.randn(T, generator=g)
+    mask = torch.rand(T, generator=g) > 0.3
+    cfg = dict(eps_clip=0.4, eps_clip_higher=None, c_clip=3.0, behav_imp_weight_cap=5.0)
+    scale = 0.37
+    x1 = logits.to(D).requires_grad_()
+    loss1, st1 = F.fused_actor_loss(x1, labels.to(D), 0.9, prox.to(D), old.to(D), adv.to(D), mask.to(D),
+                                    loss_scale=scale, cluster_size=cluster, n_buffers=nbuf, **cfg)
+    (loss1 * scale).backward()
+    x2 = logits.to(D).requires_grad_()
+    loss2, st2 = F.fused_actor_loss(x2, labels.to(D), 0.9, prox.to(D), old.to(D), adv.to(D), mask.to(D), **cfg)
+    (loss2 * scale).backward()
+    assert torch.allclose(loss1, loss2, rtol=2e-6, atol=1e-7)
+    for name in st2:
+        a, b = st1[name], st2[name]
+        if a.dtype == torch.bool:
+            assert torch.equal(a, b), name
+        else:
+            assert torch.allclose(a, b, rtol=2e-5, atol=2e-6), name
+    assert torch.allclose(x1.grad.float(), x2.grad.float(), rtol=2 ** -7, atol=1e-10)
+    # a different upstream scalar than announced: still correct (rescaled in place)
+    x3 = logits.to(D).requires_grad_()
+    loss3, _ = F.fused_actor_loss(x3, labels.to(D), 0.9, prox.to(D), old.to(D), adv.to(D), mask.to(D),
+                                  loss_scale=scale, cluster_size=cluster, n_buffers=nbuf, **cfg)
+    (loss3 * 1.5).backward()
+    assert torch.allclose(x3.grad.float() * (scale / 1.5), x2.grad.float(), rtol=2 ** -6, atol=1e-10)
