@@ -31,7 +31,7 @@ constexpr int kGroupThreads = kGroupWarps * 32;      // 256
 constexpr int kRRThreads = 2 * kGroupThreads + 64;   // group A (stats) + group B (gradient) + producer + exchange warps
 constexpr int kMaxCluster = 8;
 constexpr int kTmaPiece = 16384;
-constexpr int kNBuf = 2;
+constexpr int kMaxBuf = 3;
 
 __device__ __forceinline__ uint32_t cluster_ctarank() {
   uint32_t r;
@@ -79,9 +79,9 @@ __device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity)
 }
 
 struct RRShared {
-  float m[2][kGroupWarps], s[2][kGroupWarps], w[2][kGroupWarps], mn[2][kGroupWarps];   // [row parity]
+  float m[kMaxBuf][kGroupWarps], s[kMaxBuf][kGroupWarps], w[kMaxBuf][kGroupWarps], mn[kMaxBuf][kGroupWarps];   // [slice buffer]
   float xchg[2][kMaxCluster][8];    // [row parity][source CTA rank][m, S, W, xl, mn]
-  float rowinfo[kNBuf][4];          // per slice buffer, group A -> group B: m, -log2 S, gl
+  float rowinfo[kMaxBuf][4];          // per slice buffer, group A -> group B: m, -log2 S, gl
   float count;
 };
 
@@ -92,13 +92,13 @@ struct RRShared {
 //   group B  (warps 8-15): gradient pass over the same slice, one row behind group A
 __global__ void __launch_bounds__(kRRThreads, 1)
 fused_rowres_kernel(const LogitsFwdParams p, void* __restrict__ dlogits, int64_t d_row_stride_bytes,
-                    const float* __restrict__ loss_scale, uint32_t buf_stride) {
+                    const float* __restrict__ loss_scale, uint32_t buf_stride, int nbuf) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t full_bar[kNBuf];    // slice landed (TMA tx bytes)
-  __shared__ __align__(8) uint64_t ready_bar[kNBuf];   // row statistics published by group A
-  __shared__ __align__(8) uint64_t empty_bar[kNBuf];   // group B is done with the slice
+  __shared__ __align__(8) uint64_t full_bar[kMaxBuf];    // slice landed (TMA tx bytes)
+  __shared__ __align__(8) uint64_t ready_bar[kMaxBuf];   // row statistics published by group A
+  __shared__ __align__(8) uint64_t empty_bar[kMaxBuf];   // group B is done with the slice
   __shared__ __align__(8) uint64_t xchg_bar[2];        // all C partials of a row have arrived
-  __shared__ __align__(8) uint64_t part_bar[2];        // group A's 8 warp partials of a row are in shared memory
+  __shared__ __align__(8) uint64_t part_bar[kMaxBuf];        // group A's 8 warp partials of a row are in shared memory
   __shared__ RRShared sh;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -126,13 +126,13 @@ fused_rowres_kernel(const LogitsFwdParams p, void* __restrict__ dlogits, int64_t
       float tot = 0.f;
       for (int w = 0; w < kRRThreads / 32; ++w) tot += tmp[w];
       sh.count = tot;
-      for (int i = 0; i < kNBuf; ++i) {
+      for (int i = 0; i < kMaxBuf; ++i) {
         mbar_init(smem_u32(&full_bar[i]), 1);
         mbar_init(smem_u32(&ready_bar[i]), 1);
         mbar_init(smem_u32(&empty_bar[i]), kGroupWarps);
+        mbar_init(smem_u32(&part_bar[i]), kGroupWarps);
       }
       for (int i = 0; i < 2; ++i) mbar_init(smem_u32(&xchg_bar[i]), 1);
-      for (int i = 0; i < 2; ++i) mbar_init(smem_u32(&part_bar[i]), kGroupWarps);
       mbar_fence_init();
     }
     __syncthreads();
@@ -150,8 +150,8 @@ fused_rowres_kernel(const LogitsFwdParams p, void* __restrict__ dlogits, int64_t
       const uint64_t pol = policy_evict_first();
       int64_t it = 0;
       for (int64_t row = cid; row < p.T; row += ncl, ++it) {
-        const int b = static_cast<int>(it & 1);
-        if (it >= kNBuf) mbar_wait(smem_u32(&empty_bar[b]), static_cast<uint32_t>(((it >> 1) - 1) & 1));
+        const int b = static_cast<int>(it % nbuf);
+        if (it >= nbuf) mbar_wait(smem_u32(&empty_bar[b]), static_cast<uint32_t>(((it / nbuf) - 1) & 1));
         const char* src = reinterpret_cast<const char*>(p.logits) + row * p.row_stride_bytes + v0 * 16;
         const uint32_t bar = smem_u32(&full_bar[b]);
         mbar_arrive_expect_tx(bar, my_bytes);
@@ -165,8 +165,8 @@ fused_rowres_kernel(const LogitsFwdParams p, void* __restrict__ dlogits, int64_t
     // ===== group A: statistics pass only; hands 8 warp partials to the exchange warp ================
     int64_t it = 0;
     for (int64_t row = cid; row < p.T; row += ncl, ++it) {
-      const int b = static_cast<int>(it & 1);
-      const uint32_t ph = static_cast<uint32_t>((it >> 1) & 1);
+      const int b = static_cast<int>(it % nbuf);
+      const uint32_t ph = static_cast<uint32_t>((it / nbuf) & 1);
       const uint32_t sbase = ring + uint32_t(b) * buf_stride;
       if (my_bytes) mbar_wait(smem_u32(&full_bar[b]), ph);
       RowState st;
@@ -217,9 +217,10 @@ fused_rowres_kernel(const LogitsFwdParams p, void* __restrict__ dlogits, int64_t
     float loss_sum = 0.f;   // rank 0, lane 0 only
     int64_t it = 0;
     for (int64_t row = cid; row < p.T; row += ncl, ++it) {
-      const int b = static_cast<int>(it & 1);
-      const int par = b;
-      const uint32_t ph = static_cast<uint32_t>((it >> 1) & 1);
+      const int b = static_cast<int>(it % nbuf);
+      const int par = static_cast<int>(it & 1);
+      const uint32_t ph = static_cast<uint32_t>((it / nbuf) & 1);
+      const uint32_t phx = static_cast<uint32_t>((it >> 1) & 1);
       // per-row scalars: issue the global loads now, consume them after the exchange
       const int64_t lab = p.labels[row] - p.vocab_start;
       float t_old = 0.f, t_prox = 0.f, t_adv = 0.f;
@@ -230,14 +231,14 @@ fused_rowres_kernel(const LogitsFwdParams p, void* __restrict__ dlogits, int64_t
         t_adv = p.adv[row];
         t_mask = p.loss_mask[row] != 0;
       }
-      mbar_wait(smem_u32(&part_bar[par]), ph);
+      mbar_wait(smem_u32(&part_bar[b]), ph);
       RowState st;
       {
         const int l = lane & (kGroupWarps - 1);
-        st.m = *reinterpret_cast<const volatile float*>(&sh.m[par][l]);
-        st.s = *reinterpret_cast<const volatile float*>(&sh.s[par][l]);
-        st.w = *reinterpret_cast<const volatile float*>(&sh.w[par][l]);
-        st.mn = *reinterpret_cast<const volatile float*>(&sh.mn[par][l]);
+        st.m = *reinterpret_cast<const volatile float*>(&sh.m[b][l]);
+        st.s = *reinterpret_cast<const volatile float*>(&sh.s[b][l]);
+        st.w = *reinterpret_cast<const volatile float*>(&sh.w[b][l]);
+        st.mn = *reinterpret_cast<const volatile float*>(&sh.mn[b][l]);
 #pragma unroll
         for (int o = kGroupWarps / 2; o > 0; o >>= 1) {
           const float m2 = __shfl_xor_sync(0xffffffffu, st.m, o);
@@ -266,7 +267,7 @@ fused_rowres_kernel(const LogitsFwdParams p, void* __restrict__ dlogits, int64_t
         st_async_f32(dst + 12, xl, rbar);
         st_async_f32(dst + 16, st.mn, rbar);
       }
-      mbar_wait_cluster(smem_u32(&xchg_bar[par]), ph);
+      mbar_wait_cluster(smem_u32(&xchg_bar[par]), phx);
 
       float m = -INFINITY, s = 0.f, w = 0.f, mn = INFINITY;
       xl = 0.f;
@@ -334,8 +335,8 @@ fused_rowres_kernel(const LogitsFwdParams p, void* __restrict__ dlogits, int64_t
     const int gt = tid - kGroupThreads;
     int64_t it = 0;
     for (int64_t row = cid; row < p.T; row += ncl, ++it) {
-      const int b = static_cast<int>(it & 1);
-      const uint32_t ph = static_cast<uint32_t>((it >> 1) & 1);
+      const int b = static_cast<int>(it % nbuf);
+      const uint32_t ph = static_cast<uint32_t>((it / nbuf) & 1);
       const uint32_t sbase = ring + uint32_t(b) * buf_stride;
       const int64_t lab = p.labels[row] - p.vocab_start;
       mbar_wait(smem_u32(&ready_bar[b]), ph);
@@ -409,7 +410,6 @@ int launch_rescale_if_needed(void* dlogits, int64_t T, int64_t V, int64_t row_st
 // occupancy API, launches.  Returns kUnsupported when the rows cannot take this path.
 int launch_fused_rowres(const LogitsFwdParams& p, void* dlogits, int64_t d_row_stride_bytes,
                         const float* loss_scale, int force_cluster, int force_nbuf, cudaStream_t stream) {
-  (void)force_nbuf;
   if (p.T == 0) return kOk;
   const bool aligned = p.dtype == kBF16 && (reinterpret_cast<uintptr_t>(p.logits) & 15) == 0 &&
                        (p.V % 8) == 0 && (p.row_stride_bytes % 16) == 0 &&
@@ -419,25 +419,32 @@ int launch_fused_rowres(const LogitsFwdParams& p, void* dlogits, int64_t d_row_s
     return kUnsupported;
   }
   const int64_t nvec = p.V / 8;
-  constexpr int64_t kBudget = 220 * 1024;
+  constexpr int64_t kBudget = 228 * 1024;    // dynamic shared memory available to one CTA per SM (minus statics)
   auto slice_of = [&](int c) { return (((nvec + c - 1) / c) * 16 + 127) & ~int64_t(127); };
-  int C = 0;
+  int C = 0, nbuf = 2;
   if (force_cluster > 0) {
     C = force_cluster;
+    nbuf = force_nbuf >= 2 && force_nbuf <= kMaxBuf ? force_nbuf : (3 * slice_of(C) <= kBudget ? 3 : 2);
   } else {
-    for (int c = 1; c <= kMaxCluster; ++c) {
-      if (kNBuf * slice_of(c) <= kBudget) {
+    // prefer three slices in flight (measured: C=4 x 3 beats C=3 x 2 at V=151,936 although a cluster of 4
+    // leaves 16 of 148 SMs idle); fall back to two
+    for (int c = 1; c <= kMaxCluster && C == 0; ++c)
+      if (3 * slice_of(c) <= kBudget) {
         C = c;
-        break;
+        nbuf = 3;
       }
-    }
+    for (int c = 1; c <= kMaxCluster && C == 0; ++c)
+      if (2 * slice_of(c) <= kBudget) {
+        C = c;
+        nbuf = 2;
+      }
   }
-  if (C <= 0 || C > kMaxCluster || kNBuf * slice_of(C) > 226 * 1024) {
+  if (C <= 0 || C > kMaxCluster || nbuf * slice_of(C) > kBudget) {
     set_error("row-resident path: V=%lld does not fit a cluster of at most %d CTAs", (long long)p.V, kMaxCluster);
     return kUnsupported;
   }
   const uint32_t buf_stride = static_cast<uint32_t>(slice_of(C));
-  const size_t smem = size_t(buf_stride) * kNBuf + 1024;
+  const size_t smem = size_t(buf_stride) * nbuf + 1024;
   AB_CUDA(cudaFuncSetAttribute(fused_rowres_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
   cudaLaunchConfig_t cfg = {};
   cfg.blockDim = dim3(kRRThreads);
@@ -459,7 +466,7 @@ int launch_fused_rowres(const LogitsFwdParams& p, void* dlogits, int64_t d_row_s
   }
   const int64_t ncl = p.T < max_clusters ? p.T : max_clusters;
   cfg.gridDim = dim3(static_cast<unsigned int>(ncl * C));
-  AB_CUDA(cudaLaunchKernelEx(&cfg, fused_rowres_kernel, p, dlogits, d_row_stride_bytes, loss_scale, buf_stride));
+  AB_CUDA(cudaLaunchKernelEx(&cfg, fused_rowres_kernel, p, dlogits, d_row_stride_bytes, loss_scale, buf_stride, nbuf));
   return check_launch("fused_rowres");
 }
 

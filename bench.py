@@ -3,11 +3,13 @@
 
 One STEP = what one PPO/GRPO micro-batch costs on this path, for a packed batch of T tokens:
   (1) packed GAE over the batch               (areal_b200_gae1d_nolp_misalign)
-  (2) fused log-prob + entropy + decoupled PPO actor loss from [T, V] bf16 logits, forward
-                                              (areal_b200_fused_actor_fwd)
-  (3) loss.backward() -> dlogits [T, V] bf16  (areal_b200_logits_bwd)
+  (2) fused log-prob + entropy + decoupled PPO actor loss from [T, V] bf16 logits
+  (3) (loss * loss_scale).backward() -> dlogits [T, V] bf16
 called through the public Python API (`areal_b200.functional.fused_actor_loss`, autograd), i.e.
-through the C ABI.  N = 1 workload: BASELINE.json configs[1] (Qwen2.5-1.5B GRPO math shape,
+through the C ABI.  Default mode "single": the caller announces loss_scale, and (2)+(3) are ONE kernel
+that reads the logits once (areal_b200_fused_actor_fwd_bwd, cluster-resident rows, 4TV bytes).
+`--mode twopass` times the drop-in split instead (areal_b200_fused_actor_fwd then
+areal_b200_logits_bwd, 6TV bytes); its per-kernel numbers are always reported under "two_pass".  N = 1 workload: BASELINE.json configs[1] (Qwen2.5-1.5B GRPO math shape,
 T = 16,384 packed tokens, V = 151,936).  N > 1 (torchrun, one rank per GPU): the batch is sharded by
 packed sequence, every rank holds its own T tokens (weak scaling), and the only exchange is one
 NCCL all-reduce of (loss numerator, token count) per step.
@@ -159,115 +161,151 @@ def run_ours(args):
         b["prox_logp"] = lp_true + 0.02 * torch.randn(T, generator=g, device=dev)
         b["old_logp"] = lp_true + 0.05 * torch.randn(T, generator=g, device=dev)
     logits = b["logits"].requires_grad_()
+    loss_scale = torch.full((1,), 0.5, dtype=torch.float32, device=dev)   # the engine's loss_scale (fsdp_engine.py:578-586)
     red_pool = [torch.zeros(2, dtype=torch.float32, device=dev) for _ in range(8)]
     n_valid = float(b["loss_mask"].sum().item())
     cnt_vec = torch.tensor([n_valid, 0.0], device=dev)     # loss * count -> numerator
     cnt_vec_add = torch.tensor([0.0, n_valid], device=dev)
-    works = []
 
-    ev = {k: [] for k in ("start", "gae", "fwd", "bwd")}
-    pool = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(args.steps)]
+    def timed_loop(mode, steps, warmup, main):
+        """W warm-up steps, then `steps` timed steps between barrier+synchronize, CUDA events on the launch
+        stream; returns per-step time (max over ranks), per-segment spreads, host enqueue time, clocks."""
+        ev = {k: [] for k in ("start", "gae", "fwd", "bwd")}
+        pool = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(steps)]
+        works = []
+        out = {}
 
-    def step(record=False):
-        if record:
-            e = pool[len(ev["start"])]
-            e[0].record()
-        adv_gae, ret = P.cugae1d_nolp_misalign_func(b["rewards"], b["values"], b["cu_seqlens"], b["bootstrap"], GAMMA, LAM)
-        if record:
-            e[1].record()
-        loss, st = F.fused_actor_loss(logits, b["labels"], TEMPERATURE, b["prox_logp"], b["old_logp"],
-                                      b["advantages"], b["loss_mask"], **CFG)
-        if record:
-            e[2].record()
-        logits.grad = None
-        loss.backward()
-        if record:
-            e[3].record()
-            for k, x in zip(("start", "gae", "fwd", "bwd"), e):
-                ev[k].append(x)
+        def step(record=False):
+            if record:
+                e = pool[len(ev["start"])]
+                e[0].record()
+            P.cugae1d_nolp_misalign_func(b["rewards"], b["values"], b["cu_seqlens"], b["bootstrap"], GAMMA, LAM)
+            if record:
+                e[1].record()
+            logits.grad = None
+            loss, st = F.fused_actor_loss(logits, b["labels"], TEMPERATURE, b["prox_logp"], b["old_logp"],
+                                          b["advantages"], b["loss_mask"],
+                                          loss_scale=loss_scale if mode == "single" else None, **CFG)
+            if record:
+                e[2].record()
+            (loss * loss_scale[0]).backward()
+            if record:
+                e[3].record()
+                for k, x in zip(("start", "gae", "fwd", "bwd"), e):
+                    ev[k].append(x)
+            if world > 1:
+                # the path's only exchange: (loss numerator, token count) -> global masked-mean loss.
+                # Issued asynchronously on NCCL's stream so it overlaps the next step's kernels; every
+                # handle is waited on before the timed region closes.
+                buf = red_pool[len(works) % len(red_pool)]
+                torch.addcmul(cnt_vec_add, cnt_vec, loss.detach(), out=buf)   # [loss*count, count]
+                works.append(dist.all_reduce(buf, async_op=True))
+            return loss, st
+
+        for _ in range(warmup):
+            step()
+        for w in works:
+            w.wait()
+        works.clear()
+        sampler = ClockSampler(local_rank, period=float(os.environ.get('BENCH_CLOCK_PERIOD', '0.02')))
+        if main and os.environ.get('BENCH_NO_SAMPLER') != '1':
+            sampler.start()
+        sync_all()
+        t0 = time.perf_counter()
+        e_start = torch.cuda.Event(enable_timing=True)
+        e_stop = torch.cuda.Event(enable_timing=True)
+        if main:
+            torch.cuda.profiler.start()      # ncu --profile-from-start off captures exactly the timed region
+        e_start.record()
+        h0 = time.perf_counter()
+        for _ in range(steps):
+            loss, st = step(record=True)
+        for w in works:
+            w.wait()                      # stream-level wait: the all-reduces are inside the timed region
+        e_stop.record()
+        host_ms = (time.perf_counter() - h0) * 1e3 / steps     # CPU enqueue time per step
+        sync_all()
+        if main:
+            torch.cuda.profiler.stop()
+        t1 = time.perf_counter()
+        sampler.stop_flag = True
+        ms_total = e_start.elapsed_time(e_stop)
         if world > 1:
-            # the path's only exchange: (loss numerator, token count) -> global masked-mean loss.
-            # Issued asynchronously on NCCL's stream so it overlaps the next step's kernels; every
-            # handle is waited on before the timed region closes.
-            buf = red_pool[len(works) % len(red_pool)]
-            torch.addcmul(cnt_vec_add, cnt_vec, loss.detach(), out=buf)   # [loss*count, count]
-            works.append(dist.all_reduce(buf, async_op=True))
-        return loss, st
+            mt = torch.tensor([ms_total], device=dev)
+            dist.all_reduce(mt, op=dist.ReduceOp.MAX)
+            ms_total = float(mt.item())
+
+        def spread(a, c):
+            v = sorted(x.elapsed_time(y) for x, y in zip(ev[a], ev[c]))
+            return {"min": v[0], "median": v[len(v) // 2], "mean": float(np.mean(v)), "max": v[-1]}
+        out["ms_step"] = ms_total / steps
+        out["spreads"] = {"gae": spread("start", "gae"), "fwd": spread("gae", "fwd"), "bwd": spread("fwd", "bwd")}
+        out["host_ms"] = host_ms
+        out["clocks"] = sampler.summary(t0, t1) if main else None
+        out["loss"] = float(loss.detach())
+        out["global_loss"] = None
+        if world > 1 and works:
+            last = red_pool[(len(works) - 1) % len(red_pool)]
+            out["global_loss"] = float((last[0] / last[1]).item())
+        return out
 
     def sync_all():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize(dev)
 
-    for _ in range(max(args.warmup, 3)):
-        step()
-    for w in works:
-        w.wait()
-    works.clear()
-    sampler = ClockSampler(local_rank, period=float(os.environ.get('BENCH_CLOCK_PERIOD', '0.02')))
-    if os.environ.get('BENCH_NO_SAMPLER') != '1':
-        sampler.start()
-    sync_all()
-    t0 = time.perf_counter()
-    e_start = torch.cuda.Event(enable_timing=True)
-    e_stop = torch.cuda.Event(enable_timing=True)
-    torch.cuda.profiler.start()      # ncu --profile-from-start off captures exactly the timed region
-    e_start.record()
-    h0 = time.perf_counter()
-    for _ in range(args.steps):
-        loss, st = step(record=True)
-    for w in works:
-        w.wait()                      # stream-level wait: the all-reduces are inside the timed region
-    e_stop.record()
-    host_ms = (time.perf_counter() - h0) * 1e3 / args.steps     # CPU enqueue time per step
-    sync_all()
-    torch.cuda.profiler.stop()
-    t1 = time.perf_counter()
-    sampler.stop_flag = True
-    ms_total = e_start.elapsed_time(e_stop)
-    if world > 1:
-        mt = torch.tensor([ms_total], device=dev)
-        dist.all_reduce(mt, op=dist.ReduceOp.MAX)
-        ms_total = float(mt.item())
-    ms_step = ms_total / args.steps
+    W = max(args.warmup, 3)
+    main = timed_loop(args.mode, args.steps, W, True)
+    other_mode = "twopass" if args.mode == "single" else "single"
+    other = timed_loop(other_mode, max(3, min(args.steps, 20)), 3, False)
+    single, twopass = (main, other) if args.mode == "single" else (other, main)
+    ms_step = main["ms_step"]
     value = world * T / (ms_step * 1e-3)
+    spreads = main["spreads"]
+    host_ms = main["host_ms"]
 
-    # per-kernel device times inside the timed region
-    def spread(a, c):
-        v = sorted(x.elapsed_time(y) for x, y in zip(ev[a], ev[c]))
-        return {"min": v[0], "median": v[len(v) // 2], "mean": float(np.mean(v)), "max": v[-1]}
-    spreads = {"gae": spread("start", "gae"), "fwd": spread("gae", "fwd"), "bwd": spread("fwd", "bwd")}
     # per-kernel launch duration = MEDIAN over the timed steps of the event-to-event gap on the launch
     # stream (the mean also counts the host's launch latency whenever the queue runs dry, e.g. on the
     # first timed step right after the barrier; both are reported in kernel_ms_spread)
-    ms_gae, ms_fwd, ms_bwd = spreads["gae"]["median"], spreads["fwd"]["median"], spreads["bwd"]["median"]
     coef_rows = int(torch.count_nonzero(logits.grad[:, :8].float().abs().sum(-1)).item()) if T else 0
     active = coef_rows / T
     peak, peak_src = measured_peaks()
-    bwd_bytes = 2.0 * T * V * (1.0 + active)      # write every row, read only rows with a gradient
-    fwd_bytes = 2.0 * T * V + 64.0 * T
+    ms_gae = spreads["gae"]["median"]
     gae_bytes = 16.0 * T + 9.0 * b["n_seqs"] + 4
-    roof = {"bound": "hbm", "kernel": "logits_bwd_tma_kernel",
-            "achieved": bwd_bytes / (ms_bwd * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
-            "frac": bwd_bytes / (ms_bwd * 1e-3) / 1e9 / peak, "traffic": None,
-            "peak_source": peak_src, "ms": ms_bwd,
-            "algorithmic_bytes": bwd_bytes, "active_row_frac": active,
-            "note": "bytes = 2TV written + 2TV*active read (rows whose gradient is zero are not read); "
-                    "the reference's split API needs 4TV"}
-    roof_fwd = {"bound": "hbm", "kernel": "logits_fwd_tma_kernel", "achieved": fwd_bytes / (ms_fwd * 1e-3) / 1e9,
-                "peak": peak, "unit": "GB/s", "frac": fwd_bytes / (ms_fwd * 1e-3) / 1e9 / peak, "ms": ms_fwd,
-                "algorithmic_bytes": fwd_bytes}
+
+    def roof(kernel, bytes_, ms, **kw):
+        gbs = bytes_ / (ms * 1e-3) / 1e9
+        return dict({"bound": "hbm", "kernel": kernel, "achieved": gbs, "peak": peak, "unit": "GB/s",
+                     "frac": gbs / peak, "traffic": None, "peak_source": peak_src, "ms": ms,
+                     "algorithmic_bytes": bytes_}, **kw)
+    tp_fwd, tp_bwd = twopass["spreads"]["fwd"]["median"], twopass["spreads"]["bwd"]["median"]
+    roof_two = {
+        "ms_per_step": twopass["ms_step"], "tokens_per_s": world * T / (twopass["ms_step"] * 1e-3),
+        "fwd": roof("logits_fwd_tma_kernel", 2.0 * T * V + 64.0 * T, tp_fwd),
+        "bwd": roof("logits_bwd_tma_kernel", 2.0 * T * V * (1.0 + active), tp_bwd, active_row_frac=active,
+                    note="bytes = 2TV written + 2TV*active read (rows whose gradient is zero are not read); "
+                         "the reference's split API needs 4TV"),
+    }
+    sp_ms = single["spreads"]["fwd"]["median"]
+    roof_single = roof("fused_rowres_kernel", 4.0 * T * V + 64.0 * T, sp_ms,
+                       note="one read of the logits (2TV) + dlogits written (2TV); the two-pass split moves 6TV",
+                       ms_per_step=single["ms_step"], tokens_per_s=world * T / (single["ms_step"] * 1e-3))
+    if args.mode == "single":
+        roofline = roof_single
+    else:
+        roofline = roof_two["bwd"]
     roof_gae = {"bound": "launch-latency", "kernel": "gae1d_kernel", "ms": ms_gae,
                 "achieved": gae_bytes / (ms_gae * 1e-3) / 1e9, "unit": "GB/s", "algorithmic_bytes": gae_bytes}
+    loss_value = main["loss"]
 
-    clocks = sampler.summary(t0, t1)
+    clocks = main["clocks"]
 
     # ---- end to end through the public API with HOST buffers (pinned), copies inside the timed region
     e2e = None
     try:
         if args.skip_e2e:
             raise RuntimeError("skipped (--skip-e2e)")
-        e2e = run_e2e(torch, dist, F, P, dev, b, world, max(3, min(args.steps, 5)))
+        e2e = run_e2e(torch, dist, F, P, dev, b, world, max(3, min(args.steps, 5)), args.mode)
     except Exception as ex:  # pinned allocation can fail on a small host: say so instead of faking
         e2e = {"value": None, "unit": "tokens/s", "error": repr(ex)[:200]}
 
@@ -281,18 +319,18 @@ def run_ours(args):
         "vs_baseline": None, "dtype": "bf16", "accumulate_dtype": "f32 (GAE scan f64)", "data": "synthetic",
         "config": {"workload": "BASELINE.json configs[1]: Qwen2.5-1.5B GRPO math shape, T=16384 packed tokens "
                                "per GPU, V=151936 bf16 logits; step = packed GAE + fused logprob+entropy+decoupled "
-                               "PPO loss fwd + dlogits bwd", "tokens_per_gpu": T, "vocab": V,
+                               "PPO loss + dlogits (mode=" + args.mode + ")", "tokens_per_gpu": T, "vocab": V,
                    "parallelism": f"dp{world} (batch-sharded by packed sequence)",
                    "l2": "inputs (4.98 GB logits per GPU) larger than the 126 MB L2; no flush needed",
                    "loss_cfg": {k: v for k, v in CFG.items()}, "temperature": TEMPERATURE},
-        "roofline": roof, "roofline_fwd": roof_fwd, "roofline_gae": roof_gae,
+        "roofline": roofline, "single_pass": roof_single, "two_pass": roof_two, "roofline_gae": roof_gae,
+        "mode": args.mode,
         "e2e": e2e, "gpu_launches": 3 * args.steps, "clocks": clocks, "host_enqueue_ms_per_step": host_ms,
         "kernel_ms_spread": spreads,
-        "loss": float(loss.detach()),
+        "loss": loss_value,
     }
-    if world > 1:
-        last = red_pool[(len(works) - 1) % len(red_pool)]
-        line["global_loss"] = float((last[0] / last[1]).item())
+    if main["global_loss"] is not None:
+        line["global_loss"] = main["global_loss"]
     if world == 1 and not args.skip_cpu:
         line["cpu_baseline"] = cpu_baseline()
     emit(line)
@@ -300,11 +338,12 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
-def run_e2e(torch, dist, F, P, dev, b, world, steps):
+def run_e2e(torch, dist, F, P, dev, b, world, steps, mode="single"):
     """Same step, but the inputs start in pinned HOST memory every step and the results are read back:
     H2D of logits + per-token vectors, GAE + fused fwd + bwd on the device, D2H of the loss and the
     per-token logp / entropy / advantages."""
     T, V = b["logits"].shape
+    scale = torch.full((1,), 0.5, dtype=torch.float32, device=dev)
     host = {}
     for k in ("logits", "labels", "loss_mask", "advantages", "rewards", "values", "cu_seqlens", "bootstrap",
               "prox_logp", "old_logp"):
@@ -324,8 +363,9 @@ def run_e2e(torch, dist, F, P, dev, b, world, steps):
         x = dst["logits"].requires_grad_()
         adv, ret = P.cugae1d_nolp_misalign_func(dst["rewards"], dst["values"], dst["cu_seqlens"], dst["bootstrap"], GAMMA, LAM)
         loss, st = F.fused_actor_loss(x, dst["labels"], TEMPERATURE, dst["prox_logp"], dst["old_logp"],
-                                      dst["advantages"], dst["loss_mask"], **CFG)
-        loss.backward()
+                                      dst["advantages"], dst["loss_mask"],
+                                      loss_scale=scale if mode == "single" else None, **CFG)
+        (loss * scale[0]).backward()
         loss_host.copy_(loss.detach(), non_blocking=True)
         out_host["logp"].copy_(st["logprobs"], non_blocking=True)
         out_host["entropy"].copy_(st["entropy"], non_blocking=True)
@@ -417,6 +457,8 @@ def main():
     ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--mode", default="single", choices=["single", "twopass"],
+                    help="single: one-pass fused forward+gradient (loss_scale announced); twopass: forward then backward")
     ap.add_argument("--skip-e2e", action="store_true", help="profiling runs: skip the host-buffer leg")
     ap.add_argument("--skip-cpu", action="store_true", help="profiling runs: skip the CPU baseline leg")
     args = ap.parse_args()

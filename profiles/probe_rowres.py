@@ -23,7 +23,7 @@ def two_pass():
     l, _ = F.fused_actor_loss(x, b["labels"], 1.0, prox, old, b["advantages"], b["loss_mask"], eps_clip=0.4, behav_imp_weight_cap=5.0)
     (l * scale).backward()
 print("two-pass step ms:", round(timeloop(two_pass), 4))
-for (c, nb) in ((0, 0), (3, 0), (4, 0), (5, 0), (6, 0), (8, 0)):
+for (c, nb) in ((3, 2), (4, 2), (4, 3), (5, 3), (6, 3), (8, 3)):
     def one_pass():
         x.grad = None
         l, _ = F.fused_actor_loss(x, b["labels"], 1.0, prox, old, b["advantages"], b["loss_mask"], eps_clip=0.4,

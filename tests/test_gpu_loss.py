@@ -163,8 +163,8 @@ def test_fused_actor_equals_split_path_and_oracle(V):
     assert np.all(np.abs(got - ref_grad) <= 2 ** -8 * np.abs(ref_grad) + 2 * H.TOL_LOGITS * scale + 1e-30)
 
 
-@pytest.mark.parametrize("V,cluster,nbuf", [(151936, 0, 0), (151936, 8, 0), (151936, 4, 0), (151936, 3, 0),
-                                           (32768, 0, 0), (4096, 0, 0), (8200, 2, 0), (8200, 5, 0)])
+@pytest.mark.parametrize("V,cluster,nbuf", [(151936, 0, 0), (151936, 8, 3), (151936, 4, 3), (151936, 3, 2),
+                                           (151936, 4, 2), (32768, 0, 0), (4096, 0, 0), (8200, 2, 2), (8200, 5, 3)])
 def test_single_pass_row_resident_equals_two_pass(V, cluster, nbuf):
     """fused_actor_loss(..., loss_scale=s): one kernel, rows resident in a thread-block cluster; must
     give the two-pass path's loss, stats and (loss*s).backward() gradient."""
