@@ -76,39 +76,64 @@ __device__ __forceinline__ void block_suffix_scan(const Affine& agg, Affine* wsm
 }
 
 // ---- decoupled look-back descriptors --------------------------------------------------------------
+// Three self-validating 8-byte words per tile: a word is "not published yet" while it holds kEmpty
+// (all ones -- never produced by arithmetic; canonicalised below), so publishing is ONE relaxed
+// 8-byte store per word and needs no fence: there is no separate flag to order against.
 struct __align__(16) TileDesc {
-  unsigned int flag;   // 0 = nothing, 1 = aggregate published, 2 = inclusive value published
-  unsigned int pad;
-  double inc;          // A at the first token of the tile (valid when flag == 2)
-  double agg_a, agg_b; // tile map (valid when flag >= 1)
+  unsigned long long inc;      // bits of A at the first token of the tile, once known
+  unsigned long long agg_a;    // bits of the tile map (a, b)
+  unsigned long long agg_b;
+  int seq0;                    // sequence of the tile's first token (written by the prep kernel)
+  int end0;                    // cu[seq0 + 1]: saves the tile one dependent load
 };
 struct WorkspaceHeader {
-  unsigned int ticket;
-  unsigned int done;
-  unsigned int pad[14];
+  unsigned int pad[16];
 };
 static_assert(sizeof(TileDesc) == 32, "TileDesc layout");
 static_assert(sizeof(WorkspaceHeader) == 64, "header layout");
+constexpr unsigned long long kEmpty = ~0ull;
 
-__device__ __forceinline__ unsigned int ld_acquire_u32(const unsigned int* p) {
-  unsigned int v;
-  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+__device__ __forceinline__ unsigned long long ld_relaxed_u64(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
   return v;
 }
-__device__ __forceinline__ void st_release_u32(unsigned int* p, unsigned int v) {
-  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+__device__ __forceinline__ void st_relaxed_f64(unsigned long long* p, double x) {
+  unsigned long long v = static_cast<unsigned long long>(__double_as_longlong(x));
+  if (v == kEmpty) v = 0x7ff8000000000000ull;      // canonical NaN instead of the reserved pattern
+  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
-__device__ __forceinline__ double ld_volatile_f64(const double* p) {
-  double v;
-  asm volatile("ld.volatile.global.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
-  return v;
+
+// One thread per tile: mark the descriptor empty and look up the sequence that holds the tile's first
+// token (smallest i with cu[i+1] > first token).  Replaces a memset node, so it costs no extra launch.
+__global__ void gae1d_prep_kernel(const int32_t* __restrict__ cu, int B, int64_t T, int64_t ntiles,
+                                  TileDesc* __restrict__ desc, int tile_tokens) {
+  const int64_t t = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+  if (t >= ntiles) return;
+  const int64_t tok = t * tile_tokens;
+  int lo = 0, hi = B - 1;
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (int64_t(__ldg(cu + mid + 1)) > tok) hi = mid; else lo = mid + 1;
+  }
+  TileDesc d;
+  d.inc = kEmpty;
+  d.agg_a = kEmpty;
+  d.agg_b = kEmpty;
+  d.seq0 = lo;
+  d.end0 = __ldg(cu + lo + 1);
+  desc[t] = d;
 }
 
 // ---- 1D packed, misaligned values ------------------------------------------------------------------
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, 8)
 gae1d_kernel(const Gae1dParams p) {
   __shared__ Affine wsm[kWarps];
   __shared__ double carry_sm;
+  // per-token values parked in shared memory ([item][thread]: conflict-free) while the scan runs, so
+  // that 8 CTAs fit an SM (32 registers per thread): this kernel lives on memory-level parallelism
+  __shared__ float v_sm[kItems][kThreads];
+  __shared__ float d_sm[kItems][kThreads];
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int64_t ntiles = (p.T + kTile - 1) / kTile;
@@ -119,63 +144,104 @@ gae1d_kernel(const Gae1dParams p) {
   // hardware dispatching thread blocks in increasing blockIdx order (waiting never blocks a
   // predecessor from being scheduled).
   const int64_t tile = ntiles - 1 - int64_t(blockIdx.x);
+  const int64_t tile_start = tile * kTile;
+  const int ntok = static_cast<int>(p.T - tile_start < kTile ? p.T - tile_start : kTile);
+  const int B = static_cast<int>(p.B);
 
-  const int64_t j0 = tile * kTile + int64_t(tid) * kItems;
-  int nvalid = 0;
-  if (j0 < p.T) nvalid = (p.T - j0) < kItems ? int(p.T - j0) : kItems;
+  const int p0 = tid * kItems;                      // first token of this thread, relative to the tile
+  const int nvalid = p0 >= ntok ? 0 : (ntok - p0 < kItems ? ntok - p0 : kItems);
+  const float* rew = p.rewards + tile_start;
+  const float* val = p.values + tile_start;         // + sequence id per token ("misaligned")
 
-  float r[kItems], vcur[kItems], delta[kItems];
+  // rewards do not depend on the sequence lookup: get them in flight first
+  float r[kItems];
+  if (p.vec_ok && nvalid == kItems) {
+    const float4 a = __ldg(reinterpret_cast<const float4*>(rew + p0));
+    const float4 b = __ldg(reinterpret_cast<const float4*>(rew + p0) + 1);
+    r[0] = a.x; r[1] = a.y; r[2] = a.z; r[3] = a.w;
+    r[4] = b.x; r[5] = b.y; r[6] = b.z; r[7] = b.w;
+  } else {
+#pragma unroll
+    for (int k = 0; k < kItems; ++k) r[k] = (k < nvalid) ? __ldg(rew + p0 + k) : 0.f;
+  }
+
+  float vcur[kItems], delta[kItems];
   unsigned int last_bits = 0;
   const double gl = double(p.gl);
-
   if (nvalid > 0) {
-    // rewards do not depend on the sequence lookup: get them in flight first
-    if (p.vec_ok && nvalid == kItems) {
-      const float4 a = __ldg(reinterpret_cast<const float4*>(p.rewards + j0));
-      const float4 b = __ldg(reinterpret_cast<const float4*>(p.rewards + j0) + 1);
-      r[0] = a.x; r[1] = a.y; r[2] = a.z; r[3] = a.w;
-      r[4] = b.x; r[5] = b.y; r[6] = b.z; r[7] = b.w;
+    // my sequence: start from the tile's (prep kernel, or sequence 0 for a single tile) and walk the
+    // few sequence ends that lie before my first token; cu entries are shared by the CTA -> L1 hits
+    int seq = 0;
+    int64_t end0;
+    if (ntiles > 1) {
+      const int2 se = *reinterpret_cast<const int2*>(&desc[tile].seq0);
+      seq = se.x;
+      end0 = se.y;
     } else {
-#pragma unroll
-      for (int k = 0; k < kItems; ++k) r[k] = (k < nvalid) ? __ldg(p.rewards + j0 + k) : 0.f;
+      end0 = __ldg(p.cu + 1);
     }
-    // sequence of the first token: smallest i with cu[i+1] > j0
-    int64_t lo = 0, hi = p.B - 1;
-    while (lo < hi) {
-      const int64_t mid = (lo + hi) >> 1;
-      if (int64_t(__ldg(p.cu + mid + 1)) > j0) hi = mid; else lo = mid + 1;
+    int next_b = static_cast<int>(end0 - tile_start);   // position right after `seq` ends
+    int steps = 0;
+    while (next_b <= p0 && seq < B - 1) {
+      if (++steps > 16) {           // many tiny sequences: finish with a binary search
+        int lo = seq, hi = B - 1;
+        const int64_t j0 = tile_start + p0;
+        while (lo < hi) {
+          const int mid = (lo + hi) >> 1;
+          if (int64_t(__ldg(p.cu + mid + 1)) > j0) hi = mid; else lo = mid + 1;
+        }
+        seq = lo;
+        next_b = static_cast<int>(int64_t(__ldg(p.cu + seq + 1)) - tile_start);
+        break;
+      }
+      ++seq;
+      next_b = static_cast<int>(int64_t(__ldg(p.cu + seq + 1)) - tile_start);
     }
-    int64_t seq = lo;
-    int64_t cu_next = __ldg(p.cu + seq + 1);
-    float vprev = 0.f;
-    bool chain = false;       // vprev holds values[j + seq] for the current token
+    if (nvalid == kItems && next_b >= p0 + kItems) {
+      // fast path: all 8 tokens in one sequence; only the last one can be a sequence end
+      const float* vp = val + p0 + seq;
+      float v[kItems + 1];
 #pragma unroll
-    for (int k = 0; k < kItems; ++k) {
-      if (k < nvalid) {
-        const int64_t j = j0 + k;
-        while (seq < p.B - 1 && j >= cu_next) {
-          ++seq;
-          cu_next = p.cu[seq + 1];
-          chain = false;
+      for (int k = 0; k <= kItems; ++k) v[k] = __ldg(vp + k);
+      if (next_b == p0 + kItems) {
+        last_bits = 1u << (kItems - 1);
+        if (!p.bootstrap[seq]) v[kItems] = 0.f;                  // gae.cu:23
+      }
+#pragma unroll
+      for (int k = 0; k < kItems; ++k) {
+        vcur[k] = v[k];
+        delta[k] = __fsub_rn(__fadd_rn(r[k], __fmul_rn(p.g, v[k + 1])), v[k]);   // ppo_functional.py:316
+      }
+    } else {
+      // a sequence end inside this thread's tokens (or a ragged last tile): walk token by token
+      float vprev = 0.f;
+      bool chain = false;
+#pragma unroll
+      for (int k = 0; k < kItems; ++k) {
+        if (k < nvalid) {
+          const int pos = p0 + k;
+          while (seq < B - 1 && pos >= next_b) {
+            ++seq;
+            next_b = static_cast<int>(int64_t(__ldg(p.cu + seq + 1)) - tile_start);
+            chain = false;
+          }
+          const bool is_last = (pos + 1 == next_b);
+          const float v = chain ? vprev : __ldg(val + pos + seq);
+          float nv = __ldg(val + pos + seq + 1);
+          vprev = nv;
+          chain = !is_last;
+          if (is_last) {
+            last_bits |= 1u << k;
+            if (!p.bootstrap[seq]) nv = 0.f;
+          }
+          vcur[k] = v;
+          delta[k] = __fsub_rn(__fadd_rn(r[k], __fmul_rn(p.g, nv)), v);
         }
-        const bool is_last = (j + 1 == cu_next);
-        const int64_t vi = j + seq;
-        const float v = chain ? vprev : __ldg(p.values + vi);
-        float nv = __ldg(p.values + vi + 1);
-        vprev = nv;
-        chain = !is_last;      // next token of the same sequence reads values[vi + 1]
-        if (is_last) {
-          last_bits |= 1u << k;
-          if (!p.bootstrap[seq]) nv = 0.f;                      // gae.cu:23
-        }
-        vcur[k] = v;
-        // ppo_functional.py:316, fp32, unfused
-        delta[k] = __fsub_rn(__fadd_rn(r[k], __fmul_rn(p.g, nv)), v);
       }
     }
   }
 
-  // fold the thread's maps right-to-left
+  // fold the thread's maps right-to-left, parking the per-token values on the way
   Affine agg = ident();
 #pragma unroll
   for (int k = kItems - 1; k >= 0; --k) {
@@ -183,23 +249,35 @@ gae1d_kernel(const Gae1dParams p) {
       const double a = (last_bits >> k) & 1u ? 0.0 : gl;
       agg.b = fma(a, agg.b, double(delta[k]));
       agg.a = a * agg.a;
+      v_sm[k][tid] = vcur[k];
+      d_sm[k][tid] = delta[k];
     }
   }
 
-  Affine excl, tagg;
-  block_suffix_scan(agg, wsm, warp, lane, excl, tagg);
+  // block-wide suffix scan: warp shuffle, then warps through shared memory
+  Affine inc = agg;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const Affine o = shfl_down(inc, d);
+    if (lane + d < 32) inc = compose(inc, o);
+  }
+  if (lane == 0) wsm[warp] = inc;
+  __syncthreads();
+  Affine W = ident();
+  for (int w = kWarps - 1; w > warp; --w) W = compose(wsm[w], W);
+  const Affine nxt = shfl_down(inc, 1);
+  const Affine excl = (lane < 31) ? compose(nxt, W) : W;
 
   double carry = 0.0;
   if (ntiles > 1) {
     if (tid == 0) {
+      const Affine tagg = compose(inc, W);          // thread 0: whole tile
       TileDesc* me = desc + tile;
       if (tile == ntiles - 1) {
-        me->inc = tagg.b;            // nothing to the right: A_{T} = 0
-        st_release_u32(&me->flag, 2u);
+        st_relaxed_f64(&me->inc, tagg.b);           // nothing to the right: A_{T} = 0
       } else {
-        me->agg_a = tagg.a;
-        me->agg_b = tagg.b;
-        st_release_u32(&me->flag, 1u);
+        st_relaxed_f64(&me->agg_a, tagg.a);
+        st_relaxed_f64(&me->agg_b, tagg.b);
         Affine run = ident();        // maps of tiles tile+1 .. k-1
         for (int64_t k = tile + 1;; ++k) {
           if (k >= ntiles || run.a == 0.0) {
@@ -207,16 +285,23 @@ gae1d_kernel(const Gae1dParams p) {
             break;
           }
           const TileDesc* d = desc + k;
-          unsigned int f;
-          while ((f = ld_acquire_u32(&d->flag)) == 0u) { __nanosleep(20); }
-          if (f == 2u) {
-            carry = fma(run.a, ld_volatile_f64(&d->inc), run.b);
+          unsigned long long vi, va, vb;
+          for (;;) {
+            vi = ld_relaxed_u64(&d->inc);
+            if (vi != kEmpty) break;
+            va = ld_relaxed_u64(&d->agg_a);
+            vb = ld_relaxed_u64(&d->agg_b);
+            if (va != kEmpty && vb != kEmpty) break;
+            __nanosleep(20);
+          }
+          if (vi != kEmpty) {
+            carry = fma(run.a, __longlong_as_double(static_cast<long long>(vi)), run.b);
             break;
           }
-          run = compose(run, Affine{ld_volatile_f64(&d->agg_a), ld_volatile_f64(&d->agg_b)});
+          run = compose(run, Affine{__longlong_as_double(static_cast<long long>(va)),
+                                    __longlong_as_double(static_cast<long long>(vb))});
         }
-        me->inc = fma(tagg.a, carry, tagg.b);
-        st_release_u32(&me->flag, 2u);
+        st_relaxed_f64(&me->inc, fma(tagg.a, carry, tagg.b));
       }
       carry_sm = carry;
     }
@@ -231,28 +316,27 @@ gae1d_kernel(const Gae1dParams p) {
     for (int k = kItems - 1; k >= 0; --k) {
       if (k < nvalid) {
         const double a = (last_bits >> k) & 1u ? 0.0 : gl;
-        A = fma(a, A, double(delta[k]));
+        A = fma(a, A, double(d_sm[k][tid]));
         adv[k] = float(A);
-        ret[k] = __fadd_rn(adv[k], vcur[k]);                    // ppo_functional.py:319
+        ret[k] = __fadd_rn(adv[k], v_sm[k][tid]);               // ppo_functional.py:319
       }
     }
+    float* ao = p.adv + tile_start + p0;
+    float* ro = p.ret + tile_start + p0;
     if (p.vec_ok && nvalid == kItems) {
-      float4* ao = reinterpret_cast<float4*>(p.adv + j0);
-      float4* ro = reinterpret_cast<float4*>(p.ret + j0);
-      ao[0] = make_float4(adv[0], adv[1], adv[2], adv[3]);
-      ao[1] = make_float4(adv[4], adv[5], adv[6], adv[7]);
-      ro[0] = make_float4(ret[0], ret[1], ret[2], ret[3]);
-      ro[1] = make_float4(ret[4], ret[5], ret[6], ret[7]);
+      reinterpret_cast<float4*>(ao)[0] = make_float4(adv[0], adv[1], adv[2], adv[3]);
+      reinterpret_cast<float4*>(ao)[1] = make_float4(adv[4], adv[5], adv[6], adv[7]);
+      reinterpret_cast<float4*>(ro)[0] = make_float4(ret[0], ret[1], ret[2], ret[3]);
+      reinterpret_cast<float4*>(ro)[1] = make_float4(ret[4], ret[5], ret[6], ret[7]);
     } else {
 #pragma unroll
       for (int k = 0; k < kItems; ++k)
         if (k < nvalid) {
-          p.adv[j0 + k] = adv[k];
-          p.ret[j0 + k] = ret[k];
+          ao[k] = adv[k];
+          ro[k] = ret[k];
         }
     }
   }
-
 }
 
 // ---- padded [B,S] masked (areal-lite) ----------------------------------------------------------------
@@ -441,8 +525,10 @@ int launch_gae1d(const Gae1dParams& p, cudaStream_t stream) {
   if (p.T == 0) return kOk;
   const int64_t ntiles = (p.T + kTile - 1) / kTile;
   if (ntiles > 1) {
-    // the tile flags must start at zero: clear exactly the descriptors this launch uses
-    AB_CUDA(cudaMemsetAsync(p.workspace, 0, sizeof(WorkspaceHeader) + size_t(ntiles) * sizeof(TileDesc), stream));
+    // descriptors start "empty" and carry each tile's first sequence: one tiny kernel, stream-ordered
+    TileDesc* desc = reinterpret_cast<TileDesc*>(reinterpret_cast<char*>(p.workspace) + sizeof(WorkspaceHeader));
+    gae1d_prep_kernel<<<static_cast<unsigned int>((ntiles + 255) / 256), 256, 0, stream>>>(
+        p.cu, static_cast<int>(p.B), p.T, ntiles, desc, kTile);
   }
   gae1d_kernel<<<static_cast<unsigned int>(ntiles), kThreads, 0, stream>>>(p);
   return check_launch("gae1d");
@@ -451,8 +537,8 @@ int launch_gae1d(const Gae1dParams& p, cudaStream_t stream) {
 // Allocation-free launch: same kernel, look-back descriptors in g_gae1d_static_scratch.
 // Set-up happens on the first call per device (with that device current): the symbol is resolved to
 // its address on THAT device and cached.  Every call then clears the part of the array it is about
-// to use (ticket, done counter and the tile flags must start at zero, and the array still holds
-// whatever the previous call -- possibly a larger or an aborted one -- left there).
+// to use (every tile descriptor must start out "empty", and the array still holds whatever the
+// previous call -- possibly a larger or an aborted one -- left there).
 int launch_gae1d_static(Gae1dParams p, cudaStream_t stream) {
   static_assert(AB_GAE1D_STATIC_SCRATCH_BYTES ==
                     int64_t(sizeof(WorkspaceHeader)) + (AB_GAE1D_STATIC_MAX_TOKENS / kTile) * int64_t(sizeof(TileDesc)),
@@ -487,7 +573,9 @@ int launch_gae1d_static(Gae1dParams p, cudaStream_t stream) {
   }
   const int64_t ntiles = (p.T + kTile - 1) / kTile;
   if (ntiles > 1) {
-    AB_CUDA(cudaMemsetAsync(scratch, 0, sizeof(WorkspaceHeader) + size_t(ntiles) * sizeof(TileDesc), stream));
+    TileDesc* desc = reinterpret_cast<TileDesc*>(reinterpret_cast<char*>(scratch) + sizeof(WorkspaceHeader));
+    gae1d_prep_kernel<<<static_cast<unsigned int>((ntiles + 255) / 256), 256, 0, stream>>>(
+        p.cu, static_cast<int>(p.B), p.T, ntiles, desc, kTile);
   }
   p.workspace = scratch;
   gae1d_kernel<<<static_cast<unsigned int>(ntiles), kThreads, 0, stream>>>(p);
