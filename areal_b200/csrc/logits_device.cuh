@@ -127,5 +127,97 @@ __device__ __forceinline__ uint4 grad_vec(const uint4& q, const RowGrad& g, floa
 }
 
 
+// ---- element traits: how a 16-byte vector of logits unpacks to fp32 and packs back -------------------
+struct ElemBF16 {
+  static constexpr int kN = 8, kSize = 2;
+  __device__ static __forceinline__ void unpack(const uint4& q, float (&x)[8]) {
+    x[0] = bf16_lo(q.x); x[1] = bf16_hi(q.x); x[2] = bf16_lo(q.y); x[3] = bf16_hi(q.y);
+    x[4] = bf16_lo(q.z); x[5] = bf16_hi(q.z); x[6] = bf16_lo(q.w); x[7] = bf16_hi(q.w);
+  }
+  __device__ static __forceinline__ uint4 pack(const float (&d)[8]) {
+    return make_uint4(pack_bf16x2(d[0], d[1]), pack_bf16x2(d[2], d[3]), pack_bf16x2(d[4], d[5]), pack_bf16x2(d[6], d[7]));
+  }
+};
+struct ElemFP16 {
+  static constexpr int kN = 8, kSize = 2;
+  __device__ static __forceinline__ void unpack(const uint4& q, float (&x)[8]) {
+    const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&w[i]));
+      x[2 * i] = f.x;
+      x[2 * i + 1] = f.y;
+    }
+  }
+  __device__ static __forceinline__ uint4 pack(const float (&d)[8]) {
+    uint32_t w[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const __half2 h = __floats2half2_rn(d[2 * i], d[2 * i + 1]);
+      w[i] = *reinterpret_cast<const uint32_t*>(&h);
+    }
+    return make_uint4(w[0], w[1], w[2], w[3]);
+  }
+};
+struct ElemFP32 {
+  static constexpr int kN = 4, kSize = 4;
+  __device__ static __forceinline__ void unpack(const uint4& q, float (&x)[4]) {
+    x[0] = __uint_as_float(q.x); x[1] = __uint_as_float(q.y); x[2] = __uint_as_float(q.z); x[3] = __uint_as_float(q.w);
+  }
+  __device__ static __forceinline__ uint4 pack(const float (&d)[4]) {
+    return make_uint4(__float_as_uint(d[0]), __float_as_uint(d[1]), __float_as_uint(d[2]), __float_as_uint(d[3]));
+  }
+};
+
+// statistics of kV vectors at once (one rebase per batch), any element type
+template <typename E, bool kMinMax, int kV>
+__device__ __forceinline__ void consume_batch(RowState& st, const uint4 (&q)[kV], float c2) {
+  float x[kV][E::kN];
+  float mx = -INFINITY, mn = INFINITY;
+#pragma unroll
+  for (int j = 0; j < kV; ++j) {
+    E::unpack(q[j], x[j]);
+#pragma unroll
+    for (int i = 0; i < E::kN; ++i) {
+      mx = fmaxf(mx, x[j][i]);
+      if (kMinMax) mn = fminf(mn, x[j][i]);
+    }
+  }
+  if (kMinMax) st.mn = fminf(st.mn, mn);
+  const float nb = state_rebase(st, mx, c2);
+  float s0 = 0.f, s1 = 0.f, w0 = 0.f, w1 = 0.f;
+#pragma unroll
+  for (int j = 0; j < kV; ++j) {
+#pragma unroll
+    for (int i = 0; i < E::kN; i += 2) {
+      const float t0 = fmaf(x[j][i], c2, nb), t1 = fmaf(x[j][i + 1], c2, nb);
+      const float e0 = ex2_approx(t0), e1 = ex2_approx(t1);
+      s0 += e0;
+      w0 = fmaf(e0, t0, w0);
+      s1 += e1;
+      w1 = fmaf(e1, t1, w1);
+    }
+  }
+  st.s += s0 + s1;
+  st.w += w0 + w1;
+}
+
+template <typename E>
+__device__ __forceinline__ uint4 grad_vec_t(const uint4& q, const RowGrad& g, float c2, int64_t lab_off) {
+  float x[E::kN], d[E::kN];
+  E::unpack(q, x);
+#pragma unroll
+  for (int i = 0; i < E::kN; ++i) {
+    const float pv = ex2_approx(fmaf(x[i] - g.m, c2, g.nl2s));
+    d[i] = pv * fmaf(x[i], g.k1, g.k0);
+  }
+  if (lab_off >= 0 && lab_off < E::kN) {
+#pragma unroll
+    for (int i = 0; i < E::kN; ++i)
+      if (i == lab_off) d[i] += g.gl;
+  }
+  return E::pack(d);
+}
+
 }  // namespace dev
 }  // namespace ab

@@ -178,8 +178,11 @@ __device__ __forceinline__ void loss_finalize(const LogitsFwdParams& p, const Lo
   }
 }
 
+template <typename E> struct IsBF16 { static constexpr bool value = false; };
+template <> struct IsBF16<ElemBF16> { static constexpr bool value = true; };
+
 // ---- TMA-staged forward ------------------------------------------------------------------------
-template <bool kMinMax>
+template <bool kMinMax, typename E>
 __global__ void __launch_bounds__(kThreads, kCtasPerSm)
 logits_fwd_tma_kernel(const LogitsFwdParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -190,7 +193,7 @@ logits_fwd_tma_kernel(const LogitsFwdParams p) {
   const int tid = threadIdx.x;
   const int warp = tid >> 5, lane = tid & 31;
   const uint32_t ring = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const int64_t row_bytes = p.V * 2;
+  const int64_t row_bytes = p.V * E::kSize;
   const int nchunk = static_cast<int>((row_bytes + kStageBytes - 1) / kStageBytes);
   const uint32_t tail_bytes = static_cast<uint32_t>(row_bytes - int64_t(nchunk - 1) * kStageBytes);
 
@@ -240,13 +243,23 @@ logits_fwd_tma_kernel(const LogitsFwdParams p) {
       mbar_wait(smem_u32(&full_bar[stage]), phase);
       const uint32_t sbase = ring + stage * kStageBytes;
       if (c != nchunk - 1 || tail_bytes == kStageBytes) {
-        consume_full_stage<kMinMax>(st, sbase, tid, c2);
+        if constexpr (E::kSize == 2 && E::kN == 8 && sizeof(E) == sizeof(ElemBF16) && IsBF16<E>::value) {
+          consume_full_stage<kMinMax>(st, sbase, tid, c2);
+        } else {
+          uint4 q[kVecPerThread];
+#pragma unroll
+          for (int j = 0; j < kVecPerThread; ++j) q[j] = lds_v4(sbase + (tid + j * kConsumers) * 16);
+          consume_batch<E, kMinMax, kVecPerThread>(st, q, c2);
+        }
       } else {
         const int nvec = tail_bytes >> 4;
 #pragma unroll
         for (int j = 0; j < kVecPerThread; ++j) {
           const int v = tid + j * kConsumers;
-          if (v < nvec) consume_vec<kMinMax>(st, lds_v4(sbase + v * 16), c2);
+          if (v < nvec) {
+            const uint4 q1[1] = {lds_v4(sbase + v * 16)};
+            consume_batch<E, kMinMax, 1>(st, q1, c2);
+          }
         }
       }
       __syncwarp();
@@ -337,6 +350,7 @@ __device__ __forceinline__ RowGrad row_grad(const LogitsBwdParams& p, int64_t ro
   return g;
 }
 
+template <typename E>
 __global__ void __launch_bounds__(kThreads, kCtasPerSm)
 logits_bwd_tma_kernel(const LogitsBwdParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -346,7 +360,7 @@ logits_bwd_tma_kernel(const LogitsBwdParams p) {
   const int tid = threadIdx.x;
   const int warp = tid >> 5, lane = tid & 31;
   const uint32_t ring = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const int64_t row_bytes = p.V * 2;
+  const int64_t row_bytes = p.V * E::kSize;
   const int nchunk = static_cast<int>((row_bytes + kStageBytes - 1) / kStageBytes);
   const uint32_t tail_bytes = static_cast<uint32_t>(row_bytes - int64_t(nchunk - 1) * kStageBytes);
 
@@ -414,8 +428,8 @@ logits_bwd_tma_kernel(const LogitsBwdParams p) {
       for (int j = 0; j < kVecPerThread; ++j) {
         const int v = tid + j * kConsumers;
         if (v < nvec) {
-          const int64_t e0 = int64_t(c) * (kStageBytes / 2) + int64_t(v) * 8;
-          stg_stream_v4(dst + e0 * 2, grad_vec(q[j], g, c2, lab - e0));
+          const int64_t e0 = int64_t(c) * (kStageBytes / E::kSize) + int64_t(v) * E::kN;
+          stg_stream_v4(dst + e0 * E::kSize, grad_vec_t<E>(q[j], g, c2, lab - e0));
         }
       }
       if (++stage == kStages) {
@@ -521,8 +535,14 @@ __global__ void vocab_combine_kernel(const float* __restrict__ parts, int R, int
 }
 
 bool tma_ok(const void* ptr, int dtype, int64_t V, int64_t row_stride_bytes) {
-  return dtype == kBF16 && (reinterpret_cast<uintptr_t>(ptr) & 15) == 0 && (V % 8) == 0 &&
-         (row_stride_bytes % 16) == 0;
+  const int64_t es = dtype == kFP32 ? 4 : 2;
+  return (reinterpret_cast<uintptr_t>(ptr) & 15) == 0 && ((V * es) % 16) == 0 && (row_stride_bytes % 16) == 0;
+}
+
+template <typename K>
+int set_smem(K kern) {
+  AB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kSmemBytes)));
+  return kOk;
 }
 
 int grid_for(int64_t T, int per_sm) {
@@ -538,13 +558,21 @@ int launch_logits_fwd(const LogitsFwdParams& p, cudaStream_t stream) {
   if (p.T == 0) return kOk;
   const bool minmax = p.raw_min != nullptr;
   if (tma_ok(p.logits, p.dtype, p.V, p.row_stride_bytes)) {
-    static bool attr_set[2] = {false, false};
-    auto kern = minmax ? logits_fwd_tma_kernel<true> : logits_fwd_tma_kernel<false>;
-    if (!attr_set[minmax]) {
-      AB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kSmemBytes)));
-      attr_set[minmax] = true;
-    }
-    kern<<<grid_for(p.T, kCtasPerSm), kThreads, kSmemBytes, stream>>>(p);
+    const int grid = grid_for(p.T, kCtasPerSm);
+#define AB_LAUNCH_FWD(MM, E)                                                       \
+  {                                                                                \
+    static bool done = false;                                                      \
+    if (!done) {                                                                   \
+      const int rc = set_smem(logits_fwd_tma_kernel<MM, E>);                       \
+      if (rc) return rc;                                                           \
+      done = true;                                                                 \
+    }                                                                              \
+    logits_fwd_tma_kernel<MM, E><<<grid, kThreads, kSmemBytes, stream>>>(p);       \
+  }
+    if (p.dtype == kBF16) { if (minmax) AB_LAUNCH_FWD(true, ElemBF16) else AB_LAUNCH_FWD(false, ElemBF16) }
+    else if (p.dtype == kFP16) { if (minmax) AB_LAUNCH_FWD(true, ElemFP16) else AB_LAUNCH_FWD(false, ElemFP16) }
+    else { if (minmax) AB_LAUNCH_FWD(true, ElemFP32) else AB_LAUNCH_FWD(false, ElemFP32) }
+#undef AB_LAUNCH_FWD
   } else {
     const int grid = grid_for(p.T, 8);
     if (p.dtype == kBF16) logits_fwd_generic_kernel<__nv_bfloat16><<<grid, kConsumers, 0, stream>>>(p);
@@ -558,13 +586,21 @@ int launch_logits_bwd(const LogitsBwdParams& p, cudaStream_t stream) {
   if (p.T == 0) return kOk;
   if (tma_ok(p.logits, p.dtype, p.V, p.row_stride_bytes) &&
       tma_ok(p.dlogits, p.dtype, p.V, p.d_row_stride_bytes)) {
-    static bool attr_set = false;
-    if (!attr_set) {
-      AB_CUDA(cudaFuncSetAttribute(logits_bwd_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                   int(kSmemBytes)));
-      attr_set = true;
-    }
-    logits_bwd_tma_kernel<<<grid_for(p.T, kCtasPerSm), kThreads, kSmemBytes, stream>>>(p);
+    const int grid = grid_for(p.T, kCtasPerSm);
+#define AB_LAUNCH_BWD(E)                                                           \
+  {                                                                                \
+    static bool done = false;                                                      \
+    if (!done) {                                                                   \
+      const int rc = set_smem(logits_bwd_tma_kernel<E>);                           \
+      if (rc) return rc;                                                           \
+      done = true;                                                                 \
+    }                                                                              \
+    logits_bwd_tma_kernel<E><<<grid, kThreads, kSmemBytes, stream>>>(p);           \
+  }
+    if (p.dtype == kBF16) AB_LAUNCH_BWD(ElemBF16)
+    else if (p.dtype == kFP16) AB_LAUNCH_BWD(ElemFP16)
+    else AB_LAUNCH_BWD(ElemFP32)
+#undef AB_LAUNCH_BWD
   } else {
     const int grid = grid_for(p.T, 8);
     if (p.dtype == kBF16) logits_bwd_generic_kernel<__nv_bfloat16><<<grid, kConsumers, 0, stream>>>(p);

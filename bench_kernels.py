@@ -240,7 +240,7 @@ def bench_logits(out):
     Tf = 2048
     lf = torch.randn(Tf, V, device=DEV)
     ms = timeit(lambda: F.gather_logprobs_entropy(lf, labels[:Tf], 1.0))
-    out.append(row("logits_fwd generic kernel (fp32 logits)", ms, 4 * Tf * V, tokens_per_s=Tf / (ms * 1e-3)))
+    out.append(row("logits_fwd TMA kernel (fp32 logits)", ms, 4 * Tf * V, tokens_per_s=Tf / (ms * 1e-3)))
     odd = logits.detach()[:Tf, 1:V - 7]
     ms = timeit(lambda: F.gather_logprobs_entropy(odd, labels[:Tf] % (V - 8), 1.0))
     out.append(row("logits_fwd generic kernel (bf16, misaligned rows)", ms, 2 * Tf * (V - 8), tokens_per_s=Tf / (ms * 1e-3)))

@@ -225,3 +225,27 @@ def test_peaked_rows_keep_relative_accuracy():
     lab = labels.numpy()
     at_label = got[np.arange(T), lab]
     assert np.all(np.abs(at_label - ref_g[np.arange(T), lab]) <= 0.05 * np.abs(ref_g[np.arange(T), lab]) + 1.5e-7)
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.float32])
+@pytest.mark.parametrize("V", [18992, 4099])
+def test_backward_other_dtypes(dtype, V):
+    """fp16 / fp32 logits (Megatron can hand fp32, areal/utils/data.py:762-763): TMA-staged kernels when
+    rows are 16-byte aligned, generic kernel otherwise; gradient in the logits' dtype."""
+    from areal_b200 import functional as F
+    g = torch.Generator().manual_seed(V + 1)
+    T = 41
+    logits = (torch.randn(T, V, generator=g) * 2.0).to(dtype)
+    labels = torch.randint(0, V, (T,), generator=g)
+    labels[0], labels[1] = 0, V - 1
+    x = logits.to(D).requires_grad_()
+    lp, ent = F.gather_logprobs_entropy(x, labels.to(D), 0.8)
+    w = torch.randn(T, generator=g)
+    wh = torch.randn(T, generator=g) * 0.1
+    ((lp * w.to(D)).sum() + (ent * wh.to(D)).sum()).backward()
+    assert x.grad.dtype == dtype
+    ref = O.dlogits(logits.float().numpy(), labels.numpy(), 0.8, w.numpy(), wh.numpy())
+    got = x.grad.float().cpu().numpy().astype(np.float64)
+    scale = np.maximum(np.abs(ref).max(-1, keepdims=True), 1e-3 * (np.abs(w.numpy()) + 12 * np.abs(wh.numpy()))[:, None] / 0.8)
+    ulp = 2 ** -11 if dtype == torch.float16 else 2 ** -23
+    assert np.all(np.abs(got - ref) <= ulp * np.abs(ref) + H.TOL_LOGITS * scale + 1e-30)
