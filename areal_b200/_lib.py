@@ -44,6 +44,12 @@ SIGNATURES = {
                                                P, P, P, P, P, P, P, P, P, P, P, P, P, P, P, P,
                                                P, P, I64, c_int, c_int, P, I64, P]),
     "areal_b200_rescale_grad_if_needed": (c_int, [P, I64, I64, I64, P, P, P]),
+    "areal_b200_norm_num_partials": (I64, [I64]),
+    "areal_b200_masked_moments": (c_int, [P, P, I64, I64, I64, P, P]),
+    "areal_b200_norm_centered_sumsq": (c_int, [P, P, c_int, c_int, c_int, I64, I64, P, I64, I64, I64, P, P]),
+    "areal_b200_norm_apply": (c_int, [P, P, I64, c_int, c_int, c_int, I64, I64, P, c_int, c_int, c_int, I64, I64, P,
+                                      F64, P, P, P]),
+    "areal_b200_masked_normalization_apply": (c_int, [P, P, I64, P, c_int, F64, P, P]),
     "areal_b200_interval_workspace_bytes": (I64, [I64]),
     "areal_b200_slice_intervals": (c_int, [P, I64, P, I64, P, I64, I64, P, I64, P]),
     "areal_b200_set_intervals": (c_int, [P, I64, P, I64, P, I64, I64, P, I64, P]),

@@ -9,6 +9,7 @@
 #include "gae_scan.h"
 #include "interval_copy.h"
 #include "logits_fused.h"
+#include "masked_norm.h"
 #include "ppo_loss.h"
 
 namespace ab {
@@ -504,6 +505,87 @@ AREAL_B200_API int areal_b200_rescale_grad_if_needed(void* dlogits, int64_t T, i
   AB_REQUIRE(T == 0 || (dlogits && upstream), "null pointer");
   return launch_rescale_if_needed(dlogits, T, V, d_row_stride * 2, upstream, assumed,
                                   static_cast<cudaStream_t>(stream));
+}
+
+// ---- next row: normalisation -------------------------------------------------------------------------
+AREAL_B200_API int64_t areal_b200_norm_num_partials(int64_t group_elems) {
+  return norm_num_partials(group_elems < 0 ? 0 : group_elems);
+}
+
+AREAL_B200_API int areal_b200_masked_moments(const float* x, const float* mask, int64_t n_groups,
+                                             int64_t group_elems, int64_t n_partials, double* partials,
+                                             void* stream) {
+  AB_REQUIRE(n_groups >= 0 && group_elems >= 0 && n_partials >= 1 && n_partials <= 65535, "bad sizes");
+  AB_REQUIRE(n_groups <= 65535, "at most 65535 groups per call");
+  if (n_groups == 0 || group_elems == 0) return kOk;
+  AB_REQUIRE(x && partials, "null pointer");
+  return launch_moments(x, mask, n_groups, group_elems, n_partials, partials, static_cast<cudaStream_t>(stream));
+}
+
+static int fill_mean_spec(NormMeanSpec* ms, int mean_mode, int leave_one_out, int mean_zero_special,
+                          int64_t mean_group_elems, int64_t n_mean_groups, const double* mean_stats) {
+  AB_REQUIRE(mean_mode >= 0 && mean_mode <= 2, "mean_mode must be 0 (batch), 1 (group) or 2 (none)");
+  AB_REQUIRE(mean_mode == kNormNone || (mean_group_elems > 0 && mean_stats), "mean statistics required");
+  ms->mode = mean_mode;
+  ms->leave_one_out = leave_one_out;
+  ms->zero_special = mean_zero_special;
+  ms->group_elems = mean_group_elems > 0 ? mean_group_elems : 1;
+  ms->n_groups = n_mean_groups;
+  ms->stats = mean_stats;
+  return kOk;
+}
+
+AREAL_B200_API int areal_b200_norm_centered_sumsq(const float* x, const float* mask, int mean_mode,
+                                                  int leave_one_out, int mean_zero_special,
+                                                  int64_t mean_group_elems, int64_t n_mean_groups,
+                                                  const double* mean_stats, int64_t n_std_groups,
+                                                  int64_t std_group_elems, int64_t n_partials,
+                                                  double* partials, void* stream) {
+  AB_REQUIRE(n_std_groups >= 0 && n_std_groups <= 65535 && std_group_elems >= 0, "bad std grouping");
+  AB_REQUIRE(n_partials >= 1 && n_partials <= 65535, "bad n_partials");
+  if (n_std_groups == 0 || std_group_elems == 0) return kOk;
+  AB_REQUIRE(x && partials, "null pointer");
+  NormMeanSpec ms;
+  const int rc = fill_mean_spec(&ms, mean_mode, leave_one_out, mean_zero_special, mean_group_elems, n_mean_groups,
+                                mean_stats);
+  if (rc) return rc;
+  return launch_centered_sumsq(x, mask, ms, n_std_groups, std_group_elems, n_partials, partials,
+                               static_cast<cudaStream_t>(stream));
+}
+
+AREAL_B200_API int areal_b200_norm_apply(const float* x, const float* mask, int64_t N, int mean_mode,
+                                         int leave_one_out, int mean_zero_special, int64_t mean_group_elems,
+                                         int64_t n_mean_groups, const double* mean_stats, int std_mode,
+                                         int std_unbiased, int std_one_special, int64_t std_group_elems,
+                                         int64_t n_std_groups, const double* std_stats, double eps,
+                                         const float* total_mask_sum, float* out, void* stream) {
+  AB_REQUIRE(N >= 0, "negative N");
+  if (N == 0) return kOk;
+  AB_REQUIRE(x && out, "null pointer");
+  AB_REQUIRE(std_mode >= 0 && std_mode <= 2, "std_mode must be 0 (batch), 1 (group) or 2 (none)");
+  AB_REQUIRE(std_mode == kNormNone || (std_group_elems > 0 && std_stats), "std statistics required");
+  NormMeanSpec ms;
+  const int rc = fill_mean_spec(&ms, mean_mode, leave_one_out, mean_zero_special, mean_group_elems, n_mean_groups,
+                                mean_stats);
+  if (rc) return rc;
+  NormStdSpec ss;
+  ss.mode = std_mode;
+  ss.unbiased = std_unbiased;
+  ss.one_special = std_one_special;
+  ss.group_elems = std_group_elems > 0 ? std_group_elems : 1;
+  ss.n_groups = n_std_groups;
+  ss.stats = std_stats;
+  ss.eps = eps;
+  return launch_norm_apply(x, mask, N, ms, ss, total_mask_sum, out, static_cast<cudaStream_t>(stream));
+}
+
+AREAL_B200_API int areal_b200_masked_normalization_apply(const float* x, const float* mask, int64_t N,
+                                                         const double* stats, int unbiased, double eps,
+                                                         float* out, void* stream) {
+  AB_REQUIRE(N >= 0, "negative N");
+  if (N == 0) return kOk;
+  AB_REQUIRE(x && stats && out, "null pointer");
+  return launch_masked_normalization_apply(x, mask, N, stats, unbiased, eps, out, static_cast<cudaStream_t>(stream));
 }
 
 // ---- P4 ------------------------------------------------------------------------------------------

@@ -1,0 +1,140 @@
+"""Host-side mirror of the normalisation entry points next to the hot path:
+`Normalization` / `NormConfig` (areal/utils/data.py:1073-1304, areal/api/cli_args.py:24-59) and
+`masked_normalization` (areal/utils/functional.py:130-168).  Same constructor checks, call signature and
+results; three kernel launches instead of a Python loop over groups, no `.item()` host syncs, and ONE
+all-reduce per statistic under data parallelism.  CUDA tensors only."""
+from __future__ import annotations
+
+import dataclasses
+from typing import Optional
+
+import torch
+import torch.distributed as dist
+
+from . import _lib
+from ._lib import call, ptr, stream_ptr
+
+_MODE = {"batch": 0, "group": 1, None: 2}
+
+
+@dataclasses.dataclass
+class NormConfig:
+    """Field names and defaults of the reference's NormConfig (areal/api/cli_args.py:24-59)."""
+    mean_level: Optional[str] = "batch"
+    mean_leave1out: bool = False
+    std_level: Optional[str] = "batch"
+    std_unbiased: bool = True
+    eps: float = 1e-5
+    group_size: int = 1
+
+
+def _f32c(t: torch.Tensor) -> torch.Tensor:
+    return t.float().contiguous()
+
+
+def _moments(x, mask, n_groups, group_elems):
+    dev = x.device
+    P = _lib.lib().areal_b200_norm_num_partials(group_elems)
+    partials = torch.empty(n_groups, P, 3, dtype=torch.float64, device=dev)
+    with torch.cuda.device(dev):
+        call("areal_b200_masked_moments", ptr(x), ptr(mask), n_groups, group_elems, P, ptr(partials), stream_ptr(dev))
+    return partials.sum(1)
+
+
+class Normalization:
+    """Adaptive normalisation with independent levels for mean and std ("batch", "group", None);
+    drop-in for the reference class (areal/utils/data.py:1073-1204)."""
+
+    def __init__(self, config):
+        if config.mean_level not in {"batch", "group", None}:
+            raise ValueError(f"mean_level must be 'batch', 'group' or None, got {config.mean_level}")
+        if config.std_level not in {"batch", "group", None}:
+            raise ValueError(f"std_level must be 'batch', 'group', or None, got {config.std_level}")
+        if (config.mean_level == "group" or config.std_level == "group") and config.group_size is None:
+            raise ValueError("group_size must be provided if using group normalization")
+        self.mean_level = config.mean_level
+        self.mean_leave1out = config.mean_leave1out
+        self.std_level = config.std_level
+        self.std_unbiased = config.std_unbiased
+        self.group_size = config.group_size
+        self.eps = config.eps
+
+    @torch.no_grad()
+    def __call__(self, x: torch.Tensor, loss_mask: Optional[torch.Tensor] = None, high_precision: bool = True,
+                 reduce_group=None) -> torch.Tensor:
+        """`high_precision` is accepted for compatibility; statistics are always accumulated in fp64."""
+        dev = _lib.require_cuda(x, loss_mask)
+        shape = x.shape
+        bs = x.size(0)
+        xf = _f32c(x).reshape(-1)
+        mf = None if loss_mask is None else _f32c(loss_mask).reshape(-1)
+        N = xf.numel()
+        row = N // bs if bs else 0
+        total_mask = None if mf is None else mf.sum().reshape(1)            # device scalar, no sync
+        world = dist.get_world_size(reduce_group) if dist.is_initialized() else 1
+
+        def grouping(level):
+            if level == "batch":
+                return 1, N
+            if level == "group":
+                return bs // self.group_size, self.group_size * row
+            return 0, 0
+
+        # ---- mean statistics
+        gm, gem = grouping(self.mean_level)
+        mean_stats = None
+        if self.mean_level is not None and gm > 0:
+            mean_stats = _moments(xf, mf, gm, gem)
+            if self.mean_level == "batch" and world > 1:
+                dist.all_reduce(mean_stats, group=reduce_group)
+        mean_zero_special = int(self.mean_level == "group" and self.group_size == 1 and self.mean_leave1out)
+        mean_args = (_MODE[self.mean_level] if gm > 0 or self.mean_level is None else 2,
+                     int(self.mean_leave1out), mean_zero_special, gem, gm, ptr(mean_stats))
+        if self.mean_level == "group" and gm == 0:
+            mean_args = (2, 0, 0, 0, 0, None)          # no complete group: zeros_like, as upstream
+
+        # ---- std statistics
+        gs, ges = grouping(self.std_level)
+        std_stats = None
+        if self.std_level is not None and gs > 0:
+            P = _lib.lib().areal_b200_norm_num_partials(ges)
+            partials = torch.empty(gs, P, 2, dtype=torch.float64, device=dev)
+            with torch.cuda.device(dev):
+                call("areal_b200_norm_centered_sumsq", ptr(xf), ptr(mf), *mean_args, gs, ges, P, ptr(partials),
+                     stream_ptr(dev))
+            std_stats = partials.sum(1)
+            if self.std_level == "batch" and world > 1:
+                dist.all_reduce(std_stats, group=reduce_group)
+        std_one_special = int(self.std_level == "group" and self.group_size == 1 and self.std_unbiased)
+        std_mode = _MODE[self.std_level]
+        if self.std_level == "group" and gs == 0:
+            std_stats = torch.zeros(1, 2, dtype=torch.float64, device=dev)     # std stays zeros_like
+            ges, gs = max(N, 1), 0
+
+        out = torch.empty(N, dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            call("areal_b200_norm_apply", ptr(xf), ptr(mf), N, *mean_args, std_mode, int(self.std_unbiased),
+                 std_one_special, ges, gs, ptr(std_stats), float(self.eps), ptr(total_mask), ptr(out), stream_ptr(dev))
+        return out.view(shape)
+
+
+@torch.no_grad()
+def masked_normalization(x: torch.Tensor, mask: Optional[torch.Tensor] = None, dim=None, unbiased: bool = False,
+                         eps: float = 1e-5, high_precision: bool = True, all_reduce: bool = True, reduce_group=None):
+    """Drop-in for `masked_normalization` (areal/utils/functional.py:130-168) for `dim=None`: fp64
+    moments of x*mask (one all-reduce of a 3-vector instead of three), output in fp32."""
+    if dim is not None and tuple(dim) != tuple(range(x.dim())):
+        raise NotImplementedError("areal_b200.masked_normalization supports dim=None (all dimensions) only")
+    dev = _lib.require_cuda(x, mask)
+    shape = x.shape
+    xf = _f32c(x).reshape(-1)
+    mf = None if mask is None else _f32c(mask).reshape(-1)
+    N = xf.numel()
+    stats = _moments(xf, mf, 1, N).reshape(3)
+    if dist.is_initialized() and all_reduce and dist.get_world_size(reduce_group) > 1:
+        dist.all_reduce(stats, group=reduce_group)
+    out = torch.empty(N, dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        call("areal_b200_masked_normalization_apply", ptr(xf), ptr(mf), N, ptr(stats), int(unbiased), float(eps),
+             ptr(out), stream_ptr(dev))
+    return out.view(shape)

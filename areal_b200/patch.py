@@ -9,6 +9,7 @@
                     with from-imports (areal/engine/ppo/actor.py:16-22, critic.py:11,
                     areal/engine/sft/lm_engine.py:10, recipe/AEnt/actor.py:15-17).
   patch_realhf()    rebinds the GAE / loss / interval entry points of realhf's functional modules.
+  patch_areal() also rebinds `Normalization` / `masked_normalization` where they are already imported.
 """
 from __future__ import annotations
 
@@ -17,6 +18,7 @@ import os
 import sys
 import types
 
+from . import data as _D
 from . import flatten_param as _fp
 from . import functional as _F
 from . import ppo_functional as _P
@@ -59,6 +61,15 @@ def patch_areal(extra_modules=()):
     """Rebind the four functional ops wherever they are already imported; returns the patched module
     names.  Modules not imported yet are patched through `areal.utils.functional` when they import."""
     patched = []
+    # the first "next" row: Normalization / masked_normalization (areal/utils/data.py, functional.py)
+    for name in ("areal.utils.data", "areal.engine.ppo.actor", "areal.engine.ppo.critic", "areal.utils.functional"):
+        mod = sys.modules.get(name)
+        if mod is None:
+            continue
+        if hasattr(mod, "Normalization"):
+            setattr(mod, "Normalization", _D.Normalization)
+        if hasattr(mod, "masked_normalization"):
+            setattr(mod, "masked_normalization", _D.masked_normalization)
     for name in tuple(_AREAL_IMPORT_SITES) + tuple(extra_modules):
         mod = sys.modules.get(name)
         if mod is None:

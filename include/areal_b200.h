@@ -249,6 +249,46 @@ AREAL_B200_API int areal_b200_rescale_grad_if_needed(void* dlogits, int64_t T, i
                                                      const float* assumed, void* stream);
 
 /* ------------------------------------------------------------------------------------------ *
+ * Next row: advantage / reward normalisation
+ * ------------------------------------------------------------------------------------------ */
+
+/* Replaces `Normalization` (areal/utils/data.py:1073-1304: Python loops over groups, `.item()`
+ * syncs, up to 4 scalar all-reduces) and `masked_normalization` (areal/utils/functional.py:130-168)
+ * with three launches whatever the number of groups.  x, mask f32[N] (mask nullable = all ones;
+ * a float weight, as in the reference); a "group" is `group_elems` consecutive elements.
+ *   1. areal_b200_masked_moments: partials f64[n_groups, n_partials, 3] = per-slab
+ *      (sum m, sum x*m, sum (x*m)^2); the caller sums over n_partials (fixed order) and, for
+ *      batch-level statistics under data parallelism, all-reduces that one small tensor.
+ *   2. areal_b200_norm_centered_sumsq: partials f64[n_std_groups, n_partials, 2] =
+ *      (sum m, sum (x*m - mean*m)^2) with the per-element mean of `_compute_mean` (:1206-1262).
+ *   3. areal_b200_norm_apply: out = ((x - mean) * m) / (std + eps) with `_compute_std`'s rules
+ *      (:1264-1304) and the reference's dtype path (batch-level statistics fp64, group-level fp32).
+ *   modes: 0 = batch, 1 = group, 2 = none.  *_special flags: the group_size == 1 cases
+ *   (:1138-1143, :1180-1185).  total_mask_sum (device scalar, nullable): when it is 0 the input is
+ *   returned unchanged (:1115-1116) without a host sync. */
+AREAL_B200_API int64_t areal_b200_norm_num_partials(int64_t group_elems);
+AREAL_B200_API int areal_b200_masked_moments(const float* x, const float* mask, int64_t n_groups,
+                                             int64_t group_elems, int64_t n_partials, double* partials,
+                                             void* stream);
+AREAL_B200_API int areal_b200_norm_centered_sumsq(const float* x, const float* mask, int mean_mode,
+                                                  int leave_one_out, int mean_zero_special,
+                                                  int64_t mean_group_elems, int64_t n_mean_groups,
+                                                  const double* mean_stats, int64_t n_std_groups,
+                                                  int64_t std_group_elems, int64_t n_partials,
+                                                  double* partials, void* stream);
+AREAL_B200_API int areal_b200_norm_apply(const float* x, const float* mask, int64_t N, int mean_mode,
+                                         int leave_one_out, int mean_zero_special, int64_t mean_group_elems,
+                                         int64_t n_mean_groups, const double* mean_stats, int std_mode,
+                                         int std_unbiased, int std_one_special, int64_t std_group_elems,
+                                         int64_t n_std_groups, const double* std_stats, double eps,
+                                         const float* total_mask_sum, float* out, void* stream);
+/* masked_normalization's apply: stats f64[3] = (sum m, sum x*m, sum (x*m)^2);
+ * out = ((x*m - mean) / (sqrt(E[(xm)^2] - mean^2 [* n/(n-1)]) + eps)).float() */
+AREAL_B200_API int areal_b200_masked_normalization_apply(const float* x, const float* mask, int64_t N,
+                                                         const double* stats, int unbiased, double eps,
+                                                         float* out, void* stream);
+
+/* ------------------------------------------------------------------------------------------ *
  * P4  interval ops (parameter reallocation)
  * ------------------------------------------------------------------------------------------ */
 

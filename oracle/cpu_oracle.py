@@ -482,3 +482,104 @@ def gather_packed_shifted_log_probs(logits, cu_seqlens, ids):
 def calc_entropy_packed(logits, cu_seqlens):
     """`calc_entropy` (realhf/impl/model/interface/ppo_interface.py:52-58)."""
     return calc_entropy_legacy(logits)[leave_one_indices(np.asarray(logits).shape[0], cu_seqlens)]
+
+
+# --------------------------------------------------------------------------- #
+# next row (SURVEY 8f-1): advantage / reward normalisation
+# --------------------------------------------------------------------------- #
+def masked_normalization(x, mask=None, unbiased=False, eps=1e-5):
+    """`masked_normalization` (areal/utils/functional.py:130-168), dim=None, high_precision, single
+    process: fp64 moments of x*mask, var = E[x^2] - mean^2, output ((x*mask - mean)/(sqrt(var)+eps)).float()."""
+    xd = np.asarray(x, dtype=np.float64)
+    if mask is None:
+        factor = float(xd.size)
+    else:
+        md = np.asarray(mask).astype(np.float64)
+        xd = xd * md
+        factor = md.sum()
+    mean = xd.sum() / factor
+    var = (xd ** 2).sum() / factor - mean ** 2
+    if unbiased:
+        var *= factor / (factor - 1)
+    return ((xd - mean) / (np.sqrt(var) + eps)).astype(np.float32)
+
+
+def normalization(x, loss_mask, mean_level, std_level, mean_leave1out, std_unbiased, eps, group_size):
+    """`Normalization.__call__` (areal/utils/data.py:1105-1204) with `_compute_mean` (:1206-1262) and
+    `_compute_std` (:1264-1304), single process, high_precision.  The dtype path is part of the result:
+    batch-level statistics stay fp64 until the final `.float()`, group-level ones are stored into
+    `zeros_like(x)` (fp32) first (:1131, :1173)."""
+    x32 = np.asarray(x, dtype=np.float32)
+    bs = x32.shape[0]
+    m32 = None if loss_mask is None else np.asarray(loss_mask, dtype=np.float32)
+    if m32 is not None and m32.sum() == 0:
+        return x32.copy()                                                   # :1115-1116
+
+    def compute_mean(xx, mm, loo):
+        xd = xx.astype(np.float64)
+        if mm is None:
+            factor = float(xd.size)
+            xm = xd
+        else:
+            md = mm.astype(np.float64)
+            xm = xd * md
+            factor = md.sum()
+        xs = xm.sum()
+        if loo:
+            if factor <= 1:
+                return np.zeros((1,) * xd.ndim)
+            if mm is None:
+                return (xs - xd) / (factor - 1)
+            return np.where(md > 0, (xs - xm) / np.maximum(factor - md, 1.0), xs / factor)
+        if factor == 0:
+            return np.zeros((1,) * xd.ndim)
+        return np.full((1,) * xd.ndim, xs / factor)
+
+    def compute_std(xx, mm, mean, unbiased):
+        xd = xx.astype(np.float64)
+        mean = np.asarray(mean, dtype=np.float64)
+        if mm is None:
+            factor = float(xd.size)
+            ss = ((xd - mean) ** 2).sum()
+        else:
+            md = mm.astype(np.float64)
+            factor = md.sum()
+            ss = ((xd * md - mean * md) ** 2).sum()
+        if unbiased:
+            return 1.0 if factor <= 1 else np.sqrt(ss / (factor - 1))
+        return 1.0 if factor == 0 else np.sqrt(ss / factor)
+
+    ng = bs // group_size if group_size else 0
+    if mean_level == "batch":
+        mean = np.broadcast_to(compute_mean(x32, m32, mean_leave1out), x32.shape).astype(np.float64)
+    elif mean_level == "group":
+        mean = np.zeros_like(x32)
+        for i in range(ng):
+            s = slice(i * group_size, (i + 1) * group_size)
+            if group_size == 1 and mean_leave1out:
+                gm = np.zeros((1, x32.shape[1]))
+            else:
+                gm = compute_mean(x32[s], None if m32 is None else m32[s], mean_leave1out)
+            mean[s] = np.broadcast_to(gm, x32[s].shape).astype(np.float32)
+    else:
+        mean = np.zeros_like(x32)
+    xc = x32 - mean                      # fp64 for batch level, fp32 otherwise (type promotion)
+    if m32 is not None:
+        xc = xc * m32
+    if std_level == "batch":
+        std = np.float64(compute_std(x32, m32, mean, std_unbiased))
+    elif std_level == "group":
+        std = np.zeros_like(x32)
+        for i in range(ng):
+            s = slice(i * group_size, (i + 1) * group_size)
+            if group_size == 1 and std_unbiased:
+                gs_ = 1.0
+            else:
+                gs_ = compute_std(x32[s], None if m32 is None else m32[s], mean[s], std_unbiased)
+            std[s] = np.float32(gs_)
+    else:
+        std = np.ones_like(x32)
+        eps = 0.0
+    if isinstance(std, np.ndarray) and std.dtype == np.float32 and xc.dtype == np.float32:
+        return (xc / (std + np.float32(eps))).astype(np.float32)
+    return (xc / (std + eps)).astype(np.float32)

@@ -289,6 +289,59 @@ def gen_legacy_packed():
     print("legacy_packed cases:", k)
 
 
+def gen_normalization(af):
+    """`Normalization` (areal/utils/data.py:1073-1304) over the grid its own tests walk
+    (areal/tests/test_adv_norm_config.py): mean/std level x leave-one-out x unbiased x mask x group size;
+    plus `masked_normalization` (areal/utils/functional.py:130-168)."""
+    Norm, NormConfig = R.load_areal_normalization()
+    out = {}
+    g = torch.Generator().manual_seed(4242)
+    k = 0
+    for (bs, S, gs) in ((8, 16, 4), (6, 33, 2), (5, 7, 1), (7, 12, 3)):
+        for mean_level in ("batch", "group", None):
+            for std_level in ("batch", "group", None):
+                for loo in (False, True):
+                    for unbiased in (False, True):
+                        for mask_mode in ("none", "rand", "zero"):
+                            if mask_mode == "zero" and not (mean_level == "batch" and std_level == "batch"):
+                                continue
+                            if (bs, S, gs) != (8, 16, 4) and (k % 3) != 0 and mask_mode == "none":
+                                pass
+                            cfg = NormConfig(mean_level=mean_level, mean_leave1out=loo, std_level=std_level,
+                                             std_unbiased=unbiased, eps=1e-5, group_size=gs)
+                            x = torch.randn(bs, S, generator=g) * 3 + 1.5
+                            if mask_mode == "none":
+                                m = None
+                            elif mask_mode == "rand":
+                                m = (torch.rand(bs, S, generator=g) > 0.35).float()
+                                m[0] = 0.0            # a fully masked row
+                            else:
+                                m = torch.zeros(bs, S)
+                            y = Norm(cfg)(x.clone(), None if m is None else m.clone())
+                            p = f"c{k}_"
+                            out.update({p + "x": x.numpy(), p + "has_mask": np.array(m is not None),
+                                        p + "mask": (m if m is not None else torch.ones(bs, S)).numpy(),
+                                        p + "cfg": np.array([{"batch": 0, "group": 1, None: 2}[mean_level],
+                                                             {"batch": 0, "group": 1, None: 2}[std_level],
+                                                             int(loo), int(unbiased), gs]),
+                                        p + "y": y.numpy()})
+                            k += 1
+    out["n_cases"] = np.array(k)
+    j = 0
+    for (shape, use_mask, unbiased) in (((300,), True, False), ((7, 41), True, True), ((64,), False, False)):
+        x = torch.randn(*shape, generator=g) * 2 - 0.7
+        m = (torch.rand(*shape, generator=g) > 0.3) if use_mask else None
+        y = af.masked_normalization(x, m, unbiased=unbiased)
+        p = f"m{j}_"
+        out.update({p + "x": x.numpy(), p + "has_mask": np.array(use_mask),
+                    p + "mask": (m if use_mask else torch.ones(*shape, dtype=torch.bool)).numpy(),
+                    p + "unbiased": np.array(unbiased), p + "y": y.numpy()})
+        j += 1
+    out["n_masked_norm"] = np.array(j)
+    np.savez_compressed(os.path.join(OUT, "normalization.npz"), **out)
+    print("normalization cases:", k, "masked_normalization:", j)
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     assert R.available(), "needs /root/reference"
@@ -303,6 +356,7 @@ def main():
     gen_critic_loss(af, pf)
     gen_intervals(fp)
     gen_legacy_packed()
+    gen_normalization(af)
 
 
 if __name__ == "__main__":

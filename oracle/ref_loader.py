@@ -180,3 +180,36 @@ def run_realhf_calc_entropy(logits, cu_seqlens):
     exec(compile(src, "ppo_interface.py[calc_entropy]", "exec"), ns)
     with torch.no_grad():
         return ns["calc_entropy"](logits, cu_seqlens)
+
+
+def load_areal_normalization():
+    """The `Normalization` class of areal/utils/data.py (:1073-1304), extracted by AST and executed
+    where it lies (the module itself needs tensordict / einops-heavy imports).  Returns (cls, NormConfig)
+    where NormConfig is a stand-in dataclass with the reference's field names and defaults
+    (areal/api/cli_args.py:24-59)."""
+    import ast
+    import dataclasses
+    from typing import Optional
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    path = os.path.join(REF_ROOT, "areal/utils/data.py")
+    with open(path) as f:
+        src = f.read()
+    tree = ast.parse(src)
+    node = next(n for n in tree.body if isinstance(n, ast.ClassDef) and n.name == "Normalization")
+    code = ast.get_source_segment(src, node)
+
+    @dataclasses.dataclass
+    class NormConfig:
+        mean_level: Optional[str] = "batch"
+        mean_leave1out: bool = False
+        std_level: Optional[str] = "batch"
+        std_unbiased: bool = True
+        eps: float = 1e-5
+        group_size: int = 1
+
+    ns = dict(torch=torch, np=np, dist=dist, Optional=Optional, NormConfig=NormConfig)
+    exec(compile(code, "data.py[Normalization]", "exec"), ns)
+    return ns["Normalization"], NormConfig

@@ -1,0 +1,64 @@
+"""GPU parity: Normalization / masked_normalization through the C ABI vs golden vectors of the
+unmodified reference class over the grid its own tests walk (areal/tests/test_adv_norm_config.py)."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import cpu_oracle as O
+from tests import helpers as H
+
+pytestmark = pytest.mark.gpu
+D = "cuda:0"
+LEVEL = {0: "batch", 1: "group", 2: None}
+
+
+def test_normalization_golden_grid():
+    from areal_b200.data import NormConfig, Normalization
+    z = H.load("normalization.npz")
+    n = 0
+    for k, c in H.cases(z):
+        ml, sl, loo, unb, gs = (int(v) for v in c["cfg"])
+        cfg = NormConfig(mean_level=LEVEL[ml], mean_leave1out=bool(loo), std_level=LEVEL[sl], std_unbiased=bool(unb),
+                         eps=1e-5, group_size=gs)
+        x = torch.from_numpy(c["x"]).to(D)
+        m = torch.from_numpy(c["mask"]).to(D) if bool(c["has_mask"]) else None
+        y = Normalization(cfg)(x, m)
+        assert y.dtype == torch.float32 and y.shape == x.shape
+        got = y.cpu().numpy()
+        assert np.allclose(got, c["y"], rtol=1e-5, atol=1e-5), (k, c["cfg"], float(np.abs(got - c["y"]).max()))
+        n += 1
+    assert n == 304
+
+
+def test_masked_normalization_golden_and_large():
+    from areal_b200.data import masked_normalization
+    z = H.load("normalization.npz")
+    for k, c in H.cases(z, prefix="m", count_key="n_masked_norm"):
+        x = torch.from_numpy(c["x"]).to(D)
+        m = torch.from_numpy(c["mask"]).to(D) if bool(c["has_mask"]) else None
+        y = masked_normalization(x, m, unbiased=bool(c["unbiased"]))
+        assert np.allclose(y.cpu().numpy(), c["y"], rtol=1e-5, atol=1e-5), k
+    # a realistic size: [512, 4096] advantages, several slabs per group
+    rng = np.random.RandomState(0)
+    x = (rng.randn(512, 4096) * 2 + 0.3).astype(np.float32)
+    m = (rng.rand(512, 4096) > 0.4).astype(np.float32)
+    want = O.masked_normalization(x, m)
+    got = masked_normalization(torch.from_numpy(x).to(D), torch.from_numpy(m).to(D)).cpu().numpy()
+    assert np.allclose(got, want, rtol=1e-5, atol=1e-5)
+    from areal_b200.data import NormConfig, Normalization
+    for cfg in (NormConfig("batch", False, "batch", True, 1e-5, 1), NormConfig("group", True, "group", False, 1e-5, 8),
+                NormConfig("group", False, "batch", True, 1e-5, 16)):
+        want = O.normalization(x, m, cfg.mean_level, cfg.std_level, cfg.mean_leave1out, cfg.std_unbiased, cfg.eps,
+                               cfg.group_size)
+        got = Normalization(cfg)(torch.from_numpy(x).to(D), torch.from_numpy(m).to(D)).cpu().numpy()
+        assert np.allclose(got, want, rtol=2e-5, atol=2e-5), cfg
+
+
+def test_normalization_errors():
+    from areal_b200.data import NormConfig, Normalization
+    with pytest.raises(ValueError):
+        Normalization(NormConfig(mean_level="token"))
+    with pytest.raises(ValueError):
+        Normalization(NormConfig(std_level="seq"))
+    with pytest.raises(ValueError):
+        Normalization(NormConfig(mean_level="group", group_size=None))

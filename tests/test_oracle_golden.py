@@ -211,3 +211,24 @@ def test_legacy_packed_vs_reference():
         else:
             assert np.allclose(lp, c["logp"], rtol=1e-5, atol=1e-5), k
             assert np.allclose(ent, c["entropy"], rtol=1e-5, atol=1e-5), k
+
+
+_LEVEL = {0: "batch", 1: "group", 2: None}
+
+
+def test_normalization_vs_reference():
+    """`Normalization` over the grid of the reference's own tests, and `masked_normalization`."""
+    z = H.load("normalization.npz")
+    n = 0
+    for k, c in H.cases(z):
+        ml, sl, loo, unb, gs = (int(v) for v in c["cfg"])
+        mask = c["mask"] if bool(c["has_mask"]) else None
+        y = O.normalization(c["x"], mask, _LEVEL[ml], _LEVEL[sl], bool(loo), bool(unb), 1e-5, gs)
+        assert y.dtype == np.float32
+        assert np.allclose(y, c["y"], rtol=2e-6, atol=2e-6), (k, c["cfg"], np.abs(y - c["y"]).max())
+        n += 1
+    assert n == 304
+    for k, c in H.cases(z, prefix="m", count_key="n_masked_norm"):
+        mask = c["mask"] if bool(c["has_mask"]) else None
+        y = O.masked_normalization(c["x"], mask, bool(c["unbiased"]))
+        assert np.allclose(y, c["y"], rtol=2e-6, atol=2e-6), k
