@@ -138,3 +138,70 @@ def masked_normalization(x: torch.Tensor, mask: Optional[torch.Tensor] = None, d
         call("areal_b200_masked_normalization_apply", ptr(xf), ptr(mf), N, ptr(stats), int(unbiased), float(eps),
              ptr(out), stream_ptr(dev))
     return out.view(shape)
+
+
+# --------------------------------------------------------------------------------------------------
+# packing glue: padded [B, S, ...] <-> packed [total, ...] through the interval kernels
+# --------------------------------------------------------------------------------------------------
+def _row_intervals(lens: torch.Tensor, S: int, inner: int) -> torch.Tensor:
+    starts = torch.arange(lens.numel(), device=lens.device, dtype=torch.int64) * (S * inner)
+    return torch.stack([starts, starts + lens.to(torch.int64) * inner], dim=1).contiguous()
+
+
+def pack_tensor_dict(data: dict) -> dict:
+    """Drop-in for `pack_tensor_dict` (areal/utils/data.py:266-315): every tensor of shape [B, S, ...]
+    becomes [total_length, ...] (the first `len_i` positions of row i, in order), "attention_mask" is
+    replaced by "cu_seqlens" (+ "max_seqlen"), other entries pass through.  One gather launch per
+    tensor and ONE host sync in total (the reference loops over sequences in Python with two `.item()`
+    calls per sequence and per key)."""
+    from . import flatten_param as fp
+    assert "attention_mask" in data, "Input data must contain 'attention_mask' key."
+    attention_mask = data["attention_mask"]
+    assert attention_mask.ndim == 2, "Attention mask must be a 2D tensor."
+    _lib.require_cuda(attention_mask)
+    bs, seq_len = attention_mask.shape
+    lens = attention_mask.sum(dim=1, dtype=torch.int32)
+    cu_seqlens = torch.nn.functional.pad(torch.cumsum(lens, dim=0, dtype=torch.int32), (1, 0), value=0)
+    max_seqlen, total_length = (int(v) for v in torch.stack([lens.max(), cu_seqlens[-1]]).tolist()) if bs else (0, 0)
+    packed = {}
+    iv_cache = {}
+    for key, value in data.items():
+        if key == "attention_mask":
+            packed["cu_seqlens"] = cu_seqlens
+            packed["max_seqlen"] = max_seqlen
+            continue
+        if torch.is_tensor(value) and value.ndim >= 2 and value.shape[0] == bs and value.shape[1] == seq_len:
+            inner = 1
+            for d in value.shape[2:]:
+                inner *= int(d)
+            if inner not in iv_cache:
+                iv_cache[inner] = _row_intervals(lens, seq_len, inner)
+            flat = value.contiguous().view(-1)
+            as_u8 = flat.dtype == torch.bool
+            out = fp.slice_intervals_any(flat.view(torch.uint8) if as_u8 else flat, iv_cache[inner], total_length * inner)
+            if as_u8:
+                out = out.view(torch.bool)
+            packed[key] = out.view(total_length, *value.shape[2:])
+        else:
+            packed[key] = value
+    return packed
+
+
+def unpack_to_padded(packed: torch.Tensor, cu_seqlens: torch.Tensor, seq_len: int, fill=0) -> torch.Tensor:
+    """Inverse of the packing above for one tensor: [total, ...] -> [B, seq_len, ...], `fill` elsewhere
+    (what `pad_and_stack_tensors_along_first_dim(unpack_sequence(...))` produces, data.py:318-330)."""
+    from . import flatten_param as fp
+    _lib.require_cuda(packed, cu_seqlens)
+    lens = (cu_seqlens[1:] - cu_seqlens[:-1])
+    bs = lens.numel()
+    inner = 1
+    for d in packed.shape[1:]:
+        inner *= int(d)
+    out = torch.full((bs, seq_len, *packed.shape[1:]), fill, dtype=packed.dtype, device=packed.device)
+    iv = _row_intervals(lens, seq_len, inner)
+    src = packed.contiguous().view(-1)
+    dst = out.view(-1)
+    if packed.dtype == torch.bool:
+        src, dst = src.view(torch.uint8), dst.view(torch.uint8)
+    fp.set_intervals_any(src, dst, iv)
+    return out

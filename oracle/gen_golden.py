@@ -342,6 +342,31 @@ def gen_normalization(af):
     print("normalization cases:", k, "masked_normalization:", j)
 
 
+def gen_pack():
+    """`pack_tensor_dict` (areal/utils/data.py:266-315) on a padded batch with mixed dtypes / trailing dims."""
+    pack = R.load_areal_pack_tensor_dict()
+    g = torch.Generator().manual_seed(11)
+    B, S = 7, 29
+    lens = torch.tensor([29, 1, 13, 0, 20, 7, 29])
+    am = (torch.arange(S)[None, :] < lens[:, None]).long()
+    data = dict(attention_mask=am,
+                input_ids=torch.randint(0, 50000, (B, S), generator=g),
+                loss_mask=(torch.rand(B, S, generator=g) > 0.5),
+                logprobs=torch.randn(B, S, generator=g),
+                hidden=torch.randn(B, S, 3, generator=g).bfloat16(),
+                rewards=torch.randn(B, generator=g),          # [B] only: left unchanged
+                tag="keep")
+    out = pack({k: (v.clone() if torch.is_tensor(v) else v) for k, v in data.items()})
+    z = {"attention_mask": am.numpy(), "cu_seqlens": out["cu_seqlens"].numpy(), "max_seqlen": np.array(out["max_seqlen"])}
+    for k in ("input_ids", "loss_mask", "logprobs", "rewards"):
+        z["in_" + k] = data[k].numpy()
+        z["out_" + k] = out[k].numpy()
+    z["in_hidden"] = bf16_bits(data["hidden"].reshape(-1)).reshape(B, S, 3)
+    z["out_hidden"] = bf16_bits(out["hidden"].reshape(-1)).reshape(-1, 3)
+    np.savez_compressed(os.path.join(OUT, "pack.npz"), **z)
+    print("pack golden: total", int(out["cu_seqlens"][-1]))
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     assert R.available(), "needs /root/reference"
@@ -357,6 +382,7 @@ def main():
     gen_intervals(fp)
     gen_legacy_packed()
     gen_normalization(af)
+    gen_pack()
 
 
 if __name__ == "__main__":

@@ -213,3 +213,20 @@ def load_areal_normalization():
     ns = dict(torch=torch, np=np, dist=dist, Optional=Optional, NormConfig=NormConfig)
     exec(compile(code, "data.py[Normalization]", "exec"), ns)
     return ns["Normalization"], NormConfig
+
+
+def load_areal_pack_tensor_dict():
+    """`pack_tensor_dict` (areal/utils/data.py:266-315), extracted by AST and executed where it lies."""
+    import ast
+    from typing import Any, Dict
+
+    import torch
+    import torch.nn.functional as F
+    path = os.path.join(REF_ROOT, "areal/utils/data.py")
+    with open(path) as f:
+        src = f.read()
+    tree = ast.parse(src)
+    node = next(n for n in tree.body if isinstance(n, ast.FunctionDef) and n.name == "pack_tensor_dict")
+    ns = dict(torch=torch, F=F, Dict=Dict, Any=Any)
+    exec(compile(ast.get_source_segment(src, node), "data.py[pack_tensor_dict]", "exec"), ns)
+    return ns["pack_tensor_dict"]

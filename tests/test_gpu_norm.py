@@ -62,3 +62,29 @@ def test_normalization_errors():
         Normalization(NormConfig(std_level="seq"))
     with pytest.raises(ValueError):
         Normalization(NormConfig(mean_level="group", group_size=None))
+
+
+def test_pack_tensor_dict_golden_and_round_trip():
+    """pack_tensor_dict through the interval gather kernel == the reference's Python loop
+    (golden from the unmodified function), bit for bit, for int64 / bool / fp32 / bf16 [B,S,3]."""
+    from areal_b200.data import pack_tensor_dict, unpack_to_padded
+    z = H.load("pack.npz")
+    B, S = z["attention_mask"].shape
+    data = dict(attention_mask=torch.from_numpy(z["attention_mask"]).to(D),
+                input_ids=torch.from_numpy(z["in_input_ids"]).to(D),
+                loss_mask=torch.from_numpy(z["in_loss_mask"]).to(D),
+                logprobs=torch.from_numpy(z["in_logprobs"]).to(D),
+                hidden=H.bf16_from_bits(z["in_hidden"].reshape(-1)).reshape(B, S, 3).to(D),
+                rewards=torch.from_numpy(z["in_rewards"]).to(D), tag="keep")
+    out = pack_tensor_dict(data)
+    assert "attention_mask" not in out and out["tag"] == "keep" and out["max_seqlen"] == int(z["max_seqlen"])
+    assert np.array_equal(out["cu_seqlens"].cpu().numpy(), z["cu_seqlens"]) and out["cu_seqlens"].dtype == torch.int32
+    for k in ("input_ids", "loss_mask", "logprobs", "rewards"):
+        assert out[k].dtype == data[k].dtype
+        assert np.array_equal(out[k].cpu().numpy(), z["out_" + k]), k
+    assert np.array_equal(H.torch_bits(out["hidden"].reshape(-1)).reshape(-1, 3), z["out_hidden"])
+    back = unpack_to_padded(out["logprobs"], out["cu_seqlens"], S)
+    am = data["attention_mask"].bool()
+    assert torch.equal(back[am], data["logprobs"][am]) and bool((back[~am] == 0).all())
+    hb = unpack_to_padded(out["hidden"], out["cu_seqlens"], S)
+    assert torch.equal(hb[am], data["hidden"][am])
