@@ -120,6 +120,41 @@ def test_gae1d_long_chain_and_workspace_reuse():
         assert np.array_equal(adv, outs[0][0]) and np.array_equal(ret, outs[0][1])
 
 
+@pytest.mark.parametrize("odd", [0, 3])
+def test_gae1d_large_batch(odd):
+    """~3.7M tokens (1800 tiles, more than one wave of resident CTAs): a 1M-token sequence, runs of
+    length-1 sequences (2048 sequence ends in one tile), empty sequences, and T not a multiple of 4
+    (scalar load/store path).  The static-scratch entry must give the same bits."""
+    rng = np.random.RandomState(31 + odd)
+    lens = np.concatenate([rng.randint(1, 3000, 600), [1 << 20], np.ones(5000, np.int64), [0, 0, 7],
+                           rng.randint(1, 40, 20000), rng.randint(1, 9000, 300)])
+    lens = np.concatenate([lens, [4 + (odd - int(lens.sum())) % 4]])          # T % 4 == odd
+    cu = np.concatenate([[0], np.cumsum(lens)]).astype(np.int32)
+    B, T = len(lens), int(cu[-1])
+    assert 2_600_000 < T <= 4194304 and T % 4 == odd
+    r = rng.randn(T).astype(np.float32)
+    v = rng.randn(T + B).astype(np.float32)
+    boot = rng.rand(B) > 0.5
+    a_ref, r_ref = C.gae1d_nolp_misalign(r, v, cu, boot, 0.9995, 0.98)
+    a64, _ = O.gae1d_nolp_misalign_f64(r, v, cu, boot, 0.9995, 0.98)
+    outs = [run1d(r, v, cu, boot, 0.9995, 0.98) for _ in range(2)]
+    for adv, ret in outs:
+        assert per_seq_rel(adv, a_ref, cu) <= H.TOL_GAE and per_seq_rel(ret, r_ref, cu) <= H.TOL_GAE
+        assert per_seq_rel(adv, a64, cu) <= 2 ** -23
+        assert np.array_equal(adv, outs[0][0]) and np.array_equal(ret, outs[0][1])
+    if T <= 4194304:
+        # the static-scratch entry runs the one-tile-per-CTA kernel on the same batch: same bits
+        from areal_b200 import _lib
+        from areal_b200._lib import call, ptr, stream_ptr
+        d = dev()
+        tr, tv = torch.from_numpy(r).to(d), torch.from_numpy(v).to(d)
+        tcu, tb = torch.from_numpy(cu).to(d), torch.from_numpy(boot.astype(np.uint8)).to(d)
+        adv2, ret2 = torch.empty(T, device=d), torch.empty(T, device=d)
+        call("areal_b200_gae1d_nolp_misalign_static", ptr(tr), ptr(tv), ptr(tcu), ptr(tb), T, B, 0.9995, 0.98,
+             ptr(adv2), ptr(ret2), stream_ptr(d))
+        assert np.array_equal(adv2.cpu().numpy(), outs[0][0]) and np.array_equal(ret2.cpu().numpy(), outs[0][1])
+
+
 def test_gae1d_inputs_untouched_and_checks():
     from areal_b200 import ppo_functional as P
     d = dev()
