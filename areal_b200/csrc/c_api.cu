@@ -10,6 +10,7 @@
 #include "interval_copy.h"
 #include "logits_fused.h"
 #include "masked_norm.h"
+#include "masked_stats.h"
 #include "ppo_loss.h"
 
 namespace ab {
@@ -167,6 +168,61 @@ AREAL_B200_API int areal_b200_gae_padded_masked(const float* rewards, const floa
   p.adv = adv_out;
   p.ret = ret_out;
   return launch_gae_padded(p, static_cast<cudaStream_t>(stream));
+}
+
+AREAL_B200_API int areal_b200_advantages_padded(
+    float* score, int overlong, int64_t overlong_tokens, int64_t max_response_length,
+    double overlong_penalty_factor, const void* loss_mask, int loss_mask_code, const float* logp, int roll_logp,
+    float* ref_logp, const void* attn_mask, int attn_code, const float* values, int64_t B, int64_t S,
+    int apply_scaling, double reward_bias, double reward_scaling, double reward_clip, double kl_ctl,
+    int kl_kind, int kl_clamp, int mask_no_eos_with_zero, double gamma, double lam, float* adv_out,
+    float* ret_out, float* kl_rewards_out, float* tot_rewards_out, float* loss_mask_out,
+    float* old_logp_out, void* stream) {
+  AB_REQUIRE(B >= 0 && S >= 0, "negative size");
+  if (B == 0 || S == 0) return kOk;
+  AB_REQUIRE(score && loss_mask && logp && attn_mask && adv_out && ret_out && kl_rewards_out &&
+                 tot_rewards_out && loss_mask_out && old_logp_out, "null pointer");
+  AB_REQUIRE(loss_mask_code >= 0 && loss_mask_code <= 3 && attn_code >= 0 && attn_code <= 3,
+             "mask element code must be 0 (f32), 1 (u8/bool), 2 (i32) or 3 (i64)");
+  AB_REQUIRE(!overlong || overlong_tokens != 0, "overlong_tokens must be non-zero");
+  AB_REQUIRE(kl_kind >= 1 && kl_kind <= 3, "Invalid KL estimator: k%d. Valid choices: k1, k2, k3", kl_kind);
+  GaePaddedParams p;
+  p.rewards = nullptr;
+  p.values = values;
+  p.mask = nullptr;
+  p.no_eos = nullptr;
+  p.B = B;
+  p.S = S;
+  p.g = static_cast<float>(gamma);
+  p.gl = static_cast<float>(gamma * lam);
+  p.adv = adv_out;
+  p.ret = ret_out;
+  AdvFusedParams f;
+  f.score = score;
+  f.overlong = overlong;
+  f.overlong_tokens = overlong_tokens;
+  f.expected_len = max_response_length - overlong_tokens;
+  f.overlong_factor = static_cast<float>(overlong_penalty_factor);
+  f.loss_mask = loss_mask;
+  f.loss_mask_code = loss_mask_code;
+  f.logp = logp;
+  f.roll_logp = roll_logp;
+  f.ref_logp = ref_logp;
+  f.attn_mask = attn_mask;
+  f.attn_code = attn_code;
+  f.apply_scaling = apply_scaling;
+  f.bias = static_cast<float>(reward_bias);
+  f.scaling = static_cast<float>(reward_scaling);
+  f.clip = static_cast<float>(reward_clip);
+  f.neg_kl_ctl = static_cast<float>(-kl_ctl);
+  f.kl_kind = kl_kind;
+  f.kl_clamp = kl_clamp;
+  f.mask_no_eos_with_zero = mask_no_eos_with_zero;
+  f.kl_rewards = kl_rewards_out;
+  f.tot_rewards = tot_rewards_out;
+  f.loss_mask_out = loss_mask_out;
+  f.old_logp_out = old_logp_out;
+  return launch_advantages_padded(p, f, static_cast<cudaStream_t>(stream));
 }
 
 AREAL_B200_API int areal_b200_gae2d_olp(const float* rewards, const float* values, const uint8_t* done,
@@ -646,6 +702,37 @@ AREAL_B200_API int64_t areal_b200_merge_intervals(const uint64_t* iv, int64_t n,
     }
   }
   return k;
+}
+
+AREAL_B200_API int64_t areal_b200_masked_stats_workspace_bytes(int64_t n_keys, int64_t n) {
+  if (n_keys < 0 || n < 0) return -1;
+  return masked_stats_workspace_bytes(n_keys, n);
+}
+
+AREAL_B200_API int areal_b200_masked_stats(const float* const* values, const uint8_t* const* masks,
+                                           double* const* outs, uint32_t value_is_u8_bits,
+                                           int64_t n_keys, int64_t n, int accumulate, void* workspace,
+                                           int64_t workspace_bytes, void* stream) {
+  AB_REQUIRE(n_keys >= 0 && n >= 0, "negative size");
+  if (n_keys == 0) return kOk;
+  AB_REQUIRE(n_keys <= kMaxStatKeys, "masked_stats: at most %d keys per call, got %lld", kMaxStatKeys,
+             static_cast<long long>(n_keys));
+  AB_REQUIRE(n > 0, "masked_stats: arrays must be non-empty");   // stats_tracker.py:113-114
+  AB_REQUIRE(values && masks && outs && workspace, "null pointer");
+  if (workspace_bytes < masked_stats_workspace_bytes(n_keys, n)) {
+    set_error("masked_stats: workspace of %lld bytes is too small (need %lld)", static_cast<long long>(workspace_bytes),
+              static_cast<long long>(masked_stats_workspace_bytes(n_keys, n)));
+    return kWorkspaceTooSmall;
+  }
+  StatsTable tab;
+  tab.val_u8_bits = value_is_u8_bits;
+  for (int k = 0; k < kMaxStatKeys; ++k) {
+    tab.val[k] = k < n_keys ? values[k] : nullptr;
+    tab.mask[k] = k < n_keys ? masks[k] : nullptr;
+    tab.out[k] = k < n_keys ? outs[k] : nullptr;
+    AB_REQUIRE(k >= n_keys || outs[k] != nullptr, "masked_stats: null output slot for key %d", k);
+  }
+  return launch_masked_stats(tab, static_cast<int>(n_keys), n, accumulate, workspace, static_cast<cudaStream_t>(stream));
 }
 
 }  // extern "C"

@@ -340,25 +340,129 @@ gae1d_kernel(const Gae1dParams p) {
 }
 
 // ---- padded [B,S] masked (areal-lite) ----------------------------------------------------------------
+__device__ __forceinline__ float mask_as_float(const void* base, int code, int64_t i) {
+  switch (code) {
+    case 0: return __ldg(reinterpret_cast<const float*>(base) + i);
+    case 1: return float(__ldg(reinterpret_cast<const uint8_t*>(base) + i));
+    case 2: return float(__ldg(reinterpret_cast<const int32_t*>(base) + i));
+    default: return float(__ldg(reinterpret_cast<const int64_t*>(base) + i));
+  }
+}
+__device__ __forceinline__ int64_t mask_as_int(const void* base, int code, int64_t i) {
+  switch (code) {
+    case 0: return int64_t(__ldg(reinterpret_cast<const float*>(base) + i));
+    case 1: return int64_t(__ldg(reinterpret_cast<const uint8_t*>(base) + i));
+    case 2: return int64_t(__ldg(reinterpret_cast<const int32_t*>(base) + i));
+    default: return __ldg(reinterpret_cast<const int64_t*>(base) + i);
+  }
+}
+
+// Reward of token t of one row as PPOActor.compute_advantages builds it (actor.py:109-138), with
+// the side outputs the reference stores back into the batch.  Returns (tot_reward, mask).
+struct RowCtx {
+  int64_t row_off, S, zero_col, add_col;
+  float add_score;
+};
+__device__ __forceinline__ float2 fused_token(const AdvFusedParams& f, const RowCtx& c, int64_t t) {
+  const int64_t tn = (t + 1 == c.S) ? 0 : t + 1;                               // roll(-1), :110
+  const float lm = mask_as_float(f.loss_mask, f.loss_mask_code, c.row_off + tn);
+  const float old = __fmul_rn(__ldg(f.logp + c.row_off + (f.roll_logp ? tn : t)), lm);   // :116, :122
+  float ref = 0.f;
+  if (f.ref_logp) {
+    ref = __fmul_rn(f.ref_logp[c.row_off + t], lm);                            // :121 (in place)
+    f.ref_logp[c.row_off + t] = ref;
+  }
+  float kl = __fsub_rn(old, ref);                                              // data.py:1344
+  if (f.kl_kind == 2) {
+    kl = __fmul_rn(__fmul_rn(kl, kl), 0.5f);                                   // :1353
+  } else if (f.kl_kind == 3) {
+    const float lr = -kl;                                                      // :1359
+    kl = __fsub_rn(__fsub_rn(expf(lr), 1.f), lr);                              // :1360
+  }
+  if (f.kl_clamp) kl = fminf(fmaxf(kl, -10.f), 10.f);                          // :1363 (NaN stays NaN)
+  const float klr = __fmul_rn(f.neg_kl_ctl, kl);                               // actor.py:128
+  float tot = klr;
+  if (t == c.zero_col) tot = 0.f;                                              // :131
+  if (t == c.add_col) tot = __fadd_rn(tot, c.add_score);                       // :133-138
+  f.kl_rewards[c.row_off + t] = klr;
+  f.tot_rewards[c.row_off + t] = tot;
+  f.loss_mask_out[c.row_off + t] = lm;
+  f.old_logp_out[c.row_off + t] = old;
+  return make_float2(tot, lm);
+}
+
+template <bool kFused>
 __global__ void __launch_bounds__(kThreads)
-gae_padded_kernel(const GaePaddedParams p) {
+gae_padded_kernel(const GaePaddedParams p, const AdvFusedParams f) {
   __shared__ Affine wsm[kWarps];
   __shared__ float nv_val[kWarps];
   __shared__ int nv_has[kWarps];
+  __shared__ long long len_sm[kWarps];
+  __shared__ long long resp_sm[kWarps];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const double gl = double(p.gl);
   for (int64_t row = blockIdx.x; row < p.B; row += gridDim.x) {
-    const float* r = p.rewards + row * p.S;
-    const float* v = p.values + row * p.S;
-    const float* m = p.mask + row * p.S;
+    const float* r = kFused ? nullptr : p.rewards + row * p.S;
+    const float* v = p.values ? p.values + row * p.S : nullptr;  // null (fused only): zeros, :141
+    const float* m = kFused ? nullptr : p.mask + row * p.S;
     float* adv = p.adv + row * p.S;
     float* ret = p.ret + row * p.S;
     const int64_t L = p.S - 1;                                  // positions taking part in the loop
-    float nv_carry = p.no_eos[row] ? v[p.S - 1] : 0.f;          // actor.py:135 (bool * value)
+    RowCtx ctx;
+    bool no_eos;
+    if (kFused) {
+      // seqlens = attention_mask.sum(-1) (:126)
+      long long part = 0, resp = 0;
+      for (int64_t i = tid; i < p.S; i += kThreads) {
+        part += mask_as_int(f.attn_mask, f.attn_code, row * p.S + i);
+        if (f.overlong) resp += mask_as_int(f.loss_mask, f.loss_mask_code, row * p.S + i);
+      }
+#pragma unroll
+      for (int d = 16; d; d >>= 1) {
+        part += __shfl_xor_sync(0xffffffffu, part, d);
+        resp += __shfl_xor_sync(0xffffffffu, resp, d);
+      }
+      if (lane == 0) {
+        len_sm[warp] = part;
+        resp_sm[warp] = resp;
+      }
+      __syncthreads();
+      long long seqlen = 0, resp_len = 0;
+      for (int w = 0; w < kWarps; ++w) {
+        seqlen += len_sm[w];
+        resp_len += resp_sm[w];
+      }
+      no_eos = seqlen == p.S;                                    // :127
+      float sc = f.score[row];
+      if (f.overlong) {
+        // areal/utils/functional.py:389-394: min(-exceed / overlong_tokens * factor, 0) added to the score
+        const float a = __fmul_rn(__fdiv_rn(__ll2float_rn(-(resp_len - f.expected_len)),
+                                            __ll2float_rn(f.overlong_tokens)), f.overlong_factor);
+        if (!(0.f < a)) sc = __fadd_rn(sc, a);
+        __syncthreads();                                         // every thread has read score[row]
+        if (tid == 0) f.score[row] = sc;
+      }
+      if (f.apply_scaling) {
+        sc = __fmul_rn(__fadd_rn(sc, f.bias), f.scaling);        // :98
+        sc = fminf(fmaxf(sc, -f.clip), f.clip);                  // :99-101
+      }
+      ctx.row_off = row * p.S;
+      ctx.S = p.S;
+      ctx.zero_col = seqlen - 1 < 0 ? seqlen - 1 + p.S : seqlen - 1;   // negative index wraps (:131)
+      ctx.add_col = seqlen - 2 < 0 ? 0 : seqlen - 2;             // :132
+      ctx.add_score = (f.mask_no_eos_with_zero && no_eos) ? 0.f : sc;
+      if (ctx.zero_col >= p.S) ctx.zero_col = -1;                // out-of-range sums: the reference raises
+      if (ctx.add_col >= p.S) ctx.add_col = -1;
+    } else {
+      no_eos = p.no_eos[row] != 0;
+    }
+    const float v_last = v ? v[p.S - 1] : 0.f;
+    float nv_carry = no_eos ? v_last : 0.f;                     // actor.py:135 (bool * value)
     double a_carry = 0.0;                                       // adv[:, S-1] = 0
     if (tid == 0) {
+      if (kFused) fused_token(f, ctx, p.S - 1);
       adv[p.S - 1] = 0.f;
-      ret[p.S - 1] = v[p.S - 1];                                // returns = advantages + values, :152
+      ret[p.S - 1] = v_last;                                    // returns = advantages + values, :152
     }
     const int64_t ntiles = (L + kTile - 1) / kTile;
     for (int64_t tile = ntiles - 1; tile >= 0; --tile) {
@@ -370,9 +474,16 @@ gae_padded_kernel(const GaePaddedParams p) {
 #pragma unroll
       for (int k = 0; k < kItems; ++k) {
         if (k < nvalid) {
-          rr[k] = __ldg(r + t0 + k);
-          vv[k] = __ldg(v + t0 + k);
-          if (__ldg(m + t0 + k) != 0.f) valid_bits |= 1u << k;
+          if (kFused) {
+            const float2 tm = fused_token(f, ctx, t0 + k);
+            rr[k] = tm.x;
+            vv[k] = v ? __ldg(v + t0 + k) : 0.f;
+            if (tm.y != 0.f) valid_bits |= 1u << k;
+          } else {
+            rr[k] = __ldg(r + t0 + k);
+            vv[k] = __ldg(v + t0 + k);
+            if (__ldg(m + t0 + k) != 0.f) valid_bits |= 1u << k;
+          }
         }
       }
       // nearest valid value to the right of this thread
@@ -585,8 +696,16 @@ int launch_gae1d_static(Gae1dParams p, cudaStream_t stream) {
 int launch_gae_padded(const GaePaddedParams& p, cudaStream_t stream) {
   if (p.B == 0 || p.S == 0) return kOk;
   const int64_t cap = int64_t(num_sms()) * 8;
-  gae_padded_kernel<<<static_cast<unsigned int>(p.B < cap ? p.B : cap), kThreads, 0, stream>>>(p);
+  gae_padded_kernel<false><<<static_cast<unsigned int>(p.B < cap ? p.B : cap), kThreads, 0, stream>>>(
+      p, AdvFusedParams{});
   return check_launch("gae_padded");
+}
+
+int launch_advantages_padded(const GaePaddedParams& p, const AdvFusedParams& f, cudaStream_t stream) {
+  if (p.B == 0 || p.S == 0) return kOk;
+  const int64_t cap = int64_t(num_sms()) * 8;
+  gae_padded_kernel<true><<<static_cast<unsigned int>(p.B < cap ? p.B : cap), kThreads, 0, stream>>>(p, f);
+  return check_launch("advantages_padded");
 }
 
 int launch_gae2d_olp(const Gae2dParams& p, cudaStream_t stream) {

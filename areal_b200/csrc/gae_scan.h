@@ -29,6 +29,35 @@ struct GaePaddedParams {
   float* ret;
 };
 
+// Reward construction of PPOActor.compute_advantages fused in front of the padded GAE
+// (areal/engine/ppo/actor.py:92-129).  Mask element codes: 0 f32, 1 u8/bool, 2 i32, 3 i64.
+struct AdvFusedParams {
+  float* score;                // [B] task reward per sequence (data["rewards"]); the overlong penalty is
+                               // added IN PLACE like areal/utils/functional.py:394-397
+  int overlong;                // 1: reward_overlong_penalty first (actor.py:80-90)
+  int64_t overlong_tokens, expected_len;   // expected_len = max_response_length - overlong_tokens
+  float overlong_factor;
+  const void* loss_mask;       // [B, S] NOT rolled; the kernel reads column (t+1) mod S  (:109-110)
+  int loss_mask_code;
+  const float* logp;           // [B, S] behaviour / proximal log-probs
+  int roll_logp;               // 1: old_logp = roll(logp, -1) (:116); 0: used as is (:114)
+  float* ref_logp;             // [B, S] or null (zeros, :120); multiplied by the mask IN PLACE (:121)
+  const void* attn_mask;       // [B, S]; seqlens = row sum (:126)
+  int attn_code;
+  int apply_scaling;           // 1: score = clip((score + bias) * scaling, +-clip) (:98-102)
+  float bias, scaling, clip;
+  float neg_kl_ctl;            // float(-kl_ctl) (:128)
+  int kl_kind;                 // 1, 2, 3 (areal/utils/data.py:1343-1360)
+  int kl_clamp;                // clamp to [-10, 10] (:1362)
+  int mask_no_eos_with_zero;   // (:133-138)
+  float* kl_rewards;           // [B, S] out
+  float* tot_rewards;          // [B, S] out
+  float* loss_mask_out;        // [B, S] out, rolled, f32
+  float* old_logp_out;         // [B, S] out, rolled (if roll_logp) and masked
+};
+
+int launch_advantages_padded(const GaePaddedParams& p, const AdvFusedParams& f, cudaStream_t stream);
+
 struct Gae2dParams {
   const float* rewards;            // [B, H]
   const float* values;             // [B, H + 1]

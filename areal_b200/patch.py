@@ -70,6 +70,24 @@ def patch_areal(extra_modules=()):
             setattr(mod, "Normalization", _D.Normalization)
         if hasattr(mod, "masked_normalization"):
             setattr(mod, "masked_normalization", _D.masked_normalization)
+    # reward construction + GAE of the actor (areal/engine/ppo/actor.py:72-164) as one launch
+    mod = sys.modules.get("areal.engine.ppo.actor")
+    if mod is not None and hasattr(mod, "PPOActor"):
+        from . import actor as _A
+        mod.PPOActor.compute_advantages = _A.compute_advantages
+        patched.append("areal.engine.ppo.actor.PPOActor.compute_advantages")
+    # stats epilogue: the tracker that reduces at record time, and the grpo_loss_fn that feeds it
+    st = sys.modules.get("areal.utils.stats_tracker")
+    if st is not None:
+        from . import stats_tracker as _ST
+        for name in ("ReduceType", "DistributedStatsTracker", "DEFAULT_TRACKER", "stat", "denominator", "export",
+                     "scope", "scalar", "record_timing", "TRACKERS", "LOCK", "get", "export_all"):
+            setattr(st, name, getattr(_ST, name))
+        patched.append("areal.utils.stats_tracker")
+        if mod is not None and hasattr(mod, "grpo_loss_fn"):
+            from . import actor as _A
+            mod.grpo_loss_fn = _A.grpo_loss_fn
+            patched.append("areal.engine.ppo.actor.grpo_loss_fn")
     for name in tuple(_AREAL_IMPORT_SITES) + tuple(extra_modules):
         mod = sys.modules.get(name)
         if mod is None:

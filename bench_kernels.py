@@ -4,7 +4,7 @@ bench.py).  Times every kernel family alone with CUDA events after warm-up, inpu
 flushed between iterations, and -- where present -- the reference's own CUDA kernels rebuilt for
 sm_100a (oracle/_ref/*.so, timing baseline only) and the reference-style torch path.
 
-    python bench_kernels.py [--what gae,padded,intervals,logits,loss,ref] [--out file.json]
+    python bench_kernels.py [--what gae,padded,advantages,intervals,logits,loss,ref] [--out file.json]
 """
 import argparse
 import glob
@@ -260,9 +260,54 @@ def bench_loss(out):
         out.append(row("ppo_critic_loss", ms, 22 * T, T=T, tokens_per_s=T / (ms * 1e-3)))
 
 
+def bench_advantages(out):
+    """compute_advantages (reward construction + GAE, one launch) vs the reference's op sequence for the
+    reward construction alone (actor.py:96-138 restated with torch ops on the GPU; its GAE loop is timed
+    in bench_padded)."""
+    import types
+    from areal_b200.actor import compute_advantages
+    for B, S in ((512, 4096), (2048, 8192)):
+        lens = torch.randint(2, S + 1, (B,), device=DEV)
+        am = torch.arange(S, device=DEV)[None, :] < lens[:, None]
+        lm = am & (torch.rand(B, S, device=DEV) > 0.2)
+        base = dict(input_ids=torch.zeros(B, S, dtype=torch.long, device=DEV), attention_mask=am, loss_mask=lm,
+                    logprobs=-torch.rand(B, S, device=DEV), ref_logp=-torch.rand(B, S, device=DEV),
+                    values=torch.randn(B, S, device=DEV), rewards=torch.randn(B, device=DEV))
+        actor = types.SimpleNamespace(
+            config=types.SimpleNamespace(use_decoupled_loss=True, recompute_logprob=True, overlong_reward_penalty=False),
+            reward_bias=0.0, reward_scaling=1.0, reward_clip=20.0, kl_ctl=0.1,
+            kl_estimator=types.SimpleNamespace(kl_estimator="k1", apply_clamp=True), discount=1.0, gae_lambda=0.95,
+            mask_no_eos_with_zero=False, adv_norm=None, reward_norm=None)
+        # bytes: masks 1+1, logp 4, ref 4 (+4 in-place write), values 4; six f32 outputs
+        nbytes = (2 + 4 + 8 + 4 + 24) * B * S
+        ms = timeit(lambda: compute_advantages(actor, dict(base)), flush=nbytes < (200 << 20))
+        out.append(row("advantages_padded (compute_advantages, one launch)", ms, nbytes, B=B, S=S,
+                       tokens_per_s=B * S / (ms * 1e-3)))
+
+        def ref_rewards():
+            rs = (base["rewards"] + 0.0) * 1.0
+            rs = torch.clip(rs, max=20.0, min=-20.0)
+            m = torch.roll(base["loss_mask"].float(), shifts=-1, dims=-1)
+            old = torch.roll(base["logprobs"], shifts=-1, dims=-1)
+            ref = base["ref_logp"]
+            ref *= m
+            old *= m
+            seqlens = base["attention_mask"].sum(-1).long()
+            no_eos = seqlens == S
+            rw = -0.1 * (old.float() - ref.float()).clamp(min=-10, max=10)
+            klr = rw.clone()
+            bi = torch.arange(B, device=DEV)
+            rw[bi, seqlens - 1] = 0
+            rw[bi, torch.clip(seqlens - 2, min=0)] += rs
+            return rw, klr, no_eos
+        msr = timeit(ref_rewards, iters=10, warmup=3)
+        out.append(row("reference reward construction only (torch ops, actor.py:96-138)", msr, nbytes, B=B, S=S,
+                       tokens_per_s=B * S / (msr * 1e-3)))
+
+
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--what", default="gae,padded,loss,logits,intervals")
+    ap.add_argument("--what", default="gae,padded,advantages,loss,logits,intervals")
     ap.add_argument("--out", default=None)
     args = ap.parse_args()
     what = set(args.what.split(","))
@@ -273,6 +318,8 @@ def main():
         bench_gae(out, ref_gae)
     if "padded" in what:
         bench_padded(out)
+    if "advantages" in what:
+        bench_advantages(out)
     if "loss" in what:
         bench_loss(out)
     if "logits" in what:

@@ -88,6 +88,27 @@ AREAL_B200_API int areal_b200_gae_padded_masked(const float* rewards, const floa
                                  int64_t S, double gamma, double lam, float* adv_out,
                                  float* ret_out, void* stream);
 
+/* Reward construction + padded masked GAE in ONE launch: everything `PPOActor.compute_advantages`
+ * does between reward scaling and `returns` (areal/engine/ppo/actor.py:96-152; KL estimators k1/k2/k3
+ * of areal/utils/data.py:1343-1363).  ~25 torch kernels and the S-step Python loop of the reference.
+ *   score f32[B] (data["rewards"]; with overlong=1 the length penalty of
+ *   areal/utils/functional.py:376-398 is added to it IN PLACE first); loss_mask [B,S] NOT rolled, element code 0 f32 / 1 u8,bool /
+ *   2 i32 / 3 i64; logp f32[B,S] (roll_logp=1: rolled by -1 inside, :116; 0: used as is, :114);
+ *   ref_logp f32[B,S] or NULL (zeros, :120) -- multiplied by the rolled mask IN PLACE like :121;
+ *   attn_mask [B,S] with its own element code (seqlens = row sums, :126); values f32[B,S] or NULL
+ *   (zeros, :141).  apply_scaling: score = clip((score+bias)*scaling, +-clip) (:98-102); pass 0 when
+ *   the caller already scaled (e.g. a reward_norm in between, :103).  kl_kind 1|2|3, kl_clamp 0|1.
+ *   Outputs f32[B,S]: advantages (before adv_norm), returns, kl_rewards, tot_rewards, loss_mask_out
+ *   (rolled, as float), old_logp_out (rolled and masked). */
+AREAL_B200_API int areal_b200_advantages_padded(
+    float* score, int overlong, int64_t overlong_tokens, int64_t max_response_length,
+    double overlong_penalty_factor, const void* loss_mask, int loss_mask_code, const float* logp, int roll_logp,
+    float* ref_logp, const void* attn_mask, int attn_code, const float* values, int64_t B, int64_t S,
+    int apply_scaling, double reward_bias, double reward_scaling, double reward_clip, double kl_ctl,
+    int kl_kind, int kl_clamp, int mask_no_eos_with_zero, double gamma, double lam, float* adv_out,
+    float* ret_out, float* kl_rewards_out, float* tot_rewards_out, float* loss_mask_out,
+    float* old_logp_out, void* stream);
+
 /* Segment-table 2D GAE.  Replaces `gae_2d_olp` AND `gae_2d_nolp` (csrc/cugae/gae.cu:91-134,
  * 163-206, pybind :213-215): the reference's `_nolp` host wrapper launches the `_olp` kernel
  * (:199), so both exports have olp semantics.
@@ -318,6 +339,25 @@ AREAL_B200_API int areal_b200_set_intervals(const void* packed, int64_t packed_n
  * -> (a,c) for neighbours in input order.  in/out are u64[n,2] host arrays (out capacity n);
  * returns the number of merged intervals, or -1 on a null pointer. */
 AREAL_B200_API int64_t areal_b200_merge_intervals(const uint64_t* intervals, int64_t n, uint64_t* out);
+
+/* Masked sum / count / min / max of n_keys (<= 32) float arrays of n elements in ONE launch: the
+ * reductions `DistributedStatsTracker` does per key at export time
+ * (areal/utils/stats_tracker.py:210-289: torch.where(d, v, fill) + sum/min/max per key and per
+ * recorded micro-batch) for the keys `grpo_loss_fn` records (areal/engine/ppo/actor.py:352-391).
+ *   values[k] f32[n] device pointer or NULL (every element is 1: a denominator's own count); bit k
+ *   of value_is_u8_bits says values[k] points at u8/bool elements instead (`mask.float()`, :367-368);
+ *   masks[k] u8/bool[n] device pointer or NULL (every element counts).  `values` / `masks` are HOST
+ *   arrays of n_keys device pointers, and so is `outs`: outs[k] -> f64[4] = (sum, count, min, max) of
+ *   key k (distinct per key); min/max are +inf/-inf when nothing is selected.  accumulate=1 folds the
+ *   result into what outs[k] already holds (running totals over micro-batches; initialise a slot to
+ *   0, 0, +inf, -inf).  Sums are fp64, in a fixed order.
+ *   workspace: areal_b200_masked_stats_workspace_bytes(n_keys, n) bytes, zeroed before first use
+ *   (the kernel leaves it zeroed). */
+AREAL_B200_API int64_t areal_b200_masked_stats_workspace_bytes(int64_t n_keys, int64_t n);
+AREAL_B200_API int areal_b200_masked_stats(const float* const* values, const uint8_t* const* masks,
+                                           double* const* outs, uint32_t value_is_u8_bits,
+                                           int64_t n_keys, int64_t n, int accumulate, void* workspace,
+                                           int64_t workspace_bytes, void* stream);
 
 #ifdef __cplusplus
 }

@@ -583,3 +583,60 @@ def normalization(x, loss_mask, mean_level, std_level, mean_leave1out, std_unbia
     if isinstance(std, np.ndarray) and std.dtype == np.float32 and xc.dtype == np.float32:
         return (xc / (std + np.float32(eps))).astype(np.float32)
     return (xc / (std + eps)).astype(np.float32)
+
+
+# --------------------------------------------------------------------------------------------------
+# PPOActor.compute_advantages: reward construction + padded GAE (areal/engine/ppo/actor.py:92-152)
+# --------------------------------------------------------------------------------------------------
+def approx_kl(log_probs, log_probs_base, kind: str = "k1", apply_clamp: bool = True):
+    """KLEstimator._compute_approx_kl (areal/utils/data.py:1328-1364), float32 step by step."""
+    f = np.float32
+    lr = log_probs.astype(f) - log_probs_base.astype(f)                     # :1344
+    if kind == "k2":
+        lr = (lr * lr) / f(2.0)                                             # :1353
+    elif kind == "k3":
+        lr = -lr                                                            # :1359
+        lr = (np.exp(lr).astype(f) - f(1)) - lr                             # :1360
+    elif kind != "k1":
+        raise ValueError(f"Invalid KL estimator: {kind}. Valid choices: k1, k2, k3")
+    if apply_clamp:
+        lr = np.clip(lr, f(-10), f(10))                                     # :1363
+    return lr.astype(f)
+
+
+def overlong_penalty(score, loss_mask, overlong_tokens: int, factor: float, max_response_length: int):
+    """reward_overlong_penalty (areal/utils/functional.py:376-398); returns the new scores."""
+    f = np.float32
+    resp = loss_mask.astype(np.int64).sum(-1)                               # :384
+    exceed = resp - (max_response_length - overlong_tokens)                 # :389-390
+    a = ((-exceed).astype(f) / f(overlong_tokens)) * f(factor)              # :392
+    return (score.astype(f) + np.where(a > 0, f(0), a).astype(f)).astype(f)  # min(a, 0), :391-394
+
+
+def compute_advantages(score, loss_mask, logprobs, attention_mask, *, ref_logp=None, values=None, roll_logp=True,
+                       reward_bias=0.0, reward_scaling=1.0, reward_clip=20.0, apply_scaling=True, kl_ctl=0.1,
+                       kl_estimator="k1", kl_clamp=True, mask_no_eos_with_zero=False, discount=1.0, gae_lambda=1.0):
+    """actor.py:96-152 between the optional penalties / normalisations.  `loss_mask` is NOT rolled.
+    Returns dict(advantages, returns, kl_rewards, tot_rewards, loss_mask, logprobs, ref_logp)."""
+    f = np.float32
+    B, S = logprobs.shape
+    sc = score.astype(f)
+    if apply_scaling:
+        sc = (sc + f(reward_bias)) * f(reward_scaling)                      # :98
+        sc = np.clip(sc, f(-reward_clip), f(reward_clip))                   # :99-101
+    lm = np.roll(loss_mask.astype(f), -1, axis=-1)                          # :109-110
+    old = (np.roll(logprobs.astype(f), -1, axis=-1) if roll_logp else logprobs.astype(f)) * lm   # :114-116, :122
+    ref = (np.zeros_like(old) if ref_logp is None else ref_logp.astype(f)) * lm                  # :120-121
+    seqlens = attention_mask.astype(np.int64).sum(-1)                       # :126
+    no_eos = seqlens == S                                                   # :127
+    kl_rewards = (f(-kl_ctl) * approx_kl(old, ref, kl_estimator, kl_clamp)).astype(f)             # :128
+    rewards = kl_rewards.copy()
+    rows = np.arange(B)
+    rewards[rows, seqlens - 1] = 0                                          # :131 (negative index wraps)
+    idx = np.clip(seqlens - 2, 0, None)                                     # :132
+    add = np.where(no_eos, f(0), sc) if mask_no_eos_with_zero else sc       # :133-138
+    rewards[rows, idx] = rewards[rows, idx] + add.astype(f)
+    vals = np.zeros_like(rewards) if values is None else values.astype(f)   # :141-144
+    adv, ret = gae_padded_masked(rewards, vals, lm, no_eos, discount, gae_lambda)
+    return dict(advantages=adv, returns=ret, kl_rewards=kl_rewards, tot_rewards=rewards, loss_mask=lm, logprobs=old,
+                ref_logp=ref)

@@ -367,6 +367,113 @@ def gen_pack():
     print("pack golden: total", int(out["cu_seqlens"][-1]))
 
 
+def adv_case_grid():
+    """Configurations of PPOActor.compute_advantages covered by the golden file."""
+    base = dict(reward_bias=0.0, reward_scaling=1.0, reward_clip=20.0, kl_ctl=0.1, kl_estimator="k1",
+                discount=1.0, gae_lambda=1.0, mask_no_eos_with_zero=False, use_decoupled_loss=True,
+                recompute_logprob=True, overlong_reward_penalty=False, overlong_tokens=8, overlong_penalty_factor=1.0,
+                max_new_tokens=24, with_values=False, with_ref=True, adv_norm=False, reward_norm=False)
+    grid = [dict(),
+            dict(kl_estimator="k2", kl_ctl=0.5, discount=0.99, gae_lambda=0.95, with_values=True),
+            dict(kl_estimator="k3", kl_ctl=0.05, reward_bias=-0.5, reward_scaling=3.0, reward_clip=2.5,
+                 mask_no_eos_with_zero=True, with_values=True, discount=0.9, gae_lambda=0.8),
+            dict(with_ref=False, kl_ctl=0.0, adv_norm=True),
+            dict(use_decoupled_loss=False, recompute_logprob=True, with_values=True, discount=0.97, gae_lambda=0.9),
+            dict(use_decoupled_loss=False, recompute_logprob=False, kl_estimator="k2"),
+            dict(overlong_reward_penalty=True, overlong_tokens=6, overlong_penalty_factor=0.75, max_new_tokens=20,
+                 reward_scaling=2.0, with_values=True, discount=0.95, gae_lambda=0.9),
+            dict(reward_norm=True, adv_norm=True, kl_estimator="k3", with_values=True, gae_lambda=0.7)]
+    return [dict(base, **g) for g in grid]
+
+
+def adv_case_inputs(ci, B=12, S=37):
+    g = torch.Generator().manual_seed(400 + ci)
+    lens = torch.randint(2, S + 1, (B,), generator=g)
+    lens[0], lens[1], lens[2] = S, 1, 2                      # no-eos row, shortest rows
+    if ci % 2:
+        lens[3] = S
+    am = torch.arange(S)[None, :] < lens[:, None]
+    prompt = torch.minimum(torch.randint(0, 9, (B,), generator=g), lens)
+    lm = am & (torch.arange(S)[None, :] >= prompt[:, None]) & (torch.rand(B, S, generator=g) > 0.15)
+    return dict(input_ids=torch.randint(0, 1000, (B, S), generator=g), attention_mask=am, loss_mask=lm.long(),
+                logprobs=-torch.rand(B, S, generator=g) * 4, prox_logp=-torch.rand(B, S, generator=g) * 4,
+                ref_logp=-torch.rand(B, S, generator=g) * 4, values=torch.randn(B, S, generator=g),
+                rewards=torch.randn(B, generator=g) * 3)
+
+
+def gen_advantages():
+    """PPOActor.compute_advantages (areal/engine/ppo/actor.py:72-164) run unmodified on CPU over the grid."""
+    import types
+    fn, KLEstimator, Normalization, NormConfig = R.load_areal_compute_advantages()
+    z = {}
+    for ci, c in enumerate(adv_case_grid()):
+        d = adv_case_inputs(ci)
+        if not c["with_values"]:
+            d.pop("values")
+        if not c["with_ref"]:
+            d.pop("ref_logp")
+        for k, v in d.items():
+            z[f"c{ci}_in_{k}"] = v.numpy().copy()
+        cfg = types.SimpleNamespace(**{k: c[k] for k in ("use_decoupled_loss", "recompute_logprob", "overlong_reward_penalty",
+                                                          "overlong_tokens", "overlong_penalty_factor", "max_new_tokens")})
+        actor = types.SimpleNamespace(
+            config=cfg, reward_bias=c["reward_bias"], reward_scaling=c["reward_scaling"], reward_clip=c["reward_clip"],
+            kl_ctl=c["kl_ctl"], kl_estimator=KLEstimator(c["kl_estimator"]), discount=c["discount"],
+            gae_lambda=c["gae_lambda"], mask_no_eos_with_zero=c["mask_no_eos_with_zero"],
+            adv_norm=Normalization(NormConfig(mean_level="batch", std_level="batch")) if c["adv_norm"] else None,
+            reward_norm=Normalization(NormConfig(mean_level="group", std_level="group", group_size=4)) if c["reward_norm"] else None)
+        with torch.no_grad():
+            fn(actor, d)
+        for k in ("advantages", "returns", "kl_rewards", "tot_rewards", "loss_mask", "logprobs", "rewards", "ref_logp", "prox_logp"):
+            if k in d:
+                z[f"c{ci}_out_{k}"] = d[k].numpy().copy()
+    z["n_cases"] = np.array(len(adv_case_grid()))
+    np.savez_compressed(os.path.join(OUT, "advantages.npz"), **z)
+    print("advantages golden:", len(adv_case_grid()), "cases")
+
+
+def grpo_case(mb, T=300, V=977):
+    g = torch.Generator().manual_seed(900 + mb)
+    logits = (torch.randn(T, V, generator=g) * 2.5).bfloat16()
+    ids = torch.randint(0, V, (T,), generator=g)
+    old = -torch.rand(T, generator=g) * 3
+    prox = old + torch.randn(T, generator=g) * 0.3
+    adv = torch.randn(T, generator=g)
+    mask = torch.rand(T, generator=g) > (0.3 if mb < 2 else 2.0)        # third micro-batch: nothing valid
+    return dict(logits=logits, input_ids=ids, logprobs=old, prox_logp=prox, advantages=adv, loss_mask=mask)
+
+
+GRPO_ARGS = [dict(temperature=1.0, eps_clip=0.2, eps_clip_higher=None, c_clip=None, behav_imp_weight_cap=None),
+             dict(temperature=0.7, eps_clip=0.1, eps_clip_higher=0.3, c_clip=3.0, behav_imp_weight_cap=2.0)]
+
+
+def gen_grpo_stats():
+    """grpo_loss_fn + DistributedStatsTracker.export (actor.py:313-391, stats_tracker.py) run unmodified over
+    three micro-batches (the last with an all-false loss mask) inside a scope; fp32 logits on CPU."""
+    fn, st = R.load_areal_grpo_loss_fn()
+    z = {}
+    for ai, a in enumerate(GRPO_ARGS):
+        tr = st.DistributedStatsTracker()
+        st.denominator, st.stat = tr.denominator, tr.stat               # what grpo_loss_fn calls
+        losses = []
+        with tr.scope("ppo_actor"):
+            for mb in range(3):
+                c = grpo_case(mb)
+                if ai == 0:
+                    for k, v in c.items():
+                        z[f"mb{mb}_{k}"] = bf16_bits(v) if v.dtype == torch.bfloat16 else v.numpy()
+                d = {k: v for k, v in c.items() if k != "logits"}
+                losses.append(float(fn(c["logits"].float(), d, **a)))
+            tr.scalar(lr=1e-3)
+            tr.scalar(lr=3e-3)
+        out = tr.export()
+        z[f"a{ai}_losses"] = np.array(losses)
+        z[f"a{ai}_keys"] = np.array(sorted(out.keys()))
+        z[f"a{ai}_vals"] = np.array([out[k] for k in sorted(out.keys())], dtype=np.float64)
+    np.savez_compressed(os.path.join(OUT, "grpo_stats.npz"), **z)
+    print("grpo_stats golden:", len(out), "keys; e.g.", list(out.items())[:3])
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     assert R.available(), "needs /root/reference"
@@ -383,6 +490,8 @@ def main():
     gen_legacy_packed()
     gen_normalization(af)
     gen_pack()
+    gen_advantages()
+    gen_grpo_stats()
 
 
 if __name__ == "__main__":

@@ -230,3 +230,73 @@ def load_areal_pack_tensor_dict():
     ns = dict(torch=torch, F=F, Dict=Dict, Any=Any)
     exec(compile(ast.get_source_segment(src, node), "data.py[pack_tensor_dict]", "exec"), ns)
     return ns["pack_tensor_dict"]
+
+
+def load_areal_compute_advantages():
+    """`PPOActor.compute_advantages` (areal/engine/ppo/actor.py:72-164) as a plain function of
+    (self, data), extracted by AST and executed where it lies together with `KLEstimator`
+    (areal/utils/data.py:1306-1364), `reward_overlong_penalty` (areal/utils/functional.py:376-398) and
+    the reference `Normalization`.  Returns (compute_advantages, KLEstimator, Normalization, NormConfig)."""
+    import ast
+    from typing import Any, Dict, List, Optional
+
+    import torch
+    Normalization, NormConfig = load_areal_normalization()
+
+    def segment(path, kind, name, parent=None):
+        with open(os.path.join(REF_ROOT, path)) as f:
+            src = f.read()
+        body = ast.parse(src).body
+        if parent is not None:
+            body = next(n for n in body if isinstance(n, ast.ClassDef) and n.name == parent).body
+        node = next(n for n in body if isinstance(n, kind) and n.name == name)
+        node.decorator_list = []
+        return ast.unparse(node)
+
+    ns = dict(torch=torch, Dict=Dict, Any=Any, List=List, Optional=Optional, Normalization=Normalization)
+    exec(compile(segment("areal/utils/data.py", ast.ClassDef, "KLEstimator"), "data.py[KLEstimator]", "exec"), ns)
+    exec(compile(segment("areal/utils/functional.py", ast.FunctionDef, "reward_overlong_penalty"),
+                 "functional.py[reward_overlong_penalty]", "exec"), ns)
+    exec(compile(segment("areal/engine/ppo/actor.py", ast.FunctionDef, "compute_advantages", parent="PPOActor"),
+                 "actor.py[compute_advantages]", "exec"), ns)
+    return ns["compute_advantages"], ns["KLEstimator"], Normalization, NormConfig
+
+
+def load_areal_stats_tracker():
+    """areal/utils/stats_tracker.py executed where it lies (stubs: areal.platforms.current_platform,
+    areal.utils.logging, areal.utils.datapack.flat2d)."""
+    import itertools
+    import logging as _logging
+    names = ["areal", "areal.platforms", "areal.utils", "areal.utils.logging", "areal.utils.datapack"]
+    saved = {k: sys.modules.get(k) for k in names}
+    try:
+        _stub("areal")
+        _stub("areal.platforms", current_platform=types.SimpleNamespace(is_initialized=lambda: False, device_type="cpu"))
+        lg = _stub("areal.utils.logging", getLogger=lambda name=None: _logging.getLogger(name))
+        dp = _stub("areal.utils.datapack", flat2d=lambda arr: list(itertools.chain(*arr)))
+        _stub("areal.utils", logging=lg, datapack=dp)
+        return _load("areal/utils/stats_tracker.py", "_ref_areal_stats_tracker")
+    finally:
+        for k, v in saved.items():
+            if v is None:
+                sys.modules.pop(k, None)
+            else:
+                sys.modules[k] = v
+
+
+def load_areal_grpo_loss_fn():
+    """`grpo_loss_fn` (areal/engine/ppo/actor.py:313-391) bound to the reference's own
+    gather_logprobs_entropy / ppo_actor_loss_fn and stats_tracker.  Returns (fn, stats_tracker module)."""
+    import ast
+    from typing import Dict
+
+    import torch
+    af = load_areal_functional()
+    st = load_areal_stats_tracker()
+    with open(os.path.join(REF_ROOT, "areal/engine/ppo/actor.py")) as f:
+        src = f.read()
+    node = next(n for n in ast.parse(src).body if isinstance(n, ast.FunctionDef) and n.name == "grpo_loss_fn")
+    ns = dict(torch=torch, Dict=Dict, gather_logprobs_entropy=af.gather_logprobs_entropy,
+              ppo_actor_loss_fn=af.ppo_actor_loss_fn, stats_tracker=st)
+    exec(compile(ast.get_source_segment(src, node), "actor.py[grpo_loss_fn]", "exec"), ns)
+    return ns["grpo_loss_fn"], st

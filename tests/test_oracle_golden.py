@@ -232,3 +232,40 @@ def test_normalization_vs_reference():
         mask = c["mask"] if bool(c["has_mask"]) else None
         y = O.masked_normalization(c["x"], mask, bool(c["unbiased"]))
         assert np.allclose(y, c["y"], rtol=2e-6, atol=2e-6), k
+
+
+def test_compute_advantages_oracle_vs_reference():
+    """oracle compute_advantages == PPOActor.compute_advantages run unmodified (cases without a
+    Normalization: the scaling / KL / reward placement / GAE are bit-exact; k3 within 2 ulp of exp)."""
+    from tests import adv_cases as A
+    n = 0
+    for c, ins, outs in A.load():
+        if c["reward_norm"]:
+            continue
+        score = ins["rewards"]
+        if c["overlong_reward_penalty"]:
+            score = O.overlong_penalty(score, ins["loss_mask"], c["overlong_tokens"], c["overlong_penalty_factor"],
+                                       c["max_new_tokens"])
+            assert np.array_equal(score, outs["rewards"])
+        swap = (not c["use_decoupled_loss"]) and c["recompute_logprob"]
+        r = O.compute_advantages(score, ins["loss_mask"], ins["prox_logp"] if swap else ins["logprobs"],
+                                 ins["attention_mask"], ref_logp=ins.get("ref_logp"), values=ins.get("values"),
+                                 roll_logp=not swap, reward_bias=c["reward_bias"], reward_scaling=c["reward_scaling"],
+                                 reward_clip=c["reward_clip"], kl_ctl=c["kl_ctl"], kl_estimator=c["kl_estimator"],
+                                 mask_no_eos_with_zero=c["mask_no_eos_with_zero"], discount=c["discount"],
+                                 gae_lambda=c["gae_lambda"])
+        for k in ("loss_mask", "logprobs"):
+            assert np.array_equal(r[k], outs[k]), k
+        if "ref_logp" in outs:
+            assert np.array_equal(r["ref_logp"], outs["ref_logp"])
+        if c["kl_estimator"] == "k3":
+            np.testing.assert_allclose(r["kl_rewards"], outs["kl_rewards"], rtol=3e-7, atol=1e-7)
+            np.testing.assert_allclose(r["tot_rewards"], outs["tot_rewards"], rtol=3e-7, atol=1e-7)
+            A.assert_gae_close(r["returns"], outs["returns"], "returns")
+        else:
+            for k in ("kl_rewards", "tot_rewards", "returns"):
+                assert np.array_equal(r[k], outs[k]), (k, c)
+            if not c["adv_norm"]:
+                assert np.array_equal(r["advantages"], outs["advantages"])
+        n += 1
+    assert n >= 7

@@ -32,9 +32,16 @@ def test_patch_areal_rebinds_from_import_sites():
         actor = types.ModuleType("areal.engine.ppo.actor")
         actor.gather_logprobs_entropy = fun.gather_logprobs_entropy    # `from ... import ...` binding
         actor.ppo_actor_loss_fn = fun.ppo_actor_loss_fn
+        class PPOActor:                                                 # stands for the reference class
+            def compute_advantages(self, data):
+                return "reference"
+        actor.PPOActor = PPOActor
         sys.modules["areal.utils.functional"] = fun
         sys.modules["areal.engine.ppo.actor"] = actor
         patched = patch.patch_areal()
+        from areal_b200 import actor as A
+        assert PPOActor.compute_advantages is A.compute_advantages
+        assert "areal.engine.ppo.actor.PPOActor.compute_advantages" in patched
         assert "areal.utils.functional" in patched and "areal.engine.ppo.actor" in patched
         assert actor.gather_logprobs_entropy is F.gather_logprobs_entropy
         assert actor.ppo_actor_loss_fn is F.ppo_actor_loss_fn
