@@ -363,16 +363,16 @@ struct RowCtx {
   int64_t row_off, S, zero_col, add_col;
   float add_score;
 };
-__device__ __forceinline__ float2 fused_token(const AdvFusedParams& f, const RowCtx& c, int64_t t) {
-  const int64_t tn = (t + 1 == c.S) ? 0 : t + 1;                               // roll(-1), :110
-  const float lm = mask_as_float(f.loss_mask, f.loss_mask_code, c.row_off + tn);
-  const float old = __fmul_rn(__ldg(f.logp + c.row_off + (f.roll_logp ? tn : t)), lm);   // :116, :122
-  float ref = 0.f;
-  if (f.ref_logp) {
-    ref = __fmul_rn(f.ref_logp[c.row_off + t], lm);                            // :121 (in place)
-    f.ref_logp[c.row_off + t] = ref;
-  }
-  float kl = __fsub_rn(old, ref);                                              // data.py:1344
+struct TokOut {
+  float klr, tot, old, ref;
+};
+// lm: rolled mask of token t, lp: its (rolled) log-prob, rf: its reference log-prob (unmasked)
+__device__ __forceinline__ TokOut fused_math(const AdvFusedParams& f, const RowCtx& c, int64_t t, float lm,
+                                             float lp, float rf) {
+  TokOut o;
+  o.old = __fmul_rn(lp, lm);                                                   // :116, :122
+  o.ref = f.ref_logp ? __fmul_rn(rf, lm) : 0.f;                                // :120-121
+  float kl = __fsub_rn(o.old, o.ref);                                          // data.py:1344
   if (f.kl_kind == 2) {
     kl = __fmul_rn(__fmul_rn(kl, kl), 0.5f);                                   // :1353
   } else if (f.kl_kind == 3) {
@@ -380,15 +380,54 @@ __device__ __forceinline__ float2 fused_token(const AdvFusedParams& f, const Row
     kl = __fsub_rn(__fsub_rn(expf(lr), 1.f), lr);                              // :1360
   }
   if (f.kl_clamp) kl = fminf(fmaxf(kl, -10.f), 10.f);                          // :1363 (NaN stays NaN)
-  const float klr = __fmul_rn(f.neg_kl_ctl, kl);                               // actor.py:128
-  float tot = klr;
-  if (t == c.zero_col) tot = 0.f;                                              // :131
-  if (t == c.add_col) tot = __fadd_rn(tot, c.add_score);                       // :133-138
-  f.kl_rewards[c.row_off + t] = klr;
-  f.tot_rewards[c.row_off + t] = tot;
+  o.klr = __fmul_rn(f.neg_kl_ctl, kl);                                         // actor.py:128
+  o.tot = o.klr;
+  if (t == c.zero_col) o.tot = 0.f;                                            // :131
+  if (t == c.add_col) o.tot = __fadd_rn(o.tot, c.add_score);                   // :133-138
+  return o;
+}
+// scalar path: loads, math and the side outputs of one token; returns (tot_reward, mask)
+__device__ __forceinline__ float2 fused_token(const AdvFusedParams& f, const RowCtx& c, int64_t t) {
+  const int64_t tn = (t + 1 == c.S) ? 0 : t + 1;                               // roll(-1), :110
+  const float lm = mask_as_float(f.loss_mask, f.loss_mask_code, c.row_off + tn);
+  const float lp = __ldg(f.logp + c.row_off + (f.roll_logp ? tn : t));
+  const float rf = f.ref_logp ? f.ref_logp[c.row_off + t] : 0.f;
+  const TokOut o = fused_math(f, c, t, lm, lp, rf);
+  if (f.ref_logp) f.ref_logp[c.row_off + t] = o.ref;                           // in place, :121
+  f.kl_rewards[c.row_off + t] = o.klr;
+  f.tot_rewards[c.row_off + t] = o.tot;
   f.loss_mask_out[c.row_off + t] = lm;
-  f.old_logp_out[c.row_off + t] = old;
-  return make_float2(tot, lm);
+  f.old_logp_out[c.row_off + t] = o.old;
+  return make_float2(o.tot, lm);
+}
+
+__device__ __forceinline__ void ld8(const float* p, float* o) {
+  const float4 a = __ldg(reinterpret_cast<const float4*>(p));
+  const float4 b = __ldg(reinterpret_cast<const float4*>(p) + 1);
+  o[0] = a.x; o[1] = a.y; o[2] = a.z; o[3] = a.w;
+  o[4] = b.x; o[5] = b.y; o[6] = b.z; o[7] = b.w;
+}
+__device__ __forceinline__ void st8(float* p, const float* v) {
+  reinterpret_cast<float4*>(p)[0] = make_float4(v[0], v[1], v[2], v[3]);
+  reinterpret_cast<float4*>(p)[1] = make_float4(v[4], v[5], v[6], v[7]);
+}
+// mask elements i .. i+8 as floats (i a multiple of 8 elements from an aligned base)
+__device__ __forceinline__ void ld9_mask(const void* base, int code, int64_t i, float* o) {
+  if (code == 0) {
+    ld8(reinterpret_cast<const float*>(base) + i, o);
+    o[8] = __ldg(reinterpret_cast<const float*>(base) + i + 8);
+  } else if (code == 1) {
+    const uint2 w = __ldg(reinterpret_cast<const uint2*>(reinterpret_cast<const uint8_t*>(base) + i));
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      o[k] = float((w.x >> (8 * k)) & 0xffu);
+      o[4 + k] = float((w.y >> (8 * k)) & 0xffu);
+    }
+    o[8] = float(__ldg(reinterpret_cast<const uint8_t*>(base) + i + 8));
+  } else {
+#pragma unroll
+    for (int k = 0; k < 9; ++k) o[k] = mask_as_float(base, code, i + k);
+  }
 }
 
 template <bool kFused>
@@ -471,18 +510,55 @@ gae_padded_kernel(const GaePaddedParams p, const AdvFusedParams f) {
       if (t0 < L) nvalid = (L - t0) < kItems ? int(L - t0) : kItems;
       float rr[kItems], vv[kItems];
       unsigned int valid_bits = 0;
+      const bool vec = p.vec_ok && nvalid == kItems;               // whole 8-token piece, 16-byte aligned
+      if (vec) {
+        if (kFused) {
+          const int64_t g0 = ctx.row_off + t0;
+          float m9[kItems + 1], lp9[kItems + 1], rf[kItems], klr[kItems], old[kItems];
+          ld9_mask(f.loss_mask, f.loss_mask_code, g0, m9);         // t0+8 <= S-1 here: no wrap
+          ld8(f.logp + g0, lp9);
+          lp9[kItems] = __ldg(f.logp + g0 + kItems);
+          if (f.ref_logp) ld8(f.ref_logp + g0, rf);
+          if (v) ld8(v + t0, vv);
 #pragma unroll
-      for (int k = 0; k < kItems; ++k) {
-        if (k < nvalid) {
-          if (kFused) {
-            const float2 tm = fused_token(f, ctx, t0 + k);
-            rr[k] = tm.x;
-            vv[k] = v ? __ldg(v + t0 + k) : 0.f;
-            if (tm.y != 0.f) valid_bits |= 1u << k;
-          } else {
-            rr[k] = __ldg(r + t0 + k);
-            vv[k] = __ldg(v + t0 + k);
-            if (__ldg(m + t0 + k) != 0.f) valid_bits |= 1u << k;
+          for (int k = 0; k < kItems; ++k) {
+            if (!v) vv[k] = 0.f;
+            const TokOut o = fused_math(f, ctx, t0 + k, m9[k + 1], f.roll_logp ? lp9[k + 1] : lp9[k],
+                                        f.ref_logp ? rf[k] : 0.f);
+            rr[k] = o.tot;
+            klr[k] = o.klr;
+            old[k] = o.old;
+            rf[k] = o.ref;
+            if (m9[k + 1] != 0.f) valid_bits |= 1u << k;
+          }
+          if (f.ref_logp) st8(f.ref_logp + g0, rf);
+          st8(f.kl_rewards + g0, klr);
+          st8(f.tot_rewards + g0, rr);
+          st8(f.loss_mask_out + g0, m9 + 1);
+          st8(f.old_logp_out + g0, old);
+        } else {
+          float mm[kItems];
+          ld8(r + t0, rr);
+          ld8(v + t0, vv);
+          ld8(m + t0, mm);
+#pragma unroll
+          for (int k = 0; k < kItems; ++k)
+            if (mm[k] != 0.f) valid_bits |= 1u << k;
+        }
+      } else {
+#pragma unroll
+        for (int k = 0; k < kItems; ++k) {
+          if (k < nvalid) {
+            if (kFused) {
+              const float2 tm = fused_token(f, ctx, t0 + k);
+              rr[k] = tm.x;
+              vv[k] = v ? __ldg(v + t0 + k) : 0.f;
+              if (tm.y != 0.f) valid_bits |= 1u << k;
+            } else {
+              rr[k] = __ldg(r + t0 + k);
+              vv[k] = __ldg(v + t0 + k);
+              if (__ldg(m + t0 + k) != 0.f) valid_bits |= 1u << k;
+            }
           }
         }
       }
@@ -536,9 +612,18 @@ gae_padded_kernel(const GaePaddedParams p, const AdvFusedParams f) {
         if (k < nvalid) {
           if ((valid_bits >> k) & 1u) A = fma(gl, A, double(delta[k]));
           const float af = float(A);
-          adv[t0 + k] = af;
-          ret[t0 + k] = __fadd_rn(af, vv[k]);
+          if (vec) {
+            rr[k] = af;                                            // rewards are dead: reuse as staging
+            vv[k] = __fadd_rn(af, vv[k]);
+          } else {
+            adv[t0 + k] = af;
+            ret[t0 + k] = __fadd_rn(af, vv[k]);
+          }
         }
+      }
+      if (vec) {
+        st8(adv + t0, rr);
+        st8(ret + t0, vv);
       }
       a_carry = fma(tagg.a, a_carry, tagg.b);
       nv_carry = nv_tile;
@@ -693,16 +778,27 @@ int launch_gae1d_static(Gae1dParams p, cudaStream_t stream) {
   return check_launch("gae1d (static scratch)");
 }
 
-int launch_gae_padded(const GaePaddedParams& p, cudaStream_t stream) {
+static bool aligned16(const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; }
+
+int launch_gae_padded(const GaePaddedParams& p_in, cudaStream_t stream) {
+  GaePaddedParams p = p_in;
   if (p.B == 0 || p.S == 0) return kOk;
+  p.vec_ok = p.S % 4 == 0 && aligned16(p.rewards) && aligned16(p.values) && aligned16(p.mask) &&
+             aligned16(p.adv) && aligned16(p.ret);
   const int64_t cap = int64_t(num_sms()) * 8;
   gae_padded_kernel<false><<<static_cast<unsigned int>(p.B < cap ? p.B : cap), kThreads, 0, stream>>>(
       p, AdvFusedParams{});
   return check_launch("gae_padded");
 }
 
-int launch_advantages_padded(const GaePaddedParams& p, const AdvFusedParams& f, cudaStream_t stream) {
+int launch_advantages_padded(const GaePaddedParams& p_in, const AdvFusedParams& f, cudaStream_t stream) {
+  GaePaddedParams p = p_in;
   if (p.B == 0 || p.S == 0) return kOk;
+  // S % 8: rows of 1-byte masks start on an 8-byte boundary too
+  p.vec_ok = p.S % 8 == 0 && aligned16(p.values) && aligned16(p.adv) && aligned16(p.ret) &&
+             aligned16(f.loss_mask) && aligned16(f.logp) && aligned16(f.ref_logp) &&
+             aligned16(f.kl_rewards) && aligned16(f.tot_rewards) && aligned16(f.loss_mask_out) &&
+             aligned16(f.old_logp_out);
   const int64_t cap = int64_t(num_sms()) * 8;
   gae_padded_kernel<true><<<static_cast<unsigned int>(p.B < cap ? p.B : cap), kThreads, 0, stream>>>(p, f);
   return check_launch("advantages_padded");

@@ -23,6 +23,7 @@ struct GaePaddedParams {
   const float* values;       // [B, S]
   const float* mask;         // [B, S] already rolled by -1 (actor.py:110); != 0 means "counts"
   const uint8_t* no_eos;     // [B]
+  int vec_ok;                // set by the launcher: 128-bit row access allowed
   int64_t B, S;
   float g, gl;
   float* adv;

@@ -57,7 +57,10 @@ def test_compute_advantages_golden(ci):
 
 
 @pytest.mark.parametrize("B,S,mask_dtype", [(64, 4099, torch.bool), (3, 1, torch.int64), (5, 2, torch.float32),
-                                            (300, 513, torch.int32)])
+                                            (300, 513, torch.int32),
+                                            # S % 8 == 0: the 128-bit path (byte masks, float masks, generic)
+                                            (33, 4096, torch.bool), (16, 2056, torch.float32), (9, 8, torch.bool),
+                                            (20, 1024, torch.int64), (7, 6152, torch.uint8)])
 def test_compute_advantages_vs_oracle(B, S, mask_dtype):
     from areal_b200.actor import compute_advantages
     rng = np.random.RandomState(B + S)
