@@ -44,8 +44,8 @@ def build(verbose=False, force=False):
         return OUT
     with cf.ThreadPoolExecutor(max_workers=len(SOURCES)) as ex:
         objs = list(ex.map(lambda s: _compile(s, verbose), SOURCES))
-    cmd = [NVCC, "-shared", "-cudart", "shared", "-Xlinker", "-rpath,/usr/local/cuda/lib64",
-           "-o", OUT, *objs]
+    cmd = [NVCC, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-cudart", "shared", "-Xlinker",
+           "-rpath,/usr/local/cuda/lib64", "-o", OUT, *objs]
     if verbose:
         print(" ".join(cmd), flush=True)
     subprocess.check_call(cmd)

@@ -108,6 +108,9 @@ __device__ __forceinline__ void st_relaxed_f64(unsigned long long* p, double x) 
 // token (smallest i with cu[i+1] > first token).  Replaces a memset node, so it costs no extra launch.
 __global__ void gae1d_prep_kernel(const int32_t* __restrict__ cu, int B, int64_t T, int64_t ntiles,
                                   TileDesc* __restrict__ desc, int tile_tokens) {
+  // programmatic dependent launch: the scan kernel may start (and prefetch its rewards) while this
+  // grid runs; it waits (griddepcontrol.wait) for this grid to COMPLETE before it reads a descriptor
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   const int64_t t = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
   if (t >= ntiles) return;
   const int64_t tok = t * tile_tokens;
@@ -164,6 +167,10 @@ gae1d_kernel(const Gae1dParams p) {
 #pragma unroll
     for (int k = 0; k < kItems; ++k) r[k] = (k < nvalid) ? __ldg(rew + p0 + k) : 0.f;
   }
+
+  // everything above is independent of the prep kernel; from here on its descriptors are read
+  // (no-op unless launched as a programmatic dependent)
+  asm volatile("griddepcontrol.wait;" ::: "memory");
 
   float vcur[kItems], delta[kItems];
   unsigned int last_bits = 0;
@@ -725,6 +732,22 @@ int launch_gae1d(const Gae1dParams& p, cudaStream_t stream) {
     TileDesc* desc = reinterpret_cast<TileDesc*>(reinterpret_cast<char*>(p.workspace) + sizeof(WorkspaceHeader));
     gae1d_prep_kernel<<<static_cast<unsigned int>((ntiles + 255) / 256), 256, 0, stream>>>(
         p.cu, static_cast<int>(p.B), p.T, ntiles, desc, kTile);
+  }
+  if (ntiles > 1) {
+    // launched as a programmatic dependent of the prep kernel: its launch latency and the reward
+    // loads overlap the prep grid
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(static_cast<unsigned int>(ntiles));
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    AB_CUDA(cudaLaunchKernelEx(&cfg, gae1d_kernel, p));
+    return kOk;
   }
   gae1d_kernel<<<static_cast<unsigned int>(ntiles), kThreads, 0, stream>>>(p);
   return check_launch("gae1d");
