@@ -249,3 +249,55 @@ def test_backward_other_dtypes(dtype, V):
     scale = np.maximum(np.abs(ref).max(-1, keepdims=True), 1e-3 * (np.abs(w.numpy()) + 12 * np.abs(wh.numpy()))[:, None] / 0.8)
     ulp = 2 ** -11 if dtype == torch.float16 else 2 ** -23
     assert np.all(np.abs(got - ref) <= ulp * np.abs(ref) + H.TOL_LOGITS * scale + 1e-30)
+
+
+def test_full_size_runs_are_bit_identical():
+    """Full-size config 2, three runs of every logits path (split forward + backward, fused two-pass,
+    fused single-pass) with the allocator's free memory overwritten in between: outputs and gradients
+    must not change by a bit.  Catches shared-memory ring hand-off races (a stage released before its
+    last 128-byte wavefront was read shows up as a few wrong 64-column runs per launch)."""
+    from areal_b200 import functional as F
+    T, V = 16384, 151936
+    g = torch.Generator(device=D).manual_seed(5)
+    logits = torch.empty(T, V, dtype=torch.bfloat16, device=D)
+    for i in range(0, T, 2048):
+        logits[i:i + 2048] = (torch.randn(2048, V, generator=g, device=D) * 2.0).bfloat16()
+    labels = torch.randint(0, V, (T,), generator=g, device=D)
+    w = torch.randn(T, generator=g, device=D)
+    w[torch.rand(T, generator=g, device=D) < 0.3] = 0.0
+    old = -torch.rand(T, generator=g, device=D) * 12 - 6
+    prox = old + 0.1 * torch.randn(T, generator=g, device=D)
+    adv = torch.randn(T, generator=g, device=D)
+    mask = torch.rand(T, generator=g, device=D) > 0.2
+    scale = torch.full((1,), 0.5, device=D)
+
+    def bits(t):
+        return t.view(torch.int16) if t.dtype == torch.bfloat16 else t.view(torch.int32)
+
+    def run(path):
+        x = logits.detach().requires_grad_()
+        if path == "split":
+            lp, ent = F.gather_logprobs_entropy(x, labels, 1.0)
+            (grad,) = torch.autograd.grad((lp * w).sum(), x)
+            return [lp.detach(), ent.detach(), grad]
+        loss, st = F.fused_actor_loss(x, labels, 1.0, prox, old, adv, mask, eps_clip=0.4, behav_imp_weight_cap=5.0,
+                                      loss_scale=scale if path == "single" else None)
+        (loss * scale[0]).backward()
+        return [loss.detach().reshape(1), st["logprobs"], st["entropy"], x.grad]
+
+    for path in ("split", "twopass", "single"):
+        ref = None
+        for it in range(3):
+            junk = torch.empty(T, V, dtype=torch.bfloat16, device=D)
+            junk.view(torch.int16).fill_(0x7FC1 if it % 2 else 0x4142)
+            del junk
+            cur = run(path)
+            if ref is None:
+                ref = [c.clone() for c in cur]
+                if path == "split":
+                    assert int(torch.count_nonzero(cur[2][w == 0])) == 0
+            else:
+                for a, b in zip(cur, ref):
+                    assert torch.equal(bits(a), bits(b)), (path, it)
+            del cur
+        del ref
