@@ -704,6 +704,25 @@ AREAL_B200_API int64_t areal_b200_merge_intervals(const uint64_t* iv, int64_t n,
   return k;
 }
 
+AREAL_B200_API int areal_b200_packed_rewards(const float* log_probs, const float* ref_log_probs,
+                                             const float* score, const int32_t* short1cu_seqlens,
+                                             const uint8_t* seq_no_eos, int64_t total_short_tokens,
+                                             int64_t batch_size, double kl_ctl, double clip_reward_value,
+                                             int mask_no_eos_with_zero, int mode, float* kl_rewards_out,
+                                             float* tot_rewards_out, void* stream) {
+  AB_REQUIRE(total_short_tokens >= 0 && batch_size >= 0, "negative size");
+  if (total_short_tokens == 0) return kOk;
+  AB_REQUIRE(batch_size > 0, "packed_rewards: tokens without sequences");
+  AB_REQUIRE(mode >= 0 && mode <= 2, "packed_rewards: mode must be 0 (sparse), 1 (dense) or 2 (dense delta)");
+  AB_REQUIRE(log_probs && ref_log_probs && score && short1cu_seqlens && kl_rewards_out && tot_rewards_out,
+             "null pointer");
+  AB_REQUIRE(!(mode == 0 && mask_no_eos_with_zero) || seq_no_eos, "packed_rewards: seq_no_eos is required");
+  return launch_packed_rewards(log_probs, ref_log_probs, score, short1cu_seqlens, seq_no_eos, total_short_tokens,
+                               batch_size, static_cast<float>(-kl_ctl), static_cast<float>(clip_reward_value),
+                               mask_no_eos_with_zero, mode, kl_rewards_out, tot_rewards_out,
+                               static_cast<cudaStream_t>(stream));
+}
+
 AREAL_B200_API int64_t areal_b200_masked_stats_workspace_bytes(int64_t n_keys, int64_t n) {
   if (n_keys < 0 || n < 0) return -1;
   return masked_stats_workspace_bytes(n_keys, n);

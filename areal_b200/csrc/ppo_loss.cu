@@ -112,6 +112,64 @@ __global__ void scale_kernel(const float* __restrict__ coef, const float* __rest
     out[t] = coef[t] * s;
 }
 
+// get_packed_rewards / get_packed_reward_dense (realhf ppo_functional.py:228-289): KL reward per token,
+// plus the clipped task reward on the last token of each sequence (mode 0) or a per-token dense reward
+// (mode 1: d[j+1]; mode 2: d[j+1] - d[j], indices in the one-longer-per-sequence layout).
+constexpr int kRewItems = 4;
+__global__ void __launch_bounds__(kThreads)
+packed_rewards_kernel(const float* __restrict__ logp, const float* __restrict__ ref,
+                      const float* __restrict__ score, const int32_t* __restrict__ cu,
+                      const uint8_t* __restrict__ no_eos, int64_t Ts, int B, float neg_kl_ctl, float clip,
+                      int mask_no_eos_with_zero, int mode, float* __restrict__ kl_out,
+                      float* __restrict__ tot_out) {
+  const int64_t nthreads = (Ts + kRewItems - 1) / kRewItems;
+  for (int64_t th = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; th < nthreads;
+       th += int64_t(gridDim.x) * blockDim.x) {
+    const int64_t t0 = th * kRewItems;
+    // sequence of t0: smallest i with cu[i+1] > t0
+    int lo = 0, hi = B - 1;
+    while (lo < hi) {
+      const int mid = (lo + hi) >> 1;
+      if (int64_t(__ldg(cu + mid + 1)) > t0) hi = mid; else lo = mid + 1;
+    }
+    int seq = lo;
+    int64_t end = __ldg(cu + seq + 1);
+#pragma unroll
+    for (int k = 0; k < kRewItems; ++k) {
+      const int64_t t = t0 + k;
+      if (t >= Ts) break;
+      while (t >= end && seq < B - 1) {
+        ++seq;
+        end = __ldg(cu + seq + 1);
+      }
+      const float klr = __fmul_rn(neg_kl_ctl, __fsub_rn(__ldg(logp + t), __ldg(ref + t)));   // :241
+      float tot = klr;
+      if (mode == 0) {
+        // the LAST sequence ending at t+1 adds its score (duplicates: an empty sequence shares the index
+        // of its predecessor and, as in the reference's index assignment, the later one wins)
+        if (t + 1 == end) {
+          int s2 = seq;
+          while (s2 + 1 < B && int64_t(__ldg(cu + s2 + 2)) == end) ++s2;
+          float sc = fminf(fmaxf(__ldg(score + s2), -clip), clip);                            // :243
+          if (mask_no_eos_with_zero && no_eos[s2]) sc = 0.f;                                  // :245-248
+          tot = __fadd_rn(tot, sc);
+        }
+      } else {
+        const int64_t j = t + seq;                                                             // offset2 + (t - offset)
+        const float d1 = fminf(fmaxf(__ldg(score + j + 1), -clip), clip);
+        if (mode == 2) {
+          const float d0 = fminf(fmaxf(__ldg(score + j), -clip), clip);
+          tot = __fadd_rn(tot, __fsub_rn(d1, d0));                                            // :272-275
+        } else {
+          tot = __fadd_rn(tot, d1);                                                           // :277-279
+        }
+      }
+      kl_out[t] = klr;
+      tot_out[t] = tot;
+    }
+  }
+}
+
 unsigned int grid_for(int64_t T) {
   const int64_t cap = int64_t(num_sms()) * 4;
   const int64_t need = (T + kThreads - 1) / kThreads;
@@ -130,6 +188,17 @@ int launch_actor_loss(const ActorLossParams& p, cudaStream_t stream) {
 int launch_critic_loss(const CriticLossParams& p, cudaStream_t stream) {
   critic_loss_kernel<<<grid_for(p.T), kThreads, 0, stream>>>(p);
   return check_launch("critic_loss");
+}
+
+int launch_packed_rewards(const float* logp, const float* ref, const float* score, const int32_t* cu,
+                          const uint8_t* no_eos, int64_t Ts, int64_t B, float neg_kl_ctl, float clip,
+                          int mask_no_eos_with_zero, int mode, float* kl_out, float* tot_out,
+                          cudaStream_t stream) {
+  if (Ts == 0) return kOk;
+  packed_rewards_kernel<<<grid_for((Ts + kRewItems - 1) / kRewItems), kThreads, 0, stream>>>(
+      logp, ref, score, cu, no_eos, Ts, static_cast<int>(B), neg_kl_ctl, clip, mask_no_eos_with_zero, mode, kl_out,
+      tot_out);
+  return check_launch("packed_rewards");
 }
 
 int launch_scale(const float* coef, const float* s0, const float* s1, int64_t T, float* out,

@@ -37,4 +37,9 @@ int launch_critic_loss(const CriticLossParams& p, cudaStream_t stream);
 int launch_scale(const float* coef, const float* s0, const float* s1, int64_t T, float* out,
                  cudaStream_t stream);
 
+int launch_packed_rewards(const float* logp, const float* ref, const float* score, const int32_t* cu,
+                          const uint8_t* no_eos, int64_t Ts, int64_t B, float neg_kl_ctl, float clip,
+                          int mask_no_eos_with_zero, int mode, float* kl_out, float* tot_out,
+                          cudaStream_t stream);
+
 }  // namespace ab

@@ -109,7 +109,7 @@ def patch_realhf():
     m = sys.modules.get("realhf.impl.model.utils.ppo_functional")
     if m is not None:
         for fn in ("cugae1d_nolp_misalign_func", "get_packed_advantages_and_returns", "actor_loss_fn",
-                   "critic_loss_fn"):
+                   "critic_loss_fn", "get_packed_rewards", "get_packed_reward_dense"):
             setattr(m, fn, getattr(_P, fn))
         patched.append(m.__name__)
     m = sys.modules.get("realhf.impl.model.nn.flatten_param")

@@ -66,6 +66,46 @@ def get_packed_advantages_and_returns(gamma: float, lam: float, values: torch.Te
                                       seq_no_eos_mask.bool().contiguous(), gamma, lam)
 
 
+def _packed_rewards(mode, kl_ctl, clip_reward_value, log_probs, ref_log_probs, score, short1cu_seqlens,
+                    seq_no_eos_mask, mask_no_eos_with_zero):
+    dev = _lib.require_cuda(log_probs, ref_log_probs, score, short1cu_seqlens)
+    lp = log_probs.float().contiguous()
+    rf = ref_log_probs.float().contiguous()
+    _check(lp.dim() == 1 and lp.shape == rf.shape, "log_probs / ref_log_probs must be 1D with equal shapes")
+    cu = short1cu_seqlens.int().contiguous()
+    B, Ts = cu.numel() - 1, lp.numel()
+    sc = score.float().contiguous()
+    _check(sc.numel() == (B if mode == 0 else Ts + B), "reward tensor does not match the sequence table")
+    ne = None
+    if seq_no_eos_mask is not None and mode == 0:
+        ne = seq_no_eos_mask.bool().contiguous().view(torch.uint8)
+    kl = torch.empty_like(lp)
+    tot = torch.empty_like(lp)
+    with torch.cuda.device(dev):
+        call("areal_b200_packed_rewards", ptr(lp), ptr(rf), ptr(sc), ptr(cu), ptr(ne), Ts, B, float(kl_ctl),
+             float(clip_reward_value), int(bool(mask_no_eos_with_zero)), mode, ptr(kl), ptr(tot), stream_ptr(dev))
+    return kl, tot
+
+
+@torch.no_grad()
+def get_packed_rewards(kl_ctl: float, clip_reward_value: float, log_probs: torch.Tensor, ref_log_probs: torch.Tensor,
+                       reward_score: torch.Tensor, short1cu_seqlens: torch.Tensor, seq_no_eos_mask: torch.Tensor,
+                       mask_no_eos_with_zero: bool = False) -> Tuple[torch.Tensor, torch.Tensor]:
+    """Drop-in for `get_packed_rewards` (ppo_functional.py:228-253): (kl_rewards, tot_rewards), one launch."""
+    return _packed_rewards(0, kl_ctl, clip_reward_value, log_probs, ref_log_probs, reward_score, short1cu_seqlens,
+                           seq_no_eos_mask, mask_no_eos_with_zero)
+
+
+@torch.no_grad()
+def get_packed_reward_dense(kl_ctl: float, clip_reward_value: float, log_probs: torch.Tensor,
+                            ref_log_probs: torch.Tensor, dense_reward_score: torch.Tensor,
+                            short1cu_seqlens: torch.Tensor, seq_no_eos_mask: torch.Tensor, reward_delta: bool):
+    """Drop-in for `get_packed_reward_dense` (ppo_functional.py:256-289): the reference walks the
+    sequences in a Python loop (a host sync per sequence); here one launch."""
+    return _packed_rewards(2 if reward_delta == True else 1, kl_ctl, clip_reward_value, log_probs,  # noqa: E712
+                           ref_log_probs, dense_reward_score, short1cu_seqlens, None, False)
+
+
 @torch.no_grad()
 def gae_padded_masked(rewards: torch.Tensor, values: torch.Tensor, loss_mask: torch.Tensor,
                       seq_no_eos_mask: torch.Tensor, discount: float, gae_lambda: float):

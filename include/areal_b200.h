@@ -340,6 +340,21 @@ AREAL_B200_API int areal_b200_set_intervals(const void* packed, int64_t packed_n
  * returns the number of merged intervals, or -1 on a null pointer. */
 AREAL_B200_API int64_t areal_b200_merge_intervals(const uint64_t* intervals, int64_t n, uint64_t* out);
 
+/* KL-regularised token rewards of the legacy packed path in ONE launch.  Replaces
+ * `get_packed_rewards` (mode 0) and `get_packed_reward_dense` (mode 1; mode 2 = reward_delta)
+ * (realhf/impl/model/utils/ppo_functional.py:228-289; 6 torch kernels, or a Python loop over the
+ * sequences with 2 kernels each for the dense variant).
+ *   log_probs, ref_log_probs f32[Ts] (one step shorter per sequence than the packed ids);
+ *   short1cu_seqlens i32[B+1]; score f32[B] (mode 0) or f32[Ts+B] dense (modes 1, 2);
+ *   seq_no_eos u8/bool[B] (mode 0 with mask_no_eos_with_zero; may be NULL otherwise).
+ *   Outputs kl_rewards, tot_rewards f32[Ts]. */
+AREAL_B200_API int areal_b200_packed_rewards(const float* log_probs, const float* ref_log_probs,
+                                             const float* score, const int32_t* short1cu_seqlens,
+                                             const uint8_t* seq_no_eos, int64_t total_short_tokens,
+                                             int64_t batch_size, double kl_ctl, double clip_reward_value,
+                                             int mask_no_eos_with_zero, int mode, float* kl_rewards_out,
+                                             float* tot_rewards_out, void* stream);
+
 /* Masked sum / count / min / max of n_keys (<= 32) float arrays of n elements in ONE launch: the
  * reductions `DistributedStatsTracker` does per key at export time
  * (areal/utils/stats_tracker.py:210-289: torch.where(d, v, fill) + sum/min/max per key and per

@@ -640,3 +640,28 @@ def compute_advantages(score, loss_mask, logprobs, attention_mask, *, ref_logp=N
     adv, ret = gae_padded_masked(rewards, vals, lm, no_eos, discount, gae_lambda)
     return dict(advantages=adv, returns=ret, kl_rewards=kl_rewards, tot_rewards=rewards, loss_mask=lm, logprobs=old,
                 ref_logp=ref)
+
+
+def packed_rewards(kl_ctl, clip_reward_value, log_probs, ref_log_probs, score, short1cu_seqlens, seq_no_eos_mask=None,
+                   mask_no_eos_with_zero=False, dense=False, reward_delta=False):
+    """get_packed_rewards / get_packed_reward_dense (realhf/impl/model/utils/ppo_functional.py:228-289)."""
+    f = np.float32
+    cu = np.asarray(short1cu_seqlens, dtype=np.int64)
+    tot = (f(-kl_ctl) * (log_probs.astype(f) - ref_log_probs.astype(f))).astype(f)      # :241 / :267
+    kl = tot.copy()
+    sc = np.clip(score.astype(f), f(-clip_reward_value), f(clip_reward_value))         # :243 / :269
+    if not dense:
+        add = np.where(seq_no_eos_mask, f(0), sc) if mask_no_eos_with_zero else sc      # :245-250
+        idx = cu[1:] - 1
+        tot[idx] = tot[idx] + add.astype(f)
+        return kl, tot
+    off = off2 = 0
+    for n in (cu[1:] - cu[:-1]):                                                        # :272-288
+        n = int(n)
+        if reward_delta:
+            tot[off:off + n] = tot[off:off + n] + (sc[off2 + 1:off2 + n + 1] - sc[off2:off2 + n]).astype(f)
+        else:
+            tot[off:off + n] = tot[off:off + n] + sc[off2 + 1:off2 + n + 1]
+        off += n
+        off2 += n + 1
+    return kl, tot

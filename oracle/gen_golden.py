@@ -474,6 +474,31 @@ def gen_grpo_stats():
     print("grpo_stats golden:", len(out), "keys; e.g.", list(out.items())[:3])
 
 
+def gen_packed_rewards(pf):
+    """get_packed_rewards / get_packed_reward_dense (realhf ppo_functional.py:228-289) run unmodified."""
+    g = torch.Generator().manual_seed(321)
+    z = {}
+    k = 0
+    for lens in ([5, 1, 17, 2, 300], [1], [64] * 9, list(range(1, 40))):
+        cu = torch.tensor([0] + list(np.cumsum(lens)), dtype=torch.int32)
+        B, Ts = len(lens), int(cu[-1])
+        lp, rf = -torch.rand(Ts, generator=g) * 5, -torch.rand(Ts, generator=g) * 5
+        score = torch.randn(B, generator=g) * 6
+        dense = torch.randn(Ts + B, generator=g) * 6
+        ne = torch.rand(B, generator=g) > 0.5
+        for kl_ctl, clip, mz in ((0.1, 5.0, False), (0.02, 2.0, True)):
+            a, b = pf.get_packed_rewards(kl_ctl, clip, lp, rf, score, cu, ne, mz)
+            for delta in (False, True):
+                c, d = pf.get_packed_reward_dense(kl_ctl, clip, lp, rf, dense, cu, ne.float(), delta)
+                z.update({f"c{k}_cu": cu.numpy(), f"c{k}_lp": lp.numpy(), f"c{k}_rf": rf.numpy(), f"c{k}_score": score.numpy(),
+                          f"c{k}_dense": dense.numpy(), f"c{k}_ne": ne.numpy(), f"c{k}_cfg": np.array([kl_ctl, clip, mz, delta]),
+                          f"c{k}_kl": a.numpy(), f"c{k}_tot": b.numpy(), f"c{k}_dkl": c.numpy(), f"c{k}_dtot": d.numpy()})
+                k += 1
+    z["n_cases"] = np.array(k)
+    np.savez_compressed(os.path.join(OUT, "packed_rewards.npz"), **z)
+    print("packed_rewards golden:", k, "cases")
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     assert R.available(), "needs /root/reference"
@@ -492,6 +517,7 @@ def main():
     gen_pack()
     gen_advantages()
     gen_grpo_stats()
+    gen_packed_rewards(pf)
 
 
 if __name__ == "__main__":

@@ -45,3 +45,34 @@ def test_legacy_packed_golden():
         scale = np.maximum(np.abs(ref).max(-1, keepdims=True), 1e-3 * np.abs(gfull)[:, None]) + 1e-30
         slack = 2 ** -8 if bf16 else 1e-6
         assert np.all(np.abs(got - ref) <= slack * np.abs(ref) + (3e-3 if bf16 else 1e-3) * scale + 1e-30), k
+
+
+def test_packed_rewards_golden_and_large():
+    """get_packed_rewards / get_packed_reward_dense: bit-exact vs golden outputs of the reference
+    functions, and vs the pinned oracle on a 200k-token batch with 1-token sequences."""
+    from areal_b200 import ppo_functional as P
+    z = H.load("packed_rewards.npz")
+    dev = torch.device("cuda:0")
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)   # noqa: E731
+    for k in range(int(z["n_cases"])):
+        kl_ctl, clip, mz, delta = [float(v) for v in z[f"c{k}_cfg"]]
+        a, b = P.get_packed_rewards(kl_ctl, clip, t(z[f"c{k}_lp"]), t(z[f"c{k}_rf"]), t(z[f"c{k}_score"]),
+                                    t(z[f"c{k}_cu"]), t(z[f"c{k}_ne"]), bool(mz))
+        assert np.array_equal(a.cpu().numpy(), z[f"c{k}_kl"]) and np.array_equal(b.cpu().numpy(), z[f"c{k}_tot"]), k
+        c, d = P.get_packed_reward_dense(kl_ctl, clip, t(z[f"c{k}_lp"]), t(z[f"c{k}_rf"]), t(z[f"c{k}_dense"]),
+                                         t(z[f"c{k}_cu"]), t(z[f"c{k}_ne"]).float(), bool(delta))
+        assert np.array_equal(c.cpu().numpy(), z[f"c{k}_dkl"]) and np.array_equal(d.cpu().numpy(), z[f"c{k}_dtot"]), k
+    rng = np.random.RandomState(4)
+    lens = np.concatenate([rng.randint(1, 3000, 120), np.ones(500, np.int64), rng.randint(1, 9, 3000)])
+    cu = np.concatenate([[0], np.cumsum(lens)]).astype(np.int32)
+    B, Ts = len(lens), int(cu[-1])
+    lp, rf = -rng.rand(Ts).astype(np.float32) * 5, -rng.rand(Ts).astype(np.float32) * 5
+    score, dense = (rng.randn(B) * 6).astype(np.float32), (rng.randn(Ts + B) * 6).astype(np.float32)
+    ne = rng.rand(B) > 0.5
+    a, b = P.get_packed_rewards(0.05, 3.0, t(lp), t(rf), t(score), t(cu), t(ne), True)
+    ra, rb = O.packed_rewards(0.05, 3.0, lp, rf, score, cu, ne, True)
+    assert np.array_equal(a.cpu().numpy(), ra) and np.array_equal(b.cpu().numpy(), rb)
+    for delta in (False, True):
+        c, d = P.get_packed_reward_dense(0.05, 3.0, t(lp), t(rf), t(dense), t(cu), t(ne).float(), delta)
+        rc, rd = O.packed_rewards(0.05, 3.0, lp, rf, dense, cu, dense=True, reward_delta=delta)
+        assert np.array_equal(c.cpu().numpy(), rc) and np.array_equal(d.cpu().numpy(), rd)

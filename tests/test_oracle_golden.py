@@ -269,3 +269,15 @@ def test_compute_advantages_oracle_vs_reference():
                 assert np.array_equal(r["advantages"], outs["advantages"])
         n += 1
     assert n >= 7
+
+
+def test_packed_rewards_oracle_bit_exact_vs_reference():
+    z = H.load("packed_rewards.npz")
+    for k in range(int(z["n_cases"])):
+        kl_ctl, clip, mz, delta = [float(v) for v in z[f"c{k}_cfg"]]
+        a, b = O.packed_rewards(kl_ctl, clip, z[f"c{k}_lp"], z[f"c{k}_rf"], z[f"c{k}_score"], z[f"c{k}_cu"],
+                                z[f"c{k}_ne"], bool(mz))
+        assert np.array_equal(a, z[f"c{k}_kl"]) and np.array_equal(b, z[f"c{k}_tot"])
+        c, d = O.packed_rewards(kl_ctl, clip, z[f"c{k}_lp"], z[f"c{k}_rf"], z[f"c{k}_dense"], z[f"c{k}_cu"],
+                                dense=True, reward_delta=bool(delta))
+        assert np.array_equal(c, z[f"c{k}_dkl"]) and np.array_equal(d, z[f"c{k}_dtot"])
