@@ -140,9 +140,79 @@ __device__ __forceinline__ void warp_copy_vec(char* d, const char* s, int64_t n,
   }
 }
 
+// Source and destination disagree modulo 16: read ALIGNED 16-byte vectors around the source bytes and
+// funnel-shift neighbouring pairs into aligned 16-byte stores (instead of falling back to 8/4/2/1-byte
+// accesses).  kQ = whole words of the shift (0..3); the byte part r is a run-time funnel-shift amount.
+// The aligned reads touch up to 15 bytes outside [s, s+n), always inside a 16-byte block that also
+// holds requested bytes (so inside the same allocation).
+__device__ __forceinline__ uint4 shift_pair(const uint4& a, const uint4& b, unsigned int q, unsigned int rbits) {
+  // v[j] = w[j + q] for the 8 words w = (a, b), j = 0..4; q is warp-uniform
+  uint32_t v0 = a.x, v1 = a.y, v2 = a.z, v3 = a.w, v4 = b.x;
+  if (q & 1u) { v0 = v1; v1 = v2; v2 = v3; v3 = v4; v4 = b.y; }
+  if (q & 2u) {
+    const uint32_t n3 = (q & 1u) ? b.z : b.y, n4 = (q & 1u) ? b.w : b.z;
+    v0 = v2; v1 = v3; v2 = v4; v3 = n3; v4 = n4;
+  }
+  uint4 o;
+  o.x = __funnelshift_r(v0, v1, rbits);
+  o.y = __funnelshift_r(v1, v2, rbits);
+  o.z = __funnelshift_r(v2, v3, rbits);
+  o.w = __funnelshift_r(v3, v4, rbits);
+  return o;
+}
+
+__device__ __noinline__ void warp_copy_shifted(char* d, const char* s, int64_t n, int lane) {
+  int64_t head = (16 - (reinterpret_cast<uintptr_t>(d) & 15)) & 15;
+  if (head > n) head = n;
+  if (lane < head) d[lane] = s[lane];
+  d += head;
+  s += head;
+  n -= head;
+  const int64_t nv = n >> 4;
+  if (nv > 0) {
+    const unsigned int sh = static_cast<unsigned int>(reinterpret_cast<uintptr_t>(s) & 15);   // 1..15 here
+    const uint4* sa = reinterpret_cast<const uint4*>(s - sh);
+    uint4* dv = reinterpret_cast<uint4*>(d);
+    const unsigned int rbits = (sh & 3u) * 8u, q = sh >> 2;
+    // each aligned source vector is loaded ONCE: lane l holds vectors i, i+32, i+64, i+96 of a 128-vector
+    // batch and gets the successor of each from lane l+1 (lane 31: lane 0's next vector / one extra load)
+    constexpr int kU = 4;
+#pragma unroll 1
+    for (int64_t base = 0; base < nv; base += kU * 32) {
+      uint4 a[kU + 1];
+#pragma unroll
+      for (int u = 0; u < kU; ++u) {
+        a[u] = make_uint4(0, 0, 0, 0);
+        if (base + u * 32 + lane <= nv) a[u] = ld_stream<uint4>(sa + base + u * 32 + lane);
+      }
+      a[kU] = make_uint4(0, 0, 0, 0);
+      if (lane == 0 && base + kU * 32 <= nv) a[kU] = ld_stream<uint4>(sa + base + kU * 32);
+      const int src = (lane + 1) & 31;
+      uint4 nx[kU + 1];
+#pragma unroll
+      for (int u = 0; u <= kU; ++u) {
+        nx[u].x = __shfl_sync(0xffffffffu, a[u].x, src);
+        nx[u].y = __shfl_sync(0xffffffffu, a[u].y, src);
+        nx[u].z = __shfl_sync(0xffffffffu, a[u].z, src);
+        nx[u].w = __shfl_sync(0xffffffffu, a[u].w, src);
+      }
+#pragma unroll
+      for (int u = 0; u < kU; ++u) {
+        const int64_t i = base + u * 32 + lane;
+        const uint4 b = lane < 31 ? nx[u] : nx[u + 1];       // lane 31's successor is lane 0's next vector
+        if (i < nv) stg_stream_v4(dv + i, shift_pair(a[u], b, q, rbits));
+      }
+    }
+  }
+  const int64_t done = nv << 4;
+  const int64_t tail = n - done;
+  if (lane < tail) d[done + lane] = s[done + lane];
+}
+
 __device__ __forceinline__ void warp_copy(char* d, const char* s, int64_t n, int lane) {
   const uintptr_t diff = reinterpret_cast<uintptr_t>(d) - reinterpret_cast<uintptr_t>(s);
   if ((diff & 15) == 0) warp_copy_vec<uint4>(d, s, n, lane);
+  else if (n >= 256) warp_copy_shifted(d, s, n, lane);
   else if ((diff & 7) == 0) warp_copy_vec<uint2>(d, s, n, lane);
   else if ((diff & 3) == 0) warp_copy_vec<uint32_t>(d, s, n, lane);
   else if ((diff & 1) == 0) warp_copy_vec<uint16_t>(d, s, n, lane);
@@ -151,7 +221,7 @@ __device__ __forceinline__ void warp_copy(char* d, const char* s, int64_t n, int
 
 // kSlice: flat -> packed (slice_intervals); otherwise packed -> flat (set_intervals)
 template <bool kSlice>
-__global__ void __launch_bounds__(kCopyThreads)
+__global__ void __launch_bounds__(kCopyThreads, 2)
 interval_copy_kernel(const char* __restrict__ flat_in, char* __restrict__ flat_out,
                      const char* __restrict__ packed_in, char* __restrict__ packed_out,
                      const int64_t* __restrict__ iv, int64_t n, int64_t elem_size,
