@@ -108,3 +108,42 @@ def test_invalid_tables_write_nothing():
         fp.set_intervals_any(new.half(), dst, torch.tensor([[0, 20]], dtype=torch.long, device=D))
     with pytest.raises(RuntimeError):
         fp.slice_intervals_any(src, torch.tensor([[0, 20]], dtype=torch.int32, device=D), 20)
+
+
+def test_every_byte_shift_long_pieces():
+    """1-byte elements, pieces of 256..6000 bytes whose source and destination offsets take every
+    relative shift 0..15 (the funnel-shift path and its head / tail handling), gather and scatter; pieces
+    end flush against the end of the buffers (the aligned over-read stays inside the last 16-byte block)."""
+    from areal_b200 import flatten_param as fp
+    rng = np.random.RandomState(17)
+    n = 1 << 22
+    src = rng.randint(0, 256, n, dtype=np.uint8)
+    starts, ends, pos = [], [], 3
+    while True:
+        size = int(rng.randint(256, 6000))
+        if pos + size > n:
+            break
+        starts.append(pos)
+        ends.append(pos + size)
+        pos += size + int(rng.randint(0, 37))
+    starts.append(n - 1000 - 5)             # last piece ends exactly at the end of the flat buffer
+    ends.append(n)
+    iv = np.stack([np.array(starts), np.array(ends)], 1).astype(np.int64)
+    rng.shuffle(iv)
+    shifts = set()
+    off = 0
+    for s, e in iv:
+        shifts.add((off - s) & 15)
+        off += e - s
+    assert shifts == set(range(16))
+    want = C.slice_intervals(src, iv)
+    tsrc = torch.from_numpy(src).to(D)
+    tiv = torch.from_numpy(iv).to(D)
+    out = fp.slice_intervals_any(tsrc, tiv, want.shape[0])
+    assert np.array_equal(out.cpu().numpy(), want)
+    new = rng.randint(0, 256, want.shape[0], dtype=np.uint8)
+    dst = torch.from_numpy(src.copy()).to(D)
+    fp.set_intervals_any(torch.from_numpy(new).to(D), dst, tiv)
+    ref = src.copy()
+    C.set_intervals(new, ref, iv)
+    assert np.array_equal(dst.cpu().numpy(), ref)
