@@ -54,9 +54,6 @@ __device__ __forceinline__ uint32_t map_to_rank(const void* local_ptr, uint32_t 
   asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(smem_u32(local_ptr)), "r"(target_rank));
   return remote;
 }
-__device__ __forceinline__ void st_cluster_f32(uint32_t remote, float v) {
-  asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(remote), "f"(v) : "memory");
-}
 // 4-byte store into another CTA's shared memory that also counts 4 bytes on that CTA's mbarrier
 // (no release fence needed: the receiver sees the data once its barrier phase completes)
 __device__ __forceinline__ void st_async_f32(uint32_t remote_addr, float v, uint32_t remote_bar) {

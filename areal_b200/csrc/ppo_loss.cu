@@ -22,7 +22,6 @@ __device__ __forceinline__ void block_finalize(float sum, float cnt, void* works
                                                float* loss_out, float* inv_count_out,
                                                bool guard_zero, double fixed_count) {
   __shared__ float ssum[kThreads / 32], scnt[kThreads / 32];
-  __shared__ unsigned int last_sm;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   sum = warp_sum(sum);
   cnt = warp_sum(cnt);
