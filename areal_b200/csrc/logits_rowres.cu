@@ -31,7 +31,7 @@ constexpr int kGroupThreads = kGroupWarps * 32;      // 256
 constexpr int kRRThreads = 2 * kGroupThreads + 64;   // group A (stats) + group B (gradient) + producer + exchange warps
 constexpr int kMaxCluster = 8;
 constexpr int kTmaPiece = 16384;
-constexpr int kMaxBuf = 3;
+constexpr int kMaxBuf = 6;
 
 __device__ __forceinline__ uint32_t cluster_ctarank() {
   uint32_t r;
