@@ -254,6 +254,39 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize(dev)
 
+    def graph_replay(mode, steps):
+        """The same step captured once in a CUDA graph and replayed: what a trainer that graphs its
+        post-processing pays per step (no per-launch host work).  N=1 only; reported beside `value`."""
+        def step():
+            P.cugae1d_nolp_misalign_func(b["rewards"], b["values"], b["cu_seqlens"], b["bootstrap"], GAMMA, LAM)
+            logits.grad = None
+            loss, st = F.fused_actor_loss(logits, b["labels"], TEMPERATURE, b["prox_logp"], b["old_logp"],
+                                          b["advantages"], b["loss_mask"],
+                                          loss_scale=loss_scale if mode == "single" else None, **CFG)
+            (loss * loss_scale[0]).backward()
+            return loss
+        side = torch.cuda.Stream(dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):
+            for _ in range(3):
+                step()
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            loss = step()
+        for _ in range(3):
+            g.replay()
+        torch.cuda.synchronize(dev)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            g.replay()
+        e1.record()
+        torch.cuda.synchronize(dev)
+        ms = e0.elapsed_time(e1) / steps
+        return {"ms_per_step": ms, "tokens_per_s": T / (ms * 1e-3), "steps": steps, "loss": float(loss.detach())}
+
     W = max(args.warmup, 3)
     main = timed_loop(args.mode, args.steps, W, True)
     other_mode = "twopass" if args.mode == "single" else "single"
@@ -261,6 +294,12 @@ def run_ours(args):
     single, twopass = (main, other) if args.mode == "single" else (other, main)
     ms_step = main["ms_step"]
     value = world * T / (ms_step * 1e-3)
+    graph = None
+    if world == 1 and os.environ.get("BENCH_NO_GRAPH") != "1":
+        try:
+            graph = graph_replay(args.mode, max(3, min(args.steps, 30)))
+        except Exception as exc:            # reported, never fatal: the eager loop above is the headline
+            graph = {"error": str(exc)[:200]}
     spreads = main["spreads"]
     host_ms = main["host_ms"]
 
@@ -329,7 +368,9 @@ def run_ours(args):
                    "loss_cfg": {k: v for k, v in CFG.items()}, "temperature": TEMPERATURE},
         "roofline": roofline, "single_pass": roof_single, "two_pass": roof_two, "roofline_gae": roof_gae,
         "mode": args.mode,
-        "e2e": e2e, "gpu_launches": 3 * args.steps, "clocks": clocks, "host_enqueue_ms_per_step": host_ms,
+        # our kernels per step: gae1d_prep + gae1d + (fused_rowres + rescale_if_needed | logits_fwd + scale + logits_bwd)
+        "e2e": e2e, "gpu_launches": (4 if args.mode == "single" else 5) * args.steps, "clocks": clocks,
+        "host_enqueue_ms_per_step": host_ms, "graph_replay": graph,
         "kernel_ms_spread": spreads,
         "loss": loss_value,
     }
