@@ -25,34 +25,43 @@ constexpr int kScanThreads = 1024;
 constexpr int kCopyThreads = 256;
 constexpr int kCopyWarps = kCopyThreads / 32;
 
-// workspace: int64 status[2] | int64 off[N + 1]   (byte offsets into the packed buffer)
+constexpr int64_t kShiftMinBytes = 256;   // shorter misaligned pieces keep the narrow-vector path
+
+// workspace: int64 status[2] | int64 off[N + 1] (byte offsets into the packed buffer) | int64 any_shift
+// any_shift != 0: some interval of >= 256 bytes has flat and packed addresses that disagree modulo 16,
+// i.e. the second (funnel-shift) copy kernel has work to do.
 __global__ void __launch_bounds__(kScanThreads)
 interval_scan_kernel(const int64_t* __restrict__ iv, int64_t n, int64_t elem_size,
-                     int64_t flat_numel, int64_t packed_numel, int64_t* __restrict__ ws) {
+                     int64_t flat_numel, int64_t packed_numel, int64_t* __restrict__ ws,
+                     uint64_t flat_base, uint64_t packed_base) {
   __shared__ int64_t warp_sums[32];
   __shared__ int64_t base_sm;
   __shared__ int bad_sm;
+  __shared__ int shift_sm;
   int64_t* status = ws;
   int64_t* off = ws + 2;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (tid == 0) {
     base_sm = 0;
     bad_sm = 0;
+    shift_sm = 0;
   }
   __syncthreads();
   constexpr int kPer = 4;
   for (int64_t start = 0; start < n; start += int64_t(kScanThreads) * kPer) {
-    int64_t sz[kPer];
+    int64_t sz[kPer], st0[kPer];
     int64_t local = 0;
     bool bad = false;
 #pragma unroll
     for (int k = 0; k < kPer; ++k) {
       const int64_t i = start + int64_t(tid) * kPer + k;
       sz[k] = 0;
+      st0[k] = 0;
       if (i < n) {
         const longlong2 se = reinterpret_cast<const longlong2*>(iv)[i];
         if (se.x < 0 || se.y < se.x || se.y > flat_numel) bad = true;
         else sz[k] = (se.y - se.x) * elem_size;
+        st0[k] = se.x * elem_size;
       }
       local += sz[k];
     }
@@ -82,6 +91,8 @@ interval_scan_kernel(const int64_t* __restrict__ iv, int64_t n, int64_t elem_siz
     for (int k = 0; k < kPer; ++k) {
       const int64_t i = start + int64_t(tid) * kPer + k;
       if (i < n) off[i] = run;
+      if (sz[k] >= kShiftMinBytes && (((flat_base + uint64_t(st0[k])) - (packed_base + uint64_t(run))) & 15u) != 0)
+        shift_sm = 1;
       run += sz[k];
     }
     __syncthreads();
@@ -95,6 +106,7 @@ interval_scan_kernel(const int64_t* __restrict__ iv, int64_t n, int64_t elem_siz
     else if (base_sm != packed_numel * elem_size) st = 2;
     status[0] = st;
     status[1] = base_sm;
+    off[n + 1] = shift_sm;
   }
 }
 
@@ -161,7 +173,7 @@ __device__ __forceinline__ uint4 shift_pair(const uint4& a, const uint4& b, unsi
   return o;
 }
 
-__device__ __noinline__ void warp_copy_shifted(char* d, const char* s, int64_t n, int lane) {
+__device__ __forceinline__ void warp_copy_shifted(char* d, const char* s, int64_t n, int lane) {
   int64_t head = (16 - (reinterpret_cast<uintptr_t>(d) & 15)) & 15;
   if (head > n) head = n;
   if (lane < head) d[lane] = s[lane];
@@ -176,7 +188,7 @@ __device__ __noinline__ void warp_copy_shifted(char* d, const char* s, int64_t n
     const unsigned int rbits = (sh & 3u) * 8u, q = sh >> 2;
     // each aligned source vector is loaded ONCE: lane l holds vectors i, i+32, i+64, i+96 of a 128-vector
     // batch and gets the successor of each from lane l+1 (lane 31: lane 0's next vector / one extra load)
-    constexpr int kU = 4;
+    constexpr int kU = 8;
 #pragma unroll 1
     for (int64_t base = 0; base < nv; base += kU * 32) {
       uint4 a[kU + 1];
@@ -212,16 +224,22 @@ __device__ __noinline__ void warp_copy_shifted(char* d, const char* s, int64_t n
 __device__ __forceinline__ void warp_copy(char* d, const char* s, int64_t n, int lane) {
   const uintptr_t diff = reinterpret_cast<uintptr_t>(d) - reinterpret_cast<uintptr_t>(s);
   if ((diff & 15) == 0) warp_copy_vec<uint4>(d, s, n, lane);
-  else if (n >= 256) warp_copy_shifted(d, s, n, lane);
   else if ((diff & 7) == 0) warp_copy_vec<uint2>(d, s, n, lane);
   else if ((diff & 3) == 0) warp_copy_vec<uint32_t>(d, s, n, lane);
   else if ((diff & 1) == 0) warp_copy_vec<uint16_t>(d, s, n, lane);
   else warp_copy_vec<uint8_t>(d, s, n, lane);
 }
 
-// kSlice: flat -> packed (slice_intervals); otherwise packed -> flat (set_intervals)
-template <bool kSlice>
-__global__ void __launch_bounds__(kCopyThreads, 2)
+__device__ __forceinline__ bool takes_shift_path(const char* d, const char* s, int64_t n) {
+  return n >= kShiftMinBytes && ((reinterpret_cast<uintptr_t>(d) - reinterpret_cast<uintptr_t>(s)) & 15) != 0;
+}
+
+// kSlice: flat -> packed (slice_intervals); otherwise packed -> flat (set_intervals).
+// Two launches share the chunking: kShifted = false moves every piece except the long misaligned ones
+// (its code and register budget are those of the plain vector copy); kShifted = true moves exactly
+// those, and returns at once when the scan found none.
+template <bool kSlice, bool kShifted>
+__global__ void __launch_bounds__(kCopyThreads)
 interval_copy_kernel(const char* __restrict__ flat_in, char* __restrict__ flat_out,
                      const char* __restrict__ packed_in, char* __restrict__ packed_out,
                      const int64_t* __restrict__ iv, int64_t n, int64_t elem_size,
@@ -229,6 +247,7 @@ interval_copy_kernel(const char* __restrict__ flat_in, char* __restrict__ flat_o
   const int64_t* status = ws;
   const int64_t* off = ws + 2;
   if (status[0] != 0) return;   // invalid table: touch nothing (status stays readable by the host)
+  if (kShifted && off[n + 1] == 0) return;
   const int lane = threadIdx.x & 31;
   const int64_t total = off[n];
   const int64_t gwarp = int64_t(blockIdx.x) * kCopyWarps + (threadIdx.x >> 5);
@@ -248,8 +267,13 @@ interval_copy_kernel(const char* __restrict__ flat_in, char* __restrict__ flat_o
   while (pos < end) {
     const int64_t piece_end = k_end < end ? k_end : end;
     const int64_t fpos = iv[2 * k] * elem_size + (pos - k_off);
-    if (kSlice) warp_copy(packed_out + pos, flat_in + fpos, piece_end - pos, lane);
-    else warp_copy(flat_out + fpos, packed_in + pos, piece_end - pos, lane);
+    char* d = kSlice ? packed_out + pos : flat_out + fpos;
+    const char* s = kSlice ? flat_in + fpos : packed_in + pos;
+    const int64_t len = piece_end - pos;
+    if (takes_shift_path(d, s, len) == kShifted) {
+      if (kShifted) warp_copy_shifted(d, s, len, lane);
+      else warp_copy(d, s, len, lane);
+    }
     pos = piece_end;
     while (pos == k_end && k + 1 < n) {
       ++k;
@@ -261,15 +285,17 @@ interval_copy_kernel(const char* __restrict__ flat_in, char* __restrict__ flat_o
 
 }  // namespace
 
-int64_t interval_workspace_bytes(int64_t n) { return (n + 3) * int64_t(sizeof(int64_t)); }
+int64_t interval_workspace_bytes(int64_t n) { return (n + 4) * int64_t(sizeof(int64_t)); }
 
 int launch_interval_copy(bool slice, const void* flat_in, void* flat_out, const void* packed_in,
                          void* packed_out, const int64_t* intervals, int64_t n, int64_t elem_size,
                          int64_t flat_numel, int64_t packed_numel, void* workspace,
                          cudaStream_t stream) {
   int64_t* ws = reinterpret_cast<int64_t*>(workspace);
-  interval_scan_kernel<<<1, kScanThreads, 0, stream>>>(intervals, n, elem_size, flat_numel,
-                                                       packed_numel, ws);
+  const uint64_t flat_base = reinterpret_cast<uint64_t>(slice ? flat_in : flat_out);
+  const uint64_t packed_base = reinterpret_cast<uint64_t>(slice ? packed_out : packed_in);
+  interval_scan_kernel<<<1, kScanThreads, 0, stream>>>(intervals, n, elem_size, flat_numel, packed_numel, ws,
+                                                       flat_base, packed_base);
   int rc = check_launch("interval_scan");
   if (rc) return rc;
   const int64_t total = packed_numel * elem_size;
@@ -281,14 +307,21 @@ int launch_interval_copy(bool slice, const void* flat_in, void* flat_out, const 
   chunk = (chunk + 15) & ~int64_t(15);
   const int64_t nwarps = (total + chunk - 1) / chunk;
   const unsigned int grid = static_cast<unsigned int>((nwarps + kCopyWarps - 1) / kCopyWarps);
-  if (slice)
-    interval_copy_kernel<true><<<grid, kCopyThreads, 0, stream>>>(
-        reinterpret_cast<const char*>(flat_in), nullptr, nullptr, reinterpret_cast<char*>(packed_out),
-        intervals, n, elem_size, ws, chunk);
-  else
-    interval_copy_kernel<false><<<grid, kCopyThreads, 0, stream>>>(
-        nullptr, reinterpret_cast<char*>(flat_out), reinterpret_cast<const char*>(packed_in), nullptr,
-        intervals, n, elem_size, ws, chunk);
+  const char* fi = reinterpret_cast<const char*>(flat_in);
+  char* fo = reinterpret_cast<char*>(flat_out);
+  const char* pi = reinterpret_cast<const char*>(packed_in);
+  char* po = reinterpret_cast<char*>(packed_out);
+  if (slice) {
+    interval_copy_kernel<true, false><<<grid, kCopyThreads, 0, stream>>>(fi, nullptr, nullptr, po, intervals, n,
+                                                                         elem_size, ws, chunk);
+    interval_copy_kernel<true, true><<<grid, kCopyThreads, 0, stream>>>(fi, nullptr, nullptr, po, intervals, n,
+                                                                        elem_size, ws, chunk);
+  } else {
+    interval_copy_kernel<false, false><<<grid, kCopyThreads, 0, stream>>>(nullptr, fo, pi, nullptr, intervals, n,
+                                                                          elem_size, ws, chunk);
+    interval_copy_kernel<false, true><<<grid, kCopyThreads, 0, stream>>>(nullptr, fo, pi, nullptr, intervals, n,
+                                                                         elem_size, ws, chunk);
+  }
   return check_launch("interval_copy");
 }
 
