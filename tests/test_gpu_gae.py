@@ -155,6 +155,39 @@ def test_gae1d_large_batch(odd):
         assert np.array_equal(adv2.cpu().numpy(), outs[0][0]) and np.array_equal(ret2.cpu().numpy(), outs[0][1])
 
 
+def test_gae1d_alternating_sizes_share_a_workspace():
+    """Small and large batches alternate on the same cached workspace (2 to 300 tiles, ragged last
+    tiles, one long sequence spanning every tile); each is checked against the oracle, twice in a row."""
+    rng = np.random.RandomState(77)
+    for ntok in (2 * 2048 + 1, 300 * 2048 - 5, 64 * 2048, 2049, 65 * 2048, 64 * 2048 - 7, 5000, 63 * 2048 + 9):
+        if ntok % 3 == 0:
+            lens = np.array([ntok])                                  # one sequence across all tiles
+        else:
+            lens = []
+            left = ntok
+            while left > 0:
+                n = min(left, int(rng.randint(1, 5000)))
+                lens.append(n)
+                left -= n
+            lens = np.array(lens)
+        cu = np.concatenate([[0], np.cumsum(lens)]).astype(np.int32)
+        B, T = len(lens), int(cu[-1])
+        r = rng.randn(T).astype(np.float32)
+        v = rng.randn(T + B).astype(np.float32)
+        boot = rng.rand(B) > 0.5
+        a_ref, r_ref = C.gae1d_nolp_misalign(r, v, cu, boot, 0.9999, 0.97)
+        a64, _ = O.gae1d_nolp_misalign_f64(r, v, cu, boot, 0.9999, 0.97)
+        first = None
+        for _ in range(2):
+            adv, ret = run1d(r, v, cu, boot, 0.9999, 0.97)
+            assert per_seq_rel(adv, a64, cu) <= 2 ** -23, ntok
+            assert per_seq_rel(adv, a_ref, cu) <= H.TOL_GAE * 5 and per_seq_rel(ret, r_ref, cu) <= H.TOL_GAE * 5, ntok
+            if first is None:
+                first = (adv, ret)
+            else:
+                assert np.array_equal(adv, first[0]) and np.array_equal(ret, first[1]), ntok
+
+
 def test_gae1d_inputs_untouched_and_checks():
     from areal_b200 import ppo_functional as P
     d = dev()
