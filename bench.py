@@ -404,15 +404,33 @@ def run_e2e(torch, dist, F, P, dev, b, world, steps, mode="single"):
         h = torch.empty(t.shape, dtype=t.dtype, device="cpu", pin_memory=True)
         h.copy_(t)
         host[k] = h
-    dst = {k: torch.empty_like(b[k].detach()) for k in host}
+    # two device-side input sets: step i's host->device copies run on a copy stream while step i-1
+    # computes (what a trainer streaming micro-batches from host memory does); every byte of every
+    # step is still copied inside the timed region
+    dst2 = [{k: torch.empty_like(b[k].detach()) for k in host} for _ in range(2)]
     out_host = {k: torch.empty(T, dtype=torch.float32, pin_memory=True) for k in ("logp", "entropy", "adv", "ret")}
     loss_host = torch.empty((), dtype=torch.float32, pin_memory=True)
     h2d = sum(h.numel() * h.element_size() for h in host.values())
     d2h = 4 + sum(h.numel() * 4 for h in out_host.values())
+    copy_stream = torch.cuda.Stream(dev)
+    main_stream = torch.cuda.current_stream(dev)
+    copied = [torch.cuda.Event() for _ in range(2)]
+    consumed = [torch.cuda.Event() for _ in range(2)]
+    for e in consumed:
+        e.record(main_stream)
 
-    def step():
-        for k in host:
-            dst[k].copy_(host[k], non_blocking=True)
+    def upload(i):
+        s = i & 1
+        copy_stream.wait_event(consumed[s])           # the compute that last read this set is done
+        with torch.cuda.stream(copy_stream):
+            for k in host:
+                dst2[s][k].copy_(host[k], non_blocking=True)
+            copied[s].record(copy_stream)
+
+    def compute(i):
+        s = i & 1
+        dst = dst2[s]
+        main_stream.wait_event(copied[s])
         x = dst["logits"].requires_grad_()
         adv, ret = P.cugae1d_nolp_misalign_func(dst["rewards"], dst["values"], dst["cu_seqlens"], dst["bootstrap"], GAMMA, LAM)
         loss, st = F.fused_actor_loss(x, dst["labels"], TEMPERATURE, dst["prox_logp"], dst["old_logp"],
@@ -426,17 +444,23 @@ def run_e2e(torch, dist, F, P, dev, b, world, steps, mode="single"):
         out_host["ret"].copy_(ret, non_blocking=True)
         x.grad = None
         dst["logits"] = x.detach()
+        consumed[s].record(main_stream)
 
-    for _ in range(2):
-        step()
+    def run(n):
+        upload(0)
+        for i in range(n):
+            if i + 1 < n:
+                upload(i + 1)
+            compute(i)
+
+    run(2)
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize(dev)
     e0 = torch.cuda.Event(enable_timing=True)
     e1 = torch.cuda.Event(enable_timing=True)
     e0.record()
-    for _ in range(steps):
-        step()
+    run(steps)
     e1.record()
     if world > 1:
         dist.barrier()
@@ -448,7 +472,8 @@ def run_e2e(torch, dist, F, P, dev, b, world, steps, mode="single"):
         ms = float(mt.item())
     return {"value": world * T / (ms * 1e-3), "unit": "tokens/s", "h2d_bytes_per_step": int(h2d),
             "d2h_bytes_per_step": int(d2h), "ms_per_step": ms, "steps": steps,
-            "note": "dominated by the 4.98 GB host->device copy of the logits over PCIe"}
+            "note": "dominated by the 4.98 GB host->device copy of the logits over PCIe; copies of step i+1 overlap "
+                    "the kernels of step i (two device-side input sets, copy stream)"}
 
 
 def cpu_baseline(sample_rows=1024, steps=2, warmup=1):
