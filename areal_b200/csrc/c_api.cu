@@ -704,6 +704,23 @@ AREAL_B200_API int64_t areal_b200_merge_intervals(const uint64_t* iv, int64_t n,
   return k;
 }
 
+AREAL_B200_API int areal_b200_rms_update(const double* partials, int64_t n_partials, void* state,
+                                         int state_is_f64, int mode, double beta, void* stream) {
+  AB_REQUIRE(partials && state, "null pointer");
+  AB_REQUIRE(n_partials >= 1, "rms_update: need at least one partial row");
+  AB_REQUIRE(mode == 0 || mode == 1, "rms_update: mode must be 0 (exponential) or 1 (moving average)");
+  return launch_rms_update(partials, n_partials, state, state_is_f64, mode, beta, static_cast<cudaStream_t>(stream));
+}
+
+AREAL_B200_API int areal_b200_rms_apply(const float* x, int64_t N, const void* state, int state_is_f64,
+                                        int mode, double eps, int denormalize, float* out, void* stream) {
+  AB_REQUIRE(N >= 0, "negative size");
+  if (N == 0) return kOk;
+  AB_REQUIRE(x && state && out, "null pointer");
+  AB_REQUIRE(mode == 0 || mode == 1, "rms_apply: mode must be 0 (exponential) or 1 (moving average)");
+  return launch_rms_apply(x, N, state, state_is_f64, mode, eps, denormalize, out, static_cast<cudaStream_t>(stream));
+}
+
 AREAL_B200_API int areal_b200_packed_rewards(const float* log_probs, const float* ref_log_probs,
                                              const float* score, const int32_t* short1cu_seqlens,
                                              const uint8_t* seq_no_eos, int64_t total_short_tokens,

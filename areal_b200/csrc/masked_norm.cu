@@ -200,6 +200,68 @@ unsigned int grid_1d(int64_t N) {
   return static_cast<unsigned int>(need < 1 ? 1 : (need < cap ? need : cap));
 }
 
+// ---- legacy running value statistics (realhf/impl/model/modules/rms.py) ---------------------------
+// state (module dtype R = double or float): [0] mean, [1] mean of squares, [2] debiasing term
+// (exponential) or accumulated denominator (moving average).  One thread: the update is scalar work;
+// what matters is that it stays on the device (no .item()) between the moments kernel and the next use.
+template <typename R>
+__global__ void rms_update_kernel(const double* __restrict__ partials, int64_t P, R* __restrict__ state, int mode,
+                                  double beta) {
+  if (blockIdx.x != 0 || threadIdx.x != 0) return;
+  double factor = 0.0, x_sum = 0.0, x_sum_sq = 0.0;
+  for (int64_t i = 0; i < P; ++i) {                 // fixed order
+    factor += partials[3 * i + 0];
+    x_sum += partials[3 * i + 1];
+    x_sum_sq += partials[3 * i + 2];
+  }
+  const R f = R(factor), sx = R(x_sum), sq = R(x_sum_sq);
+  if (mode == 0) {                                  // rms.py:74-83
+    const R b = R(beta), omb = R(1.0 - beta);
+    const R batch_mean = sx / f, batch_sq_mean = sq / f;
+    state[0] = b * state[0] + batch_mean * omb;
+    state[1] = b * state[1] + batch_sq_mean * omb;
+    state[2] = b * state[2] + R(1.0) - b;
+  } else {                                          // rms.py:164-170
+    const R acc = state[2];
+    state[0] = (acc * state[0] + sx) / (acc + f);
+    state[1] = (acc * state[1] + sq) / (acc + f);
+    state[2] = acc + f;
+  }
+}
+
+template <typename R>
+__device__ __forceinline__ void rms_mean_std(const R* state, int mode, R eps, R& mean, R& std_) {
+  R m = state[0], msq = state[1];
+  if (mode == 0) {                                  // rms.py:86-90
+    R d = state[2];
+    d = d < eps ? eps : d;                          // clamp(min=eps)
+    m = m / d;
+    msq = msq / d;
+  }
+  R var = msq - m * m;                              // :89 / :176
+  var = var < R(1e-2) ? R(1e-2) : var;              // clamp(min=1e-2); NaN stays NaN
+  mean = m;
+  std_ = sqrt(var);
+}
+
+template <typename R, bool kDenorm>
+__global__ void __launch_bounds__(kThreads)
+rms_apply_kernel(const float* __restrict__ x, int64_t N, const R* __restrict__ state, int mode, R eps,
+                 float* __restrict__ out) {
+  R mean, std_;
+  rms_mean_std<R>(state, mode, eps, mean, std_);
+  for (int64_t i = blockIdx.x * int64_t(kThreads) + threadIdx.x; i < N; i += int64_t(gridDim.x) * kThreads) {
+    const R v = R(x[i]);
+    if (kDenorm) {
+      out[i] = float(v * std_ + mean);              // rms.py:104-108
+    } else {
+      R y = (v - mean) / std_;                      // rms.py:95-101
+      y = y < R(-5) ? R(-5) : (y > R(5) ? R(5) : y);
+      out[i] = float(y);
+    }
+  }
+}
+
 }  // namespace
 
 int64_t norm_num_partials(int64_t group_elems) {
@@ -235,6 +297,29 @@ int launch_masked_normalization_apply(const float* x, const float* mask, int64_t
   if (N == 0) return kOk;
   masked_normalization_apply_kernel<<<grid_1d(N), kThreads, 0, stream>>>(x, mask, N, stats, unbiased, eps, out);
   return check_launch("masked_normalization apply");
+}
+
+int launch_rms_update(const double* partials, int64_t P, void* state, int state_is_f64, int mode, double beta,
+                      cudaStream_t stream) {
+  if (state_is_f64) rms_update_kernel<double><<<1, 32, 0, stream>>>(partials, P, static_cast<double*>(state), mode, beta);
+  else rms_update_kernel<float><<<1, 32, 0, stream>>>(partials, P, static_cast<float*>(state), mode, beta);
+  return check_launch("rms update");
+}
+
+int launch_rms_apply(const float* x, int64_t N, const void* state, int state_is_f64, int mode, double eps,
+                     int denormalize, float* out, cudaStream_t stream) {
+  if (N == 0) return kOk;
+  const unsigned int grid = grid_1d(N);
+  if (state_is_f64) {
+    const double* st = static_cast<const double*>(state);
+    if (denormalize) rms_apply_kernel<double, true><<<grid, kThreads, 0, stream>>>(x, N, st, mode, eps, out);
+    else rms_apply_kernel<double, false><<<grid, kThreads, 0, stream>>>(x, N, st, mode, eps, out);
+  } else {
+    const float* st = static_cast<const float*>(state);
+    if (denormalize) rms_apply_kernel<float, true><<<grid, kThreads, 0, stream>>>(x, N, st, mode, float(eps), out);
+    else rms_apply_kernel<float, false><<<grid, kThreads, 0, stream>>>(x, N, st, mode, float(eps), out);
+  }
+  return check_launch("rms apply");
 }
 
 }  // namespace ab

@@ -35,4 +35,9 @@ int launch_norm_apply(const float* x, const float* mask, int64_t N, const NormMe
 int launch_masked_normalization_apply(const float* x, const float* mask, int64_t N, const double* stats,
                                       int unbiased, double eps, float* out, cudaStream_t stream);
 
+int launch_rms_update(const double* partials, int64_t P, void* state, int state_is_f64, int mode, double beta,
+                      cudaStream_t stream);
+int launch_rms_apply(const float* x, int64_t N, const void* state, int state_is_f64, int mode, double eps,
+                     int denormalize, float* out, cudaStream_t stream);
+
 }  // namespace ab

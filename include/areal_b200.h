@@ -340,6 +340,21 @@ AREAL_B200_API int areal_b200_set_intervals(const void* packed, int64_t packed_n
  * returns the number of merged intervals, or -1 on a null pointer. */
 AREAL_B200_API int64_t areal_b200_merge_intervals(const uint64_t* intervals, int64_t n, uint64_t* out);
 
+/* Legacy running value statistics.  Replaces the arithmetic of `ExponentialRunningMeanStd` /
+ * `MovingAverageRunningMeanStd` (realhf/impl/model/modules/rms.py:19-183): update = three reductions
+ * + ~10 scalar kernels there; here areal_b200_masked_moments (one group) followed by
+ * areal_b200_rms_update, and one elementwise launch for normalize / denormalize.
+ *   state: 3 values of the module dtype (state_is_f64 = 1: double, 0: float): mean, mean of squares,
+ *   and the debiasing term (mode 0, exponential) or the accumulated denominator (mode 1, moving
+ *   average).  partials f64[n_partials,3] as written by areal_b200_masked_moments (or one already
+ *   all-reduced row with n_partials = 1).
+ *   rms_apply: out = clip((x - mean) / std, -5, 5) or x * std + mean (denormalize = 1), computed in
+ *   the module dtype and rounded to f32; std = sqrt(max(mean_sq - mean^2, 1e-2)). */
+AREAL_B200_API int areal_b200_rms_update(const double* partials, int64_t n_partials, void* state,
+                                         int state_is_f64, int mode, double beta, void* stream);
+AREAL_B200_API int areal_b200_rms_apply(const float* x, int64_t N, const void* state, int state_is_f64,
+                                        int mode, double eps, int denormalize, float* out, void* stream);
+
 /* KL-regularised token rewards of the legacy packed path in ONE launch.  Replaces
  * `get_packed_rewards` (mode 0) and `get_packed_reward_dense` (mode 1; mode 2 = reward_delta)
  * (realhf/impl/model/utils/ppo_functional.py:228-289; 6 torch kernels, or a Python loop over the

@@ -665,3 +665,55 @@ def packed_rewards(kl_ctl, clip_reward_value, log_probs, ref_log_probs, score, s
         off += n
         off2 += n + 1
     return kl, tot
+
+
+# --------------------------------------------------------------------------------------------------
+# legacy running value statistics (realhf/impl/model/modules/rms.py)
+# --------------------------------------------------------------------------------------------------
+class RunningMeanStd:
+    """ExponentialRunningMeanStd (rms.py:19-109, exponential=True) / MovingAverageRunningMeanStd
+    (:112-183) in numpy, module dtype float64 (high_precision) or float32."""
+
+    def __init__(self, exponential=True, beta=0.999, epsilon=1e-5, high_precision=True):
+        self.dt = np.float64 if high_precision else np.float32
+        self.exp, self.beta, self.eps = exponential, self.dt(beta), self.dt(epsilon)
+        self.mean = self.dt(0)
+        self.mean_sq = self.dt(0)
+        self.aux = self.dt(0)          # debiasing term / accumulated denominator
+
+    def update(self, x, mask=None):
+        dt = self.dt
+        x = np.asarray(x).astype(dt)
+        if mask is None:
+            factor = dt(x.size)                                            # :57-58
+        else:
+            m = np.asarray(mask).astype(dt)
+            x = x * m                                                      # :60
+            factor = m.sum(dtype=dt)
+        s, sq = x.sum(dtype=dt), np.square(x).sum(dtype=dt)                # :63-64
+        if self.exp:
+            one = dt(1.0)
+            self.mean = self.beta * self.mean + (s / factor) * (one - self.beta)        # :77-79
+            self.mean_sq = self.beta * self.mean_sq + (sq / factor) * (one - self.beta)  # :80-82
+            self.aux = self.beta * self.aux + one - self.beta                            # :83-85
+        else:
+            self.mean = (self.aux * self.mean + s) / (self.aux + factor)                # :164-166
+            self.mean_sq = (self.aux * self.mean_sq + sq) / (self.aux + factor)          # :167-169
+            self.aux = self.aux + factor
+
+    def mean_std(self):
+        dt = self.dt
+        if self.exp:
+            d = max(self.aux, self.eps)                                    # :88-89
+            mean, msq = self.mean / d, self.mean_sq / d
+        else:
+            mean, msq = self.mean, self.mean_sq
+        return dt(mean), dt(np.sqrt(max(msq - mean * mean, dt(1e-2))))      # :90-91 / :175-177
+
+    def normalize(self, x):
+        mean, std = self.mean_std()
+        return np.clip((np.asarray(x).astype(self.dt) - mean) / std, -5, 5).astype(np.float32)   # :95-101
+
+    def denormalize(self, x):
+        mean, std = self.mean_std()
+        return (np.asarray(x).astype(self.dt) * std + mean).astype(np.float32)                   # :104-108

@@ -499,6 +499,38 @@ def gen_packed_rewards(pf):
     print("packed_rewards golden:", k, "cases")
 
 
+def gen_rms():
+    """ExponentialRunningMeanStd / MovingAverageRunningMeanStd (realhf/impl/model/modules/rms.py:19-183):
+    three updates (unmasked, masked, masked 2-D), then mean_std / normalize / denormalize."""
+    rms = R.load_realhf_rms()
+    g = torch.Generator().manual_seed(808)
+    xs = [torch.randn(5000, generator=g) * 3 + 1.5, torch.randn(777, generator=g) * 0.2 - 4.0,
+          torch.randn(64, 100, generator=g) * 10]
+    ms = [None, torch.rand(777, generator=g) > 0.4, torch.rand(64, 100, generator=g) > 0.7]
+    probe = torch.randn(3000, generator=g) * 8
+    z = {"probe": probe.numpy()}
+    for i, (x, m) in enumerate(zip(xs, ms)):
+        z[f"x{i}"] = x.numpy()
+        if m is not None:
+            z[f"m{i}"] = m.numpy()
+    k = 0
+    for cls in ("ExponentialRunningMeanStd", "MovingAverageRunningMeanStd"):
+        for hp in (True, False):
+            mod = getattr(rms, cls)(beta=0.9, epsilon=1e-5, high_precision=hp) if cls.startswith("Exp") else getattr(rms, cls)(high_precision=hp)
+            for step, (x, m) in enumerate(zip(xs, ms)):
+                mod.update(x, m)
+                mean, std = mod.mean_std()
+                z[f"c{k}_mean{step}"] = mean.double().numpy()
+                z[f"c{k}_std{step}"] = std.double().numpy()
+                z[f"c{k}_norm{step}"] = mod.normalize(probe).numpy()
+                z[f"c{k}_denorm{step}"] = mod.denormalize(probe).numpy()
+            z[f"c{k}_cfg"] = np.array([cls.startswith("Exp"), hp])
+            k += 1
+    z["n_cases"] = np.array(k)
+    np.savez_compressed(os.path.join(OUT, "rms.npz"), **z)
+    print("rms golden:", k, "cases")
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     assert R.available(), "needs /root/reference"
@@ -518,6 +550,7 @@ def main():
     gen_advantages()
     gen_grpo_stats()
     gen_packed_rewards(pf)
+    gen_rms()
 
 
 if __name__ == "__main__":

@@ -300,3 +300,23 @@ def load_areal_grpo_loss_fn():
               ppo_actor_loss_fn=af.ppo_actor_loss_fn, stats_tracker=st)
     exec(compile(ast.get_source_segment(src, node), "actor.py[grpo_loss_fn]", "exec"), ns)
     return ns["grpo_loss_fn"], st
+
+
+def load_realhf_rms():
+    """realhf/impl/model/modules/rms.py executed where it lies (stubs: realhf.base.constants with
+    current_device() = "cpu", realhf.base.logging)."""
+    import logging as _logging
+    names = ["realhf", "realhf.base", "realhf.base.constants", "realhf.base.logging"]
+    saved = {k: sys.modules.get(k) for k in names}
+    try:
+        const = _stub("realhf.base.constants", current_device=lambda: "cpu", data_parallel_group=lambda: None)
+        lg = _stub("realhf.base.logging", getLogger=lambda name=None: _logging.getLogger(name))
+        base = _stub("realhf.base", constants=const, logging=lg)
+        _stub("realhf", base=base)
+        return _load("realhf/impl/model/modules/rms.py", "_ref_realhf_rms")
+    finally:
+        for k, v in saved.items():
+            if v is None:
+                sys.modules.pop(k, None)
+            else:
+                sys.modules[k] = v

@@ -88,3 +88,44 @@ def test_pack_tensor_dict_golden_and_round_trip():
     assert torch.equal(back[am], data["logprobs"][am]) and bool((back[~am] == 0).all())
     hb = unpack_to_padded(out["hidden"], out["cu_seqlens"], S)
     assert torch.equal(hb[am], data["hidden"][am])
+
+
+def test_legacy_running_mean_std_vs_reference():
+    """ExponentialRunningMeanStd / MovingAverageRunningMeanStd, float64 and float32 state: after each of
+    three updates (no mask, 1-D mask, 2-D mask) mean/std and normalize/denormalize of a probe vector match
+    golden outputs of the unmodified reference modules; state_dict keys are the reference's mangled names."""
+    from areal_b200 import rms
+    z = H.load("rms.npz")
+    dev = torch.device("cuda:0")
+    probe = torch.from_numpy(z["probe"]).to(dev)
+    for k in range(int(z["n_cases"])):
+        exp, hp = [bool(v) for v in z[f"c{k}_cfg"]]
+        mod = rms.ExponentialRunningMeanStd(beta=0.9, epsilon=1e-5, high_precision=hp) if exp else \
+            rms.MovingAverageRunningMeanStd(high_precision=hp)
+        tol = 1e-12 if hp else 2e-6
+        for step in range(3):
+            x = torch.from_numpy(z[f"x{step}"]).to(dev)
+            m = torch.from_numpy(z[f"m{step}"]).to(dev) if f"m{step}" in z else None
+            mod.update(x, m)
+            mean, std = mod.mean_std()
+            assert mean.dtype == (torch.float64 if hp else torch.float32) and mean.shape == (1,)
+            np.testing.assert_allclose(mean.double().cpu().numpy(), z[f"c{k}_mean{step}"], rtol=tol, atol=tol)
+            np.testing.assert_allclose(std.double().cpu().numpy(), z[f"c{k}_std{step}"], rtol=tol, atol=tol)
+            n, d = mod.normalize(probe), mod.denormalize(probe)
+            assert n.dtype == torch.float32 and d.dtype == torch.float32
+            np.testing.assert_allclose(n.cpu().numpy(), z[f"c{k}_norm{step}"], rtol=2e-6, atol=2e-6)
+            np.testing.assert_allclose(d.cpu().numpy(), z[f"c{k}_denorm{step}"], rtol=2e-6, atol=2e-6)
+            if hp:                                   # same fp64 arithmetic: identical after the f32 rounding
+                assert (n.cpu().numpy() != z[f"c{k}_norm{step}"]).mean() < 1e-3
+        keys = set(mod.state_dict().keys())
+        cls = "ExponentialRunningMeanStd" if exp else "MovingAverageRunningMeanStd"
+        want = {f"_{cls}__mean", f"_{cls}__mean_sq"} | ({f"_{cls}__debiasing_term"} if exp else set())
+        assert keys == want, keys
+        # a checkpoint round trip keeps the kernels' buffer and the parameters tied together
+        clone = (rms.ExponentialRunningMeanStd(beta=0.9, epsilon=1e-5, high_precision=hp) if exp
+                 else rms.MovingAverageRunningMeanStd(high_precision=hp))
+        clone.load_state_dict(mod.state_dict())
+        if exp:
+            assert torch.equal(clone.normalize(probe), mod.normalize(probe))
+    with pytest.raises(NotImplementedError):
+        mod.forward(probe)

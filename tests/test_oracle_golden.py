@@ -281,3 +281,18 @@ def test_packed_rewards_oracle_bit_exact_vs_reference():
         c, d = O.packed_rewards(kl_ctl, clip, z[f"c{k}_lp"], z[f"c{k}_rf"], z[f"c{k}_dense"], z[f"c{k}_cu"],
                                 dense=True, reward_delta=bool(delta))
         assert np.array_equal(c, z[f"c{k}_dkl"]) and np.array_equal(d, z[f"c{k}_dtot"])
+
+
+def test_running_mean_std_oracle_vs_reference():
+    z = H.load("rms.npz")
+    for k in range(int(z["n_cases"])):
+        exp, hp = [bool(v) for v in z[f"c{k}_cfg"]]
+        mod = O.RunningMeanStd(exponential=exp, beta=0.9, epsilon=1e-5, high_precision=hp)
+        tol = 1e-13 if hp else 3e-6
+        for step in range(3):
+            mod.update(z[f"x{step}"], z[f"m{step}"] if f"m{step}" in z else None)
+            mean, std = mod.mean_std()
+            np.testing.assert_allclose(mean, z[f"c{k}_mean{step}"][0], rtol=tol, atol=tol)
+            np.testing.assert_allclose(std, z[f"c{k}_std{step}"][0], rtol=tol, atol=tol)
+            np.testing.assert_allclose(mod.normalize(z["probe"]), z[f"c{k}_norm{step}"], rtol=3e-6, atol=3e-6)
+            np.testing.assert_allclose(mod.denormalize(z["probe"]), z[f"c{k}_denorm{step}"], rtol=3e-6, atol=3e-6)
