@@ -129,3 +129,88 @@ def test_padded_gae_random_shapes():
         scale = np.maximum(1.0, np.abs(ra).max(-1, keepdims=True))
         assert float((np.abs(a.cpu().numpy() - ra) / scale).max()) <= 5 * H.TOL_GAE, (case, B, S)
         assert float((np.abs(rt.cpu().numpy() - rr) / np.maximum(scale, np.abs(rr).max(-1, keepdims=True))).max()) <= 5 * H.TOL_GAE
+
+
+def test_fused_actor_random_shapes_single_and_two_pass():
+    """fused_actor_loss with and without loss_scale (single-pass row-resident kernel / two-pass) on random
+    T, V (multiples of 8, so rows are 16-byte aligned), temperatures and clip settings: loss vs the fp64
+    oracle, the two paths against each other."""
+    from areal_b200 import functional as F
+    rng = np.random.RandomState(4242)
+    for case in range(16):
+        T = int(rng.randint(1, 400))
+        V = 8 * int(rng.choice([rng.randint(1, 64), rng.randint(64, 4000), rng.randint(4000, 19000)]))
+        temp = float(rng.choice([1.0, 0.8, 1.3]))
+        g = torch.Generator().manual_seed(1000 + case)
+        logits = (torch.randn(T, V, generator=g) * 2.5).bfloat16()
+        labels = torch.randint(0, V, (T,), generator=g)
+        lp_ref, *_ = O.gather_logprobs_entropy(logits.float().numpy(), labels.numpy(), temp)
+        prox = (torch.from_numpy(lp_ref) + 0.05 * torch.randn(T, generator=g)).float()
+        old = (torch.from_numpy(lp_ref) + 0.1 * torch.randn(T, generator=g)).float()
+        adv = torch.randn(T, generator=g)
+        mask = torch.rand(T, generator=g) > float(rng.choice([0.0, 0.3, 0.9]))
+        cfg = dict(eps_clip=float(rng.choice([0.1, 0.2, 0.4])), eps_clip_higher=rng.choice([None, 0.5]),
+                   c_clip=rng.choice([None, 3.0]), behav_imp_weight_cap=rng.choice([None, 2.0, 5.0]))
+        cfg = {k: (None if v is None else float(v)) for k, v in cfg.items()}
+        scale = float(rng.choice([1.0, 0.25, 0.01]))
+        res = {}
+        for path in ("single", "twopass"):
+            x = logits.to(D).requires_grad_()
+            loss, st = F.fused_actor_loss(x, labels.to(D), temp, prox.to(D), old.to(D), adv.to(D), mask.to(D),
+                                          loss_scale=scale if path == "single" else None, **cfg)
+            (loss * scale).backward()
+            res[path] = (float(loss.detach()), st["logprobs"].cpu().numpy(), x.grad.float().cpu().numpy())
+        want, _, coef = O.ppo_actor_loss(lp_ref, prox.numpy().astype(np.float64), old.numpy().astype(np.float64),
+                                         adv.numpy().astype(np.float64), cfg["eps_clip"], mask.numpy(),
+                                         eps_clip_higher=cfg["eps_clip_higher"], c_clip=cfg["c_clip"],
+                                         behav_imp_weight_cap=cfg["behav_imp_weight_cap"], dtype=np.float64)
+        for path in res:
+            assert abs(res[path][0] - want) <= 2e-3 * max(1.0, abs(want)), (case, path, T, V, res[path][0], want)
+            assert H.rel_err(res[path][1], lp_ref) <= H.TOL_LOGITS, (case, path)
+        assert np.allclose(res["single"][2], res["twopass"][2], rtol=2 ** -7, atol=1e-12), (case, T, V)
+
+
+def test_compute_advantages_random_configs():
+    import types
+    from areal_b200.actor import compute_advantages
+    rng = np.random.RandomState(31337)
+    for case in range(24):
+        B, S = int(rng.randint(1, 50)), int(rng.choice([1, 2, 3, 8, 16, 40, 512, 1000, 1024, rng.randint(2, 3000)]))
+        lens = rng.randint(0, S + 1, B)
+        am = np.arange(S)[None, :] < lens[:, None]
+        lm = am & (rng.rand(B, S) > 0.3)
+        logp = -rng.rand(B, S).astype(np.float32) * 5
+        ref = -rng.rand(B, S).astype(np.float32) * 5
+        val = rng.randn(B, S).astype(np.float32)
+        score = (rng.randn(B) * 4).astype(np.float32)
+        kl = str(rng.choice(["k1", "k2", "k3"]))
+        with_ref, with_val = bool(rng.rand() < 0.7), bool(rng.rand() < 0.7)
+        cfgv = dict(reward_bias=float(rng.choice([0.0, -0.5])), reward_scaling=float(rng.choice([1.0, 2.0])),
+                    reward_clip=float(rng.choice([20.0, 1.5])), kl_ctl=float(rng.choice([0.0, 0.1, 1.0])),
+                    discount=float(rng.choice([1.0, 0.99])), gae_lambda=float(rng.choice([1.0, 0.9])),
+                    mask_no_eos_with_zero=bool(rng.rand() < 0.5))
+        mdt = [torch.bool, torch.float32, torch.int64][case % 3]
+        data = dict(input_ids=torch.zeros(B, S, dtype=torch.long, device=D),
+                    attention_mask=torch.from_numpy(am).to(D).to(mdt), loss_mask=torch.from_numpy(lm).to(D).to(mdt),
+                    logprobs=torch.from_numpy(logp).to(D), rewards=torch.from_numpy(score).to(D))
+        if with_ref:
+            data["ref_logp"] = torch.from_numpy(ref).to(D)
+        if with_val:
+            data["values"] = torch.from_numpy(val).to(D)
+        actor = types.SimpleNamespace(
+            config=types.SimpleNamespace(use_decoupled_loss=True, recompute_logprob=True, overlong_reward_penalty=False),
+            kl_estimator=types.SimpleNamespace(kl_estimator=kl, apply_clamp=True), adv_norm=None, reward_norm=None, **cfgv)
+        compute_advantages(actor, data)
+        r = O.compute_advantages(score, lm, logp, am, ref_logp=ref if with_ref else None, values=val if with_val else None,
+                                 roll_logp=True, kl_estimator=kl, **cfgv)
+        for k in ("loss_mask", "logprobs"):
+            assert np.array_equal(data[k].cpu().numpy(), r[k]), (case, k)
+        if kl == "k3":
+            np.testing.assert_allclose(data["tot_rewards"].cpu().numpy(), r["tot_rewards"], rtol=1e-5, atol=1e-6)
+        else:
+            assert np.array_equal(data["kl_rewards"].cpu().numpy(), r["kl_rewards"]), case
+            assert np.array_equal(data["tot_rewards"].cpu().numpy(), r["tot_rewards"]), case
+        for k in ("advantages", "returns"):
+            got, want = data[k].cpu().numpy(), r[k]
+            scale = np.maximum(1.0, np.abs(want).max(-1, keepdims=True))
+            assert float((np.abs(got - want) / scale).max()) <= 10 * H.TOL_GAE, (case, k, B, S)
