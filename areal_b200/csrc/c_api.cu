@@ -704,6 +704,31 @@ AREAL_B200_API int64_t areal_b200_merge_intervals(const uint64_t* iv, int64_t n,
   return k;
 }
 
+AREAL_B200_API int64_t areal_b200_vocab_p2p_buffer_bytes(int64_t max_tokens) {
+  if (max_tokens < 0) return -1;
+  return 256 + 2 * 4 * max_tokens * int64_t(sizeof(float));
+}
+
+AREAL_B200_API int areal_b200_vocab_combine_p2p(void* const* peer_bases, int rank, int world_size,
+                                                int64_t T, int64_t max_tokens, int64_t epoch,
+                                                double temperature, int64_t timeout_cycles, float* logp,
+                                                float* entropy, float* row_max, float* ln_sumexp,
+                                                int* status, void* stream) {
+  AB_REQUIRE(world_size >= 1 && world_size <= 16, "vocab_combine_p2p: world size must be 1..16, got %d", world_size);
+  AB_REQUIRE(rank >= 0 && rank < world_size, "vocab_combine_p2p: rank %d out of range", rank);
+  AB_REQUIRE(T >= 0 && T <= max_tokens, "vocab_combine_p2p: T=%lld exceeds the buffer's %lld tokens",
+             static_cast<long long>(T), static_cast<long long>(max_tokens));
+  AB_REQUIRE(epoch >= 1, "vocab_combine_p2p: epochs start at 1");
+  AB_REQUIRE(temperature > 0.0, "temperature must be positive");
+  AB_REQUIRE(peer_bases && status, "null pointer");
+  AB_REQUIRE(T == 0 || (logp && row_max && ln_sumexp), "null output");
+  for (int r = 0; r < world_size; ++r) AB_REQUIRE(peer_bases[r] != nullptr, "vocab_combine_p2p: null peer buffer %d", r);
+  return launch_vocab_combine_p2p(peer_bases, rank, world_size, T, max_tokens, static_cast<int>(epoch & 1),
+                                  static_cast<unsigned int>(epoch), static_cast<float>(1.0 / temperature),
+                                  static_cast<long long>(timeout_cycles), logp, entropy, row_max, ln_sumexp, status,
+                                  static_cast<cudaStream_t>(stream));
+}
+
 AREAL_B200_API int areal_b200_rms_update(const double* partials, int64_t n_partials, void* state,
                                          int state_is_f64, int mode, double beta, void* stream) {
   AB_REQUIRE(partials && state, "null pointer");

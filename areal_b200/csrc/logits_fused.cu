@@ -546,6 +546,97 @@ __global__ void vocab_combine_kernel(const float* __restrict__ parts, int R, int
   ln_s_out[t] = ln_s;
 }
 
+// ---- cross-shard combine over NVLink peer memory (no all-gather) --------------------------------------
+// Every rank owns a symmetric buffer: uint32 flag[kMaxPeers] (256 B) | parts[2][4][Tmax] f32.  The partial
+// kernel of step e has written this rank's parts into slot e & 1 (same stream, already complete).  This
+// kernel (a) tells every peer "my parts of step e are there" with one release store per peer into THAT
+// peer's flag[my rank], (b) waits until all peers have said so here, (c) reads the R partial sets straight
+// out of the peers' memory and combines them in rank order -- bit-identical to vocab_combine_kernel.
+// Reuse of a slot two steps later needs no second handshake: a rank can only pass (b) of step e+1 after every
+// peer has launched its partial kernel of step e+1, i.e. after that peer's combine of step e has finished.
+constexpr int kMaxPeers = 16;
+struct PeerTable {
+  char* base[kMaxPeers];
+};
+constexpr int64_t kPeerHeaderBytes = 256;
+
+__device__ __forceinline__ unsigned int ld_acquire_sys_u32(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys_u32(unsigned int* p, unsigned int v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+// peer memory is cached in the local L1 only: read around it, or a slot's previous contents come back
+__device__ __forceinline__ float ld_peer_f32(const float* p) {
+  float v;
+  asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
+  return v;
+}
+
+__global__ void __launch_bounds__(256)
+vocab_combine_p2p_kernel(const PeerTable peers, int rank, int R, int64_t T, int64_t Tmax, int slot,
+                         unsigned int epoch, float inv_t, long long timeout_cycles, float* __restrict__ logp,
+                         float* __restrict__ entropy, float* __restrict__ row_max, float* __restrict__ ln_s_out,
+                         int* __restrict__ status) {
+  __shared__ int ok_sm;
+  if (blockIdx.x == 0 && threadIdx.x < R) {
+    __threadfence_system();
+    st_release_sys_u32(reinterpret_cast<unsigned int*>(peers.base[threadIdx.x]) + rank, epoch);
+  }
+  if (threadIdx.x == 0) {
+    const unsigned int* mine = reinterpret_cast<const unsigned int*>(peers.base[rank]);
+    const long long t0 = clock64();
+    int ok = 1;
+    for (int r = 0; r < R && ok; ++r) {
+      // epochs only grow; the signed difference survives wrap-around
+      while (static_cast<int>(ld_acquire_sys_u32(mine + r) - epoch) < 0) {
+        if (clock64() - t0 > timeout_cycles) {
+          ok = 0;
+          break;
+        }
+        __nanosleep(100);
+      }
+    }
+    if (!ok) atomicExch(status, 1);
+    ok_sm = ok;
+  }
+  __syncthreads();
+  if (!ok_sm) return;                       // a peer never arrived: outputs untouched, status says so
+  const int64_t t = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+  if (t >= T) return;
+  const float c2 = inv_t * kLog2e;
+  float m_r[kMaxPeers], s_r[kMaxPeers], w_r[kMaxPeers];
+  float XL = 0.f, M = -INFINITY;
+#pragma unroll
+  for (int r = 0; r < kMaxPeers; ++r) {
+    if (r < R) {
+      const float* q = reinterpret_cast<const float*>(peers.base[r] + kPeerHeaderBytes) + int64_t(slot) * 4 * Tmax + t;
+      m_r[r] = ld_peer_f32(q);
+      s_r[r] = ld_peer_f32(q + T);
+      w_r[r] = ld_peer_f32(q + 2 * T);
+      XL += ld_peer_f32(q + 3 * T);
+      M = fmaxf(M, m_r[r]);
+    }
+  }
+  float S = 0.f, W = 0.f;
+#pragma unroll
+  for (int r = 0; r < kMaxPeers; ++r) {
+    if (r < R && m_r[r] != -INFINITY) {
+      const float d = (m_r[r] - M) * c2;
+      const float f = exp2f(d);
+      S = fmaf(s_r[r], f, S);
+      W = fmaf(f, fmaf(d, s_r[r], w_r[r]), W);
+    }
+  }
+  const float ln_s = logf(S);
+  logp[t] = (XL - M) * inv_t - ln_s;
+  if (entropy) entropy[t] = ln_s - kLn2 * (W / S);
+  row_max[t] = M;
+  ln_s_out[t] = ln_s;
+}
+
 bool tma_ok(const void* ptr, int dtype, int64_t V, int64_t row_stride_bytes) {
   const int64_t es = dtype == kFP32 ? 4 : 2;
   return (reinterpret_cast<uintptr_t>(ptr) & 15) == 0 && ((V * es) % 16) == 0 && (row_stride_bytes % 16) == 0;
@@ -643,6 +734,18 @@ int launch_vocab_combine(const float* parts, int R, int64_t T, float inv_t, floa
   vocab_combine_kernel<<<static_cast<int>((T + threads - 1) / threads), threads, 0, stream>>>(
       parts, R, T, inv_t, logp, entropy, row_max, ln_s);
   return check_launch("vocab_combine");
+}
+
+int launch_vocab_combine_p2p(void* const* peer_bases, int rank, int R, int64_t T, int64_t Tmax, int slot,
+                             unsigned int epoch, float inv_t, long long timeout_cycles, float* logp, float* entropy,
+                             float* row_max, float* ln_s, int* status, cudaStream_t stream) {
+  PeerTable tab;
+  for (int r = 0; r < kMaxPeers; ++r) tab.base[r] = r < R ? static_cast<char*>(peer_bases[r]) : nullptr;
+  const int threads = 256;
+  const int64_t blocks = T > 0 ? (T + threads - 1) / threads : 1;   // T == 0 still takes part in the handshake
+  vocab_combine_p2p_kernel<<<static_cast<unsigned int>(blocks), threads, 0, stream>>>(
+      tab, rank, R, T, Tmax, slot, epoch, inv_t, timeout_cycles, logp, entropy, row_max, ln_s, status);
+  return check_launch("vocab_combine_p2p");
 }
 
 }  // namespace ab

@@ -67,4 +67,8 @@ int launch_legacy_entropy(const void* logits, int dtype, int64_t T, int64_t V, i
 int launch_vocab_combine(const float* parts, int R, int64_t T, float inv_t, float* logp,
                          float* entropy, float* row_max, float* ln_s, cudaStream_t stream);
 
+int launch_vocab_combine_p2p(void* const* peer_bases, int rank, int R, int64_t T, int64_t Tmax, int slot,
+                             unsigned int epoch, float inv_t, long long timeout_cycles, float* logp, float* entropy,
+                             float* row_max, float* ln_s, int* status, cudaStream_t stream);
+
 }  // namespace ab

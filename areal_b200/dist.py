@@ -15,6 +15,7 @@ Two ways the path shards:
 """
 from __future__ import annotations
 
+import ctypes
 from typing import Callable, List, Optional, Sequence, Tuple
 
 import torch
@@ -115,6 +116,72 @@ def _cuda_combine(all_parts: torch.Tensor, temperature: float):
     return logp, ent, row_max, ln_s
 
 
+class PeerExchange:
+    """NVLink peer-memory exchange for the vocab-sharded forward: every rank's `[4,T]` partials live in a
+    buffer that all ranks of `group` have mapped (torch symmetric memory does the rendezvous and the
+    mapping -- plumbing), and `areal_b200_vocab_combine_p2p` reads them where they are.  Replaces the
+    all-gather + combine pair by one launch; results are bit-identical.
+
+    One instance per (group, stream of use); `max_tokens` bounds T.  All ranks must call `forward` the
+    same number of times (the step counter is the handshake's epoch)."""
+
+    TIMEOUT_CYCLES = 20_000_000_000          # ~10 s of SM clocks: a peer that never shows up is an error, not a hang
+
+    def __init__(self, max_tokens: int, group=None, device=None):
+        import torch.distributed._symmetric_memory as symm
+        if not dist.is_initialized():
+            raise RuntimeError("PeerExchange needs an initialised process group")
+        self.group = dist.group.WORLD if group is None else group
+        self.rank, self.world = dist.get_rank(self.group), dist.get_world_size(self.group)
+        if self.world > 16:
+            raise ValueError("PeerExchange supports at most 16 ranks")
+        self.max_tokens = int(max_tokens)
+        dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self.device = dev
+        nbytes = int(_lib.lib().areal_b200_vocab_p2p_buffer_bytes(self.max_tokens))
+        try:
+            symm.enable_symm_mem_for_group(self.group.group_name)
+        except Exception:
+            pass                              # newer torch enables groups on demand
+        self.buf = symm.empty(nbytes, dtype=torch.uint8, device=dev)
+        self.buf.zero_()
+        self.handle = symm.rendezvous(self.buf, self.group)
+        self._peers = (ctypes.c_void_p * self.world)(*[int(p) for p in self.handle.buffer_ptrs])
+        self.status = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.epoch = 0
+        torch.cuda.synchronize(dev)
+        dist.barrier(self.group)              # every buffer is zeroed before anybody's first flag lands
+
+    def parts_slot(self, epoch: int, T: int) -> torch.Tensor:
+        """The `[4,T]` f32 window of this rank's buffer that step `epoch` writes."""
+        off = 256 + (epoch & 1) * 16 * self.max_tokens
+        return self.buf[off: off + 16 * T].view(torch.float32).view(4, T)
+
+    def forward(self, shard: torch.Tensor, labels: torch.Tensor, vocab_start: int, temperature: float):
+        T, V = shard.shape
+        if T > self.max_tokens:
+            raise ValueError(f"T={T} exceeds the exchange buffer ({self.max_tokens} tokens)")
+        dev = self.device
+        self.epoch += 1
+        parts = self.parts_slot(self.epoch, T)
+        f32 = dict(dtype=torch.float32, device=dev)
+        logp, ent, row_max, ln_s = (torch.empty(T, **f32) for _ in range(4))
+        with torch.cuda.device(dev):
+            if T:
+                call("areal_b200_logits_partial_fwd", ptr(shard), _lib.DTYPE_CODE[shard.dtype], T, V,
+                     shard.stride(0) if T > 1 else V, ptr(labels), int(vocab_start), float(temperature), ptr(parts),
+                     None, stream_ptr(dev))
+            call("areal_b200_vocab_combine_p2p", self._peers, self.rank, self.world, T, self.max_tokens, self.epoch,
+                 float(temperature), self.TIMEOUT_CYCLES, ptr(logp), ptr(ent), ptr(row_max), ptr(ln_s),
+                 ptr(self.status), stream_ptr(dev))
+        return logp, ent, row_max, ln_s
+
+    def check(self):
+        """Host sync: raises if some step timed out waiting for a peer."""
+        if int(self.status.item()) != 0:
+            raise RuntimeError("areal_b200 peer exchange: a rank did not publish its partials in time")
+
+
 def vocab_parallel_forward(shard: torch.Tensor, labels: torch.Tensor, vocab_start: int, temperature: float,
                            group=None, partials_fn: Optional[Callable] = None,
                            combine_fn: Optional[Callable] = None):
@@ -127,12 +194,15 @@ def vocab_parallel_forward(shard: torch.Tensor, labels: torch.Tensor, vocab_star
 
 class _VocabParallelLogprobsEntropy(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, shard, labels, vocab_start, temperature, group):
+    def forward(ctx, shard, labels, vocab_start, temperature, group, exchange=None):
         if shard.dim() != 2 or shard.stride(1) != 1:
             shard = shard.reshape(-1, shard.shape[-1]).contiguous()
         _lib.require_cuda(shard, labels)
         lab = labels.reshape(-1).long().contiguous()
-        logp, ent, row_max, ln_s = vocab_parallel_forward(shard, lab, vocab_start, temperature, group)
+        if exchange is not None:
+            logp, ent, row_max, ln_s = exchange.forward(shard, lab, vocab_start, temperature)
+        else:
+            logp, ent, row_max, ln_s = vocab_parallel_forward(shard, lab, vocab_start, temperature, group)
         ctx.save_for_backward(shard, lab, row_max, ln_s, ent)
         ctx.vocab_start, ctx.temperature = int(vocab_start), float(temperature)
         ctx.set_materialize_grads(False)
@@ -142,21 +212,24 @@ class _VocabParallelLogprobsEntropy(torch.autograd.Function):
     def backward(ctx, g_logp, g_ent):
         shard, lab, row_max, ln_s, ent = ctx.saved_tensors
         if g_logp is None and g_ent is None:
-            return None, None, None, None, None
+            return None, None, None, None, None, None
         from .functional import _f32, _logits_backward
         gl = None if g_logp is None else _f32(g_logp.reshape(-1))
         gh = None if g_ent is None else _f32(g_ent.reshape(-1))
         d = _logits_backward(shard, lab, ctx.temperature, row_max, ln_s, ent, gl, gh, vocab_start=ctx.vocab_start)
-        return d, None, None, None, None
+        return d, None, None, None, None, None
 
 
 def vocab_parallel_logprobs_entropy(shard_logits: torch.Tensor, labels: torch.Tensor, temperature: float = 1.0,
-                                    group=None, vocab_start: Optional[int] = None):
+                                    group=None, vocab_start: Optional[int] = None,
+                                    exchange: Optional[PeerExchange] = None):
     """Log-prob of `labels` (GLOBAL vocabulary ids) and entropy from vocab-sharded logits
     `[T, V/R]`; replaces the Megatron-TP branch of gather_logprobs_entropy
     (areal/utils/functional.py:91-98).  `vocab_start` defaults to rank * shard_width.  Every rank gets
-    the full `[T]` results (as after the reference's all-reduces); gradients flow to the local shard."""
+    the full `[T]` results (as after the reference's all-reduces); gradients flow to the local shard.
+    `exchange`: a `PeerExchange` -- the partials are then read from the peers' memory over NVLink by the
+    combine kernel itself instead of being all-gathered first (same bits, one launch less)."""
     if vocab_start is None:
         rank = dist.get_rank(group) if dist.is_initialized() else 0
         vocab_start = rank * shard_logits.shape[-1]
-    return _VocabParallelLogprobsEntropy.apply(shard_logits, labels, vocab_start, temperature, group)
+    return _VocabParallelLogprobsEntropy.apply(shard_logits, labels, vocab_start, temperature, group, exchange)

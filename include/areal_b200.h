@@ -340,6 +340,27 @@ AREAL_B200_API int areal_b200_set_intervals(const void* packed, int64_t packed_n
  * returns the number of merged intervals, or -1 on a null pointer. */
 AREAL_B200_API int64_t areal_b200_merge_intervals(const uint64_t* intervals, int64_t n, uint64_t* out);
 
+/* Vocab-sharded combine WITHOUT the all-gather: the partial sets are read straight out of the peers'
+ * memory over NVLink (the reference does six all-reduces here: areal/utils/mcore/functional.py:16-31 +
+ * Megatron's vocab_parallel_cross_entropy).  No counterpart as a single reference function.
+ *   Every rank owns a peer-mapped ("symmetric") buffer of areal_b200_vocab_p2p_buffer_bytes(Tmax)
+ *   bytes, ZEROED once: u32 flag[16] (256 B) | parts[2][4][Tmax] f32.  peer_bases: HOST array of R
+ *   device pointers, peer_bases[r] = rank r's buffer as mapped into THIS process (peer_bases[rank] is
+ *   the local one).  Protocol per step e = 1, 2, 3, ... (the same e on every rank):
+ *     1. areal_b200_logits_partial_fwd writes this rank's parts [4,T] at
+ *        (char*)local + 256 + (e & 1) * 16 * Tmax   (same stream);
+ *     2. this call: release-stores e into flag[rank] of every peer, waits (at most timeout_cycles SM
+ *        clocks) until all R flags here are >= e, then combines in rank order -- bit-identical to
+ *        areal_b200_vocab_combine on the gathered parts.
+ *   *status (device int, zeroed by the caller) is set to 1 if a peer did not arrive in time; the
+ *   outputs are then left untouched.  T may be 0 (the rank still takes part in the handshake). */
+AREAL_B200_API int64_t areal_b200_vocab_p2p_buffer_bytes(int64_t max_tokens);
+AREAL_B200_API int areal_b200_vocab_combine_p2p(void* const* peer_bases, int rank, int world_size,
+                                                int64_t T, int64_t max_tokens, int64_t epoch,
+                                                double temperature, int64_t timeout_cycles, float* logp,
+                                                float* entropy, float* row_max, float* ln_sumexp,
+                                                int* status, void* stream);
+
 /* Legacy running value statistics.  Replaces the arithmetic of `ExponentialRunningMeanStd` /
  * `MovingAverageRunningMeanStd` (realhf/impl/model/modules/rms.py:19-183): update = three reductions
  * + ~10 scalar kernels there; here areal_b200_masked_moments (one group) followed by

@@ -42,6 +42,57 @@ def main():
     gs = full.grad[:, rank * Vs:(rank + 1) * Vs].float()
     assert torch.allclose(shard.grad.float(), gs, rtol=2 ** -7, atol=1e-9), (shard.grad.float() - gs).abs().max()
 
+    # ---------------- the same exchange over NVLink peer memory (no all-gather) -------------------------
+    try:
+        ex = D.PeerExchange(max_tokens=4096)
+    except Exception as exc:                                  # no peer mapping on this box: reported, not fatal
+        ex = None
+        if rank == 0:
+            print("P2P_UNAVAILABLE", repr(exc)[:300])
+    if ex is not None:
+        for step, Tp in enumerate((96, 1, 4096, 777, 0, 96)):   # both slots several times, ragged and empty T
+            gp = torch.Generator(device=dev).manual_seed(100 + step)
+            lg_p = (torch.randn(max(Tp, 1), V, generator=gp, device=dev) * 2).bfloat16()[:Tp]
+            lab_p = torch.randint(0, V, (Tp,), generator=gp, device=dev)
+            sh = lg_p[:, rank * Vs:(rank + 1) * Vs].contiguous()
+            a = D.vocab_parallel_forward(sh, lab_p, rank * Vs, 0.9) if Tp else None
+            b = ex.forward(sh, lab_p, rank * Vs, 0.9)
+            if Tp:
+                for u, v in zip(a, b):
+                    assert torch.equal(u, v), (step, Tp, (u - v).abs().max())
+        ex.check()
+        # autograd path through the exchange
+        shard2 = logits[:, rank * Vs:(rank + 1) * Vs].detach().clone().requires_grad_()
+        lp2, ent2 = D.vocab_parallel_logprobs_entropy(shard2, labels, 0.9, exchange=ex)
+        ((lp2 * w_lp).sum() + (ent2 * w_h).sum()).backward()
+        assert torch.equal(lp2, lp) and torch.equal(ent2, ent) and torch.equal(shard2.grad, shard.grad)
+        # device time of one vocab-sharded forward (T = 4096, V/world columns), both ways
+        Tp = 4096
+        sh = (torch.randn(Tp, Vs, generator=g, device=dev) * 2).bfloat16()
+        lab_p = torch.randint(0, V, (Tp,), generator=g, device=dev)
+
+        def t_nccl():
+            D.vocab_parallel_forward(sh, lab_p, rank * Vs, 0.9)   # partial kernel, all-gather, combine
+
+        def t_p2p():
+            ex.forward(sh, lab_p, rank * Vs, 0.9)                 # partial kernel, peer-memory combine
+        res = {}
+        for name, fn in (("partial+allgather+combine", t_nccl), ("partial+peer_combine", t_p2p)):
+            for _ in range(5):
+                fn()
+            dist.barrier()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(50):
+                fn()
+            e1.record()
+            torch.cuda.synchronize()
+            res[name] = e0.elapsed_time(e1) / 50 * 1e3
+        ex.check()
+        if rank == 0:
+            print("P2P_OK", world, {k: round(v, 1) for k, v in res.items()}, "us per call")
+
     # ---------------- batch-sharded (cfg 3 in miniature) ------------------------------------------------
     rng = np.random.RandomState(3)
     lens = rng.randint(16, 200, 24)

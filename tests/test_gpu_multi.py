@@ -40,3 +40,6 @@ def test_nccl_sharded_paths(world):
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert f"MULTI_GPU_OK {world}" in r.stdout
+    # the NVLink peer-memory exchange ran bit-identically to the all-gather path, or the box cannot map peers
+    assert f"P2P_OK {world}" in r.stdout or "P2P_UNAVAILABLE" in r.stdout, r.stdout[-2000:]
+    print(next(line for line in r.stdout.splitlines() if line.startswith("P2P_")))
