@@ -53,3 +53,13 @@ def test_patch_areal_rebinds_from_import_sites():
                 sys.modules.pop(k, None)
             else:
                 sys.modules[k] = v
+
+
+def test_peer_exchange_needs_a_process_group():
+    import pytest
+    import torch.distributed as dist
+    from areal_b200 import dist as D
+    if dist.is_initialized():
+        pytest.skip("a process group is already up in this interpreter")
+    with pytest.raises(RuntimeError, match="initialised process group"):
+        D.PeerExchange(max_tokens=16)
