@@ -129,8 +129,12 @@ __global__ void gae1d_prep_kernel(const int32_t* __restrict__ cu, int B, int64_t
 }
 
 // ---- 1D packed, misaligned values ------------------------------------------------------------------
-__global__ void __launch_bounds__(kThreads, 8)
+// kT threads per CTA: 256 (2048-token tiles, 8 CTAs/SM) or 512 (4096-token tiles, 4 CTAs/SM: half as many
+// look-backs and CTA barriers per token; used for large batches)
+template <int kT>
+__global__ void __launch_bounds__(kT, 2048 / kT)
 gae1d_kernel(const Gae1dParams p) {
+  constexpr int kThreads = kT, kWarps = kT / 32, kTile = kT * kItems;
   __shared__ Affine wsm[kWarps];
   __shared__ double carry_sm;
   // per-token values parked in shared memory ([item][thread]: conflict-free) while the scan runs, so
@@ -720,25 +724,30 @@ gae2d_olp_kernel(const Gae2dParams p) {
 }  // namespace
 
 int64_t gae1d_workspace_bytes(int64_t T) {
-  const int64_t ntiles = (T + kTile - 1) / kTile;
+  const int64_t ntiles = (T + 512 - 1) / 512;        // the smallest tile any variant uses
   return int64_t(sizeof(WorkspaceHeader)) + (ntiles > 1 ? ntiles : 0) * int64_t(sizeof(TileDesc));
 }
 
+constexpr int64_t kWideFromTokens = 1 << 20;   // batches of at least this many tokens use 512-thread CTAs
+
 int launch_gae1d(const Gae1dParams& p, cudaStream_t stream) {
   if (p.T == 0) return kOk;
-  const int64_t ntiles = (p.T + kTile - 1) / kTile;
+  const bool wide = p.T >= kWideFromTokens;
+  const int threads = wide ? 64 : kThreads;
+  const int tile_tokens = threads * kItems;
+  const int64_t ntiles = (p.T + tile_tokens - 1) / tile_tokens;
   if (ntiles > 1) {
     // descriptors start "empty" and carry each tile's first sequence: one tiny kernel, stream-ordered
     TileDesc* desc = reinterpret_cast<TileDesc*>(reinterpret_cast<char*>(p.workspace) + sizeof(WorkspaceHeader));
     gae1d_prep_kernel<<<static_cast<unsigned int>((ntiles + 255) / 256), 256, 0, stream>>>(
-        p.cu, static_cast<int>(p.B), p.T, ntiles, desc, kTile);
+        p.cu, static_cast<int>(p.B), p.T, ntiles, desc, tile_tokens);
   }
   if (ntiles > 1) {
     // launched as a programmatic dependent of the prep kernel: its launch latency and the reward
     // loads overlap the prep grid
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(static_cast<unsigned int>(ntiles));
-    cfg.blockDim = dim3(kThreads);
+    cfg.blockDim = dim3(threads);
     cfg.dynamicSmemBytes = 0;
     cfg.stream = stream;
     cudaLaunchAttribute attr[1];
@@ -746,10 +755,11 @@ int launch_gae1d(const Gae1dParams& p, cudaStream_t stream) {
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    AB_CUDA(cudaLaunchKernelEx(&cfg, gae1d_kernel, p));
+    if (wide) AB_CUDA(cudaLaunchKernelEx(&cfg, gae1d_kernel<64>, p));
+    else AB_CUDA(cudaLaunchKernelEx(&cfg, gae1d_kernel<256>, p));
     return kOk;
   }
-  gae1d_kernel<<<static_cast<unsigned int>(ntiles), kThreads, 0, stream>>>(p);
+  gae1d_kernel<256><<<static_cast<unsigned int>(ntiles), kThreads, 0, stream>>>(p);
   return check_launch("gae1d");
 }
 
@@ -797,7 +807,7 @@ int launch_gae1d_static(Gae1dParams p, cudaStream_t stream) {
         p.cu, static_cast<int>(p.B), p.T, ntiles, desc, kTile);
   }
   p.workspace = scratch;
-  gae1d_kernel<<<static_cast<unsigned int>(ntiles), kThreads, 0, stream>>>(p);
+  gae1d_kernel<256><<<static_cast<unsigned int>(ntiles), kThreads, 0, stream>>>(p);
   return check_launch("gae1d (static scratch)");
 }
 

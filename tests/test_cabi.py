@@ -38,7 +38,7 @@ def test_header_symbols_exported(lib):
 def test_host_only_entry_points(lib):
     assert lib.areal_b200_version() >= 100
     assert lib.areal_b200_gae1d_workspace_bytes(100) == 64
-    assert lib.areal_b200_gae1d_workspace_bytes(2049) == 64 + 2 * 32
+    assert lib.areal_b200_gae1d_workspace_bytes(2049) == 64 + 5 * 32      # sized for the smallest (512-token) tile
     assert lib.areal_b200_interval_workspace_bytes(10) == 14 * 8    # status[2] | off[n+1] | any_shift
     assert lib.areal_b200_loss_workspace_bytes() >= 16 + 8 * 8
 
