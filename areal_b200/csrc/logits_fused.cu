@@ -33,11 +33,11 @@ constexpr int kStages = 4;
 constexpr int kCtasPerSm = 2;
 constexpr size_t kSmemBytes = size_t(kStages) * kStageBytes + 1024;
 
-template <bool kMinMax>
+template <bool kMinMax, int kCons = kConsumers>
 __device__ __forceinline__ void consume_full_stage(RowState& st, uint32_t sbase, int tid, float c2) {
   uint4 q[kVecPerThread];
 #pragma unroll
-  for (int j = 0; j < kVecPerThread; ++j) q[j] = lds_v4(sbase + (tid + j * kConsumers) * 16);
+  for (int j = 0; j < kVecPerThread; ++j) q[j] = lds_v4(sbase + (tid + j * kCons) * 16);
   uint32_t mx = vec_max_bf16(q[0]);
 #pragma unroll
   for (int j = 1; j < kVecPerThread; ++j) mx = max_bf16x2(mx, vec_max_bf16(q[j]));
@@ -86,6 +86,61 @@ __device__ __forceinline__ bool row_reduce(RowState& st, RowReduceSmem* red, int
   st.s = red->s[parity][l];
   st.w = red->w[parity][l];
   st.mn = red->mn[parity][l];
+#pragma unroll
+  for (int o = kConsumerWarps / 2; o > 0; o >>= 1) {
+    const float m2 = __shfl_xor_sync(0xffffffffu, st.m, o);
+    const float s2 = __shfl_xor_sync(0xffffffffu, st.s, o);
+    const float w2 = __shfl_xor_sync(0xffffffffu, st.w, o);
+    const float n2 = __shfl_xor_sync(0xffffffffu, st.mn, o);
+    state_merge(st.m, st.s, st.w, m2, s2, w2, c2);
+    st.mn = fminf(st.mn, n2);
+  }
+  return lane == 0;
+}
+
+// Rotating variant for the TMA kernel: the finishing work of row number `it` (CTA-local count) belongs to
+// warp it % 8.  The other seven warps only ARRIVE on the row's named barrier and go on with the next row;
+// the finishing warp waits for them, merges the eight partials and runs the epilogue, so its global loads
+// and stores are off the other warps' path and the duty (and its lag) moves from warp to warp.  Eight
+// partial slots / barrier ids: warps cannot drift more than kStages (4) rows apart, the ring holds them.
+constexpr int kRedSlots = 8;
+template <int kCW>
+struct RowReduceRot {
+  float m[kRedSlots][kCW], s[kRedSlots][kCW], w[kRedSlots][kCW], mn[kRedSlots][kCW];
+};
+template <int kCW>
+__device__ __forceinline__ bool row_reduce_rot(RowState& st, RowReduceRot<kCW>* red, int64_t it, int warp, int lane,
+                                               float c2) {
+  constexpr int kConsumerWarps = kCW, kConsumers = kCW * 32;
+  state_canonical(st, c2);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float m2 = __shfl_xor_sync(0xffffffffu, st.m, o);
+    const float s2 = __shfl_xor_sync(0xffffffffu, st.s, o);
+    const float w2 = __shfl_xor_sync(0xffffffffu, st.w, o);
+    const float n2 = __shfl_xor_sync(0xffffffffu, st.mn, o);
+    state_merge(st.m, st.s, st.w, m2, s2, w2, c2);
+    st.mn = fminf(st.mn, n2);
+  }
+  const int slot = static_cast<int>(it % kRedSlots);
+  if (lane == 0) {
+    red->m[slot][warp] = st.m;
+    red->s[slot][warp] = st.s;
+    red->w[slot][warp] = st.w;
+    red->mn[slot][warp] = st.mn;
+  }
+  const int fin = static_cast<int>(it % kConsumerWarps);
+  if (warp != fin) {
+    __syncwarp();
+    named_bar_arrive(1 + slot, kConsumers);
+    return false;
+  }
+  named_bar_sync(1 + slot, kConsumers);
+  const int l = lane & (kConsumerWarps - 1);
+  st.m = red->m[slot][l];
+  st.s = red->s[slot][l];
+  st.w = red->w[slot][l];
+  st.mn = red->mn[slot][l];
 #pragma unroll
   for (int o = kConsumerWarps / 2; o > 0; o >>= 1) {
     const float m2 = __shfl_xor_sync(0xffffffffu, st.m, o);
@@ -182,13 +237,18 @@ template <typename E> struct IsBF16 { static constexpr bool value = false; };
 template <> struct IsBF16<ElemBF16> { static constexpr bool value = true; };
 
 // ---- TMA-staged forward ------------------------------------------------------------------------
-template <bool kMinMax, typename E>
-__global__ void __launch_bounds__(kThreads, kCtasPerSm)
+// kCW consumer warps per CTA: 8 (16 KB stages, 2 CTAs/SM) for long rows; 4 (8 KB stages, 4 CTAs/SM) for short
+// ones (vocabulary shards), where a row gives each of 256 threads too little to do between two row ends
+template <bool kMinMax, typename E, int kCW>
+__global__ void __launch_bounds__((kCW + 1) * 32, 16 / kCW)
 logits_fwd_tma_kernel(const LogitsFwdParams p) {
+  constexpr int kConsumerWarps = kCW, kConsumers = kCW * 32, kStageBytes = kCW * 2048;
+  static_assert(kStageBytes / 16 / kConsumers == kVecPerThread, "four vectors per thread and stage");
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t full_bar[kStages];
   __shared__ __align__(8) uint64_t empty_bar[kStages];
-  __shared__ RowReduceSmem red;
+  __shared__ RowReduceRot<kCW> red;
+  __shared__ LossAcc acc_sm[kConsumerWarps];
 
   const int tid = threadIdx.x;
   const int warp = tid >> 5, lane = tid & 31;
@@ -234,9 +294,9 @@ logits_fwd_tma_kernel(const LogitsFwdParams p) {
   const float c2 = p.inv_temperature * kLog2e;
   int stage = 0;
   uint32_t phase = 0;
-  int parity = 0;
   LossAcc acc = {0.f, 0.f};
-  for (int64_t row = blockIdx.x; row < p.T; row += gridDim.x) {
+  int64_t it = 0;
+  for (int64_t row = blockIdx.x; row < p.T; row += gridDim.x, ++it) {
     RowState st;
     state_init(st);
     for (int c = 0; c < nchunk; ++c) {
@@ -244,7 +304,7 @@ logits_fwd_tma_kernel(const LogitsFwdParams p) {
       const uint32_t sbase = ring + stage * kStageBytes;
       if (c != nchunk - 1 || tail_bytes == kStageBytes) {
         if constexpr (E::kSize == 2 && E::kN == 8 && sizeof(E) == sizeof(ElemBF16) && IsBF16<E>::value) {
-          consume_full_stage<kMinMax>(st, sbase, tid, c2);
+          consume_full_stage<kMinMax, kConsumers>(st, sbase, tid, c2);
         } else {
           uint4 q[kVecPerThread];
 #pragma unroll
@@ -269,10 +329,21 @@ logits_fwd_tma_kernel(const LogitsFwdParams p) {
         phase ^= 1u;
       }
     }
-    if (row_reduce(st, &red, parity, warp, lane, c2)) row_epilogue(p, row, st, acc);
-    parity ^= 1;
+    if (row_reduce_rot<kCW>(st, &red, it, warp, lane, c2)) row_epilogue(p, row, st, acc);
   }
-  if (p.mode == kModeFusedActor && tid == 0) loss_finalize(p, acc);
+  if (p.mode == kModeFusedActor) {
+    // every warp's lane 0 holds the loss terms of the rows it finished: add them up in warp order
+    if (lane == 0) acc_sm[warp] = acc;
+    named_bar_sync(1 + kRedSlots, kConsumers);
+    if (tid == 0) {
+      LossAcc tot = {0.f, 0.f};
+      for (int w = 0; w < kConsumerWarps; ++w) {
+        tot.sum += acc_sm[w].sum;
+        tot.count += acc_sm[w].count;
+      }
+      loss_finalize(p, tot);
+    }
+  }
 }
 
 // ---- generic forward (any alignment, bf16 / fp16 / fp32): one CTA per row, LDG -----------------
@@ -661,20 +732,27 @@ int launch_logits_fwd(const LogitsFwdParams& p, cudaStream_t stream) {
   if (p.T == 0) return kOk;
   const bool minmax = p.raw_min != nullptr;
   if (tma_ok(p.logits, p.dtype, p.V, p.row_stride_bytes)) {
-    const int grid = grid_for(p.T, kCtasPerSm);
+    // rows of at most 64 KB (vocabulary shards): half-width CTAs, twice as many of them
+    const bool narrow = p.V * (p.dtype == kFP32 ? 4 : 2) <= 65536;
+#define AB_LAUNCH_FWD_W(MM, E, W)                                                                  \
+  {                                                                                                \
+    static bool done = false;                                                                      \
+    constexpr size_t smem = size_t(kStages) * (W * 2048) + 1024;                                   \
+    if (!done) {                                                                                   \
+      AB_CUDA(cudaFuncSetAttribute(logits_fwd_tma_kernel<MM, E, W>,                                \
+                                   cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));       \
+      done = true;                                                                                 \
+    }                                                                                              \
+    logits_fwd_tma_kernel<MM, E, W><<<grid_for(p.T, 16 / W), (W + 1) * 32, smem, stream>>>(p);     \
+  }
 #define AB_LAUNCH_FWD(MM, E)                                                       \
   {                                                                                \
-    static bool done = false;                                                      \
-    if (!done) {                                                                   \
-      const int rc = set_smem(logits_fwd_tma_kernel<MM, E>);                       \
-      if (rc) return rc;                                                           \
-      done = true;                                                                 \
-    }                                                                              \
-    logits_fwd_tma_kernel<MM, E><<<grid, kThreads, kSmemBytes, stream>>>(p);       \
+    if (narrow) AB_LAUNCH_FWD_W(MM, E, 4) else AB_LAUNCH_FWD_W(MM, E, 8)           \
   }
     if (p.dtype == kBF16) { if (minmax) AB_LAUNCH_FWD(true, ElemBF16) else AB_LAUNCH_FWD(false, ElemBF16) }
     else if (p.dtype == kFP16) { if (minmax) AB_LAUNCH_FWD(true, ElemFP16) else AB_LAUNCH_FWD(false, ElemFP16) }
     else { if (minmax) AB_LAUNCH_FWD(true, ElemFP32) else AB_LAUNCH_FWD(false, ElemFP32) }
+#undef AB_LAUNCH_FWD_W
 #undef AB_LAUNCH_FWD
   } else {
     const int grid = grid_for(p.T, 8);

@@ -1,0 +1,93 @@
+"""BASELINE.json configs[3] shape: T = 131,072 packed tokens, V = 151,936 bf16 logits vocab-sharded over the
+ranks of one node (Megatron-TP layout).  Per step: partial statistics of the local [T, V/R] shard, exchange,
+combine, local backward.  Launch: python -m torch.distributed.run --nproc-per-node R bench_vocab_parallel.py
+Prints one JSON line (rank 0); time = max over ranks of the CUDA-event time."""
+import json
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+
+def main():
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    local = int(os.environ.get("LOCAL_RANK", rank))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    from areal_b200 import dist as D
+    T, V = int(os.environ.get("VP_TOKENS", 131072)), 151936
+    Vs = V // world
+    steps = int(os.environ.get("VP_STEPS", 20))
+    g = torch.Generator(device=dev).manual_seed(rank)
+    shard = torch.empty(T, Vs, dtype=torch.bfloat16, device=dev)
+    for i in range(0, T, 8192):
+        shard[i:i + 8192] = (torch.randn(min(8192, T - i), Vs, generator=g, device=dev) * 2).bfloat16()
+    gl = torch.Generator(device=dev).manual_seed(1234)          # same labels / weights on every rank
+    labels = torch.randint(0, V, (T,), generator=gl, device=dev)
+    w = torch.randn(T, generator=gl, device=dev)
+    w[torch.rand(T, generator=gl, device=dev) < 0.2] = 0.0
+    peak = 6539.9
+    try:
+        peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
+    except Exception:
+        pass
+    try:
+        ex = D.PeerExchange(max_tokens=T)
+    except Exception as exc:
+        ex = None
+        why = repr(exc)[:200]
+    out = {"workload": f"BASELINE.json configs[3]: T={T} tokens, V={V} bf16 vocab-sharded over {world} GPUs "
+                       f"(shard [T, {Vs}]), logprob+entropy forward and dlogits backward per step",
+           "n_gpus": world, "steps": steps, "unit": "tokens/s", "peak_gbs": peak}
+    for name, exch in (("allgather", None), ("peer_memory", ex)):
+        if name == "peer_memory" and ex is None:
+            out[name] = {"unavailable": why}
+            continue
+        x = shard.requires_grad_()
+
+        def step():
+            x.grad = None
+            lp, ent = D.vocab_parallel_logprobs_entropy(x, labels, 1.0, exchange=exch)
+            return lp, ent
+
+        def step_bwd():
+            lp, ent = step()
+            (lp * w).sum().backward()
+        res = {}
+        for label, fn in (("fwd", step), ("fwd_bwd", step_bwd)):
+            for _ in range(3):
+                fn()
+            dist.barrier()
+            torch.cuda.synchronize(dev)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(steps):
+                fn()
+            e1.record()
+            dist.barrier()
+            torch.cuda.synchronize(dev)
+            ms = torch.tensor([e0.elapsed_time(e1) / steps], device=dev)
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+            res[label + "_ms"] = float(ms.item())
+        active = float((w != 0).float().mean().item())
+        fwd_bytes = 2.0 * T * Vs
+        bwd_bytes = 2.0 * T * Vs * (1.0 + active)
+        res["tokens_per_s"] = T / (res["fwd_bwd_ms"] * 1e-3)
+        res["fwd_hbm_frac"] = fwd_bytes / (res["fwd_ms"] * 1e-3) / 1e9 / peak
+        res["fwd_bwd_hbm_frac"] = (fwd_bytes + bwd_bytes) / (res["fwd_bwd_ms"] * 1e-3) / 1e9 / peak
+        out[name] = res
+        if exch is not None:
+            exch.check()
+    if rank == 0:
+        print(json.dumps(out), flush=True)
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
