@@ -55,6 +55,33 @@ __device__ __forceinline__ void consume_full_stage(RowState& st, uint32_t sbase,
   st.w += w0 + w1;
 }
 
+// A stage that is not full (the end of a row): the same batch -- one rebase for all the vectors this thread
+// has -- with the missing vectors predicated off, instead of one rebase per vector.
+template <bool kMinMax, int kCons>
+__device__ __forceinline__ void consume_partial_stage(RowState& st, uint32_t sbase, int tid, int nvec, float c2) {
+  if (tid >= nvec) return;
+  uint4 q[kVecPerThread];
+  q[0] = lds_v4(sbase + tid * 16);
+  uint32_t mx = vec_max_bf16(q[0]);
+  uint32_t mn = kMinMax ? vec_min_bf16(q[0]) : 0u;
+#pragma unroll
+  for (int j = 1; j < kVecPerThread; ++j) {
+    if (tid + j * kCons < nvec) {
+      q[j] = lds_v4(sbase + (tid + j * kCons) * 16);
+      mx = max_bf16x2(mx, vec_max_bf16(q[j]));
+      if (kMinMax) mn = min_bf16x2(mn, vec_min_bf16(q[j]));
+    }
+  }
+  if (kMinMax) st.mn = fminf(st.mn, fminf(bf16_lo(mn), bf16_hi(mn)));
+  const float nb = state_rebase(st, fmaxf(bf16_lo(mx), bf16_hi(mx)), c2);
+  float s0 = 0.f, s1 = 0.f, w0 = 0.f, w1 = 0.f;
+#pragma unroll
+  for (int j = 0; j < kVecPerThread; ++j)
+    if (tid + j * kCons < nvec) vec_accumulate(q[j], c2, nb, s0, s1, w0, w1);
+  st.s += s0 + s1;
+  st.w += w0 + w1;
+}
+
 struct RowReduceSmem {
   float m[2][kConsumerWarps], s[2][kConsumerWarps], w[2][kConsumerWarps], mn[2][kConsumerWarps];
 };
@@ -313,12 +340,16 @@ logits_fwd_tma_kernel(const LogitsFwdParams p) {
         }
       } else {
         const int nvec = tail_bytes >> 4;
+        if constexpr (IsBF16<E>::value) {
+          consume_partial_stage<kMinMax, kConsumers>(st, sbase, tid, nvec, c2);
+        } else {
 #pragma unroll
-        for (int j = 0; j < kVecPerThread; ++j) {
-          const int v = tid + j * kConsumers;
-          if (v < nvec) {
-            const uint4 q1[1] = {lds_v4(sbase + v * 16)};
-            consume_batch<E, kMinMax, 1>(st, q1, c2);
+          for (int j = 0; j < kVecPerThread; ++j) {
+            const int v = tid + j * kConsumers;
+            if (v < nvec) {
+              const uint4 q1[1] = {lds_v4(sbase + v * 16)};
+              consume_batch<E, kMinMax, 1>(st, q1, c2);
+            }
           }
         }
       }
