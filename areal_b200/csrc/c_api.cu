@@ -11,6 +11,7 @@
 #include "logits_fused.h"
 #include "masked_norm.h"
 #include "masked_stats.h"
+#include "clamped_entropy.h"
 #include "ppo_loss.h"
 
 namespace ab {
@@ -702,6 +703,58 @@ AREAL_B200_API int64_t areal_b200_merge_intervals(const uint64_t* iv, int64_t n,
     }
   }
   return k;
+}
+
+static int clamped_params(ClampedParams& p, const void* logits, int dtype, int64_t T, int64_t V, int64_t row_stride,
+                          const int64_t* labels, double temperature) {
+  AB_REQUIRE(T >= 0 && V > 0, "bad shape");
+  AB_REQUIRE(dtype == kBF16 || dtype == kFP16, "clamped entropy: bf16 or fp16 logits only (16-bit radix select)");
+  AB_REQUIRE(row_stride >= V, "row stride smaller than V");
+  AB_REQUIRE(V < (int64_t(1) << 24), "clamped entropy: V too large for the 16-bit per-thread histograms");
+  AB_REQUIRE(temperature > 0.0, "temperature must be positive");
+  AB_REQUIRE(T == 0 || (logits && labels), "null pointer");
+  p.logits = logits;
+  p.dtype = dtype;
+  p.T = T;
+  p.V = V;
+  p.row_stride_bytes = row_stride * 2;
+  p.labels = labels;
+  p.inv_temperature = static_cast<float>(1.0 / temperature);
+  return kOk;
+}
+
+AREAL_B200_API int areal_b200_clamped_entropy_fwd(const void* logits, int dtype, int64_t T, int64_t V,
+                                                  int64_t row_stride, const int64_t* labels,
+                                                  double temperature, int64_t k_removed, float* logp,
+                                                  float* entropy, float* saved, void* stream) {
+  ClampedParams p;
+  const int rc = clamped_params(p, logits, dtype, T, V, row_stride, labels, temperature);
+  if (rc) return rc;
+  AB_REQUIRE(k_removed >= 0 && k_removed < V, "clamped entropy: k_removed=%lld must be in [0, V)",
+             static_cast<long long>(k_removed));
+  AB_REQUIRE(T == 0 || (logp && entropy && saved), "null output");
+  p.k = k_removed;
+  p.logp = logp;
+  p.entropy = entropy;
+  p.saved = saved;
+  return launch_clamped_entropy_fwd(p, static_cast<cudaStream_t>(stream));
+}
+
+AREAL_B200_API int areal_b200_clamped_entropy_bwd(const void* logits, int dtype, int64_t T, int64_t V,
+                                                  int64_t row_stride, const int64_t* labels,
+                                                  double temperature, const float* saved,
+                                                  const float* g_logp, const float* g_entropy,
+                                                  void* dlogits, int64_t d_row_stride, void* stream) {
+  ClampedParams p;
+  const int rc = clamped_params(p, logits, dtype, T, V, row_stride, labels, temperature);
+  if (rc) return rc;
+  AB_REQUIRE(d_row_stride >= V, "gradient row stride smaller than V");
+  AB_REQUIRE(T == 0 || (saved && dlogits), "null pointer");
+  p.k = 0;
+  p.logp = nullptr;
+  p.entropy = nullptr;
+  p.saved = const_cast<float*>(saved);
+  return launch_clamped_entropy_bwd(p, g_logp, g_entropy, dlogits, d_row_stride * 2, static_cast<cudaStream_t>(stream));
 }
 
 AREAL_B200_API int64_t areal_b200_vocab_p2p_buffer_bytes(int64_t max_tokens) {

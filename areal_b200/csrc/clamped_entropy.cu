@@ -1,0 +1,362 @@
+// Token log-prob + CLAMPED softmax entropy (AEnt recipe) and their gradient.
+//
+// Replaces (reference, relative to its root):
+//   recipe/AEnt/functional.py:15-36   clamped_softmax_entropy: the k = int(V * clamp) smallest logits of
+//       every row are masked out before the softmax entropy.  The reference finds them with a top-k on a
+//       CPU copy of the logits (`logits.cpu()`, :18-27) and materialises a [T,V] bool mask and five
+//       [T,V] float temporaries per 1024-row chunk.
+//   recipe/AEnt/functional.py:39-80   gather_logprobs_clamped_entropy (log-softmax gather + the above)
+//
+// Design.  Only the VALUE of the k-th smallest logit matters: equal logits are interchangeable for the
+// entropy, so a row needs (tau, r) = (the largest removed value, how many elements equal to tau are
+// removed).  16-bit logits have 16-bit order-preserving keys, so tau comes from a two-level radix select
+// (high byte, then low byte inside the chosen bucket).  The histograms are PRIVATE per thread in shared
+// memory ([bin][thread] u16, 128 KB: no contention -- the high byte of a bf16 key is so concentrated
+// that a shared histogram would serialise), bumped with result-less shared atomics, summed with a rotated read.  Pass 1 also takes the
+// row max; pass 3 accumulates the full and the clamped softmax sums together, so one kernel yields
+// log-prob and clamped entropy from three reads of the row, the last two out of L2 (one CTA per row,
+// 148 rows = 45 MB in flight).  Elements equal to tau carry the weight f = (n_tau - r) / n_tau in the
+// sums and in the gradient: the expected value over the reference's arbitrary tie-breaking (its top-k
+// picks SOME r of the n_tau equal elements), identical per class of equal logits.
+#include "clamped_entropy.h"
+
+#include "logits_device.cuh"
+
+namespace ab {
+namespace {
+
+constexpr int kCeThreads = 256;     // backward kernel
+constexpr int kFwdThreads = 512;    // forward kernel: two threads share a histogram slot
+constexpr int kSlots = 256;         // private counters per bin
+constexpr int kBins = 256;
+constexpr size_t kHistBytes = size_t(kBins) * kSlots * sizeof(uint16_t);   // 128 KB
+
+// order-preserving 16-bit key of a bf16 / fp16 bit pattern (sign-magnitude -> unsigned ascending)
+__device__ __forceinline__ uint32_t key16(uint32_t b) { return (b & 0x8000u) ? (~b & 0xffffu) : (b | 0x8000u); }
+
+template <bool kIsBF16>
+__device__ __forceinline__ float half_to_f32(uint32_t b) {
+  if (kIsBF16) return __uint_as_float(b << 16);
+  return __half2float(__ushort_as_half(static_cast<unsigned short>(b)));
+}
+
+template <int kCeWarps>
+__device__ __forceinline__ float block_max(float v, float* red, int warp, int lane) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  if (lane == 0) red[warp] = v;
+  __syncthreads();
+  float r = red[0];
+  for (int w = 1; w < kCeWarps; ++w) r = fmaxf(r, red[w]);
+  __syncthreads();
+  return r;
+}
+template <int kCeWarps>
+__device__ __forceinline__ float block_sum(float v, float* red, int warp, int lane) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  if (lane == 0) red[warp] = v;
+  __syncthreads();
+  float r = 0.f;
+  for (int w = 0; w < kCeWarps; ++w) r += red[w];      // fixed order
+  __syncthreads();
+  return r;
+}
+
+// Sum the private histograms (thread b owns bin b: rotated read, conflict-free), then find the bin that
+// holds 0-based rank `rank`: returns that bin, the number of elements in lower bins and the bin's count.
+// The search is a warp scan: lane l owns bins 8l .. 8l+7.
+__device__ __forceinline__ void select_bin(const uint16_t* hist, int* tot, int tid, int rank, int& bin_out,
+                                           int& below_out, int& count_out, int* bcast) {
+  const uint32_t* h32 = reinterpret_cast<const uint32_t*>(hist);
+  if (tid < kBins) {
+    int sum = 0;
+#pragma unroll 8
+    for (int j = 0; j < kSlots / 2; ++j) {
+      const uint32_t w = h32[tid * (kSlots / 2) + ((j + tid) & (kSlots / 2 - 1))];
+      sum += int(w & 0xffffu) + int(w >> 16);
+    }
+    tot[tid] = sum;
+  }
+  __syncthreads();
+  if (tid < 32) {
+    int c[8], mine = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      c[j] = tot[tid * 8 + j];
+      mine += c[j];
+    }
+    int incl = mine;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int o = __shfl_up_sync(0xffffffffu, incl, d);
+      if (tid >= d) incl += o;
+    }
+    int acc = incl - mine;                       // elements in bins below this lane's first bin
+    const bool here = rank >= acc && rank < incl;
+    if (here) {
+      int b = 0;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        if (b == j && acc + c[j] <= rank) {
+          acc += c[j];
+          b = j + 1;
+        }
+      }
+      b = b > 7 ? 7 : b;
+      bcast[0] = tid * 8 + b;
+      bcast[1] = acc;
+      int cnt = 0;
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        if (j == b) cnt = c[j];
+      bcast[2] = cnt;
+    }
+  }
+  __syncthreads();
+  bin_out = bcast[0];
+  below_out = bcast[1];
+  count_out = bcast[2];
+  __syncthreads();
+}
+
+__device__ __forceinline__ void clear_hist(uint32_t* hist32, int tid) {
+  uint4* h = reinterpret_cast<uint4*>(hist32);
+  for (int i = tid; i < int(kHistBytes / 16); i += kFwdThreads) h[i] = make_uint4(0u, 0u, 0u, 0u);
+  __syncthreads();
+}
+
+// f(bits, element index) for every element of a row; 128-bit loads when the row allows them
+template <bool kVec, int kNT, typename F>
+__device__ __forceinline__ void for_each_elem(const uint16_t* __restrict__ row, int64_t V, int tid, F f) {
+  if (kVec) {
+    const uint4* rv = reinterpret_cast<const uint4*>(row);
+    const int64_t nv = V >> 3;
+    constexpr int kU = 8;                         // independent 128-bit loads in flight per thread
+    for (int64_t v0 = tid; v0 < nv; v0 += kU * kNT) {
+      uint4 q[kU];
+#pragma unroll
+      for (int u = 0; u < kU; ++u)
+        if (v0 + u * kNT < nv) q[u] = __ldg(rv + v0 + u * kNT);
+#pragma unroll
+      for (int u = 0; u < kU; ++u) {
+        const int64_t v = v0 + u * kNT;
+        if (v < nv) {
+          const uint32_t w[4] = {q[u].x, q[u].y, q[u].z, q[u].w};
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            f(w[j] & 0xffffu, v * 8 + 2 * j);
+            f(w[j] >> 16, v * 8 + 2 * j + 1);
+          }
+        }
+      }
+    }
+  } else {
+    for (int64_t i = tid; i < V; i += kNT) f(static_cast<uint32_t>(__ldg(row + i)), i);
+  }
+}
+
+// per-row results kept for the backward: [0] row max, [1] ln S_full, [2] ln S_kept, [3] H_kept,
+// [4] tau key (as float bits), [5] tie weight f
+constexpr int kSaved = 6;
+
+template <bool kIsBF16, bool kVec>
+__global__ void __launch_bounds__(kFwdThreads, 1)
+clamped_entropy_fwd_kernel(const ClampedParams p) {
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  uint16_t* hist = reinterpret_cast<uint16_t*>(smem_raw);
+  // [bin][thread] u16 counters, two threads per 32-bit word; incremented with result-less shared atomics
+  // (no read-modify-write chain through shared memory; a thread's count per row stays below 65536)
+  uint32_t* hist32 = reinterpret_cast<uint32_t*>(smem_raw);
+  const int slot = threadIdx.x & (kSlots - 1);     // threads t and t + 256 share a counter
+  const uint32_t my_inc = (slot & 1) ? 65536u : 1u;
+  __shared__ int tot[kBins];
+  __shared__ int bcast[4];
+  __shared__ float red[kFwdThreads / 32];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const float inv_t = p.inv_temperature;
+  const float c2 = inv_t * kLog2e;
+  for (int64_t row = blockIdx.x; row < p.T; row += gridDim.x) {
+    const uint16_t* x = reinterpret_cast<const uint16_t*>(reinterpret_cast<const char*>(p.logits) + row * p.row_stride_bytes);
+    // ---- pass 1: row max + histogram of the high key byte ----
+    clear_hist(reinterpret_cast<uint32_t*>(hist), tid);
+    uint32_t kmax = 0;                             // the key order is the value order: max on keys
+    for_each_elem<kVec, kFwdThreads>(x, p.V, tid, [&](uint32_t b, int64_t) {
+      const uint32_t key = key16(b);
+      kmax = max(kmax, key);
+      atomicAdd(hist32 + (key >> 8) * (kSlots / 2) + (slot >> 1), my_inc);
+    });
+    const uint32_t bmax = (kmax & 0x8000u) ? (kmax & 0x7fffu) : (~kmax & 0xffffu);
+    const float mx = kmax ? half_to_f32<kIsBF16>(bmax) : -INFINITY;
+    __syncthreads();
+    const float m = block_max<kFwdThreads / 32>(mx, red, warp, lane);
+    uint32_t tau_key = 0;        // keys <= tau_key are candidates for removal
+    float f_tie = 1.f;           // weight of elements with key == tau_key
+    if (p.k > 0) {
+      int hi_bin, below, cnt;
+      select_bin(hist, tot, tid, static_cast<int>(p.k - 1), hi_bin, below, cnt, bcast);
+      // ---- pass 2: histogram of the low key byte inside that bucket ----
+      clear_hist(reinterpret_cast<uint32_t*>(hist), tid);
+      for_each_elem<kVec, kFwdThreads>(x, p.V, tid, [&](uint32_t b, int64_t) {
+        const uint32_t key = key16(b);
+        if (int(key >> 8) == hi_bin) atomicAdd(hist32 + (key & 0xffu) * (kSlots / 2) + (slot >> 1), my_inc);
+      });
+      __syncthreads();
+      int lo_bin, below2, n_tau;
+      select_bin(hist, tot, tid, static_cast<int>(p.k - 1) - below, lo_bin, below2, n_tau, bcast);
+      tau_key = (uint32_t(hi_bin) << 8) | uint32_t(lo_bin);
+      const int removed_at_tau = static_cast<int>(p.k) - (below + below2);        // 1 .. n_tau
+      f_tie = float(n_tau - removed_at_tau) / float(n_tau);
+    }
+    // ---- pass 3: full and clamped softmax sums relative to the row max ----
+    const int64_t lab = p.labels[row];
+    float s_full = 0.f, s_kept = 0.f, w_kept = 0.f, xl = 0.f;
+    for_each_elem<kVec, kFwdThreads>(x, p.V, tid, [&](uint32_t b, int64_t i) {
+      const float xv = half_to_f32<kIsBF16>(b);
+      const float t = (xv - m) * c2;                       // <= 0, log2 units
+      const float e = ex2_approx(t);
+      s_full += e;
+      const uint32_t key = key16(b);
+      const float wgt = p.k == 0 ? 1.f : (key > tau_key ? 1.f : (key == tau_key ? f_tie : 0.f));
+      s_kept = fmaf(wgt, e, s_kept);
+      w_kept = fmaf(wgt * e, t, w_kept);
+      if (i == lab) xl = xv;
+    });
+    const float S = block_sum<kFwdThreads / 32>(s_full, red, warp, lane);
+    const float SK = block_sum<kFwdThreads / 32>(s_kept, red, warp, lane);
+    const float WK = block_sum<kFwdThreads / 32>(w_kept, red, warp, lane);
+    const float XL = block_sum<kFwdThreads / 32>(xl, red, warp, lane);
+    if (tid == 0) {
+      const float ln_s = lg2_approx(S) * kLn2;
+      const float ln_sk = lg2_approx(SK) * kLn2;
+      const bool has_label = lab >= 0 && lab < p.V;
+      p.logp[row] = has_label ? (XL - m) * inv_t - ln_s : __int_as_float(0x7fc00000);
+      const float h = ln_sk - kLn2 * (WK / SK);
+      p.entropy[row] = h;
+      float* sv = p.saved + row * kSaved;
+      sv[0] = m;
+      sv[1] = ln_s;
+      sv[2] = ln_sk;
+      sv[3] = h;
+      sv[4] = __uint_as_float(p.k == 0 ? 0xffffffffu : tau_key);
+      sv[5] = f_tie;
+    }
+  }
+}
+
+// dlogits_i = [ gl * (1[i = label] - p_i) + gh * w_i * (-q_i * (ln q_i + H)) ] / temp
+//   p_i = softmax over the whole row, q_i = softmax over the kept set (w_i = 1, f at tau, 0 removed)
+template <bool kIsBF16, bool kVec>
+__global__ void __launch_bounds__(kCeThreads)
+clamped_entropy_bwd_kernel(const ClampedParams p, const float* __restrict__ g_logp, const float* __restrict__ g_ent,
+                           void* __restrict__ dlogits, int64_t d_row_stride_bytes) {
+  const int tid = threadIdx.x;
+  const float inv_t = p.inv_temperature;
+  const float c2 = inv_t * kLog2e;
+  for (int64_t row = blockIdx.x; row < p.T; row += gridDim.x) {
+    const uint16_t* x = reinterpret_cast<const uint16_t*>(reinterpret_cast<const char*>(p.logits) + row * p.row_stride_bytes);
+    uint16_t* d = reinterpret_cast<uint16_t*>(reinterpret_cast<char*>(dlogits) + row * d_row_stride_bytes);
+    const float gl = (g_logp ? g_logp[row] : 0.f) * inv_t;
+    const float gh = (g_ent ? g_ent[row] : 0.f) * inv_t;
+    const float* sv = p.saved + row * kSaved;
+    const float m = sv[0], ln_s = sv[1], ln_sk = sv[2], h = sv[3], f_tie = sv[5];
+    const uint32_t tau_key = __float_as_uint(sv[4]);
+    const bool no_clamp = tau_key == 0xffffffffu;
+    const float nl2s = -ln_s * kLog2e, nl2sk = -ln_sk * kLog2e;
+    const int64_t lab = p.labels[row];
+    auto grad = [&](uint32_t b, int64_t i) -> uint32_t {
+      const float xv = half_to_f32<kIsBF16>(b);
+      const float t = (xv - m) * c2;
+      float g = 0.f;
+      if (gl != 0.f) {
+        g = -gl * ex2_approx(t + nl2s);
+        if (i == lab) g += gl;
+      }
+      if (gh != 0.f) {
+        const uint32_t key = key16(b);
+        const float wgt = no_clamp ? 1.f : (key > tau_key ? 1.f : (key == tau_key ? f_tie : 0.f));
+        if (wgt != 0.f) {
+          const float lq2 = t + nl2sk;                         // log2 q_i
+          const float q = ex2_approx(lq2);
+          g -= gh * wgt * q * fmaf(lq2, kLn2, h);
+        }
+      }
+      if (kIsBF16) return static_cast<uint32_t>(__bfloat16_as_ushort(__float2bfloat16_rn(g)));
+      return static_cast<uint32_t>(__half_as_ushort(__float2half_rn(g)));
+    };
+    if (gl == 0.f && gh == 0.f) {
+      if (kVec) {
+        uint4* dv = reinterpret_cast<uint4*>(d);
+        for (int64_t v = tid; v < (p.V >> 3); v += kCeThreads) dv[v] = make_uint4(0u, 0u, 0u, 0u);
+      } else {
+        for (int64_t i = tid; i < p.V; i += kCeThreads) d[i] = 0;
+      }
+      continue;
+    }
+    if (kVec) {
+      const uint4* rv = reinterpret_cast<const uint4*>(x);
+      uint4* dv = reinterpret_cast<uint4*>(d);
+      constexpr int kU = 4;
+      const int64_t nv = p.V >> 3;
+      for (int64_t v0 = tid; v0 < nv; v0 += kU * kCeThreads) {
+        uint4 q[kU];
+#pragma unroll
+        for (int u = 0; u < kU; ++u)
+          if (v0 + u * kCeThreads < nv) q[u] = __ldg(rv + v0 + u * kCeThreads);
+#pragma unroll
+        for (int u = 0; u < kU; ++u) {
+          const int64_t v = v0 + u * kCeThreads;
+          if (v < nv) {
+            const uint32_t w[4] = {q[u].x, q[u].y, q[u].z, q[u].w};
+            uint32_t o[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              o[j] = grad(w[j] & 0xffffu, v * 8 + 2 * j) | (grad(w[j] >> 16, v * 8 + 2 * j + 1) << 16);
+            dv[v] = make_uint4(o[0], o[1], o[2], o[3]);
+          }
+        }
+      }
+    } else {
+      for (int64_t i = tid; i < p.V; i += kCeThreads) d[i] = static_cast<uint16_t>(grad(__ldg(x + i), i));
+    }
+  }
+}
+
+bool vec_ok(const void* ptr, int64_t V, int64_t stride_bytes) {
+  return (reinterpret_cast<uintptr_t>(ptr) & 15) == 0 && (V % 8) == 0 && (stride_bytes % 16) == 0;
+}
+
+}  // namespace
+
+int launch_clamped_entropy_fwd(const ClampedParams& p, cudaStream_t stream) {
+  if (p.T == 0) return kOk;
+  const bool vec = vec_ok(p.logits, p.V, p.row_stride_bytes);
+  const int64_t cap = num_sms();
+  const unsigned int grid = static_cast<unsigned int>(p.T < cap ? p.T : cap);
+#define AB_CE_FWD(BF, VEC)                                                                                    \
+  {                                                                                                           \
+    AB_CUDA(cudaFuncSetAttribute(clamped_entropy_fwd_kernel<BF, VEC>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                 int(kHistBytes)));                                                           \
+    clamped_entropy_fwd_kernel<BF, VEC><<<grid, kFwdThreads, kHistBytes, stream>>>(p);                         \
+  }
+  if (p.dtype == kBF16) { if (vec) AB_CE_FWD(true, true) else AB_CE_FWD(true, false) }
+  else { if (vec) AB_CE_FWD(false, true) else AB_CE_FWD(false, false) }
+#undef AB_CE_FWD
+  return check_launch("clamped_entropy_fwd");
+}
+
+int launch_clamped_entropy_bwd(const ClampedParams& p, const float* g_logp, const float* g_ent, void* dlogits,
+                               int64_t d_row_stride_bytes, cudaStream_t stream) {
+  if (p.T == 0) return kOk;
+  const bool vec = vec_ok(p.logits, p.V, p.row_stride_bytes) && vec_ok(dlogits, p.V, d_row_stride_bytes);
+  const int64_t cap = int64_t(num_sms()) * 8;
+  const unsigned int grid = static_cast<unsigned int>(p.T < cap ? p.T : cap);
+#define AB_CE_BWD(BF, VEC) \
+  clamped_entropy_bwd_kernel<BF, VEC><<<grid, kCeThreads, 0, stream>>>(p, g_logp, g_ent, dlogits, d_row_stride_bytes);
+  if (p.dtype == kBF16) { if (vec) AB_CE_BWD(true, true) else AB_CE_BWD(true, false) }
+  else { if (vec) AB_CE_BWD(false, true) else AB_CE_BWD(false, false) }
+#undef AB_CE_BWD
+  return check_launch("clamped_entropy_bwd");
+}
+
+}  // namespace ab

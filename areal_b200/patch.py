@@ -88,6 +88,15 @@ def patch_areal(extra_modules=()):
             from . import actor as _A
             mod.grpo_loss_fn = _A.grpo_loss_fn
             patched.append("areal.engine.ppo.actor.grpo_loss_fn")
+    # AEnt recipe: clamped entropy without the CPU top-k (recipe/AEnt/functional.py, actor.py:21)
+    from . import aent_functional as _AE
+    for name in ("recipe.AEnt.functional", "recipe.AEnt.actor"):
+        m = sys.modules.get(name)
+        if m is not None and hasattr(m, "gather_logprobs_clamped_entropy"):
+            m.gather_logprobs_clamped_entropy = _AE.gather_logprobs_clamped_entropy
+            if hasattr(m, "clamped_softmax_entropy"):
+                m.clamped_softmax_entropy = _AE.clamped_softmax_entropy
+            patched.append(name)
     for name in tuple(_AREAL_IMPORT_SITES) + tuple(extra_modules):
         mod = sys.modules.get(name)
         if mod is None:

@@ -305,9 +305,51 @@ def bench_advantages(out):
                        tokens_per_s=B * S / (msr * 1e-3)))
 
 
+def bench_aent(out):
+    """AEnt clamped entropy: log-prob + clamped entropy forward and its backward at the bench shape; the
+    reference's path (recipe/AEnt/functional.py:15-52: CPU top-k on a copy of the logits, [T,V] mask and
+    temporaries) restated with torch ops on a 256-row sample."""
+    from areal_b200 import aent_functional as A
+    T, V = 16384, 151936
+    g = torch.Generator(device=DEV).manual_seed(0)
+    x = torch.empty(T, V, dtype=torch.bfloat16, device=DEV)
+    for i in range(0, T, 2048):
+        x[i:i + 2048] = (torch.randn(2048, V, generator=g, device=DEV) * 2).bfloat16()
+    lab = torch.randint(0, V, (T,), generator=g, device=DEV)
+    w = torch.randn(T, generator=g, device=DEV)
+    xr = x.requires_grad_()
+    ms = timeit(lambda: A.gather_logprobs_clamped_entropy(xr, lab, 0.3, 1.0), iters=10, warmup=3)
+    out.append(row("clamped entropy fwd (logp + clamped H, clamp 0.3)", ms, 2.0 * T * V, T=T, V=V,
+                   tokens_per_s=T / (ms * 1e-3)))
+
+    def fb():
+        xr.grad = None
+        lp, h = A.gather_logprobs_clamped_entropy(xr, lab, 0.3, 1.0)
+        ((lp * w).sum() + (h * w).sum()).backward()
+    ms2 = timeit(fb, iters=10, warmup=3)
+    out.append(row("clamped entropy fwd+bwd", ms2, 6.0 * T * V, T=T, V=V, tokens_per_s=T / (ms2 * 1e-3)))
+    Ts = 256
+    xs = x[:Ts].detach()
+
+    def ref():
+        z = xs.float()
+        lc = z.cpu()
+        k = int(V * 0.3)
+        _, idx = torch.topk(lc, k=k, dim=-1, largest=False)
+        rm = torch.zeros_like(lc, dtype=torch.bool)
+        rm[torch.arange(Ts).unsqueeze(1), idx] = True
+        rm = rm.to(DEV)
+        cl = z.masked_fill(rm, -torch.inf)
+        lpz = torch.where(rm, 0.0, torch.log_softmax(cl, dim=-1))
+        return -torch.sum(torch.softmax(cl, dim=-1) * lpz, dim=-1)
+    msr = timeit(ref, iters=3, warmup=1)
+    out.append(row("reference clamped entropy forward (CPU top-k path), 256 rows", msr, 2.0 * Ts * V, T=Ts, V=V,
+                   tokens_per_s=Ts / (msr * 1e-3), speedup_ours=(msr / Ts) / (ms / T)))
+
+
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--what", default="gae,padded,advantages,loss,logits,intervals")
+    ap.add_argument("--what", default="gae,padded,advantages,aent,loss,logits,intervals")
     ap.add_argument("--out", default=None)
     args = ap.parse_args()
     what = set(args.what.split(","))
@@ -320,6 +362,8 @@ def main():
         bench_padded(out)
     if "advantages" in what:
         bench_advantages(out)
+    if "aent" in what:
+        bench_aent(out)
     if "loss" in what:
         bench_loss(out)
     if "logits" in what:

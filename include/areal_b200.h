@@ -361,6 +361,28 @@ AREAL_B200_API int areal_b200_vocab_combine_p2p(void* const* peer_bases, int ran
                                                 float* entropy, float* row_max, float* ln_sumexp,
                                                 int* status, void* stream);
 
+/* Token log-prob + CLAMPED softmax entropy of the AEnt recipe, and their gradient.  Replaces
+ * `gather_logprobs_clamped_entropy` / `clamped_softmax_entropy` (recipe/AEnt/functional.py:15-80): the
+ * k = int(V * entropy_clamp) smallest logits of every row are left out of the entropy's softmax.  The
+ * reference finds them with a top-k on a CPU copy of the logits (:18-27).
+ *   logits [T,V] bf16 (dtype 0) or fp16 (dtype 1), rows `row_stride` elements apart; labels i64[T];
+ *   k_removed in [0, V).  Outputs logp f32[T] (full softmax, as gather_logprobs), entropy f32[T]
+ *   (clamped), saved f32[T,6] (row max, ln S, ln S_kept, H, threshold key, tie weight) for the backward.
+ *   Logits equal to the threshold value are interchangeable: each carries the weight
+ *   (n_tie - removed_tie) / n_tie in the sums and in the gradient (the reference's top-k removes some
+ *   `removed_tie` of them, which ones is unspecified).
+ *   backward: dlogits (same dtype / shape) = d(sum g_logp*logp + g_entropy*entropy)/dlogits;
+ *   g_logp / g_entropy f32[T], either may be NULL. */
+AREAL_B200_API int areal_b200_clamped_entropy_fwd(const void* logits, int dtype, int64_t T, int64_t V,
+                                                  int64_t row_stride, const int64_t* labels,
+                                                  double temperature, int64_t k_removed, float* logp,
+                                                  float* entropy, float* saved, void* stream);
+AREAL_B200_API int areal_b200_clamped_entropy_bwd(const void* logits, int dtype, int64_t T, int64_t V,
+                                                  int64_t row_stride, const int64_t* labels,
+                                                  double temperature, const float* saved,
+                                                  const float* g_logp, const float* g_entropy,
+                                                  void* dlogits, int64_t d_row_stride, void* stream);
+
 /* Legacy running value statistics.  Replaces the arithmetic of `ExponentialRunningMeanStd` /
  * `MovingAverageRunningMeanStd` (realhf/impl/model/modules/rms.py:19-183): update = three reductions
  * + ~10 scalar kernels there; here areal_b200_masked_moments (one group) followed by

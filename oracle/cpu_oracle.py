@@ -717,3 +717,64 @@ class RunningMeanStd:
     def denormalize(self, x):
         mean, std = self.mean_std()
         return (np.asarray(x).astype(self.dt) * std + mean).astype(np.float32)                   # :104-108
+
+
+# --------------------------------------------------------------------------------------------------
+# AEnt clamped entropy (recipe/AEnt/functional.py:15-52)
+# --------------------------------------------------------------------------------------------------
+def clamped_weights(logits_row, k: int):
+    """Weight of each element in the clamped softmax: 0 for the k smallest, 1 for the rest; the elements
+    equal to the k-th smallest value share the kept count equally (top-k's tie-break is unspecified,
+    recipe/AEnt/functional.py:22)."""
+    x = np.asarray(logits_row, dtype=np.float64)
+    w = np.ones_like(x)
+    if k <= 0:
+        return w
+    tau = np.partition(x, k - 1)[k - 1]
+    less = x < tau
+    ties = x == tau
+    removed_at_tau = k - int(less.sum())
+    w[less] = 0.0
+    w[ties] = (int(ties.sum()) - removed_at_tau) / int(ties.sum())
+    return w
+
+
+def gather_logprobs_clamped_entropy(logits, labels, entropy_clamp: float, temperature: float = 1.0):
+    """(log-prob of the labels under the full softmax, clamped entropy) in float64 (:39-52); the masked
+    elements contribute p*0 to the entropy sum (:30-33)."""
+    z = np.asarray(logits, dtype=np.float64) / temperature
+    T, V = z.shape
+    k = int(V * entropy_clamp)                                             # :21
+    m = z.max(-1, keepdims=True)
+    lse = m[:, 0] + np.log(np.exp(z - m).sum(-1))
+    logp = z[np.arange(T), labels] - lse
+    ent = np.empty(T)
+    for t in range(T):
+        w = clamped_weights(z[t], k)
+        e = w * np.exp(z[t] - m[t])
+        q = e / e.sum()
+        lq = (z[t] - m[t]) - np.log(e.sum())
+        ent[t] = -(q * np.where(w > 0, lq, 0.0)).sum()
+    return logp, ent
+
+
+def clamped_entropy_dlogits(logits, labels, entropy_clamp, temperature, g_logp, g_ent):
+    """d(sum g_logp*logp + g_ent*H_clamped)/dlogits in float64, ties sharing their weight."""
+    z = np.asarray(logits, dtype=np.float64) / temperature
+    T, V = z.shape
+    k = int(V * entropy_clamp)
+    out = np.zeros_like(z)
+    for t in range(T):
+        m = z[t].max()
+        p = np.exp(z[t] - m)
+        p /= p.sum()
+        g = -g_logp[t] * p
+        g[labels[t]] += g_logp[t]
+        w = clamped_weights(z[t], k)
+        e = w * np.exp(z[t] - m)
+        q = e / e.sum()
+        lq = (z[t] - m) - np.log(e.sum())
+        h = -(q * np.where(w > 0, lq, 0.0)).sum()
+        g += g_ent[t] * np.where(w > 0, -q * (lq + h), 0.0)
+        out[t] = g / temperature
+    return out

@@ -531,6 +531,30 @@ def gen_rms():
     print("rms golden:", k, "cases")
 
 
+def gen_clamped_entropy():
+    """gather_logprobs_clamped_entropy (recipe/AEnt/functional.py:39-52) and its autograd gradient, run
+    unmodified on CPU.  bf16 logits (few distinct values: ties at the threshold are the rule)."""
+    _, gather = R.load_aent_functional()
+    g = torch.Generator().manual_seed(4711)
+    z = {}
+    k = 0
+    for (T, V), clamp, temp in (((12, 1000), 0.1, 1.0), ((12, 1000), 0.5, 0.7), ((6, 4096), 0.9, 1.0),
+                                ((3, 151936), 0.3, 1.0), ((5, 777), 0.0, 1.3), ((4, 64), 0.25, 1.0)):
+        logits = (torch.randn(T, V, generator=g) * 3).bfloat16()
+        labels = torch.randint(0, V, (T,), generator=g)
+        w_lp, w_h = torch.randn(T, generator=g), torch.randn(T, generator=g)
+        x = logits.float().requires_grad_()
+        lp, ent = gather(x, labels, clamp, temp)
+        ((lp * w_lp).sum() + (ent * w_h).sum()).backward()
+        z.update({f"c{k}_logits_bits": bf16_bits(logits.reshape(-1)).reshape(T, V), f"c{k}_labels": labels.numpy(),
+                  f"c{k}_cfg": np.array([clamp, temp]), f"c{k}_w_lp": w_lp.numpy(), f"c{k}_w_h": w_h.numpy(),
+                  f"c{k}_logp": lp.detach().numpy(), f"c{k}_ent": ent.detach().numpy(), f"c{k}_grad": x.grad.numpy()})
+        k += 1
+    z["n_cases"] = np.array(k)
+    np.savez_compressed(os.path.join(OUT, "clamped_entropy.npz"), **z)
+    print("clamped_entropy golden:", k, "cases")
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     assert R.available(), "needs /root/reference"
@@ -551,6 +575,7 @@ def main():
     gen_grpo_stats()
     gen_packed_rewards(pf)
     gen_rms()
+    gen_clamped_entropy()
 
 
 if __name__ == "__main__":

@@ -320,3 +320,21 @@ def load_realhf_rms():
                 sys.modules.pop(k, None)
             else:
                 sys.modules[k] = v
+
+
+def load_aent_functional():
+    """`clamped_softmax_entropy` / `_gather_logprobs_clamped_entropy` (recipe/AEnt/functional.py:15-52),
+    extracted by AST with the `@torch.compile` decorators dropped and executed where they lie.
+    Returns (clamped_softmax_entropy, gather_fn(logits, labels, entropy_clamp, temperature))."""
+    import ast
+
+    import torch
+    import torch.nn.functional as F
+    with open(os.path.join(REF_ROOT, "recipe/AEnt/functional.py")) as f:
+        src = f.read()
+    ns = dict(torch=torch, F=F)
+    for name in ("clamped_softmax_entropy", "_gather_logprobs_clamped_entropy"):
+        node = next(n for n in ast.parse(src).body if isinstance(n, ast.FunctionDef) and n.name == name)
+        node.decorator_list = []
+        exec(compile(ast.unparse(node), f"AEnt/functional.py[{name}]", "exec"), ns)
+    return ns["clamped_softmax_entropy"], ns["_gather_logprobs_clamped_entropy"]

@@ -296,3 +296,15 @@ def test_running_mean_std_oracle_vs_reference():
             np.testing.assert_allclose(std, z[f"c{k}_std{step}"][0], rtol=tol, atol=tol)
             np.testing.assert_allclose(mod.normalize(z["probe"]), z[f"c{k}_norm{step}"], rtol=3e-6, atol=3e-6)
             np.testing.assert_allclose(mod.denormalize(z["probe"]), z[f"c{k}_denorm{step}"], rtol=3e-6, atol=3e-6)
+
+
+def test_clamped_entropy_oracle_vs_reference():
+    """oracle == gather_logprobs_clamped_entropy + autograd run unmodified (recipe/AEnt/functional.py)."""
+    from tests import clamp_cases as CC
+    for c in CC.load():
+        x = H.bf16_from_bits(c["bits"]).float().numpy()
+        lp, ent = O.gather_logprobs_clamped_entropy(x, c["labels"], c["clamp"], c["temp"])
+        np.testing.assert_allclose(lp, c["logp"], rtol=2e-5, atol=2e-5)
+        np.testing.assert_allclose(ent, c["ent"], rtol=2e-5, atol=2e-5)
+        g = O.clamped_entropy_dlogits(x, c["labels"], c["clamp"], c["temp"], c["w_lp"], c["w_h"])
+        CC.check_grad(g, c["grad"].astype(np.float64), x, c["clamp"], 2e-5, "oracle")
