@@ -126,6 +126,11 @@ __device__ __forceinline__ void clear_hist(uint32_t* hist32, int tid) {
   __syncthreads();
 }
 
+// result-less add on a 32-bit SHARED address (RED.shared: no generic-address path, nothing to wait for)
+__device__ __forceinline__ void red_shared_add(uint32_t saddr, uint32_t v) {
+  asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(saddr), "r"(v) : "memory");
+}
+
 // f(bits, element index) for every element of a row; 128-bit loads when the row allows them
 template <bool kVec, int kNT, typename F>
 __device__ __forceinline__ void for_each_elem(const uint16_t* __restrict__ row, int64_t V, int tid, F f) {
@@ -167,9 +172,10 @@ clamped_entropy_fwd_kernel(const ClampedParams p) {
   uint16_t* hist = reinterpret_cast<uint16_t*>(smem_raw);
   // [bin][thread] u16 counters, two threads per 32-bit word; incremented with result-less shared atomics
   // (no read-modify-write chain through shared memory; a thread's count per row stays below 65536)
-  uint32_t* hist32 = reinterpret_cast<uint32_t*>(smem_raw);
   const int slot = threadIdx.x & (kSlots - 1);     // threads t and t + 256 share a counter
   const uint32_t my_inc = (slot & 1) ? 65536u : 1u;
+  static_assert(kSlots / 2 * 4 == 512, "a bin is 512 bytes of counters");
+  const uint32_t my_word = smem_u32(smem_raw) + uint32_t(slot >> 1) * 4u;       // + bin * 512
   __shared__ int tot[kBins];
   __shared__ int bcast[4];
   __shared__ float red[kFwdThreads / 32];
@@ -184,7 +190,7 @@ clamped_entropy_fwd_kernel(const ClampedParams p) {
     for_each_elem<kVec, kFwdThreads>(x, p.V, tid, [&](uint32_t b, int64_t) {
       const uint32_t key = key16(b);
       kmax = max(kmax, key);
-      atomicAdd(hist32 + (key >> 8) * (kSlots / 2) + (slot >> 1), my_inc);
+      red_shared_add(my_word + ((key >> 8) << 9), my_inc);
     });
     const uint32_t bmax = (kmax & 0x8000u) ? (kmax & 0x7fffu) : (~kmax & 0xffffu);
     const float mx = kmax ? half_to_f32<kIsBF16>(bmax) : -INFINITY;
@@ -199,7 +205,7 @@ clamped_entropy_fwd_kernel(const ClampedParams p) {
       clear_hist(reinterpret_cast<uint32_t*>(hist), tid);
       for_each_elem<kVec, kFwdThreads>(x, p.V, tid, [&](uint32_t b, int64_t) {
         const uint32_t key = key16(b);
-        if (int(key >> 8) == hi_bin) atomicAdd(hist32 + (key & 0xffu) * (kSlots / 2) + (slot >> 1), my_inc);
+        if (int(key >> 8) == hi_bin) red_shared_add(my_word + ((key & 0xffu) << 9), my_inc);
       });
       __syncthreads();
       int lo_bin, below2, n_tau;
@@ -210,8 +216,9 @@ clamped_entropy_fwd_kernel(const ClampedParams p) {
     }
     // ---- pass 3: full and clamped softmax sums relative to the row max ----
     const int64_t lab = p.labels[row];
-    float s_full = 0.f, s_kept = 0.f, w_kept = 0.f, xl = 0.f;
-    for_each_elem<kVec, kFwdThreads>(x, p.V, tid, [&](uint32_t b, int64_t i) {
+    float s_full = 0.f, s_kept = 0.f, w_kept = 0.f;
+    const float xl = (tid == 0 && lab >= 0 && lab < p.V) ? half_to_f32<kIsBF16>(__ldg(x + lab)) : 0.f;
+    for_each_elem<kVec, kFwdThreads>(x, p.V, tid, [&](uint32_t b, int64_t) {
       const float xv = half_to_f32<kIsBF16>(b);
       const float t = (xv - m) * c2;                       // <= 0, log2 units
       const float e = ex2_approx(t);
@@ -220,7 +227,6 @@ clamped_entropy_fwd_kernel(const ClampedParams p) {
       const float wgt = p.k == 0 ? 1.f : (key > tau_key ? 1.f : (key == tau_key ? f_tie : 0.f));
       s_kept = fmaf(wgt, e, s_kept);
       w_kept = fmaf(wgt * e, t, w_kept);
-      if (i == lab) xl = xv;
     });
     const float S = block_sum<kFwdThreads / 32>(s_full, red, warp, lane);
     const float SK = block_sum<kFwdThreads / 32>(s_kept, red, warp, lane);
