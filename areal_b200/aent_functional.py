@@ -34,7 +34,7 @@ class _ClampedEntropy(torch.autograd.Function):
             raise ValueError(f"entropy_clamp={entropy_clamp} removes {k} of {V} logits; need 0 <= k < V")
         f32 = dict(dtype=torch.float32, device=dev)
         logp, ent = torch.empty(T, **f32), torch.empty(T, **f32)
-        saved = torch.empty(T, 6, **f32)
+        saved = torch.empty(T, 8, **f32)
         with torch.cuda.device(dev):
             call("areal_b200_clamped_entropy_fwd", ptr(x), _lib.DTYPE_CODE[x.dtype], T, V, x.stride(0) if T > 1 else V,
                  ptr(lab), float(temperature), k, ptr(logp), ptr(ent), ptr(saved), stream_ptr(dev))
@@ -42,10 +42,12 @@ class _ClampedEntropy(torch.autograd.Function):
         ctx.temperature = float(temperature)
         ctx.in_shape = logits.shape
         ctx.set_materialize_grads(False)
-        return logp.view(lead), ent.view(lead)
+        row_max, row_min = saved[:, 0].view(lead), saved[:, 6].view(lead)
+        ctx.mark_non_differentiable(row_max, row_min)
+        return logp.view(lead), ent.view(lead), row_max, row_min
 
     @staticmethod
-    def backward(ctx, g_logp, g_ent):
+    def backward(ctx, g_logp, g_ent, *unused):
         x, lab, saved = ctx.saved_tensors
         if g_logp is None and g_ent is None:
             return None, None, None, None
@@ -66,7 +68,7 @@ def gather_logprobs_clamped_entropy(logits: torch.Tensor, labels: torch.Tensor, 
     `labels` under the full softmax, entropy of the softmax with the `int(V * entropy_clamp)` smallest
     logits of each row masked out), both f32 with the shape of `labels`, differentiable w.r.t. `logits`.
     `chunk_size` is accepted for signature compatibility (rows are streamed; no chunking needed)."""
-    return _ClampedEntropy.apply(logits, labels, entropy_clamp, temperature)
+    return _ClampedEntropy.apply(logits, labels, entropy_clamp, temperature)[:2]
 
 
 def clamped_softmax_entropy(logits: torch.Tensor, entropy_clamp: float) -> torch.Tensor:
@@ -74,3 +76,58 @@ def clamped_softmax_entropy(logits: torch.Tensor, entropy_clamp: float) -> torch
     by the temperature, as the reference calls it (:48-50)."""
     labels = torch.zeros(logits.shape[:-1], dtype=torch.long, device=logits.device)
     return _ClampedEntropy.apply(logits, labels, entropy_clamp, 1.0)[1]
+
+
+def clamped_entropy_loss_fn(clamped_entropy: torch.Tensor, loss_mask: torch.Tensor) -> torch.Tensor:
+    """Drop-in for `clamped_entropy_loss_fn` (recipe/AEnt/actor.py:273-278): masked mean of the clamped
+    entropy; `loss_mask.count_nonzero() or 1` without the host sync."""
+    m = loss_mask.bool()
+    count = torch.clamp(m.sum(), min=1)
+    return torch.where(m, clamped_entropy, 0.0).sum() / count
+
+
+def aent_grpo_loss_fn(logits: torch.Tensor, input_data: dict, temperature: float, eps_clip: float,
+                      entropy_coeff: float, entropy_clamp: float, eps_clip_higher: float | None,
+                      c_clip: float | None, behav_imp_weight_cap: float | None, tracker=None):
+    """Drop-in for `aent_grpo_loss_fn` (recipe/AEnt/actor.py:185-270): PPO actor loss minus
+    `entropy_coeff` times the masked mean clamped entropy, the same keys recorded in the stats tracker.
+    The logits are read by the clamped-entropy kernel only (its row max / min feed the vocab statistics);
+    with `entropy_clamp == 0` the fused forward of `areal_b200.functional` is used, as upstream does (:207-212)."""
+    from . import functional as F
+    from . import stats_tracker as ST
+    from .actor import _all_tokens
+    tracker = ST.DEFAULT_TRACKER if tracker is None else tracker
+    labels = input_data.get("rolled_input_ids", None)
+    if labels is None:
+        labels = torch.roll(input_data["input_ids"], shifts=-1, dims=-1)
+    old_logp = input_data["logprobs"]
+    advantages = input_data["advantages"]
+    loss_mask = input_data.get("full_loss_mask", input_data["loss_mask"]).bool()
+    prox_logp = input_data["prox_logp"]
+    if entropy_clamp > 0:
+        logprobs, ent, vmax, vmin = _ClampedEntropy.apply(logits, labels, entropy_clamp, temperature)
+    else:
+        st = F.logits_stats(logits.detach(), labels, temperature)
+        logprobs, ent = F.gather_logprobs_entropy(logits, labels, temperature)
+        vmax, vmin = st["vocab_max_logits"], st["vocab_min_logits"]
+    ppo_loss, stat = F.ppo_actor_loss_fn(logprobs=logprobs, old_logprobs=old_logp, advantages=advantages,
+                                         eps_clip=eps_clip, eps_clip_higher=eps_clip_higher, loss_mask=loss_mask,
+                                         c_clip=c_clip, proximal_logprobs=prox_logp,
+                                         behav_imp_weight_cap=behav_imp_weight_cap)
+    loss = ppo_loss - entropy_coeff * clamped_entropy_loss_fn(ent, loss_mask)
+    old_f = old_logp if old_logp.dtype == torch.float32 else old_logp.float()
+    lp_d = logprobs.detach()
+    denominators = dict(n_tokens=_all_tokens(logits.shape[0], logits.device), n_valid_tokens=loss_mask,
+                        clipped_tokens=stat["clip_mask"], dual_clipped_tokens=stat["dual_clip_mask"])
+    stats = [("n_valid_tokens", dict(importance_weight=stat["importance_weight"], approx_kl=stat["approx_kl"],
+                                     new_logp=lp_d, old_logp=old_f, entropy=ent.detach().float(),
+                                     actor_loss=stat["loss"], clip_ratio=stat["clip_mask"],
+                                     dual_clip_ratio=stat["dual_clip_mask"]))]
+    if "behave_imp_weight" in stat:
+        denominators["unclipped_behave_tokens"] = stat["behave_mask"]
+        stats.append(("unclipped_behave_tokens", dict(behave_imp_weight=stat["behave_imp_weight"],
+                                                      behave_approx_kl=stat["behave_approx_kl"])))
+    stats.append(("n_tokens", dict(vocab_min_logits=vmin.float(), vocab_max_logits=vmax.float())))
+    stats.append(("clipped_tokens", dict(clipped_new_logp=lp_d, clipped_old_logp=old_f)))
+    tracker.record(denominators, stats)
+    return loss

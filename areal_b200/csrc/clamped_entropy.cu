@@ -162,8 +162,8 @@ __device__ __forceinline__ void for_each_elem(const uint16_t* __restrict__ row, 
 }
 
 // per-row results kept for the backward: [0] row max, [1] ln S_full, [2] ln S_kept, [3] H_kept,
-// [4] tau key (as float bits), [5] tie weight f
-constexpr int kSaved = 6;
+// [4] tau key (as float bits), [5] tie weight f, [6] row min, [7] unused
+constexpr int kSaved = 8;
 
 template <bool kIsBF16, bool kVec>
 __global__ void __launch_bounds__(kFwdThreads, 1)
@@ -186,16 +186,19 @@ clamped_entropy_fwd_kernel(const ClampedParams p) {
     const uint16_t* x = reinterpret_cast<const uint16_t*>(reinterpret_cast<const char*>(p.logits) + row * p.row_stride_bytes);
     // ---- pass 1: row max + histogram of the high key byte ----
     clear_hist(reinterpret_cast<uint32_t*>(hist), tid);
-    uint32_t kmax = 0;                             // the key order is the value order: max on keys
+    uint32_t kmax = 0, kmin = 0xffffu;             // the key order is the value order: max / min on keys
     for_each_elem<kVec, kFwdThreads>(x, p.V, tid, [&](uint32_t b, int64_t) {
       const uint32_t key = key16(b);
       kmax = max(kmax, key);
+      kmin = min(kmin, key);
       red_shared_add(my_word + ((key >> 8) << 9), my_inc);
     });
     const uint32_t bmax = (kmax & 0x8000u) ? (kmax & 0x7fffu) : (~kmax & 0xffffu);
     const float mx = kmax ? half_to_f32<kIsBF16>(bmax) : -INFINITY;
+    const uint32_t bmin = (kmin & 0x8000u) ? (kmin & 0x7fffu) : (~kmin & 0xffffu);
     __syncthreads();
     const float m = block_max<kFwdThreads / 32>(mx, red, warp, lane);
+    const float row_min = -block_max<kFwdThreads / 32>(-half_to_f32<kIsBF16>(bmin), red, warp, lane);
     uint32_t tau_key = 0;        // keys <= tau_key are candidates for removal
     float f_tie = 1.f;           // weight of elements with key == tau_key
     if (p.k > 0) {
@@ -246,6 +249,8 @@ clamped_entropy_fwd_kernel(const ClampedParams p) {
       sv[3] = h;
       sv[4] = __uint_as_float(p.k == 0 ? 0xffffffffu : tau_key);
       sv[5] = f_tie;
+      sv[6] = row_min;
+      sv[7] = 0.f;
     }
   }
 }

@@ -96,6 +96,9 @@ def patch_areal(extra_modules=()):
             m.gather_logprobs_clamped_entropy = _AE.gather_logprobs_clamped_entropy
             if hasattr(m, "clamped_softmax_entropy"):
                 m.clamped_softmax_entropy = _AE.clamped_softmax_entropy
+            for fn in ("aent_grpo_loss_fn", "clamped_entropy_loss_fn"):
+                if hasattr(m, fn):
+                    setattr(m, fn, getattr(_AE, fn))
             patched.append(name)
     for name in tuple(_AREAL_IMPORT_SITES) + tuple(extra_modules):
         mod = sys.modules.get(name)

@@ -367,7 +367,8 @@ AREAL_B200_API int areal_b200_vocab_combine_p2p(void* const* peer_bases, int ran
  * reference finds them with a top-k on a CPU copy of the logits (:18-27).
  *   logits [T,V] bf16 (dtype 0) or fp16 (dtype 1), rows `row_stride` elements apart; labels i64[T];
  *   k_removed in [0, V).  Outputs logp f32[T] (full softmax, as gather_logprobs), entropy f32[T]
- *   (clamped), saved f32[T,6] (row max, ln S, ln S_kept, H, threshold key, tie weight) for the backward.
+ *   (clamped), saved f32[T,8] (row max, ln S, ln S_kept, H, threshold key, tie weight, row min, 0) for
+ *   the backward and the vocab_min / vocab_max statistics.
  *   Logits equal to the threshold value are interchangeable: each carries the weight
  *   (n_tie - removed_tie) / n_tie in the sums and in the gradient (the reference's top-k removes some
  *   `removed_tie` of them, which ones is unspecified).

@@ -555,6 +555,29 @@ def gen_clamped_entropy():
     print("clamped_entropy golden:", k, "cases")
 
 
+def gen_aent_stats():
+    """aent_grpo_loss_fn + tracker export (recipe/AEnt/actor.py:185-270) run unmodified over the micro-batches of
+    gen_grpo_stats (inputs shared with grpo_stats.npz), entropy_clamp 0.25 and 0."""
+    fn, st = R.load_aent_grpo_loss_fn()
+    z = {}
+    for ai, (coeff, clamp) in enumerate(((0.01, 0.25), (0.002, 0.0))):
+        tr = st.DistributedStatsTracker()
+        st.denominator, st.stat = tr.denominator, tr.stat
+        losses = []
+        with tr.scope("aent"):
+            for mb in range(3):
+                c = grpo_case(mb)
+                d = {k: v for k, v in c.items() if k != "logits"}
+                losses.append(float(fn(c["logits"].float(), d, entropy_coeff=coeff, entropy_clamp=clamp, **GRPO_ARGS[1])))
+        out = tr.export()
+        z[f"a{ai}_cfg"] = np.array([coeff, clamp])
+        z[f"a{ai}_losses"] = np.array(losses)
+        z[f"a{ai}_keys"] = np.array(sorted(out.keys()))
+        z[f"a{ai}_vals"] = np.array([out[k] for k in sorted(out.keys())], dtype=np.float64)
+    np.savez_compressed(os.path.join(OUT, "aent_stats.npz"), **z)
+    print("aent_stats golden:", len(out), "keys, losses", losses)
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     assert R.available(), "needs /root/reference"
@@ -576,6 +599,7 @@ def main():
     gen_packed_rewards(pf)
     gen_rms()
     gen_clamped_entropy()
+    gen_aent_stats()
 
 
 if __name__ == "__main__":

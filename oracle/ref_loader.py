@@ -338,3 +338,29 @@ def load_aent_functional():
         node.decorator_list = []
         exec(compile(ast.unparse(node), f"AEnt/functional.py[{name}]", "exec"), ns)
     return ns["clamped_softmax_entropy"], ns["_gather_logprobs_clamped_entropy"]
+
+
+def load_aent_grpo_loss_fn():
+    """`aent_grpo_loss_fn` + `clamped_entropy_loss_fn` (recipe/AEnt/actor.py:185-278) bound to the reference's own
+    `gather_logprobs_clamped_entropy` (recipe/AEnt/functional.py:54-86, Ulysses world size stubbed to 1),
+    areal functional and stats_tracker.  Returns (fn, stats_tracker module)."""
+    import ast
+    from typing import Dict
+
+    import torch
+    import torch.nn.functional as F
+    af = load_areal_functional()
+    st = load_areal_stats_tracker()
+    _, inner = load_aent_functional()
+    ns = dict(torch=torch, F=F, Dict=Dict, _gather_logprobs_clamped_entropy=inner,
+              get_ulysses_sequence_parallel_world_size=lambda: 1, get_ulysses_sequence_parallel_group=lambda: None,
+              gather_logprobs_entropy=af.gather_logprobs_entropy, ppo_actor_loss_fn=af.ppo_actor_loss_fn,
+              stats_tracker=st)
+    for path, name in (("recipe/AEnt/functional.py", "gather_logprobs_clamped_entropy"),
+                       ("recipe/AEnt/actor.py", "clamped_entropy_loss_fn"), ("recipe/AEnt/actor.py", "aent_grpo_loss_fn")):
+        with open(os.path.join(REF_ROOT, path)) as f:
+            src = f.read()
+        node = next(n for n in ast.parse(src).body if isinstance(n, ast.FunctionDef) and n.name == name)
+        node.decorator_list = []
+        exec(compile(ast.unparse(node), f"AEnt[{name}]", "exec"), ns)
+    return ns["aent_grpo_loss_fn"], st

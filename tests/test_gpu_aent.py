@@ -75,3 +75,32 @@ def test_clamped_entropy_errors_and_zero_clamp():
         A.gather_logprobs_clamped_entropy(x.float(), lab, 0.1, 1.0)
     with pytest.raises(Exception):
         A.gather_logprobs_clamped_entropy(x.cpu(), lab.cpu(), 0.1, 1.0)
+
+
+@pytest.mark.parametrize("ai", [0, 1])
+def test_aent_grpo_loss_fn_and_export_vs_reference(ai):
+    """aent_grpo_loss_fn over three micro-batches (one fully masked) + tracker export: the reference's
+    losses and every exported key (inputs shared with tests/golden/grpo_stats.npz)."""
+    from areal_b200 import aent_functional as A
+    from areal_b200 import stats_tracker as ST
+    from tests.test_gpu_stats import GRPO_ARGS, load_mb
+    zin, z = H.load("grpo_stats.npz"), H.load("aent_stats.npz")
+    coeff, clamp = [float(v) for v in z[f"a{ai}_cfg"]]
+    tr = ST.DistributedStatsTracker()
+    losses = []
+    with tr.scope("aent"):
+        for mb in range(3):
+            c = load_mb(zin, mb)
+            logits = c.pop("logits").requires_grad_(mb == 0)
+            loss = A.aent_grpo_loss_fn(logits, c, entropy_coeff=coeff, entropy_clamp=clamp, tracker=tr, **GRPO_ARGS[1])
+            if mb == 0:
+                loss.backward()
+                assert torch.isfinite(logits.grad.float()).all() and float(logits.grad.float().abs().max()) > 0
+            losses.append(float(loss.detach()))
+    np.testing.assert_allclose(losses, z[f"a{ai}_losses"], rtol=1e-4, atol=1e-6)
+    out = tr.export()
+    keys = [str(k) for k in z[f"a{ai}_keys"]]
+    assert sorted(out.keys()) == keys
+    for k, ref in zip(keys, z[f"a{ai}_vals"]):
+        tol = 2e-3 if any(s in k for s in ("logp", "entropy", "kl", "weight", "loss")) else 2e-6
+        assert abs(out[k] - ref) <= tol * max(1.0, abs(ref)), (k, out[k], ref)
