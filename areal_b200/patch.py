@@ -124,6 +124,20 @@ def patch_realhf():
                    "critic_loss_fn", "get_packed_rewards", "get_packed_reward_dense"):
             setattr(m, fn, getattr(_P, fn))
         patched.append(m.__name__)
+    m = sys.modules.get("realhf.impl.model.utils.functional")
+    if m is not None:
+        from . import realhf_functional as _RF
+        for fn in ("build_shift_one_indices", "build_leave_one_indices", "gather_logprobs",
+                   "gather_packed_shifted_log_probs", "masked_normalization"):
+            if hasattr(m, fn):
+                setattr(m, fn, getattr(_RF, fn))
+        patched.append(m.__name__)
+    m = sys.modules.get("realhf.impl.model.modules.rms")
+    if m is not None:
+        from . import rms as _RMS
+        for cls in ("ExponentialRunningMeanStd", "MovingAverageRunningMeanStd"):
+            setattr(m, cls, getattr(_RMS, cls))
+        patched.append(m.__name__)
     m = sys.modules.get("realhf.impl.model.nn.flatten_param")
     if m is not None:
         for fn in ("slice_intervals", "set_intervals", "merge_intervals"):

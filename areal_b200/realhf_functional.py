@@ -57,3 +57,14 @@ def calc_entropy(logits: torch.Tensor, cu_seqlens: torch.Tensor) -> torch.Tensor
         call("areal_b200_legacy_entropy", ptr(x), _lib.DTYPE_CODE[x.dtype], T, V, x.stride(0) if T > 1 else V,
              ptr(row_max), ptr(ln_s), 1e-7, ptr(out), stream_ptr(dev))
     return out[build_leave_one_indices(logits, cu_seqlens)].to(logits.dtype)
+
+
+def masked_normalization(x: torch.Tensor, mask=None, dim=None, inplace: bool = False, unbiased: bool = False,
+                         eps: float = 1e-5, high_precision: bool = True, all_reduce: bool = True, group=None):
+    """Drop-in for the legacy `masked_normalization` (realhf/impl/model/utils/functional.py:252-319), `dim=None`
+    (how the PPO interface calls it): fp64 moments, one all-reduce of three numbers instead of three
+    all-reduces, fp32 result.  `inplace` is accepted; the reference returns a new fp32 tensor either way
+    (`.float()` of its float64 working copy)."""
+    from . import data as _D
+    return _D.masked_normalization(x, mask, dim=dim, unbiased=unbiased, eps=eps, high_precision=high_precision,
+                                   all_reduce=all_reduce, reduce_group=group)

@@ -263,6 +263,26 @@ def gen_intervals(fp):
     print("interval cases:", k)
 
 
+def gen_legacy_masked_norm():
+    """Legacy masked_normalization (realhf/impl/model/utils/functional.py:252-319), dim=None."""
+    rf = R.load_realhf_functional()
+    g = torch.Generator().manual_seed(606)
+    z = {}
+    k = 0
+    for shape in ((1000,), (37, 129), (4, 5, 6)):
+        x = torch.randn(*shape, generator=g) * 3 + 0.7
+        m = torch.rand(*shape, generator=g) > 0.4
+        for mask in (None, m):
+            for unbiased in (False, True):
+                out = rf.masked_normalization(x, mask, unbiased=unbiased, all_reduce=False)
+                z.update({f"c{k}_x": x.numpy(), f"c{k}_mask": (mask if mask is not None else torch.ones_like(m)).numpy(),
+                          f"c{k}_cfg": np.array([mask is not None, unbiased]), f"c{k}_out": out.numpy()})
+                k += 1
+    z["n_cases"] = np.array(k)
+    np.savez_compressed(os.path.join(OUT, "legacy_masked_norm.npz"), **z)
+    print("legacy masked_normalization golden:", k, "cases")
+
+
 def gen_legacy_packed():
     """realhf spelling of P2: gather_packed_shifted_log_probs / build_*_indices / calc_entropy."""
     rf = R.load_realhf_functional()
@@ -592,6 +612,7 @@ def main():
     gen_critic_loss(af, pf)
     gen_intervals(fp)
     gen_legacy_packed()
+    gen_legacy_masked_norm()
     gen_normalization(af)
     gen_pack()
     gen_advantages()

@@ -76,3 +76,18 @@ def test_packed_rewards_golden_and_large():
         c, d = P.get_packed_reward_dense(0.05, 3.0, t(lp), t(rf), t(dense), t(cu), t(ne).float(), delta)
         rc, rd = O.packed_rewards(0.05, 3.0, lp, rf, dense, cu, dense=True, reward_delta=delta)
         assert np.array_equal(c.cpu().numpy(), rc) and np.array_equal(d.cpu().numpy(), rd)
+
+
+def test_legacy_masked_normalization_golden():
+    """realhf masked_normalization (dim=None), with and without mask, biased / unbiased: golden outputs of
+    the unmodified reference function."""
+    from areal_b200 import realhf_functional as RF
+    z = H.load("legacy_masked_norm.npz")
+    dev = torch.device("cuda:0")
+    for k in range(int(z["n_cases"])):
+        has_mask, unbiased = [bool(v) for v in z[f"c{k}_cfg"]]
+        x = torch.from_numpy(z[f"c{k}_x"]).to(dev)
+        m = torch.from_numpy(z[f"c{k}_mask"]).to(dev) if has_mask else None
+        out = RF.masked_normalization(x, m, unbiased=unbiased, all_reduce=False)
+        assert out.dtype == torch.float32 and out.shape == x.shape
+        np.testing.assert_allclose(out.cpu().numpy(), z[f"c{k}_out"], rtol=1e-5, atol=1e-5)
