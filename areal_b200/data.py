@@ -205,3 +205,59 @@ def unpack_to_padded(packed: torch.Tensor, cu_seqlens: torch.Tensor, seq_len: in
         src, dst = src.view(torch.uint8), dst.view(torch.uint8)
     fp.set_intervals_any(src, dst, iv)
     return out
+
+
+# --------------------------------------------------------------------------------------------------
+# dynamic sampling (areal/utils/functional.py:314-373): drop the groups whose rewards are all equal
+# --------------------------------------------------------------------------------------------------
+def dynamic_sampling(data: dict, group_size: int):
+    """Drop-in for `dynamic_sampling` (areal/utils/functional.py:314-373): samples of a group are adjacent;
+    groups whose rewards are all equal are removed from every tensor whose first dimension is the batch.
+    Same return value (filtered dict, stats dict) and the same early exits.  The reference indexes each
+    tensor with a boolean mask (a `nonzero` + host sync per key, plus two `.item()`s); here ONE host sync
+    reads the kept groups and each tensor is gathered by one launch of the interval kernels (kept groups
+    are contiguous row ranges)."""
+    import warnings
+
+    from . import flatten_param as fp
+    rewards = data["rewards"]
+    if not torch.is_tensor(rewards):
+        raise TypeError("data['rewards'] must be a torch.Tensor")
+    batch_size = rewards.shape[0]
+    if group_size <= 0:
+        warnings.warn("group_size <= 0; returning original data")
+        return data, dict(n_group_kept=0, n_group_filtered=0)
+    if batch_size % group_size != 0:
+        warnings.warn("The group size is not divisible by the batch size. Return the original data")
+        return data, dict(n_group_kept=batch_size // max(group_size, 1), n_group_filtered=0)
+    _lib.require_cuda(rewards)
+    num_groups = batch_size // group_size
+    r = rewards.view(num_groups, group_size)
+    valid = ~(r == r[:, 0:1]).all(dim=1)
+    kept = torch.nonzero(valid).flatten().tolist()          # the one host sync
+    if not kept:
+        return data, dict(n_group_kept=0, n_group_filtered=num_groups)
+    n_kept = len(kept)
+    starts = torch.tensor(kept, dtype=torch.int64, device=rewards.device) * group_size     # first row of each kept group
+    filtered = {}
+    iv_cache = {}
+    for k, v in data.items():
+        if torch.is_tensor(v) and v.shape[:1] == (batch_size,):
+            if n_kept == num_groups:
+                filtered[k] = v.clone()                      # v[mask] with an all-true mask copies
+                continue
+            inner = 1
+            for d in v.shape[1:]:
+                inner *= int(d)
+            if inner not in iv_cache:
+                iv_cache[inner] = torch.stack([starts * inner, (starts + group_size) * inner], dim=1).contiguous()
+            flat = v.contiguous().view(-1)
+            as_u8 = flat.dtype == torch.bool
+            out = fp.slice_intervals_any(flat.view(torch.uint8) if as_u8 else flat, iv_cache[inner],
+                                         n_kept * group_size * inner)
+            if as_u8:
+                out = out.view(torch.bool)
+            filtered[k] = out.view(n_kept * group_size, *v.shape[1:])
+        else:
+            filtered[k] = v
+    return filtered, dict(n_group_kept=n_kept, n_group_filtered=int(num_groups - n_kept))

@@ -70,6 +70,8 @@ def patch_areal(extra_modules=()):
             setattr(mod, "Normalization", _D.Normalization)
         if hasattr(mod, "masked_normalization"):
             setattr(mod, "masked_normalization", _D.masked_normalization)
+        if hasattr(mod, "dynamic_sampling"):
+            setattr(mod, "dynamic_sampling", _D.dynamic_sampling)
     # reward construction + GAE of the actor (areal/engine/ppo/actor.py:72-164) as one launch
     mod = sys.modules.get("areal.engine.ppo.actor")
     if mod is not None and hasattr(mod, "PPOActor"):

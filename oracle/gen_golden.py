@@ -362,6 +362,34 @@ def gen_normalization(af):
     print("normalization cases:", k, "masked_normalization:", j)
 
 
+def gen_dynamic_sampling(af):
+    """dynamic_sampling (areal/utils/functional.py:314-373): mixed dtypes / trailing dims, groups of 4."""
+    g = torch.Generator().manual_seed(12)
+    z = {}
+    for ci, pattern in enumerate(("mixed", "all_kept", "none_kept")):
+        B, S, G = 24, 11, 4
+        rewards = torch.randint(0, 2, (B,), generator=g).float()
+        if pattern == "all_kept":
+            rewards = torch.arange(B).float()
+        elif pattern == "none_kept":
+            rewards = torch.ones(B)
+        else:
+            rewards[4:8] = 1.0          # one all-equal group, one all-zero group
+            rewards[12:16] = 0.0
+        data = dict(rewards=rewards, input_ids=torch.randint(0, 999, (B, S), generator=g),
+                    loss_mask=torch.rand(B, S, generator=g) > 0.5, logprobs=torch.randn(B, S, generator=g),
+                    hidden=torch.randn(B, S, 3, generator=g).bfloat16(), meta="keep", other=torch.randn(7, generator=g))
+        out, stat = af.dynamic_sampling({k: (v.clone() if torch.is_tensor(v) else v) for k, v in data.items()}, G)
+        for k in ("rewards", "input_ids", "loss_mask", "logprobs", "other"):
+            z[f"c{ci}_in_{k}"] = data[k].numpy()
+            z[f"c{ci}_out_{k}"] = out[k].numpy()
+        z[f"c{ci}_in_hidden"] = bf16_bits(data["hidden"].reshape(-1)).reshape(B, S, 3)
+        z[f"c{ci}_out_hidden"] = bf16_bits(out["hidden"].reshape(-1)).reshape(-1, S, 3)
+        z[f"c{ci}_stat"] = np.array([stat["n_group_kept"], stat["n_group_filtered"]])
+    np.savez_compressed(os.path.join(OUT, "dynamic_sampling.npz"), **z)
+    print("dynamic_sampling golden ok")
+
+
 def gen_pack():
     """`pack_tensor_dict` (areal/utils/data.py:266-315) on a padded batch with mixed dtypes / trailing dims."""
     pack = R.load_areal_pack_tensor_dict()
@@ -615,6 +643,7 @@ def main():
     gen_legacy_masked_norm()
     gen_normalization(af)
     gen_pack()
+    gen_dynamic_sampling(af)
     gen_advantages()
     gen_grpo_stats()
     gen_packed_rewards(pf)

@@ -129,3 +129,31 @@ def test_legacy_running_mean_std_vs_reference():
             assert torch.equal(clone.normalize(probe), mod.normalize(probe))
     with pytest.raises(NotImplementedError):
         mod.forward(probe)
+
+
+def test_dynamic_sampling_golden():
+    """dynamic_sampling: bit-exact vs the reference function (mixed / nothing filtered / everything equal),
+    pass-through of non-batch entries, the early exits."""
+    import warnings
+    from areal_b200.data import dynamic_sampling
+    z = H.load("dynamic_sampling.npz")
+    dev = torch.device("cuda:0")
+    for ci in range(3):
+        data = {k: torch.from_numpy(z[f"c{ci}_in_{k}"]).to(dev) for k in ("rewards", "input_ids", "loss_mask", "logprobs", "other")}
+        data["hidden"] = H.bf16_from_bits(z[f"c{ci}_in_hidden"]).to(dev)
+        data["meta"] = "keep"
+        out, stat = dynamic_sampling(data, 4)
+        assert [stat["n_group_kept"], stat["n_group_filtered"]] == z[f"c{ci}_stat"].tolist()
+        assert out["meta"] == "keep"
+        for k in ("rewards", "input_ids", "loss_mask", "logprobs", "other"):
+            got = out[k].cpu().numpy()
+            assert got.dtype == z[f"c{ci}_out_{k}"].dtype and np.array_equal(got, z[f"c{ci}_out_{k}"]), (ci, k)
+        assert np.array_equal(H.torch_bits(out["hidden"].reshape(-1)).reshape(-1, 11, 3), z[f"c{ci}_out_hidden"])
+    with warnings.catch_warnings(record=True) as w:
+        warnings.simplefilter("always")
+        same, stat = dynamic_sampling(data, 5)                       # 24 % 5 != 0: untouched
+        assert same is data and stat == dict(n_group_kept=4, n_group_filtered=0) and w
+        same, stat = dynamic_sampling(data, 0)
+        assert same is data and stat == dict(n_group_kept=0, n_group_filtered=0)
+    with pytest.raises(TypeError):
+        dynamic_sampling(dict(rewards=[1, 2]), 2)
