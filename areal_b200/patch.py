@@ -90,6 +90,11 @@ def patch_areal(extra_modules=()):
             from . import actor as _A
             mod.grpo_loss_fn = _A.grpo_loss_fn
             patched.append("areal.engine.ppo.actor.grpo_loss_fn")
+        cmod = sys.modules.get("areal.engine.ppo.critic")
+        if cmod is not None and hasattr(cmod, "ppo_loss_fn"):
+            from . import critic as _C
+            cmod.ppo_loss_fn = _C.ppo_loss_fn
+            patched.append("areal.engine.ppo.critic.ppo_loss_fn")
     # AEnt recipe: clamped entropy without the CPU top-k (recipe/AEnt/functional.py, actor.py:21)
     from . import aent_functional as _AE
     for name in ("recipe.AEnt.functional", "recipe.AEnt.actor"):

@@ -626,6 +626,34 @@ def gen_aent_stats():
     print("aent_stats golden:", len(out), "keys, losses", losses)
 
 
+def critic_case(mb, T=700):
+    g = torch.Generator().manual_seed(1300 + mb)
+    old = torch.randn(T, generator=g)
+    return dict(value=(old + 0.3 * torch.randn(T, generator=g)).unsqueeze(-1), values=old,
+                returns=old + torch.randn(T, generator=g), loss_mask=torch.rand(T, generator=g) > (0.4 if mb < 2 else 2.0))
+
+
+def gen_critic_stats():
+    """ppo_loss_fn of the critic + tracker export (areal/engine/ppo/critic.py:81-127), three micro-batches."""
+    fn, st = R.load_areal_critic_loss_fn()
+    z = {}
+    tr = st.DistributedStatsTracker()
+    st.denominator, st.stat = tr.denominator, tr.stat
+    losses = []
+    with tr.scope("ppo_critic"):
+        for mb in range(3):
+            c = critic_case(mb)
+            for k, v in c.items():
+                z[f"mb{mb}_{k}"] = v.numpy()
+            losses.append(float(fn(c["value"], {k: v for k, v in c.items() if k != "value"}, 0.2)))
+    out = tr.export()
+    z["losses"] = np.array(losses)
+    z["keys"] = np.array(sorted(out.keys()))
+    z["vals"] = np.array([out[k] for k in sorted(out.keys())], dtype=np.float64)
+    np.savez_compressed(os.path.join(OUT, "critic_stats.npz"), **z)
+    print("critic_stats golden:", len(out), "keys")
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     assert R.available(), "needs /root/reference"
@@ -650,6 +678,7 @@ def main():
     gen_rms()
     gen_clamped_entropy()
     gen_aent_stats()
+    gen_critic_stats()
 
 
 if __name__ == "__main__":

@@ -364,3 +364,20 @@ def load_aent_grpo_loss_fn():
         node.decorator_list = []
         exec(compile(ast.unparse(node), f"AEnt[{name}]", "exec"), ns)
     return ns["aent_grpo_loss_fn"], st
+
+
+def load_areal_critic_loss_fn():
+    """`ppo_loss_fn` (areal/engine/ppo/critic.py:81-127) bound to the reference's ppo_critic_loss_fn and
+    stats_tracker.  Returns (fn, stats_tracker module)."""
+    import ast
+    from typing import Dict
+
+    import torch
+    af = load_areal_functional()
+    st = load_areal_stats_tracker()
+    with open(os.path.join(REF_ROOT, "areal/engine/ppo/critic.py")) as f:
+        src = f.read()
+    node = next(n for n in ast.parse(src).body if isinstance(n, ast.FunctionDef) and n.name == "ppo_loss_fn")
+    ns = dict(torch=torch, Dict=Dict, ppo_critic_loss_fn=af.ppo_critic_loss_fn, stats_tracker=st)
+    exec(compile(ast.get_source_segment(src, node), "critic.py[ppo_loss_fn]", "exec"), ns)
+    return ns["ppo_loss_fn"], st

@@ -152,3 +152,31 @@ def test_tracker_api_matches_record():
             a.stat(denominator="valid", z=torch.zeros(n + 1, device=DEV))
     ea, eb = a.export(), b.export()
     assert ea == eb and set(ea) == {"valid", "x/avg", "x/min", "x/max", "y"}
+
+
+def test_critic_ppo_loss_fn_and_export_vs_reference():
+    """The critic's ppo_loss_fn over three micro-batches (one fully masked) + export: the reference's
+    losses, every exported key, and a gradient that flows to the [T,1] value head output."""
+    from areal_b200 import stats_tracker as ST
+    from areal_b200.critic import ppo_loss_fn
+    z = H.load("critic_stats.npz")
+    tr = ST.DistributedStatsTracker()
+    losses = []
+    with tr.scope("ppo_critic"):
+        for mb in range(3):
+            c = {k: torch.from_numpy(z[f"mb{mb}_{k}"]).to(DEV) for k in ("value", "values", "returns", "loss_mask")}
+            value = c.pop("value").requires_grad_()
+            loss = ppo_loss_fn(value, c, 0.2, tracker=tr)
+            loss.backward()
+            assert value.grad.shape == value.shape
+            if mb < 2:
+                assert torch.isfinite(value.grad).all()
+            losses.append(float(loss.detach()))
+    # the fully masked micro-batch: the reference divides by count_nonzero() = 0 (functional.py:309), so does this
+    assert np.isnan(z["losses"][2]) and np.isnan(losses[2])
+    np.testing.assert_allclose(losses[:2], z["losses"][:2], rtol=2e-6, atol=1e-7)
+    out = tr.export()
+    keys = [str(k) for k in z["keys"]]
+    assert sorted(out.keys()) == keys
+    for k, ref in zip(keys, z["vals"]):
+        assert abs(out[k] - ref) <= 3e-6 * max(1.0, abs(ref)), (k, out[k], ref)
