@@ -36,6 +36,7 @@ SIGNATURES = {
     "areal_b200_rms_update": (c_int, [P, I64, P, c_int, c_int, F64, P]),
     "areal_b200_rms_apply": (c_int, [P, I64, P, c_int, c_int, F64, c_int, P, P]),
     "areal_b200_packed_rewards": (c_int, [P, P, P, P, P, I64, I64, F64, F64, c_int, c_int, P, P, P]),
+    "areal_b200_segment_masked_mean": (c_int, [P, P, P, I64, P, P, P]),
     "areal_b200_masked_stats_workspace_bytes": (I64, [I64, I64]),
     "areal_b200_masked_stats": (c_int, [P, P, P, ctypes.c_uint32, I64, I64, c_int, P, I64, P]),
     "areal_b200_gae2d_olp": (c_int, [P, P, P, P, P, P, I64, I64, I64, F64, F64, P, P, P]),

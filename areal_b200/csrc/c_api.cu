@@ -818,6 +818,15 @@ AREAL_B200_API int areal_b200_packed_rewards(const float* log_probs, const float
                                static_cast<cudaStream_t>(stream));
 }
 
+AREAL_B200_API int areal_b200_segment_masked_mean(const float* v, const uint8_t* mask,
+                                                  const int32_t* cu_seqlens, int64_t batch_size,
+                                                  double* mean, uint8_t* valid, void* stream) {
+  AB_REQUIRE(batch_size >= 0, "negative size");
+  if (batch_size == 0) return kOk;
+  AB_REQUIRE(v && cu_seqlens && mean && valid, "null pointer");
+  return launch_segment_masked_mean(v, mask, cu_seqlens, batch_size, mean, valid, static_cast<cudaStream_t>(stream));
+}
+
 AREAL_B200_API int64_t areal_b200_masked_stats_workspace_bytes(int64_t n_keys, int64_t n) {
   if (n_keys < 0 || n < 0) return -1;
   return masked_stats_workspace_bytes(n_keys, n);

@@ -114,7 +114,43 @@ masked_stats_kernel(const __grid_constant__ StatsTable tab, int64_t n, int chunk
   }
 }
 
+// Per-sequence masked mean of a packed [T] vector: one warp per sequence (fp64 sum, lanes stride the
+// sequence, fixed shuffle order).  mean[i] = sum(mask ? v : 0) / count, valid[i] = count > 0 (mean 0 otherwise).
+__global__ void __launch_bounds__(kThreads)
+segment_masked_mean_kernel(const float* __restrict__ v, const uint8_t* __restrict__ mask, const int32_t* __restrict__ cu,
+                           int64_t B, double* __restrict__ mean, uint8_t* __restrict__ valid) {
+  const int lane = threadIdx.x & 31;
+  const int64_t seq = (blockIdx.x * int64_t(kThreads) + threadIdx.x) >> 5;
+  if (seq >= B) return;
+  const int64_t s = cu[seq], e = cu[seq + 1];
+  double sum = 0.0;
+  int cnt = 0;
+  for (int64_t i = s + lane; i < e; i += 32) {
+    if (!mask || mask[i]) {
+      sum += double(v[i]);
+      ++cnt;
+    }
+  }
+#pragma unroll
+  for (int d = 16; d; d >>= 1) {
+    sum += __shfl_down_sync(0xffffffffu, sum, d);
+    cnt += __shfl_down_sync(0xffffffffu, cnt, d);
+  }
+  if (lane == 0) {
+    mean[seq] = cnt ? sum / double(cnt) : 0.0;
+    valid[seq] = cnt > 0;
+  }
+}
+
 }  // namespace
+
+int launch_segment_masked_mean(const float* v, const uint8_t* mask, const int32_t* cu, int64_t B, double* mean,
+                               uint8_t* valid, cudaStream_t stream) {
+  if (B == 0) return kOk;
+  const int64_t blocks = (B * 32 + kThreads - 1) / kThreads;
+  segment_masked_mean_kernel<<<static_cast<unsigned int>(blocks), kThreads, 0, stream>>>(v, mask, cu, B, mean, valid);
+  return check_launch("segment_masked_mean");
+}
 
 int64_t masked_stats_workspace_bytes(int64_t n_keys, int64_t n) {
   const int64_t chunks = (n + kStatChunk - 1) / kStatChunk;

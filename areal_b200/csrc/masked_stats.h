@@ -18,4 +18,7 @@ int64_t masked_stats_workspace_bytes(int64_t n_keys, int64_t n);
 int launch_masked_stats(const StatsTable& tab, int n_keys, int64_t n, int accumulate, void* workspace,
                         cudaStream_t stream);
 
+int launch_segment_masked_mean(const float* v, const uint8_t* mask, const int32_t* cu, int64_t B, double* mean,
+                               uint8_t* valid, cudaStream_t stream);
+
 }  // namespace ab

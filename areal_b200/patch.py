@@ -90,6 +90,11 @@ def patch_areal(extra_modules=()):
             from . import actor as _A
             mod.grpo_loss_fn = _A.grpo_loss_fn
             patched.append("areal.engine.ppo.actor.grpo_loss_fn")
+        smod = sys.modules.get("areal.engine.sft.lm_engine")
+        if smod is not None and hasattr(smod, "compute_packed_sft_loss"):
+            from . import sft as _S
+            smod.compute_packed_sft_loss = _S.compute_packed_sft_loss
+            patched.append("areal.engine.sft.lm_engine.compute_packed_sft_loss")
         cmod = sys.modules.get("areal.engine.ppo.critic")
         if cmod is not None and hasattr(cmod, "ppo_loss_fn"):
             from . import critic as _C

@@ -340,6 +340,15 @@ AREAL_B200_API int areal_b200_set_intervals(const void* packed, int64_t packed_n
  * returns the number of merged intervals, or -1 on a null pointer. */
 AREAL_B200_API int64_t areal_b200_merge_intervals(const uint64_t* intervals, int64_t n, uint64_t* out);
 
+/* Per-sequence masked mean of a packed vector: mean[i] = sum over cu[i] <= t < cu[i+1] of (mask[t] ? v[t] : 0)
+ * divided by the number of selected tokens (0 and valid[i] = 0 when there is none).  Replaces the
+ * Python loop over sequences with one `.item()` each in `compute_packed_sft_loss`
+ * (areal/engine/sft/lm_engine.py:80-91).  v f32[T], mask u8/bool[T] or NULL, cu_seqlens i32[B+1];
+ * mean f64[B], valid u8[B]. */
+AREAL_B200_API int areal_b200_segment_masked_mean(const float* v, const uint8_t* mask,
+                                                  const int32_t* cu_seqlens, int64_t batch_size,
+                                                  double* mean, uint8_t* valid, void* stream);
+
 /* Vocab-sharded combine WITHOUT the all-gather: the partial sets are read straight out of the peers'
  * memory over NVLink (the reference does six all-reduces here: areal/utils/mcore/functional.py:16-31 +
  * Megatron's vocab_parallel_cross_entropy).  No counterpart as a single reference function.

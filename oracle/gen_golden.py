@@ -654,6 +654,39 @@ def gen_critic_stats():
     print("critic_stats golden:", len(out), "keys")
 
 
+def sft_case(mb, V=977):
+    g = torch.Generator().manual_seed(1700 + mb)
+    lens = torch.randint(3, 60, (9,), generator=g)
+    cu = torch.zeros(10, dtype=torch.int32)
+    cu[1:] = lens.cumsum(0)
+    T = int(cu[-1])
+    mask = torch.rand(T, generator=g) > 0.5
+    mask[int(cu[3]):int(cu[4]) + 1] = False                      # one sequence without any target token
+    return dict(logits=(torch.randn(T, V, generator=g) * 2.5).bfloat16(), input_ids=torch.randint(0, V, (T,), generator=g),
+                cu_seqlens=cu, loss_mask=mask)
+
+
+def gen_sft_stats():
+    """compute_packed_sft_loss + tracker export (areal/engine/sft/lm_engine.py:58-110), two micro-batches."""
+    fn, st = R.load_areal_sft_loss_fn()
+    z = {}
+    tr = st.DistributedStatsTracker()
+    st.denominator, st.stat = tr.denominator, tr.stat
+    losses = []
+    with tr.scope("sft"):
+        for mb in range(2):
+            c = sft_case(mb)
+            for k, v in c.items():
+                z[f"mb{mb}_{k}"] = bf16_bits(v) if v.dtype == torch.bfloat16 else v.numpy()
+            losses.append(float(fn(c["logits"].float(), {k: v for k, v in c.items() if k != "logits"})))
+    out = tr.export()
+    z["losses"] = np.array(losses)
+    z["keys"] = np.array(sorted(out.keys()))
+    z["vals"] = np.array([out[k] for k in sorted(out.keys())], dtype=np.float64)
+    np.savez_compressed(os.path.join(OUT, "sft_stats.npz"), **z)
+    print("sft_stats golden:", len(out), "keys", losses)
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     assert R.available(), "needs /root/reference"
@@ -679,6 +712,7 @@ def main():
     gen_clamped_entropy()
     gen_aent_stats()
     gen_critic_stats()
+    gen_sft_stats()
 
 
 if __name__ == "__main__":

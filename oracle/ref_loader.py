@@ -381,3 +381,20 @@ def load_areal_critic_loss_fn():
     ns = dict(torch=torch, Dict=Dict, ppo_critic_loss_fn=af.ppo_critic_loss_fn, stats_tracker=st)
     exec(compile(ast.get_source_segment(src, node), "critic.py[ppo_loss_fn]", "exec"), ns)
     return ns["ppo_loss_fn"], st
+
+
+def load_areal_sft_loss_fn():
+    """`compute_packed_sft_loss` (areal/engine/sft/lm_engine.py:58-110) bound to the reference's gather_logprobs
+    and stats_tracker.  Returns (fn, stats_tracker module)."""
+    import ast
+    from typing import Any, Dict
+
+    import torch
+    af = load_areal_functional()
+    st = load_areal_stats_tracker()
+    with open(os.path.join(REF_ROOT, "areal/engine/sft/lm_engine.py")) as f:
+        src = f.read()
+    node = next(n for n in ast.parse(src).body if isinstance(n, ast.FunctionDef) and n.name == "compute_packed_sft_loss")
+    ns = dict(torch=torch, Dict=Dict, Any=Any, gather_logprobs=af.gather_logprobs, stats_tracker=st)
+    exec(compile(ast.get_source_segment(src, node), "lm_engine.py[compute_packed_sft_loss]", "exec"), ns)
+    return ns["compute_packed_sft_loss"], st

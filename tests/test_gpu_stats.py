@@ -180,3 +180,34 @@ def test_critic_ppo_loss_fn_and_export_vs_reference():
     assert sorted(out.keys()) == keys
     for k, ref in zip(keys, z["vals"]):
         assert abs(out[k] - ref) <= 3e-6 * max(1.0, abs(ref)), (k, out[k], ref)
+
+
+def test_sft_loss_fn_and_export_vs_reference():
+    """compute_packed_sft_loss over two packed micro-batches (one sequence without any target token):
+    losses, every exported key (ppl per sequence, loss per token, vocab min / max), and a finite gradient."""
+    from areal_b200 import stats_tracker as ST
+    from areal_b200.sft import compute_packed_sft_loss, segment_masked_mean
+    z = H.load("sft_stats.npz")
+    tr = ST.DistributedStatsTracker()
+    losses = []
+    with tr.scope("sft"):
+        for mb in range(2):
+            c = {k: torch.from_numpy(z[f"mb{mb}_{k}"]).to(DEV) for k in ("input_ids", "cu_seqlens", "loss_mask")}
+            logits = torch.from_numpy(z[f"mb{mb}_logits"].view(np.int16)).view(torch.bfloat16).to(DEV).requires_grad_()
+            loss = compute_packed_sft_loss(logits, c, tracker=tr)
+            loss.backward()
+            assert torch.isfinite(logits.grad.float()).all() and float(logits.grad.float().abs().max()) > 0
+            losses.append(float(loss.detach()))
+    np.testing.assert_allclose(losses, z["losses"], rtol=1e-4)
+    out = tr.export()
+    keys = [str(k) for k in z["keys"]]
+    assert sorted(out.keys()) == keys
+    for k, ref in zip(keys, z["vals"]):
+        tol = 2e-3 if ("ppl" in k or "loss" in k) else 2e-6
+        assert abs(out[k] - ref) <= tol * max(1.0, abs(ref)), (k, out[k], ref)
+    # the segment kernel on its own: empty sequences, no mask hits
+    v = torch.arange(10, dtype=torch.float32, device=DEV)
+    m = torch.tensor([1, 1, 0, 0, 0, 1, 0, 1, 1, 1], dtype=torch.bool, device=DEV)
+    cu = torch.tensor([0, 2, 2, 5, 10], dtype=torch.int32, device=DEV)
+    mean, valid = segment_masked_mean(v, m, cu)
+    assert mean.tolist() == [0.5, 0.0, 0.0, (5 + 7 + 8 + 9) / 4] and valid.tolist() == [True, False, False, True]
