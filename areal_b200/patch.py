@@ -139,7 +139,7 @@ def patch_realhf():
     m = sys.modules.get("realhf.impl.model.utils.functional")
     if m is not None:
         from . import realhf_functional as _RF
-        for fn in ("build_shift_one_indices", "build_leave_one_indices", "gather_logprobs",
+        for fn in ("build_shift_one_indices", "build_leave_one_indices", "gather_logprobs", "gather_shifted_log_probs",
                    "gather_packed_shifted_log_probs", "masked_normalization"):
             if hasattr(m, fn):
                 setattr(m, fn, getattr(_RF, fn))

@@ -68,3 +68,15 @@ def masked_normalization(x: torch.Tensor, mask=None, dim=None, inplace: bool = F
     from . import data as _D
     return _D.masked_normalization(x, mask, dim=dim, unbiased=unbiased, eps=eps, high_precision=high_precision,
                                    all_reduce=all_reduce, reduce_group=group)
+
+
+def gather_shifted_log_probs(logits: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
+    """Drop-in for the padded `gather_shifted_log_probs` (realhf/impl/model/utils/functional.py:70-88):
+    log-prob of `labels[:, 1:]` under `logits[:, :-1]`, shape [bs, seqlen - 1], in the logits' dtype.
+    The logits are streamed where they are (rows [b, s] of the full tensor with the labels rolled by one);
+    the last position of every sequence is computed and dropped instead of copying `logits[:, :-1]`."""
+    if logits.dim() != 3 or labels.shape != logits.shape[:2]:
+        raise RuntimeError(f"expected logits [bs, seqlen, V] and labels [bs, seqlen], got {tuple(logits.shape)} / {tuple(labels.shape)}")
+    shifted = torch.roll(labels, shifts=-1, dims=1)
+    lp = F.gather_logprobs(logits, shifted, 1.0)
+    return lp[:, :-1].to(logits.dtype)

@@ -91,3 +91,17 @@ def test_legacy_masked_normalization_golden():
         out = RF.masked_normalization(x, m, unbiased=unbiased, all_reduce=False)
         assert out.dtype == torch.float32 and out.shape == x.shape
         np.testing.assert_allclose(out.cpu().numpy(), z[f"c{k}_out"], rtol=1e-5, atol=1e-5)
+
+
+def test_gather_shifted_log_probs_padded():
+    """Padded legacy spelling: [bs, seqlen, V] -> [bs, seqlen-1]; torch's own log_softmax as the check
+    (the function is three torch calls upstream, realhf functional.py:84-88)."""
+    from areal_b200 import realhf_functional as RF
+    g = torch.Generator().manual_seed(2)
+    logits = (torch.randn(3, 17, 1000, generator=g) * 2).bfloat16()
+    labels = torch.randint(0, 1000, (3, 17), generator=g)
+    got = RF.gather_shifted_log_probs(logits.to("cuda:0").requires_grad_(), labels.to("cuda:0"))
+    ref = torch.log_softmax(logits[:, :-1].float(), dim=-1).gather(-1, labels[:, 1:].unsqueeze(-1)).squeeze(-1)
+    assert got.shape == (3, 16) and got.dtype == torch.bfloat16
+    assert torch.allclose(got.float().cpu(), ref, rtol=2 ** -7, atol=2 ** -7)
+    got.float().sum().backward()
