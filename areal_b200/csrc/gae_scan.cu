@@ -21,6 +21,8 @@
 // reference is the reference's own sequential fp32 rounding (tests report both against fp64).
 #include <mutex>
 
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "gae_scan.h"
 
@@ -57,8 +59,10 @@ __device__ __forceinline__ Affine shfl_down(const Affine& v, int d) {
 // excl  = F_{x+1} o F_{x+2} o ... o F_{last}   (apply to the tile carry-in to get the value
 //         entering thread x from the right);  tile = F_0 o ... o F_last.
 // Contains one __syncthreads(); `wsm` may be rewritten after the caller's next barrier.
+template <int kNW = kWarps>
 __device__ __forceinline__ void block_suffix_scan(const Affine& agg, Affine* wsm, int warp, int lane,
                                                   Affine& excl, Affine& tile) {
+  constexpr int kWarps = kNW;
   Affine inc = agg;
 #pragma unroll
   for (int d = 1; d < 32; d <<= 1) {
@@ -441,9 +445,10 @@ __device__ __forceinline__ void ld9_mask(const void* base, int code, int64_t i, 
   }
 }
 
-template <bool kFused>
-__global__ void __launch_bounds__(kThreads)
+template <bool kFused, int kT>
+__global__ void __launch_bounds__(kT)
 gae_padded_kernel(const GaePaddedParams p, const AdvFusedParams f) {
+  constexpr int kThreads = kT, kWarps = kT / 32, kTile = kT * kItems;
   __shared__ Affine wsm[kWarps];
   __shared__ float nv_val[kWarps];
   __shared__ int nv_has[kWarps];
@@ -616,7 +621,7 @@ gae_padded_kernel(const GaePaddedParams p, const AdvFusedParams f) {
         }
       }
       Affine excl, tagg;
-      block_suffix_scan(agg, wsm, warp, lane, excl, tagg);       // barrier #2 inside
+      block_suffix_scan<kWarps>(agg, wsm, warp, lane, excl, tagg);       // barrier #2 inside
       double A = fma(excl.a, a_carry, excl.b);
 #pragma unroll
       for (int k = kItems - 1; k >= 0; --k) {
@@ -811,16 +816,36 @@ int launch_gae1d_static(Gae1dParams p, cudaStream_t stream) {
   return check_launch("gae1d (static scratch)");
 }
 
+constexpr int kPaddedThreadsDefault = 256;
+
 static bool aligned16(const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; }
+
+// CTA width of the padded kernels: AREAL_B200_PADDED_THREADS = 64 | 128 | 256 overrides the default (benchmarks)
+static int padded_threads() {
+  static const int v = [] {
+    const char* e = getenv("AREAL_B200_PADDED_THREADS");
+    const int t = e ? atoi(e) : 0;
+    return (t == 64 || t == 128 || t == 256) ? t : kPaddedThreadsDefault;
+  }();
+  return v;
+}
+
+template <bool kFused>
+static void launch_padded_t(const GaePaddedParams& p, const AdvFusedParams& f, cudaStream_t stream) {
+  const int t = padded_threads();
+  const int64_t cap = int64_t(num_sms()) * (2048 / t);
+  const unsigned int grid = static_cast<unsigned int>(p.B < cap ? p.B : cap);
+  if (t == 64) gae_padded_kernel<kFused, 64><<<grid, 64, 0, stream>>>(p, f);
+  else if (t == 128) gae_padded_kernel<kFused, 128><<<grid, 128, 0, stream>>>(p, f);
+  else gae_padded_kernel<kFused, 256><<<grid, 256, 0, stream>>>(p, f);
+}
 
 int launch_gae_padded(const GaePaddedParams& p_in, cudaStream_t stream) {
   GaePaddedParams p = p_in;
   if (p.B == 0 || p.S == 0) return kOk;
   p.vec_ok = p.S % 4 == 0 && aligned16(p.rewards) && aligned16(p.values) && aligned16(p.mask) &&
              aligned16(p.adv) && aligned16(p.ret);
-  const int64_t cap = int64_t(num_sms()) * 8;
-  gae_padded_kernel<false><<<static_cast<unsigned int>(p.B < cap ? p.B : cap), kThreads, 0, stream>>>(
-      p, AdvFusedParams{});
+  launch_padded_t<false>(p, AdvFusedParams{}, stream);
   return check_launch("gae_padded");
 }
 
@@ -832,8 +857,7 @@ int launch_advantages_padded(const GaePaddedParams& p_in, const AdvFusedParams& 
              aligned16(f.loss_mask) && aligned16(f.logp) && aligned16(f.ref_logp) &&
              aligned16(f.kl_rewards) && aligned16(f.tot_rewards) && aligned16(f.loss_mask_out) &&
              aligned16(f.old_logp_out);
-  const int64_t cap = int64_t(num_sms()) * 8;
-  gae_padded_kernel<true><<<static_cast<unsigned int>(p.B < cap ? p.B : cap), kThreads, 0, stream>>>(p, f);
+  launch_padded_t<true>(p, f, stream);
   return check_launch("advantages_padded");
 }
 
