@@ -84,6 +84,21 @@ def main():
         out[name] = res
         if exch is not None:
             exch.check()
+    # full-size properties: log-prob <= 0, 0 <= entropy <= ln V, both exchanges agree bit for bit, the
+    # gradient of sum(logp) sums to ~0 over the WHOLE vocabulary row (all-reduced over the shards)
+    import math
+    x = shard.detach().requires_grad_()
+    lp_a, ent_a = D.vocab_parallel_logprobs_entropy(x, labels, 1.0)
+    checks = {"logp_le_0": bool((lp_a <= 0).all()), "entropy_in_range": bool(((ent_a >= 0) & (ent_a <= math.log(V) + 1e-3)).all())}
+    if ex is not None:
+        lp_b, ent_b = D.vocab_parallel_logprobs_entropy(shard.detach(), labels, 1.0, exchange=ex)
+        checks["exchanges_bit_identical"] = bool(torch.equal(lp_a.detach(), lp_b) and torch.equal(ent_a.detach(), ent_b))
+        ex.check()
+    lp_a.sum().backward()
+    rs = x.grad[:4096].float().sum(-1)
+    dist.all_reduce(rs)
+    checks["grad_rows_sum_to_zero"] = bool((rs.abs() <= 3e-2).all())
+    out["checks"] = checks
     if rank == 0:
         print(json.dumps(out), flush=True)
     dist.destroy_process_group()
