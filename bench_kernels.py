@@ -347,9 +347,48 @@ def bench_aent(out):
                    tokens_per_s=Ts / (msr * 1e-3), speedup_ours=(msr / Ts) / (ms / T)))
 
 
+def bench_cfg2(out):
+    """BASELINE.json configs[2] per-GPU step: 32k packed tokens, packed GAE + single-pass actor loss with
+    dlogits + critic loss with its gradient (batch-sharded: every GPU runs exactly this)."""
+    T, V = 32768, 151936
+    rng = np.random.RandomState(2)
+    lens = make_packed(T, rng)
+    B = len(lens)
+    cu = torch.from_numpy(np.concatenate([[0], np.cumsum(lens)]).astype(np.int32)).to(DEV)
+    g = torch.Generator(device=DEV).manual_seed(2)
+    x = torch.empty(T, V, dtype=torch.bfloat16, device=DEV)
+    for i in range(0, T, 2048):
+        x[i:i + 2048] = (torch.randn(2048, V, generator=g, device=DEV) * 2).bfloat16()
+    lab = torch.randint(0, V, (T,), generator=g, device=DEV)
+    with torch.no_grad():
+        lp = F.gather_logprobs(x, lab, 1.0)
+    prox = lp + 0.02 * torch.randn(T, generator=g, device=DEV)
+    old = lp + 0.05 * torch.randn(T, generator=g, device=DEV)
+    mask = torch.rand(T, generator=g, device=DEV) > 0.2
+    rew = torch.randn(T, generator=g, device=DEV)
+    val = torch.randn(T + B, generator=g, device=DEV)
+    boot = torch.rand(B, generator=g, device=DEV) > 0.5
+    newv = torch.randn(T, generator=g, device=DEV, requires_grad=True)
+    scale = torch.full((1,), 0.5, device=DEV)
+    xr = x.requires_grad_()
+
+    def step():
+        xr.grad = None
+        newv.grad = None
+        adv, ret = P.cugae1d_nolp_misalign_func(rew, val, cu, boot, 1.0, 0.95)
+        loss, _ = F.fused_actor_loss(xr, lab, 1.0, prox, old, adv, mask, eps_clip=0.2, behav_imp_weight_cap=5.0,
+                                     loss_scale=scale)
+        (loss * scale[0]).backward()
+        closs, _ = F.ppo_critic_loss_fn(newv, val[:T], ret, 0.2, mask)
+        closs.backward()
+    ms = timeit(step, iters=10, warmup=3)
+    out.append(row("configs[2] per-GPU step (32k tokens: GAE + actor single pass + critic)", ms, 4.0 * T * V, T=T, V=V,
+                   tokens_per_s=T / (ms * 1e-3)))
+
+
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--what", default="gae,padded,advantages,aent,loss,logits,intervals")
+    ap.add_argument("--what", default="gae,padded,advantages,aent,cfg2,loss,logits,intervals")
     ap.add_argument("--out", default=None)
     args = ap.parse_args()
     what = set(args.what.split(","))
@@ -362,6 +401,8 @@ def main():
         bench_padded(out)
     if "advantages" in what:
         bench_advantages(out)
+    if "cfg2" in what:
+        bench_cfg2(out)
     if "aent" in what:
         bench_aent(out)
     if "loss" in what:
