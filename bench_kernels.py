@@ -86,7 +86,7 @@ def make_packed(T, rng, lo=128, hi=4097):
 
 def bench_gae(out, ref):
     rng = np.random.RandomState(0)
-    for logT in (15, 17, 20, 22, 24, 26, 27):
+    for logT in (15, 17, 20, 22, 24, 26, 27, 28):
         T = 1 << logT
         lens = make_packed(T, rng)
         B = len(lens)
