@@ -386,6 +386,54 @@ def bench_cfg2(out):
                    tokens_per_s=T / (ms * 1e-3)))
 
 
+def bench_lmhead(out):
+    """SURVEY 8f-4 at the configs[1] shape (Qwen2.5-1.5B: H=1536, V=151936, T=16384): LM head + actor loss +
+    all gradients, over row blocks (no [T,V] tensor) against the materialised-logits path."""
+    from areal_b200.lm_head import fused_lm_head_actor_loss
+    T, Hd, V = 16384, 1536, 151936
+    g = torch.Generator(device=DEV).manual_seed(3)
+    h = (torch.randn(T, Hd, generator=g, device=DEV)).bfloat16().requires_grad_()
+    w = (torch.randn(V, Hd, generator=g, device=DEV) * (2.0 / Hd ** 0.5)).bfloat16().requires_grad_()
+    lab = torch.randint(0, V, (T,), generator=g, device=DEV)
+    with torch.no_grad():
+        lp = torch.cat([F.gather_logprobs(torch.mm(h[i:i + 2048], w.t()), lab[i:i + 2048], 1.0)
+                        for i in range(0, T, 2048)])
+    prox = lp + 0.02 * torch.randn(T, generator=g, device=DEV)
+    old = lp + 0.05 * torch.randn(T, generator=g, device=DEV)
+    adv = torch.randn(T, generator=g, device=DEV)
+    mask = torch.rand(T, generator=g, device=DEV) > 0.2
+    scale = torch.full((1,), 0.5, device=DEV)
+    kw = dict(eps_clip=0.2, behav_imp_weight_cap=5.0)
+    flops = 3 * 2.0 * T * Hd * V
+
+    def run(fn, name, **extra):
+        torch.cuda.synchronize()
+        torch.cuda.empty_cache()
+        torch.cuda.reset_peak_memory_stats()
+        base = torch.cuda.memory_allocated()
+        ms = timeit(fn, iters=5, warmup=2)
+        peak = torch.cuda.max_memory_allocated() - base
+        out.append(row(name, ms, 4.0 * T * V, T=T, H=Hd, V=V, tokens_per_s=T / (ms * 1e-3),
+                       gemm_tflops=round(flops / (ms * 1e-3) / 1e12, 1), peak_extra_bytes=int(peak), **extra))
+
+    def materialised():
+        h.grad = None
+        w.grad = None
+        logits = torch.mm(h, w.t())
+        loss, _ = F.fused_actor_loss(logits, lab, 1.0, prox, old, adv, mask, loss_scale=scale, **kw)
+        (loss * scale[0]).backward()
+    run(materialised, "lm head + actor loss, materialised [T,V] logits (torch.mm + single pass + autograd GEMMs)")
+    for chunk, wd in ((4096, torch.float32), (2048, torch.float32), (4096, torch.bfloat16), (1024, torch.bfloat16)):
+        def blocks():
+            h.grad = None
+            w.grad = None
+            loss, _ = fused_lm_head_actor_loss(h, w, lab, 1.0, prox, old, adv, mask, loss_scale=scale,
+                                               chunk_rows=chunk, wgrad_dtype=wd, **kw)
+            (loss * scale[0]).backward()
+        run(blocks, "lm head + actor loss over row blocks (no [T,V] tensor)", chunk_rows=chunk,
+            wgrad_accumulator=str(wd).replace("torch.", ""))
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--what", default="gae,padded,advantages,aent,cfg2,loss,logits,intervals")
@@ -405,6 +453,8 @@ def main():
         bench_cfg2(out)
     if "aent" in what:
         bench_aent(out)
+    if "lmhead" in what:
+        bench_lmhead(out)
     if "loss" in what:
         bench_loss(out)
     if "logits" in what:
