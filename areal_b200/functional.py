@@ -14,6 +14,7 @@ CUDA tensors only; there is no CPU / eager fallback.
 from __future__ import annotations
 
 import math
+import sys
 from typing import Dict, Optional, Tuple
 
 import torch
@@ -114,18 +115,97 @@ class _GatherLogprobsEntropy(torch.autograd.Function):
         return d.view(ctx.in_shape), None, None, None
 
 
+# The two distributed branches INSIDE the reference functions (areal/utils/functional.py:50-58 and 91-98:
+# Megatron tensor parallelism, logits sharded over the vocabulary; :76-79 and :120-125: Ulysses sequence
+# parallelism, every rank holds a slice of the tokens and the results are all-gathered).
+_GROUPS = {"explicit": False, "tp": None, "sp": None}
+
+
+def set_parallel_groups(tp_group=None, sp_group=None) -> None:
+    """Tell gather_logprobs / gather_logprobs_entropy which process groups shard the vocabulary (tp) and
+    the sequence (sp).  Without this call the groups are looked up where the reference looks them up --
+    `megatron.core.parallel_state` and `areal.utils.ulysses` -- if the host program has imported them.
+    `set_parallel_groups()` with no arguments pins both branches off."""
+    _GROUPS.update(explicit=True, tp=tp_group, sp=sp_group)
+
+
+def reset_parallel_groups() -> None:
+    _GROUPS.update(explicit=False, tp=None, sp=None)
+
+
+def _world(group) -> int:
+    import torch.distributed as dist
+    return dist.get_world_size(group) if (group is not None and dist.is_initialized()) else 1
+
+
+def _tp_group():
+    if _GROUPS["explicit"]:
+        g = _GROUPS["tp"]
+        return g if _world(g) > 1 else None
+    mpu = sys.modules.get("megatron.core.parallel_state")
+    try:
+        if mpu is not None and mpu.is_initialized() and mpu.get_tensor_model_parallel_world_size() > 1:
+            return mpu.get_tensor_model_parallel_group()
+    except Exception:
+        pass
+    return None
+
+
+def _sp_group():
+    if _GROUPS["explicit"]:
+        g = _GROUPS["sp"]
+        return g if _world(g) > 1 else None
+    uly = sys.modules.get("areal.utils.ulysses")
+    try:
+        if uly is not None and uly.get_ulysses_sequence_parallel_world_size() > 1:
+            return uly.get_ulysses_sequence_parallel_group()
+    except Exception:
+        pass
+    return None
+
+
+def _sp_all_gather(x: torch.Tensor, group) -> torch.Tensor:
+    """functional.py:76-79: differentiable all-gather over the sequence-parallel group, concatenated on
+    the last (token) dimension in rank order."""
+    import torch.distributed.nn.functional as dist_F
+    return torch.cat(dist_F.all_gather(x, group=group), dim=-1)
+
+
+def _vocab_parallel(logits, labels, temperature, group):
+    from .dist import vocab_parallel_logprobs_entropy
+    lp, ent = vocab_parallel_logprobs_entropy(logits, labels, temperature, group=group)
+    return lp.view(labels.shape), ent.view(labels.shape)
+
+
 def gather_logprobs(logits: torch.Tensor, labels: torch.Tensor, temperature: float = 1.0,
                     chunk_size: int = 1024) -> torch.Tensor:
     """log_softmax(logits.float() / temperature)[..., labels]  (reference functional.py:43-81).
     `chunk_size` is accepted for signature compatibility; the kernel streams rows and needs no
-    chunking.  Differentiable w.r.t. `logits` (gradient in the logits' dtype)."""
-    return _GatherLogprobsEntropy.apply(logits, labels, temperature, False)
+    chunking.  Differentiable w.r.t. `logits` (gradient in the logits' dtype).  Under tensor
+    parallelism `logits` is this rank's vocabulary shard and `labels` hold global ids (:50-58); under
+    Ulysses the per-rank results are all-gathered (:76-79)."""
+    tp = _tp_group()
+    if tp is not None:
+        return _vocab_parallel(logits, labels, temperature, tp)[0]
+    logp = _GatherLogprobsEntropy.apply(logits, labels, temperature, False)
+    sp = _sp_group()
+    if sp is not None:
+        logp = _sp_all_gather(logp, sp)
+    return logp
 
 
 def gather_logprobs_entropy(logits: torch.Tensor, labels: torch.Tensor, temperature: float = 1.0,
                             chunk_size: int = 1024) -> Tuple[torch.Tensor, torch.Tensor]:
-    """(log-prob of labels, entropy of softmax(logits/temperature))  (reference functional.py:84-127)."""
-    return _GatherLogprobsEntropy.apply(logits, labels, temperature, True)
+    """(log-prob of labels, entropy of softmax(logits/temperature))  (reference functional.py:84-127),
+    with the same two distributed branches (:91-98, :120-125)."""
+    tp = _tp_group()
+    if tp is not None:
+        return _vocab_parallel(logits, labels, temperature, tp)
+    logp, ent = _GatherLogprobsEntropy.apply(logits, labels, temperature, True)
+    sp = _sp_group()
+    if sp is not None:
+        logp, ent = _sp_all_gather(logp, sp), _sp_all_gather(ent, sp)
+    return logp, ent
 
 
 @torch.no_grad()

@@ -42,6 +42,26 @@ def main():
     gs = full.grad[:, rank * Vs:(rank + 1) * Vs].float()
     assert torch.allclose(shard.grad.float(), gs, rtol=2 ** -7, atol=1e-9), (shard.grad.float() - gs).abs().max()
 
+    # ---------------- the two distributed branches inside gather_logprobs(_entropy) ---------------------
+    # (areal/utils/functional.py:50-58, 91-98: vocabulary shards; :76-79, 120-125: Ulysses token slices)
+    F.set_parallel_groups(tp_group=dist.group.WORLD)
+    shard_tp = logits[:, rank * Vs:(rank + 1) * Vs].detach().clone().requires_grad_()
+    lp_tp, ent_tp = F.gather_logprobs_entropy(shard_tp, labels, 0.9)
+    ((lp_tp * w_lp).sum() + (ent_tp * w_h).sum()).backward()
+    assert torch.equal(lp_tp, lp) and torch.equal(ent_tp, ent) and torch.equal(shard_tp.grad, shard.grad)
+    assert torch.equal(F.gather_logprobs(shard_tp.detach(), labels, 0.9), lp.detach())
+    F.set_parallel_groups(sp_group=dist.group.WORLD)
+    Tr = T // world
+    rows = logits[rank * Tr:(rank + 1) * Tr].detach().clone().requires_grad_()
+    lp_sp, ent_sp = F.gather_logprobs_entropy(rows, labels[rank * Tr:(rank + 1) * Tr], 0.9)
+    assert lp_sp.shape == (Tr * world,)
+    assert torch.equal(lp_sp.detach(), lp1.detach()[:Tr * world]) and torch.equal(ent_sp.detach(), ent1.detach()[:Tr * world])
+    ((lp_sp * w_lp[:Tr * world]).sum() + (ent_sp * w_h[:Tr * world]).sum()).backward()
+    # every rank back-propagates the same (replicated) loss, so the gathered gradient is world x the local one
+    want_rows = full.grad[rank * Tr:(rank + 1) * Tr].float() * world
+    assert torch.allclose(rows.grad.float(), want_rows, rtol=2 ** -6, atol=1e-9), (rows.grad.float() - want_rows).abs().max()
+    F.reset_parallel_groups()
+
     # ---------------- the same exchange over NVLink peer memory (no all-gather) -------------------------
     try:
         ex = D.PeerExchange(max_tokens=4096)

@@ -74,6 +74,23 @@ def _worker(rank, world, port, out):
         assert np.allclose(logp.numpy(), ref_lp, atol=1e-4) and np.allclose(ent.numpy(), ref_ent, atol=1e-4)
         assert np.array_equal(row_max.numpy(), ref_max.astype(np.float64))
         assert np.allclose(row_max.numpy() / 0.7 + ln_s.numpy(), ref_lse, atol=1e-4)
+        # ---- Ulysses branch of gather_logprobs (areal/utils/functional.py:76-79): differentiable
+        # all-gather of the per-rank token slices, concatenated in rank order; group look-up rules
+        from areal_b200 import functional as F
+        F.reset_parallel_groups()
+        assert F._tp_group() is None and F._sp_group() is None        # nothing imported, nothing set
+        F.set_parallel_groups(sp_group=dist.group.WORLD)
+        assert F._tp_group() is None and F._sp_group() is dist.group.WORLD
+        mine_lp = torch.arange(5, dtype=torch.float32) + 10.0 * rank
+        mine_lp.requires_grad_()
+        both = F._sp_all_gather(mine_lp, F._sp_group())
+        assert torch.equal(both.detach(), torch.cat([torch.arange(5.0), torch.arange(5.0) + 10.0]))
+        wts = torch.arange(10, dtype=torch.float32) + 1.0
+        (both * wts).sum().backward()                                  # every rank back-propagates the same loss
+        assert torch.equal(mine_lp.grad, world * wts[rank * 5:(rank + 1) * 5])
+        F.set_parallel_groups()                                        # pinned off
+        assert F._sp_group() is None
+        F.reset_parallel_groups()
         out[rank] = 1
     finally:
         dist.destroy_process_group()
