@@ -75,6 +75,56 @@ __device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity)
       : "memory");
 }
 
+// Gradient of one 16-byte vector when only the log-prob carries a gradient (k1 == 0, the fused actor
+// step: the entropy is detached): d = -gl * p = -/+ 2^(x*c2 + nbias) with nbias = -m*c2 - log2 S + log2|gl|,
+// i.e. the scale rides in the exponent: one FFMA + one MUFU per element, the sign folded into the pack.
+template <bool kNeg>
+__device__ __forceinline__ uint32_t grad_pair_exp(uint32_t wd, float c2, float nbias) {
+  const float e0 = ex2_approx(fmaf(bf16_lo(wd), c2, nbias));
+  const float e1 = ex2_approx(fmaf(bf16_hi(wd), c2, nbias));
+  const uint32_t o = pack_bf16x2(e0, e1);
+  return kNeg ? (o ^ 0x80008000u) : o;
+}
+
+template <bool kNeg>
+__device__ __forceinline__ uint4 grad_vec_exp(const uint4& q, float c2, float nbias, float gl, int lab_off) {
+  uint4 o;
+  o.x = grad_pair_exp<kNeg>(q.x, c2, nbias);
+  o.y = grad_pair_exp<kNeg>(q.y, c2, nbias);
+  o.z = grad_pair_exp<kNeg>(q.z, c2, nbias);
+  o.w = grad_pair_exp<kNeg>(q.w, c2, nbias);
+  if (static_cast<unsigned>(lab_off) < 8u) {   // one vector per row: the label's element gets + gl before rounding
+    const int wi = lab_off >> 1;
+    const uint32_t wd = wi == 0 ? q.x : (wi == 1 ? q.y : (wi == 2 ? q.z : q.w));
+    const bool hi = lab_off & 1;
+    const float e = ex2_approx(fmaf(hi ? bf16_hi(wd) : bf16_lo(wd), c2, nbias));
+    const float dd = (kNeg ? -e : e) + gl;
+    const uint32_t keep = hi ? 0x0000ffffu : 0xffff0000u;
+    const uint32_t h = pack_bf16x2(dd, dd) & ~keep;
+    if (wi == 0) o.x = (o.x & keep) | h;
+    else if (wi == 1) o.y = (o.y & keep) | h;
+    else if (wi == 2) o.z = (o.z & keep) | h;
+    else o.w = (o.w & keep) | h;
+  }
+  return o;
+}
+
+// lab32: the label's element index inside this CTA's slice, or a large negative number
+template <bool kNeg>
+__device__ __forceinline__ void grad_slice(uint32_t sbase, char* dst, int my_nvec, int gt, float c2, float nbias,
+                                           float gl, int lab32) {
+  int v = gt;
+  for (; v + kGroupThreads < my_nvec; v += 2 * kGroupThreads) {
+    const uint4 q0 = lds_v4(sbase + v * 16);
+    const uint4 q1 = lds_v4(sbase + (v + kGroupThreads) * 16);
+    stg_stream_v4(dst + int64_t(v) * 16, grad_vec_exp<kNeg>(q0, c2, nbias, gl, lab32 - v * 8));
+    stg_stream_v4(dst + int64_t(v + kGroupThreads) * 16,
+                  grad_vec_exp<kNeg>(q1, c2, nbias, gl, lab32 - (v + kGroupThreads) * 8));
+  }
+  if (v < my_nvec)
+    stg_stream_v4(dst + int64_t(v) * 16, grad_vec_exp<kNeg>(lds_v4(sbase + v * 16), c2, nbias, gl, lab32 - v * 8));
+}
+
 struct RRShared {
   float m[kMaxBuf][kGroupWarps], s[kMaxBuf][kGroupWarps], w[kMaxBuf][kGroupWarps], mn[kMaxBuf][kGroupWarps];   // [slice buffer]
   float xchg[2][kMaxCluster][8];    // [row parity][source CTA rank][m, S, W, xl, mn]
@@ -338,24 +388,19 @@ fused_rowres_kernel(const LogitsFwdParams p, void* __restrict__ dlogits, int64_t
       const int64_t lab = p.labels[row] - p.vocab_start;
       mbar_wait(smem_u32(&ready_bar[b]), ph);
       if (my_bytes) mbar_wait(smem_u32(&full_bar[b]), ph);
-      RowGrad g;
-      g.m = *reinterpret_cast<const volatile float*>(&sh.rowinfo[b][0]);
-      g.nl2s = *reinterpret_cast<const volatile float*>(&sh.rowinfo[b][1]);
-      g.gl = *reinterpret_cast<const volatile float*>(&sh.rowinfo[b][2]);
-      g.k0 = -g.gl;
-      g.k1 = 0.f;
+      const float row_m = *reinterpret_cast<const volatile float*>(&sh.rowinfo[b][0]);
+      const float nl2s = *reinterpret_cast<const volatile float*>(&sh.rowinfo[b][1]);   // -log2 S
+      const float gl = *reinterpret_cast<const volatile float*>(&sh.rowinfo[b][2]);
       char* dst = reinterpret_cast<char*>(dlogits) + row * d_row_stride_bytes + v0 * 16;
-      if (g.gl != 0.f) {
+      if (gl != 0.f) {
+        // d = gl * (1[label] - p):  -gl * p = -/+ 2^((x - m) * c2 - log2 S + log2 |gl|)
+        const float nbias = fmaf(-row_m, c2, nl2s + lg2_approx(fabsf(gl)));
         const int64_t lab_local = lab - v0 * 8;
-        int v = gt;
-        for (; v + kGroupThreads < my_nvec; v += 2 * kGroupThreads) {
-          const uint4 q0 = lds_v4(sbase + v * 16);
-          const uint4 q1 = lds_v4(sbase + (v + kGroupThreads) * 16);
-          stg_stream_v4(dst + int64_t(v) * 16, grad_vec(q0, g, c2, lab_local - int64_t(v) * 8));
-          stg_stream_v4(dst + int64_t(v + kGroupThreads) * 16,
-                        grad_vec(q1, g, c2, lab_local - int64_t(v + kGroupThreads) * 8));
-        }
-        if (v < my_nvec) stg_stream_v4(dst + int64_t(v) * 16, grad_vec(lds_v4(sbase + v * 16), g, c2, lab_local - int64_t(v) * 8));
+        const int lab32 = (lab_local >= 0 && lab_local < int64_t(my_nvec) * 8) ? static_cast<int>(lab_local) : -(1 << 30);
+        if (gl > 0.f)
+          grad_slice<true>(sbase, dst, my_nvec, gt, c2, nbias, gl, lab32);
+        else
+          grad_slice<false>(sbase, dst, my_nvec, gt, c2, nbias, gl, lab32);
       } else {
         const uint4 z = make_uint4(0u, 0u, 0u, 0u);
         for (int v = gt; v < my_nvec; v += kGroupThreads) stg_stream_v4(dst + int64_t(v) * 16, z);
