@@ -91,6 +91,14 @@ __device__ __forceinline__ void stg_stream_v4(void* p, const uint4& v) {
                "r"(v.z), "r"(v.w)
                : "memory");
 }
+__device__ __forceinline__ void stg_u16(void* p, uint16_t v) {
+  asm volatile("st.global.L1::no_allocate.u16 [%0], %1;" ::"l"(p), "h"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t lds_u16(uint32_t saddr) {
+  uint16_t r;
+  asm volatile("ld.shared.u16 %0, [%1];" : "=h"(r) : "r"(saddr));
+  return r;
+}
 __device__ __forceinline__ uint4 lds_v4(uint32_t saddr) {
   uint4 r;
   asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"

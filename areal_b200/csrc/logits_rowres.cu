@@ -75,6 +75,27 @@ __device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity)
       : "memory");
 }
 
+// statistics of kN vectors (kGroupThreads apart) with ONE rebase: packed bf16x2 max / min first
+template <int kN>
+__device__ __forceinline__ void stats_step(RowState& st, uint32_t sbase, int v, float c2) {
+  uint4 q[kN];
+#pragma unroll
+  for (int j = 0; j < kN; ++j) q[j] = lds_v4(sbase + (v + j * kGroupThreads) * 16);
+  uint32_t mx = vec_max_bf16(q[0]), mn = vec_min_bf16(q[0]);
+#pragma unroll
+  for (int j = 1; j < kN; ++j) {
+    mx = max_bf16x2(mx, vec_max_bf16(q[j]));
+    mn = min_bf16x2(mn, vec_min_bf16(q[j]));
+  }
+  st.mn = fminf(st.mn, fminf(bf16_lo(mn), bf16_hi(mn)));
+  const float nb = state_rebase(st, fmaxf(bf16_lo(mx), bf16_hi(mx)), c2);
+  float s0 = 0.f, s1 = 0.f, w0 = 0.f, w1 = 0.f;
+#pragma unroll
+  for (int j = 0; j < kN; ++j) vec_accumulate(q[j], c2, nb, s0, s1, w0, w1);
+  st.s += s0 + s1;
+  st.w += w0 + w1;
+}
+
 // Gradient of one 16-byte vector when only the log-prob carries a gradient (k1 == 0, the fused actor
 // step: the entropy is detached): d = -gl * p = -/+ 2^(x*c2 + nbias) with nbias = -m*c2 - log2 S + log2|gl|,
 // i.e. the scale rides in the exponent: one FFMA + one MUFU per element, the sign folded into the pack.
@@ -87,29 +108,18 @@ __device__ __forceinline__ uint32_t grad_pair_exp(uint32_t wd, float c2, float n
 }
 
 template <bool kNeg>
-__device__ __forceinline__ uint4 grad_vec_exp(const uint4& q, float c2, float nbias, float gl, int lab_off) {
+__device__ __forceinline__ uint4 grad_vec_exp(const uint4& q, float c2, float nbias) {
   uint4 o;
   o.x = grad_pair_exp<kNeg>(q.x, c2, nbias);
   o.y = grad_pair_exp<kNeg>(q.y, c2, nbias);
   o.z = grad_pair_exp<kNeg>(q.z, c2, nbias);
   o.w = grad_pair_exp<kNeg>(q.w, c2, nbias);
-  if (static_cast<unsigned>(lab_off) < 8u) {   // one vector per row: the label's element gets + gl before rounding
-    const int wi = lab_off >> 1;
-    const uint32_t wd = wi == 0 ? q.x : (wi == 1 ? q.y : (wi == 2 ? q.z : q.w));
-    const bool hi = lab_off & 1;
-    const float e = ex2_approx(fmaf(hi ? bf16_hi(wd) : bf16_lo(wd), c2, nbias));
-    const float dd = (kNeg ? -e : e) + gl;
-    const uint32_t keep = hi ? 0x0000ffffu : 0xffff0000u;
-    const uint32_t h = pack_bf16x2(dd, dd) & ~keep;
-    if (wi == 0) o.x = (o.x & keep) | h;
-    else if (wi == 1) o.y = (o.y & keep) | h;
-    else if (wi == 2) o.z = (o.z & keep) | h;
-    else o.w = (o.w & keep) | h;
-  }
   return o;
 }
 
-// lab32: the label's element index inside this CTA's slice, or a large negative number
+// lab32: the label's element index inside this CTA's slice, or negative.  The label's element is the
+// only one that gets + gl: the thread that stored its vector overwrites those 2 bytes afterwards (same
+// thread, same address: program order), so the vector loop carries no label test.
 template <bool kNeg>
 __device__ __forceinline__ void grad_slice(uint32_t sbase, char* dst, int my_nvec, int gt, float c2, float nbias,
                                            float gl, int lab32) {
@@ -117,12 +127,16 @@ __device__ __forceinline__ void grad_slice(uint32_t sbase, char* dst, int my_nve
   for (; v + kGroupThreads < my_nvec; v += 2 * kGroupThreads) {
     const uint4 q0 = lds_v4(sbase + v * 16);
     const uint4 q1 = lds_v4(sbase + (v + kGroupThreads) * 16);
-    stg_stream_v4(dst + int64_t(v) * 16, grad_vec_exp<kNeg>(q0, c2, nbias, gl, lab32 - v * 8));
-    stg_stream_v4(dst + int64_t(v + kGroupThreads) * 16,
-                  grad_vec_exp<kNeg>(q1, c2, nbias, gl, lab32 - (v + kGroupThreads) * 8));
+    stg_stream_v4(dst + int64_t(v) * 16, grad_vec_exp<kNeg>(q0, c2, nbias));
+    stg_stream_v4(dst + int64_t(v + kGroupThreads) * 16, grad_vec_exp<kNeg>(q1, c2, nbias));
   }
-  if (v < my_nvec)
-    stg_stream_v4(dst + int64_t(v) * 16, grad_vec_exp<kNeg>(lds_v4(sbase + v * 16), c2, nbias, gl, lab32 - v * 8));
+  if (v < my_nvec) stg_stream_v4(dst + int64_t(v) * 16, grad_vec_exp<kNeg>(lds_v4(sbase + v * 16), c2, nbias));
+  if (lab32 >= 0 && ((lab32 >> 3) & (kGroupThreads - 1)) == gt) {
+    const uint32_t raw = lds_u16(sbase + uint32_t(lab32) * 2u);
+    const float e = ex2_approx(fmaf(__uint_as_float(raw << 16), c2, nbias));
+    const float dd = (kNeg ? -e : e) + gl;
+    stg_u16(dst + int64_t(lab32) * 2, static_cast<uint16_t>(pack_bf16x2(dd, dd) & 0xffffu));
+  }
 }
 
 struct RRShared {
@@ -220,26 +234,12 @@ fused_rowres_kernel(const LogitsFwdParams p, void* __restrict__ dlogits, int64_t
       state_init(st);
       {
         int v = tid;
-        for (; v + 3 * kGroupThreads < my_nvec; v += 4 * kGroupThreads) {
-          const uint4 q0 = lds_v4(sbase + v * 16);
-          const uint4 q1 = lds_v4(sbase + (v + kGroupThreads) * 16);
-          const uint4 q2 = lds_v4(sbase + (v + 2 * kGroupThreads) * 16);
-          const uint4 q3 = lds_v4(sbase + (v + 3 * kGroupThreads) * 16);
-          const uint32_t mx = max_bf16x2(max_bf16x2(vec_max_bf16(q0), vec_max_bf16(q1)),
-                                         max_bf16x2(vec_max_bf16(q2), vec_max_bf16(q3)));
-          const uint32_t mn = min_bf16x2(min_bf16x2(vec_min_bf16(q0), vec_min_bf16(q1)),
-                                         min_bf16x2(vec_min_bf16(q2), vec_min_bf16(q3)));
-          st.mn = fminf(st.mn, fminf(bf16_lo(mn), bf16_hi(mn)));
-          const float nb = state_rebase(st, fmaxf(bf16_lo(mx), bf16_hi(mx)), c2);
-          float s0 = 0.f, s1 = 0.f, w0 = 0.f, w1 = 0.f;
-          vec_accumulate(q0, c2, nb, s0, s1, w0, w1);
-          vec_accumulate(q1, c2, nb, s0, s1, w0, w1);
-          vec_accumulate(q2, c2, nb, s0, s1, w0, w1);
-          vec_accumulate(q3, c2, nb, s0, s1, w0, w1);
-          st.s += s0 + s1;
-          st.w += w0 + w1;
+        for (; v + 3 * kGroupThreads < my_nvec; v += 4 * kGroupThreads) stats_step<4>(st, sbase, v, c2);
+        if (v + kGroupThreads < my_nvec) {      // fewer than four vectors left for this thread: 2 + 1
+          stats_step<2>(st, sbase, v, c2);
+          v += 2 * kGroupThreads;
         }
-        for (; v < my_nvec; v += kGroupThreads) consume_vec<true>(st, lds_v4(sbase + v * 16), c2);
+        if (v < my_nvec) stats_step<1>(st, sbase, v, c2);
       }
       state_canonical(st, c2);
 #pragma unroll
@@ -396,7 +396,7 @@ fused_rowres_kernel(const LogitsFwdParams p, void* __restrict__ dlogits, int64_t
         // d = gl * (1[label] - p):  -gl * p = -/+ 2^((x - m) * c2 - log2 S + log2 |gl|)
         const float nbias = fmaf(-row_m, c2, nl2s + lg2_approx(fabsf(gl)));
         const int64_t lab_local = lab - v0 * 8;
-        const int lab32 = (lab_local >= 0 && lab_local < int64_t(my_nvec) * 8) ? static_cast<int>(lab_local) : -(1 << 30);
+        const int lab32 = (lab_local >= 0 && lab_local < int64_t(my_nvec) * 8) ? static_cast<int>(lab_local) : -1;
         if (gl > 0.f)
           grad_slice<true>(sbase, dst, my_nvec, gt, c2, nbias, gl, lab32);
         else
