@@ -127,6 +127,28 @@ __device__ __forceinline__ uint4 grad_vec(const uint4& q, const RowGrad& g, floa
 }
 
 
+// Gradient of one 16-byte vector when only the log-prob carries a gradient (k1 == 0, the fused actor
+// step: the entropy is detached): d = -gl * p = -/+ 2^(x*c2 + nbias) with nbias = -m*c2 - log2 S + log2|gl|,
+// i.e. the scale rides in the exponent: one FFMA + one MUFU per element, the sign folded into the pack.
+template <bool kNeg>
+__device__ __forceinline__ uint32_t grad_pair_exp(uint32_t wd, float c2, float nbias) {
+  const float e0 = ex2_approx(fmaf(bf16_lo(wd), c2, nbias));
+  const float e1 = ex2_approx(fmaf(bf16_hi(wd), c2, nbias));
+  const uint32_t o = pack_bf16x2(e0, e1);
+  return kNeg ? (o ^ 0x80008000u) : o;
+}
+
+template <bool kNeg>
+__device__ __forceinline__ uint4 grad_vec_exp(const uint4& q, float c2, float nbias) {
+  uint4 o;
+  o.x = grad_pair_exp<kNeg>(q.x, c2, nbias);
+  o.y = grad_pair_exp<kNeg>(q.y, c2, nbias);
+  o.z = grad_pair_exp<kNeg>(q.z, c2, nbias);
+  o.w = grad_pair_exp<kNeg>(q.w, c2, nbias);
+  return o;
+}
+
+
 // ---- element traits: how a 16-byte vector of logits unpacks to fp32 and packs back -------------------
 struct ElemBF16 {
   static constexpr int kN = 8, kSize = 2;

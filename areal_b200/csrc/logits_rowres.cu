@@ -96,33 +96,14 @@ __device__ __forceinline__ void stats_step(RowState& st, uint32_t sbase, int v, 
   st.w += w0 + w1;
 }
 
-// Gradient of one 16-byte vector when only the log-prob carries a gradient (k1 == 0, the fused actor
-// step: the entropy is detached): d = -gl * p = -/+ 2^(x*c2 + nbias) with nbias = -m*c2 - log2 S + log2|gl|,
-// i.e. the scale rides in the exponent: one FFMA + one MUFU per element, the sign folded into the pack.
-template <bool kNeg>
-__device__ __forceinline__ uint32_t grad_pair_exp(uint32_t wd, float c2, float nbias) {
-  const float e0 = ex2_approx(fmaf(bf16_lo(wd), c2, nbias));
-  const float e1 = ex2_approx(fmaf(bf16_hi(wd), c2, nbias));
-  const uint32_t o = pack_bf16x2(e0, e1);
-  return kNeg ? (o ^ 0x80008000u) : o;
-}
-
-template <bool kNeg>
-__device__ __forceinline__ uint4 grad_vec_exp(const uint4& q, float c2, float nbias) {
-  uint4 o;
-  o.x = grad_pair_exp<kNeg>(q.x, c2, nbias);
-  o.y = grad_pair_exp<kNeg>(q.y, c2, nbias);
-  o.z = grad_pair_exp<kNeg>(q.z, c2, nbias);
-  o.w = grad_pair_exp<kNeg>(q.w, c2, nbias);
-  return o;
-}
-
 // lab32: the label's element index inside this CTA's slice, or negative.  The label's element is the
 // only one that gets + gl: the thread that stored its vector overwrites those 2 bytes afterwards (same
-// thread, same address: program order), so the vector loop carries no label test.
+// thread, same address: program order), so the vector loop carries no label test.  That element is
+// gl * (1 - p), a cancellation when the row is peaked (p -> 1): p comes from (x - m) * c2 - log2 S there,
+// exact in its leading term, not from the folded exponent (whose 1e-6 relative error would be the result).
 template <bool kNeg>
 __device__ __forceinline__ void grad_slice(uint32_t sbase, char* dst, int my_nvec, int gt, float c2, float nbias,
-                                           float gl, int lab32) {
+                                           float gl, float row_m, float nl2s, int lab32) {
   int v = gt;
   for (; v + kGroupThreads < my_nvec; v += 2 * kGroupThreads) {
     const uint4 q0 = lds_v4(sbase + v * 16);
@@ -132,9 +113,9 @@ __device__ __forceinline__ void grad_slice(uint32_t sbase, char* dst, int my_nve
   }
   if (v < my_nvec) stg_stream_v4(dst + int64_t(v) * 16, grad_vec_exp<kNeg>(lds_v4(sbase + v * 16), c2, nbias));
   if (lab32 >= 0 && ((lab32 >> 3) & (kGroupThreads - 1)) == gt) {
-    const uint32_t raw = lds_u16(sbase + uint32_t(lab32) * 2u);
-    const float e = ex2_approx(fmaf(__uint_as_float(raw << 16), c2, nbias));
-    const float dd = (kNeg ? -e : e) + gl;
+    const float x = __uint_as_float(lds_u16(sbase + uint32_t(lab32) * 2u) << 16);
+    const float pv = ex2_approx(fmaf(x - row_m, c2, nl2s));
+    const float dd = fmaf(-gl, pv, gl);
     stg_u16(dst + int64_t(lab32) * 2, static_cast<uint16_t>(pack_bf16x2(dd, dd) & 0xffffu));
   }
 }
@@ -398,9 +379,9 @@ fused_rowres_kernel(const LogitsFwdParams p, void* __restrict__ dlogits, int64_t
         const int64_t lab_local = lab - v0 * 8;
         const int lab32 = (lab_local >= 0 && lab_local < int64_t(my_nvec) * 8) ? static_cast<int>(lab_local) : -1;
         if (gl > 0.f)
-          grad_slice<true>(sbase, dst, my_nvec, gt, c2, nbias, gl, lab32);
+          grad_slice<true>(sbase, dst, my_nvec, gt, c2, nbias, gl, row_m, nl2s, lab32);
         else
-          grad_slice<false>(sbase, dst, my_nvec, gt, c2, nbias, gl, lab32);
+          grad_slice<false>(sbase, dst, my_nvec, gt, c2, nbias, gl, row_m, nl2s, lab32);
       } else {
         const uint4 z = make_uint4(0u, 0u, 0u, 0u);
         for (int v = gt; v < my_nvec; v += kGroupThreads) stg_stream_v4(dst + int64_t(v) * 16, z);

@@ -202,3 +202,36 @@ def test_single_pass_row_resident_equals_two_pass(V, cluster, nbuf):
                                   loss_scale=scale, cluster_size=cluster, n_buffers=nbuf, **cfg)
     (loss3 * 1.5).backward()
     assert torch.allclose(x3.grad.float() * (scale / 1.5), x2.grad.float(), rtol=2 ** -6, atol=1e-10)
+
+
+def test_single_pass_peaked_rows_keep_relative_accuracy_at_the_label():
+    """p_label -> 1: the label's gradient gl * (1 - p) is a cancellation; the single-pass kernel writes the
+    other elements as 2^(x*c2 + bias) with the scale folded into the exponent, but must keep the label's
+    element right to a few percent RELATIVE (same bar as the two-pass test in test_gpu_logits.py)."""
+    from areal_b200 import functional as F
+    g = torch.Generator().manual_seed(22)
+    T, V = 12, 151936
+    logits = (torch.randn(T, V, generator=g) * 2.0).bfloat16()
+    labels = torch.randint(0, V, (T,), generator=g)
+    for t in range(T):
+        logits[t, labels[t]] = 21.0 + 0.5 * t      # 1 - p_label from ~8e-4 down to ~3e-6
+    lp_ref, *_ = O.gather_logprobs_entropy(logits.float().numpy(), labels.numpy(), 1.0)
+    old = torch.from_numpy(lp_ref).float()
+    adv = torch.randn(T, generator=g).sign() * (0.5 + torch.rand(T, generator=g))    # both signs of gl
+    mask = torch.ones(T, dtype=torch.bool)
+    scale = 0.7
+    x = logits.to(D).requires_grad_()
+    loss, _ = F.fused_actor_loss(x, labels.to(D), 1.0, None, old.to(D), adv.to(D), mask.to(D), eps_clip=0.2,
+                                 loss_scale=scale)
+    (loss * scale).backward()
+    _, _, coef = O.ppo_actor_loss(lp_ref, None, old.numpy().astype(np.float64), adv.numpy().astype(np.float64),
+                                  eps_clip=0.2, loss_mask=mask.numpy(), dtype=np.float64)
+    ref = O.dlogits(logits.float().numpy(), labels.numpy(), 1.0, scale * coef)
+    got = x.grad.float().cpu().numpy().astype(np.float64)
+    lab = labels.numpy()
+    r_lab = ref[np.arange(T), lab]
+    assert np.all(np.abs(got[np.arange(T), lab] - r_lab) <= 0.05 * np.abs(r_lab) + 1e-12)
+    # everything else: bf16 rounding of the reference plus 1e-3 of the row scale
+    rs = np.abs(ref).max(-1, keepdims=True)
+    assert np.all(np.abs(got - ref) <= 2 ** -8 * np.abs(ref) + 0.05 * np.abs(r_lab)[:, None] * (np.arange(V)[None, :] == lab[:, None])
+                  + H.TOL_LOGITS * 1e-3 * rs + 1e-30)
