@@ -140,10 +140,22 @@ def grpo_loss_fn(logits: torch.Tensor, input_data: Dict, temperature: float, eps
     loss_mask = input_data.get("full_loss_mask", input_data["loss_mask"]).bool()
     prox_logp = input_data["prox_logp"]
 
-    loss, stat = F.fused_actor_loss(logits, labels, temperature, prox_logp, old_logp, advantages, loss_mask, eps_clip,
-                                    eps_clip_higher=eps_clip_higher, c_clip=c_clip,
-                                    behav_imp_weight_cap=behav_imp_weight_cap, with_logits_minmax=True,
-                                    loss_scale=loss_scale)
+    if F._tp_group() is not None or F._sp_group() is not None:
+        # vocabulary shards (Megatron TP) or token slices (Ulysses): the log-probs cross ranks inside
+        # gather_logprobs_entropy, so the loss runs on its result as upstream (:329-347); min / max are of
+        # the local logits, as upstream (:375-376)
+        logprobs, entropy = F.gather_logprobs_entropy(logits, labels, temperature)
+        loss, stat = F.ppo_actor_loss_fn(logprobs, prox_logp, old_logp, advantages, eps_clip, loss_mask,
+                                         eps_clip_higher=eps_clip_higher, c_clip=c_clip,
+                                         behav_imp_weight_cap=behav_imp_weight_cap)
+        stat = dict(stat, logprobs=logprobs.detach(), entropy=entropy.detach().float(),
+                    vocab_min_logits=logits.detach().min(-1).values.float(),
+                    vocab_max_logits=logits.detach().max(-1).values.float())
+    else:
+        loss, stat = F.fused_actor_loss(logits, labels, temperature, prox_logp, old_logp, advantages, loss_mask,
+                                        eps_clip, eps_clip_higher=eps_clip_higher, c_clip=c_clip,
+                                        behav_imp_weight_cap=behav_imp_weight_cap, with_logits_minmax=True,
+                                        loss_scale=loss_scale)
     old_f = old_logp if old_logp.dtype == torch.float32 else old_logp.float()
     denominators = dict(n_tokens=_all_tokens(logits.shape[0], logits.device), n_valid_tokens=loss_mask,
                         clipped_tokens=stat["clip_mask"], dual_clipped_tokens=stat["dual_clip_mask"])

@@ -385,7 +385,7 @@ def run_ours(args):
 
 # dram__bytes_read.sum + dram__bytes_write.sum of one launch, (kernel, T, V) -> (bytes, capture)
 NCU_DRAM_BYTES = {
-    ("fused_rowres_kernel", 16384, 151936): (4.979197e9 + 4.926511e9, "profiles/ncu_rowres_r1.txt"),
+    ("fused_rowres_kernel", 16384, 151936): (4.980306e9 + 4.924858e9, "profiles/ncu_rowres_r1g.txt"),
     ("logits_fwd_tma_kernel", 16384, 151936): (4.979488e9 + 0.003926e9, "profiles/ncu_logits_r1.txt"),
     ("logits_bwd_tma_kernel", 16384, 151936): (4.091398e9 + 4.932738e9, "profiles/ncu_logits_r1.txt"),
 }

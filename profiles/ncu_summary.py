@@ -21,18 +21,23 @@ for r in rows[2:]:
     st = [(float(r[i]), h) for i, h in enumerate(hdr) if "issue_stalled" in h and h.endswith("per_issue_active.ratio") and "not_issued" not in h and r[i]]
     st.sort(reverse=True)
     print("top stalls (warps per issue):", ", ".join(f"{h.split('issue_stalled_')[1].split('_per')[0]}={v:.2f}" for v, h in st[:7]))
-src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "cuda"], capture_output=True, text=True).stdout
-try:
+def hottest(view):
+    src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", view], capture_output=True, text=True).stdout
     srows = list(csv.reader(io.StringIO(src)))
-    # find header row
     hi = next(i for i, r in enumerate(srows) if "Source" in r and any("Sampling" in c for c in r))
     h = srows[hi]
-    ci = h.index("Source"); si = next(i for i, c in enumerate(h) if c.startswith("# Samples") or c == "Warp Stall Sampling (All Samples)" or "Sampling (All" in c)
+    ci = h.index("Source"); si = next(i for i, c in enumerate(h) if "Sampling (All" in c)
     body = [r for r in srows[hi + 1:] if len(r) > si and r[si] not in ("", "0")]
     body.sort(key=lambda r: -float(r[si]))
     tot = sum(float(r[si]) for r in body) or 1
-    print("-" * 100); print("hottest source lines (stall samples):")
+    print("-" * 100); print(f"hottest {view} lines (share of warp-stall samples):")
     for r in body[:ntop]:
         print(f"{100 * float(r[si]) / tot:5.1f}%  {r[ci].strip()[:120]}")
-except Exception as e:
-    print("source page unavailable:", repr(e)[:200])
+
+
+for view in ("cuda", "sass"):
+    try:
+        hottest(view)
+        break
+    except Exception as e:
+        print(f"source page ({view}) unavailable:", repr(e)[:200])

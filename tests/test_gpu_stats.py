@@ -134,6 +134,34 @@ def test_grpo_loss_fn_and_export_vs_reference(ai):
     assert tr.export() == {}
 
 
+def test_grpo_loss_fn_distributed_branch_equals_fused(monkeypatch):
+    """With a vocabulary-shard (or Ulysses) group active grpo_loss_fn takes the split path -- log-probs through
+    gather_logprobs_entropy's distributed branch, then ppo_actor_loss_fn -- and must export what the fused
+    single-process path exports.  A world of one rank exercises that path on one GPU."""
+    from areal_b200 import functional as F
+    from areal_b200 import stats_tracker as ST
+    from areal_b200.actor import grpo_loss_fn
+    z = H.load("grpo_stats.npz")
+    outs, grads = [], []
+    for distributed in (False, True):
+        if distributed:
+            monkeypatch.setattr(F, "_tp_group", lambda: "one-rank world")
+        tr = ST.DistributedStatsTracker()
+        with tr.scope("ppo_actor"):
+            for mb in range(3):
+                c = load_mb(z, mb)
+                logits = c.pop("logits").requires_grad_(mb == 0)
+                loss = grpo_loss_fn(logits, c, tracker=tr, **GRPO_ARGS[1])
+                if mb == 0:
+                    loss.backward()
+                    grads.append(logits.grad.float())
+        outs.append(tr.export())
+    assert sorted(outs[0]) == sorted(outs[1])
+    for k in outs[0]:
+        assert abs(outs[0][k] - outs[1][k]) <= 2e-5 * max(1.0, abs(outs[0][k])), (k, outs[0][k], outs[1][k])
+    assert torch.allclose(grads[0], grads[1], rtol=2 ** -7, atol=1e-9)
+
+
 def test_tracker_api_matches_record():
     """denominator()/stat() one by one == record() in one launch; masks change between micro-batches."""
     from areal_b200 import stats_tracker as ST
