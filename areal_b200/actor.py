@@ -156,8 +156,14 @@ def grpo_loss_fn(logits: torch.Tensor, input_data: Dict, temperature: float, eps
                                         eps_clip, eps_clip_higher=eps_clip_higher, c_clip=c_clip,
                                         behav_imp_weight_cap=behav_imp_weight_cap, with_logits_minmax=True,
                                         loss_scale=loss_scale)
+    _record_actor_stats(tracker, stat, old_logp, loss_mask, logits.shape[0], logits.device)
+    return loss
+
+
+def _record_actor_stats(tracker, stat, old_logp, loss_mask, n_rows, device) -> None:
+    """The tracker calls of grpo_loss_fn (actor.py:349-390) as ONE record(): same keys, same denominators."""
     old_f = old_logp if old_logp.dtype == torch.float32 else old_logp.float()
-    denominators = dict(n_tokens=_all_tokens(logits.shape[0], logits.device), n_valid_tokens=loss_mask,
+    denominators = dict(n_tokens=_all_tokens(n_rows, device), n_valid_tokens=loss_mask,
                         clipped_tokens=stat["clip_mask"], dual_clipped_tokens=stat["dual_clip_mask"])
     stats = [("n_valid_tokens", dict(importance_weight=stat["importance_weight"], approx_kl=stat["approx_kl"],
                                      new_logp=stat["logprobs"], old_logp=old_f, entropy=stat["entropy"],
@@ -172,4 +178,28 @@ def grpo_loss_fn(logits: torch.Tensor, input_data: Dict, temperature: float, eps
     # the clipped entries of x: no temporaries needed
     stats.append(("clipped_tokens", dict(clipped_new_logp=stat["logprobs"], clipped_old_logp=old_f)))
     tracker.record(denominators, stats)
+
+
+def grpo_loss_fn_from_hidden(hidden: torch.Tensor, lm_head_weight: torch.Tensor, input_data: Dict, temperature: float,
+                             eps_clip: float, eps_clip_higher: float | None, c_clip: float | None,
+                             behav_imp_weight_cap: float | None, tracker=None, loss_scale=1.0,
+                             chunk_rows: int = 4096):
+    """`grpo_loss_fn` for an engine that hands over the last hidden state `[T, H]` and the LM-head weight
+    `[V, H]` instead of `[T, V]` logits (areal_b200/lm_head.py): same micro-batch keys read, same tracker
+    keys recorded, same returned loss; `(loss * loss_scale).backward()` delivers the gradients of the hidden
+    state and of the weight, which were computed block by block in the forward."""
+    from . import stats_tracker as ST
+    from .lm_head import fused_lm_head_actor_loss
+    tracker = ST.DEFAULT_TRACKER if tracker is None else tracker
+    labels = input_data.get("rolled_input_ids", None)
+    if labels is None:
+        labels = torch.roll(input_data["input_ids"], shifts=-1, dims=-1)
+    old_logp = input_data["logprobs"]
+    loss_mask = input_data.get("full_loss_mask", input_data["loss_mask"]).bool()
+    loss, stat = fused_lm_head_actor_loss(hidden, lm_head_weight, labels, temperature, input_data["prox_logp"],
+                                          old_logp, input_data["advantages"], loss_mask, eps_clip,
+                                          eps_clip_higher=eps_clip_higher, c_clip=c_clip,
+                                          behav_imp_weight_cap=behav_imp_weight_cap, with_logits_minmax=True,
+                                          loss_scale=loss_scale, chunk_rows=chunk_rows)
+    _record_actor_stats(tracker, stat, old_logp, loss_mask, hidden.shape[0], hidden.device)
     return loss

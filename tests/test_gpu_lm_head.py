@@ -144,3 +144,29 @@ def test_lm_head_logprobs_forward_only(chunk, with_entropy):
     with torch.no_grad():
         want = F.gather_logprobs(logits.to(D), labels.to(D), 0.9)
     assert torch.equal(lp, want)
+
+
+def test_grpo_loss_fn_from_hidden_exports_what_grpo_loss_fn_exports():
+    """The loss function on (hidden state, LM-head weight) records the same tracker keys and values as
+    grpo_loss_fn on the materialised logits (areal/engine/ppo/actor.py:313-391)."""
+    from areal_b200 import stats_tracker as ST
+    from areal_b200.actor import grpo_loss_fn, grpo_loss_fn_from_hidden
+    T, Hd, V = 500, 64, 8200
+    h, w, labels, logits, prox, old, adv, mask, _ = exact_inputs(T, Hd, V, 31)
+    mb = dict(input_ids=torch.roll(labels, 1).to(D), logprobs=old.to(D), prox_logp=prox.to(D),
+              advantages=adv.to(D), loss_mask=mask.to(D))
+    args = dict(temperature=0.9, eps_clip=0.4, eps_clip_higher=None, c_clip=3.0, behav_imp_weight_cap=5.0)
+    tr_a, tr_b = ST.DistributedStatsTracker(), ST.DistributedStatsTracker()
+    hh, ww = h.to(D).requires_grad_(), w.to(D).requires_grad_()
+    with tr_a.scope("ppo_actor"):
+        loss_a = grpo_loss_fn_from_hidden(hh, ww, mb, tracker=tr_a, loss_scale=0.5, chunk_rows=128, **args)
+    (loss_a * 0.5).backward()
+    x = logits.to(D).requires_grad_()
+    with tr_b.scope("ppo_actor"):
+        loss_b = grpo_loss_fn(x, mb, tracker=tr_b, **args)
+    out_a, out_b = tr_a.export(), tr_b.export()
+    assert sorted(out_a) == sorted(out_b) and len(out_a) > 20
+    for k in out_a:
+        assert abs(out_a[k] - out_b[k]) <= 2e-5 * max(1.0, abs(out_b[k])), (k, out_a[k], out_b[k])
+    assert torch.allclose(loss_a.detach(), loss_b.detach(), rtol=5e-6, atol=1e-7)
+    assert hh.grad is not None and ww.grad is not None
