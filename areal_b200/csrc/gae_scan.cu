@@ -256,16 +256,33 @@ gae1d_kernel(const Gae1dParams p) {
     }
   }
 
-  // fold the thread's maps right-to-left, parking the per-token values on the way
+  // fold the thread's maps right-to-left, parking the per-token values on the way.  The common case --
+  // all 8 tokens inside one sequence, only the last one possibly its end -- has a = gl for 7 of the 8 maps:
+  // no per-token selects or guards.
+  const bool plain = (nvalid == kItems) && ((last_bits & ((1u << (kItems - 1)) - 1u)) == 0u);
   Affine agg = ident();
+  if (plain) {
+    double b = double(delta[kItems - 1]);
 #pragma unroll
-  for (int k = kItems - 1; k >= 0; --k) {
-    if (k < nvalid) {
-      const double a = (last_bits >> k) & 1u ? 0.0 : gl;
-      agg.b = fma(a, agg.b, double(delta[k]));
-      agg.a = a * agg.a;
+    for (int k = kItems - 2; k >= 0; --k) b = fma(gl, b, double(delta[k]));
+    const double gl2 = gl * gl, gl4 = gl2 * gl2;
+    agg.a = last_bits ? 0.0 : gl4 * gl4;
+    agg.b = b;
+#pragma unroll
+    for (int k = 0; k < kItems; ++k) {
       v_sm[k][tid] = vcur[k];
       d_sm[k][tid] = delta[k];
+    }
+  } else {
+#pragma unroll
+    for (int k = kItems - 1; k >= 0; --k) {
+      if (k < nvalid) {
+        const double a = (last_bits >> k) & 1u ? 0.0 : gl;
+        agg.b = fma(a, agg.b, double(delta[k]));
+        agg.a = a * agg.a;
+        v_sm[k][tid] = vcur[k];
+        d_sm[k][tid] = delta[k];
+      }
     }
   }
 
@@ -327,13 +344,25 @@ gae1d_kernel(const Gae1dParams p) {
   if (nvalid > 0) {
     double A = fma(excl.a, carry, excl.b);   // value entering this thread from the right
     float adv[kItems], ret[kItems];
+    if (plain) {
+      A = fma(last_bits ? 0.0 : gl, A, double(d_sm[kItems - 1][tid]));
+      adv[kItems - 1] = float(A);
+      ret[kItems - 1] = __fadd_rn(adv[kItems - 1], v_sm[kItems - 1][tid]);
 #pragma unroll
-    for (int k = kItems - 1; k >= 0; --k) {
-      if (k < nvalid) {
-        const double a = (last_bits >> k) & 1u ? 0.0 : gl;
-        A = fma(a, A, double(d_sm[k][tid]));
+      for (int k = kItems - 2; k >= 0; --k) {
+        A = fma(gl, A, double(d_sm[k][tid]));
         adv[k] = float(A);
-        ret[k] = __fadd_rn(adv[k], v_sm[k][tid]);               // ppo_functional.py:319
+        ret[k] = __fadd_rn(adv[k], v_sm[k][tid]);                 // ppo_functional.py:319
+      }
+    } else {
+#pragma unroll
+      for (int k = kItems - 1; k >= 0; --k) {
+        if (k < nvalid) {
+          const double a = (last_bits >> k) & 1u ? 0.0 : gl;
+          A = fma(a, A, double(d_sm[k][tid]));
+          adv[k] = float(A);
+          ret[k] = __fadd_rn(adv[k], v_sm[k][tid]);               // ppo_functional.py:319
+        }
       }
     }
     float* ao = p.adv + tile_start + p0;
