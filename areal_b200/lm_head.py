@@ -102,7 +102,9 @@ class _LMHeadActor(torch.autograd.Function):
 
         need_dh, need_dw = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
         d_h = torch.empty_like(h) if need_dh else None
-        d_w = torch.empty((V, H), dtype=wgrad_dtype, device=dev) if need_dw else None
+        d_w = None
+        if need_dw:     # written by the first block's GEMM; an empty batch has no block
+            d_w = (torch.empty if n_blk else torch.zeros)((V, H), dtype=wgrad_dtype, device=dev)
         logits = torch.empty((R, V), dtype=torch.bfloat16, device=dev)
         dlogits = torch.empty((R, V), dtype=torch.bfloat16, device=dev)
         w_t = w.t()

@@ -170,3 +170,15 @@ def test_grpo_loss_fn_from_hidden_exports_what_grpo_loss_fn_exports():
         assert abs(out_a[k] - out_b[k]) <= 2e-5 * max(1.0, abs(out_b[k])), (k, out_a[k], out_b[k])
     assert torch.allclose(loss_a.detach(), loss_b.detach(), rtol=5e-6, atol=1e-7)
     assert hh.grad is not None and ww.grad is not None
+
+
+def test_lm_head_empty_batch():
+    from areal_b200.lm_head import fused_lm_head_actor_loss
+    h = torch.zeros(0, 64, dtype=torch.bfloat16, device=D, requires_grad=True)
+    w = torch.ones(4104, 64, dtype=torch.bfloat16, device=D, requires_grad=True)
+    e = torch.zeros(0, device=D)
+    loss, st = fused_lm_head_actor_loss(h, w, torch.zeros(0, dtype=torch.long, device=D), 1.0, e, e, e,
+                                        torch.zeros(0, dtype=torch.bool, device=D), loss_scale=1.0, **CFG)
+    loss.backward()
+    assert float(loss) == 0.0 and st["logprobs"].shape == (0,)
+    assert h.grad.shape == (0, 64) and not torch.any(w.grad != 0)
