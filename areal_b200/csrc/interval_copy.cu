@@ -15,6 +15,8 @@
 // piece is moved with the widest vector the relative alignment of source and destination allows
 // (16/8/4/2/1 B), 8 independent 128-bit loads in flight per lane, streaming cache hints; heads and
 // tails are byte-granular, so any element size and any alignment is bit-exact.
+#include <cstdlib>
+
 #include "common.cuh"
 #include "interval_copy.h"
 
@@ -27,86 +29,134 @@ constexpr int kCopyWarps = kCopyThreads / 32;
 
 constexpr int64_t kShiftMinBytes = 256;   // shorter misaligned pieces keep the narrow-vector path
 
-// workspace: int64 status[2] | int64 off[N + 1] (byte offsets into the packed buffer) | int64 any_shift
+// workspace (int64 words): status[2] | off[N + 1] (byte offsets into the packed buffer) | any_shift |
+//                          scan scratch: ticket, flags, total, pad | one look-back word per scan tile
 // any_shift != 0: some interval of >= 256 bytes has flat and packed addresses that disagree modulo 16,
 // i.e. the second (funnel-shift) copy kernel has work to do.
+//
+// The scan runs on ceil(N / 4096) CTAs chained by a decoupled look-back (one self-describing 8-byte word
+// per tile: 2 flag bits + 62 value bits, so publishing needs no fence): a table of 200 k intervals takes a
+// few microseconds instead of the ~200 us of a single CTA walking it in 49 dependent steps -- which was a
+// fifth of the whole copy for the 7B tensor-parallel re-shard (many row-sized pieces).
+constexpr int kScanPer = 4;
+constexpr int kScanTile = kScanThreads * kScanPer;          // 4096 intervals per CTA
+constexpr int kScratchWords = 4;                            // ticket, flags, total, pad
+constexpr unsigned long long kFlagAgg = 1ull << 62, kFlagInc = 2ull << 62, kValMask = (1ull << 62) - 1;
+
+__device__ __forceinline__ unsigned long long ld_relaxed(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_relaxed(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
 __global__ void __launch_bounds__(kScanThreads)
 interval_scan_kernel(const int64_t* __restrict__ iv, int64_t n, int64_t elem_size,
                      int64_t flat_numel, int64_t packed_numel, int64_t* __restrict__ ws,
                      uint64_t flat_base, uint64_t packed_base) {
   __shared__ int64_t warp_sums[32];
-  __shared__ int64_t base_sm;
-  __shared__ int bad_sm;
-  __shared__ int shift_sm;
+  __shared__ int64_t excl_sm;
+  __shared__ int flags_sm;                  // bit 0: invalid interval, bit 1: a long misaligned piece
   int64_t* status = ws;
   int64_t* off = ws + 2;
+  unsigned long long* scratch = reinterpret_cast<unsigned long long*>(ws + n + 4);
+  unsigned long long* desc = scratch + kScratchWords;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  if (tid == 0) {
-    base_sm = 0;
-    bad_sm = 0;
-    shift_sm = 0;
-  }
+  const int64_t tile = blockIdx.x, ntiles = gridDim.x;
+  if (tid == 0) flags_sm = 0;
   __syncthreads();
-  constexpr int kPer = 4;
-  for (int64_t start = 0; start < n; start += int64_t(kScanThreads) * kPer) {
-    int64_t sz[kPer], st0[kPer];
-    int64_t local = 0;
-    bool bad = false;
+
+  int64_t sz[kScanPer], st0[kScanPer];
+  int64_t local = 0;
+  bool bad = false;
 #pragma unroll
-    for (int k = 0; k < kPer; ++k) {
-      const int64_t i = start + int64_t(tid) * kPer + k;
-      sz[k] = 0;
-      st0[k] = 0;
-      if (i < n) {
-        const longlong2 se = reinterpret_cast<const longlong2*>(iv)[i];
-        if (se.x < 0 || se.y < se.x || se.y > flat_numel) bad = true;
-        else sz[k] = (se.y - se.x) * elem_size;
-        st0[k] = se.x * elem_size;
-      }
-      local += sz[k];
+  for (int k = 0; k < kScanPer; ++k) {
+    const int64_t i = tile * kScanTile + int64_t(tid) * kScanPer + k;
+    sz[k] = 0;
+    st0[k] = 0;
+    if (i < n) {
+      const longlong2 se = reinterpret_cast<const longlong2*>(iv)[i];
+      if (se.x < 0 || se.y < se.x || se.y > flat_numel) bad = true;
+      else sz[k] = (se.y - se.x) * elem_size;
+      st0[k] = se.x * elem_size;
     }
-    if (bad) bad_sm = 1;
-    // block exclusive scan of `local`
-    int64_t inc = local;
+    local += sz[k];
+  }
+  if (bad) atomicOr(&flags_sm, 1);
+  // block exclusive scan of `local`
+  int64_t inc = local;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const int64_t o = __shfl_up_sync(0xffffffffu, inc, d);
+    if (lane >= d) inc += o;
+  }
+  if (lane == 31) warp_sums[warp] = inc;
+  __syncthreads();
+  if (warp == 0) {
+    int64_t w = warp_sums[lane];
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
-      const int64_t o = __shfl_up_sync(0xffffffffu, inc, d);
-      if (lane >= d) inc += o;
+      const int64_t o = __shfl_up_sync(0xffffffffu, w, d);
+      if (lane >= d) w += o;
     }
-    if (lane == 31) warp_sums[warp] = inc;
-    __syncthreads();
-    if (warp == 0) {
-      int64_t w = warp_sums[lane];
-#pragma unroll
-      for (int d = 1; d < 32; d <<= 1) {
-        const int64_t o = __shfl_up_sync(0xffffffffu, w, d);
-        if (lane >= d) w += o;
+    warp_sums[lane] = w;   // inclusive over warps
+    // ---- decoupled look-back by warp 0: lane j inspects tile (look - j) --------------------------------
+    const unsigned long long agg = static_cast<unsigned long long>(__shfl_sync(0xffffffffu, w, 31)) & kValMask;
+    if (lane == 0 && tile > 0) st_relaxed(&desc[tile], kFlagAgg | agg);
+    int64_t excl = 0;
+    for (int64_t look = tile - 1; look >= 0; look -= 32) {
+      const int64_t idx = look - lane;
+      unsigned long long word = kFlagInc;                    // before tile 0: inclusive prefix 0
+      if (idx >= 0) {
+        do {
+          word = ld_relaxed(&desc[idx]);
+        } while ((word >> 62) == 0);
       }
-      warp_sums[lane] = w;   // inclusive over warps
-    }
-    __syncthreads();
-    const int64_t base = base_sm;
-    int64_t run = base + (warp ? warp_sums[warp - 1] : 0) + (inc - local);
+      const unsigned int inc_mask = __ballot_sync(0xffffffffu, (word >> 62) == 2);
+      const int first = inc_mask ? __ffs(inc_mask) - 1 : 31;   // nearest tile with a finished prefix
+      int64_t v = lane <= first ? static_cast<int64_t>(word & kValMask) : 0;
 #pragma unroll
-    for (int k = 0; k < kPer; ++k) {
-      const int64_t i = start + int64_t(tid) * kPer + k;
-      if (i < n) off[i] = run;
-      if (sz[k] >= kShiftMinBytes && (((flat_base + uint64_t(st0[k])) - (packed_base + uint64_t(run))) & 15u) != 0)
-        shift_sm = 1;
-      run += sz[k];
+      for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+      excl += v;
+      if (inc_mask) break;
     }
-    __syncthreads();
-    if (tid == 0) base_sm = base + warp_sums[31];
-    __syncthreads();
+    if (lane == 0) {
+      st_relaxed(&desc[tile], kFlagInc | ((static_cast<unsigned long long>(excl) + agg) & kValMask));
+      excl_sm = excl;
+    }
   }
+  __syncthreads();
+  int64_t run = excl_sm + (warp ? warp_sums[warp - 1] : 0) + (inc - local);
+  bool shift = false;
+#pragma unroll
+  for (int k = 0; k < kScanPer; ++k) {
+    const int64_t i = tile * kScanTile + int64_t(tid) * kScanPer + k;
+    if (i < n) off[i] = run;
+    if (sz[k] >= kShiftMinBytes && (((flat_base + uint64_t(st0[k])) - (packed_base + uint64_t(run))) & 15u) != 0)
+      shift = true;
+    run += sz[k];
+  }
+  if (shift) atomicOr(&flags_sm, 2);
+  __syncthreads();
   if (tid == 0) {
-    off[n] = base_sm;
-    int64_t st = 0;
-    if (bad_sm) st = 1;
-    else if (base_sm != packed_numel * elem_size) st = 2;
-    status[0] = st;
-    status[1] = base_sm;
-    off[n + 1] = shift_sm;
+    if (flags_sm) atomicOr(&scratch[1], static_cast<unsigned long long>(flags_sm));
+    if (tile == ntiles - 1) st_relaxed(&scratch[2], static_cast<unsigned long long>(excl_sm + warp_sums[31]));
+    __threadfence();
+    const unsigned long long t = atomicAdd(&scratch[0], 1ull);
+    if (t == static_cast<unsigned long long>(ntiles) - 1) {       // last CTA: everything is published
+      __threadfence();
+      const int64_t total = static_cast<int64_t>(ld_relaxed(&scratch[2]));
+      const unsigned long long fl = ld_relaxed(&scratch[1]);
+      off[n] = total;
+      int64_t st = 0;
+      if (fl & 1) st = 1;
+      else if (total != packed_numel * elem_size) st = 2;
+      status[0] = st;
+      status[1] = total;
+      off[n + 1] = (fl & 2) ? 1 : 0;
+    }
   }
 }
 
@@ -285,7 +335,10 @@ interval_copy_kernel(const char* __restrict__ flat_in, char* __restrict__ flat_o
 
 }  // namespace
 
-int64_t interval_workspace_bytes(int64_t n) { return (n + 4) * int64_t(sizeof(int64_t)); }
+int64_t interval_workspace_bytes(int64_t n) {
+  const int64_t ntiles = n > 0 ? (n + kScanTile - 1) / kScanTile : 1;
+  return (n + 4 + kScratchWords + ntiles) * int64_t(sizeof(int64_t));
+}
 
 int launch_interval_copy(bool slice, const void* flat_in, void* flat_out, const void* packed_in,
                          void* packed_out, const int64_t* intervals, int64_t n, int64_t elem_size,
@@ -294,14 +347,24 @@ int launch_interval_copy(bool slice, const void* flat_in, void* flat_out, const 
   int64_t* ws = reinterpret_cast<int64_t*>(workspace);
   const uint64_t flat_base = reinterpret_cast<uint64_t>(slice ? flat_in : flat_out);
   const uint64_t packed_base = reinterpret_cast<uint64_t>(slice ? packed_out : packed_in);
-  interval_scan_kernel<<<1, kScanThreads, 0, stream>>>(intervals, n, elem_size, flat_numel, packed_numel, ws,
-                                                       flat_base, packed_base);
+  const int64_t ntiles = n > 0 ? (n + kScanTile - 1) / kScanTile : 1;
+  // ticket, flags, total and the look-back words start at zero ("empty")
+  AB_CUDA(cudaMemsetAsync(ws + n + 4, 0, size_t(kScratchWords + ntiles) * sizeof(int64_t), stream));
+  interval_scan_kernel<<<static_cast<unsigned int>(ntiles), kScanThreads, 0, stream>>>(
+      intervals, n, elem_size, flat_numel, packed_numel, ws, flat_base, packed_base);
   int rc = check_launch("interval_scan");
   if (rc) return rc;
   const int64_t total = packed_numel * elem_size;
   if (total == 0 || n == 0) return kOk;
   // equal contiguous chunks of packed bytes, one per warp; >= 4 KB each, 16 B granular
-  const int64_t target_warps = int64_t(num_sms()) * 8 * kCopyWarps;
+  // AREAL_B200_INTERVAL_CHUNKS_PER_SM (benchmarks): how many chunks of kCopyWarps warps the packed bytes are cut
+  // into per SM; the default 8 gives four full waves of 2 resident CTAs
+  static const int chunks_per_sm = [] {
+    const char* e = getenv("AREAL_B200_INTERVAL_CHUNKS_PER_SM");
+    const int v = e ? atoi(e) : 0;
+    return v > 0 ? v : 8;
+  }();
+  const int64_t target_warps = int64_t(num_sms()) * chunks_per_sm * kCopyWarps;
   int64_t chunk = (total + target_warps - 1) / target_warps;
   if (chunk < 4096) chunk = 4096;
   chunk = (chunk + 15) & ~int64_t(15);

@@ -313,7 +313,8 @@ AREAL_B200_API int areal_b200_masked_normalization_apply(const float* x, const f
  * P4  interval ops (parameter reallocation)
  * ------------------------------------------------------------------------------------------ */
 
-/* (n_intervals + 3) * 8 bytes; need not be zeroed.  After the call, workspace[0] (int64) holds 0
+/* Scratch for the packed offsets and their scan: (n_intervals + 8 + ceil(n_intervals / 4096)) * 8 bytes; need not be
+ * zeroed.  After the call, workspace[0] (int64) holds 0
  * (ok), 1 (an interval is negative / reversed / beyond the flat buffer) or 2 (sum of sizes !=
  * packed_numel); on a non-zero status no byte of the destination is written. */
 AREAL_B200_API int64_t areal_b200_interval_workspace_bytes(int64_t n_intervals);

@@ -39,7 +39,8 @@ def test_host_only_entry_points(lib):
     assert lib.areal_b200_version() >= 100
     assert lib.areal_b200_gae1d_workspace_bytes(100) == 64
     assert lib.areal_b200_gae1d_workspace_bytes(2049) == 64 + 5 * 32      # sized for the smallest (512-token) tile
-    assert lib.areal_b200_interval_workspace_bytes(10) == 14 * 8    # status[2] | off[n+1] | any_shift
+    assert lib.areal_b200_interval_workspace_bytes(10) == (14 + 4 + 1) * 8    # status[2] | off[n+1] | any_shift | scan scratch[4] | one word per 4096 intervals
+    assert lib.areal_b200_interval_workspace_bytes(200704) == (200704 + 4 + 4 + 49) * 8
     assert lib.areal_b200_loss_workspace_bytes() >= 16 + 8 * 8
 
 
