@@ -97,6 +97,15 @@ def bench_gae(out, ref):
         small = (16 * T) < (200 << 20)
         ms = timeit(lambda: P.gae_1d_nolp_misalign(r, v, cu, boot, 1.0, 0.95), flush=small)
         out.append(row("gae1d", ms, 16 * T + 9 * B + 4, T=T, B=B, tokens_per_s=T / (ms * 1e-3), l2_flushed=small))
+        if not small:
+            # device time per call: four calls enqueued back to back, so the ~13 us the Python wrapper spends
+            # before its first launch (the GPU is idle when a lone call starts) overlaps the previous call
+            def four():
+                for _ in range(4):
+                    P.gae_1d_nolp_misalign(r, v, cu, boot, 1.0, 0.95)
+            ms4 = timeit(four) / 4
+            out.append(row("gae1d (4 calls back to back, per call)", ms4, 16 * T + 9 * B + 4, T=T, B=B,
+                           tokens_per_s=T / (ms4 * 1e-3), l2_flushed=False))
         if ref is not None and logT <= 24:
             msr = timeit(lambda: ref.gae_1d_nolp_misalign(r, v, cu, boot, 1.0, 0.95), iters=5, warmup=2, flush=small)
             out.append(row("reference gae_1d_nolp_misalign (sm_100a rebuild)", msr, 16 * T + 9 * B + 4, T=T, B=B,
