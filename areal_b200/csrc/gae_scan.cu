@@ -762,6 +762,44 @@ int64_t gae1d_workspace_bytes(int64_t T) {
   return int64_t(sizeof(WorkspaceHeader)) + (ntiles > 1 ? ntiles : 0) * int64_t(sizeof(TileDesc));
 }
 
+// The same table written from the sequences' side: one WARP per sequence stores the descriptors of the tiles
+// whose first token lies inside it (none for an empty sequence) -- two loads of `cu` and a few coalesced
+// stores instead of a 16-step dependent binary search per tile.  Used unless sequences are so long that a
+// warp would loop over more than a few hundred tiles (then the per-tile search above is the cheaper one).
+__global__ void gae1d_prep_by_sequence_kernel(const int32_t* __restrict__ cu, int B, int64_t ntiles,
+                                              TileDesc* __restrict__ desc, int tile_tokens) {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  const int64_t seq = (blockIdx.x * int64_t(blockDim.x) + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (seq >= B) return;
+  const int64_t s = __ldg(cu + seq), e = __ldg(cu + seq + 1);
+  int64_t t0 = (s + tile_tokens - 1) / tile_tokens;           // first tile that starts at or after s
+  int64_t t1 = (e + tile_tokens - 1) / tile_tokens;           // first tile that starts at or after e
+  // every descriptor gets initialised even if the caller's table does not start at 0 / end at T
+  if (seq == 0) t0 = 0;
+  if (seq == B - 1 || t1 > ntiles) t1 = ntiles;
+  TileDesc d;
+  d.inc = kEmpty;
+  d.agg_a = kEmpty;
+  d.agg_b = kEmpty;
+  d.seq0 = static_cast<int>(seq);
+  d.end0 = static_cast<int>(e);
+  for (int64_t t = t0 + lane; t < t1; t += 32) desc[t] = d;
+}
+
+static void launch_gae1d_prep(const Gae1dParams& p, int64_t ntiles, TileDesc* desc, int tile_tokens, cudaStream_t stream) {
+  // measured (A/B on one box): 4 M tokens 31.7 -> 27.7 us, 16 M tokens 80.0 -> 76.7 us per call; from 128 M tokens on
+  // the B warps cost more to launch than the per-tile search saves (66.3 -> 65.8 %), hence the tile limit
+  if (ntiles <= 65536 && ntiles <= 256 * p.B) {       // on average at most 8 rounds of 32 tiles per warp
+    const int64_t threads = p.B * 32;
+    gae1d_prep_by_sequence_kernel<<<static_cast<unsigned int>((threads + 255) / 256), 256, 0, stream>>>(
+        p.cu, static_cast<int>(p.B), ntiles, desc, tile_tokens);
+  } else {
+    gae1d_prep_kernel<<<static_cast<unsigned int>((ntiles + 255) / 256), 256, 0, stream>>>(
+        p.cu, static_cast<int>(p.B), p.T, ntiles, desc, tile_tokens);
+  }
+}
+
 constexpr int64_t kWideFromTokens = 1 << 20;   // batches of at least this many tokens use 512-thread CTAs
 
 int launch_gae1d(const Gae1dParams& p, cudaStream_t stream) {
@@ -773,8 +811,7 @@ int launch_gae1d(const Gae1dParams& p, cudaStream_t stream) {
   if (ntiles > 1) {
     // descriptors start "empty" and carry each tile's first sequence: one tiny kernel, stream-ordered
     TileDesc* desc = reinterpret_cast<TileDesc*>(reinterpret_cast<char*>(p.workspace) + sizeof(WorkspaceHeader));
-    gae1d_prep_kernel<<<static_cast<unsigned int>((ntiles + 255) / 256), 256, 0, stream>>>(
-        p.cu, static_cast<int>(p.B), p.T, ntiles, desc, tile_tokens);
+    launch_gae1d_prep(p, ntiles, desc, tile_tokens, stream);
   }
   if (ntiles > 1) {
     // launched as a programmatic dependent of the prep kernel: its launch latency and the reward
@@ -837,8 +874,7 @@ int launch_gae1d_static(Gae1dParams p, cudaStream_t stream) {
   const int64_t ntiles = (p.T + kTile - 1) / kTile;
   if (ntiles > 1) {
     TileDesc* desc = reinterpret_cast<TileDesc*>(reinterpret_cast<char*>(scratch) + sizeof(WorkspaceHeader));
-    gae1d_prep_kernel<<<static_cast<unsigned int>((ntiles + 255) / 256), 256, 0, stream>>>(
-        p.cu, static_cast<int>(p.B), p.T, ntiles, desc, kTile);
+    launch_gae1d_prep(p, ntiles, desc, kTile, stream);
   }
   p.workspace = scratch;
   gae1d_kernel<256><<<static_cast<unsigned int>(ntiles), kThreads, 0, stream>>>(p);
