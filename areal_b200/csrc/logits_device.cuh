@@ -99,6 +99,31 @@ __device__ __forceinline__ void state_merge(float& m, float& s, float& w, float 
   m = M;
 }
 
+// Merge the 32 canonical states of a warp: the row max first (shuffles only), then every lane rebases its
+// (s, w) to it ONCE -- one ex2 per lane instead of two per butterfly round -- and s, w, mn are plain
+// butterfly sums / minima.  All lanes end with the warp's state.
+__device__ __forceinline__ void warp_merge_state(RowState& st, float c2) {
+  float M = st.m;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) M = fmaxf(M, __shfl_xor_sync(0xffffffffu, M, o));
+  const bool empty = st.m == -INFINITY;
+  const float d = empty ? 0.f : (st.m - M) * c2;
+  const float f = empty ? 0.f : ex2_approx(d);
+  float s = st.s * f;
+  float w = f * fmaf(d, st.s, st.w);
+  float mn = st.mn;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    s += __shfl_xor_sync(0xffffffffu, s, o);
+    w += __shfl_xor_sync(0xffffffffu, w, o);
+    mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+  }
+  st.m = M;
+  st.s = s;
+  st.w = w;
+  st.mn = mn;
+}
+
 struct RowGrad {
   float k0, k1, gl, m, nl2s;   // nl2s = -log2 S
   bool active;

@@ -91,15 +91,7 @@ struct RowReduceSmem {
 __device__ __forceinline__ bool row_reduce(RowState& st, RowReduceSmem* red, int parity, int warp,
                                            int lane, float c2) {
   state_canonical(st, c2);
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-    const float m2 = __shfl_xor_sync(0xffffffffu, st.m, o);
-    const float s2 = __shfl_xor_sync(0xffffffffu, st.s, o);
-    const float w2 = __shfl_xor_sync(0xffffffffu, st.w, o);
-    const float n2 = __shfl_xor_sync(0xffffffffu, st.mn, o);
-    state_merge(st.m, st.s, st.w, m2, s2, w2, c2);
-    st.mn = fminf(st.mn, n2);
-  }
+  warp_merge_state(st, c2);
   if (lane == 0) {
     red->m[parity][warp] = st.m;
     red->s[parity][warp] = st.s;
@@ -140,15 +132,7 @@ __device__ __forceinline__ bool row_reduce_rot(RowState& st, RowReduceRot<kCW>* 
                                                float c2) {
   constexpr int kConsumerWarps = kCW, kConsumers = kCW * 32;
   state_canonical(st, c2);
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-    const float m2 = __shfl_xor_sync(0xffffffffu, st.m, o);
-    const float s2 = __shfl_xor_sync(0xffffffffu, st.s, o);
-    const float w2 = __shfl_xor_sync(0xffffffffu, st.w, o);
-    const float n2 = __shfl_xor_sync(0xffffffffu, st.mn, o);
-    state_merge(st.m, st.s, st.w, m2, s2, w2, c2);
-    st.mn = fminf(st.mn, n2);
-  }
+  warp_merge_state(st, c2);
   const int slot = static_cast<int>(it % kRedSlots);
   if (lane == 0) {
     red->m[slot][warp] = st.m;

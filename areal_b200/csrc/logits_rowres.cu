@@ -223,15 +223,7 @@ fused_rowres_kernel(const LogitsFwdParams p, void* __restrict__ dlogits, int64_t
         if (v < my_nvec) stats_step<1>(st, sbase, v, c2);
       }
       state_canonical(st, c2);
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-        const float m2 = __shfl_xor_sync(0xffffffffu, st.m, o);
-        const float s2 = __shfl_xor_sync(0xffffffffu, st.s, o);
-        const float w2 = __shfl_xor_sync(0xffffffffu, st.w, o);
-        const float n2 = __shfl_xor_sync(0xffffffffu, st.mn, o);
-        state_merge(st.m, st.s, st.w, m2, s2, w2, c2);
-        st.mn = fminf(st.mn, n2);
-      }
+      warp_merge_state(st, c2);
       if (lane == 0) {
         sh.m[b][warp] = st.m;
         sh.s[b][warp] = st.s;
