@@ -147,3 +147,39 @@ def test_every_byte_shift_long_pieces():
     ref = src.copy()
     C.set_intervals(new, ref, iv)
     assert np.array_equal(dst.cpu().numpy(), ref)
+
+
+def test_many_intervals_span_several_look_back_rounds():
+    """300,000 intervals = 74 scan tiles: the offset scan's warp-wide look-back needs three rounds for the last
+    tiles.  Ragged sizes incl. empty intervals and odd offsets, shuffled order; bit-exact vs numpy, round trip
+    through set_intervals, and an invalid interval in a late tile still stops every write."""
+    from areal_b200 import flatten_param as fp
+    rng = np.random.RandomState(11)
+    n = 300_000
+    sizes = rng.randint(0, 90, n).astype(np.int64)
+    sizes[rng.rand(n) < 0.05] = 0
+    gaps = rng.randint(0, 7, n).astype(np.int64)
+    starts = np.cumsum(sizes + gaps) - sizes
+    numel = int(starts[-1] + sizes[-1] + 5)
+    iv = np.stack([starts, starts + sizes], 1)
+    rng.shuffle(iv)
+    total = int(sizes.sum())
+    src_np = rng.randint(0, 65536, numel).astype(np.uint16)
+    src = torch.from_numpy(src_np.view(np.int16)).view(torch.bfloat16).to(D)
+    ivc = torch.from_numpy(iv).to(D)
+    out, st = fp.slice_intervals_any(src, ivc, total, return_status=True)
+    assert int(st[0]) == 0
+    want = np.concatenate([src_np[a:b] for a, b in iv])
+    assert np.array_equal(H.torch_bits(out), want)
+    dst = torch.zeros_like(src)
+    fp.set_intervals_any(out, dst, ivc)
+    covered = np.zeros(numel, bool)
+    for a, b in iv:
+        covered[a:b] = True
+    assert np.array_equal(H.torch_bits(dst), np.where(covered, src_np, 0))
+    bad = iv.copy()
+    bad[n - 1000] = (numel - 3, numel + 40)          # beyond the flat buffer, in tile 73
+    sentinel = torch.full((total,), 7.0, dtype=torch.bfloat16, device=D)
+    st = fp.set_intervals_any(sentinel, dst, torch.from_numpy(bad).to(D), return_status=True)
+    assert int(st[0]) == 1
+    assert np.array_equal(H.torch_bits(dst), np.where(covered, src_np, 0))
