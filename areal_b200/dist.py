@@ -233,3 +233,70 @@ def vocab_parallel_logprobs_entropy(shard_logits: torch.Tensor, labels: torch.Te
         rank = dist.get_rank(group) if dist.is_initialized() else 0
         vocab_start = rank * shard_logits.shape[-1]
     return _VocabParallelLogprobsEntropy.apply(shard_logits, labels, vocab_start, temperature, group, exchange)
+
+
+# --------------------------------------------------------------------------------------------------
+# parameter reallocation: slice straight into a peer's staging buffer over NVLink
+# --------------------------------------------------------------------------------------------------
+class PeerPackedBuffer:
+    """Packed staging buffers that every rank of `group` has mapped (torch symmetric memory does the
+    rendezvous -- plumbing).  The reference moves re-sharded parameters as slice_intervals -> broadcast of
+    the packed buffer -> set_intervals (realhf/impl/model/nn/real_llm_api.py:745-805).  Here the sender's
+    `slice_intervals` kernel writes its pieces directly into the RECEIVER's buffer with plain streaming
+    stores over NVLink (`slice_into`), so there is no sender-side staging buffer and no collective; the
+    receiver then runs `set_from_local` on its own copy.  `fence()` is the host-level hand-off between
+    the two (the sender's stream is drained, then the group meets at a barrier).
+
+    `numel` elements of `dtype` per rank.  One instance per group; every rank constructs it together."""
+
+    def __init__(self, numel: int, dtype: torch.dtype, group=None, device=None):
+        import torch.distributed._symmetric_memory as symm
+        if not dist.is_initialized():
+            raise RuntimeError("PeerPackedBuffer needs an initialised process group")
+        self.group = dist.group.WORLD if group is None else group
+        self.rank, self.world = dist.get_rank(self.group), dist.get_world_size(self.group)
+        dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self.device, self.numel, self.dtype = dev, int(numel), dtype
+        try:
+            symm.enable_symm_mem_for_group(self.group.group_name)
+        except Exception:
+            pass                              # newer torch enables groups on demand
+        self.buf = symm.empty(max(self.numel, 1), dtype=dtype, device=dev)
+        self.handle = symm.rendezvous(self.buf, self.group)
+        self._ptrs = [int(p) for p in self.handle.buffer_ptrs]
+        torch.cuda.synchronize(dev)
+        dist.barrier(self.group)
+
+    def local(self, numel: Optional[int] = None) -> torch.Tensor:
+        """This rank's staging buffer (what the peers write into)."""
+        return self.buf[: self.numel if numel is None else int(numel)]
+
+    def slice_into(self, peer: int, src: torch.Tensor, intervals_cuda: torch.Tensor, total_size: int,
+                   offset: int = 0) -> None:
+        """`slice_intervals(src, intervals, total_size)` with the packed result written at element
+        `offset` of rank `peer`'s staging buffer (this rank's own buffer when peer == rank)."""
+        from .flatten_param import _check, _intervals_cuda
+        _check(src.is_cuda and src.is_contiguous() and src.dim() == 1, "src must be a contiguous 1-D CUDA tensor")
+        _check(src.dtype == self.dtype, "Source and destination tensors must have the same dtype")
+        _check(0 <= peer < self.world, "peer rank out of range")
+        total_size, offset = int(total_size), int(offset)
+        _check(offset >= 0 and offset + total_size <= self.numel, "packed range exceeds the staging buffer")
+        iv = _intervals_cuda(None, intervals_cuda, src.device)
+        n = iv.size(0)
+        dst = ctypes.c_void_p(self._ptrs[peer] + offset * src.element_size())
+        with torch.cuda.device(self.device):
+            nbytes = _lib.lib().areal_b200_interval_workspace_bytes(n)
+            ws = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
+            call("areal_b200_slice_intervals", ptr(src), src.numel(), dst, total_size, ptr(iv), n,
+                 src.element_size(), ptr(ws), nbytes, stream_ptr(self.device))
+
+    def set_from_local(self, dst: torch.Tensor, intervals_cuda: torch.Tensor, total_size: int, offset: int = 0) -> None:
+        """`set_intervals(local staging[offset : offset + total_size], dst, intervals)` on this rank."""
+        from .flatten_param import set_intervals_any
+        set_intervals_any(self.buf[int(offset): int(offset) + int(total_size)], dst, intervals_cuda)
+
+    def fence(self) -> None:
+        """Everything `slice_into` enqueued so far on this rank's current stream has landed in the peers'
+        buffers, and every rank has got here: the receivers may read, the senders may overwrite."""
+        torch.cuda.current_stream(self.device).synchronize()
+        dist.barrier(self.group)

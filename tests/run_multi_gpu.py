@@ -113,6 +113,58 @@ def main():
         if rank == 0:
             print("P2P_OK", world, {k: round(v, 1) for k, v in res.items()}, "us per call")
 
+    # ---------------- parameter reallocation: slice straight into the neighbour's staging buffer -----------
+    from areal_b200 import flatten_param as FP
+    try:
+        pb = D.PeerPackedBuffer(numel=200_000, dtype=torch.bfloat16)
+    except Exception as exc:                                  # no peer mapping on this box: reported, not fatal
+        pb = None
+        if rank == 0:
+            print("PEERBUF_UNAVAILABLE", repr(exc)[:300])
+    if pb is not None:
+        gsrc = torch.Generator(device=dev).manual_seed(55)    # same stream on every rank: row r = rank r's parameters
+        flat_all = torch.randn(world, 400_000, generator=gsrc, device=dev).bfloat16()
+        rs = np.random.RandomState(9)
+        sizes = rs.randint(1, 300, 900)
+        starts = np.cumsum(sizes + rs.randint(0, 100, 900)) - sizes
+        iv_np = np.stack([starts, starts + sizes], 1).astype(np.int64)
+        rs.shuffle(iv_np)
+        total = int(sizes.sum())
+        ivc = torch.from_numpy(iv_np).to(dev)
+        nxt, prv = (rank + 1) % world, (rank - 1) % world
+        for offset in (16, 3):                                # 16-byte aligned, then a 6-byte shift (funnel path)
+            pb.slice_into(nxt, flat_all[rank].contiguous(), ivc, total, offset=offset)
+            pb.fence()
+            want = FP.slice_intervals_any(flat_all[prv].contiguous(), ivc, total)   # what my left neighbour sent
+            got = pb.local()[offset: offset + total]
+            assert torch.equal(got.view(torch.int16), want.view(torch.int16)), offset
+            mine, ref = torch.zeros(400_000, dtype=torch.bfloat16, device=dev), torch.zeros(400_000, dtype=torch.bfloat16, device=dev)
+            pb.set_from_local(mine, ivc, total, offset=offset)
+            FP.set_intervals_any(want, ref, ivc)
+            assert torch.equal(mine.view(torch.int16), ref.view(torch.int16))
+            pb.fence()                                        # receivers are done before the next round overwrites
+        # device time of a 256 MB re-shard write into the neighbour (128 Mi bf16 in 4,096 pieces), against the same
+        # slice into local memory
+        big = D.PeerPackedBuffer(numel=1 << 27, dtype=torch.bfloat16)
+        flat_big = torch.empty(1 << 28, dtype=torch.bfloat16, device=dev)
+        flat_big.view(torch.int16).random_(-30000, 30000)
+        piece = (1 << 28) // 4096
+        iv_big = torch.stack([torch.arange(4096, device=dev) * piece, torch.arange(4096, device=dev) * piece + piece // 2], 1)
+        res = {}
+        for name, target in (("into the neighbour over NVLink", nxt), ("into local memory", rank)):
+            for _ in range(3):
+                big.slice_into(target, flat_big, iv_big, 1 << 27)
+            big.fence()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(10):
+                big.slice_into(target, flat_big, iv_big, 1 << 27)
+            e1.record()
+            big.fence()
+            res[name] = round(e0.elapsed_time(e1) / 10, 3)
+        if rank == 0:
+            print("PEERBUF_OK", world, {k: f"{v} ms ({0.268435456 / v * 1e3:.0f} GB/s written)" for k, v in res.items()})
+
     # ---------------- batch-sharded (cfg 3 in miniature) ------------------------------------------------
     rng = np.random.RandomState(3)
     lens = rng.randint(16, 200, 24)
