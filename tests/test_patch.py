@@ -63,3 +63,32 @@ def test_peer_exchange_needs_a_process_group():
         pytest.skip("a process group is already up in this interpreter")
     with pytest.raises(RuntimeError, match="initialised process group"):
         D.PeerExchange(max_tokens=16)
+    with pytest.raises(RuntimeError, match="initialised process group"):
+        import torch
+        D.PeerPackedBuffer(numel=16, dtype=torch.bfloat16)
+
+
+def test_parallel_group_lookup_without_a_process_group():
+    """gather_logprobs' distributed branches stay off unless a group with more than one rank is set or found where
+    the reference looks (megatron.core.parallel_state / areal.utils.ulysses, only if already imported)."""
+    from areal_b200 import functional as F
+    F.reset_parallel_groups()
+    assert F._tp_group() is None and F._sp_group() is None
+    F.set_parallel_groups(tp_group="not a real group", sp_group="neither")     # no process group: world of one
+    assert F._tp_group() is None and F._sp_group() is None
+    F.reset_parallel_groups()
+    fake = types.ModuleType("megatron.core.parallel_state")
+    fake.is_initialized = lambda: True
+    fake.get_tensor_model_parallel_world_size = lambda: 4
+    fake.get_tensor_model_parallel_group = lambda: "tp-group"
+    saved = sys.modules.get("megatron.core.parallel_state")
+    sys.modules["megatron.core.parallel_state"] = fake
+    try:
+        assert F._tp_group() == "tp-group"
+        fake.get_tensor_model_parallel_world_size = lambda: 1
+        assert F._tp_group() is None
+    finally:
+        if saved is None:
+            del sys.modules["megatron.core.parallel_state"]
+        else:
+            sys.modules["megatron.core.parallel_state"] = saved
