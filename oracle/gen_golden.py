@@ -687,6 +687,46 @@ def gen_sft_stats():
     print("sft_stats golden:", len(out), "keys", losses)
 
 
+def gen_lm_head(af):
+    """The step BEFORE the path: logits = hidden @ lm_head.weight.T as the engine materialises them
+    (areal/engine/fsdp_engine.py:571-573), then the unmodified gather_logprobs_entropy + ppo_actor_loss_fn and
+    `(loss * loss_scale).backward()` down to the hidden state and the weight.  Hidden states / weights sit on
+    coarse binary grids so that every dot product is exact in fp32: the bf16 logits are the same bits on the CPU
+    here and in any GEMM on the GPU."""
+    z = {}
+    k = 0
+    for (T, Hd, V, temp, scale, cfg) in ((300, 64, 4104, 0.9, 0.37, dict(eps_clip=0.4, c_clip=3.0, behav_imp_weight_cap=5.0)),
+                                         (130, 64, 8200, 1.0, 1.0, dict(eps_clip=0.2, eps_clip_higher=0.28))):
+        g = torch.Generator().manual_seed(4200 + k)
+        h = (torch.randint(-16, 17, (T, Hd), generator=g).float() / 8).bfloat16().requires_grad_()
+        w = (torch.randint(-16, 17, (V, Hd), generator=g).float() / 32).bfloat16().requires_grad_()
+        labels = torch.randint(0, V, (T,), generator=g)
+        logits = torch.nn.functional.linear(h, w)
+        exact = (h.detach().double() @ w.detach().double().t()).float().bfloat16()
+        assert torch.equal(logits.detach(), exact), "CPU bf16 linear is not the exactly rounded product"
+        lp, ent = af.gather_logprobs_entropy(logits, labels, temp)
+        prox = (lp.detach() + 0.02 * torch.randn(T, generator=g)).float()
+        old = (lp.detach() + 0.05 * torch.randn(T, generator=g)).float()
+        adv = torch.randn(T, generator=g)
+        mask = torch.rand(T, generator=g) > 0.3
+        loss, stat = af.ppo_actor_loss_fn(logprobs=lp, proximal_logprobs=prox, old_logprobs=old, advantages=adv,
+                                          loss_mask=mask, **cfg)
+        (loss * scale).backward()
+        pfx = f"c{k}_"
+        z.update({pfx + "h_bits": bf16_bits(h.detach()), pfx + "w_bits": bf16_bits(w.detach()), pfx + "labels": labels.numpy(),
+                  pfx + "temp": np.array(temp), pfx + "scale": np.array(scale), pfx + "prox": prox.numpy(),
+                  pfx + "old": old.numpy(), pfx + "adv": adv.numpy(), pfx + "mask": mask.numpy(),
+                  pfx + "loss": np.array(float(loss.detach())), pfx + "logp": lp.detach().numpy(),
+                  pfx + "entropy": ent.detach().numpy(), pfx + "dh_bits": bf16_bits(h.grad), pfx + "dw_bits": bf16_bits(w.grad),
+                  pfx + "importance_weight": stat["importance_weight"].numpy(), pfx + "clip_mask": stat["clip_mask"].numpy()})
+        for name, val in cfg.items():
+            z[pfx + "cfg_" + name] = np.array(val)
+        k += 1
+    z["n_cases"] = np.array(k)
+    np.savez_compressed(os.path.join(OUT, "lm_head.npz"), **z)
+    print("lm_head golden cases:", k)
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     assert R.available(), "needs /root/reference"
@@ -713,6 +753,7 @@ def main():
     gen_aent_stats()
     gen_critic_stats()
     gen_sft_stats()
+    gen_lm_head(af)
 
 
 if __name__ == "__main__":

@@ -182,3 +182,32 @@ def test_lm_head_empty_batch():
     loss.backward()
     assert float(loss) == 0.0 and st["logprobs"].shape == (0,)
     assert h.grad.shape == (0, 64) and not torch.any(w.grad != 0)
+
+
+def test_lm_head_golden_from_the_reference():
+    """Golden vectors of the UNMODIFIED reference (oracle/gen_golden.py::gen_lm_head): logits = F.linear(hidden,
+    weight), gather_logprobs_entropy, ppo_actor_loss_fn, (loss * scale).backward() down to hidden and weight."""
+    from areal_b200.lm_head import fused_lm_head_actor_loss
+    z = H.load("lm_head.npz")
+    for k, c in H.cases(z):
+        h = H.bf16_from_bits(c["h_bits"]).to(D).requires_grad_()
+        w = H.bf16_from_bits(c["w_bits"]).to(D).requires_grad_()
+        cfg = {name: (float(c["cfg_" + name]) if "cfg_" + name in c else None)
+               for name in ("eps_clip", "eps_clip_higher", "c_clip", "behav_imp_weight_cap")}
+        t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(D)
+        scale = float(c["scale"])
+        loss, st = fused_lm_head_actor_loss(h, w, t(c["labels"]), float(c["temp"]), t(c["prox"]), t(c["old"]),
+                                            t(c["adv"]), t(c["mask"]), loss_scale=scale, chunk_rows=64, **cfg)
+        (loss * scale).backward()
+        want = float(c["loss"])
+        assert abs(float(loss.detach()) - want) <= H.TOL_LOGITS * max(1.0, abs(want)), k
+        assert np.allclose(st["logprobs"].cpu().numpy(), c["logp"], rtol=H.TOL_LOGITS, atol=H.TOL_LOGITS), k
+        assert np.allclose(st["entropy"].cpu().numpy(), c["entropy"], rtol=H.TOL_LOGITS, atol=H.TOL_LOGITS), k
+        assert np.allclose(st["importance_weight"].cpu().numpy(), c["importance_weight"], rtol=1e-4, atol=1e-5), k
+        assert np.array_equal(st["clip_mask"].cpu().numpy(), c["clip_mask"]), k
+        # both sides feed bf16 dlogits to bf16 GEMMs: one bf16 ulp per element, plus the accumulation noise
+        for got, bits in ((h.grad, c["dh_bits"]), (w.grad, c["dw_bits"])):
+            ref = H.bf16_from_bits(bits).float().numpy().astype(np.float64)
+            got = got.float().cpu().numpy().astype(np.float64)
+            assert got.shape == ref.shape
+            assert np.all(np.abs(got - ref) <= 2 ** -6 * np.abs(ref) + 2 ** -7 * np.abs(ref).max() + 1e-30), k

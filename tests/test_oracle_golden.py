@@ -308,3 +308,28 @@ def test_clamped_entropy_oracle_vs_reference():
         np.testing.assert_allclose(ent, c["ent"], rtol=2e-5, atol=2e-5)
         g = O.clamped_entropy_dlogits(x, c["labels"], c["clamp"], c["temp"], c["w_lp"], c["w_h"])
         CC.check_grad(g, c["grad"].astype(np.float64), x, c["clamp"], 2e-5, "oracle")
+
+
+def test_lm_head_golden_vs_oracle():
+    """The LM-head golden (reference run on hidden @ weight.T, oracle/gen_golden.py::gen_lm_head): the oracle applied to
+    the exactly rounded logits reproduces the reference's log-probs, entropy, loss, and -- through the fp64 chain
+    rule -- its gradients w.r.t. hidden state and weight up to their bf16 rounding."""
+    import torch
+    z = H.load("lm_head.npz")
+    for k, c in H.cases(z):
+        h = H.bf16_from_bits(c["h_bits"]).double().numpy()
+        w = H.bf16_from_bits(c["w_bits"]).double().numpy()
+        logits = torch.from_numpy(h @ w.T).float().bfloat16().float().numpy()
+        temp, scale = float(c["temp"]), float(c["scale"])
+        lp, ent, *_ = O.gather_logprobs_entropy(logits, c["labels"], temp)
+        assert np.allclose(lp, c["logp"], rtol=1e-5, atol=1e-5) and np.allclose(ent, c["entropy"], rtol=1e-5, atol=1e-5)
+        cfg = {name: (float(c["cfg_" + name]) if "cfg_" + name in c else None)
+               for name in ("eps_clip", "eps_clip_higher", "c_clip", "behav_imp_weight_cap")}
+        loss, st, coef = O.ppo_actor_loss(lp, c["prox"].astype(np.float64), c["old"].astype(np.float64),
+                                          c["adv"].astype(np.float64), loss_mask=c["mask"], dtype=np.float64, **cfg)
+        assert abs(loss - float(c["loss"])) <= 1e-5 * max(1.0, abs(float(c["loss"])))
+        assert np.array_equal(st["clip_mask"], c["clip_mask"])
+        dl = O.dlogits(logits, c["labels"], temp, scale * coef)
+        for ref_bits, mine in ((c["dh_bits"], dl @ w), (c["dw_bits"], dl.T @ h)):
+            ref = H.bf16_from_bits(ref_bits).double().numpy()
+            assert np.all(np.abs(mine - ref) <= 2 ** -6 * np.abs(mine) + 2 ** -7 * np.abs(mine).max() + 1e-30), k
