@@ -398,3 +398,65 @@ def load_areal_sft_loss_fn():
     ns = dict(torch=torch, Dict=Dict, Any=Any, gather_logprobs=af.gather_logprobs, stats_tracker=st)
     exec(compile(ast.get_source_segment(src, node), "lm_engine.py[compute_packed_sft_loss]", "exec"), ns)
     return ns["compute_packed_sft_loss"], st
+
+
+def load_vocab_parallel(tp_group, tp_rank: int, tp_world: int):
+    """The reference's two vocabulary-sharded ops, executed where they lie, for a torch.distributed group
+    (gloo on CPU in the build container):
+      * `_VocabParallelEntropy` (areal/utils/mcore/functional.py:8-52) -- what gather_logprobs_entropy calls under
+        Megatron tensor parallelism (areal/utils/functional.py:91-98); its local `torch.compile` helper runs
+        eagerly here (torch.compile is made the identity while the file loads and runs);
+      * `vocab_parallel_cross_entropy` (realhf/impl/model/parallelism/tensor_parallel/modules.py:1060-1186), the
+        copy of Megatron's `tensor_parallel.vocab_parallel_cross_entropy` that the reference tree carries
+        (megatron-core itself, pyproject.toml:49, is not in the tree).
+    Returns (VocabParallelEntropy, vocab_parallel_cross_entropy)."""
+    import logging as pylogging
+    import torch
+    tp_dir = os.path.join(REF_ROOT, "realhf/impl/model/parallelism/tensor_parallel")
+    mpu = types.ModuleType("megatron.core.parallel_state")
+    mpu.get_tensor_model_parallel_group = lambda: tp_group
+    mpu.is_initialized = lambda: True
+    mpu.get_tensor_model_parallel_world_size = lambda: tp_world
+    core = types.ModuleType("megatron.core")
+    core.parallel_state = mpu
+    constants = types.ModuleType("realhf.base.constants")
+    constants.tensor_parallel_group = lambda: tp_group
+    constants.tensor_parallel_rank = lambda: tp_rank
+    constants.tensor_parallel_world_size = lambda: tp_world
+    rlog = types.ModuleType("realhf.base.logging")
+    rlog.getLogger = lambda *a, **k: pylogging.getLogger("ref")
+    base = types.ModuleType("realhf.base")
+    base.constants, base.logging = constants, rlog
+    rnd = types.ModuleType("realhf.impl.model.utils.random")
+    rnd._initialize_affine_weight_gpu = lambda *a, **k: None
+    tp_pkg = types.ModuleType("realhf.impl.model.parallelism.tensor_parallel")
+    tp_pkg.__path__ = [tp_dir]
+    stubs = {"megatron": types.ModuleType("megatron"), "megatron.core": core, "megatron.core.parallel_state": mpu,
+             "realhf": types.ModuleType("realhf"), "realhf.base": base, "realhf.base.constants": constants,
+             "realhf.base.logging": rlog, "realhf.impl": types.ModuleType("realhf.impl"),
+             "realhf.impl.model": types.ModuleType("realhf.impl.model"),
+             "realhf.impl.model.utils": types.ModuleType("realhf.impl.model.utils"),
+             "realhf.impl.model.utils.random": rnd,
+             "realhf.impl.model.parallelism": types.ModuleType("realhf.impl.model.parallelism"),
+             "realhf.impl.model.parallelism.tensor_parallel": tp_pkg}
+    for name in ("realhf", "realhf.base", "realhf.impl", "realhf.impl.model", "realhf.impl.model.utils",
+                 "realhf.impl.model.parallelism", "megatron"):
+        stubs[name].__path__ = []
+    saved = {k: sys.modules.get(k) for k in stubs}
+    real_compile = torch.compile
+    try:
+        sys.modules.update(stubs)
+        torch.compile = lambda *a, **k: (a[0] if a and callable(a[0]) else (lambda f: f))
+        ent_mod = _load("areal/utils/mcore/functional.py", "_ref_areal_mcore_functional")
+        ce_mod = _load("realhf/impl/model/parallelism/tensor_parallel/modules.py",
+                       "realhf.impl.model.parallelism.tensor_parallel.modules")
+    finally:
+        # torch.compile stays patched for the caller's run of _VocabParallelEntropy.forward (it calls
+        # torch.compile at call time); restore_compile() below puts it back
+        for k, v in saved.items():
+            if v is None:
+                sys.modules.pop(k, None)
+            else:
+                sys.modules[k] = v
+    ent_mod._restore_compile = lambda: setattr(torch, "compile", real_compile)
+    return ent_mod._VocabParallelEntropy, ce_mod.vocab_parallel_cross_entropy, ent_mod._restore_compile

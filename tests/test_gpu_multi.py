@@ -46,3 +46,35 @@ def test_nccl_sharded_paths(world):
     # slice_intervals wrote into the neighbour's staging buffer over NVLink, bit-exact, or no peer mapping here
     assert f"PEERBUF_OK {world}" in r.stdout or "PEERBUF_UNAVAILABLE" in r.stdout, r.stdout[-2000:]
     print(next(line for line in r.stdout.splitlines() if line.startswith("PEERBUF_")))
+
+
+def test_vocab_sharded_kernels_vs_reference_golden():
+    """The per-shard partial kernel, the combine kernel and the sharded backward, run shard by shard on ONE GPU,
+    against golden vectors of the reference's own vocabulary-sharded code on two gloo ranks
+    (tests/golden/vocab_parallel.npz, oracle/gen_golden_tp.py: `_VocabParallelEntropy`,
+    areal/utils/mcore/functional.py:8-52, and the tree's copy of Megatron's vocab_parallel_cross_entropy,
+    realhf/impl/model/parallelism/tensor_parallel/modules.py:1060-1186)."""
+    import numpy as np
+    from areal_b200 import dist as D
+    from areal_b200.functional import _logits_backward
+    z = H.load("vocab_parallel.npz")
+    world = int(z["world"])
+    dev = "cuda:0"
+    for k, c in H.cases(z):
+        logits = H.bf16_from_bits(c["logits_bits"]).to(dev)
+        labels = torch.from_numpy(c["labels"]).to(dev)
+        temp = float(c["temp"])
+        Vs = logits.shape[1] // world
+        shards = [logits[:, r * Vs:(r + 1) * Vs].contiguous() for r in range(world)]
+        parts = torch.stack([D._cuda_partials(shards[r], labels, r * Vs, temp) for r in range(world)])
+        logp, ent, row_max, ln_s = D._cuda_combine(parts, temp)
+        assert np.allclose(logp.cpu().numpy(), c["logp"], rtol=H.TOL_LOGITS, atol=H.TOL_LOGITS), k
+        assert np.allclose(ent.cpu().numpy(), c["entropy"], rtol=H.TOL_LOGITS, atol=H.TOL_LOGITS), k
+        g_lp, g_h = torch.from_numpy(c["g_lp"]).to(dev), torch.from_numpy(c["g_h"]).to(dev)
+        slack = 1e-6 * (np.abs(c["g_lp"]) + 12 * np.abs(c["g_h"]))[:, None] / temp
+        for r in range(world):
+            d = _logits_backward(shards[r], labels, temp, row_max, ln_s, ent, g_lp, g_h, vocab_start=r * Vs)
+            got = d.float().cpu().numpy().astype(np.float64)
+            want = H.bf16_from_bits(c[f"grad{r}_bits"]).double().numpy()
+            # both are bf16 roundings of the same gradient (the reference's with its fp32 cancellation at the label)
+            assert np.all(np.abs(got - want) <= 2 ** -6 * np.abs(want) + slack + 1e-30), (k, r)

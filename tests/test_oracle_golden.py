@@ -333,3 +333,29 @@ def test_lm_head_golden_vs_oracle():
         for ref_bits, mine in ((c["dh_bits"], dl @ w), (c["dw_bits"], dl.T @ h)):
             ref = H.bf16_from_bits(ref_bits).double().numpy()
             assert np.all(np.abs(mine - ref) <= 2 ** -6 * np.abs(mine) + 2 ** -7 * np.abs(mine).max() + 1e-30), k
+
+
+def test_vocab_parallel_golden_vs_oracle():
+    """Golden from the reference's OWN vocabulary-sharded code on two gloo ranks (oracle/gen_golden_tp.py:
+    `_VocabParallelEntropy` + the tree's copy of Megatron's vocab_parallel_cross_entropy, as
+    gather_logprobs_entropy runs them under tensor parallelism, areal/utils/functional.py:91-98): the oracle's
+    per-shard partials + combine reproduce its log-probs and entropy, the unsharded oracle gradient its per-shard
+    gradients."""
+    z = H.load("vocab_parallel.npz")
+    world = int(z["world"])
+    for k, c in H.cases(z):
+        logits = H.bf16_from_bits(c["logits_bits"]).float().numpy()
+        labels, temp = c["labels"], float(c["temp"])
+        Vs = logits.shape[1] // world
+        parts = np.stack([O.shard_partials(logits[:, r * Vs:(r + 1) * Vs], labels, r * Vs, temp) for r in range(world)])
+        logp, ent, row_max, ln_s = O.combine_partials(parts, temp)
+        assert np.allclose(logp, c["logp"], rtol=2e-5, atol=2e-5), k
+        assert np.allclose(ent, c["entropy"], rtol=2e-5, atol=2e-5), k
+        ref = O.dlogits(logits, labels, temp, c["g_lp"].astype(np.float64), c["g_h"].astype(np.float64))
+        for r in range(world):
+            got = H.bf16_from_bits(c[f"grad{r}_bits"]).double().numpy()
+            want = ref[:, r * Vs:(r + 1) * Vs]
+            # the reference forms p - 1 at the label in fp32 (a cancellation on peaked rows; exactly 0 when p rounds to 1):
+            # one bf16 ulp of the value plus 1e-6 of the upstream gradient's size
+            slack = 1e-6 * (np.abs(c["g_lp"]) + 12 * np.abs(c["g_h"]))[:, None] / temp
+            assert np.all(np.abs(got - want) <= 2 ** -7 * np.abs(want) + slack + 1e-30), (k, r)
