@@ -9,11 +9,14 @@ Parity status: PINNED.  Every function below is checked in
 UNMODIFIED reference functions in the build container
 (`oracle/gen_golden.py` -> `tests/golden/*.npz`), and -- where the reference has its
 own known-answer test -- against that test's independent formula
-(`realhf/tests/data/test_dual_clip.py:8-50`).  Exceptions, stated where they occur:
+(`realhf/tests/data/test_dual_clip.py:8-50`).  Two parts have no CPU-runnable reference
+function and are pinned by running the reference's own code another way:
 `gae_2d_olp` (no Python caller and no test in the reference; restated from
-`csrc/cugae/gae.cu:62-89`: parity unpinned) and `vocab_parallel_*` (third-party
-megatron-core 0.13.1 `vocab_parallel_cross_entropy`, absent from /root/reference;
-pinned against the unsharded oracle instead).
+`csrc/cugae/gae.cu:62-89`) against outputs of the reference's CUDA kernels compiled from
+where they lie and run on a B200 (`oracle/gen_golden_gpu.py` -> `tests/golden/gae2d.npz`),
+and `shard_partials` / `combine_partials` against the reference's vocabulary-sharded code on
+two gloo ranks (`oracle/gen_golden_tp.py` -> `tests/golden/vocab_parallel.npz`; megatron-core
+itself is third-party and absent, the tree carries a copy of its cross entropy).
 
 All file:line citations are relative to the reference root.
 """
@@ -137,7 +140,8 @@ def gae_2d_olp(rewards, values, done, done_y_indices, cu_num_dones, is_truncate,
     csrc/cugae/gae.cu:62-89; the `_nolp` host wrapper launches this same kernel,
     gae.cu:199).  Thread (b, seg) walks [t_start, t_end) backwards; nex_v = 0 when
     t is the segment tail and done[b,t+1]; a truncated non-final segment zeroes its
-    tail GAE (:85).  No Python caller / test upstream -> parity unpinned."""
+    tail GAE (:85).  No Python caller / test upstream: pinned against outputs of the kernel
+    itself (tests/golden/gae2d.npz)."""
     r = np.asarray(rewards, dtype=f32)
     v = np.asarray(values, dtype=f32)
     d = np.asarray(done).astype(bool)

@@ -252,7 +252,7 @@ def test_gae_padded_vs_oracle(B, S):
 
 
 def test_gae2d_olp_vs_oracle():
-    """No reference caller / test exists (parity unpinned upstream): compared with the restatement of
+    """No reference caller / test exists; the golden of the kernel itself is checked below.  Here: the restatement of
     gae_kernel_2d_olp (gae.cu:62-89), incl. truncated segments and the nolp alias."""
     from areal_b200 import ppo_functional as P
     d = dev()
@@ -278,3 +278,19 @@ def test_gae2d_olp_vs_oracle():
             adv, ret = fn(t(r), t(v), t(done), t(idx), t(cu), int(np.diff(cu).max(initial=0)), t(trunc), 0.99, 0.95)
             assert row_rel(adv.cpu().numpy(), a_ref) <= H.TOL_GAE
             assert row_rel(ret.cpu().numpy(), r_ref) <= H.TOL_GAE
+
+
+def test_gae2d_vs_reference_kernel_golden():
+    """Our segment-table 2D GAE against outputs of the reference's own CUDA kernels (tests/golden/gae2d.npz, made on a
+    B200 by oracle/gen_golden_gpu.py from csrc/cugae/gae.cu compiled where it lies): 1e-5 relative, both entry points."""
+    from areal_b200 import ppo_functional as P
+    d = dev()
+    z = H.load("gae2d.npz")
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(d)
+    for k, c in H.cases(z):
+        mx = int(np.diff(c["cu"]).max(initial=0))
+        for fn, tag in ((P.gae_2d_olp, "olp"), (P.gae_2d_nolp, "nolp")):
+            adv, ret = fn(t(c["rewards"]), t(c["values"]), t(c["done"]), t(c["idx"]), t(c["cu"]), mx, t(c["trunc"]),
+                          float(c["gamma"]), float(c["lam"]))
+            assert row_rel(adv.cpu().numpy(), c["adv_" + tag]) <= H.TOL_GAE, (k, tag)
+            assert row_rel(ret.cpu().numpy(), c["ret_" + tag]) <= H.TOL_GAE, (k, tag)

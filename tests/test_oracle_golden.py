@@ -36,7 +36,7 @@ def test_gae_padded_bit_exact_vs_reference():
 
 
 def test_gae_2d_olp_consistent_with_1d():
-    """No reference test exists for the 2D kernels (parity unpinned); check the restatement
+    """No reference test exists for the 2D kernels (their own outputs: test_gae2d_golden_vs_oracle); check the restatement
     reduces to the pinned 1D recurrence when every row is one bootstrapped segment."""
     rng = np.random.RandomState(3)
     B, Hh = 4, 33
@@ -359,3 +359,17 @@ def test_vocab_parallel_golden_vs_oracle():
             # one bf16 ulp of the value plus 1e-6 of the upstream gradient's size
             slack = 1e-6 * (np.abs(c["g_lp"]) + 12 * np.abs(c["g_h"]))[:, None] / temp
             assert np.all(np.abs(got - want) <= 2 ** -7 * np.abs(want) + slack + 1e-30), (k, r)
+
+
+def test_gae2d_golden_vs_oracle():
+    """tests/golden/gae2d.npz holds outputs of the reference's own `gae_2d_olp` / `gae_2d_nolp` CUDA kernels
+    (csrc/cugae/gae.cu compiled from where it lies, run on a B200 by oracle/gen_golden_gpu.py): the restatement
+    follows them to fp32 rounding, and the two entry points agree bit for bit (the `_nolp` host wrapper launches
+    the `_olp` kernel, gae.cu:199)."""
+    z = H.load("gae2d.npz")
+    for k, c in H.cases(z):
+        a, r = O.gae_2d_olp(c["rewards"], c["values"], c["done"], c["idx"], c["cu"], c["trunc"], float(c["gamma"]),
+                            float(c["lam"]))
+        scale = max(1.0, float(np.abs(c["adv_olp"]).max()))
+        assert np.abs(a - c["adv_olp"]).max() <= 1e-5 * scale and np.abs(r - c["ret_olp"]).max() <= 1e-5 * scale, k
+        assert np.array_equal(c["adv_olp"], c["adv_nolp"]) and np.array_equal(c["ret_olp"], c["ret_nolp"]), k
