@@ -92,3 +92,19 @@ def test_parallel_group_lookup_without_a_process_group():
             del sys.modules["megatron.core.parallel_state"]
         else:
             sys.modules["megatron.core.parallel_state"] = saved
+
+
+def test_lm_head_entry_points_refuse_cpu_tensors():
+    """No CPU fallback on the LM-head path either: CPU tensors raise before any work is done."""
+    import pytest
+    import torch
+    from areal_b200 import _lib
+    from areal_b200.lm_head import fused_lm_head_actor_loss, lm_head_logprobs
+    h = torch.zeros(4, 16, dtype=torch.bfloat16, requires_grad=True)
+    w = torch.zeros(32, 16, dtype=torch.bfloat16, requires_grad=True)
+    lab = torch.zeros(4, dtype=torch.long)
+    e = torch.zeros(4)
+    with pytest.raises(_lib.ArealB200Error, match="CUDA tensors only"):
+        fused_lm_head_actor_loss(h, w, lab, 1.0, e, e, e, e > 0, eps_clip=0.2)
+    with pytest.raises(_lib.ArealB200Error, match="CUDA tensors only"):
+        lm_head_logprobs(h, w, lab)
