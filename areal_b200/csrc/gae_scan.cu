@@ -423,7 +423,7 @@ __device__ __forceinline__ TokOut fused_math(const AdvFusedParams& f, const RowC
     const float lr = -kl;                                                      // :1359
     kl = __fsub_rn(__fsub_rn(expf(lr), 1.f), lr);                              // :1360
   }
-  if (f.kl_clamp) kl = fminf(fmaxf(kl, -10.f), 10.f);                          // :1363 (NaN stays NaN)
+  if (f.kl_clamp) kl = clamp_nan(kl, -10.f, 10.f);                             // :1363 (torch.clamp: NaN stays NaN)
   o.klr = __fmul_rn(f.neg_kl_ctl, kl);                                         // actor.py:128
   o.tot = o.klr;
   if (t == c.zero_col) o.tot = 0.f;                                            // :131
@@ -528,7 +528,7 @@ gae_padded_kernel(const GaePaddedParams p, const AdvFusedParams f) {
       }
       if (f.apply_scaling) {
         sc = __fmul_rn(__fadd_rn(sc, f.bias), f.scaling);        // :98
-        sc = fminf(fmaxf(sc, -f.clip), f.clip);                  // :99-101
+        sc = clamp_nan(sc, -f.clip, f.clip);                     // :99-101
       }
       ctx.row_off = row * p.S;
       ctx.S = p.S;

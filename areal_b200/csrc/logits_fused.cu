@@ -734,6 +734,14 @@ int set_smem(K kern) {
   return kOk;
 }
 
+// cudaFuncSetAttribute is per device: one "already set" flag per device ordinal
+constexpr int kMaxDevices = 64;
+int current_device_slot() {
+  int d = 0;
+  cudaGetDevice(&d);
+  return d & (kMaxDevices - 1);
+}
+
 int grid_for(int64_t T, int per_sm) {
   const int64_t g = int64_t(num_sms()) * per_sm;
   return static_cast<int>(T < g ? T : g);
@@ -746,17 +754,18 @@ int64_t logits_loss_workspace_bytes() { return 16 + 8 * int64_t(num_sms()) * 8; 
 int launch_logits_fwd(const LogitsFwdParams& p, cudaStream_t stream) {
   if (p.T == 0) return kOk;
   const bool minmax = p.raw_min != nullptr;
+  const int dev = current_device_slot();
   if (tma_ok(p.logits, p.dtype, p.V, p.row_stride_bytes)) {
     // rows of at most 64 KB (vocabulary shards): half-width CTAs, twice as many of them
     const bool narrow = p.V * (p.dtype == kFP32 ? 4 : 2) <= 65536;
 #define AB_LAUNCH_FWD_W(MM, E, W)                                                                  \
   {                                                                                                \
-    static bool done = false;                                                                      \
+    static bool done[kMaxDevices] = {};            /* the attribute is per device */              \
     constexpr size_t smem = size_t(kStages) * (W * 2048) + 1024;                                   \
-    if (!done) {                                                                                   \
+    if (!done[dev]) {                                                                              \
       AB_CUDA(cudaFuncSetAttribute(logits_fwd_tma_kernel<MM, E, W>,                                \
                                    cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));       \
-      done = true;                                                                                 \
+      done[dev] = true;                                                                            \
     }                                                                                              \
     logits_fwd_tma_kernel<MM, E, W><<<grid_for(p.T, 16 / W), (W + 1) * 32, smem, stream>>>(p);     \
   }
@@ -780,16 +789,17 @@ int launch_logits_fwd(const LogitsFwdParams& p, cudaStream_t stream) {
 
 int launch_logits_bwd(const LogitsBwdParams& p, cudaStream_t stream) {
   if (p.T == 0) return kOk;
+  const int dev = current_device_slot();
   if (tma_ok(p.logits, p.dtype, p.V, p.row_stride_bytes) &&
       tma_ok(p.dlogits, p.dtype, p.V, p.d_row_stride_bytes)) {
     const int grid = grid_for(p.T, kCtasPerSm);
 #define AB_LAUNCH_BWD(E)                                                           \
   {                                                                                \
-    static bool done = false;                                                      \
-    if (!done) {                                                                   \
+    static bool done[kMaxDevices] = {};                                            \
+    if (!done[dev]) {                                                              \
       const int rc = set_smem(logits_bwd_tma_kernel<E>);                           \
       if (rc) return rc;                                                           \
-      done = true;                                                                 \
+      done[dev] = true;                                                            \
     }                                                                              \
     logits_bwd_tma_kernel<E><<<grid, kThreads, kSmemBytes, stream>>>(p);           \
   }

@@ -434,7 +434,14 @@ int launch_fused_rowres(const LogitsFwdParams& p, void* dlogits, int64_t d_row_s
     return kUnsupported;
   }
   const int64_t nvec = p.V / 8;
-  constexpr int64_t kBudget = 228 * 1024;    // dynamic shared memory available to one CTA per SM (minus statics)
+  // dynamic shared memory one CTA can really ask for: the device's opt-in limit minus the kernel's static
+  // shared memory minus the 1 KB of alignment slack added to the request below
+  int dev = 0, optin = 0;
+  AB_CUDA(cudaGetDevice(&dev));
+  AB_CUDA(cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+  cudaFuncAttributes fa;
+  AB_CUDA(cudaFuncGetAttributes(&fa, fused_rowres_kernel));
+  const int64_t kBudget = int64_t(optin) - int64_t(fa.sharedSizeBytes) - 1024;
   auto slice_of = [&](int c) { return (((nvec + c - 1) / c) * 16 + 127) & ~int64_t(127); };
   int C = 0, nbuf = 2;
   if (force_cluster > 0) {
@@ -453,6 +460,13 @@ int launch_fused_rowres(const LogitsFwdParams& p, void* dlogits, int64_t d_row_s
         C = c;
         nbuf = 2;
       }
+  }
+  // every CTA of the cluster must own a non-empty slice (the statistics group of an empty rank would
+  // never wait on a full barrier and would run ahead of the exchange)
+  if (C > 1 && int64_t(C - 1) * ((nvec + C - 1) / C) >= nvec) {
+    set_error("row-resident path: cluster_size=%d leaves a CTA without any of the row's %lld 16-byte vectors", C,
+              (long long)nvec);
+    return kInvalidArgument;
   }
   if (C <= 0 || C > kMaxCluster || nbuf * slice_of(C) > kBudget) {
     set_error("row-resident path: V=%lld does not fit a cluster of at most %d CTAs", (long long)p.V, kMaxCluster);

@@ -149,15 +149,15 @@ packed_rewards_kernel(const float* __restrict__ logp, const float* __restrict__ 
         if (t + 1 == end) {
           int s2 = seq;
           while (s2 + 1 < B && int64_t(__ldg(cu + s2 + 2)) == end) ++s2;
-          float sc = fminf(fmaxf(__ldg(score + s2), -clip), clip);                            // :243
+          float sc = clamp_nan(__ldg(score + s2), -clip, clip);                            // :243
           if (mask_no_eos_with_zero && no_eos[s2]) sc = 0.f;                                  // :245-248
           tot = __fadd_rn(tot, sc);
         }
       } else {
         const int64_t j = t + seq;                                                             // offset2 + (t - offset)
-        const float d1 = fminf(fmaxf(__ldg(score + j + 1), -clip), clip);
+        const float d1 = clamp_nan(__ldg(score + j + 1), -clip, clip);
         if (mode == 2) {
-          const float d0 = fminf(fmaxf(__ldg(score + j), -clip), clip);
+          const float d0 = clamp_nan(__ldg(score + j), -clip, clip);
           tot = __fadd_rn(tot, __fsub_rn(d1, d0));                                            // :272-275
         } else {
           tot = __fadd_rn(tot, d1);                                                           // :277-279

@@ -34,11 +34,11 @@ __device__ __forceinline__ ActorTokenOut actor_token(float lp, float prox, float
   const float denorm = c.decoupled ? prox : old;
   o.kl = lp - denorm;
   o.ratio = mask ? expf(o.kl) : 0.0f;                         // :191
-  const float clipped = fminf(fmaxf(o.ratio, c.lo), c.hi);    // :193-197
+  const float clipped = clamp_nan(o.ratio, c.lo, c.hi);        // :193-197 (torch.clamp: NaN stays NaN)
   const float l1 = -A * o.ratio;                              // :199
   const float l2 = -A * clipped;                              // :200
   o.clip = (l1 < l2) && mask;                                 // :201, :222
-  float pg = fmaxf(l1, l2);                                   // :202
+  float pg = max_nan(l1, l2);                                 // :202 (torch.max propagates NaN)
   const float w1 = l1 > l2 ? 1.0f : (l1 == l2 ? 0.5f : 0.0f);
   const bool inside = (o.ratio >= c.lo) && (o.ratio <= c.hi);
   float dpg = -A * (w1 + (inside ? (1.0f - w1) : 0.0f));
@@ -48,7 +48,7 @@ __device__ __forceinline__ ActorTokenOut actor_token(float lp, float prox, float
     const float l3 = (sgn * c.c_clip) * A;                    // :205
     o.dual = (l3 < pg) && mask;                               // :206, :223
     const float wmin = pg < l3 ? 1.0f : (pg == l3 ? 0.5f : 0.0f);
-    pg = fminf(pg, l3);                                       // :207
+    pg = min_nan(pg, l3);                                     // :207
     dpg *= wmin;
   }
   o.w = 0.0f;
@@ -72,7 +72,7 @@ __device__ __forceinline__ ActorTokenOut actor_token(float lp, float prox, float
 __device__ __forceinline__ float critic_token(float v, float old, float tgt, float eps, bool huber,
                                               float* g, bool* clip) {
   const float diff = v - old;
-  const float vc = old + fminf(fmaxf(diff, -eps), eps);       // :291-293
+  const float vc = old + clamp_nan(diff, -eps, eps);           // :291-293
   float lo_, lc_, dlo, dlc;
   {
     const float d0 = v - tgt, d1 = vc - tgt;
@@ -94,7 +94,7 @@ __device__ __forceinline__ float critic_token(float v, float old, float tgt, flo
   const float w1 = lo_ > lc_ ? 1.0f : (lo_ == lc_ ? 0.5f : 0.0f);
   *g = w1 * dlo + (inside ? (1.0f - w1) * dlc : 0.0f);
   *clip = lc_ > lo_;                                          // :300
-  return fmaxf(lo_, lc_);                                     // :297
+  return max_nan(lo_, lc_);                                   // :297
 }
 #endif
 

@@ -195,6 +195,7 @@ def vocab_parallel_forward(shard: torch.Tensor, labels: torch.Tensor, vocab_star
 class _VocabParallelLogprobsEntropy(torch.autograd.Function):
     @staticmethod
     def forward(ctx, shard, labels, vocab_start, temperature, group, exchange=None):
+        ctx.in_shape = shard.shape
         if shard.dim() != 2 or shard.stride(1) != 1:
             shard = shard.reshape(-1, shard.shape[-1]).contiguous()
         _lib.require_cuda(shard, labels)
@@ -217,7 +218,7 @@ class _VocabParallelLogprobsEntropy(torch.autograd.Function):
         gl = None if g_logp is None else _f32(g_logp.reshape(-1))
         gh = None if g_ent is None else _f32(g_ent.reshape(-1))
         d = _logits_backward(shard, lab, ctx.temperature, row_max, ln_s, ent, gl, gh, vocab_start=ctx.vocab_start)
-        return d, None, None, None, None, None
+        return d.view(ctx.in_shape), None, None, None, None, None
 
 
 def vocab_parallel_logprobs_entropy(shard_logits: torch.Tensor, labels: torch.Tensor, temperature: float = 1.0,

@@ -477,6 +477,12 @@ class _FusedActorRowRes(torch.autograd.Function):
     def backward(ctx, g_loss, *unused):
         if g_loss is None:
             return (None,) * 15
+        if getattr(ctx, "handed_out", False):
+            # the stored gradient now belongs to the caller (autograd may have taken it as .grad and
+            # accumulated into it); a second backward through this node cannot be served from it
+            raise RuntimeError("fused_actor_loss(loss_scale=...) keeps ONE gradient buffer and has already handed it "
+                               "out; call it with loss_scale=None to back-propagate more than once (retain_graph)")
+        ctx.handed_out = True
         dlogits, scale = ctx.saved_tensors
         g = _f32(g_loss.reshape(1))
         T, V = dlogits.shape
@@ -485,6 +491,19 @@ class _FusedActorRowRes(torch.autograd.Function):
             call("areal_b200_rescale_grad_if_needed", ptr(dlogits), T, V, V, ptr(g), ptr(scale),
                  stream_ptr(dlogits.device))
         return (dlogits.view(ctx.in_shape),) + (None,) * 14
+
+
+def _single_pass_eligible(logits: torch.Tensor) -> bool:
+    """What areal_b200_fused_actor_fwd_bwd accepts: bf16 rows, unit stride in V, V % 8 == 0, rows 16-byte
+    aligned.  Anything else (fp16 / fp32 logits, odd row strides) takes the two-pass entries."""
+    if logits.dtype != torch.bfloat16 or logits.dim() < 1:
+        return False
+    V = logits.shape[-1]
+    if V % 8 != 0 or logits.stride(-1) != 1 or logits.data_ptr() % 16 != 0:
+        return False
+    if logits.dim() == 2 and logits.shape[0] > 1 and logits.stride(0) % 8 != 0:
+        return False
+    return True
 
 
 def fused_actor_loss(logits: torch.Tensor, labels: torch.Tensor, temperature: float,
@@ -506,16 +525,26 @@ def fused_actor_loss(logits: torch.Tensor, labels: torch.Tensor, temperature: fl
     logits once and writes dlogits = loss_scale * dloss/dlogits in the same pass (rows stay in a
     thread-block cluster's shared memory between the two phases); the returned loss is still
     UNSCALED, and `(loss * loss_scale).backward()` just hands the stored gradient out (it is rescaled,
-    correctly but at the cost of an extra pass, if the upstream scalar turns out to differ)."""
+    correctly but at the cost of an extra pass, if the upstream scalar turns out to differ).  That
+    single pass is used only where it applies -- bf16 logits, 16-byte aligned rows, V % 8 == 0, a row
+    that fits a cluster of 8 CTAs; every other input silently takes the two passes, with the same
+    results.  The single-pass gradient can be back-propagated once (no retain_graph re-use)."""
     if c_clip is not None:
         assert c_clip > 1.0, c_clip
-    if loss_scale is not None and logits.requires_grad:
+    res = None
+    if loss_scale is not None and logits.requires_grad and _single_pass_eligible(logits):
         if not torch.is_tensor(loss_scale):
             loss_scale = torch.full((1,), float(loss_scale), dtype=torch.float32, device=logits.device)
-        res = _FusedActorRowRes.apply(logits, labels, temperature, proximal_logprobs, old_logprobs, advantages,
-                                      loss_mask, eps_clip, eps_clip_higher, c_clip, behav_imp_weight_cap,
-                                      with_logits_minmax, loss_scale, cluster_size, n_buffers)
-    else:
+        try:
+            res = _FusedActorRowRes.apply(logits, labels, temperature, proximal_logprobs, old_logprobs, advantages,
+                                          loss_mask, eps_clip, eps_clip_higher, c_clip, behav_imp_weight_cap,
+                                          with_logits_minmax, loss_scale, cluster_size, n_buffers)
+        except _lib.ArealB200Error as e:
+            # status 4 = the rows cannot be kept on chip (e.g. a vocabulary too wide for a cluster of 8):
+            # same result from the two-pass entries
+            if "(status 4)" not in str(e):
+                raise
+    if res is None:
         res = _FusedActor.apply(logits, labels, temperature, proximal_logprobs, old_logprobs, advantages,
                                 loss_mask, eps_clip, eps_clip_higher, c_clip, behav_imp_weight_cap,
                                 with_logits_minmax)

@@ -235,7 +235,7 @@ class DistributedStatsTracker:
         if self._acc is not None:
             dev, have = self._acc.device, self._acc
         else:                                     # this rank recorded nothing: identities only
-            dev, have = torch.device("cuda", torch.cuda.current_device()) if torch.cuda.is_available() else "cpu", None
+            dev, have = self._reduce_device(), None
         idx = [self._slot.get(k, -1) for k in tensor_keys]
         table = torch.tensor(_IDENTITY, dtype=torch.float64, device=dev).repeat(len(tensor_keys), 1)
         sel = [i for i, s in enumerate(idx) if s >= 0]
@@ -254,7 +254,8 @@ class DistributedStatsTracker:
         with self.lock:
             if key is not None:
                 full_key = self._get_full_key(key)
-                result = self._aggregate(full_key, self._totals([full_key], reduce_group), reduce_group)
+                result = self._aggregate(full_key, self._totals([full_key], reduce_group),
+                                         self._scalar_totals([full_key], reduce_group))
                 if reset:
                     self.denominators.pop(full_key, None)
                     self.reduce_types.pop(full_key, None)
@@ -275,9 +276,10 @@ class DistributedStatsTracker:
                         self.denominators.setdefault(k, d)
                 keys = sorted(set(k for ks, _, _ in all_keys for k in ks))
             totals = self._totals(keys, reduce_group)
+            scalar_totals = self._scalar_totals(keys, reduce_group)
             results = {}
             for k in keys:
-                results.update(self._aggregate(k, totals, reduce_group))
+                results.update(self._aggregate(k, totals, scalar_totals))
             if reset:
                 self.denominators = {}
                 self.reduce_types = {}
@@ -285,17 +287,31 @@ class DistributedStatsTracker:
                 self._reset_device_state()
             return results
 
-    def _aggregate(self, key, totals, reduce_group):
+    @staticmethod
+    def _reduce_device():
+        """Where the small export tables live: the current CUDA device whenever there is one (an NCCL
+        group cannot reduce CPU tensors; the reference uses the platform device, stats_tracker.py:189-201)."""
+        if torch.cuda.is_available():
+            return torch.device("cuda", torch.cuda.current_device())
+        return torch.device("cpu")
+
+    def _scalar_totals(self, keys, reduce_group):
+        """{key: (sum, count)} of the SCALAR keys; ONE all-reduce of a [K, 2] table for all of them."""
+        scalar_keys = [k for k in keys if self.reduce_types.get(k, ReduceType.SCALAR) == ReduceType.SCALAR]
+        if not scalar_keys:
+            return {}
+        rows = [[float(sum(self.scalars.get(k, []))), float(len(self.scalars.get(k, [])))] for k in scalar_keys]
+        if reduce_group is not None:
+            buf = torch.tensor(rows, dtype=torch.float64, device=self._reduce_device())
+            dist.all_reduce(buf, group=reduce_group)
+            rows = buf.cpu().tolist()
+        return {k: (r[0], r[1]) for k, r in zip(scalar_keys, rows)}
+
+    def _aggregate(self, key, totals, scalar_totals):
         reduce_type = self.reduce_types.get(key, ReduceType.SCALAR)
         result = {}
         if reduce_type == ReduceType.SCALAR:
-            vals = self.scalars.get(key, [])
-            value, cnt = float(sum(vals)), float(len(vals))
-            if reduce_group is not None:
-                buf = torch.tensor([value, cnt], dtype=torch.float64,
-                                   device=self._acc.device if self._acc is not None else "cpu")
-                dist.all_reduce(buf, group=reduce_group)
-                value, cnt = buf.tolist()
+            value, cnt = scalar_totals[key]
             result[key] = float(value / cnt)
             return result
         total, count, mn, mx = totals[key]

@@ -727,6 +727,94 @@ def gen_lm_head(af):
     print("lm_head golden cases:", k)
 
 
+def gen_nan_cases(af):
+    """NaN inputs: torch.clamp / torch.max / torch.min hand a NaN on (CUDA's fminf / fmaxf would not), so a
+    NaN log-prob, advantage, value or score must come out as NaN, not as a clamp bound.  Unmodified reference
+    functions on the CPU: ppo_actor_loss_fn, ppo_critic_loss_fn, PPOActor.compute_advantages."""
+    import types
+    z = {}
+    g = torch.Generator().manual_seed(77)
+    T = 96
+    nan = float("nan")
+    k = 0
+    for s in (dict(eps_clip=0.2, eps_clip_higher=None, c_clip=None, behav_imp_weight_cap=None),
+              dict(eps_clip=0.2, eps_clip_higher=0.28, c_clip=3.0, behav_imp_weight_cap=5.0)):
+        for where in ("lp", "prox", "old", "adv", "masked_lp"):
+            lp0 = -torch.rand(T, generator=g) * 5
+            lp = lp0 + 0.3 * torch.randn(T, generator=g)
+            prox = lp0 + 0.02 * torch.randn(T, generator=g)
+            old = lp0 + 0.05 * torch.randn(T, generator=g)
+            adv = torch.randn(T, generator=g)
+            mask = torch.rand(T, generator=g) > 0.3
+            mask[[3, 40, 77]] = where != "masked_lp"
+            {"lp": lp, "prox": prox, "old": old, "adv": adv, "masked_lp": lp}[where][[3, 40, 77]] = nan
+            lp.requires_grad_()
+            loss, st = af.ppo_actor_loss_fn(lp, prox, old, adv, loss_mask=mask, **s)
+            (grad,) = torch.autograd.grad(loss, lp)
+            p = f"a{k}_"
+            z.update({p + "lp": lp.detach().numpy(), p + "prox": prox.numpy(), p + "old": old.numpy(),
+                      p + "adv": adv.numpy(), p + "mask": mask.numpy(),
+                      p + "cfg": np.array([s["eps_clip"],
+                                           np.nan if s["eps_clip_higher"] is None else s["eps_clip_higher"],
+                                           np.nan if s["c_clip"] is None else s["c_clip"],
+                                           np.nan if s["behav_imp_weight_cap"] is None else s["behav_imp_weight_cap"]]),
+                      p + "loss": loss.detach().numpy(), p + "grad": grad.numpy()})
+            for name, val in st.items():
+                z[p + "stat_" + name] = val.detach().numpy()
+            k += 1
+    z["n_actor"] = np.array(k)
+    k = 0
+    for loss_type in ("mse", "huber"):
+        for where in ("value", "old", "target"):
+            old = torch.randn(T, generator=g)
+            val = old + 0.4 * torch.randn(T, generator=g)
+            tgt = old + torch.randn(T, generator=g)
+            mask = torch.rand(T, generator=g) > 0.3
+            mask[[5, 50]] = True
+            {"value": val, "old": old, "target": tgt}[where][[5, 50]] = nan
+            val.requires_grad_()
+            loss, st = af.ppo_critic_loss_fn(val, old, tgt, 0.5, loss_mask=mask, loss_fn_type=loss_type)
+            (grad,) = torch.autograd.grad(loss, val)
+            p = f"v{k}_"
+            z.update({p + "value": val.detach().numpy(), p + "old": old.numpy(), p + "target": tgt.numpy(),
+                      p + "mask": mask.numpy(), p + "huber": np.array(loss_type == "huber"),
+                      p + "loss": loss.detach().numpy(), p + "grad": grad.numpy(),
+                      p + "stat_clip_mask": st["clip_mask"].numpy(), p + "stat_loss": st["loss"].numpy()})
+            k += 1
+    z["n_critic"] = np.array(k)
+    # compute_advantages: a NaN behaviour / reference log-prob through the clamped KL estimator, a NaN score
+    # through the reward clip (grid cases 0: k1, 1: k2, 2: k3 with scaling + clip)
+    fn, KLEstimator, Normalization, NormConfig = R.load_areal_compute_advantages()
+    for ci in (0, 1, 2):
+        c = adv_case_grid()[ci]
+        d = adv_case_inputs(50 + ci)
+        d["logprobs"][4, 6] = nan
+        d["ref_logp"][6, 3] = nan
+        d["rewards"][8] = nan
+        d["loss_mask"][4, 5:8] = 1
+        d["loss_mask"][6, 2:5] = 1
+        d["attention_mask"][4, :9] = True
+        d["attention_mask"][6, :6] = True
+        if not c["with_values"]:
+            d.pop("values")
+        for kk, v in d.items():
+            z[f"c{ci}_in_{kk}"] = v.numpy().copy()
+        cfg = types.SimpleNamespace(**{kk: c[kk] for kk in ("use_decoupled_loss", "recompute_logprob", "overlong_reward_penalty",
+                                                            "overlong_tokens", "overlong_penalty_factor", "max_new_tokens")})
+        actor = types.SimpleNamespace(
+            config=cfg, reward_bias=c["reward_bias"], reward_scaling=c["reward_scaling"], reward_clip=c["reward_clip"],
+            kl_ctl=c["kl_ctl"], kl_estimator=KLEstimator(c["kl_estimator"]), discount=c["discount"],
+            gae_lambda=c["gae_lambda"], mask_no_eos_with_zero=c["mask_no_eos_with_zero"], adv_norm=None, reward_norm=None)
+        with torch.no_grad():
+            fn(actor, d)
+        for kk in ("advantages", "returns", "kl_rewards", "tot_rewards", "loss_mask", "logprobs", "ref_logp"):
+            if kk in d:
+                z[f"c{ci}_out_{kk}"] = d[kk].numpy().copy()
+    z["n_adv"] = np.array(3)
+    np.savez_compressed(os.path.join(OUT, "nan_cases.npz"), **z)
+    print("nan cases: actor", int(z["n_actor"]), "critic", int(z["n_critic"]), "advantages 3")
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     assert R.available(), "needs /root/reference"
@@ -734,6 +822,13 @@ def main():
     pf = R.load_realhf_ppo_functional()
     af = R.load_areal_functional()
     fp = R.load_realhf_flatten_param()
+    if len(sys.argv) > 2 and sys.argv[1] == "--only":       # regenerate one fixture: --only nan_cases
+        fn = globals()["gen_" + sys.argv[2]]
+        args = {"nan_cases": (af,), "gae1d": (pf,), "logprobs": (af,), "actor_loss": (af, pf), "critic_loss": (af, pf),
+                "intervals": (fp,), "normalization": (af,), "dynamic_sampling": (af,), "packed_rewards": (pf,),
+                "lm_head": (af,)}.get(sys.argv[2], ())
+        fn(*args)
+        return
     gen_gae1d(pf)
     gen_gae_padded()
     gen_logprobs(af)
@@ -754,6 +849,7 @@ def main():
     gen_critic_stats()
     gen_sft_stats()
     gen_lm_head(af)
+    gen_nan_cases(af)
 
 
 if __name__ == "__main__":

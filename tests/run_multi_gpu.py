@@ -200,6 +200,9 @@ def main():
     assert torch.equal(st["logprobs"], take(st_full["logprobs"]))
     a, r = P.cugae1d_nolp_misalign_func(take(rewards), take(values, 1), my_cu, boot[torch.tensor(mine, device=dev)], 0.99, 0.95)
     assert torch.equal(a, take(a_full)) and torch.equal(r, take(r_full))
+    # ---------------- stats export over the NCCL group with scalar keys only (after a reset) -------------
+    from tests.run_tracker_nccl import check_scalar_only_export
+    check_scalar_only_export(dist.group.WORLD)
     dist.barrier()
     torch.cuda.synchronize()
     if rank == 0:

@@ -235,3 +235,49 @@ def test_single_pass_peaked_rows_keep_relative_accuracy_at_the_label():
     rs = np.abs(ref).max(-1, keepdims=True)
     assert np.all(np.abs(got - ref) <= 2 ** -8 * np.abs(ref) + 0.05 * np.abs(r_lab)[:, None] * (np.arange(V)[None, :] == lab[:, None])
                   + H.TOL_LOGITS * 1e-3 * rs + 1e-30)
+
+
+def test_single_pass_request_falls_back_where_it_does_not_apply():
+    """loss_scale given, but the rows cannot stay on chip (fp16 / fp32 logits, rows that are not 16-byte
+    aligned): the same results come from the two-pass entries instead of an 'unsupported' error."""
+    from areal_b200 import functional as F
+    g = torch.Generator().manual_seed(5)
+    T, V = 40, 4104
+    base = torch.randn(T, V, generator=g) * 2
+    labels = torch.randint(0, V - 8, (T,), generator=g).to(D)
+    old = -torch.rand(T, generator=g).to(D) * 6
+    adv = torch.randn(T, generator=g).to(D)
+    mask = (torch.rand(T, generator=g) > 0.3).to(D)
+    for make in (lambda: base.half().to(D), lambda: base.to(D), lambda: base.bfloat16().to(D)[:, 1:V - 7]):
+        a = make().detach().requires_grad_()
+        b = make().detach().requires_grad_()
+        la, sa = F.fused_actor_loss(a, labels, 1.0, None, old, adv, mask, eps_clip=0.2, loss_scale=0.5)
+        lb, sb = F.fused_actor_loss(b, labels, 1.0, None, old, adv, mask, eps_clip=0.2)
+        (la * 0.5).backward()
+        (lb * 0.5).backward()
+        assert torch.equal(la, lb) and torch.equal(sa["logprobs"], sb["logprobs"])
+        assert torch.equal(a.grad, b.grad)
+
+
+def test_single_pass_gradient_is_handed_out_once_and_bad_cluster_is_rejected():
+    from areal_b200 import functional as F
+    from areal_b200._lib import ArealB200Error
+    g = torch.Generator().manual_seed(6)
+    T, V = 16, 4096
+    x = (torch.randn(T, V, generator=g) * 2).bfloat16().to(D).requires_grad_()
+    labels = torch.randint(0, V, (T,), generator=g).to(D)
+    old = -torch.rand(T, generator=g).to(D) * 6
+    adv = torch.randn(T, generator=g).to(D)
+    mask = torch.ones(T, dtype=torch.bool, device=D)
+    loss, _ = F.fused_actor_loss(x, labels, 1.0, None, old, adv, mask, eps_clip=0.2, loss_scale=0.5)
+    (loss * 0.5).backward(retain_graph=True)
+    first = x.grad.clone()
+    x.grad += 1.0                                    # the caller owns the buffer now
+    with pytest.raises(RuntimeError, match="handed"):
+        (loss * 0.5).backward()
+    assert torch.equal(x.grad, first + 1.0)
+    # a forced cluster that would leave a CTA without any part of the row: an argument error, not a hang
+    tiny = (torch.randn(4, 32, generator=g)).bfloat16().to(D).requires_grad_()      # 4 vectors per row
+    with pytest.raises(ArealB200Error, match="cluster_size"):
+        F.fused_actor_loss(tiny, labels[:4] % 32, 1.0, None, old[:4], adv[:4], mask[:4], eps_clip=0.2, loss_scale=0.5,
+                           cluster_size=8)

@@ -30,6 +30,17 @@ def test_single_rank_vocab_parallel_equals_unsharded():
     assert torch.allclose(a.grad.float(), b.grad.float(), rtol=2 ** -7, atol=1e-9)
 
 
+def test_tracker_scalar_only_export_over_nccl_world1():
+    """export_all(reduce_group=NCCL group) with only SCALAR keys recorded after a reset (the reference's
+    example loop): the scalar table must be reduced on the GPU.  One rank, one GPU; the same check runs
+    inside tests/run_multi_gpu.py at world 2/4/8."""
+    r = subprocess.run([sys.executable, os.path.join(H.ROOT, "tests", "run_tracker_nccl.py")], capture_output=True,
+                       text=True, timeout=300, env=dict(os.environ, MASTER_PORT="29541", RANK="0", WORLD_SIZE="1",
+                                                        LOCAL_RANK="0"))
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
+    assert "TRACKER_NCCL_OK 1" in r.stdout
+
+
 @pytest.mark.parametrize("world", [2, 4, 8])
 def test_nccl_sharded_paths(world):
     if torch.cuda.device_count() < world:
@@ -78,3 +89,18 @@ def test_vocab_sharded_kernels_vs_reference_golden():
             want = H.bf16_from_bits(c[f"grad{r}_bits"]).double().numpy()
             # both are bf16 roundings of the same gradient (the reference's with its fp32 cancellation at the label)
             assert np.all(np.abs(got - want) <= 2 ** -6 * np.abs(want) + slack + 1e-30), (k, r)
+
+
+def test_vocab_parallel_backward_keeps_the_input_shape():
+    """A [B, S, V/R] shard (more than two dimensions) gets a gradient of its own shape."""
+    from areal_b200 import dist as D
+    g = torch.Generator().manual_seed(2)
+    x = (torch.randn(3, 7, 4096, generator=g) * 2).bfloat16().to("cuda:0").requires_grad_()
+    labels = torch.randint(0, 4096, (3, 7), generator=g).to("cuda:0")
+    lp, ent = D.vocab_parallel_logprobs_entropy(x, labels, 1.0)
+    (lp.sum() + ent.sum()).backward()
+    assert x.grad.shape == x.shape
+    y = x.detach().reshape(21, 4096).clone().requires_grad_()
+    lp2, ent2 = D.vocab_parallel_logprobs_entropy(y, labels.reshape(-1), 1.0)
+    (lp2.sum() + ent2.sum()).backward()
+    assert torch.equal(x.grad.reshape(21, 4096), y.grad)
