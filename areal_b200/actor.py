@@ -128,10 +128,16 @@ def grpo_loss_fn(logits: torch.Tensor, input_data: Dict, temperature: float, eps
     tracker's running totals (`stats_tracker.record`).
 
     `tracker`: an `areal_b200.stats_tracker.DistributedStatsTracker` (default: its DEFAULT_TRACKER).
-    `loss_scale`: see fused_actor_loss (single-pass forward+backward when the caller's scale is known)."""
+    `loss_scale`: see fused_actor_loss (single-pass forward+backward when the caller's scale is known).
+    When it is None, the scale announced by `areal_b200.engine_hooks.install_loss_scale_hook` for the
+    `train_batch` call in progress is used, if any -- that is how the unmodified engine reaches the
+    single pass."""
     from . import functional as F
     from . import stats_tracker as ST
+    from .engine_hooks import announced_loss_scale
     tracker = ST.DEFAULT_TRACKER if tracker is None else tracker
+    if loss_scale is None:
+        loss_scale = announced_loss_scale()
     labels = input_data.get("rolled_input_ids", None)
     if labels is None:
         labels = torch.roll(input_data["input_ids"], shifts=-1, dims=-1)

@@ -460,3 +460,41 @@ def load_vocab_parallel(tp_group, tp_rank: int, tp_world: int):
                 sys.modules[k] = v
     ent_mod._restore_compile = lambda: setattr(torch, "compile", real_compile)
     return ent_mod._VocabParallelEntropy, ce_mod.vocab_parallel_cross_entropy, ent_mod._restore_compile
+
+
+def load_fsdp_train_batch():
+    """`FSDPEngine.train_batch` (areal/engine/fsdp_engine.py:498-606) as a plain function `train_batch(self,
+    input_, loss_fn, loss_weight_fn)`: the method's source is cut out of the reference file by its AST node
+    and compiled where it lies (the module itself needs peft / torchdata / megatron to import).  The
+    globals it touches are the real `torch` / `dist` / `math`; the gradient-norm helper is replaced by
+    torch's own clip_grad_norm_ and the Ulysses helpers are never reached with sp_size == 1."""
+    import ast
+    import math
+    from typing import Any, Callable, Dict, List, Optional, Tuple
+
+    import torch
+    import torch.distributed as dist
+    path = os.path.join(REF_ROOT, "areal/engine/fsdp_engine.py")
+    src = open(path).read()
+    tree = ast.parse(src)
+    node = None
+    for cls in tree.body:
+        if isinstance(cls, ast.ClassDef) and cls.name == "FSDPEngine":
+            for fn in cls.body:
+                if isinstance(fn, ast.FunctionDef) and fn.name == "train_batch":
+                    node = fn
+    assert node is not None, "FSDPEngine.train_batch not found"
+    node.decorator_list = []
+    mod = ast.Module(body=[node], type_ignores=[])
+    ast.fix_missing_locations(mod)
+
+    def fsdp2_clip_grad_norm(params, mesh, max_norm):
+        return float(torch.nn.utils.clip_grad_norm_([p for p in params if p.grad is not None] or params, max_norm))
+
+    def unreachable(*a, **k):
+        raise AssertionError("Ulysses helper reached with sp_size == 1")
+    g = dict(torch=torch, dist=dist, math=math, Any=Any, Callable=Callable, Dict=Dict, List=List, Optional=Optional,
+             Tuple=Tuple, fsdp2_clip_grad_norm=fsdp2_clip_grad_norm, set_ulysses_sequence_parallel_group=unreachable,
+             ulysses_pad=unreachable, ulysses_pad_and_slice_inputs=unreachable, ulysses_prepare_inputs=unreachable)
+    exec(compile(mod, path, "exec"), g)
+    return g["train_batch"]
