@@ -51,7 +51,9 @@ def step(logits, labels, temperature, prox, old, adv, mask, cfg, gae_inputs=None
     gae_out = None
     if gae_inputs is not None:
         r, v, cu, boot, gamma, lam = gae_inputs
-        gae_out = O.gae1d_nolp_misalign(r, v, cu, boot, gamma, lam)
+        # the reference's own loop of 0-dim torch ops (not the numpy restatement, which is faster)
+        gae_out = gae1d_torch_loop(torch.as_tensor(r), torch.as_tensor(v).clone(), torch.as_tensor(cu),
+                                   torch.as_tensor(np.asarray(boot, dtype=np.float32)), gamma, lam)
     x = logits.detach().requires_grad_()
     lp, ent = logp_entropy_torch(x, labels, temperature)
     loss = actor_loss_torch(lp, prox, old, adv, cfg["eps_clip"], mask, cfg.get("eps_clip_higher"),
@@ -94,3 +96,115 @@ def time_steps(sample_rows: int, V: int, steps: int, warmup: int, cfg, temperatu
         step(logits, labels, temperature, prox, old, adv, mask, cfg, gae_inputs)
     dt = (time.perf_counter() - t0) / max(steps, 1)
     return dt, torch.get_num_threads()
+
+
+# --------------------------------------------------------------------------------------------------
+# BASELINE.json configs[0]: the reference's CPU GAE exactly as it executes -- a Python double loop
+# with one 0-dim torch op per token and per term (realhf/impl/model/utils/ppo_functional.py:292-323)
+# --------------------------------------------------------------------------------------------------
+def gae1d_torch_loop(rewards: torch.Tensor, values: torch.Tensor, cu_seqlens_: torch.Tensor, bootstrap: torch.Tensor,
+                     gamma: float, lam: float):
+    """Same tensor operations, in the same order, as `pygae1d_nolp_misalign` -- including the in-place
+    `nextvalues *= bootstrap[i]` that writes through a view into `values` (:313-315); pass a clone when the
+    caller's tensor must survive."""
+    cu = cu_seqlens_.clone()
+    cu[1:] += torch.ones_like(cu_seqlens_[1:]).cumsum(0)                       # :300-301
+    bs = cu_seqlens_.shape[0] - 1
+    assert values.shape[0] == rewards.shape[0] + bs                            # :304
+    adv_rev, ret_rev = [], []
+    for i in reversed(range(bs)):                                              # :307
+        v_off = cu[i]
+        r_off, r_end = cu_seqlens_[i], cu_seqlens_[i + 1]
+        assert cu[i + 1] - v_off - 1 == r_end - r_off                          # :310
+        last = 0
+        for t in reversed(range(r_end - r_off)):                               # :312
+            nv = values[v_off + t + 1]
+            if t == r_end - r_off - 1:
+                nv *= bootstrap[i]                                             # :314-315 (in place, through the view)
+            delta = rewards[r_off + t] + gamma * nv - values[v_off + t]        # :316
+            last = delta + gamma * lam * last                                  # :317
+            adv_rev.append(last)
+            ret_rev.append(last + values[v_off + t])                           # :319
+    return torch.stack(adv_rev[::-1]), torch.stack(ret_rev[::-1])              # :321-322
+
+
+def cfg0_batch(seed: int = 0, n_seqs: int = 64, lo: int = 128, hi: int = 4096):
+    """BASELINE.json configs[0]: 64 sequences of U[128, 4096] tokens, bootstrap mixed."""
+    rng = np.random.RandomState(seed)
+    lens = rng.randint(lo, hi + 1, n_seqs)
+    cu = np.concatenate([[0], np.cumsum(lens)]).astype(np.int32)
+    T = int(cu[-1])
+    return (torch.from_numpy(rng.randn(T).astype(np.float32)), torch.from_numpy(rng.randn(T + n_seqs).astype(np.float32)),
+            torch.from_numpy(cu), torch.from_numpy((rng.rand(n_seqs) > 0.5).astype(np.float32)))
+
+
+def time_gae_cfg0(seed: int = 0, n_seqs: int = 64, gamma: float = 1.0, lam: float = 0.95, max_seconds: float = 30.0):
+    """Times the loop above on configs[0] (single Python thread, as the reference runs it).  The batch is cut
+    to whole sequences that fit `max_seconds` at the rate of the first sequence, so that the call is
+    bounded on a slow host; returns (tokens, seconds, n_seqs_timed)."""
+    torch.set_num_threads(1)
+    r, v, cu, boot = cfg0_batch(seed, n_seqs)
+    # rate probe on the first sequence
+    n0 = int(cu[1])
+    t0 = time.perf_counter()
+    gae1d_torch_loop(r[:n0], v[:n0 + 1].clone(), cu[:2], boot[:1], gamma, lam)
+    rate = n0 / max(time.perf_counter() - t0, 1e-9)
+    budget = int(rate * max_seconds)
+    k = int(np.searchsorted(cu.numpy()[1:], budget, side="right"))
+    k = max(1, min(k, n_seqs))
+    T = int(cu[k])
+    t0 = time.perf_counter()
+    gae1d_torch_loop(r[:T], v[:T + k].clone(), cu[:k + 1], boot[:k], gamma, lam)
+    return T, time.perf_counter() - t0, k
+
+
+# --------------------------------------------------------------------------------------------------
+# interval ops on the CPU: `_slice_intervals_py` / `_set_intervals_py`
+# (realhf/impl/model/nn/flatten_param.py:65-90), the path the reference takes without its extension
+# --------------------------------------------------------------------------------------------------
+def slice_intervals_torch(src: torch.Tensor, intervals):
+    assert len(src.shape) == 1                                                 # :67
+    assert all([x[0] >= 0 for x in intervals])
+    assert all([x[1] <= src.shape[0] for x in intervals])
+    slices = []
+    for i, j in intervals:                                                     # :72-73
+        slices.append(src[i:j])
+    return torch.cat(slices, dim=0)                                            # :74
+
+
+def set_intervals_torch(src: torch.Tensor, dst: torch.Tensor, intervals):
+    assert len(dst.shape) == len(src.shape) == 1                               # :83
+    offset = 0
+    for i, j in intervals:                                                     # :85-89
+        assert i >= 0
+        assert j <= dst.shape[0], (j, dst.shape[0])
+        dst[i:j] = src[offset: offset + j - i]
+        offset += j - i
+    assert offset == src.shape[0]                                              # :90
+
+
+def time_intervals_cpu(n_elems: int = 100_000_000, n_intervals: int = 10_000, seed: int = 0, iters: int = 3,
+                       threads: Optional[int] = None):
+    """The reference test's pattern (realhf/tests/cpp_extensions/test_interval_ops.py:20-31: interval i =
+    (i*s, i*s + s//2), shuffled) on a bf16 buffer of `n_elems`; returns (bytes moved per op, seconds per
+    slice, seconds per set, threads)."""
+    if threads:
+        torch.set_num_threads(threads)
+    rng = np.random.RandomState(seed)
+    s = n_elems // n_intervals
+    iv = np.stack([np.arange(n_intervals, dtype=np.int64) * s, np.arange(n_intervals, dtype=np.int64) * s + s // 2], 1)
+    rng.shuffle(iv)
+    ivl = [(int(a), int(b)) for a, b in iv]
+    src = torch.empty(n_elems, dtype=torch.bfloat16)
+    src.view(torch.int16).random_(-30000, 30000)
+    packed = slice_intervals_torch(src, ivl)
+    t0 = time.perf_counter()
+    for _ in range(iters):
+        packed = slice_intervals_torch(src, ivl)
+    t_slice = (time.perf_counter() - t0) / iters
+    t0 = time.perf_counter()
+    for _ in range(iters):
+        set_intervals_torch(packed, src, ivl)
+    t_set = (time.perf_counter() - t0) / iters
+    nbytes = 2 * 2 * n_intervals * (s // 2)
+    return nbytes, t_slice, t_set, torch.get_num_threads()

@@ -194,6 +194,36 @@ def test_cpu_baseline_port_matches_golden():
         assert abs(float(loss) - float(c["loss"])) <= 1e-6 * max(1.0, abs(float(c["loss"]))), k
 
 
+def test_cpu_baseline_gae_loop_and_interval_ports_match_golden():
+    """The two timed CPU legs BASELINE.md section 5 names -- pygae1d_nolp_misalign's per-token torch loop and
+    `_slice_intervals_py` / `_set_intervals_py` -- as restated in oracle/cpu_baseline.py, against the
+    reference's own outputs: bit for bit."""
+    import torch
+    from oracle import cpu_baseline as CB
+    z = H.load("gae1d.npz")
+    n = 0
+    for k, c in H.cases(z):
+        if c["rewards"].size > 3000:           # the loop runs at ~10 k tokens/s: keep the CPU suite short
+            continue
+        g, l = c["gl"]
+        a, r = CB.gae1d_torch_loop(torch.from_numpy(c["rewards"]), torch.from_numpy(c["values"]).clone(),
+                                   torch.from_numpy(c["cu"]), torch.from_numpy(c["boot"].astype(np.float32)),
+                                   float(g), float(l))
+        assert np.array_equal(a.numpy(), c["adv"]) and np.array_equal(r.numpy(), c["ret"]), k
+        n += 1
+    assert n >= 10
+    z = H.load("intervals.npz")
+    for k, c in H.cases(z):
+        iv = [(int(a), int(b)) for a, b in c["intervals"]]
+        src = torch.from_numpy(c["src"].view(np.int16) if c["src"].dtype == np.uint16 else c["src"])
+        got = CB.slice_intervals_torch(src, iv).numpy()
+        assert np.array_equal(got.view(c["packed"].dtype), c["packed"]), k
+        d = torch.from_numpy((c["dst"].view(np.int16) if c["dst"].dtype == np.uint16 else c["dst"]).copy())
+        nv = torch.from_numpy(c["newvals"].view(np.int16) if c["newvals"].dtype == np.uint16 else c["newvals"])
+        CB.set_intervals_torch(nv, d, iv)
+        assert np.array_equal(d.numpy().view(c["dst_after"].dtype), c["dst_after"]), k
+
+
 def test_legacy_packed_vs_reference():
     """realhf spelling of P2 (gather_packed_shifted_log_probs, build_*_indices, calc_entropy)."""
     z = H.load("legacy_packed.npz")
