@@ -33,6 +33,8 @@ SIGNATURES = {
     "areal_b200_vocab_combine_p2p": (c_int, [P, c_int, c_int, I64, I64, I64, F64, I64, P, P, P, P, P, P]),
     "areal_b200_clamped_entropy_fwd": (c_int, [P, c_int, I64, I64, I64, P, F64, I64, P, P, P, P]),
     "areal_b200_clamped_entropy_bwd": (c_int, [P, c_int, I64, I64, I64, P, F64, P, P, P, P, I64, P]),
+    "areal_b200_lm_head_workspace_bytes": (I64, [I64, I64]),
+    "areal_b200_lm_head_logprobs": (c_int, [P, P, P, I64, I64, I64, I64, I64, F64, P, P, P, P, P, P, I64, P]),
     "areal_b200_rms_update": (c_int, [P, I64, P, c_int, c_int, F64, P]),
     "areal_b200_rms_apply": (c_int, [P, I64, P, c_int, c_int, F64, c_int, P, P]),
     "areal_b200_packed_rewards": (c_int, [P, P, P, P, P, I64, I64, F64, F64, c_int, c_int, P, P, P]),

@@ -10,7 +10,7 @@ CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libareal_b200.so")
 OBJ = os.path.join(HERE, "csrc", "_obj")
 SOURCES = ["c_api.cu", "logits_fused.cu", "logits_rowres.cu", "gae_scan.cu", "interval_copy.cu", "ppo_loss.cu", "masked_norm.cu",
-           "masked_stats.cu", "clamped_entropy.cu"]
+           "masked_stats.cu", "clamped_entropy.cu", "lm_head_tc.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
          "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden", "--expt-relaxed-constexpr"]

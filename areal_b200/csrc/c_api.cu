@@ -12,6 +12,7 @@
 #include "masked_norm.h"
 #include "masked_stats.h"
 #include "clamped_entropy.h"
+#include "lm_head_tc.h"
 #include "ppo_loss.h"
 
 namespace ab {
@@ -738,6 +739,23 @@ AREAL_B200_API int areal_b200_clamped_entropy_fwd(const void* logits, int dtype,
   p.entropy = entropy;
   p.saved = saved;
   return launch_clamped_entropy_fwd(p, static_cast<cudaStream_t>(stream));
+}
+
+AREAL_B200_API int64_t areal_b200_lm_head_workspace_bytes(int64_t T, int64_t V) {
+  return lm_head_tc_workspace_bytes(T, V);
+}
+
+AREAL_B200_API int areal_b200_lm_head_logprobs(const void* hidden, const void* weight, const int64_t* labels,
+                                               int64_t T, int64_t H, int64_t V, int64_t hidden_row_stride,
+                                               int64_t weight_row_stride, double temperature, float* logp,
+                                               float* entropy, float* row_max, float* ln_sumexp, float* raw_min,
+                                               void* workspace, int64_t workspace_bytes, void* stream) {
+  AB_REQUIRE(T >= 0 && H > 0 && V > 0, "lm_head: T=%lld H=%lld V=%lld", (long long)T, (long long)H, (long long)V);
+  AB_REQUIRE(temperature > 0.0, "temperature must be positive");
+  AB_REQUIRE(T == 0 || (hidden && weight && labels && logp && row_max && ln_sumexp), "lm_head: null pointer");
+  return launch_lm_head_tc(hidden, weight, labels, T, H, V, hidden_row_stride, weight_row_stride,
+                           static_cast<float>(1.0 / temperature), logp, entropy, row_max, ln_sumexp, raw_min, workspace,
+                           workspace_bytes, static_cast<cudaStream_t>(stream));
 }
 
 AREAL_B200_API int areal_b200_clamped_entropy_bwd(const void* logits, int dtype, int64_t T, int64_t V,

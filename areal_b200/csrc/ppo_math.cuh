@@ -33,21 +33,25 @@ __device__ __forceinline__ ActorTokenOut actor_token(float lp, float prox, float
   ActorTokenOut o;
   const float denorm = c.decoupled ? prox : old;
   o.kl = lp - denorm;
-  o.ratio = mask ? expf(o.kl) : 0.0f;                         // :191
+  const float e = expf(o.kl);
+  o.ratio = mask ? e : 0.0f;                                  // :191
   const float clipped = clamp_nan(o.ratio, c.lo, c.hi);        // :193-197 (torch.clamp: NaN stays NaN)
   const float l1 = -A * o.ratio;                              // :199
   const float l2 = -A * clipped;                              // :200
   o.clip = (l1 < l2) && mask;                                 // :201, :222
   float pg = max_nan(l1, l2);                                 // :202 (torch.max propagates NaN)
-  const float w1 = l1 > l2 ? 1.0f : (l1 == l2 ? 0.5f : 0.0f);
-  const bool inside = (o.ratio >= c.lo) && (o.ratio <= c.hi);
-  float dpg = -A * (w1 + (inside ? (1.0f - w1) : 0.0f));
+  // backward of torch.max(a, b): each side gets grad, halved on a tie, zeroed only where it is strictly the
+  // smaller one -- so with a NaN operand (every comparison false) BOTH sides get the full gradient
+  const float w1 = l1 < l2 ? 0.0f : (l1 == l2 ? 0.5f : 1.0f);
+  const float w2 = l1 > l2 ? 0.0f : (l1 == l2 ? 0.5f : 1.0f);
+  const bool inside = (o.ratio >= c.lo) && (o.ratio <= c.hi);   // clamp passes the gradient inside [lo, hi] only
+  float dpg = -A * (w1 + (inside ? w2 : 0.0f));
   o.dual = false;
   if (c.has_c) {
     const float sgn = (A > 0.0f) ? 1.0f : ((A < 0.0f) ? -1.0f : 0.0f);
     const float l3 = (sgn * c.c_clip) * A;                    // :205
     o.dual = (l3 < pg) && mask;                               // :206, :223
-    const float wmin = pg < l3 ? 1.0f : (pg == l3 ? 0.5f : 0.0f);
+    const float wmin = pg > l3 ? 0.0f : (pg == l3 ? 0.5f : 1.0f);   // torch.min backward, NaN-aware as above
     pg = min_nan(pg, l3);                                     // :207
     dpg *= wmin;
   }
@@ -64,7 +68,9 @@ __device__ __forceinline__ ActorTokenOut actor_token(float lp, float prox, float
     dpg *= o.w;
   }
   o.pg = pg;
-  o.coef = mask ? dpg * o.ratio : 0.0f;
+  // backward of torch.where(mask, exp(kl), 0): the masked side hands a ZERO gradient to exp, whose own
+  // backward multiplies it by exp(kl) -- 0 for any finite value, NaN for a NaN / infinite one, as autograd gives
+  o.coef = (mask ? dpg : 0.0f) * e;
   return o;
 }
 
@@ -91,8 +97,9 @@ __device__ __forceinline__ float critic_token(float v, float old, float tgt, flo
     }
   }
   const bool inside = (diff >= -eps) && (diff <= eps);
-  const float w1 = lo_ > lc_ ? 1.0f : (lo_ == lc_ ? 0.5f : 0.0f);
-  *g = w1 * dlo + (inside ? (1.0f - w1) * dlc : 0.0f);
+  const float w1 = lo_ < lc_ ? 0.0f : (lo_ == lc_ ? 0.5f : 1.0f);   // torch.max backward (see actor_token)
+  const float w2 = lo_ > lc_ ? 0.0f : (lo_ == lc_ ? 0.5f : 1.0f);
+  *g = w1 * dlo + (inside ? w2 * dlc : 0.0f);
   *clip = lc_ > lo_;                                          // :300
   return max_nan(lo_, lc_);                                   // :297
 }

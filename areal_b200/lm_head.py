@@ -244,3 +244,46 @@ def lm_head_logprobs(hidden: torch.Tensor, weight: torch.Tensor, labels: torch.T
     if with_entropy:
         return logp, torch.cat(ents).view(lead)
     return logp
+
+
+@torch.no_grad()
+def lm_head_logprobs_tc(hidden: torch.Tensor, weight: torch.Tensor, labels: torch.Tensor, temperature: float = 1.0,
+                        with_entropy: bool = False, with_stats: bool = False):
+    """`lm_head_logprobs` as ONE tensor-core kernel (areal_b200_lm_head_logprobs): the projection runs on
+    tcgen05 with the accumulators in tensor memory and the online softmax as its epilogue, so neither the
+    `[T, V]` logits nor a `[chunk_rows, V]` block of them ever exists in memory.  bf16 only (hidden `[T, H]`,
+    weight `[V, H]`, H % 8 == 0).  Returns logp `[T]` f32, (logp, entropy) with `with_entropy=True`, or with
+    `with_stats=True` a dict(logp, entropy, vocab_min_logits, vocab_max_logits, lse) like `functional.logits_stats`."""
+    dev = _lib.require_cuda(hidden, weight, labels)
+    if hidden.dtype != torch.bfloat16 or weight.dtype != torch.bfloat16:
+        raise TypeError("lm_head_logprobs_tc: hidden and weight must be bfloat16")
+    lead = hidden.shape[:-1]
+    if labels.shape != lead:
+        raise RuntimeError(f"labels shape {tuple(labels.shape)} does not match hidden {tuple(hidden.shape)}")
+    H, V = hidden.shape[-1], weight.shape[0]
+    if weight.dim() != 2 or weight.shape[1] != H:
+        raise RuntimeError(f"weight shape {tuple(weight.shape)} does not match hidden size {H}")
+    h = hidden.reshape(-1, H)
+    if h.stride(-1) != 1 or h.stride(0) % 8 != 0 or h.data_ptr() % 16 != 0:
+        h = h.contiguous()
+    w = weight if (weight.stride(1) == 1 and weight.stride(0) % 8 == 0 and weight.data_ptr() % 16 == 0) else weight.contiguous()
+    if H % 8 != 0:
+        raise RuntimeError("lm_head_logprobs_tc: the hidden size must be a multiple of 8")
+    lab = labels.reshape(-1).long().contiguous()
+    T = h.shape[0]
+    f32 = dict(dtype=torch.float32, device=dev)
+    logp, row_max, ln_s = torch.empty(T, **f32), torch.empty(T, **f32), torch.empty(T, **f32)
+    ent = torch.empty(T, **f32) if (with_entropy or with_stats) else None
+    mn = torch.empty(T, **f32) if with_stats else None
+    with torch.cuda.device(dev):
+        nbytes = int(_lib.lib().areal_b200_lm_head_workspace_bytes(T, V))
+        ws = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=dev)
+        _lib.call("areal_b200_lm_head_logprobs", _lib.ptr(h), _lib.ptr(w), _lib.ptr(lab), T, H, V,
+                  h.stride(0) if T > 1 else H, w.stride(0) if V > 1 else H, float(temperature), _lib.ptr(logp), _lib.ptr(ent),
+                  _lib.ptr(row_max), _lib.ptr(ln_s), _lib.ptr(mn), _lib.ptr(ws), ws.numel(), _lib.stream_ptr(dev))
+    if with_stats:
+        return dict(logp=logp.view(lead), entropy=ent.view(lead), lse=(row_max / temperature + ln_s).view(lead),
+                    vocab_min_logits=mn.view(lead), vocab_max_logits=row_max.view(lead))
+    if with_entropy:
+        return logp.view(lead), ent.view(lead)
+    return logp.view(lead)

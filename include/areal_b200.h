@@ -394,6 +394,23 @@ AREAL_B200_API int areal_b200_clamped_entropy_bwd(const void* logits, int dtype,
                                                   const float* g_logp, const float* g_entropy,
                                                   void* dlogits, int64_t d_row_stride, void* stream);
 
+/* LM head + log-prob / entropy WITHOUT the [T,V] logits tensor, forward only: a tcgen05 GEMM (TMA tensor-map
+ * loads, accumulators in tensor memory, cta_group::2 pairs) whose epilogue is the online softmax.  Replaces
+ * `outputs.logits` followed by `gather_logprobs(logits, labels, temperature)` in the actor's compute_logp
+ * hook (areal/engine/ppo/actor.py:52-70; the engine side areal/engine/fsdp_engine.py:764-777) and
+ * `gather_logprobs_entropy` on the same logits (areal/utils/functional.py:84-127).
+ *   hidden bf16[T,H] (last hidden state), weight bf16[V,H] (lm_head.weight), unit stride in H, row strides
+ *   in ELEMENTS (multiples of 8), 16-byte aligned bases; labels i64[T].
+ *   logits = bf16(hidden @ weight^T) as F.linear returns them; z = float(logits)/temperature.
+ *   Outputs f32[T] with the meaning of areal_b200_logits_fwd: logp, row_max, ln_sumexp required; entropy and
+ *   raw_min nullable.  workspace: areal_b200_lm_head_workspace_bytes(T, V) bytes, need not be zeroed. */
+AREAL_B200_API int64_t areal_b200_lm_head_workspace_bytes(int64_t T, int64_t V);
+AREAL_B200_API int areal_b200_lm_head_logprobs(const void* hidden, const void* weight, const int64_t* labels,
+                                               int64_t T, int64_t H, int64_t V, int64_t hidden_row_stride,
+                                               int64_t weight_row_stride, double temperature, float* logp,
+                                               float* entropy, float* row_max, float* ln_sumexp, float* raw_min,
+                                               void* workspace, int64_t workspace_bytes, void* stream);
+
 /* Legacy running value statistics.  Replaces the arithmetic of `ExponentialRunningMeanStd` /
  * `MovingAverageRunningMeanStd` (realhf/impl/model/modules/rms.py:19-183): update = three reductions
  * + ~10 scalar kernels there; here areal_b200_masked_moments (one group) followed by

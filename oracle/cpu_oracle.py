@@ -287,14 +287,16 @@ def ppo_actor_loss(logprobs, proximal_logprobs, old_logprobs, advantages, eps_cl
     pg = np.maximum(l1, l2)                                         # :202
     # d pg / d ratio (torch.max tie -> 1/2 each; clamp passes grad iff lo <= r <= hi)
     inside = (ratio >= lo) & (ratio <= hi)
-    w1 = np.where(l1 > l2, 1.0, np.where(l1 == l2, 0.5, 0.0))
-    w2 = 1.0 - w1
-    dpg = -A * (w1 + w2 * inside)
+    # backward of torch.max(a, b): grad, halved on a tie, zeroed only for the strictly smaller side (so a NaN
+    # operand leaves the full gradient on both sides)
+    w1 = np.where(l1 < l2, 0.0, np.where(l1 == l2, 0.5, 1.0))
+    w2 = np.where(l1 > l2, 0.0, np.where(l1 == l2, 0.5, 1.0))
+    dpg = -A * (w1 + np.where(inside, w2, 0.0))
     if c_clip is not None:
         assert c_clip > 1.0
         l3 = np.sign(A) * dtype(c_clip) * A                         # :205
         dual_mask = l3 < pg                                         # :206
-        wmin = np.where(pg < l3, 1.0, np.where(pg == l3, 0.5, 0.0))
+        wmin = np.where(pg > l3, 0.0, np.where(pg == l3, 0.5, 1.0))
         pg = np.minimum(pg, l3)                                     # :207
         dpg = dpg * wmin
     else:
@@ -313,7 +315,10 @@ def ppo_actor_loss(logprobs, proximal_logprobs, old_logprobs, advantages, eps_cl
                      behave_mask=bmask)
     logging_loss = pg.astype(dtype)
     loss = np.where(mask, pg, dtype(0)).astype(np.float64).sum() / count   # :221
-    grad = np.where(mask, dpg * ratio, 0.0) / count                 # d ratio / d lp = ratio
+    with np.errstate(over="ignore", invalid="ignore"):
+        # torch.where hands the masked side a zero gradient, exp's backward multiplies it by exp(lp - prox):
+        # 0 for finite values, NaN for NaN / inf ones (what autograd returns)
+        grad = np.where(mask, dpg, 0.0) * np.exp(lp - prox) / count
     stats.update(loss=logging_loss, importance_weight=ratio.astype(dtype),
                  approx_kl=(lp - prox).astype(dtype), clip_mask=clip_mask & mask,
                  dual_clip_mask=dual_mask & mask)
@@ -347,8 +352,9 @@ def ppo_critic_loss(value, old_value, target_value, value_eps_clip: float, loss_
     lc_, dlc = f(vc, tgt)
     inside = (diff >= -eps) & (diff <= eps)
     loss_el = np.maximum(lo_, lc_)
-    w1 = np.where(lo_ > lc_, 1.0, np.where(lo_ == lc_, 0.5, 0.0))
-    g_el = w1 * dlo + (1.0 - w1) * dlc * inside
+    w1 = np.where(lo_ < lc_, 0.0, np.where(lo_ == lc_, 0.5, 1.0))
+    w2 = np.where(lo_ > lc_, 0.0, np.where(lo_ == lc_, 0.5, 1.0))
+    g_el = w1 * dlo + np.where(inside, w2 * dlc, 0.0)
     clip_mask = lc_ > lo_
     if loss_mask is not None:
         mask = np.asarray(loss_mask).astype(bool)

@@ -795,6 +795,10 @@ def gen_nan_cases(af):
         d["loss_mask"][6, 2:5] = 1
         d["attention_mask"][4, :9] = True
         d["attention_mask"][6, :6] = True
+        # every planted NaN sits on a token that takes part in the loss (rolled mask 1), the score of row 8
+        # included (it lands on column seqlen - 2): the reference masks by multiplying with 0, which would
+        # spread a NaN from a MASKED token too (NaN * 0), an artefact the kernels do not reproduce
+        d["loss_mask"][8, int(d["attention_mask"][8].sum()) - 1] = 1
         if not c["with_values"]:
             d.pop("values")
         for kk, v in d.items():

@@ -64,6 +64,7 @@ def test_oracle_actor_critic_nan_vs_reference():
             loss, st, grad = O.ppo_actor_loss(c["lp"], c["prox"], c["old"], c["adv"], eps, c["mask"],
                                               eps_clip_higher=eps_hi, c_clip=c_clip, behav_imp_weight_cap=cap)
         same(loss, c["loss"], (k, "loss"))
+        same(grad, c["grad"], (k, "grad"), atol=1e-9)
         for name in F_STATS:
             if "stat_" + name in c:
                 same(st[name], c["stat_" + name], (k, name))
@@ -75,6 +76,7 @@ def test_oracle_actor_critic_nan_vs_reference():
             loss, st, grad = O.ppo_critic_loss(c["value"], c["old"], c["target"], 0.5, c["mask"],
                                                "huber" if bool(c["huber"]) else "mse")
         same(loss, c["loss"], (k, "loss"))
+        same(grad, c["grad"], (k, "grad"), atol=1e-9)
         same(st["loss"], c["stat_loss"], (k, "stat_loss"))
         assert np.array_equal(st["clip_mask"], c["stat_clip_mask"]), k
 
