@@ -92,8 +92,9 @@ __device__ __forceinline__ float critic_token(float v, float old, float tgt, flo
       const float a0 = fabsf(d0), a1 = fabsf(d1);
       lo_ = a0 < delta ? 0.5f * (a0 * a0) : delta * (a0 - 0.5f * delta);   // _huber_loss :238-240
       lc_ = a1 < delta ? 0.5f * (a1 * a1) : delta * (a1 - 0.5f * delta);
-      dlo = a0 < delta ? d0 : copysignf(delta, d0);
-      dlc = a1 < delta ? d1 : copysignf(delta, d1);
+      // sign(NaN) is NaN in autograd's |x| backward: a NaN difference keeps a NaN gradient
+      dlo = a0 < delta ? d0 : (d0 != d0 ? d0 : copysignf(delta, d0));
+      dlc = a1 < delta ? d1 : (d1 != d1 ? d1 : copysignf(delta, d1));
     }
   }
   const bool inside = (diff >= -eps) && (diff <= eps);
