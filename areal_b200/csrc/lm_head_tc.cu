@@ -64,13 +64,11 @@ __device__ __forceinline__ uint32_t mapa(uint32_t saddr, uint32_t rank) {
 __device__ __forceinline__ void cluster_sync_all() {
   asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
-__device__ __forceinline__ void mbar_arrive_expect_tx_cluster(uint32_t cluster_bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.release.cluster.shared::cluster.b64 _, [%0], %1;" ::"r"(cluster_bar),
-               "r"(bytes)
-               : "memory");
-}
+// arrival on a barrier of another CTA of the cluster.  RELAXED: what has to be ordered before it (tcgen05.ld of the
+// accumulator) is ordered by tcgen05.wait::ld + tcgen05.fence::before_thread_sync; a .release.cluster arrive costs a
+// cluster-scope memory barrier (~0.7 us with TMA loads in flight: measured, it serialised the whole pipeline)
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_bar) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_bar) : "memory");
+  asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_bar) : "memory");
 }
 // bounded wait: ~seconds of polling, then trap (a broken pipeline must not hang the GPU)
 __device__ __forceinline__ void mbar_wait_bounded(uint32_t bar, uint32_t parity) {
@@ -194,6 +192,8 @@ struct TcParams {
   int n_chunks;             // R
   float* parts;             // [R][4][T]
   float* part_min;          // [R][T] or null: min of the logits per row and chunk
+  int stages;               // pipeline stages in use (<= Cfg::kStages; profiling knob AREAL_B200_LMHEAD_STAGES)
+  int debug;                // profiling only (AREAL_B200_LMHEAD_DEBUG): 1 = epilogue loads TMEM but does not fold, 2 = no TMEM loads, 3 = no TMA loads, 4 = no MMAs
 };
 
 struct RowState {
@@ -286,7 +286,7 @@ lm_head_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < C::kStages; ++i) {
-      mbar_init(smem_u32(&full_bar[i]), CG);                  // one arrive.expect_tx per producer of the pair
+      mbar_init(smem_u32(&full_bar[i]), 1);                   // the leader's producer: arrive.expect_tx for the pair's bytes
       mbar_init(smem_u32(&empty_bar[i]), 1);                  // one tcgen05.commit
     }
     for (int i = 0; i < 2; ++i) {
@@ -324,12 +324,20 @@ lm_head_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
             const uint32_t sa = smem0 + stage * C::kStageBytes, sb = sa + kATileBytes;
             // the MMA issuer (leader CTA) waits on ITS full barrier for the bytes of both CTAs
             const uint32_t bar = CG == 1 ? smem_u32(&full_bar[stage]) : mapa(smem_u32(&full_bar[stage]), 0);
-            mbar_arrive_expect_tx_cluster(bar, C::kStageBytes);
-            tma_load_2d<CG>(sa, &map_a, kb * kBlockK, m0, bar);
+            // the leader arms ITS barrier for the bytes of both CTAs; the peer's loads complete on it too and the
+            // peer never arrives (it cannot run a phase ahead: its stage is released by the leader's commit)
+            uint32_t tx = C::kStageBytes * CG;
+            if (p.debug == 3) tx = 0;                        // profiling: no loads, the MMAs run on stale shared memory
+            if (p.debug == 5) tx = kATileBytes * CG;         // profiling: A loads only (no MMAs)
+            if (p.debug == 6) tx = C::kBTileBytes * CG;      // profiling: B loads only (no MMAs)
+            if (leader) mbar_arrive_expect_tx(smem_u32(&full_bar[stage]), tx);
+            if (p.debug != 3 && p.debug != 6) tma_load_2d<CG>(sa, &map_a, kb * kBlockK, m0, bar);
+            if (p.debug != 3 && p.debug != 5) {
 #pragma unroll
-            for (int r = 0; r < C::kBRows; r += 128)
-              tma_load_2d<CG>(sb + r * (kBlockK * 2), &map_b, kb * kBlockK, n0 + r, bar);
-            if (++stage == C::kStages) {
+              for (int r = 0; r < C::kBRows; r += 128)
+                tma_load_2d<CG>(sb + r * (kBlockK * 2), &map_b, kb * kBlockK, n0 + r, bar);
+            }
+            if (++stage == uint32_t(p.stages)) {
               stage = 0;
               phase ^= 1u;
             }
@@ -356,11 +364,13 @@ lm_head_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
             tc_fence_after();
             const uint32_t sa = smem0 + stage * C::kStageBytes, sb = sa + kATileBytes;
             const uint64_t da = smem_desc_sw128(sa), db = smem_desc_sw128(sb);
+            if (p.debug < 4) {                               // (4, 5, 6: profiling, loads only)
 #pragma unroll
-            for (int k = 0; k < kBlockK / kUmmaK; ++k)      // +32 bytes along K inside the swizzle atom: +2 in the address field
-              umma_bf16<CG>(d_tmem, da + uint64_t(k * 2), db + uint64_t(k * 2), idesc, uint32_t(kb | k));
+              for (int k = 0; k < kBlockK / kUmmaK; ++k)    // +32 bytes along K inside the swizzle atom: +2 in the address field
+                umma_bf16<CG>(d_tmem, da + uint64_t(k * 2), db + uint64_t(k * 2), idesc, uint32_t(kb | k));
+            }
             umma_commit<CG>(smem_u32(&empty_bar[stage]));   // the stage may be refilled once these MMAs retire
-            if (++stage == C::kStages) {
+            if (++stage == uint32_t(p.stages)) {
               stage = 0;
               phase ^= 1u;
             }
@@ -391,9 +401,14 @@ lm_head_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
 #pragma unroll 1
         for (int c = 0; c < kBlockN / 32; ++c) {
           if (col_base + c * 32 >= p.V) break;               // warp-uniform: the tile hangs over the vocabulary's end
+          if (p.debug == 2) break;
           uint32_t v[32];
           tmem_ld_x32(taddr + c * 32, v);
           tmem_ld_wait();
+          if (p.debug == 1) {
+            st.S += __uint_as_float(v[0]) + __uint_as_float(v[31]);
+            continue;
+          }
           fold32(st, v, col_base + c * 32, p.V, label, p.c2, want_min);
         }
         tc_fence_before();
@@ -566,6 +581,14 @@ int launch_lm_head_tc(const void* hidden, const void* weight, const int64_t* lab
   p.H = H;
   p.labels = labels;
   p.c2 = inv_temperature * kLog2e;
+  {
+    const char* e = getenv("AREAL_B200_LMHEAD_DEBUG");
+    p.debug = e ? atoi(e) : 0;
+    const char* st = getenv("AREAL_B200_LMHEAD_STAGES");
+    const int max_stages = cg == 1 ? Cfg<1>::kStages : Cfg<2>::kStages;
+    p.stages = st ? atoi(st) : max_stages;
+    if (p.stages < 1 || p.stages > max_stages) p.stages = max_stages;
+  }
   plan(T, V, cg, n_groups, &p.tiles_per_chunk, &p.n_chunks);
   const int64_t need = int64_t(p.n_chunks) * 5 * T * 4;
   if (workspace == nullptr || workspace_bytes < need) {
