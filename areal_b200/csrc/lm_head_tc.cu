@@ -190,6 +190,7 @@ struct TcParams {
   float c2;                 // log2(e) / temperature
   int tiles_per_chunk;      // vocabulary tiles (of 256 columns) per work item
   int n_chunks;             // R
+  int mb_per_group;         // row blocks whose hidden states share L2 at one time (see item_coords)
   float* parts;             // [R][4][T]
   float* part_min;          // [R][T] or null: min of the logits per row and chunk
   int stages;               // pipeline stages in use (<= Cfg::kStages; profiling knob AREAL_B200_LMHEAD_STAGES)
@@ -268,6 +269,18 @@ __device__ __forceinline__ void fold32(RowState& st, const uint32_t* acc, int64_
   }
 }
 
+// Work item -> (row block, vocabulary chunk).  Row blocks are taken in GROUPS small enough for their hidden
+// states to stay in L2 (a group's rows are re-read for every vocabulary tile); inside a group the row block runs
+// fastest, so the CTAs that run at the same time share the weight tiles they stream.
+__device__ __forceinline__ void item_coords(int64_t item, int64_t num_mb, int G, int R, int64_t& mb, int64_t& ch) {
+  const int64_t per_group = int64_t(G) * R;
+  const int64_t g = item / per_group, r = item - g * per_group;
+  const int64_t first = g * G;
+  const int64_t size = num_mb - first < G ? num_mb - first : G;      // the last group may be smaller
+  ch = r / size;
+  mb = first + (r - ch * size);
+}
+
 template <int CG>
 __global__ void __launch_bounds__(kTcThreads, 1)
 lm_head_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, const TcParams p) {
@@ -313,7 +326,8 @@ lm_head_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
     if (lane == 0) {
       uint32_t stage = 0, phase = 0;
       for (int64_t item = group; item < items; item += n_groups) {
-        const int64_t mb = item % num_mb, ch = item / num_mb;
+        int64_t mb, ch;
+        item_coords(item, num_mb, p.mb_per_group, p.n_chunks, mb, ch);
         const int m0 = int(mb * rows_per_item + int64_t(rank) * kBlockM);
         const int64_t nt0 = ch * p.tiles_per_chunk;
         const int64_t nt1 = nt0 + p.tiles_per_chunk < n_tiles ? nt0 + p.tiles_per_chunk : n_tiles;
@@ -351,7 +365,8 @@ lm_head_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
       constexpr uint32_t idesc = make_idesc(kBlockM * CG, kBlockN);
       uint32_t stage = 0, phase = 0, tile = 0;
       for (int64_t item = group; item < items; item += n_groups) {
-        const int64_t ch = item / num_mb;
+        int64_t mb, ch;
+        item_coords(item, num_mb, p.mb_per_group, p.n_chunks, mb, ch);
         const int64_t nt0 = ch * p.tiles_per_chunk;
         const int64_t nt1 = nt0 + p.tiles_per_chunk < n_tiles ? nt0 + p.tiles_per_chunk : n_tiles;
         for (int64_t nt = nt0; nt < nt1; ++nt, ++tile) {
@@ -386,7 +401,8 @@ lm_head_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
     const uint32_t empty_bar0 = CG == 1 ? smem_u32(&tmem_empty_bar[0]) : mapa(smem_u32(&tmem_empty_bar[0]), 0);
     uint32_t tile = 0;
     for (int64_t item = group; item < items; item += n_groups) {
-      const int64_t mb = item % num_mb, ch = item / num_mb;
+      int64_t mb, ch;
+      item_coords(item, num_mb, p.mb_per_group, p.n_chunks, mb, ch);
       const int64_t row = mb * rows_per_item + int64_t(rank) * kBlockM + q * 32 + lane;
       const int64_t label = row < p.T ? p.labels[row] : -1;
       RowState st = {-INFINITY, 0.f, 0.f, 0.f, INFINITY};
@@ -398,18 +414,25 @@ lm_head_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
         tc_fence_after();
         const uint32_t taddr = tmem_base + acc * kBlockN + (uint32_t(q * 32) << 16);
         const int64_t col_base = nt * kBlockN;
+        // 32-column pieces inside the vocabulary (warp-uniform; the last tile may hang over its end)
+        int nchunks = int((p.V - col_base + 31) / 32);
+        if (nchunks > kBlockN / 32) nchunks = kBlockN / 32;
+        if (p.debug == 2) nchunks = 0;
+        // two register buffers: the TMEM load of piece c+1 is in flight while piece c is folded
+        uint32_t va[32], vb[32];
+        if (nchunks > 0) tmem_ld_x32(taddr, va);
 #pragma unroll 1
-        for (int c = 0; c < kBlockN / 32; ++c) {
-          if (col_base + c * 32 >= p.V) break;               // warp-uniform: the tile hangs over the vocabulary's end
-          if (p.debug == 2) break;
-          uint32_t v[32];
-          tmem_ld_x32(taddr + c * 32, v);
+        for (int c = 0; c < nchunks; c += 2) {
           tmem_ld_wait();
-          if (p.debug == 1) {
-            st.S += __uint_as_float(v[0]) + __uint_as_float(v[31]);
-            continue;
+          if (c + 1 < nchunks) tmem_ld_x32(taddr + (c + 1) * 32, vb);
+          if (p.debug == 1) st.S += __uint_as_float(va[0]) + __uint_as_float(va[31]);
+          else fold32(st, va, col_base + c * 32, p.V, label, p.c2, want_min);
+          if (c + 1 < nchunks) {
+            tmem_ld_wait();
+            if (c + 2 < nchunks) tmem_ld_x32(taddr + (c + 2) * 32, va);
+            if (p.debug == 1) st.S += __uint_as_float(vb[0]) + __uint_as_float(vb[31]);
+            else fold32(st, vb, col_base + (c + 1) * 32, p.V, label, p.c2, want_min);
           }
-          fold32(st, v, col_base + c * 32, p.V, label, p.c2, want_min);
         }
         tc_fence_before();
         __syncwarp();
@@ -590,6 +613,17 @@ int launch_lm_head_tc(const void* hidden, const void* weight, const int64_t* lab
     if (p.stages < 1 || p.stages > max_stages) p.stages = max_stages;
   }
   plan(T, V, cg, n_groups, &p.tiles_per_chunk, &p.n_chunks);
+  {
+    // hidden states of one group of row blocks <= ~48 MB (L2 is 126 MB and also holds the weight tiles in flight)
+    const int64_t rows_per_item = int64_t(kBlockM) * cg;
+    const int64_t num_mb = (T + rows_per_item - 1) / rows_per_item;
+    const int64_t a_bytes = T * H * 2;
+    const char* e = getenv("AREAL_B200_LMHEAD_GROUP_MB");
+    const int64_t budget = (e ? atoll(e) : 48) << 20;
+    const int64_t n_mgroups = a_bytes <= budget + (budget >> 2) ? 1 : (a_bytes + budget - 1) / budget;
+    p.mb_per_group = int((num_mb + n_mgroups - 1) / n_mgroups);
+    if (p.mb_per_group < 1) p.mb_per_group = 1;
+  }
   const int64_t need = int64_t(p.n_chunks) * 5 * T * 4;
   if (workspace == nullptr || workspace_bytes < need) {
     set_error("lm_head: workspace too small (%lld < %lld bytes)", (long long)workspace_bytes, (long long)need);

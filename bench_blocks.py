@@ -324,27 +324,39 @@ class Blocks:
 
     def _lm_head_rows(self):
         """Forward-only log-probs from the hidden state (PPOActor.compute_logp's shape, areal/engine/ppo/actor.py:52-70)
-        at T=16384, H=1536, V=151936: the tcgen05 kernel (no [T,V] tensor) against library GEMM + streaming pass."""
+        at T=16384, V=151936 and H=1536 (Qwen2.5-1.5B) / 3584 (7B): the tcgen05 kernel (no [T,V] tensor) against
+        library GEMM + streaming pass.  `frac_of_measured_bf16_peak`: against MEASURED_PEAKS.json bf16_tflops (burst:
+        these kernels are timed alone)."""
+        import json
         torch = self.torch
         from areal_b200 import lm_head as LM
-        T, Hd = 16384, 1536
-        g = torch.Generator(device=self.dev).manual_seed(3)
-        h = torch.randn(T, Hd, generator=g, device=self.dev).bfloat16()
-        w = (torch.randn(V, Hd, generator=g, device=self.dev) * (2.0 / Hd ** 0.5)).bfloat16()
-        lab = torch.randint(0, V, (T,), generator=g, device=self.dev)
-        flops = 2.0 * T * Hd * V
+        try:
+            tpeak = float(json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "MEASURED_PEAKS.json")))["bf16_tflops"])
+            tsrc = "measured (MEASURED_PEAKS.json bf16_tflops, burst)"
+        except Exception:
+            tpeak, tsrc = 1590.0, "fallback (B200_PROFILING.md)"
         rows = []
-        ms = self.time_ms(lambda: LM.lm_head_logprobs(h, w, lab, 1.0, chunk_rows=4096, with_entropy=True), iters=5, warmup=2)
-        rows.append(dict(kernel="lm_head_logprobs: cuBLAS GEMM per 4096-row block + logits_fwd (library + streaming)", ms=ms,
-                         tflops=flops / (ms * 1e-3) / 1e12, tokens_per_s=T / (ms * 1e-3)))
-        if hasattr(LM, "lm_head_logprobs_tc"):
+        for Hd in (1536, 3584):
+            T = 16384
+            g = torch.Generator(device=self.dev).manual_seed(3)
+            h = torch.randn(T, Hd, generator=g, device=self.dev).bfloat16()
+            w = (torch.randn(V, Hd, generator=g, device=self.dev) * (2.0 / Hd ** 0.5)).bfloat16()
+            lab = torch.randint(0, V, (T,), generator=g, device=self.dev)
+            flops = 2.0 * T * Hd * V
+            ms = self.time_ms(lambda: LM.lm_head_logprobs(h, w, lab, 1.0, chunk_rows=4096, with_entropy=True), iters=5, warmup=2)
+            rows.append(dict(kernel="lm_head_logprobs: cuBLAS GEMM per 4096-row block + logits_fwd (library + streaming)", H=Hd,
+                             ms=ms, tflops=flops / (ms * 1e-3) / 1e12, tokens_per_s=T / (ms * 1e-3)))
             ms2 = self.time_ms(lambda: LM.lm_head_logprobs_tc(h, w, lab, 1.0, with_entropy=True), iters=5, warmup=2)
             a = LM.lm_head_logprobs_tc(h, w, lab, 1.0, with_entropy=True)
             b = LM.lm_head_logprobs(h, w, lab, 1.0, chunk_rows=4096, with_entropy=True)
-            rows.append(dict(kernel="lm_head_logprobs_tc: tcgen05 GEMM with the online-softmax epilogue (no [T,V] tensor)", ms=ms2,
-                             tflops=flops / (ms2 * 1e-3) / 1e12, tokens_per_s=T / (ms2 * 1e-3), bound="tensor",
+            tf = flops / (ms2 * 1e-3) / 1e12
+            rows.append(dict(kernel="lm_head_logprobs_tc: tcgen05 GEMM with the online-softmax epilogue (no [T,V] tensor)", H=Hd,
+                             ms=ms2, tflops=tf, tokens_per_s=T / (ms2 * 1e-3), bound="tensor", peak_tflops=tpeak,
+                             peak_source=tsrc, frac_of_measured_bf16_peak=tf / tpeak, speedup_vs_library_path=ms / ms2,
                              max_abs_diff_logp_vs_library_path=float((a[0] - b[0]).abs().max()),
                              max_abs_diff_entropy_vs_library_path=float((a[1] - b[1]).abs().max())))
+            del h, w
+            torch.cuda.empty_cache()
         return rows
 
     # ---- N > 1 -----------------------------------------------------------------------------------------
