@@ -132,15 +132,57 @@ __global__ void gae1d_prep_kernel(const int32_t* __restrict__ cu, int B, int64_t
   desc[t] = d;
 }
 
+// ---- cluster exchange (small batches: one launch, no global descriptors) ---------------------------
+__device__ __forceinline__ uint32_t gae_cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ uint32_t gae_mapa(uint32_t saddr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(rank));
+  return r;
+}
+// 16-byte store into another CTA's shared memory that also counts 16 bytes on that CTA's mbarrier: the
+// receiver sees the data once its barrier phase completes, no fence and no flag
+__device__ __forceinline__ void st_async_affine(uint32_t remote_addr, const double a, const double b, uint32_t remote_bar) {
+  asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v2.b64 [%0], {%1, %2}, [%3];" ::"r"(remote_addr),
+               "l"(__double_as_longlong(a)), "l"(__double_as_longlong(b)), "r"(remote_bar)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait_acq_cluster(uint32_t bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "WAITG_%=:\n\t"
+      "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONEG_%=;\n\t"
+      "bra WAITG_%=;\n\t"
+      "DONEG_%=:\n\t"
+      "}" ::"r"(bar),
+      "r"(parity)
+      : "memory");
+}
+constexpr int kGaeClusterMax = 8;
+
 // ---- 1D packed, misaligned values ------------------------------------------------------------------
 // kT threads per CTA: 256 (2048-token tiles, 8 CTAs/SM) or 512 (4096-token tiles, 4 CTAs/SM: half as many
 // look-backs and CTA barriers per token; used for large batches)
-template <int kT>
+// kCluster: the whole batch is ONE thread-block cluster (at most 8 tiles): tile aggregates travel right-to-left
+// through distributed shared memory (st.async + mbarrier complete_tx), every thread finds its sequence by a
+// binary search -- no prep kernel, no global descriptors, one launch.
+template <int kT, bool kCluster = false>
 __global__ void __launch_bounds__(kT, 2048 / kT)
 gae1d_kernel(const Gae1dParams p) {
   constexpr int kThreads = kT, kWarps = kT / 32, kTile = kT * kItems;
   __shared__ Affine wsm[kWarps];
   __shared__ double carry_sm;
+  __shared__ __align__(16) Affine inbox[kCluster ? kGaeClusterMax : 1];   // [sender rank]: maps of the tiles to the right
+  __shared__ __align__(8) uint64_t xbar;
+  // cluster mode: cu_seqlens staged in shared memory by ONE round of parallel loads, so that the per-thread
+  // sequence search costs no chain of dependent global loads (each one a DRAM round trip on a cold batch)
+  constexpr int kCuSm = kCluster ? 2048 : 1;
+  __shared__ int cu_sm[kCuSm + 1];
   // per-token values parked in shared memory ([item][thread]: conflict-free) while the scan runs, so
   // that 8 CTAs fit an SM (32 registers per thread): this kernel lives on memory-level parallelism
   __shared__ float v_sm[kItems][kThreads];
@@ -156,6 +198,16 @@ gae1d_kernel(const Gae1dParams p) {
   // predecessor from being scheduled).
   const int64_t tile = ntiles - 1 - int64_t(blockIdx.x);
   const int64_t tile_start = tile * kTile;
+  if (kCluster) {
+    // rank == blockIdx.x: rank 0 owns the LAST tile and receives nothing; rank r receives r maps
+    if (tid == 0) {
+      mbar_init(smem_u32(&xbar), 1);
+      mbar_fence_init();
+    }
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");   // waited on right before the exchange
+    if (p.B <= kCuSm)
+      for (int i = tid; i <= int(p.B); i += kThreads) cu_sm[i] = __ldg(p.cu + i);
+  }
   const int ntok = static_cast<int>(p.T - tile_start < kTile ? p.T - tile_start : kTile);
   const int B = static_cast<int>(p.B);
 
@@ -179,6 +231,7 @@ gae1d_kernel(const Gae1dParams p) {
   // everything above is independent of the prep kernel; from here on its descriptors are read
   // (no-op unless launched as a programmatic dependent)
   asm volatile("griddepcontrol.wait;" ::: "memory");
+  if (kCluster) __syncthreads();                    // cu_sm is complete
 
   float vcur[kItems], delta[kItems];
   unsigned int last_bits = 0;
@@ -188,7 +241,24 @@ gae1d_kernel(const Gae1dParams p) {
     // few sequence ends that lie before my first token; cu entries are shared by the CTA -> L1 hits
     int seq = 0;
     int64_t end0;
-    if (ntiles > 1) {
+    if (kCluster) {
+      int lo = 0, hi = B - 1;
+      const int64_t j0 = tile_start + p0;
+      if (B <= kCuSm) {
+        while (lo < hi) {
+          const int mid = (lo + hi) >> 1;
+          if (int64_t(cu_sm[mid + 1]) > j0) hi = mid; else lo = mid + 1;
+        }
+        end0 = cu_sm[lo + 1];
+      } else {
+        while (lo < hi) {
+          const int mid = (lo + hi) >> 1;
+          if (int64_t(__ldg(p.cu + mid + 1)) > j0) hi = mid; else lo = mid + 1;
+        }
+        end0 = __ldg(p.cu + lo + 1);
+      }
+      seq = lo;
+    } else if (ntiles > 1) {
       const int2 se = *reinterpret_cast<const int2*>(&desc[tile].seq0);
       seq = se.x;
       end0 = se.y;
@@ -301,7 +371,27 @@ gae1d_kernel(const Gae1dParams p) {
   const Affine excl = (lane < 31) ? compose(nxt, W) : W;
 
   double carry = 0.0;
-  if (ntiles > 1) {
+  if (kCluster) {
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");   // every CTA's barrier is initialised
+    if (ntiles > 1) {
+      if (tid == 0) {
+        const Affine tagg = compose(inc, W);        // thread 0: whole tile
+        const uint32_t me = gae_cluster_ctarank(), n = static_cast<uint32_t>(ntiles);
+        for (uint32_t dst = me + 1; dst < n; ++dst)   // every tile to the left needs this tile's map
+          st_async_affine(gae_mapa(smem_u32(&inbox[me]), dst), tagg.a, tagg.b, gae_mapa(smem_u32(&xbar), dst));
+        if (me > 0) {
+          mbar_arrive_expect_tx(smem_u32(&xbar), 16u * me);
+          mbar_wait_acq_cluster(smem_u32(&xbar), 0);
+          double x = 0.0;                             // A beyond the last token
+          for (uint32_t k = 0; k < me; ++k) x = fma(inbox[k].a, x, inbox[k].b);   // rank 0 is the rightmost tile
+          carry = x;
+        }
+        carry_sm = carry;
+      }
+      __syncthreads();
+      carry = carry_sm;
+    }
+  } else if (ntiles > 1) {
     if (tid == 0) {
       const Affine tagg = compose(inc, W);          // thread 0: whole tile
       TileDesc* me = desc + tile;
@@ -677,6 +767,174 @@ gae_padded_kernel(const GaePaddedParams p, const AdvFusedParams f) {
   }
 }
 
+// ---- padded masked GAE, few LONG rows: one thread-block cluster per row ----------------------------------
+// gae_padded_kernel gives a row to ONE CTA, which leaves most SMs idle for a batch like [16, 32768] (long
+// chains of thought).  Here a row is cut into C <= 8 tiles of 4096 tokens, one CTA each, the C CTAs forming a
+// cluster.  Two things cross tile boundaries, both right-to-left, both through distributed shared memory
+// (st.async + mbarrier complete_tx, no global memory, no flags): the "next valid value" (value of the nearest
+// token with mask != 0 to the right, actor.py:135,142) and the tile's affine map for the advantage recurrence.
+// Same arithmetic as gae_padded_kernel<false, 512>: fp32 deltas in the reference's operation order, fp64 scan.
+__device__ __forceinline__ void st_async_b64(uint32_t remote_addr, unsigned long long v, uint32_t remote_bar) {
+  asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.b64 [%0], %1, [%2];" ::"r"(remote_addr),
+               "l"(v), "r"(remote_bar)
+               : "memory");
+}
+
+__global__ void __launch_bounds__(512, 1)
+gae_padded_cluster_kernel(const GaePaddedParams p, int C) {
+  constexpr int kT = 512, kW = kT / 32, kTileC = kT * kItems;      // 4096 tokens per CTA
+  __shared__ Affine wsm[kW];
+  __shared__ float nv_val[kW];
+  __shared__ int nv_has[kW];
+  __shared__ __align__(16) Affine inbox_map[kGaeClusterMax];         // [sender rank]
+  __shared__ __align__(8) unsigned long long inbox_nv[kGaeClusterMax];   // (has << 32) | value bits
+  __shared__ __align__(8) uint64_t bar_nv, bar_map;
+  __shared__ float nv_carry_sm;
+  __shared__ double a_carry_sm;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const uint32_t rank = gae_cluster_ctarank();                       // rank 0 = RIGHTMOST tile of the row
+  const int64_t row = blockIdx.x / C;
+  const int64_t tile = C - 1 - int64_t(rank);
+  if (tid == 0) {
+    mbar_init(smem_u32(&bar_nv), 1);
+    mbar_init(smem_u32(&bar_map), 1);
+    mbar_fence_init();
+  }
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+
+  const float* r = p.rewards + row * p.S;
+  const float* v = p.values + row * p.S;
+  const float* m = p.mask + row * p.S;
+  float* adv = p.adv + row * p.S;
+  float* ret = p.ret + row * p.S;
+  const int64_t L = p.S - 1;
+  const double gl = double(p.gl);
+  const int64_t t0 = tile * kTileC + int64_t(tid) * kItems;
+  int nvalid = 0;
+  if (t0 < L) nvalid = (L - t0) < kItems ? int(L - t0) : kItems;
+  float rr[kItems], vv[kItems];
+  unsigned int valid_bits = 0;
+  const bool vec = p.vec_ok && nvalid == kItems;
+  if (vec) {
+    float mm[kItems];
+    ld8(r + t0, rr);
+    ld8(v + t0, vv);
+    ld8(m + t0, mm);
+#pragma unroll
+    for (int k = 0; k < kItems; ++k)
+      if (mm[k] != 0.f) valid_bits |= 1u << k;
+  } else {
+#pragma unroll
+    for (int k = 0; k < kItems; ++k) {
+      if (k < nvalid) {
+        rr[k] = __ldg(r + t0 + k);
+        vv[k] = __ldg(v + t0 + k);
+        if (__ldg(m + t0 + k) != 0.f) valid_bits |= 1u << k;
+      }
+    }
+  }
+  const float v_last = v[p.S - 1];
+  if (rank == 0 && tid == 0) {
+    adv[p.S - 1] = 0.f;                                              // actor.py:148
+    ret[p.S - 1] = v_last;                                           // returns = advantages + values, :152
+  }
+  // nearest valid value to the right of this thread, inside the tile
+  const int first = valid_bits ? (__ffs(valid_bits) - 1) : -1;
+  float first_val = 0.f;
+#pragma unroll
+  for (int k = 0; k < kItems; ++k)
+    if (k == first) first_val = vv[k];
+  const unsigned int ball = __ballot_sync(0xffffffffu, first >= 0);
+  const unsigned int right = (lane == 31) ? 0u : (ball >> (lane + 1));
+  const int src = right ? (lane + __ffs(right)) : lane;
+  const float wv = __shfl_sync(0xffffffffu, first_val, src);
+  const float warp_first = __shfl_sync(0xffffffffu, first_val, ball ? (__ffs(ball) - 1) : 0);
+  if (lane == 0) {
+    nv_has[warp] = ball != 0u;
+    nv_val[warp] = warp_first;
+  }
+  __syncthreads();
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");   // every CTA's barriers are initialised
+  // ---- exchange 1: (has a valid token, value of the tile's LEFTMOST valid token) to every tile on the left
+  if (tid == 0) {
+    int has = 0;
+    float val = 0.f;
+    for (int w = kW - 1; w >= 0; --w)
+      if (nv_has[w]) {
+        has = 1;
+        val = nv_val[w];
+      }
+    const unsigned long long msg = (static_cast<unsigned long long>(has) << 32) | __float_as_uint(val);
+    for (uint32_t dst = rank + 1; dst < uint32_t(C); ++dst)
+      st_async_b64(gae_mapa(smem_u32(&inbox_nv[rank]), dst), msg, gae_mapa(smem_u32(&bar_nv), dst));
+    float carry = p.no_eos[row] != 0 ? v_last : 0.f;                 // actor.py:135 (bool * value)
+    if (rank > 0) {
+      mbar_arrive_expect_tx(smem_u32(&bar_nv), 8u * rank);
+      mbar_wait_acq_cluster(smem_u32(&bar_nv), 0);
+      for (uint32_t k = 0; k < rank; ++k)                            // rank k < rank: further right the smaller k
+        if (inbox_nv[k] >> 32) carry = __uint_as_float(static_cast<unsigned int>(inbox_nv[k]));
+    }
+    nv_carry_sm = carry;
+  }
+  __syncthreads();
+  float nv_in;
+  if (right) {
+    nv_in = wv;
+  } else {
+    nv_in = nv_carry_sm;
+    for (int w = kW - 1; w > warp; --w)
+      if (nv_has[w]) nv_in = nv_val[w];
+  }
+  float delta[kItems];
+  Affine agg = ident();
+  {
+    float nv = nv_in;
+#pragma unroll
+    for (int k = kItems - 1; k >= 0; --k) {
+      if (k < nvalid && ((valid_bits >> k) & 1u)) {
+        delta[k] = __fsub_rn(__fadd_rn(rr[k], __fmul_rn(p.g, nv)), vv[k]);   // actor.py:137
+        agg.b = fma(gl, agg.b, double(delta[k]));                             // :138, :143
+        agg.a = gl * agg.a;
+        nv = vv[k];                                                           // :142
+      }
+    }
+  }
+  Affine excl, tagg;
+  block_suffix_scan<kW>(agg, wsm, warp, lane, excl, tagg);
+  // ---- exchange 2: the tile's map to every tile on the left
+  if (tid == 0) {
+    for (uint32_t dst = rank + 1; dst < uint32_t(C); ++dst)
+      st_async_affine(gae_mapa(smem_u32(&inbox_map[rank]), dst), tagg.a, tagg.b, gae_mapa(smem_u32(&bar_map), dst));
+    double x = 0.0;                                                  // adv[:, S-1] = 0
+    if (rank > 0) {
+      mbar_arrive_expect_tx(smem_u32(&bar_map), 16u * rank);
+      mbar_wait_acq_cluster(smem_u32(&bar_map), 0);
+      for (uint32_t k = 0; k < rank; ++k) x = fma(inbox_map[k].a, x, inbox_map[k].b);
+    }
+    a_carry_sm = x;
+  }
+  __syncthreads();
+  double A = fma(excl.a, a_carry_sm, excl.b);
+#pragma unroll
+  for (int k = kItems - 1; k >= 0; --k) {
+    if (k < nvalid) {
+      if ((valid_bits >> k) & 1u) A = fma(gl, A, double(delta[k]));
+      const float af = float(A);
+      if (vec) {
+        rr[k] = af;
+        vv[k] = __fadd_rn(af, vv[k]);
+      } else {
+        adv[t0 + k] = af;
+        ret[t0 + k] = __fadd_rn(af, vv[k]);
+      }
+    }
+  }
+  if (vec) {
+    st8(adv + t0, rr);
+    st8(ret + t0, vv);
+  }
+}
+
 // ---- 2D with a segment table (gae_2d_olp semantics) --------------------------------------------------
 __global__ void __launch_bounds__(kThreads)
 gae2d_olp_kernel(const Gae2dParams p) {
@@ -802,8 +1060,34 @@ static void launch_gae1d_prep(const Gae1dParams& p, int64_t ntiles, TileDesc* de
 
 constexpr int64_t kWideFromTokens = 1 << 20;   // batches of at least this many tokens use 512-thread CTAs
 
+// Batches of up to 8 x 4096 tokens: one cluster launch (no prep kernel, no descriptors, no workspace use).
+static int launch_gae1d_cluster(const Gae1dParams& p, int64_t ntiles, cudaStream_t stream) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(static_cast<unsigned int>(ntiles));
+  cfg.blockDim = dim3(512);
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = static_cast<unsigned int>(ntiles);
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  AB_CUDA(cudaLaunchKernelEx(&cfg, gae1d_kernel<512, true>, p));
+  return kOk;
+}
+
 int launch_gae1d(const Gae1dParams& p, cudaStream_t stream) {
   if (p.T == 0) return kOk;
+  {
+    static const bool use_cluster = [] {
+      const char* e = getenv("AREAL_B200_GAE_CLUSTER");
+      return !(e && e[0] == '0');
+    }();
+    const int64_t nt = (p.T + 4095) / 4096;
+    if (use_cluster && p.T > kTile && nt <= kGaeClusterMax) return launch_gae1d_cluster(p, nt, stream);
+  }
   const bool wide = p.T >= kWideFromTokens;
   const int threads = wide ? 64 : kThreads;
   const int tile_tokens = threads * kItems;
@@ -910,6 +1194,29 @@ int launch_gae_padded(const GaePaddedParams& p_in, cudaStream_t stream) {
   if (p.B == 0 || p.S == 0) return kOk;
   p.vec_ok = p.S % 4 == 0 && aligned16(p.rewards) && aligned16(p.values) && aligned16(p.mask) &&
              aligned16(p.adv) && aligned16(p.ret);
+  {
+    // few long rows: one cluster of C CTAs per row (4096 tokens each) instead of one CTA per row
+    static const bool use_cluster = [] {
+      const char* e = getenv("AREAL_B200_PADDED_CLUSTER");
+      return !(e && e[0] == '0');
+    }();
+    const int64_t C = (p.S - 1 + 4095) / 4096;
+    if (use_cluster && C >= 2 && C <= kGaeClusterMax && p.B * C <= 2 * int64_t(num_sms())) {
+      cudaLaunchConfig_t cfg = {};
+      cfg.gridDim = dim3(static_cast<unsigned int>(p.B * C));
+      cfg.blockDim = dim3(512);
+      cfg.stream = stream;
+      cudaLaunchAttribute attr[1];
+      attr[0].id = cudaLaunchAttributeClusterDimension;
+      attr[0].val.clusterDim.x = static_cast<unsigned int>(C);
+      attr[0].val.clusterDim.y = 1;
+      attr[0].val.clusterDim.z = 1;
+      cfg.attrs = attr;
+      cfg.numAttrs = 1;
+      AB_CUDA(cudaLaunchKernelEx(&cfg, gae_padded_cluster_kernel, p, int(C)));
+      return kOk;
+    }
+  }
   launch_padded_t<false>(p, AdvFusedParams{}, stream);
   return check_launch("gae_padded");
 }

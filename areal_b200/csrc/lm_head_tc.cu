@@ -194,6 +194,7 @@ struct TcParams {
   float* parts;             // [R][4][T]
   float* part_min;          // [R][T] or null: min of the logits per row and chunk
   int stages;               // pipeline stages in use (<= Cfg::kStages; profiling knob AREAL_B200_LMHEAD_STAGES)
+  int want_entropy;         // 0: log-probs only (no W sums)
   int debug;                // profiling only (AREAL_B200_LMHEAD_DEBUG): 1 = epilogue loads TMEM but does not fold, 2 = no TMEM loads, 3 = no TMA loads, 4 = no MMAs
 };
 
@@ -202,6 +203,8 @@ struct RowState {
 };
 
 // fold 32 consecutive columns [col0, col0 + 32) of one row into its online-softmax state
+// kEnt = false: log-probs only (compute_logp's case): the sum W for the entropy is not formed
+template <bool kEnt>
 __device__ __forceinline__ void fold32(RowState& st, const uint32_t* acc, int64_t col0, int64_t V, int64_t label, float c2,
                                        bool want_min) {
   // the reference rounds the projection to bf16 before the softmax (F.linear returns bf16)
@@ -221,7 +224,7 @@ __device__ __forceinline__ void fold32(RowState& st, const uint32_t* acc, int64_
       if (st.m != -INFINITY) {
         const float d = (st.m - cmax) * c2;
         const float f = ex2_approx(d);
-        st.W = f * fmaf(d, st.S, st.W);
+        if (kEnt) st.W = f * fmaf(d, st.S, st.W);
         st.S *= f;
       }
       st.m = cmax;
@@ -234,11 +237,13 @@ __device__ __forceinline__ void fold32(RowState& st, const uint32_t* acc, int64_
       const float e0 = ex2_approx(t0), e1 = ex2_approx(t1);
       s0 += e0;
       s1 += e1;
-      w0 = fmaf(e0, t0, w0);
-      w1 = fmaf(e1, t1, w1);
+      if (kEnt) {
+        w0 = fmaf(e0, t0, w0);
+        w1 = fmaf(e1, t1, w1);
+      }
     }
     st.S += s0 + s1;
-    st.W += w0 + w1;
+    if (kEnt) st.W += w0 + w1;
   } else {
     // the chunk straddles the end of the vocabulary: element-wise, columns >= V left out
     for (int j = 0; j < 32; ++j) {
@@ -249,7 +254,7 @@ __device__ __forceinline__ void fold32(RowState& st, const uint32_t* acc, int64_
           if (st.m != -INFINITY) {
             const float d = (st.m - x) * c2;
             const float f = ex2_approx(d);
-            st.W = f * fmaf(d, st.S, st.W);
+            if (kEnt) st.W = f * fmaf(d, st.S, st.W);
             st.S *= f;
           }
           st.m = x;
@@ -257,7 +262,7 @@ __device__ __forceinline__ void fold32(RowState& st, const uint32_t* acc, int64_
         const float t = (x - st.m) * c2;
         const float e = ex2_approx(t);
         st.S += e;
-        st.W = fmaf(e, t, st.W);
+        if (kEnt) st.W = fmaf(e, t, st.W);
       }
     }
   }
@@ -426,12 +431,14 @@ lm_head_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
           tmem_ld_wait();
           if (c + 1 < nchunks) tmem_ld_x32(taddr + (c + 1) * 32, vb);
           if (p.debug == 1) st.S += __uint_as_float(va[0]) + __uint_as_float(va[31]);
-          else fold32(st, va, col_base + c * 32, p.V, label, p.c2, want_min);
+          else if (p.want_entropy) fold32<true>(st, va, col_base + c * 32, p.V, label, p.c2, want_min);
+          else fold32<false>(st, va, col_base + c * 32, p.V, label, p.c2, want_min);
           if (c + 1 < nchunks) {
             tmem_ld_wait();
             if (c + 2 < nchunks) tmem_ld_x32(taddr + (c + 2) * 32, va);
             if (p.debug == 1) st.S += __uint_as_float(vb[0]) + __uint_as_float(vb[31]);
-            else fold32(st, vb, col_base + (c + 1) * 32, p.V, label, p.c2, want_min);
+            else if (p.want_entropy) fold32<true>(st, vb, col_base + (c + 1) * 32, p.V, label, p.c2, want_min);
+            else fold32<false>(st, vb, col_base + (c + 1) * 32, p.V, label, p.c2, want_min);
           }
         }
         tc_fence_before();
@@ -604,6 +611,7 @@ int launch_lm_head_tc(const void* hidden, const void* weight, const int64_t* lab
   p.H = H;
   p.labels = labels;
   p.c2 = inv_temperature * kLog2e;
+  p.want_entropy = entropy != nullptr;
   {
     const char* e = getenv("AREAL_B200_LMHEAD_DEBUG");
     p.debug = e ? atoi(e) : 0;

@@ -758,6 +758,12 @@ int launch_logits_fwd(const LogitsFwdParams& p, cudaStream_t stream) {
   if (tma_ok(p.logits, p.dtype, p.V, p.row_stride_bytes)) {
     // rows of at most 64 KB (vocabulary shards): half-width CTAs, twice as many of them
     const bool narrow = p.V * (p.dtype == kFP32 ? 4 : 2) <= 65536;
+    // consumer warps of the narrow instance: 4 (8 KB stages), or 2 (4 KB stages, 8 CTAs/SM: a row's ragged last
+    // stage wastes half as much and a thread sees twice as many elements between two row ends)
+    static const int narrow_w = [] {
+      const char* e = getenv("AREAL_B200_FWD_NARROW_W");
+      return (e && e[0] == '2') ? 2 : 4;
+    }();
 #define AB_LAUNCH_FWD_W(MM, E, W)                                                                  \
   {                                                                                                \
     static bool done[kMaxDevices] = {};            /* the attribute is per device */              \
@@ -771,7 +777,9 @@ int launch_logits_fwd(const LogitsFwdParams& p, cudaStream_t stream) {
   }
 #define AB_LAUNCH_FWD(MM, E)                                                       \
   {                                                                                \
-    if (narrow) AB_LAUNCH_FWD_W(MM, E, 4) else AB_LAUNCH_FWD_W(MM, E, 8)           \
+    if (narrow && narrow_w == 2) AB_LAUNCH_FWD_W(MM, E, 2)                         \
+    else if (narrow) AB_LAUNCH_FWD_W(MM, E, 4)                                     \
+    else AB_LAUNCH_FWD_W(MM, E, 8)                                                 \
   }
     if (p.dtype == kBF16) { if (minmax) AB_LAUNCH_FWD(true, ElemBF16) else AB_LAUNCH_FWD(false, ElemBF16) }
     else if (p.dtype == kFP16) { if (minmax) AB_LAUNCH_FWD(true, ElemFP16) else AB_LAUNCH_FWD(false, ElemFP16) }

@@ -211,14 +211,22 @@ def fused_lm_head_actor_loss(hidden: torch.Tensor, weight: torch.Tensor, labels:
 
 @torch.no_grad()
 def lm_head_logprobs(hidden: torch.Tensor, weight: torch.Tensor, labels: torch.Tensor,
-                     temperature: float = 1.0, chunk_rows: int = 4096, with_entropy: bool = False):
+                     temperature: float = 1.0, chunk_rows: int = 4096, with_entropy: bool = False, impl: str = "auto"):
     """Forward-only companion: what `PPOActor.compute_logp`'s post hook computes from the logits
     (`gather_logprobs(logits, labels, temperature)`, areal/engine/ppo/actor.py:57-63; the recompute of
     proximal / reference log-probs runs under no_grad), from the last hidden state, `chunk_rows` tokens
     at a time: one `[chunk_rows, V]` logits buffer instead of `[T, V]`.  Returns logp `[T]` f32, or
-    (logp, entropy) with `with_entropy=True`."""
+    (logp, entropy) with `with_entropy=True`.  `impl`: "auto" takes the tcgen05 kernel (`lm_head_logprobs_tc`)
+    whenever it applies, "library" forces the row-blocked cuBLAS + streaming path, "tcgen05" the kernel."""
     from .functional import _logits_forward
     dev = _lib.require_cuda(hidden, weight, labels)
+    if impl not in ("auto", "library", "tcgen05"):
+        raise ValueError(f"impl must be 'auto', 'library' or 'tcgen05', got {impl!r}")
+    # bf16 with 16-byte aligned rows: ONE tensor-core kernel (tcgen05 GEMM + online-softmax epilogue, no logits
+    # buffer at all); everything else (fp16 / fp32, odd hidden sizes): library GEMM per row block + streaming pass
+    tc_ok = (hidden.dtype == torch.bfloat16 and weight.dtype == torch.bfloat16 and hidden.shape[-1] % 8 == 0)
+    if impl == "tcgen05" or (impl == "auto" and tc_ok):
+        return lm_head_logprobs_tc(hidden, weight, labels, temperature, with_entropy=with_entropy)
     if hidden.dtype != weight.dtype or hidden.dtype not in _lib.DTYPE_CODE:
         raise TypeError("lm_head_logprobs: hidden and weight must share a dtype (bf16, fp16 or fp32)")
     lead = hidden.shape[:-1]

@@ -246,14 +246,23 @@ class Blocks:
         from areal_b200.actor import compute_advantages
         rows = []
         for B, S in ((16, 32768), (512, 4096), (4096, 4096)):
-            r = torch.randn(B, S, device=self.dev)
-            v = torch.randn(B, S, device=self.dev)
-            m = (torch.rand(B, S, device=self.dev) > 0.2).float()
-            ne = torch.rand(B, device=self.dev) > 0.5
-            ring = 20 * B * S < (256 << 20)
-            ms = self._ring_time(lambda: P.gae_padded_masked(r, v, m, ne, 1.0, 0.95), 20 * B * S)
-            rows.append(dict(kernel="gae_padded_masked", B=B, S=S, tokens_per_s=B * S / (ms * 1e-3), l2_flushed=ring,
-                             **self.frac(20.0 * B * S, ms)))
+            nbytes = 20 * B * S
+            n_sets = int(min(64, max(1, math.ceil((300 << 20) / nbytes))))
+            sets = [(torch.randn(B, S, device=self.dev), torch.randn(B, S, device=self.dev),
+                     (torch.rand(B, S, device=self.dev) > 0.2).float(), torch.rand(B, device=self.dev) > 0.5)
+                    for _ in range(n_sets)]
+
+            def sweep():
+                for r, v, m, ne in sets:
+                    P.gae_padded_masked(r, v, m, ne, 1.0, 0.95)
+            ms_eager = self.time_ms(sweep, iters=5, warmup=2) / n_sets
+            ms_gpu = self._graph_time(sweep) / n_sets
+            rows.append(dict(kernel="gae_padded_masked", B=B, S=S, input_sets_in_ring=n_sets,
+                             l2="ring of input sets larger than L2 in total",
+                             eager_us_per_call=ms_eager * 1e3, gpu_us_per_call=ms_gpu * 1e3,
+                             tokens_per_s=B * S / (ms_gpu * 1e-3), **self.frac(20.0 * B * S, ms_gpu)))
+            del sets
+            torch.cuda.empty_cache()
         B, S = 2048, 8192
         lens = torch.randint(2, S + 1, (B,), device=self.dev)
         am = torch.arange(S, device=self.dev)[None, :] < lens[:, None]
@@ -302,6 +311,22 @@ class Blocks:
         rows += self._lm_head_rows()
         return {"rows": rows}
 
+    def _graph_time(self, fn, iters=5):
+        """ms per replay of `fn` captured once in a CUDA graph: GPU time without the wrappers' host time"""
+        torch = self.torch
+        side = torch.cuda.Stream(self.dev)
+        side.wait_stream(torch.cuda.current_stream(self.dev))
+        with torch.cuda.stream(side):
+            fn()
+        torch.cuda.current_stream(self.dev).wait_stream(side)
+        torch.cuda.synchronize(self.dev)
+        gr = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(gr):
+            fn()
+        ms = self.time_ms(gr.replay, iters=iters, warmup=2)
+        del gr
+        return ms
+
     def _ring_time(self, fn, nbytes):
         """time one small call with the L2 flushed (a 256 MB write) before each timed call"""
         torch = self.torch
@@ -343,12 +368,12 @@ class Blocks:
             w = (torch.randn(V, Hd, generator=g, device=self.dev) * (2.0 / Hd ** 0.5)).bfloat16()
             lab = torch.randint(0, V, (T,), generator=g, device=self.dev)
             flops = 2.0 * T * Hd * V
-            ms = self.time_ms(lambda: LM.lm_head_logprobs(h, w, lab, 1.0, chunk_rows=4096, with_entropy=True), iters=5, warmup=2)
+            ms = self.time_ms(lambda: LM.lm_head_logprobs(h, w, lab, 1.0, chunk_rows=4096, with_entropy=True, impl="library"), iters=5, warmup=2)
             rows.append(dict(kernel="lm_head_logprobs: cuBLAS GEMM per 4096-row block + logits_fwd (library + streaming)", H=Hd,
                              ms=ms, tflops=flops / (ms * 1e-3) / 1e12, tokens_per_s=T / (ms * 1e-3)))
             ms2 = self.time_ms(lambda: LM.lm_head_logprobs_tc(h, w, lab, 1.0, with_entropy=True), iters=5, warmup=2)
             a = LM.lm_head_logprobs_tc(h, w, lab, 1.0, with_entropy=True)
-            b = LM.lm_head_logprobs(h, w, lab, 1.0, chunk_rows=4096, with_entropy=True)
+            b = LM.lm_head_logprobs(h, w, lab, 1.0, chunk_rows=4096, with_entropy=True, impl="library")
             tf = flops / (ms2 * 1e-3) / 1e12
             rows.append(dict(kernel="lm_head_logprobs_tc: tcgen05 GEMM with the online-softmax epilogue (no [T,V] tensor)", H=Hd,
                              ms=ms2, tflops=tf, tokens_per_s=T / (ms2 * 1e-3), bound="tensor", peak_tflops=tpeak,

@@ -231,7 +231,10 @@ def test_gae_padded_golden():
         assert np.array_equal(adv[:, -1], np.zeros(adv.shape[0], np.float32))
 
 
-@pytest.mark.parametrize("B,S", [(1, 1), (2, 2), (37, 5000), (300, 2049)])
+@pytest.mark.parametrize("B,S", [(1, 1), (2, 2), (37, 5000), (300, 2049),
+                                 # few long rows: one cluster of up to 8 CTAs per row (4096 tokens each); unaligned S;
+                                 # the longest row a cluster takes; beyond it (one CTA per row again)
+                                 (16, 32768), (5, 20001), (3, 32769), (2, 40000), (9, 4098)])
 def test_gae_padded_vs_oracle(B, S):
     rng = np.random.RandomState(B * 7 + S)
     r = rng.randn(B, S).astype(np.float32)

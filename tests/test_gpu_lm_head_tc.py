@@ -79,7 +79,9 @@ def test_random_inputs_vs_library_path():
     w = (torch.randn(V, Hd, generator=g) * (2.0 / Hd ** 0.5)).bfloat16().to(D)
     lab = torch.randint(0, V, (T,), generator=g).to(D)
     a_lp, a_h = lm_head_logprobs_tc(h, w, lab, 1.0, with_entropy=True)
-    b_lp, b_h = lm_head_logprobs(h, w, lab, 1.0, chunk_rows=512, with_entropy=True)
+    b_lp, b_h = lm_head_logprobs(h, w, lab, 1.0, chunk_rows=512, with_entropy=True, impl="library")
+    c_lp, c_h = lm_head_logprobs(h, w, lab, 1.0, with_entropy=True)           # "auto" takes the tensor-core kernel
+    assert torch.equal(c_lp, a_lp) and torch.equal(c_h, a_h)
     x_lab = (h.float() @ w.float().t()).gather(1, lab[:, None])[:, 0]
     tol = 2.0 ** -7 * x_lab.abs() + 2e-3            # the two GEMMs may round a logit to neighbouring bf16 values
     assert bool(((a_lp - b_lp).abs() <= tol).all()), float((a_lp - b_lp).abs().max())
