@@ -183,6 +183,7 @@ clamped_entropy_fwd_kernel(const ClampedParams p) {
   const float inv_t = p.inv_temperature;
   const float c2 = inv_t * kLog2e;
   for (int64_t row = blockIdx.x; row < p.T; row += gridDim.x) {
+    if (p.only_flagged && p.saved[row * kSaved + 7] == 0.f) continue;    // done by the one-pass kernel
     const uint16_t* x = reinterpret_cast<const uint16_t*>(reinterpret_cast<const char*>(p.logits) + row * p.row_stride_bytes);
     // ---- pass 1: row max + histogram of the high key byte ----
     clear_hist(reinterpret_cast<uint32_t*>(hist), tid);
@@ -333,17 +334,348 @@ clamped_entropy_bwd_kernel(const ClampedParams p, const float* __restrict__ g_lo
   }
 }
 
+// ---- one-pass forward (16-byte aligned rows) -------------------------------------------------------------
+// The three-pass kernel above reads a row three times and bumps a 128 KB private histogram per element.  Here
+// the row is read ONCE:
+//   1. 2,048 elements sampled evenly over the row (256 vectors) give, by a two-level select on the SAMPLE, two
+//      keys that bracket the k-th smallest logit with ~4.6 sigma to spare (sample ranks r +- 96);
+//   2. one pass over the row accumulates the full softmax sums online, the sums and the count of everything
+//      BELOW the bracket (all of it removed), and an exact histogram of the 16-bit keys INSIDE the bracket
+//      (a few thousand elements, spread over up to 1,024 bins: hardly any shared-memory conflicts);
+//   3. the threshold key, the tie count and the removed sums inside the bracket follow from that histogram
+//      (all elements of one bin have the same value), and S_kept = S_all - S_removed.
+// Counts are exact, so (tau, tie weight) are the three-pass kernel's.  A row whose bracket misses the threshold
+// (the sample was not representative) or spans more than 1,024 keys is flagged in saved[row][7] and redone by
+// the three-pass kernel, launched right after with only_flagged = 1.
+constexpr int kF1Threads = 256;
+constexpr int kF1Warps = kF1Threads / 32;
+constexpr int kSampleVecs = 256;      // sampled 16-byte vectors per row (8 elements each)
+constexpr int kBracket = 96;          // half width of the bracket in sample ranks (sigma of the rank is ~21)
+constexpr int kWinMax = 1024;         // 16-bit keys a bracket may span
+
+__device__ __forceinline__ uint32_t key_to_bits(uint32_t key) {
+  return (key & 0x8000u) ? (key & 0x7fffu) : (~key & 0xffffu);
+}
+
+// warp 0: lane l owns bins 8l .. 8l+7 of a 256-bin histogram; bin holding 0-based `rank` -> bcast[0], elements below -> bcast[1]
+__device__ __forceinline__ void find_bin256(const int* hist, int rank, int* bcast, int lane) {
+  int c[8], mine = 0;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    c[j] = hist[lane * 8 + j];
+    mine += c[j];
+  }
+  int incl = mine;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const int o = __shfl_up_sync(0xffffffffu, incl, d);
+    if (lane >= d) incl += o;
+  }
+  int acc = incl - mine;
+  if (rank >= acc && rank < incl) {
+    int b = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      if (b == j && acc + c[j] <= rank) {
+        acc += c[j];
+        b = j + 1;
+      }
+    }
+    bcast[0] = lane * 8 + (b > 7 ? 7 : b);
+    bcast[1] = acc;
+  }
+}
+
+// key of the sample element with 0-based rank `rank` (two-level select over samp[2048]); all 256 threads call it
+__device__ __forceinline__ uint32_t sample_select(const uint16_t* samp, int* hist, int* bcast, int tid, int rank) {
+  hist[tid] = 0;
+  __syncthreads();
+#pragma unroll
+  for (int j = 0; j < 8; ++j) atomicAdd(&hist[samp[tid * 8 + j] >> 8], 1);
+  __syncthreads();
+  if (tid < 32) find_bin256(hist, rank, bcast, tid);
+  __syncthreads();
+  const int hb = bcast[0], below = bcast[1];
+  __syncthreads();
+  hist[tid] = 0;
+  __syncthreads();
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const uint32_t key = samp[tid * 8 + j];
+    if (int(key >> 8) == hb) atomicAdd(&hist[key & 0xffu], 1);
+  }
+  __syncthreads();
+  if (tid < 32) find_bin256(hist, rank - below, bcast, tid);
+  __syncthreads();
+  const uint32_t key = (uint32_t(hb) << 8) | uint32_t(bcast[0]);
+  __syncthreads();
+  return key;
+}
+
+__device__ __forceinline__ int block_sum_int(int v, int* red_i, int warp, int lane) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  if (lane == 0) red_i[warp] = v;
+  __syncthreads();
+  int r = 0;
+  for (int w = 0; w < kF1Warps; ++w) r += red_i[w];
+  __syncthreads();
+  return r;
+}
+
+template <bool kIsBF16, bool kClamp>        // kClamp = (k > 0): without it the pass is a plain online softmax
+__global__ void __launch_bounds__(kF1Threads, 4)
+clamped_entropy_fwd1_kernel(const ClampedParams p) {
+  __shared__ __align__(16) uint16_t samp[kSampleVecs * 8];
+  __shared__ int hist[256];
+  __shared__ int win[kWinMax];
+  __shared__ int bcast[4];
+  __shared__ float red[kF1Warps];
+  __shared__ int red_i[kF1Warps];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const float inv_t = p.inv_temperature;
+  const float c2 = inv_t * kLog2e;
+  const int64_t nv = p.V >> 3;
+  // 32-bit shared address of the window, produced by volatile asm so that it is computed ONCE (the compiler
+  // otherwise rebuilds it -- four uniform instructions -- in front of every atomic)
+  uint32_t win_base;
+  asm volatile("{\n\t.reg .u64 t;\n\tcvta.to.shared.u64 t, %1;\n\tcvt.u32.u64 %0, t;\n\t}" : "=r"(win_base) : "l"(win));
+  for (int64_t row = blockIdx.x; row < p.T; row += gridDim.x) {
+    const uint16_t* x = reinterpret_cast<const uint16_t*>(reinterpret_cast<const char*>(p.logits) + row * p.row_stride_bytes);
+    const uint4* rv = reinterpret_cast<const uint4*>(x);
+    float* sv = p.saved + row * kSaved;
+    // ---- 1. bracket from a sample ----
+    uint32_t key_lo = 0, key_hi = 0xffffu;
+    bool slow = false;
+    if (kClamp) {
+      {
+        const uint4 q = __ldg(rv + (int64_t(tid) * nv) / kSampleVecs);
+        const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          samp[tid * 8 + 2 * j] = static_cast<uint16_t>(key16(w[j] & 0xffffu));
+          samp[tid * 8 + 2 * j + 1] = static_cast<uint16_t>(key16(w[j] >> 16));
+        }
+      }
+      __syncthreads();
+      const int n_s = kSampleVecs * 8;
+      const int r_s = static_cast<int>(((p.k - 1) * int64_t(n_s)) / p.V);
+      if (r_s - kBracket >= 0) key_lo = sample_select(samp, hist, bcast, tid, r_s - kBracket);
+      if (r_s + kBracket < n_s) key_hi = sample_select(samp, hist, bcast, tid, r_s + kBracket);
+      slow = key_hi - key_lo >= uint32_t(kWinMax);
+      for (int i = tid; i < kWinMax; i += kF1Threads) win[i] = 0;
+      __syncthreads();
+    }
+    if (slow) {                                      // uniform: the bracket is too wide for the window
+      if (tid == 0) sv[7] = 1.f;
+      continue;
+    }
+    const uint32_t span = key_hi - key_lo;           // window = keys key_lo .. key_hi
+    // ---- 2. the one pass over the row ----
+    float m_t = -INFINITY, s_all = 0.f, w_all = 0.f, s_bel = 0.f, w_bel = 0.f;
+    int cnt_bel = 0;
+    uint32_t kmin = 0xffffu;
+    constexpr int kU = 4;
+    for (int64_t v0 = tid; v0 < nv; v0 += kU * kF1Threads) {
+      uint4 q[kU];
+#pragma unroll
+      for (int u = 0; u < kU; ++u)
+        if (v0 + u * kF1Threads < nv) q[u] = __ldg(rv + v0 + u * kF1Threads);
+#pragma unroll
+      for (int u = 0; u < kU; ++u) {
+        if (v0 + u * kF1Threads < nv) {
+          const uint32_t w[4] = {q[u].x, q[u].y, q[u].z, q[u].w};
+          float xv[8];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            xv[2 * j] = half_to_f32<kIsBF16>(w[j] & 0xffffu);
+            xv[2 * j + 1] = half_to_f32<kIsBF16>(w[j] >> 16);
+          }
+          float vmax = fmaxf(fmaxf(fmaxf(xv[0], xv[1]), fmaxf(xv[2], xv[3])), fmaxf(fmaxf(xv[4], xv[5]), fmaxf(xv[6], xv[7])));
+          if (vmax > m_t) {
+            if (m_t != -INFINITY) {
+              const float d = (m_t - vmax) * c2;
+              const float f = ex2_approx(d);
+              w_all = f * fmaf(d, s_all, w_all);
+              s_all *= f;
+              w_bel = f * fmaf(d, s_bel, w_bel);
+              s_bel *= f;
+            }
+            m_t = vmax;
+          }
+          const float nb = -m_t * c2;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const uint32_t key = key16((j & 1) ? (w[j >> 1] >> 16) : (w[j >> 1] & 0xffffu));
+            const float t = fmaf(xv[j], c2, nb);
+            const float e = ex2_approx(t);
+            s_all += e;
+            w_all = fmaf(e, t, w_all);
+            kmin = min(kmin, key);
+            if (kClamp) {
+              const bool bel = key < key_lo;
+              const float eb = bel ? e : 0.f;
+              s_bel += eb;
+              w_bel = fmaf(eb, t, w_bel);
+              cnt_bel += bel ? 1 : 0;
+              // window element: one predicated result-less shared atomic, no branch
+              const uint32_t off = key - key_lo;
+              asm volatile(
+                  "{\n\t"
+                  ".reg .pred q;\n\t"
+                  "setp.le.u32 q, %1, %2;\n\t"
+                  "@q red.shared.add.u32 [%0], 1;\n\t"
+                  "}" ::"r"(win_base + off * 4u),
+                  "r"(off), "r"(span)
+                  : "memory");
+            }
+          }
+        }
+      }
+    }
+    // ---- 3. row maximum, sums rebased to it ----
+    const float m = block_max<kF1Warps>(m_t, red, warp, lane);
+    if (m_t != -INFINITY) {
+      const float d = (m_t - m) * c2;
+      const float f = ex2_approx(d);
+      w_all = f * fmaf(d, s_all, w_all);
+      s_all *= f;
+      w_bel = f * fmaf(d, s_bel, w_bel);
+      s_bel *= f;
+    }
+    const float S = block_sum<kF1Warps>(s_all, red, warp, lane);
+    const float Wa = block_sum<kF1Warps>(w_all, red, warp, lane);
+    float s_rem = block_sum<kF1Warps>(s_bel, red, warp, lane);
+    float w_rem = block_sum<kF1Warps>(w_bel, red, warp, lane);
+    const int below = block_sum_int(cnt_bel, red_i, warp, lane);
+    const uint32_t bmin = key_to_bits(kmin);
+    const float row_min = -block_max<kF1Warps>(-half_to_f32<kIsBF16>(bmin), red, warp, lane);
+    uint32_t tau_key = 0;
+    float f_tie = 1.f;
+    if (kClamp) {
+      // threshold inside the window: thread t owns bins 4t .. 4t+3
+      int c[4], mine = 0;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        c[j] = win[tid * 4 + j];
+        mine += c[j];
+      }
+      int incl = mine;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const int o = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += o;
+      }
+      if (lane == 31) red_i[warp] = incl;
+      __syncthreads();
+      int base = 0, total = 0;
+      for (int w2 = 0; w2 < kF1Warps; ++w2) {
+        if (w2 < warp) base += red_i[w2];
+        total += red_i[w2];
+      }
+      const int excl = base + incl - mine;
+      const int rank_in = static_cast<int>(p.k - 1) - below;
+      if (tid == 0) bcast[2] = (rank_in < 0 || rank_in >= total) ? 1 : 0;
+      if (rank_in >= excl && rank_in < excl + mine) {
+        int acc = excl, b = 0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          if (b == j && acc + c[j] <= rank_in) {
+            acc += c[j];
+            b = j + 1;
+          }
+        }
+        b = b > 3 ? 3 : b;
+        bcast[0] = tid * 4 + b;      // bin of the threshold key
+        bcast[1] = acc;              // window elements below that bin
+      }
+      __syncthreads();
+      const bool miss = bcast[2] != 0;
+      const int jbin = bcast[0], prefix = bcast[1];
+      __syncthreads();
+      if (miss) {                                    // uniform: the sample misled the bracket
+        if (tid == 0) sv[7] = 1.f;
+        continue;
+      }
+      tau_key = key_lo + uint32_t(jbin);
+      const int n_tau = win[jbin];
+      const int removed_at_tau = static_cast<int>(p.k) - (below + prefix);       // 1 .. n_tau
+      f_tie = float(n_tau - removed_at_tau) / float(n_tau);
+      // removed mass inside the window: whole bins below the threshold bin, a share of the threshold bin
+      float sr = 0.f, wr = 0.f;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int bin = tid * 4 + j;
+        if (bin <= jbin && c[j] > 0) {
+          const float xvv = half_to_f32<kIsBF16>(key_to_bits(key_lo + uint32_t(bin)));
+          const float t = (xvv - m) * c2;
+          const float e = ex2_approx(t);
+          const float wgt = bin < jbin ? float(c[j]) : float(removed_at_tau);
+          sr = fmaf(wgt, e, sr);
+          wr = fmaf(wgt * e, t, wr);
+        }
+      }
+      s_rem += block_sum<kF1Warps>(sr, red, warp, lane);
+      w_rem += block_sum<kF1Warps>(wr, red, warp, lane);
+    } else {
+      s_rem = 0.f;
+      w_rem = 0.f;
+    }
+    if (tid == 0) {
+      const int64_t lab = p.labels[row];
+      const bool has_label = lab >= 0 && lab < p.V;
+      const float XL = has_label ? half_to_f32<kIsBF16>(__ldg(x + lab)) : 0.f;
+      const float SK = S - s_rem, WK = Wa - w_rem;
+      const float ln_s = lg2_approx(S) * kLn2;
+      const float ln_sk = lg2_approx(SK) * kLn2;
+      p.logp[row] = has_label ? (XL - m) * inv_t - ln_s : __int_as_float(0x7fc00000);
+      const float h = ln_sk - kLn2 * (WK / SK);
+      p.entropy[row] = h;
+      sv[0] = m;
+      sv[1] = ln_s;
+      sv[2] = ln_sk;
+      sv[3] = h;
+      sv[4] = __uint_as_float(kClamp ? tau_key : 0xffffffffu);
+      sv[5] = f_tie;
+      sv[6] = row_min;
+      sv[7] = 0.f;
+    }
+    __syncthreads();
+  }
+}
+
 bool vec_ok(const void* ptr, int64_t V, int64_t stride_bytes) {
   return (reinterpret_cast<uintptr_t>(ptr) & 15) == 0 && (V % 8) == 0 && (stride_bytes % 16) == 0;
 }
 
 }  // namespace
 
-int launch_clamped_entropy_fwd(const ClampedParams& p, cudaStream_t stream) {
-  if (p.T == 0) return kOk;
-  const bool vec = vec_ok(p.logits, p.V, p.row_stride_bytes);
+int launch_clamped_entropy_fwd(const ClampedParams& p_in, cudaStream_t stream) {
+  if (p_in.T == 0) return kOk;
+  const bool vec = vec_ok(p_in.logits, p_in.V, p_in.row_stride_bytes);
   const int64_t cap = num_sms();
-  const unsigned int grid = static_cast<unsigned int>(p.T < cap ? p.T : cap);
+  const unsigned int grid = static_cast<unsigned int>(p_in.T < cap ? p_in.T : cap);
+  ClampedParams p = p_in;
+  p.only_flagged = 0;
+  static const bool one_pass = [] {
+    const char* e = getenv("AREAL_B200_AENT_ONE_PASS");
+    return !(e && e[0] == '0');
+  }();
+  if (vec && one_pass) {
+    // one read of the row; rows it cannot settle are flagged in saved[row][7] and redone by the three-pass kernel
+    const int64_t cap1 = int64_t(num_sms()) * 4;
+    const unsigned int grid1 = static_cast<unsigned int>(p.T < cap1 ? p.T : cap1);
+    if (p.dtype == kBF16) {
+      if (p.k > 0) clamped_entropy_fwd1_kernel<true, true><<<grid1, kF1Threads, 0, stream>>>(p);
+      else clamped_entropy_fwd1_kernel<true, false><<<grid1, kF1Threads, 0, stream>>>(p);
+    } else {
+      if (p.k > 0) clamped_entropy_fwd1_kernel<false, true><<<grid1, kF1Threads, 0, stream>>>(p);
+      else clamped_entropy_fwd1_kernel<false, false><<<grid1, kF1Threads, 0, stream>>>(p);
+    }
+    const int rc = check_launch("clamped_entropy_fwd1");
+    if (rc) return rc;
+    p.only_flagged = 1;
+  }
 #define AB_CE_FWD(BF, VEC)                                                                                    \
   {                                                                                                           \
     AB_CUDA(cudaFuncSetAttribute(clamped_entropy_fwd_kernel<BF, VEC>, cudaFuncAttributeMaxDynamicSharedMemorySize, \

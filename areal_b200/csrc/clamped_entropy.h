@@ -13,7 +13,8 @@ struct ClampedParams {
   int64_t k;                   // number of smallest logits masked out per row, 0 <= k < V
   float* logp;                 // [T] out
   float* entropy;              // [T] out (clamped)
-  float* saved;                // [T, 6] out (forward) / in (backward)
+  float* saved;                // [T, 8] out (forward) / in (backward)
+  int only_flagged;            // forward, internal: redo only the rows the one-pass kernel flagged in saved[row][7]
 };
 
 int launch_clamped_entropy_fwd(const ClampedParams& p, cudaStream_t stream);

@@ -104,3 +104,31 @@ def test_aent_grpo_loss_fn_and_export_vs_reference(ai):
     for k, ref in zip(keys, z[f"a{ai}_vals"]):
         tol = 2e-3 if any(s in k for s in ("logp", "entropy", "kl", "weight", "loss")) else 2e-6
         assert abs(out[k] - ref) <= tol * max(1.0, abs(ref)), (k, out[k], ref)
+
+
+def test_one_pass_forward_brackets_ties_and_fallbacks():
+    """The one-pass forward brackets the k-th smallest logit from a sample of the row and falls back to the three-pass
+    kernel where that bracket fails.  Rows built to hit every branch: a sample that lies (the sampled vectors hold
+    +40: the bracket misses the threshold), one value repeated over the whole row and over half of it (the threshold
+    sits inside a huge tie class), random bit patterns (the bracket spans far more than 1,024 keys), and plain rows."""
+    from areal_b200 import aent_functional as A
+    g = torch.Generator().manual_seed(11)
+    T, V = 7, 151936
+    x = (torch.randn(T, V, generator=g) * 3).bfloat16()
+    nv = V // 8
+    for t in range(256):                                   # the vectors the kernel samples
+        v = (t * nv) // 256
+        x[0, v * 8:(v + 1) * 8] = 40.0
+    x[1] = 1.5
+    x[2, : V // 2] = -5.0
+    bits = torch.randint(0, 0x7f7f, (V,), generator=g, dtype=torch.int32)           # finite bf16 magnitudes ...
+    sign = torch.randint(0, 2, (V,), generator=g, dtype=torch.int32) << 15
+    x[3] = ((bits | sign).to(torch.int16)).view(torch.bfloat16).float().clamp(-60, 60).bfloat16()   # ... of every exponent
+    x[4, ::3] = 0.0
+    x[4, 1::3] = -0.0
+    labels = torch.randint(0, V, (T,), generator=g)
+    for clamp in (0.3, 0.05, 0.9):
+        lp, ent = A.gather_logprobs_clamped_entropy(x.to(D), labels.to(D), clamp, 1.0)
+        rlp, rent = O.gather_logprobs_clamped_entropy(x.float().numpy(), labels.numpy(), clamp, 1.0)
+        assert H.rel_err(lp.cpu().numpy(), rlp) <= H.TOL_LOGITS, clamp
+        assert H.rel_err(ent.cpu().numpy(), rent) <= H.TOL_LOGITS, (clamp, ent.cpu().numpy(), rent)
