@@ -149,14 +149,13 @@ def grpo_loss_fn(logits: torch.Tensor, input_data: Dict, temperature: float, eps
     if F._tp_group() is not None or F._sp_group() is not None:
         # vocabulary shards (Megatron TP) or token slices (Ulysses): the log-probs cross ranks inside
         # gather_logprobs_entropy, so the loss runs on its result as upstream (:329-347); min / max are of
-        # the local logits, as upstream (:375-376)
-        logprobs, entropy = F.gather_logprobs_entropy(logits, labels, temperature)
+        # the local logits, as upstream (:375-376), and come out of the same pass over them
+        logprobs, entropy, vmin, vmax = F.gather_logprobs_entropy_minmax(logits, labels, temperature)
         loss, stat = F.ppo_actor_loss_fn(logprobs, prox_logp, old_logp, advantages, eps_clip, loss_mask,
                                          eps_clip_higher=eps_clip_higher, c_clip=c_clip,
                                          behav_imp_weight_cap=behav_imp_weight_cap)
         stat = dict(stat, logprobs=logprobs.detach(), entropy=entropy.detach().float(),
-                    vocab_min_logits=logits.detach().min(-1).values.float(),
-                    vocab_max_logits=logits.detach().max(-1).values.float())
+                    vocab_min_logits=vmin, vocab_max_logits=vmax)
     else:
         loss, stat = F.fused_actor_loss(logits, labels, temperature, prox_logp, old_logp, advantages, loss_mask,
                                         eps_clip, eps_clip_higher=eps_clip_higher, c_clip=c_clip,

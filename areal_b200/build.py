@@ -14,6 +14,8 @@ SOURCES = ["c_api.cu", "logits_fused.cu", "logits_rowres.cu", "gae_scan.cu", "in
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
          "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden", "--expt-relaxed-constexpr"]
+if os.environ.get("AREAL_B200_NVTX") == "1":      # NVTX ranges around the C-ABI calls (c_api.cu); link needs libdl only
+    FLAGS += ["-DAREAL_B200_NVTX"]
 
 
 def _deps():
@@ -45,7 +47,7 @@ def build(verbose=False, force=False):
     with cf.ThreadPoolExecutor(max_workers=len(SOURCES)) as ex:
         objs = list(ex.map(lambda s: _compile(s, verbose), SOURCES))
     cmd = [NVCC, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-cudart", "shared", "-Xlinker",
-           "-rpath,/usr/local/cuda/lib64", "-o", OUT, *objs]
+           "-rpath,/usr/local/cuda/lib64", "-o", OUT, *objs, "-ldl"]
     if verbose:
         print(" ".join(cmd), flush=True)
     subprocess.check_call(cmd)

@@ -5,6 +5,21 @@
 #include <string.h>
 
 #include "../../include/areal_b200.h"
+
+// NVTX ranges around every C-ABI call (nsys / ncu launch lists then name the entry point each kernel belongs
+// to).  Compile-time switch: AREAL_B200_NVTX=1 python -m areal_b200.build -f  (header-only NVTX v3, no extra library).
+#ifdef AREAL_B200_NVTX
+#include <nvtx3/nvToolsExt.h>
+namespace {
+struct NvtxScope {
+  explicit NvtxScope(const char* name) { nvtxRangePushA(name); }
+  ~NvtxScope() { nvtxRangePop(); }
+};
+}  // namespace
+#define AB_NVTX_RANGE(name) NvtxScope ab_nvtx_scope_(name)
+#else
+#define AB_NVTX_RANGE(name) do { } while (0)
+#endif
 #include "common.cuh"
 #include "gae_scan.h"
 #include "interval_copy.h"
@@ -95,6 +110,7 @@ AREAL_B200_API int areal_b200_gae1d_nolp_misalign(const float* rewards, const fl
                                    int64_t total_tokens, int64_t batch_size, double gamma,
                                    double lam, float* adv_out, float* ret_out, void* workspace,
                                    int64_t workspace_bytes, void* stream) {
+  AB_NVTX_RANGE("areal_b200_gae1d_nolp_misalign");
   AB_REQUIRE(total_tokens >= 0 && batch_size >= 0, "negative size");
   if (total_tokens == 0) return kOk;
   AB_REQUIRE(batch_size > 0, "total_tokens > 0 needs batch_size > 0");
@@ -130,6 +146,7 @@ AREAL_B200_API int areal_b200_gae1d_nolp_misalign_static(const float* rewards, c
                                                          int64_t total_tokens, int64_t batch_size,
                                                          double gamma, double lam, float* adv_out,
                                                          float* ret_out, void* stream) {
+  AB_NVTX_RANGE("areal_b200_gae1d_nolp_misalign_static");
   AB_REQUIRE(total_tokens >= 0 && batch_size >= 0, "negative size");
   if (total_tokens == 0) return kOk;
   AB_REQUIRE(batch_size > 0, "total_tokens > 0 needs batch_size > 0");
@@ -155,6 +172,7 @@ AREAL_B200_API int areal_b200_gae_padded_masked(const float* rewards, const floa
                                  const float* loss_mask, const uint8_t* seq_no_eos, int64_t B,
                                  int64_t S, double gamma, double lam, float* adv_out,
                                  float* ret_out, void* stream) {
+  AB_NVTX_RANGE("areal_b200_gae_padded_masked");
   AB_REQUIRE(B >= 0 && S >= 0, "negative size");
   if (B == 0 || S == 0) return kOk;
   AB_REQUIRE(rewards && values && loss_mask && seq_no_eos && adv_out && ret_out, "null pointer");
@@ -180,6 +198,7 @@ AREAL_B200_API int areal_b200_advantages_padded(
     int kl_kind, int kl_clamp, int mask_no_eos_with_zero, double gamma, double lam, float* adv_out,
     float* ret_out, float* kl_rewards_out, float* tot_rewards_out, float* loss_mask_out,
     float* old_logp_out, void* stream) {
+  AB_NVTX_RANGE("areal_b200_advantages_padded");
   AB_REQUIRE(B >= 0 && S >= 0, "negative size");
   if (B == 0 || S == 0) return kOk;
   AB_REQUIRE(score && loss_mask && logp && attn_mask && adv_out && ret_out && kl_rewards_out &&
@@ -231,6 +250,7 @@ AREAL_B200_API int areal_b200_gae2d_olp(const float* rewards, const float* value
                          const int32_t* done_y_indices, const int32_t* cu_num_dones,
                          const uint8_t* is_truncate, int64_t B, int64_t H, int64_t num_dones,
                          double gamma, double lam, float* adv_out, float* ret_out, void* stream) {
+  AB_NVTX_RANGE("areal_b200_gae2d_olp");
   AB_REQUIRE(B >= 0 && H >= 0 && num_dones >= 0, "negative size");
   if (B == 0 || H == 0) return kOk;
   AB_REQUIRE(rewards && values && done && cu_num_dones && adv_out && ret_out, "null pointer");
@@ -271,6 +291,7 @@ AREAL_B200_API int areal_b200_logits_fwd(const void* logits, int dtype, int64_t 
                                          double temperature, float* logp, float* entropy,
                                          float* row_max, float* ln_sumexp, float* raw_min,
                                          void* stream) {
+  AB_NVTX_RANGE("areal_b200_logits_fwd");
   int rc = check_logits(logits, dtype, T, V, row_stride, labels, temperature);
   if (rc) return rc;
   AB_REQUIRE(T == 0 || (logp && row_max && ln_sumexp), "logp, row_max and ln_sumexp outputs are required");
@@ -290,6 +311,7 @@ AREAL_B200_API int areal_b200_logits_partial_fwd(const void* logits, int dtype, 
                                                  const int64_t* labels, int64_t vocab_start,
                                                  double temperature, float* parts, float* raw_min,
                                                  void* stream) {
+  AB_NVTX_RANGE("areal_b200_logits_partial_fwd");
   int rc = check_logits(logits, dtype, T, V, row_stride, labels, temperature);
   if (rc) return rc;
   AB_REQUIRE(T == 0 || parts, "parts output is required");
@@ -307,6 +329,7 @@ AREAL_B200_API int areal_b200_logits_partial_fwd(const void* logits, int dtype, 
 AREAL_B200_API int areal_b200_vocab_combine(const float* parts, int64_t R, int64_t T,
                                             double temperature, float* logp, float* entropy,
                                             float* row_max, float* ln_sumexp, void* stream) {
+  AB_NVTX_RANGE("areal_b200_vocab_combine");
   AB_REQUIRE(R > 0 && R <= 4096 && T >= 0, "bad R / T");
   AB_REQUIRE(temperature > 0.0 && isfinite(temperature), "temperature must be finite and > 0");
   AB_REQUIRE(T == 0 || (parts && logp && row_max && ln_sumexp), "null pointer");
@@ -322,6 +345,7 @@ AREAL_B200_API int areal_b200_logits_bwd(const void* logits, int dtype, int64_t 
                                          const float* g_entropy, const float* scale0,
                                          const float* scale1, void* dlogits, int64_t d_row_stride,
                                          void* stream) {
+  AB_NVTX_RANGE("areal_b200_logits_bwd");
   int rc = check_logits(logits, dtype, T, V, row_stride, labels, temperature);
   if (rc) return rc;
   AB_REQUIRE(T == 0 || (row_max && ln_sumexp && dlogits), "row_max, ln_sumexp and dlogits are required");
@@ -353,6 +377,7 @@ AREAL_B200_API int areal_b200_legacy_entropy(const void* logits, int dtype, int6
                                              int64_t row_stride, const float* row_max,
                                              const float* ln_sumexp, double eps, float* entropy_out,
                                              void* stream) {
+  AB_NVTX_RANGE("areal_b200_legacy_entropy");
   AB_REQUIRE(T >= 0 && V > 0, "bad shape T=%lld V=%lld", (long long)T, (long long)V);
   AB_REQUIRE(dtype_size(dtype) != 0, "unsupported dtype %d", dtype);
   AB_REQUIRE(row_stride >= V, "row_stride < V");
@@ -387,6 +412,7 @@ AREAL_B200_API int areal_b200_ppo_actor_loss(const float* logprobs, const float*
                               float* stat_behave_imp_weight, float* stat_behave_approx_kl,
                               uint8_t* stat_behave_mask, void* workspace, int64_t workspace_bytes,
                               void* stream) {
+  AB_NVTX_RANGE("areal_b200_ppo_actor_loss");
   AB_REQUIRE(T >= 0, "negative T");
   AB_REQUIRE(loss_out && inv_count_out, "loss_out / inv_count_out required");
   AB_REQUIRE(T == 0 || (logprobs && old_logprobs && advantages && coef), "null pointer");
@@ -424,6 +450,7 @@ AREAL_B200_API int areal_b200_ppo_critic_loss(const float* value, const float* o
                                float* inv_count_out, float* coef, float* stat_loss,
                                uint8_t* stat_clip_mask, void* workspace, int64_t workspace_bytes,
                                void* stream) {
+  AB_NVTX_RANGE("areal_b200_ppo_critic_loss");
   AB_REQUIRE(T >= 0, "negative T");
   AB_REQUIRE(loss_out && inv_count_out, "loss_out / inv_count_out required");
   AB_REQUIRE(T == 0 || (value && old_value && target_value && coef), "null pointer");
@@ -449,6 +476,7 @@ AREAL_B200_API int areal_b200_ppo_critic_loss(const float* value, const float* o
 
 AREAL_B200_API int areal_b200_scale_by_scalars(const float* coef, const float* scale0, const float* scale1,
                                 int64_t T, float* out, void* stream) {
+  AB_NVTX_RANGE("areal_b200_scale_by_scalars");
   AB_REQUIRE(T >= 0, "negative T");
   AB_REQUIRE(T == 0 || (coef && scale0 && out), "null pointer");
   return launch_scale(coef, scale0, scale1, T, out, static_cast<cudaStream_t>(stream));
@@ -466,6 +494,7 @@ AREAL_B200_API int areal_b200_fused_actor_fwd(const void* logits, int dtype, int
                                uint8_t* stat_dual_clip_mask, float* stat_behave_imp_weight,
                                float* stat_behave_approx_kl, uint8_t* stat_behave_mask,
                                void* workspace, int64_t workspace_bytes, void* stream) {
+  AB_NVTX_RANGE("areal_b200_fused_actor_fwd");
   int rc = check_logits(logits, dtype, T, V, row_stride, labels, temperature);
   if (rc) return rc;
   AB_REQUIRE(T > 0, "fused entry needs T > 0");
@@ -517,6 +546,7 @@ AREAL_B200_API int areal_b200_fused_actor_fwd_bwd(const void* logits, int dtype,
                                const float* loss_scale, void* dlogits, int64_t d_row_stride,
                                int cluster_size, int n_buffers, void* workspace,
                                int64_t workspace_bytes, void* stream) {
+  AB_NVTX_RANGE("areal_b200_fused_actor_fwd_bwd");
   int rc = check_logits(logits, dtype, T, V, row_stride, labels, temperature);
   if (rc) return rc;
   AB_REQUIRE(T > 0, "fused entry needs T > 0");
@@ -559,6 +589,7 @@ AREAL_B200_API int areal_b200_fused_actor_fwd_bwd(const void* logits, int dtype,
 AREAL_B200_API int areal_b200_rescale_grad_if_needed(void* dlogits, int64_t T, int64_t V,
                                                      int64_t d_row_stride, const float* upstream,
                                                      const float* assumed, void* stream) {
+  AB_NVTX_RANGE("areal_b200_rescale_grad_if_needed");
   AB_REQUIRE(T >= 0 && V > 0 && d_row_stride >= V, "bad shape");
   AB_REQUIRE(T == 0 || (dlogits && upstream), "null pointer");
   return launch_rescale_if_needed(dlogits, T, V, d_row_stride * 2, upstream, assumed,
@@ -573,6 +604,7 @@ AREAL_B200_API int64_t areal_b200_norm_num_partials(int64_t group_elems) {
 AREAL_B200_API int areal_b200_masked_moments(const float* x, const float* mask, int64_t n_groups,
                                              int64_t group_elems, int64_t n_partials, double* partials,
                                              void* stream) {
+  AB_NVTX_RANGE("areal_b200_masked_moments");
   AB_REQUIRE(n_groups >= 0 && group_elems >= 0 && n_partials >= 1 && n_partials <= 65535, "bad sizes");
   AB_REQUIRE(n_groups <= 65535, "at most 65535 groups per call");
   if (n_groups == 0 || group_elems == 0) return kOk;
@@ -599,6 +631,7 @@ AREAL_B200_API int areal_b200_norm_centered_sumsq(const float* x, const float* m
                                                   const double* mean_stats, int64_t n_std_groups,
                                                   int64_t std_group_elems, int64_t n_partials,
                                                   double* partials, void* stream) {
+  AB_NVTX_RANGE("areal_b200_norm_centered_sumsq");
   AB_REQUIRE(n_std_groups >= 0 && n_std_groups <= 65535 && std_group_elems >= 0, "bad std grouping");
   AB_REQUIRE(n_partials >= 1 && n_partials <= 65535, "bad n_partials");
   if (n_std_groups == 0 || std_group_elems == 0) return kOk;
@@ -617,6 +650,7 @@ AREAL_B200_API int areal_b200_norm_apply(const float* x, const float* mask, int6
                                          int std_unbiased, int std_one_special, int64_t std_group_elems,
                                          int64_t n_std_groups, const double* std_stats, double eps,
                                          const float* total_mask_sum, float* out, void* stream) {
+  AB_NVTX_RANGE("areal_b200_norm_apply");
   AB_REQUIRE(N >= 0, "negative N");
   if (N == 0) return kOk;
   AB_REQUIRE(x && out, "null pointer");
@@ -640,6 +674,7 @@ AREAL_B200_API int areal_b200_norm_apply(const float* x, const float* mask, int6
 AREAL_B200_API int areal_b200_masked_normalization_apply(const float* x, const float* mask, int64_t N,
                                                          const double* stats, int unbiased, double eps,
                                                          float* out, void* stream) {
+  AB_NVTX_RANGE("areal_b200_masked_normalization_apply");
   AB_REQUIRE(N >= 0, "negative N");
   if (N == 0) return kOk;
   AB_REQUIRE(x && stats && out, "null pointer");
@@ -679,6 +714,7 @@ AREAL_B200_API int areal_b200_slice_intervals(const void* flat, int64_t flat_num
                                int64_t packed_numel, const int64_t* intervals,
                                int64_t n_intervals, int64_t elem_size, void* workspace,
                                int64_t workspace_bytes, void* stream) {
+  AB_NVTX_RANGE("areal_b200_slice_intervals");
   return interval_common(true, flat, nullptr, nullptr, packed, flat_numel, packed_numel, intervals,
                          n_intervals, elem_size, workspace, workspace_bytes, stream);
 }
@@ -687,6 +723,7 @@ AREAL_B200_API int areal_b200_set_intervals(const void* packed, int64_t packed_n
                              int64_t flat_numel, const int64_t* intervals, int64_t n_intervals,
                              int64_t elem_size, void* workspace, int64_t workspace_bytes,
                              void* stream) {
+  AB_NVTX_RANGE("areal_b200_set_intervals");
   return interval_common(false, nullptr, flat, packed, nullptr, flat_numel, packed_numel, intervals,
                          n_intervals, elem_size, workspace, workspace_bytes, stream);
 }
@@ -728,6 +765,7 @@ AREAL_B200_API int areal_b200_clamped_entropy_fwd(const void* logits, int dtype,
                                                   int64_t row_stride, const int64_t* labels,
                                                   double temperature, int64_t k_removed, float* logp,
                                                   float* entropy, float* saved, void* stream) {
+  AB_NVTX_RANGE("areal_b200_clamped_entropy_fwd");
   ClampedParams p;
   const int rc = clamped_params(p, logits, dtype, T, V, row_stride, labels, temperature);
   if (rc) return rc;
@@ -750,6 +788,7 @@ AREAL_B200_API int areal_b200_lm_head_logprobs(const void* hidden, const void* w
                                                int64_t weight_row_stride, double temperature, float* logp,
                                                float* entropy, float* row_max, float* ln_sumexp, float* raw_min,
                                                void* workspace, int64_t workspace_bytes, void* stream) {
+  AB_NVTX_RANGE("areal_b200_lm_head_logprobs");
   AB_REQUIRE(T >= 0 && H > 0 && V > 0, "lm_head: T=%lld H=%lld V=%lld", (long long)T, (long long)H, (long long)V);
   AB_REQUIRE(temperature > 0.0, "temperature must be positive");
   AB_REQUIRE(T == 0 || (hidden && weight && labels && logp && row_max && ln_sumexp), "lm_head: null pointer");
@@ -763,6 +802,7 @@ AREAL_B200_API int areal_b200_clamped_entropy_bwd(const void* logits, int dtype,
                                                   double temperature, const float* saved,
                                                   const float* g_logp, const float* g_entropy,
                                                   void* dlogits, int64_t d_row_stride, void* stream) {
+  AB_NVTX_RANGE("areal_b200_clamped_entropy_bwd");
   ClampedParams p;
   const int rc = clamped_params(p, logits, dtype, T, V, row_stride, labels, temperature);
   if (rc) return rc;
@@ -785,6 +825,7 @@ AREAL_B200_API int areal_b200_vocab_combine_p2p(void* const* peer_bases, int ran
                                                 double temperature, int64_t timeout_cycles, float* logp,
                                                 float* entropy, float* row_max, float* ln_sumexp,
                                                 int* status, void* stream) {
+  AB_NVTX_RANGE("areal_b200_vocab_combine_p2p");
   AB_REQUIRE(world_size >= 1 && world_size <= 16, "vocab_combine_p2p: world size must be 1..16, got %d", world_size);
   AB_REQUIRE(rank >= 0 && rank < world_size, "vocab_combine_p2p: rank %d out of range", rank);
   AB_REQUIRE(T >= 0 && T <= max_tokens, "vocab_combine_p2p: T=%lld exceeds the buffer's %lld tokens",
@@ -802,6 +843,7 @@ AREAL_B200_API int areal_b200_vocab_combine_p2p(void* const* peer_bases, int ran
 
 AREAL_B200_API int areal_b200_rms_update(const double* partials, int64_t n_partials, void* state,
                                          int state_is_f64, int mode, double beta, void* stream) {
+  AB_NVTX_RANGE("areal_b200_rms_update");
   AB_REQUIRE(partials && state, "null pointer");
   AB_REQUIRE(n_partials >= 1, "rms_update: need at least one partial row");
   AB_REQUIRE(mode == 0 || mode == 1, "rms_update: mode must be 0 (exponential) or 1 (moving average)");
@@ -810,6 +852,7 @@ AREAL_B200_API int areal_b200_rms_update(const double* partials, int64_t n_parti
 
 AREAL_B200_API int areal_b200_rms_apply(const float* x, int64_t N, const void* state, int state_is_f64,
                                         int mode, double eps, int denormalize, float* out, void* stream) {
+  AB_NVTX_RANGE("areal_b200_rms_apply");
   AB_REQUIRE(N >= 0, "negative size");
   if (N == 0) return kOk;
   AB_REQUIRE(x && state && out, "null pointer");
@@ -823,6 +866,7 @@ AREAL_B200_API int areal_b200_packed_rewards(const float* log_probs, const float
                                              int64_t batch_size, double kl_ctl, double clip_reward_value,
                                              int mask_no_eos_with_zero, int mode, float* kl_rewards_out,
                                              float* tot_rewards_out, void* stream) {
+  AB_NVTX_RANGE("areal_b200_packed_rewards");
   AB_REQUIRE(total_short_tokens >= 0 && batch_size >= 0, "negative size");
   if (total_short_tokens == 0) return kOk;
   AB_REQUIRE(batch_size > 0, "packed_rewards: tokens without sequences");
@@ -839,6 +883,7 @@ AREAL_B200_API int areal_b200_packed_rewards(const float* log_probs, const float
 AREAL_B200_API int areal_b200_segment_masked_mean(const float* v, const uint8_t* mask,
                                                   const int32_t* cu_seqlens, int64_t batch_size,
                                                   double* mean, uint8_t* valid, void* stream) {
+  AB_NVTX_RANGE("areal_b200_segment_masked_mean");
   AB_REQUIRE(batch_size >= 0, "negative size");
   if (batch_size == 0) return kOk;
   AB_REQUIRE(v && cu_seqlens && mean && valid, "null pointer");
@@ -854,6 +899,7 @@ AREAL_B200_API int areal_b200_masked_stats(const float* const* values, const uin
                                            double* const* outs, uint32_t value_is_u8_bits,
                                            int64_t n_keys, int64_t n, int accumulate, void* workspace,
                                            int64_t workspace_bytes, void* stream) {
+  AB_NVTX_RANGE("areal_b200_masked_stats");
   AB_REQUIRE(n_keys >= 0 && n >= 0, "negative size");
   if (n_keys == 0) return kOk;
   AB_REQUIRE(n_keys <= kMaxStatKeys, "masked_stats: at most %d keys per call, got %lld", kMaxStatKeys,

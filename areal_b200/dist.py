@@ -94,13 +94,15 @@ def gather_partials(parts: torch.Tensor, group=None) -> torch.Tensor:
     return out.view((world,) + tuple(parts.shape))
 
 
-def _cuda_partials(shard: torch.Tensor, labels: torch.Tensor, vocab_start: int, temperature: float) -> torch.Tensor:
+def _cuda_partials(shard: torch.Tensor, labels: torch.Tensor, vocab_start: int, temperature: float,
+                   raw_min: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """`raw_min` (f32 [T], optional): filled with the minimum of the shard's raw logits per row, out of the same pass."""
     T, V = shard.shape
     dev = shard.device
     parts = torch.empty(4, T, dtype=torch.float32, device=dev)
     with torch.cuda.device(dev):
         call("areal_b200_logits_partial_fwd", ptr(shard), _lib.DTYPE_CODE[shard.dtype], T, V,
-             shard.stride(0) if T > 1 else V, ptr(labels), int(vocab_start), float(temperature), ptr(parts), None,
+             shard.stride(0) if T > 1 else V, ptr(labels), int(vocab_start), float(temperature), ptr(parts), ptr(raw_min),
              stream_ptr(dev))
     return parts
 
@@ -194,46 +196,58 @@ def vocab_parallel_forward(shard: torch.Tensor, labels: torch.Tensor, vocab_star
 
 class _VocabParallelLogprobsEntropy(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, shard, labels, vocab_start, temperature, group, exchange=None):
+    def forward(ctx, shard, labels, vocab_start, temperature, group, exchange=None, with_minmax=False):
         ctx.in_shape = shard.shape
         if shard.dim() != 2 or shard.stride(1) != 1:
             shard = shard.reshape(-1, shard.shape[-1]).contiguous()
         _lib.require_cuda(shard, labels)
         lab = labels.reshape(-1).long().contiguous()
-        if exchange is not None:
+        local_min = local_max = None
+        if with_minmax:
+            # the shard's own extremes come out of the partial kernel: parts[0] is the shard maximum
+            local_min = torch.empty(shard.shape[0], dtype=torch.float32, device=shard.device)
+            parts = _cuda_partials(shard, lab, vocab_start, temperature, raw_min=local_min)
+            local_max = parts[0].clone()
+            logp, ent, row_max, ln_s = _cuda_combine(gather_partials(parts, group), temperature)
+        elif exchange is not None:
             logp, ent, row_max, ln_s = exchange.forward(shard, lab, vocab_start, temperature)
         else:
             logp, ent, row_max, ln_s = vocab_parallel_forward(shard, lab, vocab_start, temperature, group)
         ctx.save_for_backward(shard, lab, row_max, ln_s, ent)
         ctx.vocab_start, ctx.temperature = int(vocab_start), float(temperature)
         ctx.set_materialize_grads(False)
+        if with_minmax:
+            ctx.mark_non_differentiable(local_min, local_max)
+            return logp, ent, local_min, local_max
         return logp, ent
 
     @staticmethod
-    def backward(ctx, g_logp, g_ent):
+    def backward(ctx, g_logp, g_ent, *unused):
         shard, lab, row_max, ln_s, ent = ctx.saved_tensors
         if g_logp is None and g_ent is None:
-            return None, None, None, None, None, None
+            return None, None, None, None, None, None, None
         from .functional import _f32, _logits_backward
         gl = None if g_logp is None else _f32(g_logp.reshape(-1))
         gh = None if g_ent is None else _f32(g_ent.reshape(-1))
         d = _logits_backward(shard, lab, ctx.temperature, row_max, ln_s, ent, gl, gh, vocab_start=ctx.vocab_start)
-        return d.view(ctx.in_shape), None, None, None, None, None
+        return d.view(ctx.in_shape), None, None, None, None, None, None
 
 
 def vocab_parallel_logprobs_entropy(shard_logits: torch.Tensor, labels: torch.Tensor, temperature: float = 1.0,
                                     group=None, vocab_start: Optional[int] = None,
-                                    exchange: Optional[PeerExchange] = None):
+                                    exchange: Optional[PeerExchange] = None, with_minmax: bool = False):
     """Log-prob of `labels` (GLOBAL vocabulary ids) and entropy from vocab-sharded logits
     `[T, V/R]`; replaces the Megatron-TP branch of gather_logprobs_entropy
     (areal/utils/functional.py:91-98).  `vocab_start` defaults to rank * shard_width.  Every rank gets
     the full `[T]` results (as after the reference's all-reduces); gradients flow to the local shard.
     `exchange`: a `PeerExchange` -- the partials are then read from the peers' memory over NVLink by the
-    combine kernel itself instead of being all-gathered first (same bits, one launch less)."""
+    combine kernel itself instead of being all-gathered first (same bits, one launch less).
+    `with_minmax=True`: also returns the row minimum and maximum of THIS rank's shard (what the reference logs as
+    vocab_min_logits / vocab_max_logits under tensor parallelism), from the same pass over the shard."""
     if vocab_start is None:
         rank = dist.get_rank(group) if dist.is_initialized() else 0
         vocab_start = rank * shard_logits.shape[-1]
-    return _VocabParallelLogprobsEntropy.apply(shard_logits, labels, vocab_start, temperature, group, exchange)
+    return _VocabParallelLogprobsEntropy.apply(shard_logits, labels, vocab_start, temperature, group, exchange, with_minmax)
 
 
 # --------------------------------------------------------------------------------------------------

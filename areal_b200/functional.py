@@ -92,27 +92,31 @@ def _logits_backward(x, lab, temperature, row_max, ln_s, ent, g_logp, g_ent, sca
 
 class _GatherLogprobsEntropy(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, logits, labels, temperature, want_entropy):
+    def forward(ctx, logits, labels, temperature, want_entropy, want_minmax=False):
         dev, x, lab, lead, V = _rows(logits, labels)
-        logp, ent, row_max, ln_s, _ = _logits_forward(x, lab, temperature, want_entropy)
+        logp, ent, row_max, ln_s, mn = _logits_forward(x, lab, temperature, want_entropy, want_minmax)
         ctx.save_for_backward(x, lab, row_max, ln_s, ent if want_entropy else None)
         ctx.temperature = float(temperature)
         ctx.in_shape = logits.shape
         ctx.set_materialize_grads(False)
         logp = logp.view(lead)
+        if want_minmax:                       # row min / max of the raw logits out of the same pass
+            mn, mx = mn.view(lead), row_max.clone().view(lead)
+            ctx.mark_non_differentiable(mn, mx)
+            return logp, ent.view(lead), mn, mx
         if want_entropy:
             return logp, ent.view(lead)
         return logp
 
     @staticmethod
-    def backward(ctx, g_logp, g_ent=None):
+    def backward(ctx, g_logp, g_ent=None, *unused):
         x, lab, row_max, ln_s, ent = ctx.saved_tensors
         gl = None if g_logp is None else _f32(g_logp.reshape(-1))
         gh = None if (g_ent is None or ent is None) else _f32(g_ent.reshape(-1))
         if gl is None and gh is None:
-            return None, None, None, None
+            return None, None, None, None, None
         d = _logits_backward(x, lab, ctx.temperature, row_max, ln_s, ent, gl, gh)
-        return d.view(ctx.in_shape), None, None, None
+        return d.view(ctx.in_shape), None, None, None, None
 
 
 # The two distributed branches INSIDE the reference functions (areal/utils/functional.py:50-58 and 91-98:
@@ -206,6 +210,23 @@ def gather_logprobs_entropy(logits: torch.Tensor, labels: torch.Tensor, temperat
     if sp is not None:
         logp, ent = _sp_all_gather(logp, sp), _sp_all_gather(ent, sp)
     return logp, ent
+
+
+def gather_logprobs_entropy_minmax(logits: torch.Tensor, labels: torch.Tensor, temperature: float = 1.0):
+    """`gather_logprobs_entropy` plus the row minimum / maximum of the LOCAL logits -- what `grpo_loss_fn` logs as
+    vocab_min_logits / vocab_max_logits (areal/engine/ppo/actor.py:375-376: `logits.detach().min(-1)` / `.max(-1)`, two
+    more reads of the rank's logits) -- out of the same pass, on every branch: vocabulary shards (the partial kernel's
+    shard maximum and raw minimum), Ulysses token slices and the plain case (the forward kernel's)."""
+    tp = _tp_group()
+    if tp is not None:
+        from .dist import vocab_parallel_logprobs_entropy
+        lp, ent, mn, mx = vocab_parallel_logprobs_entropy(logits, labels, temperature, group=tp, with_minmax=True)
+        return lp.view(labels.shape), ent.view(labels.shape), mn.view(labels.shape), mx.view(labels.shape)
+    logp, ent, mn, mx = _GatherLogprobsEntropy.apply(logits, labels, temperature, True, True)
+    sp = _sp_group()
+    if sp is not None:
+        logp, ent = _sp_all_gather(logp, sp), _sp_all_gather(ent, sp)
+    return logp, ent, mn, mx
 
 
 @torch.no_grad()
