@@ -133,7 +133,7 @@ def test_lm_head_logprobs_forward_only(chunk, with_entropy):
     T = 300 if chunk > 1 else 6
     h, w, labels, logits, *_, (lp_ref, ent_ref, _, _) = exact_inputs(T, 64, 4104, 5 + chunk)
     hh = h.to(D).requires_grad_()
-    res = lm_head_logprobs(hh, w.to(D), labels.to(D), 0.9, chunk_rows=chunk, with_entropy=with_entropy)
+    res = lm_head_logprobs(hh, w.to(D), labels.to(D), 0.9, chunk_rows=chunk, with_entropy=with_entropy, impl="library")
     lp = res[0] if with_entropy else res
     assert not lp.requires_grad and lp.dtype == torch.float32 and lp.shape == (T,)
     assert np.allclose(lp.cpu().numpy(), lp_ref, rtol=H.TOL_LOGITS, atol=H.TOL_LOGITS)
@@ -144,6 +144,12 @@ def test_lm_head_logprobs_forward_only(chunk, with_entropy):
     with torch.no_grad():
         want = F.gather_logprobs(logits.to(D), labels.to(D), 0.9)
     assert torch.equal(lp, want)
+    # the default route (one tensor-core kernel, no logits buffer): same numbers up to the summation order
+    auto = lm_head_logprobs(hh, w.to(D), labels.to(D), 0.9, with_entropy=with_entropy)
+    lp2 = auto[0] if with_entropy else auto
+    assert not lp2.requires_grad and torch.allclose(lp2, want, rtol=2e-5, atol=2e-5)
+    if with_entropy:
+        assert np.allclose(auto[1].cpu().numpy(), ent_ref, rtol=H.TOL_LOGITS, atol=H.TOL_LOGITS)
 
 
 def test_grpo_loss_fn_from_hidden_exports_what_grpo_loss_fn_exports():
