@@ -29,7 +29,7 @@ constexpr int kConsumers = kConsumerWarps * 32;      // 256
 constexpr int kThreads = kConsumers + 32;            // + 1 producer warp
 constexpr int kStageBytes = 16384;                   // 8192 bf16 per stage
 constexpr int kVecPerThread = kStageBytes / 16 / kConsumers;   // 4 x 16 B per thread per stage
-constexpr int kStages = 4;
+constexpr int kStages = 6;
 constexpr int kCtasPerSm = 2;
 constexpr size_t kSmemBytes = size_t(kStages) * kStageBytes + 1024;
 
@@ -121,7 +121,7 @@ __device__ __forceinline__ bool row_reduce(RowState& st, RowReduceSmem* red, int
 // warp it % 8.  The other seven warps only ARRIVE on the row's named barrier and go on with the next row;
 // the finishing warp waits for them, merges the eight partials and runs the epilogue, so its global loads
 // and stores are off the other warps' path and the duty (and its lag) moves from warp to warp.  Eight
-// partial slots / barrier ids: warps cannot drift more than kStages (4) rows apart, the ring holds them.
+// partial slots / barrier ids: warps cannot drift more than kStages (6) rows apart, the ring holds them.
 constexpr int kRedSlots = 8;
 template <int kCW>
 struct RowReduceRot {

@@ -55,7 +55,7 @@ masked_stats_kernel(const __grid_constant__ StatsTable tab, int64_t n, int chunk
   const int64_t hi = lo + kStatChunk < n ? lo + kStatChunk : n;
   Partial acc{0.0, 0.0, __int_as_float(0x7f800000), __int_as_float(0xff800000)};
   int cnt = 0;
-#pragma unroll 4
+#pragma unroll 8
   for (int64_t i = lo + tid; i < hi; i += kThreads) {
     const bool on = m ? (__ldg(m + i) != 0) : true;
     const float x = !v ? 1.f : (v_u8 ? float(__ldg(reinterpret_cast<const uint8_t*>(v) + i)) : __ldg(v + i));

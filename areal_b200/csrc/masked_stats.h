@@ -5,7 +5,7 @@
 namespace ab {
 
 constexpr int kMaxStatKeys = 32;
-constexpr int64_t kStatChunk = 8192;   // elements per CTA
+constexpr int64_t kStatChunk = 2048;   // elements per CTA: 8 per thread, all loads of a thread in flight at once
 
 struct StatsTable {
   const float* val[kMaxStatKeys];      // null: the value of every element is 1 (a denominator's own count)

@@ -48,6 +48,7 @@ class LossScaleAnnouncer:
         self.dp_group, self.dp_size, self.device = dp_group, dp_size, device
         self.extra_scale = extra_scale    # e.g. Megatron's optimizer loss scale (megatron_engine.py:900)
         self.weights = []
+        self._by_mb = {}
         self.total = None
         self.last_announced = None        # for tests / diagnostics
         self.n_announced = 0
@@ -56,6 +57,7 @@ class LossScaleAnnouncer:
         w = self.user_weight_fn(mb)
         if self.total is None:            # phase 1: the engine is building total_loss_weight
             self.weights.append(w)
+            self._by_mb[id(mb)] = (mb, w)  # (the object is kept so that its id cannot be recycled)
         return w
 
     def _total(self, like: torch.Tensor) -> torch.Tensor:
@@ -77,7 +79,8 @@ class LossScaleAnnouncer:
             if not self.weights:          # an engine that never asked for the weights: nothing to announce
                 return self.user_loss_fn(logits, mb)
             self.total = self._total(logits)
-        w = self.user_weight_fn(mb)
+        seen = self._by_mb.get(id(mb))    # the weight the engine already asked for in phase 1 (same micro-batch object)
+        w = seen[1] if (seen is not None and seen[0] is mb) else self.user_weight_fn(mb)
         scale = torch.as_tensor(w).to(self.total.device) / self.total          # :580
         scale = scale * self._world()                                        # :583 (dp_size)
         if self.extra_scale is not None:
