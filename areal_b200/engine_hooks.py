@@ -10,7 +10,8 @@ first forward (:518-526).
 
 `install_loss_scale_hook(engine)` wraps the engine's bound `train_batch` (no source edit): the wrapper
 passes wrapped `loss_fn` / `loss_weight_fn` to the original method, collects the weights the engine asks
-for, repeats the engine's own arithmetic for the total (same tensor ops, same all-reduce group) and, for
+for, obtains the total -- the engine's own all-reduced tensor when the weights can be tracked to it
+(`_TrackedWeight`), else by repeating the engine's arithmetic (same tensor ops, same all-reduce group) -- and, for
 each micro-batch, announces `loss_weight_fn(mb) / total * dp_size` to `areal_b200.actor.grpo_loss_fn`
 through a context variable before calling the user's `loss_fn`.  The announced value is a promise, not a
 requirement: the backward of the single-pass path compares it on the device with the scalar that really
@@ -34,6 +35,38 @@ def announced_loss_scale():
     return ANNOUNCED_LOSS_SCALE.get()
 
 
+class _TrackedWeight(torch.Tensor):
+    """A loss weight that remembers what is derived from it.  The engine builds its total as
+    `torch.stack([loss_weight_fn(mb) ...]).sum().detach().clone().to(float32, device)` and all-reduces THAT tensor in
+    place (areal/engine/fsdp_engine.py:518-526).  Every op on a tracked tensor returns a tracked tensor and reports it
+    to the announcer, so the last one reported in phase 1 is the very tensor the engine all-reduces -- the announcer
+    can read the engine's total (stream-ordered, after the engine's own all-reduce) instead of reducing a second
+    time.  Purely an optimisation: if the chain is not recognised, the announcer reduces for itself."""
+
+    _announcer = None
+
+    @classmethod
+    def __torch_function__(cls, func, types, args=(), kwargs=None):
+        kwargs = kwargs or {}
+        ann = None
+        for a in args:
+            if isinstance(a, _TrackedWeight):
+                ann = a._announcer
+            elif isinstance(a, (list, tuple)):
+                for x in a:
+                    if isinstance(x, _TrackedWeight):
+                        ann = x._announcer
+        with torch._C.DisableTorchFunctionSubclass():
+            out = func(*args, **kwargs)
+        if ann is not None and isinstance(out, torch.Tensor) and ann.total is None:
+            if not isinstance(out, _TrackedWeight):
+                out = out.as_subclass(_TrackedWeight)
+            out._announcer = ann
+            if out.dim() == 0 and out.dtype == torch.float32:     # the total itself (not e.g. `total != 0`)
+                ann._last_derived = out
+        return out
+
+
 class LossScaleAnnouncer:
     """Wraps one `(loss_fn, loss_weight_fn)` pair for one `train_batch` call.
 
@@ -49,6 +82,9 @@ class LossScaleAnnouncer:
         self.extra_scale = extra_scale    # e.g. Megatron's optimizer loss scale (megatron_engine.py:900)
         self.weights = []
         self._by_mb = {}
+        self._last_derived = None         # see _TrackedWeight
+        self.track_engine_total = True
+        self.used_engine_total = False    # for tests / diagnostics
         self.total = None
         self.last_announced = None        # for tests / diagnostics
         self.n_announced = 0
@@ -58,10 +94,20 @@ class LossScaleAnnouncer:
         if self.total is None:            # phase 1: the engine is building total_loss_weight
             self.weights.append(w)
             self._by_mb[id(mb)] = (mb, w)  # (the object is kept so that its id cannot be recycled)
+            if self.track_engine_total and isinstance(w, torch.Tensor) and type(w) is torch.Tensor:
+                t = w.as_subclass(_TrackedWeight)
+                t._announcer = self
+                return t
         return w
 
     def _total(self, like: torch.Tensor) -> torch.Tensor:
         dev = self.device if self.device is not None else like.device
+        t = self._last_derived
+        if (t is not None and t.dim() == 0 and t.dtype == torch.float32 and t.device == torch.device(dev)
+                and len(self.weights) > 0):
+            # the engine's own total_loss_weight, already all-reduced by the engine (stream-ordered before this read)
+            self.used_engine_total = True
+            return t.as_subclass(torch.Tensor)
         # the engine's own expression (areal/engine/fsdp_engine.py:518-526)
         total = torch.stack([torch.as_tensor(w) for w in self.weights]).sum().detach().clone().to(
             dtype=torch.float32, device=dev)

@@ -106,6 +106,8 @@ def _run_cpu(rank, world, port, out):
                 dist.all_reduce = dist_all_reduce
         assert stat["update_successful"] == 1.0
         assert len(announced) == len(arrived) == len(mbs)
+        # the announcer read the engine's own all-reduced total (no second all-reduce of its own)
+        assert eng.train_batch.last_announcer.used_engine_total
         for a, b in zip(announced, arrived):
             assert a.dtype == torch.float32 and a.shape == (1,)
             assert torch.equal(a.reshape(()), b.reshape(())), (a, b)       # bit-equal to the engine's own scalar
