@@ -545,6 +545,10 @@ __device__ __forceinline__ void st8(float* p, const float* v) {
   reinterpret_cast<float4*>(p)[0] = make_float4(v[0], v[1], v[2], v[3]);
   reinterpret_cast<float4*>(p)[1] = make_float4(v[4], v[5], v[6], v[7]);
 }
+__device__ __forceinline__ void sts8(uint32_t saddr, const float* v) {
+  asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(saddr), "f"(v[0]), "f"(v[1]), "f"(v[2]), "f"(v[3]) : "memory");
+  asm volatile("st.shared.v4.f32 [%0+16], {%1, %2, %3, %4};" ::"r"(saddr), "f"(v[4]), "f"(v[5]), "f"(v[6]), "f"(v[7]) : "memory");
+}
 // mask elements i .. i+8 as floats (i a multiple of 8 elements from an aligned base)
 __device__ __forceinline__ void ld9_mask(const void* base, int code, int64_t i, float* o) {
   if (code == 0) {
@@ -558,9 +562,75 @@ __device__ __forceinline__ void ld9_mask(const void* base, int code, int64_t i, 
       o[4 + k] = float((w.y >> (8 * k)) & 0xffu);
     }
     o[8] = float(__ldg(reinterpret_cast<const uint8_t*>(base) + i + 8));
+  } else if (code == 2) {
+    const int32_t* q = reinterpret_cast<const int32_t*>(base) + i;
+    const int4 a = __ldg(reinterpret_cast<const int4*>(q));
+    const int4 b = __ldg(reinterpret_cast<const int4*>(q) + 1);
+    const int32_t c = __ldg(q + 8);
+    o[0] = float(a.x); o[1] = float(a.y); o[2] = float(a.z); o[3] = float(a.w);
+    o[4] = float(b.x); o[5] = float(b.y); o[6] = float(b.z); o[7] = float(b.w);
+    o[8] = float(c);
   } else {
+    const int64_t* q = reinterpret_cast<const int64_t*>(base) + i;
+    longlong2 a[4];
 #pragma unroll
-    for (int k = 0; k < 9; ++k) o[k] = mask_as_float(base, code, i + k);
+    for (int k = 0; k < 4; ++k) a[k] = __ldg(reinterpret_cast<const longlong2*>(q) + k);
+    const int64_t c = __ldg(q + 8);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      o[2 * k] = float(a[k].x);
+      o[2 * k + 1] = float(a[k].y);
+    }
+    o[8] = float(c);
+  }
+}
+
+// Partial sum of n mask elements starting at element `off`, for thread `tid` of kNT: the type is chosen OUTSIDE
+// the loops, so that the eight loads of a round are independent and in flight together (a per-element switch
+// serialises them: one DRAM round trip each); byte masks go sixteen to a load when the start is 16-byte aligned.
+template <typename T, int kNT>
+__device__ __forceinline__ long long mask_sum_typed(const T* q, int64_t n, int tid) {
+  long long sum = 0;
+  for (int64_t i = tid; i < n; i += int64_t(kNT) * 8) {
+    T x[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const int64_t j = i + int64_t(k) * kNT;
+      x[k] = j < n ? __ldg(q + j) : T(0);
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) sum += static_cast<long long>(x[k]);
+  }
+  return sum;
+}
+template <int kNT>
+__device__ __forceinline__ long long mask_partial_sum(const void* base, int code, int64_t off, int64_t n, int tid) {
+  switch (code) {
+    case 0: return mask_sum_typed<float, kNT>(reinterpret_cast<const float*>(base) + off, n, tid);
+    case 1: {
+      const uint8_t* q = reinterpret_cast<const uint8_t*>(base) + off;
+      if ((reinterpret_cast<uintptr_t>(q) & 15) != 0) return mask_sum_typed<uint8_t, kNT>(q, n, tid);
+      const int64_t nvec = n >> 4;
+      unsigned int acc = 0;                                          // < 2^32 for any row this library takes
+      for (int64_t i = tid; i < nvec; i += int64_t(kNT) * 4) {
+        uint4 x[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const int64_t j = i + int64_t(k) * kNT;
+          x[k] = j < nvec ? __ldg(reinterpret_cast<const uint4*>(q) + j) : make_uint4(0u, 0u, 0u, 0u);
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          acc = __dp4a(x[k].x, 0x01010101u, __dp4a(x[k].y, 0x01010101u, __dp4a(x[k].z, 0x01010101u,
+                       __dp4a(x[k].w, 0x01010101u, acc))));
+      }
+      long long sum = acc;
+      const int64_t done = nvec << 4;
+      if (done + tid < n) sum += __ldg(q + done + tid);             // < 16 elements left
+      return sum;
+    }
+    case 2: return mask_sum_typed<int32_t, kNT>(reinterpret_cast<const int32_t*>(base) + off, n, tid);
+    default: return mask_sum_typed<int64_t, kNT>(reinterpret_cast<const int64_t*>(base) + off, n, tid);
   }
 }
 
@@ -586,11 +656,8 @@ gae_padded_kernel(const GaePaddedParams p, const AdvFusedParams f) {
     bool no_eos;
     if (kFused) {
       // seqlens = attention_mask.sum(-1) (:126)
-      long long part = 0, resp = 0;
-      for (int64_t i = tid; i < p.S; i += kThreads) {
-        part += mask_as_int(f.attn_mask, f.attn_code, row * p.S + i);
-        if (f.overlong) resp += mask_as_int(f.loss_mask, f.loss_mask_code, row * p.S + i);
-      }
+      long long part = mask_partial_sum<kThreads>(f.attn_mask, f.attn_code, row * p.S, p.S, tid);
+      long long resp = f.overlong ? mask_partial_sum<kThreads>(f.loss_mask, f.loss_mask_code, row * p.S, p.S, tid) : 0;
 #pragma unroll
       for (int d = 16; d; d >>= 1) {
         part += __shfl_xor_sync(0xffffffffu, part, d);
@@ -780,17 +847,78 @@ __device__ __forceinline__ void st_async_b64(uint32_t remote_addr, unsigned long
                : "memory");
 }
 
-__global__ void __launch_bounds__(512, 1)
-gae_padded_cluster_kernel(const GaePaddedParams p, int C) {
+// kFused: the reward construction of PPOActor.compute_advantages in the same launch (what gae_padded_kernel<true>
+// does for a row in one CTA).  One more thing crosses tile boundaries then, in BOTH directions and before anything
+// else: the row's sequence length (attention-mask sum, actor.py:126) and response length (loss-mask sum, overlong
+// penalty), which place the task reward and the zeroed column.  It travels together with the "next valid value"
+// summary (which needs only the mask and the values) in ONE all-to-all of 24 bytes per pair of tiles, so the fused
+// kernel has two exchanges like the plain one.  The tile's loads are issued before that exchange is waited for; its
+// five side outputs are staged in shared memory and leave through bulk copies (direct stores sat in the SM's store
+// queue ahead of the exchange messages: 2.6-5 us of the critical path, measured).
+struct NvLocal {
+  unsigned int right;   // lanes to the right of this one (in the warp) that hold a valid token
+  float wv;             // value of the nearest of them
+};
+// nearest valid value to the right of each thread INSIDE the tile: warp part (ballot + shuffle), warp summaries to smem
+__device__ __forceinline__ NvLocal nv_local(unsigned int valid_bits, const float (&vv)[kItems], int warp, int lane,
+                                            int* nv_has, float* nv_val) {
+  const int first = valid_bits ? (__ffs(valid_bits) - 1) : -1;
+  float first_val = 0.f;
+#pragma unroll
+  for (int k = 0; k < kItems; ++k)
+    if (k == first) first_val = vv[k];
+  const unsigned int ball = __ballot_sync(0xffffffffu, first >= 0);
+  NvLocal o;
+  o.right = (lane == 31) ? 0u : (ball >> (lane + 1));
+  const int src = o.right ? (lane + __ffs(o.right)) : lane;
+  o.wv = __shfl_sync(0xffffffffu, first_val, src);
+  const float warp_first = __shfl_sync(0xffffffffu, first_val, ball ? (__ffs(ball) - 1) : 0);
+  if (lane == 0) {
+    nv_has[warp] = ball != 0u;
+    nv_val[warp] = warp_first;
+  }
+  return o;
+}
+// (has a valid token << 32) | bits of the value of the tile's LEFTMOST valid token
+template <int kW>
+__device__ __forceinline__ unsigned long long nv_summary(const int* nv_has, const float* nv_val) {
+  int has = 0;
+  float val = 0.f;
+  for (int w = kW - 1; w >= 0; --w)
+    if (nv_has[w]) {
+      has = 1;
+      val = nv_val[w];
+    }
+  return (static_cast<unsigned long long>(has) << 32) | __float_as_uint(val);
+}
+template <int kW>
+__device__ __forceinline__ float nv_entering(const NvLocal& l, float carry, int warp, const int* nv_has,
+                                             const float* nv_val) {
+  if (l.right) return l.wv;
+  float nv_in = carry;
+  for (int w = kW - 1; w > warp; --w)
+    if (nv_has[w]) nv_in = nv_val[w];
+  return nv_in;
+}
+
+template <bool kFused>
+__global__ void __launch_bounds__(512, 2)
+gae_padded_cluster_kernel(const GaePaddedParams p, const AdvFusedParams f, int C) {
   constexpr int kT = 512, kW = kT / 32, kTileC = kT * kItems;      // 4096 tokens per CTA
   __shared__ Affine wsm[kW];
   __shared__ float nv_val[kW];
   __shared__ int nv_has[kW];
   __shared__ __align__(16) Affine inbox_map[kGaeClusterMax];         // [sender rank]
   __shared__ __align__(8) unsigned long long inbox_nv[kGaeClusterMax];   // (has << 32) | value bits
+  __shared__ __align__(16) long long inbox_len[kFused ? kGaeClusterMax : 1][2];   // (attention sum, loss-mask sum)
   __shared__ __align__(8) uint64_t bar_nv, bar_map;
+  __shared__ long long len_sm[kFused ? kW : 1], resp_sm[kFused ? kW : 1];
+  __shared__ RowCtx ctx_sm;
   __shared__ float nv_carry_sm;
   __shared__ double a_carry_sm;
+  extern __shared__ __align__(128) uint8_t stage_raw[];               // kFused: 5 x 4096 floats (side outputs)
+  constexpr uint32_t kStageArr = kTileC * 4;
+  const uint32_t stage_base = smem_u32(stage_raw);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const uint32_t rank = gae_cluster_ctarank();                       // rank 0 = RIGHTMOST tile of the row
   const int64_t row = blockIdx.x / C;
@@ -802,9 +930,9 @@ gae_padded_cluster_kernel(const GaePaddedParams p, int C) {
   }
   asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
 
-  const float* r = p.rewards + row * p.S;
-  const float* v = p.values + row * p.S;
-  const float* m = p.mask + row * p.S;
+  const float* r = kFused ? nullptr : p.rewards + row * p.S;
+  const float* v = p.values ? p.values + row * p.S : nullptr;        // null (fused only): zeros, actor.py:141
+  const float* m = kFused ? nullptr : p.mask + row * p.S;
   float* adv = p.adv + row * p.S;
   float* ret = p.ret + row * p.S;
   const int64_t L = p.S - 1;
@@ -815,75 +943,189 @@ gae_padded_cluster_kernel(const GaePaddedParams p, int C) {
   float rr[kItems], vv[kItems];
   unsigned int valid_bits = 0;
   const bool vec = p.vec_ok && nvalid == kItems;
-  if (vec) {
-    float mm[kItems];
-    ld8(r + t0, rr);
-    ld8(v + t0, vv);
-    ld8(m + t0, mm);
+  const float v_last = v ? v[p.S - 1] : 0.f;
+  float nv_in;
+  if constexpr (kFused) {
+    const int64_t g0 = row * p.S + t0;
+    const float sc_early = __ldcv(f.score + row);                    // used by thread 0 only; in flight with the masks
+    // partial sums of the two masks over this tile's columns (the rightmost tile takes column S-1 too)
+    {
+      const int64_t c0 = tile * kTileC;
+      const int64_t cn = rank == 0 ? p.S - c0 : int64_t(kTileC);
+      long long part = mask_partial_sum<kT>(f.attn_mask, f.attn_code, row * p.S + c0, cn, tid);
+      long long resp = f.overlong ? mask_partial_sum<kT>(f.loss_mask, f.loss_mask_code, row * p.S + c0, cn, tid) : 0;
 #pragma unroll
-    for (int k = 0; k < kItems; ++k)
-      if (mm[k] != 0.f) valid_bits |= 1u << k;
-  } else {
-#pragma unroll
-    for (int k = 0; k < kItems; ++k) {
-      if (k < nvalid) {
-        rr[k] = __ldg(r + t0 + k);
-        vv[k] = __ldg(v + t0 + k);
-        if (__ldg(m + t0 + k) != 0.f) valid_bits |= 1u << k;
+      for (int d = 16; d; d >>= 1) {
+        part += __shfl_xor_sync(0xffffffffu, part, d);
+        resp += __shfl_xor_sync(0xffffffffu, resp, d);
+      }
+      if (lane == 0) {
+        len_sm[warp] = part;
+        resp_sm[warp] = resp;
       }
     }
+    // the tile's inputs, in flight while the lengths travel; the mask and the values are needed first
+    float m9[kItems + 1], lp9[kItems + 1], rf[kItems];
+    if (vec) {
+      ld9_mask(f.loss_mask, f.loss_mask_code, g0, m9);               // t0+8 <= S-1 here: no wrap
+      if (v) ld8(v + t0, vv);
+      ld8(f.logp + g0, lp9);
+      lp9[kItems] = __ldg(f.logp + g0 + kItems);
+      if (f.ref_logp) ld8(f.ref_logp + g0, rf);
+#pragma unroll
+      for (int k = 0; k < kItems; ++k) {
+        if (!v) vv[k] = 0.f;
+        if (m9[k + 1] != 0.f) valid_bits |= 1u << k;
+      }
+    } else {
+#pragma unroll
+      for (int k = 0; k < kItems; ++k) {
+        if (k < nvalid) {                                            // t0+k+1 <= S-1: no wrap
+          vv[k] = v ? __ldg(v + t0 + k) : 0.f;
+          if (mask_as_float(f.loss_mask, f.loss_mask_code, g0 + k + 1) != 0.f) valid_bits |= 1u << k;
+        }
+      }
+    }
+    // column S-1 (side outputs only; its mask and log-prob wrap to column 0): loaded now, finished after the exchange
+    float last_lm = 0.f, last_lp = 0.f, last_rf = 0.f;
+    const bool do_last = rank == 0 && tid == kT - 1;
+    if (do_last) {
+      last_lm = mask_as_float(f.loss_mask, f.loss_mask_code, row * p.S);
+      last_lp = __ldg(f.logp + row * p.S + (f.roll_logp ? 0 : p.S - 1));
+      if (f.ref_logp) last_rf = f.ref_logp[row * p.S + p.S - 1];
+    }
+    const NvLocal nvl = nv_local(valid_bits, vv, warp, lane, nv_has, nv_val);
+    __syncthreads();
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");   // every CTA's barriers are initialised
+    // ---- exchange 1 (all-to-all): (attention sum, loss-mask sum, next-valid summary) of every tile to every other
+    if (tid == 0) {
+      long long seqlen = 0, resp_len = 0;
+      for (int w = 0; w < kW; ++w) {
+        seqlen += len_sm[w];
+        resp_len += resp_sm[w];
+      }
+      const unsigned long long nvmsg = nv_summary<kW>(nv_has, nv_val);
+      // score[row] is read BEFORE this CTA's message leaves (the empty asm makes the message depend on the loaded
+      // value), and rewritten (penalty, in place) by rank 0 only after it has received every CTA's
+      float sc = sc_early;
+      asm volatile("" : "+l"(seqlen) : "f"(sc));
+      for (uint32_t dst = 0; dst < uint32_t(C); ++dst)
+        if (dst != rank) {
+          const uint32_t rb = gae_mapa(smem_u32(&bar_nv), dst);
+          st_async_affine(gae_mapa(smem_u32(&inbox_len[rank][0]), dst), __longlong_as_double(seqlen),
+                          __longlong_as_double(resp_len), rb);
+          st_async_b64(gae_mapa(smem_u32(&inbox_nv[rank]), dst), nvmsg, rb);
+        }
+      mbar_arrive_expect_tx(smem_u32(&bar_nv), 24u * uint32_t(C - 1));
+      mbar_wait_acq_cluster(smem_u32(&bar_nv), 0);
+      for (uint32_t k = 0; k < uint32_t(C); ++k)
+        if (k != rank) {
+          seqlen += inbox_len[k][0];
+          resp_len += inbox_len[k][1];
+        }
+      if (f.overlong) {
+        // areal/utils/functional.py:389-394: min(-exceed / overlong_tokens * factor, 0) added to the score
+        const float a = __fmul_rn(__fdiv_rn(__ll2float_rn(-(resp_len - f.expected_len)),
+                                            __ll2float_rn(f.overlong_tokens)), f.overlong_factor);
+        if (!(0.f < a)) sc = __fadd_rn(sc, a);
+        if (rank == 0) f.score[row] = sc;
+      }
+      if (f.apply_scaling) {
+        sc = __fmul_rn(__fadd_rn(sc, f.bias), f.scaling);            // actor.py:98
+        sc = clamp_nan(sc, -f.clip, f.clip);                         // :99-101
+      }
+      RowCtx c;
+      c.row_off = row * p.S;
+      c.S = p.S;
+      c.zero_col = seqlen - 1 < 0 ? seqlen - 1 + p.S : seqlen - 1;   // negative index wraps (:131)
+      c.add_col = seqlen - 2 < 0 ? 0 : seqlen - 2;                   // :132
+      const bool no_eos = seqlen == p.S;                             // :127
+      c.add_score = (f.mask_no_eos_with_zero && no_eos) ? 0.f : sc;
+      if (c.zero_col >= p.S) c.zero_col = -1;                        // out-of-range sums: the reference raises
+      if (c.add_col >= p.S) c.add_col = -1;
+      ctx_sm = c;
+      float carry = no_eos ? v_last : 0.f;                           // actor.py:135 (bool * value)
+      for (uint32_t k = 0; k < rank; ++k)                            // tiles to the right: the smaller k the further
+        if (inbox_nv[k] >> 32) carry = __uint_as_float(static_cast<unsigned int>(inbox_nv[k]));
+      nv_carry_sm = carry;
+    }
+    __syncthreads();
+    const RowCtx ctx = ctx_sm;
+    nv_in = nv_entering<kW>(nvl, nv_carry_sm, warp, nv_has, nv_val);
+    if (vec) {
+      float klr[kItems], old[kItems];
+#pragma unroll
+      for (int k = 0; k < kItems; ++k) {
+        const TokOut o = fused_math(f, ctx, t0 + k, m9[k + 1], f.roll_logp ? lp9[k + 1] : lp9[k],
+                                    f.ref_logp ? rf[k] : 0.f);
+        rr[k] = o.tot;
+        klr[k] = o.klr;
+        old[k] = o.old;
+        rf[k] = o.ref;
+      }
+      const uint32_t so = stage_base + uint32_t(tid) * 32u;
+      if (f.ref_logp) sts8(so, rf);
+      sts8(so + kStageArr, klr);
+      sts8(so + 2 * kStageArr, rr);
+      sts8(so + 3 * kStageArr, m9 + 1);
+      sts8(so + 4 * kStageArr, old);
+      fence_proxy_async();                                           // staged side outputs -> visible to the bulk copies
+    } else {
+#pragma unroll
+      for (int k = 0; k < kItems; ++k)
+        if (k < nvalid) rr[k] = fused_token(f, ctx, t0 + k).x;       // (loads, math and direct stores: ragged ends only)
+    }
+    if (do_last) {                                                   // what fused_token does, loads already here
+      const int64_t g = row * p.S + p.S - 1;
+      const TokOut o = fused_math(f, ctx, p.S - 1, last_lm, last_lp, last_rf);
+      if (f.ref_logp) f.ref_logp[g] = o.ref;
+      f.kl_rewards[g] = o.klr;
+      f.tot_rewards[g] = o.tot;
+      f.loss_mask_out[g] = last_lm;
+      f.old_logp_out[g] = o.old;
+    }
+  } else {
+    if (vec) {
+      float mm[kItems];
+      ld8(r + t0, rr);
+      ld8(v + t0, vv);
+      ld8(m + t0, mm);
+#pragma unroll
+      for (int k = 0; k < kItems; ++k)
+        if (mm[k] != 0.f) valid_bits |= 1u << k;
+    } else {
+#pragma unroll
+      for (int k = 0; k < kItems; ++k) {
+        if (k < nvalid) {
+          rr[k] = __ldg(r + t0 + k);
+          vv[k] = __ldg(v + t0 + k);
+          if (__ldg(m + t0 + k) != 0.f) valid_bits |= 1u << k;
+        }
+      }
+    }
+    const NvLocal nvl = nv_local(valid_bits, vv, warp, lane, nv_has, nv_val);
+    __syncthreads();
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");   // every CTA's barriers are initialised
+    // ---- exchange 1: (has a valid token, value of the tile's LEFTMOST valid token) to every tile on the left
+    if (tid == 0) {
+      const unsigned long long msg = nv_summary<kW>(nv_has, nv_val);
+      for (uint32_t dst = rank + 1; dst < uint32_t(C); ++dst)
+        st_async_b64(gae_mapa(smem_u32(&inbox_nv[rank]), dst), msg, gae_mapa(smem_u32(&bar_nv), dst));
+      float carry = p.no_eos[row] != 0 ? v_last : 0.f;               // actor.py:135 (bool * value)
+      if (rank > 0) {
+        mbar_arrive_expect_tx(smem_u32(&bar_nv), 8u * rank);
+        mbar_wait_acq_cluster(smem_u32(&bar_nv), 0);
+        for (uint32_t k = 0; k < rank; ++k)                          // rank k < rank: further right the smaller k
+          if (inbox_nv[k] >> 32) carry = __uint_as_float(static_cast<unsigned int>(inbox_nv[k]));
+      }
+      nv_carry_sm = carry;
+    }
+    __syncthreads();
+    nv_in = nv_entering<kW>(nvl, nv_carry_sm, warp, nv_has, nv_val);
   }
-  const float v_last = v[p.S - 1];
   if (rank == 0 && tid == 0) {
     adv[p.S - 1] = 0.f;                                              // actor.py:148
     ret[p.S - 1] = v_last;                                           // returns = advantages + values, :152
-  }
-  // nearest valid value to the right of this thread, inside the tile
-  const int first = valid_bits ? (__ffs(valid_bits) - 1) : -1;
-  float first_val = 0.f;
-#pragma unroll
-  for (int k = 0; k < kItems; ++k)
-    if (k == first) first_val = vv[k];
-  const unsigned int ball = __ballot_sync(0xffffffffu, first >= 0);
-  const unsigned int right = (lane == 31) ? 0u : (ball >> (lane + 1));
-  const int src = right ? (lane + __ffs(right)) : lane;
-  const float wv = __shfl_sync(0xffffffffu, first_val, src);
-  const float warp_first = __shfl_sync(0xffffffffu, first_val, ball ? (__ffs(ball) - 1) : 0);
-  if (lane == 0) {
-    nv_has[warp] = ball != 0u;
-    nv_val[warp] = warp_first;
-  }
-  __syncthreads();
-  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");   // every CTA's barriers are initialised
-  // ---- exchange 1: (has a valid token, value of the tile's LEFTMOST valid token) to every tile on the left
-  if (tid == 0) {
-    int has = 0;
-    float val = 0.f;
-    for (int w = kW - 1; w >= 0; --w)
-      if (nv_has[w]) {
-        has = 1;
-        val = nv_val[w];
-      }
-    const unsigned long long msg = (static_cast<unsigned long long>(has) << 32) | __float_as_uint(val);
-    for (uint32_t dst = rank + 1; dst < uint32_t(C); ++dst)
-      st_async_b64(gae_mapa(smem_u32(&inbox_nv[rank]), dst), msg, gae_mapa(smem_u32(&bar_nv), dst));
-    float carry = p.no_eos[row] != 0 ? v_last : 0.f;                 // actor.py:135 (bool * value)
-    if (rank > 0) {
-      mbar_arrive_expect_tx(smem_u32(&bar_nv), 8u * rank);
-      mbar_wait_acq_cluster(smem_u32(&bar_nv), 0);
-      for (uint32_t k = 0; k < rank; ++k)                            // rank k < rank: further right the smaller k
-        if (inbox_nv[k] >> 32) carry = __uint_as_float(static_cast<unsigned int>(inbox_nv[k]));
-    }
-    nv_carry_sm = carry;
-  }
-  __syncthreads();
-  float nv_in;
-  if (right) {
-    nv_in = wv;
-  } else {
-    nv_in = nv_carry_sm;
-    for (int w = kW - 1; w > warp; --w)
-      if (nv_has[w]) nv_in = nv_val[w];
   }
   float delta[kItems];
   Affine agg = ident();
@@ -900,7 +1142,24 @@ gae_padded_cluster_kernel(const GaePaddedParams p, int C) {
     }
   }
   Affine excl, tagg;
-  block_suffix_scan<kW>(agg, wsm, warp, lane, excl, tagg);
+  block_suffix_scan<kW>(agg, wsm, warp, lane, excl, tagg);           // one __syncthreads() inside
+  if constexpr (kFused) {
+    // whole 8-token pieces of the tile: five bulk copies shared -> global (staged before the barrier above), issued
+    // by one thread of ANOTHER warp than the one that runs the exchanges, waited for at the very end
+    if (tid == 32 && p.vec_ok) {
+      const int64_t left = L - tile * kTileC;
+      const uint32_t bytes = uint32_t((left < kTileC ? left : int64_t(kTileC)) / kItems) * (kItems * 4u);
+      const int64_t g = row * p.S + tile * kTileC;
+      if (bytes) {
+        if (f.ref_logp) tma_store_1d(f.ref_logp + g, stage_base, bytes);
+        tma_store_1d(f.kl_rewards + g, stage_base + kStageArr, bytes);
+        tma_store_1d(f.tot_rewards + g, stage_base + 2 * kStageArr, bytes);
+        tma_store_1d(f.loss_mask_out + g, stage_base + 3 * kStageArr, bytes);
+        tma_store_1d(f.old_logp_out + g, stage_base + 4 * kStageArr, bytes);
+        tma_store_commit();
+      }
+    }
+  }
   // ---- exchange 2: the tile's map to every tile on the left
   if (tid == 0) {
     for (uint32_t dst = rank + 1; dst < uint32_t(C); ++dst)
@@ -932,6 +1191,9 @@ gae_padded_cluster_kernel(const GaePaddedParams p, int C) {
   if (vec) {
     st8(adv + t0, rr);
     st8(ret + t0, vv);
+  }
+  if constexpr (kFused) {
+    if (tid == 32) tma_store_wait_read<0>();                         // shared memory stays until the copies have read it
   }
 }
 
@@ -1189,34 +1451,53 @@ static void launch_padded_t(const GaePaddedParams& p, const AdvFusedParams& f, c
   else gae_padded_kernel<kFused, 256><<<grid, 256, 0, stream>>>(p, f);
 }
 
+// few long rows: one cluster of C CTAs per row (4096 tokens each) instead of one CTA per row
+template <bool kFused>
+static bool launch_padded_cluster(const GaePaddedParams& p, const AdvFusedParams& f, cudaStream_t stream, int* status) {
+  static const bool use_cluster = [] {
+    const char* e = getenv("AREAL_B200_PADDED_CLUSTER");
+    return !(e && e[0] == '0');
+  }();
+  const int64_t C = (p.S - 1 + 4095) / 4096;
+  if (!(use_cluster && C >= 2 && C <= kGaeClusterMax && p.B * C <= 2 * int64_t(num_sms()))) return false;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(static_cast<unsigned int>(p.B * C));
+  cfg.blockDim = dim3(512);
+  cfg.stream = stream;
+  if (kFused) {
+    constexpr size_t kStage = 5 * 4096 * sizeof(float);              // side outputs of a tile
+    static const cudaError_t once = cudaFuncSetAttribute(gae_padded_cluster_kernel<kFused>,
+                                                         cudaFuncAttributeMaxDynamicSharedMemorySize, int(kStage));
+    if (once != cudaSuccess) return false;                           // (one CTA per row instead)
+    cfg.dynamicSmemBytes = kStage;
+  }
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = static_cast<unsigned int>(C);
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  static const bool debug = getenv("AREAL_B200_GAE_DEBUG") != nullptr;
+  if (debug) {
+    int n = -1;
+    const cudaError_t q = cudaOccupancyMaxActiveClusters(&n, gae_padded_cluster_kernel<kFused>, &cfg);
+    fprintf(stderr, "[areal_b200] gae_padded_cluster<%d> B=%lld C=%lld: max active clusters %d (%s)\n", int(kFused),
+            static_cast<long long>(p.B), static_cast<long long>(C), n, cudaGetErrorString(q));
+  }
+  const cudaError_t e = cudaLaunchKernelEx(&cfg, gae_padded_cluster_kernel<kFused>, p, f, int(C));
+  *status = e == cudaSuccess ? kOk : kCudaError;
+  if (e != cudaSuccess) set_error("gae_padded_cluster launch failed: %s", cudaGetErrorString(e));
+  return true;
+}
+
 int launch_gae_padded(const GaePaddedParams& p_in, cudaStream_t stream) {
   GaePaddedParams p = p_in;
   if (p.B == 0 || p.S == 0) return kOk;
   p.vec_ok = p.S % 4 == 0 && aligned16(p.rewards) && aligned16(p.values) && aligned16(p.mask) &&
              aligned16(p.adv) && aligned16(p.ret);
-  {
-    // few long rows: one cluster of C CTAs per row (4096 tokens each) instead of one CTA per row
-    static const bool use_cluster = [] {
-      const char* e = getenv("AREAL_B200_PADDED_CLUSTER");
-      return !(e && e[0] == '0');
-    }();
-    const int64_t C = (p.S - 1 + 4095) / 4096;
-    if (use_cluster && C >= 2 && C <= kGaeClusterMax && p.B * C <= 2 * int64_t(num_sms())) {
-      cudaLaunchConfig_t cfg = {};
-      cfg.gridDim = dim3(static_cast<unsigned int>(p.B * C));
-      cfg.blockDim = dim3(512);
-      cfg.stream = stream;
-      cudaLaunchAttribute attr[1];
-      attr[0].id = cudaLaunchAttributeClusterDimension;
-      attr[0].val.clusterDim.x = static_cast<unsigned int>(C);
-      attr[0].val.clusterDim.y = 1;
-      attr[0].val.clusterDim.z = 1;
-      cfg.attrs = attr;
-      cfg.numAttrs = 1;
-      AB_CUDA(cudaLaunchKernelEx(&cfg, gae_padded_cluster_kernel, p, int(C)));
-      return kOk;
-    }
-  }
+  int st = kOk;
+  if (launch_padded_cluster<false>(p, AdvFusedParams{}, stream, &st)) return st;
   launch_padded_t<false>(p, AdvFusedParams{}, stream);
   return check_launch("gae_padded");
 }
@@ -1229,6 +1510,8 @@ int launch_advantages_padded(const GaePaddedParams& p_in, const AdvFusedParams& 
              aligned16(f.loss_mask) && aligned16(f.logp) && aligned16(f.ref_logp) &&
              aligned16(f.kl_rewards) && aligned16(f.tot_rewards) && aligned16(f.loss_mask_out) &&
              aligned16(f.old_logp_out);
+  int st = kOk;
+  if (launch_padded_cluster<true>(p, f, stream, &st)) return st;
   launch_padded_t<true>(p, f, stream);
   return check_launch("advantages_padded");
 }

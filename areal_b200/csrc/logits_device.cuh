@@ -99,29 +99,44 @@ __device__ __forceinline__ void state_merge(float& m, float& s, float& w, float 
   m = M;
 }
 
-// Merge the 32 canonical states of a warp: the row max first (shuffles only), then every lane rebases its
-// (s, w) to it ONCE -- one ex2 per lane instead of two per butterfly round -- and s, w, mn are plain
-// butterfly sums / minima.  All lanes end with the warp's state.
-__device__ __forceinline__ void warp_merge_state(RowState& st, float c2) {
-  float M = st.m;
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) M = fmaxf(M, __shfl_xor_sync(0xffffffffu, M, o));
+// warp-wide max / min of an fp32 value in ONE instruction (redux.sync.f32, sm_100a: CREDUX into a uniform register).
+// NaN operands are ignored, like fmaxf / fminf.
+__device__ __forceinline__ float warp_max_f32(float v) {
+  float r;
+  asm volatile("redux.sync.max.f32 %0, %1, 0xffffffff;" : "=f"(r) : "f"(v));
+  return r;
+}
+__device__ __forceinline__ float warp_min_f32(float v) {
+  float r;
+  asm volatile("redux.sync.min.f32 %0, %1, 0xffffffff;" : "=f"(r) : "f"(v));
+  return r;
+}
+
+// (s, w) of a canonical state moved to the reference M >= st.m: one ex2
+__device__ __forceinline__ void state_shift_to(const RowState& st, float M, float c2, float& s, float& w) {
   const bool empty = st.m == -INFINITY;
   const float d = empty ? 0.f : (st.m - M) * c2;
   const float f = empty ? 0.f : ex2_approx(d);
-  float s = st.s * f;
-  float w = f * fmaf(d, st.s, st.w);
-  float mn = st.mn;
+  s = st.s * f;
+  w = f * fmaf(d, st.s, st.w);
+}
+
+// Merge the 32 canonical states of a warp: the row max first (one redux), then every lane rebases its
+// (s, w) to it ONCE -- one ex2 per lane instead of two per butterfly round -- and s, w are plain
+// butterfly sums, mn one more redux.  All lanes end with the warp's state.
+__device__ __forceinline__ void warp_merge_state(RowState& st, float c2) {
+  const float M = warp_max_f32(st.m);
+  float s, w;
+  state_shift_to(st, M, c2, s, w);
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
     s += __shfl_xor_sync(0xffffffffu, s, o);
     w += __shfl_xor_sync(0xffffffffu, w, o);
-    mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
   }
+  st.mn = warp_min_f32(st.mn);
   st.m = M;
   st.s = s;
   st.w = w;
-  st.mn = mn;
 }
 
 struct RowGrad {

@@ -123,22 +123,32 @@ __device__ __forceinline__ bool row_reduce(RowState& st, RowReduceSmem* red, int
 // and stores are off the other warps' path and the duty (and its lag) moves from warp to warp.  Eight
 // partial slots / barrier ids: warps cannot drift more than kStages (6) rows apart, the ring holds them.
 constexpr int kRedSlots = 8;
+// What a warp leaves for the finishing warp: its max, its min, and EIGHT partial (s, w) sums relative to its max
+// (two butterfly rounds instead of five: the finishing warp's own merge adds up the rest, so the seven warps that
+// only pass through a row end spend ~25 instructions there instead of ~60).
 template <int kCW>
 struct RowReduceRot {
-  float m[kRedSlots][kCW], s[kRedSlots][kCW], w[kRedSlots][kCW], mn[kRedSlots][kCW];
+  float2 sw[kRedSlots][kCW][8];
+  float m[kRedSlots][kCW], mn[kRedSlots][kCW];
 };
-template <int kCW>
+template <bool kMinMax, int kCW>
 __device__ __forceinline__ bool row_reduce_rot(RowState& st, RowReduceRot<kCW>* red, int64_t it, int warp, int lane,
                                                float c2) {
   constexpr int kConsumerWarps = kCW, kConsumers = kCW * 32;
   state_canonical(st, c2);
-  warp_merge_state(st, c2);
+  const float M = warp_max_f32(st.m);
+  float s, w;
+  state_shift_to(st, M, c2, s, w);
+  s += __shfl_xor_sync(0xffffffffu, s, 16);
+  w += __shfl_xor_sync(0xffffffffu, w, 16);
+  s += __shfl_xor_sync(0xffffffffu, s, 8);
+  w += __shfl_xor_sync(0xffffffffu, w, 8);
+  const float mn = kMinMax ? warp_min_f32(st.mn) : INFINITY;
   const int slot = static_cast<int>(it % kRedSlots);
+  if (lane < 8) red->sw[slot][warp][lane] = make_float2(s, w);
   if (lane == 0) {
-    red->m[slot][warp] = st.m;
-    red->s[slot][warp] = st.s;
-    red->w[slot][warp] = st.w;
-    red->mn[slot][warp] = st.mn;
+    red->m[slot][warp] = M;
+    if (kMinMax) red->mn[slot][warp] = mn;
   }
   const int fin = static_cast<int>(it % kConsumerWarps);
   if (warp != fin) {
@@ -147,20 +157,25 @@ __device__ __forceinline__ bool row_reduce_rot(RowState& st, RowReduceRot<kCW>* 
     return false;
   }
   named_bar_sync(1 + slot, kConsumers);
-  const int l = lane & (kConsumerWarps - 1);
-  st.m = red->m[slot][l];
-  st.s = red->s[slot][l];
-  st.w = red->w[slot][l];
-  st.mn = red->mn[slot][l];
+  // kCW * 8 partials over 32 lanes
+  st.m = -INFINITY;
+  st.s = 0.f;
+  st.w = 0.f;
 #pragma unroll
-  for (int o = kConsumerWarps / 2; o > 0; o >>= 1) {
-    const float m2 = __shfl_xor_sync(0xffffffffu, st.m, o);
-    const float s2 = __shfl_xor_sync(0xffffffffu, st.s, o);
-    const float w2 = __shfl_xor_sync(0xffffffffu, st.w, o);
-    const float n2 = __shfl_xor_sync(0xffffffffu, st.mn, o);
-    state_merge(st.m, st.s, st.w, m2, s2, w2, c2);
-    st.mn = fminf(st.mn, n2);
+  for (int e = lane; e < kCW * 8; e += 32) {
+    const float2 q = red->sw[slot][e >> 3][e & 7];
+    const float m2 = red->m[slot][e >> 3];
+    if (e < 32) {
+      st.m = m2;
+      st.s = q.x;
+      st.w = q.y;
+    } else {
+      state_merge(st.m, st.s, st.w, m2, q.x, q.y, c2);
+    }
   }
+  st.mn = INFINITY;
+  if (kMinMax && lane < kCW) st.mn = red->mn[slot][lane];
+  warp_merge_state(st, c2);
   return lane == 0;
 }
 
@@ -344,7 +359,7 @@ logits_fwd_tma_kernel(const LogitsFwdParams p) {
         phase ^= 1u;
       }
     }
-    if (row_reduce_rot<kCW>(st, &red, it, warp, lane, c2)) row_epilogue(p, row, st, acc);
+    if (row_reduce_rot<kMinMax, kCW>(st, &red, it, warp, lane, c2)) row_epilogue(p, row, st, acc);
   }
   if (p.mode == kModeFusedActor) {
     // every warp's lane 0 holds the loss terms of the rows it finished: add them up in warp order

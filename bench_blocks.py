@@ -280,6 +280,29 @@ class Blocks:
         rows.append(dict(kernel="advantages_padded (compute_advantages, one launch)", B=B, S=S,
                          tokens_per_s=B * S / (ms * 1e-3), **self.frac(nbytes, ms)))
         del base, am
+        # few long rows (long chains of thought): a cluster of 8 CTAs per row; GPU time from a graph replay over a
+        # ring of input sets that is larger than L2 in total
+        B, S = 16, 32768
+        n_sets = 16
+        ring = []
+        for _ in range(n_sets):
+            lens = torch.randint(S // 2, S + 1, (B,), device=self.dev)
+            am = torch.arange(S, device=self.dev)[None, :] < lens[:, None]
+            ring.append(dict(input_ids=torch.zeros(B, S, dtype=torch.long, device=self.dev), attention_mask=am,
+                             loss_mask=am & (torch.rand(B, S, device=self.dev) > 0.2),
+                             logprobs=-torch.rand(B, S, device=self.dev), ref_logp=-torch.rand(B, S, device=self.dev),
+                             values=torch.randn(B, S, device=self.dev), rewards=torch.randn(B, device=self.dev)))
+
+        def adv_sweep():
+            for d in ring:
+                compute_advantages(actor, dict(d))
+        ms_eager = self.time_ms(adv_sweep, iters=5, warmup=2) / n_sets
+        ms_gpu = self._graph_time(adv_sweep) / n_sets
+        rows.append(dict(kernel="advantages_padded (compute_advantages), few long rows", B=B, S=S,
+                         input_sets_in_ring=n_sets, eager_us_per_call=ms_eager * 1e3, gpu_us_per_call=ms_gpu * 1e3,
+                         note="gpu time includes the wrapper's small kernels (mask casts, clones) of the same call",
+                         **self.frac((2 + 4 + 8 + 4 + 24) * B * S, ms_gpu)))
+        del ring
         # configs[3]'s per-GPU kernel on one GPU: a [131072, V/8] vocabulary shard
         T, Vs = 131072, V // 8
         x, g = self.logits(T, Vs, 5)

@@ -90,6 +90,52 @@ def test_compute_advantages_vs_oracle(B, S, mask_dtype):
     assert np.array_equal(data["rewards"].cpu().numpy(), score)          # no penalty configured: untouched
 
 
+@pytest.mark.parametrize("B,S,mask_dtype,overlong,with_values,with_ref",
+                         # few long rows: a cluster of up to 8 CTAs per row, lengths summed across the cluster
+                         [(16, 32768, torch.bool, False, True, True), (5, 20001, torch.int64, True, True, True),
+                          (3, 32769, torch.float32, True, False, True),     # column S-1 alone beyond the last tile
+                          (9, 4098, torch.bool, False, True, False), (4, 8200, torch.uint8, True, True, True),
+                          (2, 40000, torch.bool, True, True, True)])       # beyond a cluster: one CTA per row again
+def test_compute_advantages_long_rows_vs_oracle(B, S, mask_dtype, overlong, with_values, with_ref):
+    from areal_b200.actor import compute_advantages
+    rng = np.random.RandomState(B + S)
+    lens = rng.randint(1, S + 1, B)
+    lens[0] = S                                                          # no EOS: the bootstrap value enters
+    if B > 2:
+        lens[1], lens[2] = 1, 4097                                       # reward / zeroed column in the LEFTMOST tiles
+    am = np.arange(S)[None, :] < lens[:, None]
+    lm = am & (rng.rand(B, S) > 0.3)
+    lm[-1, S // 2:] = False                                              # whole tiles without a valid token
+    logp = -rng.rand(B, S).astype(np.float32) * 5
+    ref = -rng.rand(B, S).astype(np.float32) * 5
+    val = rng.randn(B, S).astype(np.float32)
+    score = (rng.randn(B) * 4).astype(np.float32)
+    c = dict(A.BASE, kl_estimator="k2", kl_ctl=0.3, reward_bias=0.25, reward_scaling=1.5, reward_clip=3.0,
+             discount=0.999, gae_lambda=0.97, mask_no_eos_with_zero=True, overlong_reward_penalty=overlong,
+             overlong_tokens=1000, overlong_penalty_factor=0.75, max_new_tokens=S // 2)
+    data = dict(input_ids=torch.zeros(B, S, dtype=torch.long, device=DEV),
+                attention_mask=torch.from_numpy(am).to(DEV).to(mask_dtype),
+                loss_mask=torch.from_numpy(lm).to(DEV).to(mask_dtype), logprobs=torch.from_numpy(logp).to(DEV),
+                rewards=torch.from_numpy(score).to(DEV))
+    if with_ref:
+        data["ref_logp"] = torch.from_numpy(ref).to(DEV)
+    if with_values:
+        data["values"] = torch.from_numpy(val).to(DEV)
+    compute_advantages(make_actor(c), data)
+    sc = O.overlong_penalty(score, lm, 1000, 0.75, S // 2) if overlong else score
+    assert np.array_equal(data["rewards"].cpu().numpy(), sc.astype(np.float32))        # penalty in place, once
+    if overlong:
+        assert not np.array_equal(sc, score)
+    r = O.compute_advantages(sc, lm, logp, am, ref_logp=ref if with_ref else None, values=val if with_values else None,
+                             roll_logp=True, reward_bias=0.25, reward_scaling=1.5, reward_clip=3.0, kl_ctl=0.3,
+                             kl_estimator="k2", mask_no_eos_with_zero=True, discount=0.999, gae_lambda=0.97)
+    keys = ("loss_mask", "logprobs", "kl_rewards", "tot_rewards") + (("ref_logp",) if with_ref else ())
+    for k in keys:
+        assert np.array_equal(data[k].cpu().numpy(), r[k]), k
+    A.assert_gae_close(data["advantages"].cpu().numpy(), r["advantages"], "advantages")
+    A.assert_gae_close(data["returns"].cpu().numpy(), r["returns"], "returns")
+
+
 def test_compute_advantages_errors():
     from areal_b200.actor import compute_advantages
     c = dict(A.BASE, kl_estimator="k4")
