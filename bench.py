@@ -663,6 +663,21 @@ def cpu_baseline(sample_rows=1024, steps=2, warmup=1):
                                      "loop of 0-dim torch ops (ppo_functional.py:292-323) restated, single Python thread"}
     except Exception as ex:
         out["extra_error"] = repr(ex)[:200]
+    try:
+        import torch
+        if torch.cuda.is_available():
+            # the same restated reference ops, eager, on this GPU (reported: SURVEY 8d "GPU reference baseline")
+            torch.cuda.empty_cache()
+            torch.cuda.reset_peak_memory_stats(0)
+            secs, peak = CB.time_steps_on_gpu(T_TOKENS, VOCAB, 3, 1, CFG, TEMPERATURE)
+            out["torch_gpu_port"] = {"value": T_TOKENS / secs, "unit": "tokens/s", "ms_per_step": secs * 1e3,
+                                     "peak_memory_gb": peak / 1e9,
+                                     "sample": f"the same restated torch ops (chunked fp32 log_softmax / entropy, PPO loss, "
+                                               f"backward to bf16 dlogits; no GAE) run eagerly on cuda:0 at the full "
+                                               f"T={T_TOKENS}, V={VOCAB}: 3 steps after 1 warm-up, CUDA events"}
+            torch.cuda.empty_cache()
+    except Exception as ex:
+        out["torch_gpu_port_error"] = repr(ex)[:200]
     return out
 
 

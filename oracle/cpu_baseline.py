@@ -98,6 +98,43 @@ def time_steps(sample_rows: int, V: int, steps: int, warmup: int, cfg, temperatu
     return dt, torch.get_num_threads()
 
 
+def time_steps_on_gpu(rows: int, V: int, steps: int, warmup: int, cfg, temperature=1.0, seed=0, device="cuda:0"):
+    """The SAME restated torch operations (logp_entropy_torch + actor_loss_torch + backward; no GAE: the reference's
+    GPU GAE is its own CUDA extension, which cannot travel) executed eagerly on the GPU: what the reference's
+    functions cost on this device without torch.compile.  Reported beside the CPU baseline, never a target and
+    never the product path.  Returns seconds per step (CUDA events)."""
+    g = torch.Generator(device=device).manual_seed(seed)
+    logits = torch.empty(rows, V, dtype=torch.bfloat16, device=device)
+    for i in range(0, rows, 1024):
+        n = min(1024, rows - i)
+        logits[i:i + n] = (torch.randn(n, V, generator=g, device=device) * 2.0).bfloat16()
+    labels = torch.randint(0, V, (rows,), generator=g, device=device)
+    lp0 = -torch.rand(rows, generator=g, device=device) * 5
+    prox = lp0 + 0.02 * torch.randn(rows, generator=g, device=device)
+    old = lp0 + 0.05 * torch.randn(rows, generator=g, device=device)
+    adv = torch.randn(rows, generator=g, device=device)
+    mask = torch.rand(rows, generator=g, device=device) > 0.15
+
+    def one():
+        x = logits.detach().requires_grad_()
+        lp, ent = logp_entropy_torch(x, labels, temperature)
+        loss = actor_loss_torch(lp, prox, old, adv, cfg["eps_clip"], mask, cfg.get("eps_clip_higher"),
+                                cfg.get("c_clip"), cfg.get("behav_imp_weight_cap"))
+        loss.backward()
+        return x.grad
+    for _ in range(warmup):
+        one()
+    torch.cuda.synchronize(device)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        one()
+    e1.record()
+    torch.cuda.synchronize(device)
+    peak = torch.cuda.max_memory_allocated(device)
+    return e0.elapsed_time(e1) * 1e-3 / max(steps, 1), peak
+
+
 # --------------------------------------------------------------------------------------------------
 # BASELINE.json configs[0]: the reference's CPU GAE exactly as it executes -- a Python double loop
 # with one 0-dim torch op per token and per term (realhf/impl/model/utils/ppo_functional.py:292-323)
