@@ -31,6 +31,9 @@ SIGNATURES = {
                                              F64, c_int, c_int, c_int, F64, F64, P, P, P, P, P, P, P]),
     "areal_b200_vocab_p2p_buffer_bytes": (I64, [I64]),
     "areal_b200_vocab_combine_p2p": (c_int, [P, c_int, c_int, I64, I64, I64, F64, I64, P, P, P, P, P, P]),
+    "areal_b200_vocab_push_buffer_bytes": (I64, [I64, c_int]),
+    "areal_b200_logits_partial_fwd_push": (c_int, [P, c_int, I64, I64, I64, P, I64, F64, P, c_int, c_int, I64, I64, I64, I64, P, P,
+                                                   P, P, P, P, P]),
     "areal_b200_clamped_entropy_fwd": (c_int, [P, c_int, I64, I64, I64, P, F64, I64, P, P, P, P]),
     "areal_b200_clamped_entropy_bwd": (c_int, [P, c_int, I64, I64, I64, P, F64, P, P, P, P, I64, P]),
     "areal_b200_lm_head_workspace_bytes": (I64, [I64, I64]),

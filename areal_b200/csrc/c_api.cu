@@ -841,6 +841,49 @@ AREAL_B200_API int areal_b200_vocab_combine_p2p(void* const* peer_bases, int ran
                                   static_cast<cudaStream_t>(stream));
 }
 
+AREAL_B200_API int64_t areal_b200_vocab_push_buffer_bytes(int64_t max_tokens, int world_size) {
+  if (max_tokens < 0 || world_size < 1 || world_size > 16) return -1;
+  return vocab_push_buffer_bytes(max_tokens, world_size);
+}
+
+AREAL_B200_API int areal_b200_logits_partial_fwd_push(const void* logits, int dtype, int64_t T, int64_t V,
+                                                      int64_t row_stride, const int64_t* labels,
+                                                      int64_t vocab_start, double temperature,
+                                                      void* const* peer_bases, int rank, int world_size,
+                                                      int64_t max_tokens, int64_t epoch, int64_t rows_target,
+                                                      int64_t timeout_cycles, float* logp, float* entropy,
+                                                      float* row_max, float* ln_sumexp, float* raw_min,
+                                                      int* status, void* stream) {
+  AB_NVTX_RANGE("areal_b200_logits_partial_fwd_push");
+  int rc = check_logits(logits, dtype, T, V, row_stride, labels, temperature);
+  if (rc) return rc;
+  AB_REQUIRE(world_size >= 1 && world_size <= 16, "logits_partial_fwd_push: world size must be 1..16, got %d", world_size);
+  AB_REQUIRE(rank >= 0 && rank < world_size, "logits_partial_fwd_push: rank %d out of range", rank);
+  AB_REQUIRE(T <= max_tokens, "logits_partial_fwd_push: T=%lld exceeds the buffer's %lld tokens",
+             static_cast<long long>(T), static_cast<long long>(max_tokens));
+  AB_REQUIRE(epoch >= 1, "logits_partial_fwd_push: epochs start at 1");
+  AB_REQUIRE(peer_bases && status, "null pointer");
+  AB_REQUIRE(T == 0 || (logp && row_max && ln_sumexp), "null output");
+  for (int r = 0; r < world_size; ++r) AB_REQUIRE(peer_bases[r] != nullptr, "logits_partial_fwd_push: null peer buffer %d", r);
+  LogitsFwdParams p;
+  fill_fwd_common(&p, logits, dtype, T, V, row_stride, labels, vocab_start, temperature);
+  p.mode = kModePartial;
+  p.raw_min = raw_min;
+  p.logp = logp;
+  p.entropy = entropy;
+  p.row_max = row_max;
+  p.ln_s = ln_sumexp;
+  p.push_world = world_size;
+  p.push_rank = rank;
+  p.push_slot = static_cast<int>(epoch & 1);
+  p.push_tmax = max_tokens;
+  p.push_target = static_cast<unsigned int>(static_cast<uint64_t>(rows_target));
+  p.push_timeout = static_cast<long long>(timeout_cycles);
+  p.push_status = status;
+  for (int r = 0; r < world_size; ++r) p.push_base[r] = static_cast<char*>(peer_bases[r]);
+  return launch_logits_partial_push(p, static_cast<cudaStream_t>(stream));
+}
+
 AREAL_B200_API int areal_b200_rms_update(const double* partials, int64_t n_partials, void* state,
                                          int state_is_f64, int mode, double beta, void* stream) {
   AB_NVTX_RANGE("areal_b200_rms_update");

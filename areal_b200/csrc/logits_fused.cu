@@ -179,6 +179,42 @@ __device__ __forceinline__ bool row_reduce_rot(RowState& st, RowReduceRot<kCW>* 
   return lane == 0;
 }
 
+// ---- push exchange of the vocabulary-sharded forward (NVLink peer memory, plain stores) -----------------
+// Every rank owns a symmetric buffer:  u32 rows_in[2] (per slot: how many rows all ranks have delivered so far,
+// cumulative over the steps) | u32 pad[2] | u32 ticket[2] (local) | pad to 256 B | float4 parts[2][R][Tmax]  (slot,
+// sender, row) = (m, S, W, x_label).
+// The row epilogue of the partial kernel stores a row's four numbers into EVERY rank's buffer (one 16-byte store per
+// rank, the local one included); when a CTA has finished its rows it fences (system scope) and takes a local ticket, the
+// last CTA of the rank tells every rank "T more rows" (one atomic add per rank), and every CTA waits until its own
+// buffer's counter says that all R*T rows of the step are in; then the same CTAs combine the R partials of each row -- from LOCAL memory -- in rank order, with the
+// arithmetic of vocab_combine_kernel (bit-identical results).  Partial kernel, exchange and combine are one launch and
+// the transfer rides under the streaming pass; what is left after the slowest rank's last row is one fence, one
+// NVLink round trip and a 16 MB local read.
+// A slot is reused two steps later without another handshake: a rank writes slot s of step e+2 only after it has
+// seen all rows of step e+1, i.e. after every rank has started step e+1, i.e. after every rank's kernel of step e --
+// combine included -- has finished (kernels of one rank run in stream order).
+constexpr int64_t kPushHeaderBytes = 256;
+__device__ __forceinline__ float4* push_slot_ptr(char* base, int slot, int R, int sender, int64_t tmax, int64_t row) {
+  return reinterpret_cast<float4*>(base + kPushHeaderBytes) + (int64_t(slot) * R + sender) * tmax + row;
+}
+__device__ __forceinline__ void st_weak_v4(float4* q, float a, float b, float c, float d) {
+  asm volatile("st.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(q), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+// around L1 (lines of this buffer that L1 may still hold are two steps old)
+__device__ __forceinline__ float4 ld_sys_v4(const float4* q) {
+  float4 v;
+  asm volatile("ld.relaxed.sys.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(q) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int* q) {
+  unsigned int v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(q) : "memory");
+  return v;
+}
+__device__ __forceinline__ void red_add_release_sys(unsigned int* q, unsigned int v) {
+  asm volatile("red.release.sys.global.add.u32 [%0], %1;" ::"l"(q), "r"(v) : "memory");
+}
+
 // ---- row epilogue (one thread per row) ---------------------------------------------------------
 __device__ __forceinline__ float load_logit(const void* base, int dtype, int64_t idx) {
   if (dtype == kBF16) return __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(base)[idx]);
@@ -202,6 +238,12 @@ __device__ __forceinline__ void row_epilogue(const LogitsFwdParams& p, int64_t r
   if (p.raw_min) p.raw_min[row] = st.mn;
   if (p.mode == kModePartial) {
     // (raw max, S, W, raw label logit or 0) for the cross-shard combine
+    if (p.push_world > 0) {
+      for (int r = 0; r < p.push_world; ++r)
+        st_weak_v4(push_slot_ptr(p.push_base[r], p.push_slot, p.push_world, p.push_rank, p.push_tmax, row), st.m,
+                   st.s, st.w, xl);
+      return;
+    }
     p.part_m[row] = st.m;
     p.part_s[row] = st.s;
     p.part_w[row] = st.w;
@@ -256,6 +298,69 @@ __device__ __forceinline__ void loss_finalize(const LogitsFwdParams& p, const Lo
     p.loss_out[0] = static_cast<float>(sum / denom);
     p.inv_count_out[0] = static_cast<float>(1.0 / denom);
     *ticket = 0u;
+  }
+}
+
+// Second half of the push exchange, run by the consumer threads of every CTA after its last row (see above).
+template <int kCons>
+__device__ __forceinline__ void push_finish(const LogitsFwdParams& p, unsigned int rows_done, int tid, int* ok_sm) {
+  const int R = p.push_world;
+  named_bar_sync(1 + kRedSlots, kCons);              // the epilogue stores of all warps of this CTA are issued
+  if (tid == 0) {
+    __threadfence_system();                          // ... and performed before the ticket that announces them
+    // one announcement per RANK, not per CTA (592 CTAs x 8 ranks of same-address atomics over NVLink cost ~25 us at the
+    // end of every step): CTAs take a ticket in local memory, the last one tells every rank "T more rows from me"
+    unsigned int* ticket = reinterpret_cast<unsigned int*>(p.push_base[p.push_rank]) + 4 + p.push_slot;
+    if (atomicAdd(ticket, 1u) == gridDim.x - 1) {
+      __threadfence_system();                        // (acquire side of the ticket chain, release side of the adds)
+      *ticket = 0u;                                  // next use of this slot: two steps from now
+      for (int r = 0; r < R; ++r)
+        red_add_release_sys(reinterpret_cast<unsigned int*>(p.push_base[r]) + p.push_slot,
+                            static_cast<unsigned int>(p.T));
+    }
+    const unsigned int* mine = reinterpret_cast<const unsigned int*>(p.push_base[p.push_rank]) + p.push_slot;
+    const long long t0 = clock64();
+    int ok = 1;
+    // counts only grow; the signed difference survives wrap-around
+    while (static_cast<int>(ld_acquire_sys(mine) - p.push_target) < 0) {
+      if (clock64() - t0 > p.push_timeout) {
+        ok = 0;
+        break;
+      }
+      __nanosleep(200);
+    }
+    if (!ok) atomicExch(p.push_status, 1);
+    *ok_sm = ok;
+  }
+  named_bar_sync(1 + kRedSlots, kCons);
+  if (!*ok_sm) return;                               // a rank never delivered: outputs untouched, status says so
+  const float c2 = p.inv_temperature * kLog2e;
+  const int64_t per = (p.T + gridDim.x - 1) / gridDim.x;
+  const int64_t t_end = (blockIdx.x + 1) * per < p.T ? (blockIdx.x + 1) * per : p.T;
+  for (int64_t t = blockIdx.x * per + tid; t < t_end; t += kCons) {
+    // two passes over the R partials of the row (the second one hits L2): the maximum, then the sums in rank order
+    const float4* q0 = push_slot_ptr(p.push_base[p.push_rank], p.push_slot, R, 0, p.push_tmax, t);
+    float XL = 0.f, M = -INFINITY;
+    for (int r = 0; r < R; ++r) {
+      const float4 q = ld_sys_v4(q0 + int64_t(r) * p.push_tmax);
+      XL += q.w;
+      M = fmaxf(M, q.x);
+    }
+    float S = 0.f, W = 0.f;
+    for (int r = 0; r < R; ++r) {
+      const float4 q = ld_sys_v4(q0 + int64_t(r) * p.push_tmax);
+      if (q.x != -INFINITY) {
+        const float d = (q.x - M) * c2;
+        const float f = exp2f(d);
+        S = fmaf(q.y, f, S);
+        W = fmaf(f, fmaf(d, q.y, q.z), W);
+      }
+    }
+    const float ln_s = logf(S);
+    p.logp[t] = (XL - M) * p.inv_temperature - ln_s;
+    if (p.entropy) p.entropy[t] = ln_s - kLn2 * (W / S);
+    p.row_max[t] = M;
+    p.ln_s[t] = ln_s;
   }
 }
 
@@ -360,6 +465,10 @@ logits_fwd_tma_kernel(const LogitsFwdParams p) {
       }
     }
     if (row_reduce_rot<kMinMax, kCW>(st, &red, it, warp, lane, c2)) row_epilogue(p, row, st, acc);
+  }
+  if (p.mode == kModePartial && p.push_world > 0) {
+    push_finish<kConsumers>(p, static_cast<unsigned int>(it), tid, reinterpret_cast<int*>(acc_sm));
+    return;
   }
   if (p.mode == kModeFusedActor) {
     // every warp's lane 0 holds the loss terms of the rows it finished: add them up in warp order
@@ -788,7 +897,18 @@ int launch_logits_fwd(const LogitsFwdParams& p, cudaStream_t stream) {
                                    cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));       \
       done[dev] = true;                                                                            \
     }                                                                                              \
-    logits_fwd_tma_kernel<MM, E, W><<<grid_for(p.T, 16 / W), (W + 1) * 32, smem, stream>>>(p);     \
+    int per_sm = 16 / W;                                                                           \
+    if (p.push_world > 0) {                        /* its CTAs wait for each other: all co-resident */ \
+      int occ = 0;                                                                                 \
+      AB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, logits_fwd_tma_kernel<MM, E, W>, \
+                                                            (W + 1) * 32, smem));                  \
+      if (occ < 1) {                                                                               \
+        set_error("logits_partial_push: the kernel does not fit an SM");                           \
+        return kCudaError;                                                                         \
+      }                                                                                            \
+      if (occ < per_sm) per_sm = occ;                                                              \
+    }                                                                                              \
+    logits_fwd_tma_kernel<MM, E, W><<<grid_for(p.T, per_sm), (W + 1) * 32, smem, stream>>>(p);     \
   }
 #define AB_LAUNCH_FWD(MM, E)                                                       \
   {                                                                                \
@@ -808,6 +928,19 @@ int launch_logits_fwd(const LogitsFwdParams& p, cudaStream_t stream) {
     else logits_fwd_generic_kernel<float><<<grid, kConsumers, 0, stream>>>(p);
   }
   return check_launch("logits_fwd");
+}
+
+int64_t vocab_push_buffer_bytes(int64_t max_tokens, int world) {
+  return kPushHeaderBytes + 2 * int64_t(world) * max_tokens * int64_t(sizeof(float4));
+}
+
+int launch_logits_partial_push(const LogitsFwdParams& p, cudaStream_t stream) {
+  if (p.T == 0) return kOk;                  // (every rank has the same T: nobody waits for rows of an empty step)
+  if (!tma_ok(p.logits, p.dtype, p.V, p.row_stride_bytes)) {
+    set_error("logits_partial_push: rows must be 16-byte aligned (base, row width and row stride)");
+    return kInvalidArgument;
+  }
+  return launch_logits_fwd(p, stream);
 }
 
 int launch_logits_bwd(const LogitsBwdParams& p, cudaStream_t stream) {

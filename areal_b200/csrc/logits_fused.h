@@ -33,6 +33,14 @@ struct LogitsFwdParams {
   uint8_t *clip_mask, *dual_clip_mask, *behave_mask;
   float *loss_out, *inv_count_out;
   void* workspace;
+  // partial mode, push exchange (one launch for partial + exchange + combine): see launch_logits_partial_push
+  int push_world;               // 0: off
+  int push_rank, push_slot;
+  int64_t push_tmax;
+  unsigned int push_target;     // cumulative number of rows all ranks will have delivered into a buffer's slot
+  long long push_timeout;
+  int* push_status;
+  char* push_base[16];          // every rank's exchange buffer (symmetric memory), this GPU's mapping
 };
 
 struct LogitsBwdParams {
@@ -66,6 +74,12 @@ int launch_legacy_entropy(const void* logits, int dtype, int64_t T, int64_t V, i
                           cudaStream_t stream);
 int launch_vocab_combine(const float* parts, int R, int64_t T, float inv_t, float* logp,
                          float* entropy, float* row_max, float* ln_s, cudaStream_t stream);
+
+// partial statistics of a vocabulary shard PUSHED into every rank's exchange buffer from the row epilogue, then --
+// same launch -- combined into the full-vocabulary results once every rank's rows are in (p.push_* set, mode partial,
+// p.logp / entropy / row_max / ln_s = the combined outputs)
+int64_t vocab_push_buffer_bytes(int64_t max_tokens, int world);
+int launch_logits_partial_push(const LogitsFwdParams& p, cudaStream_t stream);
 
 int launch_vocab_combine_p2p(void* const* peer_bases, int rank, int R, int64_t T, int64_t Tmax, int slot,
                              unsigned int epoch, float inv_t, long long timeout_cycles, float* logp, float* entropy,

@@ -184,6 +184,69 @@ class PeerExchange:
             raise RuntimeError("areal_b200 peer exchange: a rank did not publish its partials in time")
 
 
+class FusedPeerExchange:
+    """The vocab-sharded forward as ONE launch (areal_b200_logits_partial_fwd_push): the streaming kernel's row epilogue
+    stores a row's four partial numbers into EVERY rank's exchange buffer over NVLink (plain 16-byte stores into
+    peer-mapped symmetric memory), a CTA that has finished its rows announces their number to every rank, and once a
+    rank's counter says that all R*T rows are in, the same CTAs combine them from local memory.  The transfer rides
+    under the streaming pass: no all-gather, no second launch, no remote reads.  Same bits as `PeerExchange` and as the
+    all-gather path.
+
+    One instance per (group, stream of use); `max_tokens` bounds T.  All ranks must call `forward` the same number of
+    times with the same T (the step counter picks the buffer slot; the expected row count is cumulative)."""
+
+    TIMEOUT_CYCLES = 20_000_000_000          # ~10 s of SM clocks: a rank that never delivers is an error, not a hang
+
+    def __init__(self, max_tokens: int, group=None, device=None):
+        import torch.distributed._symmetric_memory as symm
+        if not dist.is_initialized():
+            raise RuntimeError("FusedPeerExchange needs an initialised process group")
+        self.group = dist.group.WORLD if group is None else group
+        self.rank, self.world = dist.get_rank(self.group), dist.get_world_size(self.group)
+        if self.world > 16:
+            raise ValueError("FusedPeerExchange supports at most 16 ranks")
+        self.max_tokens = int(max_tokens)
+        dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self.device = dev
+        nbytes = int(_lib.lib().areal_b200_vocab_push_buffer_bytes(self.max_tokens, self.world))
+        try:
+            symm.enable_symm_mem_for_group(self.group.group_name)
+        except Exception:
+            pass                              # newer torch enables groups on demand
+        self.buf = symm.empty(nbytes, dtype=torch.uint8, device=dev)
+        self.buf.zero_()
+        self.handle = symm.rendezvous(self.buf, self.group)
+        self._peers = (ctypes.c_void_p * self.world)(*[int(p) for p in self.handle.buffer_ptrs])
+        self.status = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.epoch = 0
+        self.rows_target = [0, 0]             # per slot: rows delivered by all ranks over all steps so far
+        torch.cuda.synchronize(dev)
+        dist.barrier(self.group)              # every buffer is zeroed before anybody's first row lands
+
+    def forward(self, shard: torch.Tensor, labels: torch.Tensor, vocab_start: int, temperature: float,
+                raw_min: Optional[torch.Tensor] = None):
+        T, V = shard.shape
+        if T > self.max_tokens:
+            raise ValueError(f"T={T} exceeds the exchange buffer ({self.max_tokens} tokens)")
+        dev = self.device
+        self.epoch += 1
+        slot = self.epoch & 1
+        self.rows_target[slot] = (self.rows_target[slot] + self.world * T) & 0xFFFFFFFF
+        f32 = dict(dtype=torch.float32, device=dev)
+        logp, ent, row_max, ln_s = (torch.empty(T, **f32) for _ in range(4))
+        with torch.cuda.device(dev):
+            call("areal_b200_logits_partial_fwd_push", ptr(shard), _lib.DTYPE_CODE[shard.dtype], T, V,
+                 shard.stride(0) if T > 1 else V, ptr(labels), int(vocab_start), float(temperature), self._peers,
+                 self.rank, self.world, self.max_tokens, self.epoch, self.rows_target[slot], self.TIMEOUT_CYCLES,
+                 ptr(logp), ptr(ent), ptr(row_max), ptr(ln_s), ptr(raw_min), ptr(self.status), stream_ptr(dev))
+        return logp, ent, row_max, ln_s
+
+    def check(self):
+        """Host sync: raises if some step timed out waiting for a rank's rows."""
+        if int(self.status.item()) != 0:
+            raise RuntimeError("areal_b200 fused peer exchange: a rank did not deliver its rows in time")
+
+
 def vocab_parallel_forward(shard: torch.Tensor, labels: torch.Tensor, vocab_start: int, temperature: float,
                            group=None, partials_fn: Optional[Callable] = None,
                            combine_fn: Optional[Callable] = None):

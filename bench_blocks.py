@@ -441,6 +441,14 @@ class Blocks:
                 same = same and all(torch.equal(u, v) for u, v in zip(a, b))
             ex.check()
             checks["peer_exchange_bit_identical_to_all_gather"] = bool(same)
+            fx = D.FusedPeerExchange(max_tokens=4096)
+            same = True
+            for Tp in (96, 1, 77, 96):
+                a = D.vocab_parallel_forward(sh[:Tp], lab_ok[:Tp], lo, 0.9)
+                b = fx.forward(sh[:Tp], lab_ok[:Tp], lo, 0.9)
+                same = same and all(torch.equal(u, v) for u, v in zip(a, b))
+            fx.check()
+            checks["fused_push_exchange_bit_identical_to_all_gather"] = bool(same)
         except Exception as exc:
             checks["peer_exchange"] = "unavailable: " + repr(exc)[:120]
         flags = torch.tensor([int(all(v for v in checks.values() if isinstance(v, bool)))], device=self.dev)
@@ -463,13 +471,18 @@ class Blocks:
                "tokens": T, "shard_width": Vs, "l2": "shard larger than L2"}
         try:
             ex = D.PeerExchange(max_tokens=T)
+            fx = D.FusedPeerExchange(max_tokens=T)
         except Exception as exc:
-            ex, out["peer_memory"] = None, {"unavailable": repr(exc)[:200]}
+            ex, fx, out["peer_memory"] = None, None, {"unavailable": repr(exc)[:200]}
         x = shard.requires_grad_()
         fwd_bytes = 2.0 * T * Vs
         bwd_bytes = 2.0 * T * Vs * (1.0 + active)
-        for name, exch in (("allgather", None), ("peer_memory", ex)):
-            if name == "peer_memory" and ex is None:
+        out["variants"] = {"allgather": "partial kernel, NCCL all-gather of the partials, combine kernel",
+                           "peer_memory": "partial kernel, combine kernel that reads the peers' partials over NVLink",
+                           "fused_push": "ONE launch: the streaming kernel's row epilogue stores the partials into every "
+                                         "rank's buffer over NVLink, the same CTAs combine once all rows are in"}
+        for name, exch in (("allgather", None), ("peer_memory", ex), ("fused_push", fx)):
+            if exch is None and name != "allgather":
                 continue
 
             def fwd():
@@ -492,6 +505,27 @@ class Blocks:
         parts = D._cuda_partials(shard.detach(), labels, self.rank * Vs, 1.0)
         ms_x = self.time_ms(lambda: D.gather_partials(parts), iters=20, warmup=5)
         out["partial_kernel"] = self.frac(fwd_bytes, ms_k)
+        # Why the synchronised forward costs more than the slowest rank's kernel ALONE: every step waits for the rank
+        # that happens to be slowest in THAT step.  Per-step kernel times of every rank (one event pair per step, the
+        # ranks released together by a barrier), then mean over steps of the max over ranks against the max over
+        # ranks of the per-rank means.
+        n_it = 20
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(n_it)]
+        for a, b in evs:
+            dist.barrier()
+            a.record()
+            D._cuda_partials(shard.detach(), labels, self.rank * Vs, 1.0)
+            b.record()
+        torch.cuda.synchronize(self.dev)
+        mine = torch.tensor([a.elapsed_time(b) for a, b in evs], device=self.dev)
+        allt = [torch.empty_like(mine) for _ in range(self.world)]
+        dist.all_gather(allt, mine)
+        allt = torch.stack(allt)                                     # [ranks, steps]
+        out["partial_kernel_per_step"] = {
+            "steps": n_it, "max_over_ranks_of_mean_ms": float(allt.mean(1).max()),
+            "mean_over_steps_of_max_over_ranks_ms": float(allt.max(0).values.mean()),
+            "fastest_rank_mean_ms": float(allt.mean(1).min()), "slowest_single_step_ms": float(allt.max()),
+            "note": "a synchronised step (any exchange) costs the second figure plus the exchange, not the first"}
         out["all_gather_us"] = ms_x * 1e3
         out["nccl_payload_bytes_per_rank"] = 16 * T
         # full-size properties (size-independent): log-prob <= 0, 0 <= entropy <= ln V, gradient rows sum to 0

@@ -371,6 +371,31 @@ AREAL_B200_API int areal_b200_vocab_combine_p2p(void* const* peer_bases, int ran
                                                 float* entropy, float* row_max, float* ln_sumexp,
                                                 int* status, void* stream);
 
+/* Vocab-sharded forward as ONE launch: partial statistics of this rank's shard, their exchange over NVLink and the
+ * combine (replaces, like the pair above, the six all-reduces of areal/utils/mcore/functional.py:16-31 + Megatron's
+ * vocab_parallel_cross_entropy; arguments of the shard as in areal_b200_logits_partial_fwd).
+ *   Every rank owns a peer-mapped ("symmetric") buffer of areal_b200_vocab_push_buffer_bytes(Tmax, R) bytes, ZEROED
+ *   once: u32 rows_in[2] | u32 pad[2] | u32 ticket[2] | pad to 256 B | float4 parts[2][R][Tmax].  peer_bases as above.
+ *   The row epilogue of the streaming kernel stores a row's (max, S, W, x_label) into every rank's buffer (plain
+ *   16-byte stores, slot e & 1); a CTA that has finished its rows fences and takes a local ticket, the rank's last CTA
+ *   adds T to rows_in[e & 1] of every rank (system-scope release), and every CTA
+ *   waits (at most timeout_cycles SM clocks) until its own counter has reached rows_target -- the CUMULATIVE number
+ *   of rows delivered to that slot over all steps so far, i.e. the caller adds R*T for every step that used the
+ *   slot (mod 2^32) -- and then combines its share of the rows from local memory, in rank order: bit-identical to
+ *   areal_b200_vocab_combine on the gathered parts.  All ranks call with the same T and e = 1, 2, 3, ...
+ *   raw_min (f32[T], may be NULL): row minimum of THIS shard, from the same pass.
+ *   *status (device int, zeroed by the caller) is set to 1 if some rank's rows did not arrive in time; the outputs
+ *   are then left untouched.  Rows must be 16-byte aligned (base, row width, row stride). */
+AREAL_B200_API int64_t areal_b200_vocab_push_buffer_bytes(int64_t max_tokens, int world_size);
+AREAL_B200_API int areal_b200_logits_partial_fwd_push(const void* logits, int dtype, int64_t T, int64_t V,
+                                                      int64_t row_stride, const int64_t* labels,
+                                                      int64_t vocab_start, double temperature,
+                                                      void* const* peer_bases, int rank, int world_size,
+                                                      int64_t max_tokens, int64_t epoch, int64_t rows_target,
+                                                      int64_t timeout_cycles, float* logp, float* entropy,
+                                                      float* row_max, float* ln_sumexp, float* raw_min,
+                                                      int* status, void* stream);
+
 /* Token log-prob + CLAMPED softmax entropy of the AEnt recipe, and their gradient.  Replaces
  * `gather_logprobs_clamped_entropy` / `clamped_softmax_entropy` (recipe/AEnt/functional.py:15-80): the
  * k = int(V * entropy_clamp) smallest logits of every row are left out of the entropy's softmax.  The

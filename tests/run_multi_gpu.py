@@ -113,6 +113,49 @@ def main():
         if rank == 0:
             print("P2P_OK", world, {k: round(v, 1) for k, v in res.items()}, "us per call")
 
+    # ---------------- ONE launch: partials pushed into every rank's buffer by the streaming kernel, combined there ----
+    try:
+        fx = D.FusedPeerExchange(max_tokens=4096)
+    except Exception as exc:                                  # no peer mapping on this box: reported, not fatal
+        fx = None
+        if rank == 0:
+            print("P2P_PUSH_UNAVAILABLE", repr(exc)[:300])
+    if fx is not None:
+        for step, Tp in enumerate((96, 1, 4096, 777, 0, 96, 3000, 5)):   # both slots several times, ragged and empty T
+            gp = torch.Generator(device=dev).manual_seed(200 + step)
+            lg_p = (torch.randn(max(Tp, 1), V, generator=gp, device=dev) * 2).bfloat16()[:Tp]
+            lab_p = torch.randint(0, V, (Tp,), generator=gp, device=dev)
+            sh = lg_p[:, rank * Vs:(rank + 1) * Vs].contiguous()
+            a = D.vocab_parallel_forward(sh, lab_p, rank * Vs, 0.9) if Tp else None
+            mn = torch.empty(Tp, dtype=torch.float32, device=dev)
+            b = fx.forward(sh, lab_p, rank * Vs, 0.9, raw_min=mn)
+            if Tp:
+                for u, v in zip(a, b):
+                    assert torch.equal(u, v), (step, Tp, (u - v).abs().max())
+                assert torch.equal(mn, sh.float().min(dim=-1).values), (step, Tp)
+        fx.check()
+        # autograd path through the fused exchange
+        shard3 = logits[:, rank * Vs:(rank + 1) * Vs].detach().clone().requires_grad_()
+        lp3, ent3 = D.vocab_parallel_logprobs_entropy(shard3, labels, 0.9, exchange=fx)
+        ((lp3 * w_lp).sum() + (ent3 * w_h).sum()).backward()
+        assert torch.equal(lp3, lp) and torch.equal(ent3, ent) and torch.equal(shard3.grad, shard.grad)
+        Tp = 4096
+        sh = (torch.randn(Tp, Vs, generator=g, device=dev) * 2).bfloat16()
+        lab_p = torch.randint(0, V, (Tp,), generator=g, device=dev)
+        for _ in range(5):
+            fx.forward(sh, lab_p, rank * Vs, 0.9)
+        dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(50):
+            fx.forward(sh, lab_p, rank * Vs, 0.9)
+        e1.record()
+        torch.cuda.synchronize()
+        fx.check()
+        if rank == 0:
+            print("P2P_PUSH_OK", world, round(e0.elapsed_time(e1) / 50 * 1e3, 1), "us per call (one launch)")
+
     # ---------------- parameter reallocation: slice straight into the neighbour's staging buffer -----------
     from areal_b200 import flatten_param as FP
     try:

@@ -54,6 +54,9 @@ def test_nccl_sharded_paths(world):
     # the NVLink peer-memory exchange ran bit-identically to the all-gather path, or the box cannot map peers
     assert f"P2P_OK {world}" in r.stdout or "P2P_UNAVAILABLE" in r.stdout, r.stdout[-2000:]
     print(next(line for line in r.stdout.splitlines() if line.startswith("P2P_")))
+    # ... and so did the one-launch variant (partials pushed from the streaming kernel's row epilogue)
+    assert f"P2P_PUSH_OK {world}" in r.stdout or "P2P_PUSH_UNAVAILABLE" in r.stdout, r.stdout[-2000:]
+    print(next(line for line in r.stdout.splitlines() if line.startswith("P2P_PUSH_")))
     # slice_intervals wrote into the neighbour's staging buffer over NVLink, bit-exact, or no peer mapping here
     assert f"PEERBUF_OK {world}" in r.stdout or "PEERBUF_UNAVAILABLE" in r.stdout, r.stdout[-2000:]
     print(next(line for line in r.stdout.splitlines() if line.startswith("PEERBUF_")))
