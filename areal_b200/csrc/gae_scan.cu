@@ -357,17 +357,41 @@ gae1d_kernel(const Gae1dParams p) {
   }
 
   // block-wide suffix scan: warp shuffle, then warps through shared memory
-  Affine inc = agg;
+  Affine inc = agg, nxt;
+  bool by_ballot = false;
+  if constexpr (kT == 64 && !kCluster) by_ballot = __all_sync(0xffffffffu, plain);
+  if (by_ballot) {
+    // Every lane's map is (gl^8, b) or (0, b): the `a` halves need no shuffles.  One ballot says which lanes hold a
+    // sequence end; a lane's span of d lanes passes the right-hand part on iff none of them does, with the factor
+    // gl^(8d) (squared from round to round); the factor of the lane's whole suffix, gl^(8(32 - lane)), is put together
+    // from the same powers by the bits of its exponent.  Half the shuffles and selects of the general scan below.
+    const unsigned int mine = __ballot_sync(0xffffffffu, last_bits != 0u) >> lane;   // bit j: lane + j ends a sequence
+    const double gl2 = gl * gl, gl4 = gl2 * gl2, g8 = gl4 * gl4;
+    double b = agg.b, P = g8, apow = 1.0;           // apow -> gl^(8(31 - lane)): the suffix that starts at lane + 1
+    const int e = 31 - lane;
 #pragma unroll
-  for (int d = 1; d < 32; d <<= 1) {
-    const Affine o = shfl_down(inc, d);
-    if (lane + d < 32) inc = compose(inc, o);
+    for (int d = 1; d < 32; d <<= 1) {
+      const double ob = __shfl_down_sync(0xffffffffu, b, d);
+      if (lane + d < 32 && (mine & ((1u << d) - 1u)) == 0u) b = fma(P, ob, b);
+      if (e & d) apow *= P;
+      if (d < 16) P *= P;
+    }
+    inc.a = mine ? 0.0 : apow * g8;
+    inc.b = b;
+    nxt.a = (mine >> 1) ? 0.0 : apow;
+    nxt.b = __shfl_down_sync(0xffffffffu, b, 1);
+  } else {
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const Affine o = shfl_down(inc, d);
+      if (lane + d < 32) inc = compose(inc, o);
+    }
+    nxt = shfl_down(inc, 1);
   }
   if (lane == 0) wsm[warp] = inc;
   __syncthreads();
   Affine W = ident();
   for (int w = kWarps - 1; w > warp; --w) W = compose(wsm[w], W);
-  const Affine nxt = shfl_down(inc, 1);
   const Affine excl = (lane < 31) ? compose(nxt, W) : W;
 
   double carry = 0.0;

@@ -85,6 +85,23 @@ int main() {
     cudaEventRecord(e1); cudaEventSynchronize(e1); cudaEventElapsedTime(&ms, e0, e1);
     printf("  + prefetch.global.L2 %lld CTAs ahead: %.1f us, %.0f GB/s\n", dist, ms * 100, 16.0 * n / (ms / 10 * 1e-3) / 1e9);
   }
+  // is prefetch.global.L2 effective at all?  The same chain at ONE resident CTA per SM (200 KB of dynamic shared memory):
+  // latency-bound, so turning the next CTAs' DRAM misses into L2 hits must show if the prefetches are honoured
+  cudaFuncSetAttribute(chain_64<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+  cudaFuncSetAttribute(chain_64<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+  {
+    const long long m4 = n4 / 16;
+    cudaEventRecord(e0);
+    for (int i = 0; i < 3; ++i) chain_64<false><<<(unsigned)(m4 / 128), 64, 200 * 1024>>>(a, b, c, d, m4, 0);
+    cudaEventRecord(e1); cudaEventSynchronize(e1); cudaEventElapsedTime(&ms, e0, e1);
+    printf("1 CTA/SM, dependent chain, no prefetch: %.1f us for 2^23 elements, %.0f GB/s\n", ms / 3 * 1e3, 16.0 * n / 16 / (ms / 3 * 1e-3) / 1e9);
+    for (long long dist = 148; dist <= 148 * 16; dist *= 4) {
+      cudaEventRecord(e0);
+      for (int i = 0; i < 3; ++i) chain_64<true><<<(unsigned)(m4 / 128), 64, 200 * 1024>>>(a, b, c, d, m4, dist);
+      cudaEventRecord(e1); cudaEventSynchronize(e1); cudaEventElapsedTime(&ms, e0, e1);
+      printf("  + prefetch.global.L2 %lld CTAs ahead: %.1f us, %.0f GB/s\n", dist, ms / 3 * 1e3, 16.0 * n / 16 / (ms / 3 * 1e-3) / 1e9);
+    }
+  }
   for (int i = 0; i < 3; ++i) copy2<<<148 * 8, 256>>>(a, c, n4);
   cudaEventRecord(e0);
   for (int i = 0; i < 10; ++i) copy2<<<148 * 8, 256>>>(a, c, n4);
