@@ -480,7 +480,7 @@ def run_ours(args):
     from bench_blocks import Blocks
     blk = Blocks(torch, dist, dev, world, rank, local_rank, peak, Clocked, EngineLoop)
     if world == 1:
-        for name in ("gae_sweep", "intervals", "cfg2_step", "kernels"):
+        for name in ("e2e_from_hidden", "gae_sweep", "intervals", "cfg2_step", "kernels"):
             if want(name) and not args.skip_blocks:
                 line[name] = blk.run(name)
     else:

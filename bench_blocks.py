@@ -334,6 +334,101 @@ class Blocks:
         rows += self._lm_head_rows()
         return {"rows": rows}
 
+    def e2e_from_hidden(self):
+        """LABELLED EXTRA, not the headline `e2e`: the same step at a different boundary -- the engine hands over the
+        last hidden state [T, H] and the LM-head weight instead of [T, V] logits (areal_b200.actor.
+        grpo_loss_fn_from_hidden) -- with host buffers: every step copies the hidden state (50 MB instead
+        of 4.98 GB) and the per-token vectors from pinned host memory, runs packed GAE + loss forward + backward down
+        to d_hidden / d_weight, and reads back the loss and the advantages / returns.  The weight stays on the device
+        (it is a parameter)."""
+        torch = self.torch
+        import functools as ft
+        from areal_b200 import actor as A, ppo_functional as P, stats_tracker as ST
+        T, Hd = 16384, 1536
+        g = torch.Generator(device=self.dev).manual_seed(3)
+        weight = (torch.randn(V, Hd, generator=g, device=self.dev) * 0.03).bfloat16().requires_grad_()
+        rng = np.random.RandomState(3)
+        lens, left = [], T
+        while left > 0:
+            n = min(left, int(rng.randint(128, 4097)))
+            lens.append(n)
+            left -= n
+        B = len(lens)
+        dev_in = dict(hidden=torch.randn(T, Hd, generator=g, device=self.dev).bfloat16(),
+                      labels=torch.randint(0, V, (T,), generator=g, device=self.dev),
+                      loss_mask=torch.rand(T, generator=g, device=self.dev) > 0.15,
+                      advantages=torch.randn(T, generator=g, device=self.dev),
+                      old_logp=-torch.rand(T, generator=g, device=self.dev) * 5,
+                      prox_logp=-torch.rand(T, generator=g, device=self.dev) * 5,
+                      rewards=torch.randn(T, generator=g, device=self.dev),
+                      values=torch.randn(T + B, generator=g, device=self.dev),
+                      cu_seqlens=torch.from_numpy(np.concatenate([[0], np.cumsum(lens)]).astype(np.int32)).to(self.dev),
+                      bootstrap=torch.rand(B, generator=g, device=self.dev) > 0.5)
+        host = {}
+        for k, t in dev_in.items():
+            host[k] = torch.empty(t.shape, dtype=t.dtype, device="cpu", pin_memory=True)
+            host[k].copy_(t)
+        dst2 = [{k: torch.empty_like(t) for k, t in dev_in.items()} for _ in range(2)]
+        out_host = {k: torch.empty(T, dtype=torch.float32, pin_memory=True) for k in ("adv", "ret")}
+        loss_host = torch.empty((), dtype=torch.float32, pin_memory=True)
+        h2d = sum(h.numel() * h.element_size() for h in host.values())
+        copy_stream, main = torch.cuda.Stream(self.dev), torch.cuda.current_stream(self.dev)
+        copied = [torch.cuda.Event() for _ in range(2)]
+        consumed = [torch.cuda.Event() for _ in range(2)]
+        for e in consumed:
+            e.record(main)
+        tracker = ST.DistributedStatsTracker()
+        loss_fn = ft.partial(A.grpo_loss_fn_from_hidden, temperature=1.0, tracker=tracker, **CFG)
+
+        def upload(i):
+            s = i & 1
+            copy_stream.wait_event(consumed[s])
+            with torch.cuda.stream(copy_stream):
+                for k in host:
+                    dst2[s][k].copy_(host[k], non_blocking=True)
+                copied[s].record(copy_stream)
+
+        def compute(i):
+            s = i & 1
+            d = dst2[s]
+            main.wait_event(copied[s])
+            h = d["hidden"].requires_grad_()
+            adv, ret = P.cugae1d_nolp_misalign_func(d["rewards"], d["values"], d["cu_seqlens"], d["bootstrap"], 1.0, 0.95)
+            mb = dict(input_ids=d["labels"], rolled_input_ids=d["labels"], logprobs=d["old_logp"],
+                      prox_logp=d["prox_logp"], advantages=d["advantages"], loss_mask=d["loss_mask"])
+            loss = loss_fn(h, weight, mb)
+            loss.backward()
+            loss_host.copy_(loss.detach(), non_blocking=True)
+            out_host["adv"].copy_(adv, non_blocking=True)
+            out_host["ret"].copy_(ret, non_blocking=True)
+            h.grad = None
+            weight.grad = None
+            d["hidden"] = h.detach()
+            consumed[s].record(main)
+
+        def run(n):
+            upload(0)
+            for i in range(n):
+                if i + 1 < n:
+                    upload(i + 1)
+                compute(i)
+        run(2)
+        torch.cuda.synchronize(self.dev)
+        steps = 5
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        run(steps)
+        e1.record()
+        torch.cuda.synchronize(self.dev)
+        ms = e0.elapsed_time(e1) / steps
+        tracker.export()
+        return {"label": "EXTRA, another boundary than `e2e`: hidden state [T, H] in, no [T, V] tensor anywhere",
+                "api": "areal_b200.actor.grpo_loss_fn_from_hidden (row blocks: library GEMM for the block's logits, "
+                       "our single-pass kernel, two library GEMMs for d_hidden / d_weight)",
+                "tokens": T, "hidden_size": Hd, "vocab": V, "value": T / (ms * 1e-3), "unit": "tokens/s",
+                "ms_per_step": ms, "steps": steps, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4 + 8 * T,
+                "loss": float(loss_host)}
+
     def _graph_time(self, fn, iters=5):
         """ms per replay of `fn` captured once in a CUDA graph: GPU time without the wrappers' host time"""
         torch = self.torch
