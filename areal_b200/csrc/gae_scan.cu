@@ -1451,23 +1451,33 @@ int launch_gae1d_static(Gae1dParams p, cudaStream_t stream) {
   return check_launch("gae1d (static scratch)");
 }
 
-constexpr int kPaddedThreadsDefault = 256;
-
 static bool aligned16(const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; }
 
-// CTA width of the padded kernels: AREAL_B200_PADDED_THREADS = 64 | 128 | 256 overrides the default (benchmarks)
-static int padded_threads() {
-  static const int v = [] {
+// CTA width of the padded kernels (one CTA walks a row's tiles right to left; tile = 8 x width tokens).  Narrow CTAs keep
+// more rows in flight per SM and stall fewer warps at the two barriers of a tile; wide CTAs need fewer serial tiles per
+// row.  Measured on one box (GPU time, plain / fused): [4096, 4096] 256 threads 68.5 / 201 us, 128: 59.5 / 147, 64: 56.8 /
+// 135; [2048, 8192] 68.2 / 178, 60.8 / 144, 54.4 / 160; [1024, 2048] 12.1, 9.9, 10.7; [512, 4096] 11.7 / 44.6, 12.8 / 44.9,
+// 15.7 / 42.4; [256, 16384] 27.3 / 55, 35.8 / 68, 51.4 / 94.  Hence: many rows -> narrow, few rows -> wide.
+// AREAL_B200_PADDED_THREADS = 64 | 128 | 256 overrides the choice (benchmarks).
+static int padded_threads(bool fused, int64_t B, int64_t S) {
+  static const int forced = [] {
     const char* e = getenv("AREAL_B200_PADDED_THREADS");
     const int t = e ? atoi(e) : 0;
-    return (t == 64 || t == 128 || t == 256) ? t : kPaddedThreadsDefault;
+    return (t == 64 || t == 128 || t == 256) ? t : 0;
   }();
-  return v;
+  if (forced) return forced;
+  const int64_t sms = num_sms();
+  if (fused) {
+    if (B >= 10 * sms && S <= 4096) return 64;
+    return B >= 4 * sms ? 128 : 256;
+  }
+  if (B >= 10 * sms) return 64;
+  return B >= 5 * sms ? 128 : 256;
 }
 
 template <bool kFused>
 static void launch_padded_t(const GaePaddedParams& p, const AdvFusedParams& f, cudaStream_t stream) {
-  const int t = padded_threads();
+  const int t = padded_threads(kFused, p.B, p.S);
   const int64_t cap = int64_t(num_sms()) * (2048 / t);
   const unsigned int grid = static_cast<unsigned int>(p.B < cap ? p.B : cap);
   if (t == 64) gae_padded_kernel<kFused, 64><<<grid, 64, 0, stream>>>(p, f);
