@@ -493,7 +493,17 @@ int launch_fused_rowres(const LogitsFwdParams& p, void* dlogits, int64_t d_row_s
     set_error("row-resident path: no cluster of %d CTAs with %zu bytes of shared memory fits", C, smem);
     return kUnsupported;
   }
-  const int64_t ncl = p.T < max_clusters ? p.T : max_clusters;
+  int64_t ncl = p.T < max_clusters ? p.T : max_clusters;
+  {
+    // experiments: AREAL_B200_ROWRES_MAX_CLUSTERS caps the number of clusters (how the step scales with the SM count:
+    // 33 / 29 / 25 / 21 clusters of 4 -> 1.61 / 1.79 / 2.06 / 2.44 ms at T = 16,384, V = 151,936, i.e. time x clusters
+    // is constant within 4 %: the kernel is bound by the SMs that work on it, not yet by DRAM)
+    static const int cap = [] {
+      const char* e = getenv("AREAL_B200_ROWRES_MAX_CLUSTERS");
+      return e ? atoi(e) : 0;
+    }();
+    if (cap > 0 && ncl > cap) ncl = cap;
+  }
   cfg.gridDim = dim3(static_cast<unsigned int>(ncl * C));
   AB_CUDA(cudaLaunchKernelEx(&cfg, fused_rowres_kernel, p, dlogits, d_row_stride_bytes, loss_scale, buf_stride, nbuf));
   return check_launch("fused_rowres");
