@@ -33,6 +33,9 @@ constexpr size_t kHistBytes = size_t(kBins) * kSlots * sizeof(uint16_t);   // 12
 
 // order-preserving 16-bit key of a bf16 / fp16 bit pattern (sign-magnitude -> unsigned ascending)
 __device__ __forceinline__ uint32_t key16(uint32_t b) { return (b & 0x8000u) ? (~b & 0xffffu) : (b | 0x8000u); }
+__device__ __forceinline__ uint32_t key_to_bits(uint32_t key) {
+  return (key & 0x8000u) ? (key & 0x7fffu) : (~key & 0xffffu);
+}
 
 template <bool kIsBF16>
 __device__ __forceinline__ float half_to_f32(uint32_t b) {
@@ -310,6 +313,61 @@ clamped_entropy_bwd_kernel(const ClampedParams p, const float* __restrict__ g_lo
       uint4* dv = reinterpret_cast<uint4*>(d);
       constexpr int kU = 4;
       const int64_t nv = p.V >> 3;
+      // Lean path: the row-uniform tests (which gradients exist, clamp or not) and the label test leave the element
+      // loop; the threshold compares are float compares against the threshold VALUE, which order elements exactly
+      // like the 16-bit keys unless the threshold is a zero (-0 and +0 are different keys: such rows take the
+      // general loop below), and both exponents are one FFMA + MUFU.
+      const float tau_f = no_clamp ? -INFINITY : half_to_f32<kIsBF16>(key_to_bits(tau_key));
+      if (gh != 0.f && (no_clamp || tau_f != 0.f)) {
+        const float b1 = fmaf(-m, c2, nl2s), b2 = fmaf(-m, c2, nl2sk);
+        const float ngl = -gl, ngh = -gh, ngh_tie = no_clamp ? -gh : -gh * f_tie;
+        const int64_t lab_vec = (lab >= 0 && lab < p.V) ? (lab >> 3) : -1;
+        auto lean = [&](uint32_t b) -> float {
+          const float xv = half_to_f32<kIsBF16>(b);
+          const float lq2 = fmaf(xv, c2, b2);
+          const float q = ex2_approx(lq2);
+          const float e = ex2_approx(fmaf(xv, c2, b1));
+          float coef = xv > tau_f ? ngh : 0.f;           // kept / removed; the tie class gets its share
+          coef = xv == tau_f ? ngh_tie : coef;
+          return fmaf(coef * q, fmaf(lq2, kLn2, h), ngl * e);
+        };
+        for (int64_t v0 = tid; v0 < nv; v0 += kU * kCeThreads) {
+          uint4 q[kU];
+#pragma unroll
+          for (int u = 0; u < kU; ++u)
+            if (v0 + u * kCeThreads < nv) q[u] = __ldg(rv + v0 + u * kCeThreads);
+#pragma unroll
+          for (int u = 0; u < kU; ++u) {
+            const int64_t v = v0 + u * kCeThreads;
+            if (v < nv) {
+              const uint32_t w[4] = {q[u].x, q[u].y, q[u].z, q[u].w};
+              float g8[8];
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                g8[2 * j] = lean(w[j] & 0xffffu);
+                g8[2 * j + 1] = lean(w[j] >> 16);
+              }
+              if (v == lab_vec) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                  if (j == int(lab & 7)) g8[j] += gl;
+              }
+              uint32_t o[4];
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                if (kIsBF16) {
+                  o[j] = pack_bf16x2(g8[2 * j], g8[2 * j + 1]);
+                } else {
+                  const __half2 hh = __floats2half2_rn(g8[2 * j], g8[2 * j + 1]);
+                  o[j] = *reinterpret_cast<const uint32_t*>(&hh);
+                }
+              }
+              dv[v] = make_uint4(o[0], o[1], o[2], o[3]);
+            }
+          }
+        }
+        continue;
+      }
       for (int64_t v0 = tid; v0 < nv; v0 += kU * kCeThreads) {
         uint4 q[kU];
 #pragma unroll
@@ -352,10 +410,6 @@ constexpr int kF1Warps = kF1Threads / 32;
 constexpr int kSampleVecs = 256;      // sampled 16-byte vectors per row (8 elements each)
 constexpr int kBracket = 96;          // half width of the bracket in sample ranks (sigma of the rank is ~21)
 constexpr int kWinMax = 1024;         // 16-bit keys a bracket may span
-
-__device__ __forceinline__ uint32_t key_to_bits(uint32_t key) {
-  return (key & 0x8000u) ? (key & 0x7fffu) : (~key & 0xffffu);
-}
 
 // warp 0: lane l owns bins 8l .. 8l+7 of a 256-bin histogram; bin holding 0-based `rank` -> bcast[0], elements below -> bcast[1]
 __device__ __forceinline__ void find_bin256(const int* hist, int rank, int* bcast, int lane) {
