@@ -482,7 +482,7 @@ __global__ void __launch_bounds__(kF1Threads, 4)
 clamped_entropy_fwd1_kernel(const ClampedParams p) {
   __shared__ __align__(16) uint16_t samp[kSampleVecs * 8];
   __shared__ int hist[256];
-  __shared__ int win[kWinMax];
+  __shared__ int win[kWinMax + kF1Threads];   // + one private slot per thread: where elements outside the window count
   __shared__ int bcast[4];
   __shared__ float red[kF1Warps];
   __shared__ int red_i[kF1Warps];
@@ -529,6 +529,8 @@ clamped_entropy_fwd1_kernel(const ClampedParams p) {
     float m_t = -INFINITY, s_all = 0.f, w_all = 0.f, s_bel = 0.f, w_bel = 0.f;
     int cnt_bel = 0;
     uint32_t kmin = 0xffffu;
+    uint32_t pmin = 0x7f807f80u;                     // bf16: packed (+inf, +inf)
+    const uint32_t my_slot = span + 1u + uint32_t(tid);   // (span < kWinMax)
     constexpr int kU = 4;
     for (int64_t v0 = tid; v0 < nv; v0 += kU * kF1Threads) {
       uint4 q[kU];
@@ -546,6 +548,7 @@ clamped_entropy_fwd1_kernel(const ClampedParams p) {
             xv[2 * j + 1] = half_to_f32<kIsBF16>(w[j] >> 16);
           }
           float vmax = fmaxf(fmaxf(fmaxf(xv[0], xv[1]), fmaxf(xv[2], xv[3])), fmaxf(fmaxf(xv[4], xv[5]), fmaxf(xv[6], xv[7])));
+          if (kIsBF16) pmin = min_bf16x2(pmin, dev::vec_min_bf16(q[u]));   // row minimum: packed, on the raw words
           if (vmax > m_t) {
             if (m_t != -INFINITY) {
               const float d = (m_t - vmax) * c2;
@@ -558,30 +561,30 @@ clamped_entropy_fwd1_kernel(const ClampedParams p) {
             m_t = vmax;
           }
           const float nb = -m_t * c2;
+          // both keys of a 32-bit word at once: key = bits ^ 0x8000 ^ (sign ? 0x7fff : 0)
+          uint32_t k2[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) k2[j] = w[j] ^ 0x80008000u ^ (((w[j] >> 15) & 0x00010001u) * 0x7fffu);
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
-            const uint32_t key = key16((j & 1) ? (w[j >> 1] >> 16) : (w[j >> 1] & 0xffffu));
+            const uint32_t key = (j & 1) ? (k2[j >> 1] >> 16) : (k2[j >> 1] & 0xffffu);
             const float t = fmaf(xv[j], c2, nb);
             const float e = ex2_approx(t);
             s_all += e;
             w_all = fmaf(e, t, w_all);
-            kmin = min(kmin, key);
+            if (!kIsBF16) kmin = min(kmin, key);
             if (kClamp) {
-              const bool bel = key < key_lo;
-              const float eb = bel ? e : 0.f;
-              s_bel += eb;
-              w_bel = fmaf(eb, t, w_bel);
-              cnt_bel += bel ? 1 : 0;
-              // window element: one predicated result-less shared atomic, no branch
+              if (key < key_lo) {                      // (predicated adds)
+                s_bel += e;
+                w_bel = fmaf(e, t, w_bel);
+                cnt_bel += 1;
+              }
+              // every element bumps a counter, unconditionally (ptxas turns a predicated shared atomic into a branch with
+              // a convergence barrier: four issue slots): its window bin, or -- outside the window, where key - key_lo
+              // wraps or exceeds the span -- this thread's private slot behind the window
               const uint32_t off = key - key_lo;
-              asm volatile(
-                  "{\n\t"
-                  ".reg .pred q;\n\t"
-                  "setp.le.u32 q, %1, %2;\n\t"
-                  "@q red.shared.add.u32 [%0], 1;\n\t"
-                  "}" ::"r"(win_base + off * 4u),
-                  "r"(off), "r"(span)
-                  : "memory");
+              const uint32_t idx = min(off, my_slot);           // my_slot > span: bins beyond the span are never read
+              asm volatile("red.shared.add.u32 [%0], 1;" ::"r"(win_base + idx * 4u) : "memory");
             }
           }
         }
@@ -602,8 +605,8 @@ clamped_entropy_fwd1_kernel(const ClampedParams p) {
     float s_rem = block_sum<kF1Warps>(s_bel, red, warp, lane);
     float w_rem = block_sum<kF1Warps>(w_bel, red, warp, lane);
     const int below = block_sum_int(cnt_bel, red_i, warp, lane);
-    const uint32_t bmin = key_to_bits(kmin);
-    const float row_min = -block_max<kF1Warps>(-half_to_f32<kIsBF16>(bmin), red, warp, lane);
+    const float tmin = kIsBF16 ? fminf(bf16_lo(pmin), bf16_hi(pmin)) : half_to_f32<kIsBF16>(key_to_bits(kmin));
+    const float row_min = -block_max<kF1Warps>(-tmin, red, warp, lane);
     uint32_t tau_key = 0;
     float f_tie = 1.f;
     if (kClamp) {
@@ -611,7 +614,7 @@ clamped_entropy_fwd1_kernel(const ClampedParams p) {
       int c[4], mine = 0;
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        c[j] = win[tid * 4 + j];
+        c[j] = uint32_t(tid * 4 + j) <= span ? win[tid * 4 + j] : 0;   // beyond the span: other elements' overflow slots
         mine += c[j];
       }
       int incl = mine;
