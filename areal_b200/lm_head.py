@@ -216,8 +216,12 @@ def lm_head_logprobs(hidden: torch.Tensor, weight: torch.Tensor, labels: torch.T
     (`gather_logprobs(logits, labels, temperature)`, areal/engine/ppo/actor.py:57-63; the recompute of
     proximal / reference log-probs runs under no_grad), from the last hidden state, `chunk_rows` tokens
     at a time: one `[chunk_rows, V]` logits buffer instead of `[T, V]`.  Returns logp `[T]` f32, or
-    (logp, entropy) with `with_entropy=True`.  `impl`: "auto" takes the tcgen05 kernel (`lm_head_logprobs_tc`)
-    whenever it applies, "library" forces the row-blocked cuBLAS + streaming path, "tcgen05" the kernel."""
+    (logp, entropy) with `with_entropy=True`.  `impl`: "auto" takes the tcgen05 kernel (`lm_head_logprobs_tc`) for
+    bf16 operands with a hidden size of at most 2,048 (measured at T = 16,384, V = 151,936: H = 1,536 5.6-6.5 ms against
+    5.9-6.1 ms for the library path, the order depending on the power state of the part; H = 3,584 13.9-15.0 ms against
+    12.4-13.2 ms: the kernel streams its operands out of L2 at the L2's limit, 128 flop per byte, where the library's
+    larger effective tiles gain with K), "library" forces the row-blocked cuBLAS + streaming path, "tcgen05" the
+    kernel (no `[chunk_rows, V]` buffer at all)."""
     from .functional import _logits_forward
     dev = _lib.require_cuda(hidden, weight, labels)
     if impl not in ("auto", "library", "tcgen05"):
@@ -225,7 +229,7 @@ def lm_head_logprobs(hidden: torch.Tensor, weight: torch.Tensor, labels: torch.T
     # bf16 with 16-byte aligned rows: ONE tensor-core kernel (tcgen05 GEMM + online-softmax epilogue, no logits
     # buffer at all); everything else (fp16 / fp32, odd hidden sizes): library GEMM per row block + streaming pass
     tc_ok = (hidden.dtype == torch.bfloat16 and weight.dtype == torch.bfloat16 and hidden.shape[-1] % 8 == 0)
-    if impl == "tcgen05" or (impl == "auto" and tc_ok):
+    if impl == "tcgen05" or (impl == "auto" and tc_ok and hidden.shape[-1] <= 2048):
         return lm_head_logprobs_tc(hidden, weight, labels, temperature, with_entropy=with_entropy)
     if hidden.dtype != weight.dtype or hidden.dtype not in _lib.DTYPE_CODE:
         raise TypeError("lm_head_logprobs: hidden and weight must share a dtype (bf16, fp16 or fp32)")

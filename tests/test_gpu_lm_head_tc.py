@@ -89,6 +89,19 @@ def test_random_inputs_vs_library_path():
     assert torch.allclose(a_h, b_h, rtol=2e-3, atol=2e-3)
 
 
+def test_auto_dispatch_by_hidden_size():
+    """`impl="auto"`: the tensor-core kernel up to a hidden size of 2,048, the row-blocked library path above."""
+    from areal_b200.lm_head import lm_head_logprobs, lm_head_logprobs_tc
+    h, w, labels = grid_inputs(96, 2304, 4096, 11)
+    a = lm_head_logprobs(h.to(D), w.to(D), labels.to(D), 1.0)
+    b = lm_head_logprobs(h.to(D), w.to(D), labels.to(D), 1.0, impl="library")
+    assert torch.equal(a, b)
+    c = lm_head_logprobs_tc(h.to(D), w.to(D), labels.to(D), 1.0)              # exact inputs: same logits either way
+    assert H.rel_err(c.cpu().numpy(), a.cpu().numpy()) <= 2e-5
+    h2, w2, l2 = grid_inputs(96, 2048, 4096, 12)
+    assert torch.equal(lm_head_logprobs(h2.to(D), w2.to(D), l2.to(D), 1.0), lm_head_logprobs_tc(h2.to(D), w2.to(D), l2.to(D), 1.0))
+
+
 def test_strided_rows_and_bad_arguments():
     from areal_b200 import _lib
     from areal_b200.lm_head import lm_head_logprobs_tc
