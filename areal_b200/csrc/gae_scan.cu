@@ -1500,9 +1500,18 @@ static bool launch_padded_cluster(const GaePaddedParams& p, const AdvFusedParams
   cfg.stream = stream;
   if (kFused) {
     constexpr size_t kStage = 5 * 4096 * sizeof(float);              // side outputs of a tile
-    static const cudaError_t once = cudaFuncSetAttribute(gae_padded_cluster_kernel<kFused>,
-                                                         cudaFuncAttributeMaxDynamicSharedMemorySize, int(kStage));
-    if (once != cudaSuccess) return false;                           // (one CTA per row instead)
+    // the attribute is per device: one flag per device ordinal
+    static bool done[64] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (!done[dev & 63]) {
+      if (cudaFuncSetAttribute(gae_padded_cluster_kernel<kFused>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               int(kStage)) != cudaSuccess) {
+        (void)cudaGetLastError();
+        return false;                                                // (one CTA per row instead)
+      }
+      done[dev & 63] = true;
+    }
     cfg.dynamicSmemBytes = kStage;
   }
   cudaLaunchAttribute attr[1];
