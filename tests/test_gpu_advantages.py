@@ -121,7 +121,11 @@ def test_compute_advantages_long_rows_vs_oracle(B, S, mask_dtype, overlong, with
         data["ref_logp"] = torch.from_numpy(ref).to(DEV)
     if with_values:
         data["values"] = torch.from_numpy(val).to(DEV)
+    again = {k: v.clone() for k, v in data.items()}
     compute_advantages(make_actor(c), data)
+    compute_advantages(make_actor(c), again)                 # run-to-run: the exchanges combine in a fixed order
+    for k in ("advantages", "returns", "kl_rewards", "tot_rewards"):
+        assert torch.equal(data[k], again[k]), k
     sc = O.overlong_penalty(score, lm, 1000, 0.75, S // 2) if overlong else score
     assert np.array_equal(data["rewards"].cpu().numpy(), sc.astype(np.float32))        # penalty in place, once
     if overlong:
