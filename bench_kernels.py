@@ -452,24 +452,23 @@ def main():
     out = []
     ref_gae = load_ref("ref_cugae") if "ref" in what or True else None
     ref_iop = load_ref("ref_interval_op_cuda")
-    if "gae" in what:
-        bench_gae(out, ref_gae)
-    if "padded" in what:
-        bench_padded(out)
-    if "advantages" in what:
-        bench_advantages(out)
-    if "cfg2" in what:
-        bench_cfg2(out)
-    if "aent" in what:
-        bench_aent(out)
-    if "lmhead" in what:
-        bench_lmhead(out)
-    if "loss" in what:
-        bench_loss(out)
-    if "logits" in what:
-        bench_logits(out)
-    if "intervals" in what:
-        bench_intervals(out, ref_iop)
+    # every section runs under the clock sampler of bench.py (SM clock + throttle reasons through NVML) and is
+    # followed by a {"section", "clocks"} line, so that no fraction printed here is an unclocked claim
+    from bench import Clocked
+    sections = [("gae", lambda: bench_gae(out, ref_gae)), ("padded", lambda: bench_padded(out)),
+                ("advantages", lambda: bench_advantages(out)), ("cfg2", lambda: bench_cfg2(out)),
+                ("aent", lambda: bench_aent(out)), ("lmhead", lambda: bench_lmhead(out)),
+                ("loss", lambda: bench_loss(out)), ("logits", lambda: bench_logits(out)),
+                ("intervals", lambda: bench_intervals(out, ref_iop))]
+    for name, fn in sections:
+        if name not in what:
+            continue
+        with Clocked(0) as c:
+            fn()
+            torch.cuda.synchronize()
+        d = dict(section=name, clocks=c.clocks)
+        print(json.dumps(d), flush=True)
+        out.append(d)
     if args.out:
         json.dump(out, open(args.out, "w"), indent=1)
 

@@ -1,7 +1,8 @@
 """BASELINE.json configs[3] shape: T = 131,072 packed tokens, V = 151,936 bf16 logits vocab-sharded over the
 ranks of one node (Megatron-TP layout).  Per step: partial statistics of the local [T, V/R] shard, exchange,
 combine, local backward.  Launch: python -m torch.distributed.run --nproc-per-node R bench_vocab_parallel.py
-Prints one JSON line (rank 0); time = max over ranks of the CUDA-event time."""
+Prints one JSON line (rank 0); time = max over ranks of the CUDA-event time.  (Older stand-alone form of the
+`vocab_sharded` block of `bench.py --gpus N`, which also times the one-launch exchange and the per-step jitter.)"""
 import json
 import os
 import sys
@@ -45,11 +46,14 @@ def main():
     out = {"workload": f"BASELINE.json configs[3]: T={T} tokens, V={V} bf16 vocab-sharded over {world} GPUs "
                        f"(shard [T, {Vs}]), logprob+entropy forward and dlogits backward per step",
            "n_gpus": world, "steps": steps, "unit": "tokens/s", "peak_gbs": peak}
+    from bench import Clocked                   # SM clock + throttle reasons while the timed loops run (rank's own GPU)
     for name, exch in (("allgather", None), ("peer_memory", ex)):
         if name == "peer_memory" and ex is None:
             out[name] = {"unavailable": why}
             continue
         x = shard.requires_grad_()
+        clk = Clocked(local)
+        clk.__enter__()
 
         def step():
             x.grad = None
@@ -81,6 +85,8 @@ def main():
         res["tokens_per_s"] = T / (res["fwd_bwd_ms"] * 1e-3)
         res["fwd_hbm_frac"] = fwd_bytes / (res["fwd_ms"] * 1e-3) / 1e9 / peak
         res["fwd_bwd_hbm_frac"] = (fwd_bytes + bwd_bytes) / (res["fwd_bwd_ms"] * 1e-3) / 1e9 / peak
+        clk.__exit__(None, None, None)
+        res["clocks"] = clk.clocks
         out[name] = res
         if exch is not None:
             exch.check()
