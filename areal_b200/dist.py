@@ -322,8 +322,8 @@ class PeerPackedBuffer:
     the packed buffer -> set_intervals (realhf/impl/model/nn/real_llm_api.py:745-805).  Here the sender's
     `slice_intervals` kernel writes its pieces directly into the RECEIVER's buffer with plain streaming
     stores over NVLink (`slice_into`), so there is no sender-side staging buffer and no collective; the
-    receiver then runs `set_from_local` on its own copy.  `fence()` is the host-level hand-off between
-    the two (the sender's stream is drained, then the group meets at a barrier).
+    receiver then runs `set_from_local` on its own copy.  `fence()` is the hand-off between the two: a device-side
+    epoch handshake in stream order (no host synchronisation), or a host barrier on request.
 
     `numel` elements of `dtype` per rank.  One instance per group; every rank constructs it together."""
 
@@ -342,6 +342,13 @@ class PeerPackedBuffer:
         self.buf = symm.empty(max(self.numel, 1), dtype=dtype, device=dev)
         self.handle = symm.rendezvous(self.buf, self.group)
         self._ptrs = [int(p) for p in self.handle.buffer_ptrs]
+        # device-side fence: the epoch flags of the vocabulary exchange (a 256-byte symmetric header, no payload)
+        self._flags = symm.empty(int(_lib.lib().areal_b200_vocab_p2p_buffer_bytes(0)), dtype=torch.uint8, device=dev)
+        self._flags.zero_()
+        self._flag_handle = symm.rendezvous(self._flags, self.group)
+        self._flag_ptrs = (ctypes.c_void_p * self.world)(*[int(p) for p in self._flag_handle.buffer_ptrs])
+        self._status = torch.zeros(1, dtype=torch.int32, device=dev)
+        self._epoch = 0
         torch.cuda.synchronize(dev)
         dist.barrier(self.group)
 
@@ -373,8 +380,27 @@ class PeerPackedBuffer:
         from .flatten_param import set_intervals_any
         set_intervals_any(self.buf[int(offset): int(offset) + int(total_size)], dst, intervals_cuda)
 
-    def fence(self) -> None:
+    FENCE_TIMEOUT_CYCLES = 20_000_000_000     # ~10 s of SM clocks
+
+    def fence(self, host: bool = False) -> None:
         """Everything `slice_into` enqueued so far on this rank's current stream has landed in the peers'
-        buffers, and every rank has got here: the receivers may read, the senders may overwrite."""
-        torch.cuda.current_stream(self.device).synchronize()
-        dist.barrier(self.group)
+        buffers, and every rank has got here: the receivers may read, the senders may overwrite.
+
+        Default: a DEVICE-side fence, stream-ordered, no host synchronisation -- one tiny launch that release-stores
+        this step's epoch into every peer's flag word and waits (bounded) until every peer's epoch has arrived here
+        (the handshake of `areal_b200_vocab_combine_p2p`, called with no rows).  What follows on this stream sees the
+        peers' writes; all ranks must call it the same number of times.  `check()` reports a rank that never came.
+        `host=True`: drain the stream and meet at a `dist.barrier` instead."""
+        if host:
+            torch.cuda.current_stream(self.device).synchronize()
+            dist.barrier(self.group)
+            return
+        self._epoch += 1
+        with torch.cuda.device(self.device):
+            call("areal_b200_vocab_combine_p2p", self._flag_ptrs, self.rank, self.world, 0, 0, self._epoch, 1.0,
+                 self.FENCE_TIMEOUT_CYCLES, None, None, None, None, ptr(self._status), stream_ptr(self.device))
+
+    def check(self):
+        """Host sync: raises if a device-side fence timed out waiting for a rank."""
+        if int(self._status.item()) != 0:
+            raise RuntimeError("areal_b200 peer buffer: a rank did not reach the fence in time")

@@ -185,7 +185,8 @@ def main():
             pb.set_from_local(mine, ivc, total, offset=offset)
             FP.set_intervals_any(want, ref, ivc)
             assert torch.equal(mine.view(torch.int16), ref.view(torch.int16))
-            pb.fence()                                        # receivers are done before the next round overwrites
+            pb.fence(host=(offset == 3))                      # receivers are done before the next round overwrites
+        pb.check()                                            # (device-side fences: nobody timed out)
         # device time of a 256 MB re-shard write into the neighbour (128 Mi bf16 in 4,096 pieces), against the same
         # slice into local memory
         big = D.PeerPackedBuffer(numel=1 << 27, dtype=torch.bfloat16)
@@ -204,7 +205,9 @@ def main():
                 big.slice_into(target, flat_big, iv_big, 1 << 27)
             e1.record()
             big.fence()
+            torch.cuda.synchronize()                          # (the fence is stream-ordered, not a host sync)
             res[name] = round(e0.elapsed_time(e1) / 10, 3)
+        big.check()
         if rank == 0:
             print("PEERBUF_OK", world, {k: f"{v} ms ({0.268435456 / v * 1e3:.0f} GB/s written)" for k, v in res.items()})
 
