@@ -510,6 +510,45 @@ def ncu_traffic(kernel, T, V):
         return None
 
 
+def host_mem_policy(mode, local_rank):
+    """Experiment knob BENCH_PIN_POLICY for the pinned host buffers of the e2e leg: "interleave" spreads the pages over
+    all NUMA nodes of the host, "local" binds them to the node the GPU hangs off (sysfs), anything else leaves the
+    default (first touch).  Returns a description for the JSON line.  set_mempolicy(2) through libc's syscall()."""
+    import ctypes
+    import glob
+    nodes = sorted(int(p.rsplit("node", 1)[1]) for p in glob.glob("/sys/devices/system/node/node[0-9]*"))
+    info = {"policy": mode or "default", "numa_nodes": len(nodes)}
+    if not mode or mode == "default" or len(nodes) < 2:
+        return info
+    try:
+        libc = ctypes.CDLL(None, use_errno=True)
+        mask = ctypes.c_ulong(0)
+        if mode == "interleave":
+            for n in nodes:
+                mask.value |= 1 << n
+            pol = 3                                    # MPOL_INTERLEAVE
+        else:
+            import torch
+            pr = torch.cuda.get_device_properties(local_rank)
+            node = 0
+            try:
+                bdf = "%04x:%02x:%02x.0" % (getattr(pr, "pci_domain_id", 0), pr.pci_bus_id, pr.pci_device_id)
+                node = max(0, int(open(f"/sys/bus/pci/devices/{bdf}/numa_node").read()))
+                info["bdf"] = bdf
+            except Exception as ex:
+                info["bdf_error"] = repr(ex)[:80]
+            mask.value = 1 << node
+            pol = 2                                    # MPOL_BIND
+            info["node"] = node
+        rc = libc.syscall(238, pol, ctypes.byref(mask), ctypes.c_ulong(64))   # x86_64: __NR_set_mempolicy
+        info["rc"] = int(rc)
+        if rc != 0:
+            info["errno"] = ctypes.get_errno()
+    except Exception as ex:
+        info["error"] = repr(ex)[:120]
+    return info
+
+
 def run_e2e(torch, dist, dev, b, world, steps, mode):
     """Same step, but the inputs start in pinned HOST memory every step and the results are read back:
     H2D of logits + per-token vectors, GAE + loss_fn + backward on the device (through the engine loop of
@@ -520,6 +559,7 @@ def run_e2e(torch, dist, dev, b, world, steps, mode):
     T, V = b["logits"].shape
     keys = ("logits", "labels", "loss_mask", "advantages", "rewards", "values", "cu_seqlens", "bootstrap",
             "prox_logp", "old_logp")
+    pin_policy = host_mem_policy(os.environ.get("BENCH_PIN_POLICY", ""), dev.index or 0)
     host = {}
     for k in keys:
         t = b[k].detach()
@@ -632,7 +672,7 @@ def run_e2e(torch, dist, dev, b, world, steps, mode):
             "d2h_bytes_per_step": int(d2h), "ms_per_step": ms, "steps": steps, "mode": mode,
             "h2d_gbs_per_gpu": achieved, "h2d_ceiling_gbs_per_gpu": ceiling,
             "h2d_ceiling_gbs_all_gpus": ceiling * world, "e2e_frac_of_ceiling": achieved / ceiling,
-            "h2d_chunks_in_flight": chunks,
+            "h2d_chunks_in_flight": chunks, "host_mem_policy": pin_policy,
             "note": "bounded by the 4.98 GB pinned host->device copy of the logits per GPU and step; `h2d_ceiling_*` is "
                     "the same bytes copied with nothing else running, on all ranks at once (max over ranks); copies of "
                     "step i+1 overlap the kernels of step i (two device-side input sets, copy stream)"}
