@@ -925,9 +925,17 @@ __device__ __forceinline__ float nv_entering(const NvLocal& l, float carry, int 
   return nv_in;
 }
 
-template <bool kFused>
+// kByteMasks: both masks are one byte per token (torch.bool / uint8, the usual case): the dtype switches of the mask
+// readers fold away, which takes most of the instance's code with them (the capture of the generic instance shows
+// `no_instruction` -- instruction fetch -- among its top stalls: every CTA runs this long kernel exactly once)
+template <bool kFused, bool kByteMasks = false>
 __global__ void __launch_bounds__(512, 2)
-gae_padded_cluster_kernel(const GaePaddedParams p, const AdvFusedParams f, int C) {
+gae_padded_cluster_kernel(const GaePaddedParams p, const AdvFusedParams f_in, int C) {
+  AdvFusedParams f = f_in;
+  if (kByteMasks) {
+    f.attn_code = 1;
+    f.loss_mask_code = 1;
+  }
   constexpr int kT = 512, kW = kT / 32, kTileC = kT * kItems;      // 4096 tokens per CTA
   __shared__ Affine wsm[kW];
   __shared__ float nv_val[kW];
@@ -1505,7 +1513,9 @@ static bool launch_padded_cluster(const GaePaddedParams& p, const AdvFusedParams
     int dev = 0;
     cudaGetDevice(&dev);
     if (!done[dev & 63]) {
-      if (cudaFuncSetAttribute(gae_padded_cluster_kernel<kFused>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+      if (cudaFuncSetAttribute(gae_padded_cluster_kernel<kFused, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               int(kStage)) != cudaSuccess ||
+          cudaFuncSetAttribute(gae_padded_cluster_kernel<kFused, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                int(kStage)) != cudaSuccess) {
         (void)cudaGetLastError();
         return false;                                                // (one CTA per row instead)
@@ -1524,11 +1534,13 @@ static bool launch_padded_cluster(const GaePaddedParams& p, const AdvFusedParams
   static const bool debug = getenv("AREAL_B200_GAE_DEBUG") != nullptr;
   if (debug) {
     int n = -1;
-    const cudaError_t q = cudaOccupancyMaxActiveClusters(&n, gae_padded_cluster_kernel<kFused>, &cfg);
+    const cudaError_t q = cudaOccupancyMaxActiveClusters(&n, gae_padded_cluster_kernel<kFused, false>, &cfg);
     fprintf(stderr, "[areal_b200] gae_padded_cluster<%d> B=%lld C=%lld: max active clusters %d (%s)\n", int(kFused),
             static_cast<long long>(p.B), static_cast<long long>(C), n, cudaGetErrorString(q));
   }
-  const cudaError_t e = cudaLaunchKernelEx(&cfg, gae_padded_cluster_kernel<kFused>, p, f, int(C));
+  const bool byte_masks = kFused && f.attn_code == 1 && f.loss_mask_code == 1;
+  const cudaError_t e = byte_masks ? cudaLaunchKernelEx(&cfg, gae_padded_cluster_kernel<kFused, true>, p, f, int(C))
+                                   : cudaLaunchKernelEx(&cfg, gae_padded_cluster_kernel<kFused, false>, p, f, int(C));
   *status = e == cudaSuccess ? kOk : kCudaError;
   if (e != cudaSuccess) set_error("gae_padded_cluster launch failed: %s", cudaGetErrorString(e));
   return true;
