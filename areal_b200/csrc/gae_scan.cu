@@ -925,16 +925,19 @@ __device__ __forceinline__ float nv_entering(const NvLocal& l, float carry, int 
   return nv_in;
 }
 
-// kByteMasks: both masks are one byte per token (torch.bool / uint8, the usual case): the dtype switches of the mask
-// readers fold away, which takes most of the instance's code with them (the capture of the generic instance shows
-// `no_instruction` -- instruction fetch -- among its top stalls: every CTA runs this long kernel exactly once)
-template <bool kFused, bool kByteMasks = false>
+// kCommon: the usual configuration -- both masks one byte per token (torch.bool / uint8), the k1 KL estimator, no
+// overlong penalty.  The dtype switches of the mask readers, the other estimators and the penalty fold away, and with
+// them a third to a half of the instance's code (the capture of the generic instance shows `no_instruction` --
+// instruction fetch -- among its top stalls: every CTA runs this long kernel exactly once).
+template <bool kFused, bool kCommon = false>
 __global__ void __launch_bounds__(512, 2)
 gae_padded_cluster_kernel(const GaePaddedParams p, const AdvFusedParams f_in, int C) {
   AdvFusedParams f = f_in;
-  if (kByteMasks) {
+  if (kCommon) {
     f.attn_code = 1;
     f.loss_mask_code = 1;
+    f.kl_kind = 1;
+    f.overlong = 0;
   }
   constexpr int kT = 512, kW = kT / 32, kTileC = kT * kItems;      // 4096 tokens per CTA
   __shared__ Affine wsm[kW];
@@ -1538,8 +1541,8 @@ static bool launch_padded_cluster(const GaePaddedParams& p, const AdvFusedParams
     fprintf(stderr, "[areal_b200] gae_padded_cluster<%d> B=%lld C=%lld: max active clusters %d (%s)\n", int(kFused),
             static_cast<long long>(p.B), static_cast<long long>(C), n, cudaGetErrorString(q));
   }
-  const bool byte_masks = kFused && f.attn_code == 1 && f.loss_mask_code == 1;
-  const cudaError_t e = byte_masks ? cudaLaunchKernelEx(&cfg, gae_padded_cluster_kernel<kFused, true>, p, f, int(C))
+  const bool common = kFused && f.attn_code == 1 && f.loss_mask_code == 1 && f.kl_kind == 1 && !f.overlong;
+  const cudaError_t e = common ? cudaLaunchKernelEx(&cfg, gae_padded_cluster_kernel<kFused, true>, p, f, int(C))
                                    : cudaLaunchKernelEx(&cfg, gae_padded_cluster_kernel<kFused, false>, p, f, int(C));
   *status = e == cudaSuccess ? kOk : kCudaError;
   if (e != cudaSuccess) set_error("gae_padded_cluster launch failed: %s", cudaGetErrorString(e));

@@ -90,13 +90,16 @@ def test_compute_advantages_vs_oracle(B, S, mask_dtype):
     assert np.array_equal(data["rewards"].cpu().numpy(), score)          # no penalty configured: untouched
 
 
-@pytest.mark.parametrize("B,S,mask_dtype,overlong,with_values,with_ref",
+@pytest.mark.parametrize("B,S,mask_dtype,overlong,with_values,with_ref,kl",
                          # few long rows: a cluster of up to 8 CTAs per row, lengths summed across the cluster
-                         [(16, 32768, torch.bool, False, True, True), (5, 20001, torch.int64, True, True, True),
-                          (3, 32769, torch.float32, True, False, True),     # column S-1 alone beyond the last tile
-                          (9, 4098, torch.bool, False, True, False), (4, 8200, torch.uint8, True, True, True),
-                          (2, 40000, torch.bool, True, True, True)])       # beyond a cluster: one CTA per row again
-def test_compute_advantages_long_rows_vs_oracle(B, S, mask_dtype, overlong, with_values, with_ref):
+                         [(16, 32768, torch.bool, False, True, True, "k2"), (5, 20001, torch.int64, True, True, True, "k2"),
+                          (3, 32769, torch.float32, True, False, True, "k2"),     # column S-1 alone beyond the last tile
+                          (9, 4098, torch.bool, False, True, False, "k2"), (4, 8200, torch.uint8, True, True, True, "k1"),
+                          # byte masks, k1, no penalty: the kernel's instance for the common configuration
+                          (16, 32768, torch.bool, False, False, True, "k1"), (7, 12296, torch.uint8, False, True, True, "k1"),
+                          (3, 20001, torch.bool, False, True, False, "k1"),
+                          (2, 40000, torch.bool, True, True, True, "k2")])       # beyond a cluster: one CTA per row again
+def test_compute_advantages_long_rows_vs_oracle(B, S, mask_dtype, overlong, with_values, with_ref, kl):
     from areal_b200.actor import compute_advantages
     rng = np.random.RandomState(B + S)
     lens = rng.randint(1, S + 1, B)
@@ -110,7 +113,7 @@ def test_compute_advantages_long_rows_vs_oracle(B, S, mask_dtype, overlong, with
     ref = -rng.rand(B, S).astype(np.float32) * 5
     val = rng.randn(B, S).astype(np.float32)
     score = (rng.randn(B) * 4).astype(np.float32)
-    c = dict(A.BASE, kl_estimator="k2", kl_ctl=0.3, reward_bias=0.25, reward_scaling=1.5, reward_clip=3.0,
+    c = dict(A.BASE, kl_estimator=kl, kl_ctl=0.3, reward_bias=0.25, reward_scaling=1.5, reward_clip=3.0,
              discount=0.999, gae_lambda=0.97, mask_no_eos_with_zero=True, overlong_reward_penalty=overlong,
              overlong_tokens=1000, overlong_penalty_factor=0.75, max_new_tokens=S // 2)
     data = dict(input_ids=torch.zeros(B, S, dtype=torch.long, device=DEV),
@@ -132,7 +135,7 @@ def test_compute_advantages_long_rows_vs_oracle(B, S, mask_dtype, overlong, with
         assert not np.array_equal(sc, score)
     r = O.compute_advantages(sc, lm, logp, am, ref_logp=ref if with_ref else None, values=val if with_values else None,
                              roll_logp=True, reward_bias=0.25, reward_scaling=1.5, reward_clip=3.0, kl_ctl=0.3,
-                             kl_estimator="k2", mask_no_eos_with_zero=True, discount=0.999, gae_lambda=0.97)
+                             kl_estimator=kl, mask_no_eos_with_zero=True, discount=0.999, gae_lambda=0.97)
     keys = ("loss_mask", "logprobs", "kl_rewards", "tot_rewards") + (("ref_logp",) if with_ref else ())
     for k in keys:
         assert np.array_equal(data[k].cpu().numpy(), r[k]), k
